@@ -1,0 +1,165 @@
+"""TEST INFRASTRUCTURE ONLY -- generates tests/golden/*.npz from the UNMODIFIED reference.
+
+Run in the build container (needs /root/reference):  python oracle/gen_golden.py
+Every array written here is an input to, a weight of, or an output of the reference's own
+modules (imported by oracle/ref_import.py).  Fixtures are a few MB in total (dominated by the fp32 weights) and committed.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oracle.ref_import import load_reference  # noqa: E402
+
+OUT = os.path.join(ROOT, "tests", "golden")
+
+
+def sd_np(module, prefix="w."):
+    return {prefix + k: v.detach().cpu().numpy() for k, v in module.state_dict().items()}
+
+
+def synth_programs(rng, n, F=164, smax=32, zero_frac=0.02):
+    progs = []
+    for _ in range(n):
+        s = int(rng.integers(1, smax + 1))
+        p = (rng.random((s, F), dtype=np.float32) * rng.integers(0, 25, size=(1, F))).astype(np.float32)
+        p[:, rng.random(F) < 0.15] = 0.0
+        if rng.random() < zero_frac:
+            p[:] = 0.0
+        progs.append(p)
+    return progs
+
+
+def gen_segsum_mlp(ns):
+    """a1-a3: SegmentDataLoader + SegmentSumMLPModule + MLPModelInternal.predict."""
+    rng = np.random.default_rng(1264)
+    for tag, F, emb in (("f164", 164, False), ("f174", 174, True)):
+        torch.manual_seed(7)
+        m = ns.mlp_model.MLPModelInternal(device="cpu", use_workload_embedding=emb)
+        m.base_model = ns.mlp_model.make_net(dict(m.net_params))
+        m.base_model.eval()
+        progs = synth_programs(rng, 97)
+        progs[3][:] = 0.0  # invalid program -> -inf at the MLPModel.predict level
+        feats = np.empty(len(progs), dtype=object)
+        for i, p in enumerate(progs):
+            feats[i] = p
+        task = ns.dataset.LearningTask("wk", "cuda")
+        ds = ns.dataset.Dataset.create_one_task(task, feats, np.zeros(len(progs)))
+        loader = ns.mlp_model.SegmentDataLoader(ds, 4096, "cpu", emb, False, {}, None)
+        norm = loader.normalize()
+        m.fea_norm_vec = norm
+        flat_norm = loader.features.numpy().copy()
+        sizes = loader.segment_sizes.numpy().copy()
+        with torch.no_grad():
+            direct = m.base_model(loader.segment_sizes, loader.features).numpy()
+            m.infer_batch_size = 40  # exercise batching (ragged last batch)
+            pred = m.predict(ds)[task]
+        # MLPModel.predict's invalid-state rule (mlp_model.py:842-844), applied by hand
+        masked = pred.copy()
+        for i, p in enumerate(progs):
+            if p.min() == p.max() == 0:
+                masked[i] = -np.inf
+        np.savez_compressed(
+            os.path.join(OUT, "segsum_mlp_%s.npz" % tag),
+            raw=np.concatenate(progs, 0), sizes=sizes, norm=norm.numpy(), flat_norm_head=flat_norm[:64],
+            flat_norm_sum=flat_norm.astype(np.float64).sum(axis=0),
+            direct=direct, pred=pred, masked=masked, **sd_np(m.base_model))
+
+
+def gen_extent_vae(ns):
+    """a5, a6, a12, a13: VAE_feature_head / VAECostPredictor (extent family)."""
+    D, H, L = 48, 256, 64
+    torch.manual_seed(2023)
+    vae = ns.vae_model.VAE_feature_head(D, None, L, H).eval()
+    reg = ns.vae_model.VAECostPredictor(D, hidden_dim=H, latent_dim=L).eval()
+    reg.load_pretrained_encoder(vae.state_dict())
+    g = torch.Generator().manual_seed(2023)
+    x = torch.randn(300, D, generator=g)
+    z = torch.randn(300, L, generator=g)
+    with torch.no_grad():
+        mu, logvar = vae.encode(x)
+        dec = vae.decode(z)
+        recon = vae(x, use_mean=True)[0]
+        cost = reg.predict_cost(z)
+        cost_x, mean_x, logvar_x, z_x = reg(x, use_mean=True)
+    zz = z.clone().requires_grad_(True)
+    c = reg.predict_cost(zz)
+    grad = torch.autograd.grad(c.sum(), zz)[0]
+    # mc_predict (model.py:241-273) with explicit Bernoulli(0.9) masks in place of nn.Dropout's
+    # private Philox stream; same graph, same 1/(1-p) scaling, mean + unbiased var over T.
+    T = 5
+    gm = torch.Generator().manual_seed(99)
+    mk = (torch.rand(T, 300, H, generator=gm) >= 0.1).float()
+    with torch.no_grad():
+        preds = []
+        for t in range(T):
+            h = reg.cost_predictor[1](reg.cost_predictor[0](mean_x))
+            h = h * mk[t] / 0.9
+            h = reg.cost_predictor[4](reg.cost_predictor[3](h))
+            preds.append(reg.cost_predictor[6](h).squeeze(-1))
+        preds = torch.stack(preds, 0)
+        mc_mean, mc_var = preds.mean(0), preds.var(0)
+    np.savez_compressed(
+        os.path.join(OUT, "extent_vae.npz"),
+        x=x.numpy(), z=z.numpy(), mu=mu.numpy(), logvar=logvar.numpy(), dec=dec.numpy(),
+        recon=recon.numpy(), cost=cost.numpy(), cost_x=cost_x.numpy(), mean_x=mean_x.numpy(),
+        grad=grad.numpy(), masks=mk.numpy().astype(np.uint8), mc_mean=mc_mean.numpy(),
+        mc_var=mc_var.numpy(), **sd_np(vae, "vae."), **sd_np(reg, "reg."))
+
+
+def gen_snap(ns):
+    """a9: postprocess (vae_sch_extent.ipynb:1374-1383) + clamp(min=1) (:1457), restated
+    literally with the same torch calls (the notebook cell is not importable)."""
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(200, 48, generator=g) * 1.5
+    mean = torch.rand(48, generator=g) * 2.5 + 0.5
+    std = torch.rand(48, generator=g) * 1.2 + 0.3
+    x[0, :8] = torch.tensor([-50.0, 50.0, 0.0, 1e-3, -1e-3, 3.0, -3.0, 0.5])
+    v = x * (std + 1e-8) + mean
+    ext = torch.clamp(torch.round(torch.exp(v)).int(), min=1)
+    v2 = x * std + mean
+    ext_log1p = torch.clamp(torch.round(torch.expm1(v2)).int(), min=1)
+    np.savez_compressed(os.path.join(OUT, "snap.npz"), x=x.numpy(), mean=mean.numpy(),
+                        std=std.numpy(), ext=ext.numpy(), ext_log1p=ext_log1p.numpy())
+
+
+def gen_select(ns):
+    """a11/a12/a14: util_select_topk, select_topk_z_grad and select_programs on a seeded pool."""
+    D, H, L = 48, 256, 64
+    torch.manual_seed(11)
+    reg = ns.vae_model.VAECostPredictor(D, hidden_dim=H, latent_dim=L).eval()
+    g = torch.Generator().manual_seed(12)
+    x = torch.randn(1024, D, generator=g)
+    with torch.no_grad():
+        z, _ = reg.encode(x)
+        cost = reg.predict_cost(z).numpy()
+    remaining = set(range(1024)) - set(range(0, 1024, 7))
+    sel, rem_after = ns.select.util_select_topk(cost, set(remaining), 48)
+    used = set(range(0, 1024, 7))
+    sel_prog, rem_prog = ns.select.select_programs(
+        reg, x.numpy(), set(used), set(remaining), num_select=64, T_mc=4, uncertainty_topk=10 ** 9,
+        w_cost=1.0, w_unc=0.0, w_div=0.0, grad_num=2, rand_num=0,
+        rng=np.random.default_rng(42), device=torch.device("cpu"), topk_factor=5)
+    np.savez_compressed(
+        os.path.join(OUT, "select.npz"), x=x.numpy(), cost=cost, z=z.numpy(),
+        remaining=np.array(sorted(remaining), np.int64), topk48=np.sort(sel),
+        used=np.array(sorted(used), np.int64), sel_prog=sel_prog,
+        rem_prog=np.array(sorted(rem_prog), np.int64), **sd_np(reg, "reg."))
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    ns = load_reference()
+    gen_segsum_mlp(ns)
+    gen_extent_vae(ns)
+    gen_snap(ns)
+    gen_select(ns)
+    for f in sorted(os.listdir(OUT)):
+        print(f, os.path.getsize(os.path.join(OUT, f)))
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,108 @@
+"""TEST INFRASTRUCTURE ONLY -- imports the *unmodified* reference modules.
+
+Loads the reference's own PyTorch implementation of the hot path straight from
+``/root/reference`` (read-only checkout) under a stub ``tvm`` package, so that
+``oracle/gen_golden.py`` can produce golden vectors and ``tests/`` can pin the
+restated oracle (``oracle/torch_oracle.py``) against the real thing.
+
+``/root/reference`` exists only in the build container; on the GPU box this
+module raises ``ReferenceUnavailable`` and nothing at run time depends on it.
+
+Modules loaded:
+  python/tvm/auto_scheduler/dataset.py
+  python/tvm/auto_scheduler/cost_model/mlp_model.py
+  scripts/pre_experiments/model_myself/utils/{model,select,common}.py
+  scripts/vae_experiments/models/{vae,regression}.py
+"""
+import importlib.util
+import os
+import sys
+import types
+
+REF_ROOT = os.environ.get("VAEX_REFERENCE_ROOT", "/root/reference")
+
+
+class ReferenceUnavailable(RuntimeError):
+    pass
+
+
+def available():
+    return os.path.isfile(os.path.join(
+        REF_ROOT, "python/tvm/auto_scheduler/cost_model/mlp_model.py"))
+
+
+def _stub(name, **attrs):
+    m = types.ModuleType(name)
+    m.__dict__.update(attrs)
+    m.__path__ = []  # behave like a package
+    sys.modules[name] = m
+    return m
+
+
+def _load(modname, relpath):
+    path = os.path.join(REF_ROOT, relpath)
+    spec = importlib.util.spec_from_file_location(modname, path)
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[modname] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
+_CACHE = {}
+
+
+def load_reference():
+    """Returns a namespace with the reference modules: .mlp_model, .dataset,
+    .vae_model (utils/model.py), .select, .common, .seg_vae, .seg_reg."""
+    if "ns" in _CACHE:
+        return _CACHE["ns"]
+    if not available():
+        raise ReferenceUnavailable("%s not present (GPU box?)" % REF_ROOT)
+    import numpy as np
+
+    if "tvm" in sys.modules and not getattr(sys.modules["tvm"], "_vaex_stub", False):
+        raise RuntimeError("a real tvm is already imported")
+
+    class _Dummy:  # MeasureInput / MeasureResult / RecordReader placeholders
+        def __init__(self, *a, **k):
+            pass
+
+    def _nope(*a, **k):
+        raise NotImplementedError("TVM C++ feature extraction is not available in the stub")
+
+    tvm = _stub("tvm", _vaex_stub=True)
+    asch = _stub("tvm.auto_scheduler")
+    _stub("tvm.auto_scheduler.measure_record", RecordReader=_Dummy)
+    _stub("tvm.auto_scheduler.measure", MeasureInput=_Dummy, MeasureResult=_Dummy)
+    _stub("tvm.auto_scheduler.feature",
+          get_per_store_features_from_measure_pairs=_nope,
+          get_per_store_features_from_states=_nope,
+          get_per_store_features_from_file=_nope)
+    cm = _stub("tvm.auto_scheduler.cost_model")
+    _stub("tvm.auto_scheduler.cost_model.xgb_model",
+          get_workload_embedding=lambda key: np.zeros(9, dtype=np.float32))
+
+    class PythonBasedModel:
+        def __init__(self):
+            pass
+
+    _stub("tvm.auto_scheduler.cost_model.cost_model", PythonBasedModel=PythonBasedModel)
+    tvm.auto_scheduler = asch
+    asch.cost_model = cm
+
+    ns = types.SimpleNamespace()
+    ns.dataset = _load("tvm.auto_scheduler.dataset", "python/tvm/auto_scheduler/dataset.py")
+    ns.mlp_model = _load("tvm.auto_scheduler.cost_model.mlp_model",
+                         "python/tvm/auto_scheduler/cost_model/mlp_model.py")
+    base = "scripts/pre_experiments/model_myself/utils/"
+    ns.vae_model = _load("_vaex_ref_utils_model", base + "model.py")
+    ns.select = _load("_vaex_ref_utils_select", base + "select.py")
+    ns.common = _load("_vaex_ref_utils_common", base + "common.py")
+    ns.seg_vae = _load("_vaex_ref_seg_vae", "scripts/vae_experiments/models/vae.py")
+    try:
+        ns.seg_reg = _load("_vaex_ref_seg_reg", "scripts/vae_experiments/models/regression.py")
+    except Exception as e:  # regression.py may import its sibling by package path
+        ns.seg_reg = None
+        ns.seg_reg_error = repr(e)
+    _CACHE["ns"] = ns
+    return ns

@@ -1,0 +1,267 @@
+"""TEST INFRASTRUCTURE ONLY -- CPU restatement (oracle) of the reference hot path.
+
+Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s ``cpu_baseline`` /
+``--impl reference`` legs may import this file.  The product package never does.
+
+The reference implements this path as PyTorch eager fp32 modules; this file restates the
+same arithmetic as plain functions over ``state_dict``-style dicts (same key names as the
+reference modules, so shipped checkpoints and golden fixtures plug in directly) using torch
+CPU fp32 ops.  Each function cites the reference lines it follows (relative to
+/root/reference).  Parity pin: ``tests/test_oracle_golden.py`` checks every function here
+against ``tests/golden/*.npz`` -- outputs of the *unmodified* reference modules generated
+by ``oracle/gen_golden.py`` in the build container (the reference's own tests hold no
+vectors for this path).
+"""
+import numpy as np
+import torch
+
+F32 = torch.float32
+
+
+def _t(x, dtype=F32):
+    if isinstance(x, torch.Tensor):
+        return x if x.requires_grad else x.detach().to("cpu", dtype)
+    return torch.as_tensor(np.asarray(x), dtype=dtype)
+
+
+def _lin(x, W, b):
+    return torch.addmm(_t(b), x, _t(W).t())
+
+
+# --------------------------------------------------------------------------------------
+# a1  SegmentDataLoader: flatten / embed / normalise / offsets
+#     python/tvm/auto_scheduler/cost_model/mlp_model.py:47-92 (flatten), :95-105 (normalize)
+# --------------------------------------------------------------------------------------
+def flatten_programs(programs, task_embedding=None):
+    """programs: sequence of [S_i, F] float arrays -> (features [sum S, F(+E)], sizes int32[N])."""
+    sizes = np.array([len(p) for p in programs], dtype=np.int32)
+    rows = []
+    for p in programs:
+        p = np.asarray(p, dtype=np.float32)
+        if task_embedding is not None:
+            emb = np.tile(np.asarray(task_embedding, np.float32), (len(p), 1))
+            p = np.concatenate([p, emb], axis=1)
+        rows.append(p)
+    feats = np.concatenate(rows, axis=0).astype(np.float32) if rows else np.zeros((0, 0), np.float32)
+    return feats, sizes
+
+
+def fea_norm_vec(features):
+    """mlp_model.py:95-103: per-column max where max > 0 else 1."""
+    f = _t(features)
+    mx = f.max(dim=0).values
+    return torch.where(mx > 0, mx, torch.ones_like(mx))
+
+
+def segment_offsets(sizes):
+    """mlp_model.py:91-92: exclusive scan of segment sizes."""
+    s = np.asarray(sizes, dtype=np.int64)
+    return np.concatenate([[0], np.cumsum(s)]).astype(np.int64)
+
+
+# --------------------------------------------------------------------------------------
+# a2  SegmentSumMLPModule.forward   mlp_model.py:179-221 (ctor :148-173)
+# --------------------------------------------------------------------------------------
+def segment_sum(rows, sizes):
+    """mlp_model.py:195-208 (repeat_interleave + scatter_add) == per-program row sum."""
+    sizes = _t(sizes, torch.int64)
+    n = sizes.shape[0]
+    idx = torch.repeat_interleave(torch.arange(n), sizes)
+    out = torch.zeros((n, rows.shape[1]), dtype=rows.dtype)
+    return out.index_add_(0, idx, rows)
+
+
+def segsum_mlp_encode_rows(P, feats):
+    h = torch.relu(_lin(_t(feats), P["segment_encoder.0.weight"], P["segment_encoder.0.bias"]))
+    return torch.relu(_lin(h, P["segment_encoder.2.weight"], P["segment_encoder.2.bias"]))
+
+
+def _bn_eval(x, P, pre):
+    """BatchNorm1d in eval mode (mlp_model.py:160-161, vae.py:40, regression.py:42)."""
+    w, b = _t(P[pre + ".weight"]), _t(P[pre + ".bias"])
+    mu, var = _t(P[pre + ".running_mean"]), _t(P[pre + ".running_var"])
+    return (x - mu) / torch.sqrt(var + 1e-5) * w + b
+
+
+def segsum_mlp_head(P, s):
+    if "norm.weight" in P:
+        s = _bn_eval(s, P, "norm")
+    s = torch.relu(_lin(s, P["l0.0.weight"], P["l0.0.bias"])) + s
+    s = torch.relu(_lin(s, P["l1.0.weight"], P["l1.0.bias"])) + s
+    return s
+
+
+def segsum_mlp_forward(P, sizes, feats, add_sigmoid=False):
+    h = segsum_mlp_encode_rows(P, feats)
+    s = segsum_mlp_head(P, segment_sum(h, sizes))
+    out = _lin(s, P["decoder.weight"], P["decoder.bias"]).squeeze(-1)
+    return torch.sigmoid(out) if add_sigmoid else out
+
+
+# --------------------------------------------------------------------------------------
+# a3  MLPModelInternal._predict_a_task (mlp_model.py:669-681) + MLPModel.predict (:832-846)
+# --------------------------------------------------------------------------------------
+def predict_programs(P, programs, norm_vec=None, task_embedding=None, batch=4096,
+                     add_sigmoid=False, mask_invalid=True):
+    """Returns np.float32[N]; all-zero programs -> -inf (mlp_model.py:842-844)."""
+    if P is None:
+        return np.zeros(len(programs), dtype=np.float32)
+    feats, sizes = flatten_programs(programs, task_embedding)
+    feats = _t(feats)
+    if norm_vec is not None:
+        feats = feats / _t(norm_vec)
+    offs = segment_offsets(sizes)
+    preds = []
+    for s in range(0, len(sizes), batch):
+        e = min(s + batch, len(sizes))
+        preds.append(segsum_mlp_forward(P, sizes[s:e], feats[offs[s]:offs[e]], add_sigmoid))
+    out = torch.cat(preds).numpy().astype(np.float32) if preds else np.zeros(0, np.float32)
+    if mask_invalid:
+        for i, p in enumerate(programs):
+            p = np.asarray(p)
+            if p.min() == p.max() == 0:
+                out[i] = -np.inf
+    return out
+
+
+# --------------------------------------------------------------------------------------
+# a5  VAE_feature_head   scripts/pre_experiments/model_myself/utils/model.py:6-81
+# a6  VAECostPredictor   same file :86-273
+# --------------------------------------------------------------------------------------
+def _mlp_relu(x, P, pre, idxs, last_act=True):
+    for j, i in enumerate(idxs):
+        x = _lin(x, P["%s.%d.weight" % (pre, i)], P["%s.%d.bias" % (pre, i)])
+        if last_act or j + 1 < len(idxs):
+            x = torch.relu(x)
+    return x
+
+
+def vae_encode(P, x):
+    """model.py:52-56 / :145-160 -> (mu, logvar)."""
+    h = _mlp_relu(_t(x), P, "encoder", (0, 2, 4))
+    return _lin(h, P["fc_mu.weight"], P["fc_mu.bias"]), _lin(h, P["fc_logvar.weight"], P["fc_logvar.bias"])
+
+
+def reparameterize(mu, logvar, eps):
+    """model.py:58-61 with eps supplied (torch Philox stream is not reproducible elsewhere)."""
+    return _t(mu) + _t(eps) * torch.exp(0.5 * _t(logvar))
+
+
+def vae_decode(P, z):
+    """model.py:28-38, :63-64: 3x(Linear+ReLU) + Linear."""
+    return _mlp_relu(_t(z), P, "decoder", (0, 2, 4, 6), last_act=False)
+
+
+def predict_cost(P, z, drop_mask=None, p_drop=0.1):
+    """model.py:119-131, :168-170.  cost_predictor.{0,3,6} (2 layers) or the 3-layer segment
+    variant regression.py:48-61 is handled by predict_cost_bn.  drop_mask [N,256] of 0/1
+    reproduces train-mode Dropout(0.1) after the first ReLU (scaled by 1/(1-p))."""
+    h = torch.relu(_lin(_t(z), P["cost_predictor.0.weight"], P["cost_predictor.0.bias"]))
+    if drop_mask is not None:
+        h = h * _t(drop_mask) / (1.0 - p_drop)
+    h = torch.relu(_lin(h, P["cost_predictor.3.weight"], P["cost_predictor.3.bias"]))
+    return _lin(h, P["cost_predictor.6.weight"], P["cost_predictor.6.bias"]).squeeze(-1)
+
+
+def mc_predict(P, x, masks, p_drop=0.1):
+    """model.py:241-273: T stochastic passes; mean and *unbiased* variance over T."""
+    mu, _ = vae_encode(P, x)
+    preds = torch.stack([predict_cost(P, mu, m, p_drop) for m in masks], dim=0)
+    return preds.mean(dim=0), preds.var(dim=0)
+
+
+def cost_grad_z(P, z):
+    """utils/select.py:128-135: d(sum cost)/dz through the predictor (eval mode)."""
+    z = _t(z).clone().requires_grad_(True)
+    c = predict_cost(P, z)
+    (g,) = torch.autograd.grad(c.sum(), z)
+    return c.detach(), g
+
+
+# --------------------------------------------------------------------------------------
+# a9  postprocess + clamp   vae_sch_extent.ipynb:1374-1383,1457 ; inverse of
+#     vae_extent_search.py:394-397 (log1p + StandardScaler)
+# --------------------------------------------------------------------------------------
+def snap_round_clamp(x, mean, scale, log1p=False):
+    x = _t(x) * (_t(scale) + (0.0 if log1p else 1e-8)) + _t(mean)
+    e = torch.expm1(x) if log1p else torch.exp(x)
+    return torch.clamp(torch.round(e).to(torch.int32), min=1)
+
+
+# --------------------------------------------------------------------------------------
+# a10 tile-size legality: src/auto_scheduler/search_policy/utils.cc:446-463 (GetFactors),
+#     sketch_policy_rules.cc:493-529, max_innermost_split_factor = 64 (search_policy.py:191)
+# --------------------------------------------------------------------------------------
+def get_factors(n):
+    """Sorted divisors of n (utils.cc:446-463: loop to sqrt, push both, sort)."""
+    res = []
+    step = 2 if n % 2 == 1 else 1
+    i = 1
+    while i * i <= n:
+        if n % i == 0:
+            res.append(i)
+            if n // i != i:
+                res.append(n // i)
+        i += step
+    return sorted(res)
+
+
+def nearest_divisor(n, v, cap=None):
+    """Divisor of n nearest to v (ties -> smaller); optionally capped (innermost <= 64)."""
+    best = 1
+    for d in get_factors(int(n)):
+        if cap is not None and d > cap:
+            break
+        if abs(d - v) < abs(best - v):
+            best = d
+    return best
+
+
+def legalise_divisor(raw, slot_extent, slot_group_last, max_innermost=64):
+    """raw int32 [N,D] (already round+clamp); per slot j: slot_extent[j] = loop extent the
+    split belongs to (0 = free slot e.g. auto_unroll, kept as is); slots of one split are
+    consecutive, outer->inner; slot_group_last[j]=1 marks the innermost length of a split.
+    Each length is snapped to the nearest divisor of the *remaining* extent."""
+    raw = np.asarray(raw, dtype=np.int64)
+    out = raw.copy()
+    N, D = raw.shape
+    for i in range(N):
+        rem = None
+        for j in range(D):
+            ext = int(slot_extent[j])
+            if ext <= 0:
+                rem = None
+                continue
+            if rem is None:
+                rem = ext
+            cap = max_innermost if slot_group_last[j] else None
+            d = nearest_divisor(rem, int(raw[i, j]), cap)
+            out[i, j] = d
+            rem //= d
+            if slot_group_last[j]:
+                rem = None
+    return out.astype(np.int32)
+
+
+# --------------------------------------------------------------------------------------
+# a11 top-k   utils/select.py:54-81 (np.argsort(pred)[-k:], ascending order of score)
+# --------------------------------------------------------------------------------------
+def topk_desc(scores, k):
+    """k largest, ordered (score desc, index asc) -- the kernel's deterministic tie-break.
+    The reference's argsort is unstable so only the *set* is comparable when gaps are 0."""
+    s = np.asarray(scores, dtype=np.float32)
+    k = min(k, len(s))
+    order = np.lexsort((np.arange(len(s)), -s.astype(np.float64)))
+    idx = order[:k]
+    return s[idx], idx.astype(np.int64)
+
+
+# --------------------------------------------------------------------------------------
+# config 3: multi-step latent ascent (NEW surface; single-step precedent select.py:128-135)
+# --------------------------------------------------------------------------------------
+def latent_ascent(P, z0, steps, lr):
+    z = _t(z0).clone()
+    for _ in range(steps):
+        _, g = cost_grad_z(P, z)
+        z = z + lr * g
+    return z, predict_cost(P, z).detach()
