@@ -1,0 +1,147 @@
+/* vaex_b200 -- C ABI of the B200-native hot path of Jiw00n/vae-extent-search.
+ *
+ * This is the drop-in boundary.  The reference has no FFI of its own
+ * on this path -- it is PyTorch eager code -- so each entry point names the reference
+ * *method* whose body it replaces (paths relative to the reference checkout).  The Python
+ * mirror of the reference classes (vae-extent-search_b200/*.py) binds these with ctypes;
+ * INTEGRATION.md shows the stub a reference maintainer would add.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative VAEX_E_* code on failure; the message
+ *     is available from vaex_last_error() (thread-local).  No C++ exception crosses.
+ *   - pointers named *_dev are device pointers owned by the caller (e.g. torch tensors);
+ *     *_host are host pointers.  `stream` is a cudaStream_t passed as void* (NULL = default).
+ *   - device entry points are asynchronous with respect to the host; *_host entry points are
+ *     synchronous (they return when the host output buffer is filled).
+ *   - a handle may be used from one thread at a time.
+ *   - there is no CPU fallback: without a CUDA device every compute call returns
+ *     VAEX_E_CUDA.
+ */
+#ifndef VAEX_B200_H_
+#define VAEX_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VAEX_ABI_VERSION 1
+
+enum {
+  VAEX_OK = 0,
+  VAEX_E_INVALID = -1, /* bad argument / shape / state */
+  VAEX_E_CUDA = -2,    /* CUDA runtime error (message has the cudaError string) */
+  VAEX_E_NOMEM = -3,
+  VAEX_E_UNSUPPORTED = -4
+};
+
+/* model kinds (vaex_model_create) */
+enum {
+  /* SegmentSumMLPModule, python/tvm/auto_scheduler/cost_model/mlp_model.py:147-221.
+   * dims = {in_dim F, hidden H (=256), use_norm(0/1), add_sigmoid(0/1)} */
+  VAEX_KIND_SEGSUM_MLP = 1,
+  /* VAE_feature_head, scripts/pre_experiments/model_myself/utils/model.py:6-81.
+   * dims = {input_dim D, hidden H, latent L} */
+  VAEX_KIND_EXTENT_VAE = 2,
+  /* VAECostPredictor (extent family), utils/model.py:86-273.
+   * dims = {input_dim D, hidden H, latent L, predictor_hidden PH} */
+  VAEX_KIND_COST_PREDICTOR = 3
+};
+
+/* flags for vaex_segsum_mlp_forward */
+enum {
+  VAEX_F_MASK_INVALID = 1, /* all-zero program -> -inf (MLPModel.predict, mlp_model.py:842-844) */
+  VAEX_F_FORCE_SIMT = 2    /* run the fp32 SIMT check kernels instead of the tcgen05 kernel */
+};
+
+/* snap modes for vaex_snap_extents / vaex_decode_snap */
+enum {
+  VAEX_SNAP_EXP = 0,   /* clamp(round(exp(x*(scale+1e-8)+mean)),1): vae_sch_extent.ipynb:1374-1383,1457 */
+  VAEX_SNAP_EXPM1 = 1, /* inverse of log1p+StandardScaler: vae_extent_search.py:394-397 */
+  VAEX_SNAP_DIVISOR = 4 /* OR-able: then legalise to tile factors (utils.cc:433-463 semantics) */
+};
+
+typedef struct vaex_model* vaex_model_t;
+
+const char* vaex_last_error(void);
+int vaex_abi_version(void);
+/* number of CUDA devices visible, or a negative error */
+int vaex_device_count(void);
+/* kernels launched by this library since load (for bench.py's gpu_launches) */
+int64_t vaex_launch_count(void);
+
+/* ---- model lifetime ------------------------------------------------------------------ */
+int vaex_model_create(int kind, const int32_t* dims, int ndims, vaex_model_t* out);
+/* `name` is the reference state_dict key (e.g. "segment_encoder.0.weight", "fc_mu.bias",
+ * "norm.running_var"); data is host fp32 row-major [rows, cols] (bias: rows=1). */
+int vaex_model_load_weights(vaex_model_t h, const char* name, const float* data_host,
+                            int32_t rows, int32_t cols);
+/* Uploads + packs weights for the kernels: folds eval-mode BatchNorm, folds 1/fea_norm_vec
+ * (may be NULL) into the first layer's columns (SegmentDataLoader.normalize,
+ * mlp_model.py:95-105), builds fp16 K-major swizzled images for tcgen05 and fp32 transposed
+ * copies for the backward pass. */
+int vaex_model_pack(vaex_model_t h, const float* fea_norm_vec_host, void* stream);
+int vaex_model_destroy(vaex_model_t h);
+
+/* ---- SegmentSumMLP scoring (replaces SegmentSumMLPModule.forward, mlp_model.py:179-221,
+ *      and the batch loop of MLPModelInternal._predict_a_task, :669-681) --------------------- */
+/* exclusive scan of int32 sizes[n] -> int32 offsets[n+1] (SegmentDataLoader, :91-92) */
+int vaex_segment_offsets(const int32_t* sizes_dev, int64_t n, int32_t* offsets_dev, void* stream);
+/* feats_dev: fp32 [n_rows, F] row-major, rows of one program contiguous; seg_offsets_dev:
+ * int32[n_programs+1]; scores_dev: fp32[n_programs]. */
+int vaex_segsum_mlp_forward(vaex_model_t h, const float* feats_dev, const int32_t* seg_offsets_dev,
+                            int64_t n_programs, int64_t n_rows, float* scores_dev, int flags,
+                            void* stream);
+/* per-program 256-d segment sums of the encoded rows (SegmentVAE.segment_sum,
+ * scripts/vae_experiments/models/vae.py:68-85); segsum_dev fp32 [n_programs, H] */
+int vaex_segsum_encode(vaex_model_t h, const float* feats_dev, const int32_t* seg_offsets_dev,
+                       int64_t n_programs, int64_t n_rows, float* segsum_dev, int flags,
+                       void* stream);
+/* End-to-end host call (what MLPModel.predict costs a reference user, mlp_model.py:832-846):
+ * host fp32 features + int32 sizes in, host fp32 scores out; chunked H2D on two streams
+ * overlapped with compute.  Synchronous. */
+int vaex_segsum_mlp_predict_host(vaex_model_t h, const float* feats_host, const int32_t* sizes_host,
+                                 int64_t n_programs, int64_t n_rows, float* scores_host, int flags);
+
+/* ---- extent-VAE family ----------------------------------------------------------------- */
+/* VAE_feature_head.encode / VAECostPredictor.encode (utils/model.py:52-56, :145-160) */
+int vaex_vae_encode(vaex_model_t h, const float* x_dev, int64_t n, float* mu_dev,
+                    float* logvar_dev_or_null, void* stream);
+/* reparameterize (utils/model.py:58-61): z = mu + eps*exp(0.5*logvar); eps_dev may be NULL,
+ * then eps ~ N(0,1) from Philox4x32-10(seed, offset). */
+int vaex_reparam(const float* mu_dev, const float* logvar_dev, const float* eps_dev_or_null,
+                 uint64_t seed, uint64_t offset, float* z_dev, int64_t n, int32_t latent,
+                 void* stream);
+/* VAE_feature_head.decode (utils/model.py:63-64) -> x_cont fp32 [n, D] */
+int vaex_vae_decode(vaex_model_t h, const float* z_dev, int64_t n, float* x_dev, void* stream);
+/* postprocess + clamp (vae_sch_extent.ipynb:1374-1383,1457) and optional divisor legalise.
+ * mean/scale: fp32[D] (StandardScaler.mean_/scale_); slot_extent int32[D] (0 = free slot),
+ * slot_last uint8[D] (1 = innermost length of a split) only for VAEX_SNAP_DIVISOR. */
+int vaex_snap_extents(const float* x_dev, int64_t n, int32_t d, const float* mean_dev,
+                      const float* scale_dev, int mode, const int32_t* slot_extent_dev,
+                      const uint8_t* slot_last_dev, int32_t max_innermost, int32_t* extents_dev,
+                      void* stream);
+/* VAECostPredictor.predict_cost (utils/model.py:168-170); drop_mask_dev (uint8 [n, PH], 1=keep)
+ * or drop_seed != 0 activates Dropout(p) after the first ReLU (mc_predict, :241-273). */
+int vaex_predict_cost(vaex_model_t h, const float* z_dev, int64_t n, float* cost_dev,
+                      const uint8_t* drop_mask_dev_or_null, uint64_t drop_seed, float p_drop,
+                      void* stream);
+/* select_topk_z_grad's autograd.grad(cost.sum(), z) (utils/select.py:128-135) */
+int vaex_cost_grad_z(vaex_model_t h, const float* z_dev, int64_t n, float* cost_dev,
+                     float* grad_z_dev, float* grad_norm_dev_or_null, void* stream);
+/* multi-step ascent z += lr * dcost/dz (new surface, BASELINE config 3) */
+int vaex_latent_ascent(vaex_model_t h, float* z_inout_dev, int64_t n, int32_t steps, float lr,
+                       float* cost_dev, void* stream);
+
+/* ---- top-k (util_select_topk, utils/select.py:54-81) -------------------------------------- */
+/* k largest of scores[n] restricted to mask (uint8, 1 = eligible; NULL = all), ordered by
+ * (score desc, index asc).  out_vals fp32[k], out_idx int64[k]; *n_out_dev (int32) = number
+ * written (min(k, eligible)).  k <= 1024. */
+int vaex_topk(const float* scores_dev, int64_t n, int32_t k, const uint8_t* mask_dev_or_null,
+              float* out_vals_dev, int64_t* out_idx_dev, int32_t* n_out_dev, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VAEX_B200_H_ */

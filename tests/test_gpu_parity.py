@@ -1,0 +1,264 @@
+"""GPU parity tests: the CUDA path (through the C-ABI / its Python mirror) against the oracle
+and the committed reference goldens.  Tolerances: integer / index outputs bit-exact; fp32 SIMT
+kernels 1e-5; the tcgen05 path (fp16 operands, fp32 accumulate) 1e-3 relative to the score
+scale, as BASELINE.json's north_star states."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_golden, split_sd
+from oracle import torch_oracle as O
+
+import vaex_b200
+from vaex_b200 import _lib
+
+pytestmark = pytest.mark.gpu
+TC_RTOL = 1e-3
+
+
+def rel_err(got, want):
+    got, want = np.asarray(got, np.float64), np.asarray(want, np.float64)
+    fin = np.isfinite(want)
+    assert np.array_equal(np.isfinite(got), fin)
+    scale = max(1e-6, np.sqrt(np.mean(want[fin] ** 2))) if fin.any() else 1.0
+    return float(np.abs(got[fin] - want[fin]).max() / scale) if fin.any() else 0.0
+
+
+def make_net(g, F):
+    net = vaex_b200.SegmentSumMLPModule(F, 256, 1)
+    net.load_state_dict(split_sd(g, "w."))
+    return net.cuda().eval()
+
+
+def synth(rng, n, F=164, smax=32, zero_frac=0.01):
+    sizes = rng.integers(1, smax + 1, size=n).astype(np.int32)
+    feats = rng.random((int(sizes.sum()), F), dtype=np.float32)
+    feats[:, rng.random(F) < 0.15] = 0.0
+    offs = np.concatenate([[0], np.cumsum(sizes)])
+    for p in np.nonzero(rng.random(n) < zero_frac)[0]:
+        feats[offs[p]:offs[p + 1]] = 0.0
+    return feats, sizes
+
+
+@pytest.mark.parametrize("tag,F", [("f164", 164), ("f174", 174)])
+@pytest.mark.parametrize("flags,tol", [(_lib.F_FORCE_SIMT, 2e-5), (0, TC_RTOL)])
+def test_segsum_mlp_golden(tag, F, flags, tol):
+    g = load_golden("segsum_mlp_%s.npz" % tag)
+    net = make_net(g, F)
+    raw = g["raw"]
+    if F == 174:
+        raw = np.concatenate([raw, np.zeros((raw.shape[0], 10), np.float32)], axis=1)
+    flat_norm = torch.from_numpy(raw) / torch.from_numpy(g["norm"])
+    with torch.no_grad():
+        got = net(torch.from_numpy(g["sizes"]).cuda(), flat_norm.cuda(), flags=flags).cpu().numpy()
+    assert rel_err(got, g["direct"]) < tol
+    # host path, raw features, 1/norm folded into W0, -inf rule
+    pred = vaex_b200.predict_flat(net, raw, g["sizes"], g["norm"], flags | _lib.F_MASK_INVALID)
+    assert np.array_equal(np.isneginf(pred), np.isneginf(g["masked"]))
+    assert rel_err(pred, g["masked"]) < max(tol, 5e-5)
+
+
+@pytest.mark.parametrize("flags,tol", [(_lib.F_FORCE_SIMT, 2e-5), (0, TC_RTOL)])
+def test_segsum_mlp_seeded_vs_oracle(flags, tol):
+    rng = np.random.default_rng(3)
+    torch.manual_seed(3)
+    net = vaex_b200.SegmentSumMLPModule(164, 256, 1).cuda().eval()
+    P = {k: v.detach().cpu() for k, v in net.state_dict().items()}
+    feats, sizes = synth(rng, 20000)
+    with torch.no_grad():
+        got = net(torch.from_numpy(sizes).cuda(), torch.from_numpy(feats).cuda(), flags=flags | _lib.F_MASK_INVALID)
+    want = O.segsum_mlp_forward(P, sizes, feats).numpy()
+    offs = np.concatenate([[0], np.cumsum(sizes)])
+    zero = np.array([not feats[offs[i]:offs[i + 1]].any() for i in range(len(sizes))])
+    want[zero] = -np.inf
+    assert zero.sum() > 10
+    assert rel_err(got.cpu().numpy(), want) < tol
+
+
+@pytest.mark.parametrize("flags", [_lib.F_FORCE_SIMT, 0])
+def test_segsum_mlp_edge_cases(flags):
+    torch.manual_seed(4)
+    net = vaex_b200.SegmentSumMLPModule(164, 256, 1).cuda().eval()
+    P = {k: v.detach().cpu() for k, v in net.state_dict().items()}
+    rng = np.random.default_rng(4)
+    cases = {
+        "one_row": np.array([1], np.int32),
+        "all_ones": np.ones(300, np.int32),
+        "max32": np.full(129, 32, np.int32),
+        "with_empty_segments": np.array([3, 0, 0, 5, 1, 0, 32, 0], np.int32),
+        "long_segment": np.array([1, 700, 2], np.int32),
+        "ragged_tile_edges": np.array([127, 1, 128, 129, 255, 2], np.int32),
+    }
+    for name, sizes in cases.items():
+        feats = rng.random((int(sizes.sum()), 164), dtype=np.float32)
+        with torch.no_grad():
+            got = net(torch.from_numpy(sizes).cuda(), torch.from_numpy(feats).cuda(), flags=flags)
+        want = O.segsum_mlp_forward(P, sizes, feats).numpy()
+        got = got.cpu().numpy().reshape(-1)
+        assert got.shape == want.reshape(-1).shape, name
+        assert rel_err(got, want.reshape(-1)) < (2e-5 if flags else TC_RTOL), name
+    # empty batch
+    assert vaex_b200.predict_flat(net, np.zeros((0, 164), np.float32), np.zeros(0, np.int32)).shape == (0,)
+
+
+def test_segsum_mlp_properties_large():
+    """size-independent properties at a large size: order independence and duplicates."""
+    rng = np.random.default_rng(5)
+    torch.manual_seed(5)
+    net = vaex_b200.SegmentSumMLPModule(164, 256, 1).cuda().eval()
+    n = 200000
+    sizes = rng.integers(1, 33, size=n).astype(np.int32)
+    feats = torch.rand(int(sizes.sum()), 164, device="cuda", generator=torch.Generator("cuda").manual_seed(5))
+    st = torch.from_numpy(sizes).cuda()
+    with torch.no_grad():
+        a = net(st, feats)
+        # reversed program order (rows of each program kept in order)
+        offs = np.concatenate([[0], np.cumsum(sizes)])
+        order = np.arange(n)[::-1].copy()
+        row_idx = np.concatenate([np.arange(offs[p], offs[p + 1]) for p in order[:5000]])
+        b = net(torch.from_numpy(sizes[order[:5000]]).cuda(), feats[torch.from_numpy(row_idx).cuda()])
+        c = net(st, feats)
+    assert torch.equal(a, c), "not deterministic run to run"
+    assert torch.equal(a[torch.from_numpy(order[:5000]).cuda()], b), "score depends on batch position"
+    # host path (chunked, two streams) == device path
+    h = vaex_b200.predict_flat(net, feats[: offs[50000]].cpu().numpy(), sizes[:50000])
+    assert np.array_equal(h, a[:50000].cpu().numpy())
+
+
+def test_segment_offsets_scan():
+    lib = _lib.load()
+    for n in [0, 1, 5, 2048, 2049, 1000003]:
+        s = torch.randint(0, 33, (n,), dtype=torch.int32, device="cuda")
+        out = torch.empty(n + 1, dtype=torch.int32, device="cuda")
+        _lib.check(lib.vaex_segment_offsets(_lib.ptr(s), n, _lib.ptr(out), _lib.stream_ptr()))
+        want = np.concatenate([[0], np.cumsum(s.cpu().numpy().astype(np.int64))])
+        assert np.array_equal(out.cpu().numpy(), want)
+
+
+def test_extent_vae_golden():
+    g = load_golden("extent_vae.npz")
+    vae = vaex_b200.VAE_feature_head(48, None, 64, 256)
+    vae.load_state_dict(split_sd(g, "vae."))
+    reg = vaex_b200.VAECostPredictor(48, hidden_dim=256, latent_dim=64)
+    reg.load_state_dict(split_sd(g, "reg."))
+    vae, reg = vae.cuda().eval(), reg.cuda().eval()
+    x, z = torch.from_numpy(g["x"]).cuda(), torch.from_numpy(g["z"]).cuda()
+    tol = dict(rtol=2e-5, atol=2e-6)
+    mu, logvar = vae.encode(x)
+    np.testing.assert_allclose(mu.cpu().numpy(), g["mu"], **tol)
+    np.testing.assert_allclose(logvar.cpu().numpy(), g["logvar"], **tol)
+    np.testing.assert_allclose(vae.decode(z).cpu().numpy(), g["dec"], **tol)
+    recon, mu2, _, z2, fp = vae(x, use_mean=True)
+    np.testing.assert_allclose(recon.cpu().numpy(), g["recon"], rtol=1e-4, atol=1e-5)
+    assert fp is None and torch.equal(mu2, z2)
+    np.testing.assert_allclose(reg.predict_cost(z).cpu().numpy(), g["cost"], **tol)
+    cost_x, mean_x, _, _ = reg(x, use_mean=True)
+    np.testing.assert_allclose(cost_x.cpu().numpy(), g["cost_x"], rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(reg.encode(x, use_mean=True).cpu().numpy(), g["mean_x"], **tol)
+    # autograd.grad through the CUDA backward (select.py:128-135)
+    zz = z.clone().requires_grad_(True)
+    c = reg.predict_cost(zz)
+    grad = torch.autograd.grad(c.sum(), zz)[0]
+    np.testing.assert_allclose(grad.cpu().numpy(), g["grad"], rtol=1e-4, atol=1e-6)
+    _, g2, norm = reg.cost_grad_z(z)
+    np.testing.assert_allclose(norm.cpu().numpy(), np.linalg.norm(g["grad"], axis=1), rtol=1e-4)
+    # MC dropout with the recorded masks
+    m, v = reg.mc_predict(x, T=g["masks"].shape[0], masks=torch.from_numpy(g["masks"]).cuda())
+    np.testing.assert_allclose(m.cpu().numpy(), g["mc_mean"], rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(v.cpu().numpy(), g["mc_var"], rtol=1e-3, atol=1e-7)
+    # Philox dropout / reparameterisation: distributional checks
+    m2, v2 = reg.mc_predict(x, T=64, seed=7)
+    assert np.abs(m2.cpu().numpy() - g["cost_x"]).mean() < 0.05 and (v2 > 0).all()
+    big_mu, big_lv = torch.zeros(200000, 64, device="cuda"), torch.full((200000, 64), np.log(4.0), device="cuda")
+    zs = reg.reparameterize(big_mu, big_lv, seed=11)
+    assert abs(zs.mean().item()) < 0.01 and abs(zs.std().item() - 2.0) < 0.01
+    eps = torch.randn(300, 64, device="cuda")
+    np.testing.assert_allclose(reg.reparameterize(mu, logvar, eps=eps).cpu().numpy(),
+                               O.reparameterize(mu.cpu(), logvar.cpu(), eps.cpu()).numpy(), rtol=1e-5, atol=1e-6)
+
+
+def test_snap_bit_exact_and_legalise():
+    g = load_golden("snap.npz")
+    x = torch.from_numpy(g["x"]).cuda()
+    assert np.array_equal(vaex_b200.snap_extents(x, g["mean"], g["std"]).cpu().numpy(), g["ext"])
+    assert np.array_equal(vaex_b200.snap_extents(x, g["mean"], g["std"], log1p=True).cpu().numpy(), g["ext_log1p"])
+    rng = np.random.default_rng(9)
+    xb = (rng.standard_normal((4096, 48)) * 1.5).astype(np.float32)
+    mean = rng.uniform(0.5, 3, 48).astype(np.float32)
+    std = rng.uniform(0.3, 1.5, 48).astype(np.float32)
+    want = O.snap_round_clamp(xb, mean, std).numpy()
+    assert np.array_equal(vaex_b200.snap_extents(torch.from_numpy(xb).cuda(), mean, std).cpu().numpy(), want)
+    # divisor legalisation against the utils.cc:446-463 restatement; task-1264-like loop bounds
+    bounds = [1, 3, 4, 28, 56, 57, 64, 128, 960, 4096]
+    ext, last = [], []
+    while len(ext) < 44:
+        b = bounds[rng.integers(len(bounds))]
+        ext += [b] * 4
+        last += [0, 0, 0, 1]
+    ext, last = ext + [0] * 4, last + [0] * 4
+    got = vaex_b200.snap_extents(torch.from_numpy(xb[:512]).cuda(), mean, std, slot_extent=ext, slot_last=last).cpu().numpy()
+    assert np.array_equal(got, O.legalise_divisor(want[:512], ext, last))
+    for j0 in range(0, 44, 4):
+        prod = got[:, j0:j0 + 4].astype(np.int64).prod(axis=1)
+        assert (ext[j0] % prod == 0).all() and (got[:, j0 + 3] <= 64).all()
+
+
+def test_topk_vs_oracle():
+    rng = np.random.default_rng(10)
+    cases = [
+        (rng.standard_normal(1000).astype(np.float32), 48, None),
+        (rng.integers(0, 5, 5000).astype(np.float32), 320, None),            # heavy ties
+        (np.zeros(4096, np.float32), 64, None),                               # all equal
+        (rng.standard_normal(2_000_003).astype(np.float32), 320, None),
+        (rng.standard_normal(5000).astype(np.float32), 100, rng.random(5000) < 0.3),
+        (rng.standard_normal(50).astype(np.float32), 64, rng.random(50) < 0.5),   # k > eligible
+        (np.where(rng.random(3000) < 0.5, -np.inf, rng.standard_normal(3000)).astype(np.float32), 1024, None),
+    ]
+    for s, k, mask in cases:
+        mk = None if mask is None else torch.from_numpy(mask.astype(np.uint8)).cuda()
+        vals, idx = vaex_b200.topk(torch.from_numpy(s).cuda(), k, mk)
+        if mask is None:
+            wv, wi = O.topk_desc(s, k)
+        else:
+            el = np.nonzero(mask)[0]
+            wv, wl = O.topk_desc(s[el], k)
+            wi = el[wl]
+        assert np.array_equal(idx.cpu().numpy(), wi)
+        assert np.array_equal(vals.cpu().numpy(), wv)
+
+
+def test_select_programs_matches_reference():
+    g = load_golden("select.npz")
+    reg = vaex_b200.VAECostPredictor(48, hidden_dim=256, latent_dim=64)
+    reg.load_state_dict(split_sd(g, "reg."))
+    reg = reg.cuda().eval()
+    rem = set(g["remaining"].tolist())
+    sel, rem_after = vaex_b200.select.util_select_topk(torch.from_numpy(g["cost"]).cuda(), set(rem), 48)
+    assert np.array_equal(np.sort(sel), g["topk48"])
+    sel_prog, rem_prog = vaex_b200.select_programs(
+        reg, g["x"], set(g["used"].tolist()), set(rem), num_select=64, T_mc=4, uncertainty_topk=10 ** 9,
+        w_cost=1.0, w_unc=0.0, w_div=0.0, grad_num=2, rand_num=0, rng=np.random.default_rng(42),
+        device=torch.device("cuda"), topk_factor=5)
+    assert np.array_equal(sel_prog, g["sel_prog"])
+    assert np.array_equal(np.array(sorted(rem_prog)), g["rem_prog"])
+
+
+def test_latent_ascent_vs_oracle():
+    g = load_golden("extent_vae.npz")
+    reg = vaex_b200.VAECostPredictor(48, hidden_dim=256, latent_dim=64)
+    reg.load_state_dict(split_sd(g, "reg."))
+    reg = reg.cuda().eval()
+    z0 = g["z"][:256]
+    z, c = reg.latent_ascent(torch.from_numpy(z0).cuda(), steps=50, lr=1e-2)
+    wz, wc = O.latent_ascent(split_sd(g, "reg."), z0, 50, 1e-2)
+    np.testing.assert_allclose(z.cpu().numpy(), wz.numpy(), rtol=1e-3, atol=1e-4)
+    np.testing.assert_allclose(c.cpu().numpy(), wc.numpy(), rtol=1e-3, atol=1e-4)
+
+
+def test_errors_are_loud():
+    lib = _lib.load()
+    m = _lib.Model(_lib.KIND_SEGSUM_MLP, [164, 256, 0, 0])
+    with pytest.raises(_lib.VaexError, match="missing weight"):
+        m.load_state({})
+    x = torch.zeros(4, device="cuda")
+    assert lib.vaex_topk(_lib.ptr(x), 4, 5000, None, _lib.ptr(x), _lib.ptr(x), None, None) == -1

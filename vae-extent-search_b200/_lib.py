@@ -1,0 +1,126 @@
+"""ctypes binding of libvaex_b200.so (include/vaex_b200.h).  There is no CPU fallback: if the
+library is missing or no CUDA device is present, calls fail loudly."""
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libvaex_b200.so")
+
+KIND_SEGSUM_MLP, KIND_EXTENT_VAE, KIND_COST_PREDICTOR = 1, 2, 3
+F_MASK_INVALID, F_FORCE_SIMT = 1, 2
+SNAP_EXP, SNAP_EXPM1, SNAP_DIVISOR = 0, 1, 4
+
+c_i32p = ctypes.POINTER(ctypes.c_int32)
+c_f32p = ctypes.POINTER(ctypes.c_float)
+vp, i64, i32, u64, f32 = ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32, ctypes.c_uint64, ctypes.c_float
+
+# name -> argtypes; every symbol declared in include/vaex_b200.h (tests check the export list)
+SIGNATURES = {
+    "vaex_last_error": ([], ctypes.c_char_p),
+    "vaex_abi_version": ([], ctypes.c_int),
+    "vaex_device_count": ([], ctypes.c_int),
+    "vaex_launch_count": ([], i64),
+    "vaex_model_create": ([ctypes.c_int, c_i32p, ctypes.c_int, ctypes.POINTER(vp)], ctypes.c_int),
+    "vaex_model_load_weights": ([vp, ctypes.c_char_p, vp, i32, i32], ctypes.c_int),
+    "vaex_model_pack": ([vp, vp, vp], ctypes.c_int),
+    "vaex_model_destroy": ([vp], ctypes.c_int),
+    "vaex_segment_offsets": ([vp, i64, vp, vp], ctypes.c_int),
+    "vaex_segsum_mlp_forward": ([vp, vp, vp, i64, i64, vp, ctypes.c_int, vp], ctypes.c_int),
+    "vaex_segsum_encode": ([vp, vp, vp, i64, i64, vp, ctypes.c_int, vp], ctypes.c_int),
+    "vaex_segsum_mlp_predict_host": ([vp, vp, vp, i64, i64, vp, ctypes.c_int], ctypes.c_int),
+    "vaex_vae_encode": ([vp, vp, i64, vp, vp, vp], ctypes.c_int),
+    "vaex_reparam": ([vp, vp, vp, u64, u64, vp, i64, i32, vp], ctypes.c_int),
+    "vaex_vae_decode": ([vp, vp, i64, vp, vp], ctypes.c_int),
+    "vaex_snap_extents": ([vp, i64, i32, vp, vp, ctypes.c_int, vp, vp, i32, vp, vp], ctypes.c_int),
+    "vaex_predict_cost": ([vp, vp, i64, vp, vp, u64, f32, vp], ctypes.c_int),
+    "vaex_cost_grad_z": ([vp, vp, i64, vp, vp, vp, vp], ctypes.c_int),
+    "vaex_latent_ascent": ([vp, vp, i64, i32, f32, vp, vp], ctypes.c_int),
+    "vaex_topk": ([vp, i64, i32, vp, vp, vp, vp, vp], ctypes.c_int),
+}
+
+
+class VaexError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load():
+    """Returns the CDLL with typed signatures.  Raises if the library has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.isfile(LIB_PATH):
+        raise VaexError(
+            "%s not found: build it with vae-extent-search_b200/csrc/build.sh "
+            "(or __graft_entry__.build()).  vaex_b200 has no CPU fallback." % LIB_PATH)
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (argtypes, restype) in SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.argtypes = argtypes
+        fn.restype = restype
+    if lib.vaex_abi_version() != 1:
+        raise VaexError("ABI version mismatch")
+    _lib = lib
+    return lib
+
+
+def check(rc):
+    if rc != 0:
+        msg = load().vaex_last_error()
+        raise VaexError("vaex_b200 error %d: %s" % (rc, msg.decode() if msg else "?"))
+
+
+def ptr(t):
+    """Device (or host) pointer of a torch tensor / numpy array / None."""
+    if t is None:
+        return None
+    if isinstance(t, np.ndarray):
+        return t.ctypes.data
+    return t.data_ptr()
+
+
+def stream_ptr():
+    import torch
+    return torch.cuda.current_stream().cuda_stream
+
+
+class Model:
+    """Owns a vaex_model_t.  weights: dict name -> array-like (reference state_dict keys)."""
+
+    def __init__(self, kind, dims):
+        self.lib = load()
+        self.kind = kind
+        self.h = vp()
+        arr = (ctypes.c_int32 * len(dims))(*[int(d) for d in dims])
+        check(self.lib.vaex_model_create(kind, arr, len(dims), ctypes.byref(self.h)))
+
+    def load_state(self, state, norm_vec=None):
+        for name, t in state.items():
+            if hasattr(t, "detach"):
+                t = t.detach().to("cpu").float().numpy()
+            a = np.ascontiguousarray(np.asarray(t, dtype=np.float32))
+            if a.ndim == 0 or "num_batches_tracked" in name:
+                continue
+            rows, cols = (1, a.shape[0]) if a.ndim == 1 else a.shape
+            check(self.lib.vaex_model_load_weights(self.h, name.encode(), a.ctypes.data, rows, cols))
+        nv = None
+        if norm_vec is not None:
+            if hasattr(norm_vec, "detach"):
+                norm_vec = norm_vec.detach().to("cpu").float().numpy()
+            nv = np.ascontiguousarray(np.asarray(norm_vec, dtype=np.float32))
+        check(self.lib.vaex_model_pack(self.h, nv.ctypes.data if nv is not None else None, None))
+
+    def close(self):
+        if self.h:
+            self.lib.vaex_model_destroy(self.h)
+            self.h = vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

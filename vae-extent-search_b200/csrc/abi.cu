@@ -1,0 +1,214 @@
+// extern "C" entry points of libvaex_b200.so (declared in include/vaex_b200.h).
+#include <algorithm>
+#include <atomic>
+#include <cmath>
+#include <cstring>
+
+#include "common.cuh"
+#include "model.cuh"
+#include "simt_kernels.cuh"
+
+namespace vaex {
+
+static thread_local std::string g_err;
+static std::atomic<int64_t> g_launches{0};
+void set_error(const std::string& msg) { g_err = msg; }
+void count_launch(int n) { g_launches += n; }
+
+int DevBuf::ensure(size_t need) {
+  if (need <= bytes) return VAEX_OK;
+  if (p) VAEX_CUDA(cudaFree(p));
+  p = nullptr; bytes = 0;
+  need = (need + (1u << 20) - 1) & ~((size_t)(1u << 20) - 1);
+  VAEX_CUDA(cudaMalloc(&p, need));
+  bytes = need;
+  return VAEX_OK;
+}
+void DevBuf::release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+
+static int upload(vaex_model* m, const std::string& name, const float* src, size_t count, cudaStream_t st) {
+  float* d = nullptr;
+  auto it = m->dev.find(name);
+  if (it != m->dev.end()) { cudaFree(it->second); m->dev.erase(it); }
+  VAEX_CUDA(cudaMalloc(&d, std::max<size_t>(count, 1) * sizeof(float)));
+  VAEX_CUDA(cudaMemcpyAsync(d, src, count * sizeof(float), cudaMemcpyHostToDevice, st));
+  VAEX_CUDA(cudaStreamSynchronize(st));  // src may be a temporary
+  m->dev[name] = d;
+  return VAEX_OK;
+}
+
+static int need(vaex_model* m, const char* name, int rows, int cols) {
+  auto it = m->host.find(name);
+  if (it == m->host.end()) { set_error(std::string("missing weight ") + name); return VAEX_E_INVALID; }
+  if (it->second.rows != rows || it->second.cols != cols) {
+    set_error(std::string("bad shape for ") + name + ": got [" + std::to_string(it->second.rows) + "," +
+              std::to_string(it->second.cols) + "] want [" + std::to_string(rows) + "," + std::to_string(cols) + "]");
+    return VAEX_E_INVALID;
+  }
+  return VAEX_OK;
+}
+
+static std::vector<float> transpose(const HostTensor& t) {
+  std::vector<float> o((size_t)t.rows * t.cols);
+  for (int r = 0; r < t.rows; ++r)
+    for (int c = 0; c < t.cols; ++c) o[(size_t)c * t.rows + r] = t.v[(size_t)r * t.cols + c];
+  return o;
+}
+
+#define TRY(x) do { int rc_ = (x); if (rc_ != VAEX_OK) return rc_; } while (0)
+
+static int pack_linear(vaex_model* m, const std::string& pre, int out, int in, cudaStream_t st) {
+  TRY(need(m, (pre + ".weight").c_str(), out, in));
+  TRY(need(m, (pre + ".bias").c_str(), 1, out));
+  TRY(upload(m, pre + ".weight", m->host[pre + ".weight"].v.data(), (size_t)out * in, st));
+  TRY(upload(m, pre + ".bias", m->host[pre + ".bias"].v.data(), out, st));
+  return VAEX_OK;
+}
+
+static int pack_segsum_mlp(vaex_model* m, const float* norm, cudaStream_t st) {
+  const int F = m->F, H = m->H;
+  TRY(need(m, "segment_encoder.0.weight", H, F));
+  TRY(need(m, "segment_encoder.0.bias", 1, H));
+  // fold SegmentDataLoader.normalize (features /= norm_vec, mlp_model.py:95-105) into W0 columns
+  std::vector<float> w0 = m->host["segment_encoder.0.weight"].v;
+  if (norm)
+    for (int r = 0; r < H; ++r)
+      for (int c = 0; c < F; ++c) w0[(size_t)r * F + c] /= norm[c];
+  TRY(upload(m, "segment_encoder.0.weight", w0.data(), w0.size(), st));
+  TRY(upload(m, "segment_encoder.0.bias", m->host["segment_encoder.0.bias"].v.data(), H, st));
+  TRY(pack_linear(m, "segment_encoder.2", H, H, st));
+  TRY(pack_linear(m, "l0.0", H, H, st));
+  TRY(pack_linear(m, "l1.0", H, H, st));
+  TRY(pack_linear(m, "decoder", 1, H, st));
+  if (m->use_norm) {  // eval-mode BatchNorm1d -> per-column affine y = s*a + c
+    for (const char* k : {"norm.weight", "norm.bias", "norm.running_mean", "norm.running_var"}) TRY(need(m, k, 1, H));
+    std::vector<float> a(H), c(H);
+    for (int j = 0; j < H; ++j) {
+      const float inv = 1.0f / std::sqrt(m->host["norm.running_var"].v[j] + 1e-5f);
+      a[j] = m->host["norm.weight"].v[j] * inv;
+      c[j] = m->host["norm.bias"].v[j] - m->host["norm.running_mean"].v[j] * a[j];
+    }
+    TRY(upload(m, "norm.scale", a.data(), H, st));
+    TRY(upload(m, "norm.shift", c.data(), H, st));
+  }
+  TRY(tc_pack(m, w0, st));
+  return VAEX_OK;
+}
+
+static int pack_encoder(vaex_model* m, cudaStream_t st) {
+  const int D = m->D, H = m->H, L = m->L;
+  TRY(pack_linear(m, "encoder.0", H, D, st));
+  TRY(pack_linear(m, "encoder.2", H, H, st));
+  TRY(pack_linear(m, "encoder.4", H, H, st));
+  TRY(pack_linear(m, "fc_mu", L, H, st));
+  TRY(pack_linear(m, "fc_logvar", L, H, st));
+  return VAEX_OK;
+}
+
+static int pack_model(vaex_model* m, const float* norm, cudaStream_t st) {
+  switch (m->kind) {
+    case VAEX_KIND_SEGSUM_MLP: return pack_segsum_mlp(m, norm, st);
+    case VAEX_KIND_EXTENT_VAE: {
+      TRY(pack_encoder(m, st));
+      TRY(pack_linear(m, "decoder.0", m->H, m->L, st));
+      TRY(pack_linear(m, "decoder.2", m->H, m->H, st));
+      TRY(pack_linear(m, "decoder.4", m->H, m->H, st));
+      TRY(pack_linear(m, "decoder.6", m->D, m->H, st));
+      return VAEX_OK;
+    }
+    case VAEX_KIND_COST_PREDICTOR: {
+      TRY(pack_encoder(m, st));
+      TRY(pack_linear(m, "cost_predictor.0", m->PH, m->L, st));
+      TRY(pack_linear(m, "cost_predictor.3", m->PH, m->PH, st));
+      TRY(pack_linear(m, "cost_predictor.6", 1, m->PH, st));
+      // transposed copies for the backward pass (dcost/dz)
+      auto t3 = transpose(m->host["cost_predictor.3.weight"]);
+      auto t0 = transpose(m->host["cost_predictor.0.weight"]);
+      TRY(upload(m, "cost_predictor.3.weight_t", t3.data(), t3.size(), st));
+      TRY(upload(m, "cost_predictor.0.weight_t", t0.data(), t0.size(), st));
+      return VAEX_OK;
+    }
+  }
+  set_error("unknown model kind");
+  return VAEX_E_INVALID;
+}
+
+}  // namespace vaex
+
+using namespace vaex;
+
+extern "C" {
+
+const char* vaex_last_error(void) { return g_err.c_str(); }
+int vaex_abi_version(void) { return VAEX_ABI_VERSION; }
+int64_t vaex_launch_count(void) { return g_launches.load(); }
+
+int vaex_device_count(void) {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess) { set_error(std::string("cudaGetDeviceCount: ") + cudaGetErrorString(e)); return VAEX_E_CUDA; }
+  return n;
+}
+
+int vaex_model_create(int kind, const int32_t* dims, int ndims, vaex_model_t* out) {
+  VAEX_CHECK(out && dims, "null argument");
+  vaex_model* m = new vaex_model();
+  m->kind = kind;
+  int rc = VAEX_OK;
+  if (kind == VAEX_KIND_SEGSUM_MLP && ndims == 4) {
+    m->F = dims[0]; m->H = dims[1]; m->use_norm = dims[2]; m->add_sigmoid = dims[3];
+    if (m->F < 1 || m->H < 1) rc = VAEX_E_INVALID;
+  } else if (kind == VAEX_KIND_EXTENT_VAE && ndims == 3) {
+    m->D = dims[0]; m->H = dims[1]; m->L = dims[2];
+    if (m->D < 1 || m->H < 1 || m->L < 1) rc = VAEX_E_INVALID;
+  } else if (kind == VAEX_KIND_COST_PREDICTOR && ndims == 4) {
+    m->D = dims[0]; m->H = dims[1]; m->L = dims[2]; m->PH = dims[3];
+    if (m->D < 1 || m->H < 1 || m->L < 1 || m->PH < 1) rc = VAEX_E_INVALID;
+  } else {
+    rc = VAEX_E_INVALID;
+  }
+  if (rc != VAEX_OK) { delete m; set_error("bad kind/dims for vaex_model_create"); return rc; }
+  *out = m;
+  return VAEX_OK;
+}
+
+int vaex_model_load_weights(vaex_model_t h, const char* name, const float* data, int32_t rows, int32_t cols) {
+  VAEX_CHECK(h && name && data, "null argument");
+  VAEX_CHECK(rows >= 1 && cols >= 1, "bad shape");
+  HostTensor t;
+  t.rows = rows; t.cols = cols;
+  t.v.assign(data, data + (size_t)rows * cols);
+  h->host[name] = std::move(t);
+  h->packed = false;
+  return VAEX_OK;
+}
+
+int vaex_model_pack(vaex_model_t h, const float* fea_norm_vec_host, void* stream) {
+  VAEX_CHECK(h, "null handle");
+  int n = vaex_device_count();
+  if (n <= 0) { if (n == 0) set_error("no CUDA device: vaex_b200 has no CPU fallback"); return VAEX_E_CUDA; }
+  TRY(pack_model(h, fea_norm_vec_host, (cudaStream_t)stream));
+  h->packed = true;
+  return VAEX_OK;
+}
+
+int vaex_model_destroy(vaex_model_t h) {
+  if (!h) return VAEX_OK;
+  for (auto& kv : h->dev) cudaFree(kv.second);
+  for (auto& b : h->ws) b.release();
+  h->topk_ws.release();
+  if (h->tc.w0) cudaFree(h->tc.w0);
+  if (h->tc.w1) cudaFree(h->tc.w1);
+  if (h->tc.b0) cudaFree(h->tc.b0);
+  if (h->tc.b1) cudaFree(h->tc.b1);
+  for (auto& sl : h->slots) { if (sl.feats) cudaFree(sl.feats); if (sl.off) cudaFree(sl.off); if (sl.scores) cudaFree(sl.scores); }
+  for (auto& s : h->copy_streams) if (s) cudaStreamDestroy(s);
+  for (auto& e : h->events) if (e) cudaEventDestroy(e);
+  delete h;
+  return VAEX_OK;
+}
+
+}  // extern "C"
+
+#include "abi_segsum.inc"
+#include "abi_vae.inc"

@@ -1,0 +1,294 @@
+// Bandwidth-bound helpers: scan, reparameterisation, integer snap / legalise, dropout,
+// ReLU-mask products for the fused backward, z update.
+#include "common.cuh"
+#include "simt_kernels.cuh"
+
+namespace vaex {
+
+// ------------------------------------------------------------------ exclusive scan (int32)
+constexpr int SCAN_T = 256, SCAN_I = 8, SCAN_B = SCAN_T * SCAN_I;
+
+__device__ __forceinline__ int block_excl_scan(int v, int* total) {
+  __shared__ int wsum[SCAN_T / 32];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  int inc = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    int t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += t;
+  }
+  if (lane == 31) wsum[w] = inc;
+  __syncthreads();
+  if (w == 0) {
+    int s = lane < SCAN_T / 32 ? wsum[lane] : 0;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      int t = __shfl_up_sync(0xffffffffu, s, o);
+      if (lane >= o) s += t;
+    }
+    if (lane < SCAN_T / 32) wsum[lane] = s;
+  }
+  __syncthreads();
+  const int base = w ? wsum[w - 1] : 0;
+  *total = wsum[SCAN_T / 32 - 1];
+  __syncthreads();
+  return base + inc - v;
+}
+
+__global__ void scan_block_sums(const int32_t* __restrict__ in, int64_t n, int32_t* __restrict__ bsum) {
+  const int64_t base = (int64_t)blockIdx.x * SCAN_B + threadIdx.x * SCAN_I;
+  int s = 0;
+#pragma unroll
+  for (int i = 0; i < SCAN_I; ++i) if (base + i < n) s += in[base + i];
+  int total;
+  block_excl_scan(s, &total);
+  if (threadIdx.x == 0) bsum[blockIdx.x] = total;
+}
+
+__global__ void scan_of_sums(int32_t* bsum, int nb) {  // single block, in place exclusive
+  __shared__ int carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (int b0 = 0; b0 < nb; b0 += SCAN_T) {
+    const int i = b0 + threadIdx.x;
+    const int v = i < nb ? bsum[i] : 0;
+    int total;
+    const int ex = block_excl_scan(v, &total);
+    const int c = carry;
+    if (i < nb) bsum[i] = c + ex;
+    __syncthreads();
+    if (threadIdx.x == 0) carry = c + total;
+    __syncthreads();
+  }
+}
+
+__global__ void scan_final(const int32_t* __restrict__ in, int64_t n, const int32_t* __restrict__ bsum,
+                           int32_t* __restrict__ out) {
+  const int64_t base = (int64_t)blockIdx.x * SCAN_B + threadIdx.x * SCAN_I;
+  int v[SCAN_I], s = 0;
+#pragma unroll
+  for (int i = 0; i < SCAN_I; ++i) { v[i] = base + i < n ? in[base + i] : 0; s += v[i]; }
+  int total;
+  int run = block_excl_scan(s, &total) + bsum[blockIdx.x];
+#pragma unroll
+  for (int i = 0; i < SCAN_I; ++i) {
+    if (base + i < n) out[base + i] = run;
+    run += v[i];
+    if (base + i == n - 1) out[n] = run;
+  }
+}
+
+int exclusive_scan_i32(const int32_t* sizes, int64_t n, int32_t* offsets, cudaStream_t st) {
+  if (n == 0) {
+    VAEX_CUDA(cudaMemsetAsync(offsets, 0, sizeof(int32_t), st));
+    return VAEX_OK;
+  }
+  const int nb = (int)cdiv(n, SCAN_B);
+  int32_t* bsum = nullptr;
+  VAEX_CUDA(cudaMallocAsync(&bsum, sizeof(int32_t) * nb, st));
+  scan_block_sums<<<nb, SCAN_T, 0, st>>>(sizes, n, bsum);
+  VAEX_LAUNCH_CHECK();
+  scan_of_sums<<<1, SCAN_T, 0, st>>>(bsum, nb);
+  VAEX_LAUNCH_CHECK();
+  scan_final<<<nb, SCAN_T, 0, st>>>(sizes, n, bsum, offsets);
+  VAEX_LAUNCH_CHECK();
+  VAEX_CUDA(cudaFreeAsync(bsum, st));
+  return VAEX_OK;
+}
+
+// ------------------------------------------------------------------ Philox4x32-10
+struct Philox {
+  uint32_t k0, k1;
+  __device__ Philox(uint64_t seed) : k0((uint32_t)seed), k1((uint32_t)(seed >> 32)) {}
+  __device__ uint4 operator()(uint64_t ctr_lo, uint64_t ctr_hi) const {
+    uint32_t c0 = (uint32_t)ctr_lo, c1 = (uint32_t)(ctr_lo >> 32), c2 = (uint32_t)ctr_hi,
+             c3 = (uint32_t)(ctr_hi >> 32);
+    uint32_t a = k0, b = k1;
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+      const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+      const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+      c0 = hi1 ^ c1 ^ a; c1 = lo1; c2 = hi0 ^ c3 ^ b; c3 = lo0;
+      a += 0x9E3779B9u; b += 0xBB67AE85u;
+    }
+    return make_uint4(c0, c1, c2, c3);
+  }
+};
+__device__ __forceinline__ float u01(uint32_t x) { return (x >> 8) * (1.0f / 16777216.0f) + (0.5f / 16777216.0f); }
+
+// z = mu + eps * exp(0.5 logvar)   (utils/model.py:58-61); 4 elements per thread
+__global__ void reparam_kernel(const float* __restrict__ mu, const float* __restrict__ logvar,
+                               const float* __restrict__ eps, uint64_t seed, uint64_t offset,
+                               float* __restrict__ z, int64_t count) {
+  const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t e0 = q * 4;
+  if (e0 >= count) return;
+  float n4[4];
+  if (eps == nullptr) {
+    const uint4 r = Philox(seed)((uint64_t)q, offset);
+    const float r0 = sqrtf(-2.f * logf(u01(r.x))), r1 = sqrtf(-2.f * logf(u01(r.z)));
+    float s0, c0, s1, c1;
+    sincospif(2.f * u01(r.y), &s0, &c0);
+    sincospif(2.f * u01(r.w), &s1, &c1);
+    n4[0] = r0 * c0; n4[1] = r0 * s0; n4[2] = r1 * c1; n4[3] = r1 * s1;
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int64_t e = e0 + i;
+    if (e < count) {
+      const float n = eps ? eps[e] : n4[i];
+      z[e] = mu[e] + n * expf(0.5f * logvar[e]);
+    }
+  }
+}
+
+int reparam(const float* mu, const float* logvar, const float* eps, uint64_t seed, uint64_t offset,
+            float* z, int64_t count, cudaStream_t st) {
+  if (count == 0) return VAEX_OK;
+  reparam_kernel<<<(unsigned)cdiv(cdiv(count, 4), 256), 256, 0, st>>>(mu, logvar, eps, seed, offset, z, count);
+  VAEX_LAUNCH_CHECK();
+  return VAEX_OK;
+}
+
+// ------------------------------------------------------------------ snap + legalise
+// torch: clamp(round(exp(v)).int(), min=1); round = half-to-even; out-of-range float->int32
+// follows x86 cvttss2si (INT_MIN), which the clamp then maps to 1.
+// unfused mul/add (no FMA contraction) keeps v bit-identical with torch's x*(std+1e-8)+mean.
+__device__ __forceinline__ int32_t snap_one(float x, float mean, float scale, int mode) {
+  float e;
+  if ((mode & 3) == VAEX_SNAP_EXPM1) {
+    const float v = __fadd_rn(__fmul_rn(x, scale), mean);
+    e = (float)expm1((double)v);
+  } else {
+    const float v = __fadd_rn(__fmul_rn(x, __fadd_rn(scale, 1e-8f)), mean);
+    e = (float)exp((double)v);
+  }
+  const float r = rintf(e);
+  int32_t q = (r >= -2147483648.f && r < 2147483648.f) ? (int32_t)r : INT32_MIN;
+  return q < 1 ? 1 : q;
+}
+
+__device__ __forceinline__ int nearest_divisor(int rem, int v, int cap) {
+  int bound = rem;
+  if (cap > 0 && cap < bound) bound = cap;
+  if (v > bound) v = bound;
+  if (v < 1) v = 1;
+  for (int delta = 0;; ++delta) {
+    const int lo = v - delta, hi = v + delta;
+    if (lo >= 1 && rem % lo == 0) return lo;   // ties -> smaller
+    if (hi <= bound && rem % hi == 0) return hi;
+  }
+}
+
+__global__ void snap_kernel(const float* __restrict__ x, int64_t n, int d, const float* __restrict__ mean,
+                            const float* __restrict__ scale, int mode, int32_t* __restrict__ out) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n * d) return;
+  const int j = (int)(e % d);
+  out[e] = snap_one(x[e], mean[j], scale[j], mode);
+}
+
+__global__ void legalise_kernel(int32_t* __restrict__ ext, int64_t n, int d,
+                                const int32_t* __restrict__ slot_extent,
+                                const uint8_t* __restrict__ slot_last, int max_innermost) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int rem = 0;
+  for (int j = 0; j < d; ++j) {
+    const int se = slot_extent[j];
+    if (se <= 0) { rem = 0; continue; }
+    if (rem == 0) rem = se;
+    const int last = slot_last[j];
+    const int q = nearest_divisor(rem, ext[i * d + j], last ? max_innermost : 0);
+    ext[i * d + j] = q;
+    rem /= q;
+    if (last) rem = 0;
+  }
+}
+
+int snap_extents(const float* x, int64_t n, int d, const float* mean, const float* scale, int mode,
+                 const int32_t* slot_extent, const uint8_t* slot_last, int max_innermost,
+                 int32_t* out, cudaStream_t st) {
+  if (n == 0) return VAEX_OK;
+  snap_kernel<<<(unsigned)cdiv(n * d, 256), 256, 0, st>>>(x, n, d, mean, scale, mode, out);
+  VAEX_LAUNCH_CHECK();
+  if (mode & VAEX_SNAP_DIVISOR) {
+    VAEX_CHECK(slot_extent && slot_last, "divisor mode needs slot tables");
+    legalise_kernel<<<(unsigned)cdiv(n, 128), 128, 0, st>>>(out, n, d, slot_extent, slot_last, max_innermost);
+    VAEX_LAUNCH_CHECK();
+  }
+  return VAEX_OK;
+}
+
+// ------------------------------------------------------------------ dropout / backward helpers
+__global__ void dropout_kernel(float* __restrict__ h, int64_t count, const uint8_t* __restrict__ mask,
+                               uint64_t seed, float p) {
+  const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t e0 = q * 4;
+  if (e0 >= count) return;
+  const float inv = 1.f / (1.f - p);
+  uint4 r = make_uint4(0, 0, 0, 0);
+  if (!mask) r = Philox(seed)((uint64_t)q, 0);
+  const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int64_t e = e0 + i;
+    if (e < count) {
+      const bool keep = mask ? mask[e] != 0 : u01(rr[i]) >= p;
+      h[e] = keep ? h[e] * inv : 0.f;
+    }
+  }
+}
+
+int dropout_apply(float* h, int64_t n, int cols, const uint8_t* mask, uint64_t seed, float p,
+                  cudaStream_t st) {
+  const int64_t count = n * cols;
+  if (count == 0) return VAEX_OK;
+  dropout_kernel<<<(unsigned)cdiv(cdiv(count, 4), 256), 256, 0, st>>>(h, count, mask, seed, p);
+  VAEX_LAUNCH_CHECK();
+  return VAEX_OK;
+}
+
+// out[n, c] = (h[n, c] > 0) ? w[c] : 0    (d cost / d pre-activation of the last hidden layer)
+__global__ void relu_mask_rowvec_kernel(const float* __restrict__ h, const float* __restrict__ w,
+                                        float* __restrict__ out, int64_t count, int cols) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e < count) out[e] = h[e] > 0.f ? w[e % cols] : 0.f;
+}
+int relu_mask_rowvec(const float* h, const float* w, float* out, int64_t n, int cols, cudaStream_t st) {
+  const int64_t count = n * cols;
+  if (count == 0) return VAEX_OK;
+  relu_mask_rowvec_kernel<<<(unsigned)cdiv(count, 256), 256, 0, st>>>(h, w, out, count, cols);
+  VAEX_LAUNCH_CHECK();
+  return VAEX_OK;
+}
+
+__global__ void axpy_kernel(float* __restrict__ z, const float* __restrict__ g, float lr, int64_t count) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e < count) z[e] = z[e] + lr * g[e];
+}
+int axpy(float* z, const float* g, float lr, int64_t count, cudaStream_t st) {
+  if (count == 0) return VAEX_OK;
+  axpy_kernel<<<(unsigned)cdiv(count, 256), 256, 0, st>>>(z, g, lr, count);
+  VAEX_LAUNCH_CHECK();
+  return VAEX_OK;
+}
+
+__global__ void row_l2norm_kernel(const float* __restrict__ g, int64_t n, int cols, float* __restrict__ out) {
+  const int64_t r = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (r >= n) return;
+  const int lane = threadIdx.x & 31;
+  float s = 0.f;
+  for (int c = lane; c < cols; c += 32) { const float v = g[r * cols + c]; s = fmaf(v, v, s); }
+#pragma unroll
+  for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane == 0) out[r] = sqrtf(s);
+}
+int row_l2norm(const float* g, int64_t n, int cols, float* out, cudaStream_t st) {
+  if (n == 0) return VAEX_OK;
+  row_l2norm_kernel<<<(unsigned)cdiv(n, 8), 256, 0, st>>>(g, n, cols, out);
+  VAEX_LAUNCH_CHECK();
+  return VAEX_OK;
+}
+
+}  // namespace vaex

@@ -1,0 +1,63 @@
+// Host-side model object behind vaex_model_t: fp32 master weights as loaded from the
+// reference state_dict, packed device images, grow-only workspaces.
+#pragma once
+#include <map>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+
+namespace vaex {
+
+struct HostTensor {
+  int rows = 0, cols = 0;
+  std::vector<float> v;
+};
+
+// fp16 K-major SWIZZLE_128B images of the two row-encoder layers for the tcgen05 kernel
+struct TcPack {
+  __half* w0 = nullptr;   // [256][K0P] as 64-wide K atoms: see segsum_tc.cu
+  __half* w1 = nullptr;   // [256][256]
+  float* b0 = nullptr;    // [256]
+  float* b1 = nullptr;    // [256]
+  int F = 0, K0P = 0;
+  bool ready = false;
+};
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+  int ensure(size_t need);
+  void release();
+  template <class T> T* as() { return reinterpret_cast<T*>(p); }
+};
+
+}  // namespace vaex
+
+struct vaex_model {
+  int kind = 0;
+  int F = 0, H = 0, L = 0, D = 0, PH = 0;
+  int use_norm = 0, add_sigmoid = 0;
+  bool packed = false;
+  std::map<std::string, vaex::HostTensor> host;
+  std::map<std::string, float*> dev;   // packed fp32 device tensors, by name
+  vaex::TcPack tc;
+  vaex::DevBuf ws[6];                  // activations / staging
+  vaex::DevBuf topk_ws;
+  struct HostSlot { float* feats = nullptr; int32_t* off = nullptr; float* scores = nullptr; size_t rows = 0, progs = 0; };
+  HostSlot slots[2];                   // device staging of vaex_segsum_mlp_predict_host
+  cudaStream_t copy_streams[2] = {nullptr, nullptr};
+  cudaEvent_t events[4] = {nullptr, nullptr, nullptr, nullptr};
+
+  const float* w(const std::string& name) const {
+    auto it = dev.find(name);
+    return it == dev.end() ? nullptr : it->second;
+  }
+};
+
+namespace vaex {
+// segsum_tc.cu
+int tc_pack(vaex_model* m, const std::vector<float>& w0_folded, cudaStream_t st);
+int segsum_tc_encode(vaex_model* m, const float* feats, const int32_t* off, int64_t n_programs,
+                     int64_t n_rows, float* segsum, uint8_t* valid, cudaStream_t st);
+}  // namespace vaex

@@ -1,0 +1,363 @@
+"""Drop-in mirror of the TenSet MLP cost model's inference interface
+(reference: python/tvm/auto_scheduler/cost_model/mlp_model.py).
+
+Same class names, constructor arguments, attribute names, state_dict keys and pickle tuple as
+the reference; the bodies hand device pointers to the hand-written sm_100a kernels behind
+libvaex_b200.so.  Nothing here computes on the CPU: without the library or a CUDA device the
+calls raise.
+
+  SegmentDataLoader   mlp_model.py:26-144   -> flatten_features() + on-device offsets
+  SegmentSumMLPModule mlp_model.py:147-221  -> vaex_segsum_mlp_forward
+  MLPModelInternal    mlp_model.py:340-804  -> predict / save / load (fit_*: next round)
+  MLPModel            mlp_model.py:814-860  -> predict with the -inf rule (:842-844)
+"""
+import io
+import logging
+import pickle
+
+import numpy as np
+import torch
+
+from . import _lib
+from .dataset import Dataset, LearningTask
+
+logger = logging.getLogger("auto_scheduler")
+
+
+def get_workload_embedding(workload_key):
+    """xgb_model.py:79-87: keyword one-hot (9 wide) over the printed ComputeDAG of the
+    workload.  Printing the DAG needs TVM; without it the tags are matched on the key itself
+    (all-zero for hashed keys, which is what the synthetic configs use)."""
+    tags = ['max', 'min', 'add', 'Conv2dOutput', 'conv2d_winograd', 'DepthwiseConv2d', 'dense', 'softmax', 'compute(b, i, j)']
+    try:
+        from tvm.auto_scheduler.compute_dag import ComputeDAG
+        from tvm.auto_scheduler.workload_registry import workload_key_to_tensors
+        dag_str = str(ComputeDAG(workload_key_to_tensors(workload_key)))
+    except Exception:
+        dag_str = str(workload_key)
+    vec = [0] * len(tags)
+    for i, t in enumerate(tags):
+        if t in dag_str:
+            vec[i] = 1
+    return np.array(vec, dtype=np.float32)
+
+
+def flatten_features(features, task_embedding=None):
+    """SegmentDataLoader.__init__ (mlp_model.py:47-92) without the per-row Python loop:
+    object array of [S_i, F] -> (float32 [sum S, F(+E)], int32 sizes[N])."""
+    n = len(features)
+    sizes = np.fromiter((len(r) for r in features), dtype=np.int32, count=n)
+    if n == 0:
+        return np.zeros((0, 0), np.float32), sizes
+    flat = np.concatenate([np.asarray(r, dtype=np.float32) for r in features], axis=0)
+    if task_embedding is not None:
+        emb = np.broadcast_to(np.asarray(task_embedding, np.float32), (flat.shape[0], len(task_embedding)))
+        flat = np.concatenate([flat, emb], axis=1)
+    return np.ascontiguousarray(flat, dtype=np.float32), sizes
+
+
+class SegmentDataLoader:
+    """Inference-side mirror of mlp_model.py:26-144: same constructor, `features`,
+    `segment_sizes`, `normalize`, iteration in batches -- but batches are views of one
+    device-resident tensor (no per-batch gather / H2D)."""
+
+    def __init__(self, dataset, batch_size, device, use_workload_embedding=True, use_target_embedding=False,
+                 target_id_dict={}, fea_norm_vec=None, shuffle=False):
+        self.device = device
+        self.shuffle = shuffle
+        self.batch_size = batch_size
+        flats, sizes, labels = [], [], []
+        for task in dataset.features:
+            emb = None
+            if use_workload_embedding or use_target_embedding:
+                emb = np.zeros(10 if use_workload_embedding else 0, dtype=np.float32)
+                if use_workload_embedding:
+                    emb[:9] = get_workload_embedding(task.workload_key)
+                if use_target_embedding:
+                    tid = target_id_dict.get(str(task.target), np.random.randint(0, max(len(target_id_dict), 1)))
+                    emb[9 + tid] = 1.0
+            f, s = flatten_features(dataset.features[task], emb)
+            flats.append(f)
+            sizes.append(s)
+            thr = dataset.throughputs[task]
+            labels.append(np.zeros(len(s), np.float32) if thr is None else np.asarray(thr, np.float32))
+        self.segment_sizes = torch.from_numpy(np.concatenate(sizes) if sizes else np.zeros(0, np.int32))
+        self.labels = torch.from_numpy(np.concatenate(labels) if labels else np.zeros(0, np.float32))
+        self.number = len(self.segment_sizes)
+        self.features = torch.from_numpy(np.concatenate(flats, axis=0)) if flats else torch.zeros(0, 0)
+        if fea_norm_vec is not None:
+            self.normalize(fea_norm_vec)
+        self.feature_offsets = (torch.cumsum(self.segment_sizes, 0, dtype=torch.int32) - self.segment_sizes).numpy()
+        self.iter_order = self.pointer = None
+
+    def normalize(self, norm_vector=None):
+        if norm_vector is None:
+            mx = self.features.max(dim=0).values
+            norm_vector = torch.where(mx > 0, mx, torch.ones_like(mx))
+        self.features /= norm_vector
+        return norm_vector
+
+    def __iter__(self):
+        if self.shuffle:
+            raise NotImplementedError("shuffled (training) iteration is not part of the inference path yet")
+        self.pointer = 0
+        return self
+
+    def __next__(self):
+        if self.pointer >= self.number:
+            raise StopIteration
+        s, e = self.pointer, min(self.pointer + self.batch_size, self.number)
+        self.pointer = e
+        r0 = int(self.feature_offsets[s])
+        r1 = int(self.feature_offsets[e - 1] + self.segment_sizes[e - 1])
+        return (self.segment_sizes[s:e].to(self.device), self.features[r0:r1].to(self.device),
+                self.labels[s:e].to(self.device))
+
+    def __len__(self):
+        return self.number
+
+
+class SegmentSumMLPModule(torch.nn.Module):
+    """mlp_model.py:147-221.  Parameters live in the same nn.Linear modules (identical
+    state_dict keys, so reference pickles / checkpoints load); forward() runs the fused
+    tcgen05 row-encoder + segment-sum kernel and the residual head on the GPU."""
+
+    def __init__(self, in_dim, hidden_dim, out_dim, use_norm=False, add_sigmoid=False):
+        super().__init__()
+        assert out_dim == 1, "the cost model has a scalar output"
+        self.segment_encoder = torch.nn.Sequential(
+            torch.nn.Linear(in_dim, hidden_dim), torch.nn.ReLU(),
+            torch.nn.Linear(hidden_dim, hidden_dim), torch.nn.ReLU())
+        self.add_sigmoid = add_sigmoid
+        self.norm = torch.nn.BatchNorm1d(hidden_dim) if use_norm else torch.nn.Identity()
+        self.l0 = torch.nn.Sequential(torch.nn.Linear(hidden_dim, hidden_dim), torch.nn.ReLU())
+        self.l1 = torch.nn.Sequential(torch.nn.Linear(hidden_dim, hidden_dim), torch.nn.ReLU())
+        self.decoder = torch.nn.Linear(hidden_dim, out_dim)
+        self._in_dim, self._hidden = in_dim, hidden_dim
+        self._packed = None   # (_lib.Model, version key)
+
+    def freeze_for_fine_tuning(self):
+        for x in self.segment_encoder.parameters():
+            x.requires_grad_(False)
+
+    # -- packing ---------------------------------------------------------------------------
+    def _version_key(self, norm_vec):
+        key = tuple((id(p), p._version) for p in self.state_dict(keep_vars=True).values())
+        nk = None if norm_vec is None else (id(norm_vec), getattr(norm_vec, "_version", 0))
+        return key, nk
+
+    def packed(self, fea_norm_vec=None):
+        """Returns the packed kernel-side model (re-packed when weights / norm vector change)."""
+        # older pickles made by the reference class do not carry the private attributes
+        in_dim = self.segment_encoder[0].in_features
+        hidden = self.segment_encoder[0].out_features
+        key = self._version_key(fea_norm_vec)
+        cached = getattr(self, "_packed", None)
+        if cached is not None and cached[1] == key:
+            return cached[0]
+        use_norm = isinstance(self.norm, torch.nn.BatchNorm1d)
+        m = _lib.Model(_lib.KIND_SEGSUM_MLP, [in_dim, hidden, int(use_norm), int(bool(self.add_sigmoid))])
+        m.load_state(self.state_dict(), fea_norm_vec)
+        self._packed = (m, key)
+        return m
+
+    def __getstate__(self):
+        d = self.__dict__.copy()
+        d["_packed"] = None
+        return d
+
+    # -- forward ---------------------------------------------------------------------------
+    def forward(self, segment_sizes, features, params=None, flags=0, fea_norm_vec=None):
+        if self.training and torch.is_grad_enabled():
+            raise NotImplementedError("training through the CUDA path lands with the backward kernels")
+        if not features.is_cuda:
+            raise _lib.VaexError("SegmentSumMLPModule.forward needs CUDA tensors (no CPU fallback)")
+        lib = _lib.load()
+        m = self.packed(fea_norm_vec)
+        feats = features.detach().contiguous().float()
+        sizes = segment_sizes.detach().to(device=feats.device, dtype=torch.int32).contiguous()
+        n = sizes.shape[0]
+        offsets = torch.empty(n + 1, dtype=torch.int32, device=feats.device)
+        scores = torch.empty(n, dtype=torch.float32, device=feats.device)
+        st = _lib.stream_ptr()
+        _lib.check(lib.vaex_segment_offsets(_lib.ptr(sizes), n, _lib.ptr(offsets), st))
+        _lib.check(lib.vaex_segsum_mlp_forward(m.h, _lib.ptr(feats), _lib.ptr(offsets), n, feats.shape[0],
+                                                _lib.ptr(scores), flags, st))
+        return scores.squeeze()
+
+
+def make_net(params):
+    if params["type"] == "SegmentSumMLP":
+        return SegmentSumMLPModule(params["in_dim"], params["hidden_dim"], params["out_dim"],
+                                   add_sigmoid=params["add_sigmoid"])
+    raise ValueError("Invalid type: " + params["type"] + " (only SegmentSumMLP is on the B200 path)")
+
+
+class MLPModelInternal:
+    """mlp_model.py:340-804: same hyper-parameter attributes and predict/save/load behaviour."""
+
+    def __init__(self, device=None, few_shot_learning="base_only", use_workload_embedding=True,
+                 use_target_embedding=False, loss_type='lambdaRankLoss'):
+        if device is None:
+            device = 'cuda:0'
+        if not str(device).startswith('cuda'):
+            raise _lib.VaexError("vaex_b200 runs on CUDA devices only (no CPU fallback)")
+        self.net_params = {"type": "SegmentSumMLP", "in_dim": 164 + (10 if use_workload_embedding else 0),
+                           "hidden_dim": 256, "out_dim": 1}
+        self.target_id_dict = {}
+        self.loss_type = loss_type
+        self.n_epoch, self.lr = 100, 7e-4
+        if loss_type == 'rmse':
+            self.net_params['add_sigmoid'] = True
+        elif loss_type == 'rankNetLoss':
+            self.net_params['add_sigmoid'] = False
+            self.n_epoch = 30
+        elif loss_type == 'lambdaRankLoss':
+            self.net_params['add_sigmoid'] = False
+            self.n_epoch = 50
+        elif loss_type == 'listNetLoss':
+            self.net_params['add_sigmoid'] = False
+            self.lr, self.n_epoch = 9e-4, 50
+        else:
+            raise ValueError("Invalid loss type: " + loss_type)
+        self.grad_clip = 0.5
+        self.few_shot_learning = few_shot_learning
+        self.fea_norm_vec = None
+        self.use_workload_embedding = use_workload_embedding
+        self.use_target_embedding = use_target_embedding
+        self.batch_size, self.infer_batch_size = 512, 4096
+        self.wd = 1e-6
+        self.device = device
+        self.print_per_epoches = 5
+        self.fine_tune_lr, self.fine_tune_batch_size = 4e-2, 512
+        self.fine_tune_num_steps, self.fine_tune_wd = 10, 0
+        self.base_model = None
+        self.local_model = {}
+
+    def register_new_task(self, task):
+        target = str(task.target)
+        if target not in self.target_id_dict:
+            self.target_id_dict[target] = len(self.target_id_dict)
+
+    def fit_base(self, train_set, valid_set=None, valid_train_set=None):
+        raise NotImplementedError("training (mlp_model.py:512-600) is the next hot-path row (SURVEY 8a a4)")
+
+    def fit_local(self, train_set, valid_set=None):
+        if self.few_shot_learning == "base_only":
+            return
+        raise NotImplementedError("training (mlp_model.py:456-489) is the next hot-path row")
+
+    # -- inference ---------------------------------------------------------------------------
+    def _task_embedding(self, task):
+        if not (self.use_workload_embedding or self.use_target_embedding):
+            return None
+        emb = np.zeros(10 if self.use_workload_embedding else 0, dtype=np.float32)
+        if self.use_workload_embedding:
+            emb[:9] = get_workload_embedding(task.workload_key)
+        if self.use_target_embedding:
+            tid = self.target_id_dict.get(str(task.target), np.random.randint(0, max(len(self.target_id_dict), 1)))
+            emb[9 + tid] = 1.0
+        return emb
+
+    def _predict_a_task(self, model, task, features, flags=0):
+        """mlp_model.py:669-681.  One flatten on the host, then the C-ABI host call (pinned
+        staging + chunked H2D overlapped with the kernels)."""
+        if model is None:
+            return np.zeros(len(features), dtype=np.float32)
+        flat, sizes = flatten_features(features, self._task_embedding(task))
+        return predict_flat(model, flat, sizes, self.fea_norm_vec, flags)
+
+    def _predict_a_dataset(self, model, dataset, flags=0):
+        return {task: self._predict_a_task(model, task, feats, flags) for task, feats in dataset.features.items()}
+
+    def predict(self, dataset):
+        fsl = self.few_shot_learning
+        if fsl in ["base_only", "fine_tune_mix_task", "fine_tune_per_task", "MAML"]:
+            return self._predict_a_dataset(self.base_model, dataset)
+        if fsl in ["local_only_mix_task", "local_only_per_task"]:
+            return {t: self._predict_a_task(self.local_model[t], t, dataset.features[t]) for t in dataset.tasks()}
+        if fsl in ["plus_mix_task", "plus_per_task"]:
+            base = self._predict_a_dataset(self.base_model, dataset)
+            ret = {}
+            for t in dataset.tasks():
+                if t not in self.local_model and fsl == "plus_mix_task":
+                    self.local_model[t] = list(self.local_model.values())[0]
+                ret[t] = base[t] + self._predict_a_task(self.local_model[t], t, dataset.features[t])
+            return ret
+        raise ValueError("Invalid few show learing: " + fsl)
+
+    # -- checkpoints (same pickle tuple as mlp_model.py:788-804) -------------------------------
+    def load(self, filename):
+        self.base_model, self.local_model, self.few_shot_learning, self.fea_norm_vec = \
+            _RefUnpickler(open(filename, 'rb')).load()
+
+    def save(self, filename):
+        base = self.base_model.cpu() if self.base_model else None
+        local = self.local_model.cpu() if self.local_model and hasattr(self.local_model, "cpu") else self.local_model
+        pickle.dump((base, local, self.few_shot_learning, self.fea_norm_vec), open(filename, 'wb'))
+
+
+class _RefUnpickler(pickle.Unpickler):
+    """Loads pickles written by the reference (class path tvm.auto_scheduler.cost_model.
+    mlp_model.*) onto this module's classes, storages mapped to CPU (mlp_model.py:806-811)."""
+
+    def find_class(self, module, name):
+        if module == 'torch.storage' and name == '_load_from_bytes':
+            return lambda b: torch.load(io.BytesIO(b), map_location='cpu', weights_only=False)
+        if module.endswith("cost_model.mlp_model") and name in globals():
+            return globals()[name]
+        return super().find_class(module, name)
+
+
+def predict_flat(model, flat, sizes, fea_norm_vec=None, flags=0):
+    """Host fp32 [rows, F] + int32 sizes -> np.float32[N] through vaex_segsum_mlp_predict_host."""
+    lib = _lib.load()
+    m = model.packed(fea_norm_vec)
+    flat = np.ascontiguousarray(flat, dtype=np.float32)
+    sizes = np.ascontiguousarray(sizes, dtype=np.int32)
+    out = np.empty(len(sizes), dtype=np.float32)
+    _lib.check(lib.vaex_segsum_mlp_predict_host(m.h, flat.ctypes.data, sizes.ctypes.data, len(sizes),
+                                                 flat.shape[0], out.ctypes.data, flags))
+    return out
+
+
+class MLPModel:
+    """mlp_model.py:814-860.  `predict(task, states)` needs TVM's feature extractor
+    (get_per_store_features_from_states); `predict_features(task, features)` is the same call
+    from the point where the 164-d rows exist -- the boundary of this build."""
+
+    def __init__(self, few_shot_learning="base_only", disable_update=False):
+        self.disable_update = disable_update
+        self.model = MLPModelInternal(few_shot_learning=few_shot_learning)
+        self.dataset = Dataset()
+
+    def update(self, inputs, results):
+        if self.disable_update or len(inputs) <= 0:
+            return
+        raise NotImplementedError("online re-fit needs the training row (next round)")
+
+    def predict_features(self, task, features):
+        learning_task = LearningTask(task.workload_key, str(task.target))
+        if self.model is not None:
+            ret = self.model._predict_a_task(self.model.base_model, learning_task, features,
+                                             flags=_lib.F_MASK_INVALID if self.model.base_model is not None else 0)
+            if self.model.base_model is None:
+                for idx, feature in enumerate(features):
+                    if feature.min() == feature.max() == 0:
+                        ret[idx] = float('-inf')
+        else:
+            ret = np.random.uniform(0, 1, (len(features),))
+        return ret
+
+    def predict(self, task, states):
+        from tvm.auto_scheduler.feature import get_per_store_features_from_states
+        return self.predict_features(task, get_per_store_features_from_states(states, task))
+
+    def save(self, file_name):
+        self.model.save(file_name)
+
+    def load(self, file_name):
+        if self.model is None:
+            self.model = MLPModelInternal()
+        self.model.load(file_name)
+        self.num_warmup_sample = -1

@@ -1,0 +1,137 @@
+"""Candidate selection of the active-learning loop -- mirror of
+scripts/pre_experiments/model_myself/utils/select.py (same function names / signatures /
+return values).  Scores stay on the GPU; every top-k is the library's deterministic radix
+select (score desc, index asc) restricted by a device mask instead of
+np.argsort(pred[list(set)])[-k:] on the host (select.py:54-81)."""
+import numpy as np
+import torch
+
+from . import vae_model
+
+
+def _mask_from(indices, n, device):
+    m = torch.zeros(n, dtype=torch.uint8, device=device)
+    if len(indices):
+        m[torch.as_tensor(np.fromiter(indices, dtype=np.int64, count=len(indices)), device=device)] = 1
+    return m
+
+
+def random_select_indices(remaining_indices, select_size, rng=np.random.default_rng(42)):
+    """select.py:31-40."""
+    if select_size == 0:
+        return np.array([], dtype=np.int64), remaining_indices
+    random_indices = rng.choice(list(remaining_indices), size=select_size, replace=False)
+    remaining_indices.difference_update(set(random_indices.tolist()))
+    return random_indices, remaining_indices
+
+
+def util_select_topk(predictions, remaining_indices, num_select):
+    """select.py:54-81: indices of the num_select largest predictions among remaining_indices
+    (returned in ascending score order like argsort()[-k:]); updates the set."""
+    pred = predictions if isinstance(predictions, torch.Tensor) else torch.as_tensor(np.asarray(predictions, np.float32))
+    if not pred.is_cuda:
+        pred = pred.cuda()
+    k = min(num_select, len(remaining_indices))
+    _, idx = vae_model.topk(pred.float(), k, _mask_from(remaining_indices, pred.shape[0], pred.device))
+    selected = idx.flip(0).cpu().numpy().astype(np.int64)
+    remaining_indices.difference_update(selected.tolist())
+    return selected, remaining_indices
+
+
+def select_topk_cost(cost_pred, remaining_indices, num_select):
+    """select.py:88-108."""
+    if num_select == 0:
+        return np.array([], dtype=np.int64), remaining_indices
+    return util_select_topk(cost_pred.detach() if isinstance(cost_pred, torch.Tensor) else cost_pred,
+                            remaining_indices, num_select)
+
+
+def select_topk_z_grad(z, cost_pred, remaining_indices, num_select):
+    """select.py:111-148: top-k of ||d cost.sum()/dz||_2.  cost_pred must come from
+    model.predict_cost(z) with z.requires_grad (its backward is the fused CUDA gradient)."""
+    if num_select == 0:
+        return np.array([], dtype=np.int64), remaining_indices
+    z_grad = torch.autograd.grad(outputs=cost_pred.sum(), inputs=z, retain_graph=False, create_graph=False)[0]
+    norm = torch.norm(z_grad, dim=1)
+    remaining_indices = set(remaining_indices)
+    return util_select_topk(norm, remaining_indices, num_select)
+
+
+def select_topk_uncertainty(model, input_tensor, remaining_indices, num_select, T_mc=10):
+    """select.py:151-182: top-k of the MC-dropout variance."""
+    if num_select == 0:
+        return np.array([], dtype=np.int64), remaining_indices
+    with torch.no_grad():
+        _, mc_var = model.mc_predict(input_tensor, T=T_mc)
+    return util_select_topk(mc_var, remaining_indices, num_select)
+
+
+def select_topk_latent_diversity(z, candidate_indices, used_indices, select_n_div, chunk_size=1024, eps=1e-12):
+    """select.py:185-270: k-center greedy on L2-normalised latents, centres = used_indices.
+    M <= 320 candidates: a handful of tiny device ops (SURVEY 8f row n2 moves it into one CTA)."""
+    if select_n_div == 0 or len(candidate_indices) == 0:
+        return np.array([], dtype=np.int64), candidate_indices
+    with torch.no_grad():
+        zn = z.detach() / (z.detach().norm(dim=1, keepdim=True) + eps)
+        cand = np.array(list(candidate_indices), dtype=np.int64)
+        k = min(select_n_div, len(cand))
+        zc = zn[torch.from_numpy(cand).to(z.device)]
+        used = np.array(list(used_indices), dtype=np.int64)
+        if len(used):
+            min_d = torch.cdist(zc, zn[torch.from_numpy(used).to(z.device)]).min(dim=1).values
+        else:
+            min_d = torch.full((len(cand),), float("inf"), device=z.device)
+        selected = []
+        for _ in range(k):
+            j = int(torch.argmax(min_d).item())
+            selected.append(cand[j])
+            min_d[j] = -float("inf")
+            min_d = torch.minimum(min_d, torch.cdist(zc, zc[j:j + 1]).squeeze(1))
+    diverse = np.array(selected, dtype=np.int64)
+    candidate_indices = set(candidate_indices)
+    candidate_indices.difference_update(diverse.tolist())
+    return diverse, candidate_indices
+
+
+def select_programs(model, input_data_scaled, used_indices, remaining_indices, num_select=64, T_mc=10,
+                    uncertainty_topk=128, w_cost=0.5, w_unc=0.3, w_div=0.2, grad_num=2, rand_num=0,
+                    rng=np.random.default_rng(42), device=torch.device("cuda"), topk_factor=5):
+    """select.py:277-376, same budget arithmetic and stage order."""
+    total = num_select
+    budget = total - grad_num - rand_num
+    if num_select == 0 and rand_num > 0:
+        return random_select_indices(remaining_indices, rand_num, rng=rng)
+    n_cost, n_unc, n_div = int(budget * w_cost), int(budget * w_unc), int(budget * w_div)
+    s = n_cost + n_unc + n_div
+    if s < budget:
+        n_cost += budget - s
+    x = torch.as_tensor(input_data_scaled, dtype=torch.float32, device=device)
+    model.eval()
+    with torch.no_grad():
+        z, _ = model.encode(x)
+    z = z.detach().requires_grad_(True)
+    cost_pred = model.predict_cost(z).view(-1)
+    k_pref = min(len(remaining_indices), total * topk_factor)
+    _, pool = vae_model.topk(cost_pred.detach(), k_pref, _mask_from(remaining_indices, x.shape[0], x.device))
+    candidate = set(pool.cpu().numpy().tolist())
+    currently_used = set()
+    sel, candidate = select_topk_cost(cost_pred, candidate, n_cost)
+    currently_used.update(sel.tolist())
+    sel, candidate = select_topk_z_grad(z, cost_pred, candidate, grad_num)
+    currently_used.update(sel.tolist())
+    if len(used_indices) >= uncertainty_topk:
+        unc, candidate = select_topk_uncertainty(model, x, candidate, n_unc, T_mc=T_mc)
+    else:
+        pool_unc = set(remaining_indices)
+        pool_unc.difference_update(currently_used)
+        unc, _ = select_topk_uncertainty(model, x, pool_unc, n_unc, T_mc=T_mc)
+        candidate.difference_update(unc.tolist())
+    currently_used.update(unc.tolist())
+    used_local = set(used_indices)
+    used_local.update(currently_used)
+    div, _ = select_topk_latent_diversity(z, candidate, used_local, n_div)
+    currently_used.update(div.tolist())
+    remaining_indices.difference_update(currently_used)
+    rnd, remaining_indices = random_select_indices(remaining_indices, rand_num, rng=rng)
+    currently_used.update(rnd.tolist())
+    return np.array(sorted(currently_used), dtype=np.int64), remaining_indices
