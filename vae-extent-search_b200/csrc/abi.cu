@@ -197,6 +197,7 @@ int vaex_model_destroy(vaex_model_t h) {
   for (auto& kv : h->dev) cudaFree(kv.second);
   for (auto& b : h->ws) b.release();
   h->topk_ws.release();
+  h->tc_ws.release();
   if (h->tc.w0) cudaFree(h->tc.w0);
   if (h->tc.w1) cudaFree(h->tc.w1);
   if (h->tc.b0) cudaFree(h->tc.b0);

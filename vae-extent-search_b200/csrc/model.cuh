@@ -44,6 +44,7 @@ struct vaex_model {
   vaex::TcPack tc;
   vaex::DevBuf ws[6];                  // activations / staging
   vaex::DevBuf topk_ws;
+  vaex::DevBuf tc_ws;                  // first_prog + rowmask of the tcgen05 kernel
   struct HostSlot { float* feats = nullptr; int32_t* off = nullptr; float* scores = nullptr; size_t rows = 0, progs = 0; };
   HostSlot slots[2];                   // device staging of vaex_segsum_mlp_predict_host
   cudaStream_t copy_streams[2] = {nullptr, nullptr};
