@@ -7,22 +7,27 @@
 // One persistent CTA pair (cluster of 2, tcgen05 cta_group::2) per two SMs; a pair tile is 256
 // feature rows (128 per CTA).  fp16 operands (11-bit significand), fp32 accumulation in TMEM.
 //
-//   layer 0:  D0[256 rows x 256 hid]  = X[256 x K0] * W0^T        A = X tile (this CTA's 128 rows)
-//             (TMEM cols 0..255)                                    B = W0 (this CTA's 128 hidden units)
-//   epi 0  :  TMEM -> +b0, ReLU, fp16 -> A1 smem (K-major, 128B swizzle)       lane = row
-//   layer 1:  D1[256 hid x 256 rows] = W1[256 x 256] * A1^T       A = W1 (this CTA's 128 hidden units)
-//             (TMEM cols 256..511)                                  B = A1 (this CTA's 128 rows)
-//   epi 1  :  TMEM -> +b1, ReLU, running sum over *columns* (= rows of the tile) cut at the
-//             program boundaries -> S.  lane = hidden unit, so the segment sum needs no
-//             shuffles or shared memory and boundaries are uniform across the CTA.
+//   layer 0:  D0[256 rows x 256 hid] = [X | 1][256 x K0] * [W0 | b0]^T   (two N=128 halves)
+//             TMEM cols 0..255           A = X tile (this CTA's 128 rows), B = this CTA's 128 hidden units
+//   epi 0  :  TMEM -> ReLU + fp16 pack (one F2FP per pair) -> A1 smem (K-major, 128B swizzle); lane = row
+//   layer 1:  D1[256 hid x 256 rows] = W1[256 x 256] * A1^T              (two K halves, as epi 0 delivers them)
+//             TMEM cols 256..511         A = W1 (this CTA's 128 hidden units), B = A1 (this CTA's 128 rows)
+//   epi 1  :  TMEM -> +b1, ReLU, sum over *columns* (= rows of the tile) between program
+//             boundaries -> S.  lane = hidden unit: no shuffles, no shared memory, boundaries are
+//             uniform across the CTA; each segment is fetched with power-of-two TMEM loads.
 //
 // Layer 1 is computed transposed on purpose: it puts the segment dimension on TMEM columns.
-// Weights stay resident in shared memory (each CTA holds half of W0 and half of W1: 112 KB),
-// X is streamed with 128-bit loads, converted to fp16 and written straight into the swizzled
-// operand layout (the fp32 -> fp16 cast rules out a direct TMA load of X).
+// Weights stay resident in shared memory (each CTA holds half of W0 and of W1: 112 KB); X is
+// streamed with 128-bit loads behind an L2 bulk prefetch, cast to fp16 and written straight into
+// the swizzled operand layout (the cast rules out a TMA tensor load of X).  b0 rides in a spare
+// K column of layer 0 (X gets a constant-1 column), so epi 0 has no bias add.
 //
-// Programs cut by a tile boundary receive two partial sums through atomicAdd on zeroed rows
-// (two addends: order-independent, so results are deterministic for S_i <= 256).
+// Warp roles (17 warps): 0-7 loader, 8 MMA issuer (leader CTA), 9-16 epilogue in two groups of
+// four (one warp per TMEM lane quarter): group g runs epi 0 for hidden half g, then epi 1 for
+// 128-row block g of the tile.  All hand-offs are mbarriers; tcgen05.commit signals MMA completion.
+//
+// Programs cut by a 128-row block boundary receive two partial sums through atomicAdd on zeroed
+// rows (two addends: order-independent, so results are deterministic for S_i <= 128).
 #include <algorithm>
 #include <vector>
 
@@ -34,7 +39,7 @@ namespace vaex {
 
 namespace tc {
 constexpr int HID = 256;
-constexpr int TILE = 128;            // rows per CTA per tile
+constexpr int TILE = 128;            // rows per CTA per tile (= rows per epi-1 block)
 constexpr int PAIR = 256;            // rows per CTA pair per tile
 constexpr int K0P = 192;             // layer-0 K padded to 3 swizzle atoms of 64 fp16
 constexpr int ATOM = 128 * 128;      // bytes of one [128 rows x 64 fp16] swizzle atom
@@ -44,29 +49,27 @@ constexpr int A0_OFF = W1_OFF + W1_BYTES, A0_BYTES = 3 * ATOM;
 constexpr int A1_OFF = A0_OFF + A0_BYTES, A1_BYTES = 4 * ATOM;
 constexpr int SMEM_TILES = A1_OFF + A1_BYTES;          // 229376
 constexpr int SMEM_DYN = SMEM_TILES + 1024;            // + slack to align the base to 1024 B
-constexpr int LOAD_WARPS = 4, MMA_WARP = 4, EPI_WARP0 = 5, EPI_WARPS = 4;
-constexpr int THREADS = 32 * (LOAD_WARPS + 1 + EPI_WARPS);   // 288
-enum { B_A0_FULL = 0, B_A0_EMPTY, B_ACC0_FULL, B_A1_FULL, B_ACC1_FULL, B_ACC1_EMPTY, B_COUNT };
+constexpr int LOAD_WARPS = 8, MMA_WARP = 8, EPI_WARP0 = 9, EPI_WARPS = 8;   // epilogue: 2 groups x 4 lane quarters
+constexpr int THREADS = 32 * (EPI_WARP0 + EPI_WARPS);   // 544
+enum { B_A0_FULL = 0, B_A0_EMPTY, B_ACC0_FULL0, B_ACC0_FULL1, B_A1_FULL0, B_A1_FULL1, B_ACC1_FULL, B_ACC1_EMPTY, B_COUNT };
 
 __host__ __device__ inline uint32_t sw128_off(int row, int k) {
   return (uint32_t)((k >> 6) * ATOM + (row >> 3) * 1024 + (row & 7) * 128 + ((((k & 63) >> 3) ^ (row & 7)) << 4) +
                     (k & 7) * 2);
 }
-__device__ __forceinline__ uint32_t pack_h2(float a, float b) {
-  a = fminf(fmaxf(a, -65504.f), 65504.f);
-  b = fminf(fmaxf(b, -65504.f), 65504.f);
-  __half2 h = __floats2half2_rn(a, b);
-  return *reinterpret_cast<uint32_t*>(&h);
+// hidden unit held by layer-0 accumulator column c (two N=128 halves, 64 units per CTA each)
+__host__ __device__ inline int hidden_of_col(int c) {
+  const int h = c >> 7, j = c & 127;
+  return j < 64 ? 64 * h + j : 128 + 64 * h + (j - 64);
 }
 }  // namespace tc
 
 struct TcParams {
   const float* feats;          // [n_rows, F]
   const int32_t* off;          // [P + 1]
-  const int32_t* first_prog;   // [T] program holding the first row of pair tile t
-  const __half* w0;            // [2][W0_BYTES/2] swizzled images per CTA rank
-  const __half* w1;            // [2][W1_BYTES/2]
-  const float* b0;             // [256]
+  const int32_t* first_prog;   // [2T] program holding the first row of 128-row block b
+  const __half* w0;            // [2][W0_BYTES/2] swizzled images per CTA rank ([W0 | b0])
+  const __half* w1;            // [2][W1_BYTES/2] (K permuted to the layer-0 column order)
   const float* b1;             // [256]
   float* out;                  // [P, 256]
   uint32_t* rowmask;           // [T * 8] bit r: feature row has a non-zero
@@ -75,53 +78,111 @@ struct TcParams {
 };
 
 // ---------------------------------------------------------------------------------------------
+// loader: the CTA's 128 x F fp32 half tile is one contiguous range of global memory.  Each of
+// the 8 loader warps owns 16 consecutive rows = a contiguous run of 16*U vector units (U = F/VEC)
+// and sweeps it with fully coalesced 16/8/4-byte loads, SLOTS units per lane, issued in two
+// batches so that ~45 KB per SM are in flight.  A unit is cast to fp16 and stored at its
+// swizzled (row, k) position; a ballot per slot yields the per-row "has a non-zero" bits.
 template <int VEC>
-__device__ __forceinline__ void load_convert_tile(const TcParams& p, uint8_t* A0, int64_t row0, int warp, int lane,
-                                                  uint32_t& nzmask) {
+struct Vec;
+template <> struct Vec<4> { float4 v; __device__ void ld(const float* p) { v = ptx::ldg_stream_f4(p); }
+  __device__ bool nz() const { return ((__float_as_uint(v.x) | __float_as_uint(v.y) | __float_as_uint(v.z) | __float_as_uint(v.w)) << 1) != 0; }
+  __device__ void zero() { v = make_float4(0.f, 0.f, 0.f, 0.f); }
+  __device__ void st(uint32_t a) const { ptx::sts_v2(a, ptx::cvt_h2_sat(v.x, v.y), ptx::cvt_h2_sat(v.z, v.w)); } };
+template <> struct Vec<2> { float2 v; __device__ void ld(const float* p) { v = ptx::ldg_stream_f2(p); }
+  __device__ bool nz() const { return ((__float_as_uint(v.x) | __float_as_uint(v.y)) << 1) != 0; }
+  __device__ void zero() { v = make_float2(0.f, 0.f); }
+  __device__ void st(uint32_t a) const { ptx::sts_b32(a, ptx::cvt_h2_sat(v.x, v.y)); } };
+template <> struct Vec<1> { float v; __device__ void ld(const float* p) { v = __ldg(p); }
+  __device__ bool nz() const { return (__float_as_uint(v) << 1) != 0; }
+  __device__ void zero() { v = 0.f; }
+  __device__ void st(uint32_t a) const { ptx::sts_b16(a, ptx::cvt_h2_sat(v, 0.f)); } };
+
+template <int VEC>
+__device__ __forceinline__ uint32_t load_convert_rows(const TcParams& p, uint32_t A0, int64_t row0, int wrow0, int lane) {
   using namespace tc;
-  constexpr int RB = 8;                       // rows in flight per lane
-  const int U = p.F / VEC;                    // vector units per row
-  constexpr int UU = (K0P / VEC + 31) / 32;   // units per lane per row
-  nzmask = 0;
-  for (int rb = 0; rb < 32; rb += RB) {
-    float v[RB][UU][VEC];
+  constexpr int ROWS = TILE / LOAD_WARPS;             // 16 rows per warp
+  constexpr int MAXU = (K0P - 1) / VEC;               // F <= K0P - 1
+  constexpr int SLOTS = (ROWS * MAXU + 31) / 32;
+  constexpr int BATCH = VEC == 4 ? 12 : 16;           // slots in flight per lane
+  const int U = p.F / VEC;
+  const int total = ROWS * U;                         // units owned by this warp
+  const int64_t grow0 = row0 + wrow0;                 // first global row of this warp
+  const int64_t valid_rows = min((int64_t)ROWS, p.n_rows - grow0);
+  const int valid_units = valid_rows > 0 ? (int)valid_rows * U : 0;
+  const float* src = p.feats + grow0 * p.F;
+  uint32_t nzmask = 0;
+  int row = lane / U, col = lane - row * U;           // (row, unit) of this lane's unit in slot 0
+  int urow = 0, ucol = 0;                             // (row, unit) of lane 0's unit (warp-uniform)
+  for (int s0 = 0; s0 * 32 < total; s0 += BATCH) {
+    Vec<VEC> x[BATCH];
 #pragma unroll
-    for (int i = 0; i < RB; ++i) {
-      const int64_t row = row0 + warp * 32 + rb + i;
-      const bool ok = row < p.n_rows;
-      const float* src = p.feats + row * p.F;
-#pragma unroll
-      for (int uu = 0; uu < UU; ++uu) {
-        const int u = lane + 32 * uu;
-        if (ok && u < U) {
-          if (VEC == 4) { float4 t = ptx::ldg_stream_f4(src + u * 4); v[i][uu][0] = t.x; v[i][uu][1] = t.y; v[i][uu][2 % VEC] = t.z; v[i][uu][3 % VEC] = t.w; }
-          else if (VEC == 2) { float2 t = ptx::ldg_stream_f2(src + u * 2); v[i][uu][0] = t.x; v[i][uu][1 % VEC] = t.y; }
-          else { v[i][uu][0] = __ldg(src + u); }
-        } else {
-#pragma unroll
-          for (int e = 0; e < VEC; ++e) v[i][uu][e] = 0.f;
-        }
-      }
+    for (int j = 0; j < BATCH; ++j) {
+      const int idx = (s0 + j) * 32 + lane;
+      if (j < SLOTS && idx < valid_units) x[j].ld(src + (size_t)idx * VEC); else x[j].zero();
     }
 #pragma unroll
-    for (int i = 0; i < RB; ++i) {
-      const int r = warp * 32 + rb + i;       // row inside this CTA's half tile
-      bool nz = false;
-#pragma unroll
-      for (int uu = 0; uu < UU; ++uu) {
-        const int u = lane + 32 * uu;
-#pragma unroll
-        for (int e = 0; e < VEC; ++e) nz |= (v[i][uu][e] != 0.f);
-        if (u < U) {
-          uint8_t* dst = A0 + sw128_off(r, u * VEC);
-          if (VEC == 4) *reinterpret_cast<uint2*>(dst) = make_uint2(pack_h2(v[i][uu][0], v[i][uu][1]), pack_h2(v[i][uu][2 % VEC], v[i][uu][3 % VEC]));
-          else if (VEC == 2) *reinterpret_cast<uint32_t*>(dst) = pack_h2(v[i][uu][0], v[i][uu][1 % VEC]);
-          else *reinterpret_cast<__half*>(dst) = __float2half_rn(fminf(fmaxf(v[i][uu][0], -65504.f), 65504.f));
+    for (int j = 0; j < BATCH; ++j) {
+      const int base = (s0 + j) * 32;
+      if (j < SLOTS && base < total) {
+        if (base + lane < total) x[j].st(A0 + sw128_off(wrow0 + row, col * VEC));
+        const uint32_t bal = __ballot_sync(0xffffffffu, x[j].nz());
+        // rows touched by units [base, base+32): uniform scalar walk (1-2 rows when U >= 32)
+        int r = urow, lo = 0, rem = U - ucol;
+        while (lo < 32 && r < ROWS) {
+          const int hi = min(32, lo + rem);
+          const uint32_t m = (hi >= 32 ? 0xffffffffu : ((1u << hi) - 1u)) & ~((1u << lo) - 1u);
+          if (bal & m) nzmask |= 1u << r;
+          lo = hi;
+          rem = U;
+          ++r;
         }
+        col += 32;
+        while (col >= U) { col -= U; ++row; }
+        ucol += 32;
+        while (ucol >= U) { ucol -= U; ++urow; }
       }
-      if (__any_sync(0xffffffffu, nz)) nzmask |= 1u << (rb + i);
     }
   }
+  return nzmask;
+}
+
+template <int N>
+__device__ __forceinline__ float relu_sum(const uint32_t (&v)[N], float b1) {
+  float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+  for (int j = 0; j < N; j += 2) {
+    a0 += fmaxf(__uint_as_float(v[j]) + b1, 0.f);
+    if (j + 1 < N) a1 += fmaxf(__uint_as_float(v[j + 1]) + b1, 0.f);
+  }
+  return a0 + a1;
+}
+
+// sum_{c in [c0, c0+n)} relu(acc1[lane, c] + b1): the segment is fetched with x32 loads plus one
+// power-of-two load per set bit of the remainder, all issued before a single wait.
+__device__ __forceinline__ float segment_relu_sum(uint32_t taddr, int n, float b1) {
+  float acc = 0.f;
+  while (n >= 32) {
+    uint32_t v[32];
+    ptx::tmem_ld32(taddr, v);
+    ptx::tmem_ld_wait();
+    acc += relu_sum<32>(v, b1);
+    taddr += 32;
+    n -= 32;
+  }
+  uint32_t v16[16], v8[8], v4[4], v2[2], v1;
+  if (n & 16) { ptx::tmem_ld16(taddr, v16); taddr += 16; }
+  if (n & 8) { ptx::tmem_ld8(taddr, v8); taddr += 8; }
+  if (n & 4) { ptx::tmem_ld4(taddr, v4); taddr += 4; }
+  if (n & 2) { ptx::tmem_ld2(taddr, v2); taddr += 2; }
+  if (n & 1) { ptx::tmem_ld1(taddr, v1); }
+  ptx::tmem_ld_wait();
+  if (n & 16) acc += relu_sum<16>(v16, b1);
+  if (n & 8) acc += relu_sum<8>(v8, b1);
+  if (n & 4) acc += relu_sum<4>(v4, b1);
+  if (n & 2) acc += relu_sum<2>(v2, b1);
+  if (n & 1) acc += fmaxf(__uint_as_float(v1) + b1, 0.f);
+  return acc;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -131,7 +192,6 @@ segsum_tc_kernel(const TcParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[B_COUNT];
   __shared__ uint32_t tmem_base_slot;
-  __shared__ float b0s[HID];
 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const uint32_t sbase = ptx::smem_u32(smem);
@@ -145,8 +205,10 @@ segsum_tc_kernel(const TcParams p) {
   if (warp == MMA_WARP && lane == 0) {
     ptx::mbar_init(bar(B_A0_FULL), 2 * LOAD_WARPS);
     ptx::mbar_init(bar(B_A0_EMPTY), 1);
-    ptx::mbar_init(bar(B_ACC0_FULL), 1);
-    ptx::mbar_init(bar(B_A1_FULL), 2 * EPI_WARPS);
+    ptx::mbar_init(bar(B_ACC0_FULL0), 1);
+    ptx::mbar_init(bar(B_ACC0_FULL1), 1);
+    ptx::mbar_init(bar(B_A1_FULL0), 2 * 4);
+    ptx::mbar_init(bar(B_A1_FULL1), 2 * 4);
     ptx::mbar_init(bar(B_ACC1_FULL), 1);
     ptx::mbar_init(bar(B_ACC1_EMPTY), 2 * EPI_WARPS);
     ptx::fence_mbar_init();
@@ -162,8 +224,10 @@ segsum_tc_kernel(const TcParams p) {
     for (int i = threadIdx.x; i < W1_BYTES / 16; i += THREADS) s1[i] = __ldg(g1 + i);
     uint4* a0 = reinterpret_cast<uint4*>(smem + A0_OFF);   // zero once: K padding columns stay 0
     for (int i = threadIdx.x; i < A0_BYTES / 16; i += THREADS) a0[i] = make_uint4(0, 0, 0, 0);
-    for (int i = threadIdx.x; i < HID; i += THREADS) b0s[i] = p.b0[i];
   }
+  __syncthreads();
+  // constant-1 column at k = F multiplies the b0 column of the W0 image (bias inside the MMA)
+  if (threadIdx.x < TILE) *reinterpret_cast<uint16_t*>(smem + A0_OFF + sw128_off(threadIdx.x, p.F)) = 0x3C00;
   ptx::fence_proxy_async();
   ptx::tc_fence_before();
   __syncthreads();
@@ -174,18 +238,28 @@ segsum_tc_kernel(const TcParams p) {
   // ---- roles ----------------------------------------------------------------------------------
   if (warp < LOAD_WARPS) {
     // ===== loader: global fp32 rows -> fp16 swizzled A0 =====
-    uint8_t* A0 = smem + A0_OFF;
+    const uint32_t A0 = sbase + A0_OFF;
+    constexpr int ROWS = TILE / LOAD_WARPS;
     const bool al16 = ((reinterpret_cast<uintptr_t>(p.feats) & 15) == 0) && (p.F % 4 == 0);
     const bool al8 = ((reinterpret_cast<uintptr_t>(p.feats) & 7) == 0) && (p.F % 2 == 0);
+    auto prefetch = [&](int t) {
+      if (!al16 || t >= p.T) return;
+      const int64_t r0 = (int64_t)t * PAIR + rank * TILE + warp * ROWS;
+      const int64_t nr = min((int64_t)ROWS, p.n_rows - r0);
+      if (nr > 0) ptx::prefetch_l2_bulk(p.feats + r0 * p.F, (uint32_t)(nr * p.F * 4));
+    };
+    if (lane == 0) prefetch(cluster + n_clusters);
     int it = 0;
     for (int t = cluster; t < p.T; t += n_clusters, ++it) {
+      if (lane == 0) prefetch(t + 2 * n_clusters);
       if (it > 0) ptx::mbar_wait(bar(B_A0_EMPTY), (it - 1) & 1);
       const int64_t row0 = (int64_t)t * PAIR + rank * TILE;
       uint32_t nzmask;
-      if (al16) load_convert_tile<4>(p, A0, row0, warp, lane, nzmask);
-      else if (al8) load_convert_tile<2>(p, A0, row0, warp, lane, nzmask);
-      else load_convert_tile<1>(p, A0, row0, warp, lane, nzmask);
-      if (lane == 0) p.rowmask[(size_t)t * 8 + rank * 4 + warp] = nzmask;
+      if (al16) nzmask = load_convert_rows<4>(p, A0, row0, warp * ROWS, lane);
+      else if (al8) nzmask = load_convert_rows<2>(p, A0, row0, warp * ROWS, lane);
+      else nzmask = load_convert_rows<1>(p, A0, row0, warp * ROWS, lane);
+      // 16 flag bits per warp: two warps share one 32-bit word of the row mask
+      if (lane == 0) reinterpret_cast<uint16_t*>(p.rowmask)[((size_t)t * 8 + rank * 4) * 2 + warp] = (uint16_t)nzmask;
       ptx::fence_proxy_async();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_cluster(bar(B_A0_FULL), 0);
@@ -193,108 +267,121 @@ segsum_tc_kernel(const TcParams p) {
   } else if (warp == MMA_WARP) {
     // ===== MMA issuer: one thread of the leader CTA =====
     if (rank == 0) {
-      const uint32_t idesc = ptx::umma_idesc_f16(256, 256);
+      const uint32_t idesc_l0 = ptx::umma_idesc_f16(256, 128), idesc_l1 = ptx::umma_idesc_f16(256, 256);
       const uint64_t dW0 = ptx::umma_desc_sw128(sbase + W0_OFF), dW1 = ptx::umma_desc_sw128(sbase + W1_OFF);
       const uint64_t dA0 = ptx::umma_desc_sw128(sbase + A0_OFF), dA1 = ptx::umma_desc_sw128(sbase + A1_OFF);
       // +32 B per K=16 step inside an atom (encoded >>4 -> +2), +ATOM per 64 columns
       auto kadv = [](int k) -> uint64_t { return (uint64_t)(((k >> 2) * ATOM + (k & 3) * 32) >> 4); };
+      constexpr uint64_t half_rows = (64 * 128) >> 4;   // B rows 64.. of each CTA's W0 half
       int it = 0;
       for (int t = cluster; t < p.T; t += n_clusters, ++it) {
         ptx::mbar_wait(bar(B_A0_FULL), it & 1);
+        ptx::fence_acq_rel_cluster();
         ptx::tc_fence_after();
         if (lane == 0) {
           for (int k = 0; k < p.k0_steps; ++k)
-            ptx::umma_f16_2cta(tmem + 0, dA0 + kadv(k), dW0 + kadv(k), idesc, k > 0);
+            ptx::umma_f16_2cta(tmem + 0, dA0 + kadv(k), dW0 + kadv(k), idesc_l0, k > 0);
+          ptx::umma_commit_2cta(bar(B_ACC0_FULL0), 3);
+          for (int k = 0; k < p.k0_steps; ++k)
+            ptx::umma_f16_2cta(tmem + 128, dA0 + kadv(k), dW0 + half_rows + kadv(k), idesc_l0, k > 0);
+          ptx::umma_commit_2cta(bar(B_ACC0_FULL1), 3);
           ptx::umma_commit_2cta(bar(B_A0_EMPTY), 3);
-          ptx::umma_commit_2cta(bar(B_ACC0_FULL), 3);
         }
         __syncwarp();
-        ptx::mbar_wait(bar(B_A1_FULL), it & 1);
         if (it > 0) ptx::mbar_wait(bar(B_ACC1_EMPTY), (it - 1) & 1);
+        ptx::mbar_wait(bar(B_A1_FULL0), it & 1);
+        ptx::fence_acq_rel_cluster();
         ptx::tc_fence_after();
         if (lane == 0) {
 #pragma unroll
-          for (int k = 0; k < HID / 16; ++k)
-            ptx::umma_f16_2cta(tmem + 256, dW1 + kadv(k), dA1 + kadv(k), idesc, k > 0);
+          for (int k = 0; k < 8; ++k) ptx::umma_f16_2cta(tmem + 256, dW1 + kadv(k), dA1 + kadv(k), idesc_l1, k > 0);
+        }
+        __syncwarp();
+        ptx::mbar_wait(bar(B_A1_FULL1), it & 1);
+        ptx::fence_acq_rel_cluster();
+        ptx::tc_fence_after();
+        if (lane == 0) {
+#pragma unroll
+          for (int k = 8; k < 16; ++k) ptx::umma_f16_2cta(tmem + 256, dW1 + kadv(k), dA1 + kadv(k), idesc_l1, 1);
           ptx::umma_commit_2cta(bar(B_ACC1_FULL), 3);
         }
         __syncwarp();
       }
     }
   } else {
-    // ===== epilogue warps =====
+    // ===== epilogue group g: epi 0 for hidden half g, then epi 1 for 128-row block g =====
     const int q = warp & 3;                       // TMEM lane quarter this warp may access
+    const int g = (warp - EPI_WARP0) >> 2;
     const uint32_t lane_base = (uint32_t)(32 * q) << 16;
     const int row = 32 * q + lane;                // epi 0: row of this CTA's half tile
-    const int hu = rank * TILE + 32 * q + lane;   // epi 1: hidden unit
+    const uint32_t a1_row = sbase + A1_OFF + (row >> 3) * 1024 + (row & 7) * 128;
+    const int sw = row & 7;
+    const int hu = rank * TILE + 32 * q + lane;   // epi 1: hidden unit of this lane
     const float b1 = p.b1[hu];
-    uint8_t* A1 = smem + A1_OFF;
-    const uint32_t a1_row = (uint32_t)((row >> 3) * 1024 + (row & 7) * 128);
     int it = 0;
     for (int t = cluster; t < p.T; t += n_clusters, ++it) {
-      // ---- epi 0 ----
-      ptx::mbar_wait(bar(B_ACC0_FULL), it & 1);
+      // ---- epi 0: acc0 columns [128g, 128g+128) -> ReLU -> fp16 -> A1 atoms 2g, 2g+1 ----
+      // (A1 is free: this warp already waited for layer 1 of the previous tile in its epi 1)
+      ptx::mbar_wait(bar(B_ACC0_FULL0 + g), it & 1);
       ptx::tc_fence_after();
 #pragma unroll 1
-      for (int c = 0; c < HID / 32; ++c) {
-        uint32_t v[32];
-        ptx::tmem_ld32(tmem + lane_base + 32 * c, v);
+      for (int cc = 2 * g; cc < 2 * g + 2; ++cc) {
+        uint32_t v[32], w[32];
+        ptx::tmem_ld32(tmem + lane_base + 64 * cc, v);
+        ptx::tmem_ld32(tmem + lane_base + 64 * cc + 32, w);
         ptx::tmem_ld_wait();
-        uint32_t h[16];
+        const uint32_t base = a1_row + cc * ATOM;
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const float x0 = fmaxf(__uint_as_float(v[2 * j]) + b0s[32 * c + 2 * j], 0.f);
-          const float x1 = fmaxf(__uint_as_float(v[2 * j + 1]) + b0s[32 * c + 2 * j + 1], 0.f);
-          h[j] = pack_h2(x0, x1);
-        }
-        // columns 32c .. 32c+31 = 4 chunks of 8 fp16 inside atom (32c / 64)
-        uint8_t* base = A1 + (c >> 1) * ATOM + a1_row;
+        for (int m = 0; m < 4; ++m)
+          ptx::sts_v4(base + ((m ^ sw) << 4),
+                      ptx::cvt_h2_relu_sat(__uint_as_float(v[8 * m]), __uint_as_float(v[8 * m + 1])),
+                      ptx::cvt_h2_relu_sat(__uint_as_float(v[8 * m + 2]), __uint_as_float(v[8 * m + 3])),
+                      ptx::cvt_h2_relu_sat(__uint_as_float(v[8 * m + 4]), __uint_as_float(v[8 * m + 5])),
+                      ptx::cvt_h2_relu_sat(__uint_as_float(v[8 * m + 6]), __uint_as_float(v[8 * m + 7])));
 #pragma unroll
-        for (int m = 0; m < 4; ++m) {
-          const int chunk = (c & 1) * 4 + m;
-          *reinterpret_cast<uint4*>(base + ((chunk ^ (row & 7)) << 4)) = make_uint4(h[4 * m], h[4 * m + 1], h[4 * m + 2], h[4 * m + 3]);
-        }
+        for (int m = 0; m < 4; ++m)
+          ptx::sts_v4(base + (((m + 4) ^ sw) << 4),
+                      ptx::cvt_h2_relu_sat(__uint_as_float(w[8 * m]), __uint_as_float(w[8 * m + 1])),
+                      ptx::cvt_h2_relu_sat(__uint_as_float(w[8 * m + 2]), __uint_as_float(w[8 * m + 3])),
+                      ptx::cvt_h2_relu_sat(__uint_as_float(w[8 * m + 4]), __uint_as_float(w[8 * m + 5])),
+                      ptx::cvt_h2_relu_sat(__uint_as_float(w[8 * m + 6]), __uint_as_float(w[8 * m + 7])));
       }
       ptx::fence_proxy_async();
       ptx::tc_fence_before();
       __syncwarp();
-      if (lane == 0) ptx::mbar_arrive_cluster(bar(B_A1_FULL), 0);
+      if (lane == 0) ptx::mbar_arrive_cluster(bar(B_A1_FULL0 + g), 0);
 
-      // ---- epi 1: segment sum over the tile's rows (TMEM columns) ----
-      const int64_t R0 = (int64_t)t * PAIR;
-      const int64_t Rend = min(R0 + (int64_t)PAIR, p.n_rows);
-      int prog = p.first_prog[t];
-      int batch_base = prog;
-      int boff = p.off[min(batch_base + lane, p.P)];
+      // ---- epi 1: segment sum over the 128-row block g of the tile (TMEM columns) ----
+      const int blk = 2 * t + g;
+      const int64_t Cb = (int64_t)blk * TILE;
+      const int64_t Ce = min(Cb + (int64_t)TILE, p.n_rows);
+      int prog = 0, batch_base = 0, boff = 0, seg_begin = 0, seg_end = 0;
       auto off_at = [&](int idx) { return __shfl_sync(0xffffffffu, boff, idx - batch_base); };
-      int seg_begin = off_at(prog);
-      int seg_end = off_at(prog + 1);
+      if (Cb < Ce) {
+        prog = p.first_prog[blk];
+        batch_base = prog;
+        boff = p.off[min(batch_base + lane, p.P)];
+        seg_begin = off_at(prog);
+        seg_end = off_at(prog + 1);
+      }
       ptx::mbar_wait(bar(B_ACC1_FULL), it & 1);
       ptx::tc_fence_after();
-      float acc = 0.f;
-#pragma unroll 1
-      for (int c = 0; c < PAIR / 32; ++c) {
-        uint32_t v[32];
-        ptx::tmem_ld32(tmem + lane_base + 256 + 32 * c, v);
-        ptx::tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          acc += fmaxf(__uint_as_float(v[j]) + b1, 0.f);
-          const int r1 = (int)(R0 + 32 * c + j + 1);
-          if (r1 == seg_end) {                       // uniform across the CTA
-            float* dst = p.out + (size_t)prog * HID + hu;
-            if (seg_begin < R0) atomicAdd(dst, acc); else *dst = acc;
-            acc = 0.f;
-            do {                                     // next program, skipping empty ones
-              ++prog;
-              if (prog + 1 - batch_base > 31) { batch_base = prog; boff = p.off[min(batch_base + lane, p.P)]; }
-              seg_begin = seg_end;
-              seg_end = prog < p.P ? off_at(prog + 1) : INT32_MAX;
-            } while (seg_end == r1);
-          }
+      int64_t r = Cb;
+      while (r < Ce) {
+        const int e = (int)min((int64_t)seg_end, Ce);
+        const float s = segment_relu_sum(tmem + lane_base + 256 + (uint32_t)(r - (int64_t)t * PAIR), e - (int)r, b1);
+        float* dst = p.out + (size_t)prog * HID + hu;
+        if (seg_begin < Cb || seg_end > Ce) atomicAdd(dst, s); else *dst = s;
+        r = e;
+        if (seg_end <= Ce) {
+          do {                                     // next program, skipping empty ones
+            ++prog;
+            if (prog + 1 - batch_base > 31) { batch_base = prog; boff = p.off[min(batch_base + lane, p.P)]; }
+            seg_begin = seg_end;
+            seg_end = prog < p.P ? off_at(prog + 1) : INT32_MAX;
+          } while (prog < p.P && seg_end == seg_begin);
         }
       }
-      if (prog < p.P && seg_begin < Rend) atomicAdd(p.out + (size_t)prog * HID + hu, acc);   // continues in the next tile
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_cluster(bar(B_ACC1_EMPTY), 0);
@@ -309,13 +396,13 @@ segsum_tc_kernel(const TcParams p) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// pre-pass: first program of every pair tile; zero the output rows that receive atomics
-// (programs cut by a tile boundary) or nothing at all (empty programs).
-__global__ void tc_prepare_kernel(const int32_t* __restrict__ off, int P, int T, int32_t* __restrict__ first_prog,
+// pre-pass: first program of every 128-row block; zero the output rows that receive atomics
+// (programs cut by a block boundary) or nothing at all (empty programs).
+__global__ void tc_prepare_kernel(const int32_t* __restrict__ off, int P, int nblk, int32_t* __restrict__ first_prog,
                                   float* __restrict__ out) {
   const int gid = blockIdx.x * blockDim.x + threadIdx.x;
-  if (gid < T) {
-    const int target = gid * tc::PAIR;            // last p in [0, P) with off[p] <= target
+  if (gid < nblk) {
+    const int target = gid * tc::TILE;            // last p in [0, P) with off[p] <= target
     int lo = 0, hi = P;                           // invariant: off[lo] <= target, answer in [lo, hi)
     while (hi - lo > 1) {
       const int mid = (lo + hi) >> 1;
@@ -328,7 +415,7 @@ __global__ void tc_prepare_kernel(const int32_t* __restrict__ off, int P, int T,
   int need = 0;
   if (gid < P) {
     const int s = off[gid], e = off[gid + 1];
-    need = (e == s) || (s / tc::PAIR != (e - 1) / tc::PAIR);
+    need = (e == s) || (s / tc::TILE != (e - 1) / tc::TILE);
   }
   unsigned m = __ballot_sync(0xffffffffu, need);
   while (m) {
@@ -356,24 +443,26 @@ static __half h_clamp(float x) { return __float2half_rn(std::min(std::max(x, -65
 int tc_pack(vaex_model* m, const std::vector<float>& w0, cudaStream_t st) {
   using namespace tc;
   m->tc.ready = false;
-  if (m->H != HID || m->F > K0P || m->F < 1) return VAEX_OK;   // shape outside the tcgen05 kernel: SIMT path
+  if (m->H != HID || m->F >= K0P || m->F < 1) return VAEX_OK;   // shape outside the tcgen05 kernel: SIMT path
   const int F = m->F;
   std::vector<__half> i0(2 * W0_BYTES / 2, __float2half_rn(0.f)), i1(2 * W1_BYTES / 2);
   const std::vector<float>& w1 = m->host["segment_encoder.2.weight"].v;
+  const std::vector<float>& b0 = m->host["segment_encoder.0.bias"].v;
   for (int r = 0; r < 2; ++r)
     for (int row = 0; row < TILE; ++row) {
       const int h = r * TILE + row;
-      for (int k = 0; k < F; ++k) i0[(size_t)r * (W0_BYTES / 2) + sw128_off(row, k) / 2] = h_clamp(w0[(size_t)h * F + k]);
-      for (int k = 0; k < HID; ++k) i1[(size_t)r * (W1_BYTES / 2) + sw128_off(row, k) / 2] = h_clamp(w1[(size_t)h * HID + k]);
+      __half* d0 = i0.data() + (size_t)r * (W0_BYTES / 2);
+      __half* d1 = i1.data() + (size_t)r * (W1_BYTES / 2);
+      for (int k = 0; k < F; ++k) d0[sw128_off(row, k) / 2] = h_clamp(w0[(size_t)h * F + k]);
+      d0[sw128_off(row, F) / 2] = h_clamp(b0[h]);            // bias column (X supplies the 1)
+      for (int c = 0; c < HID; ++c) d1[sw128_off(row, c) / 2] = h_clamp(w1[(size_t)h * HID + hidden_of_col(c)]);
     }
   TcPack& t = m->tc;
   if (!t.w0) VAEX_CUDA(cudaMalloc(&t.w0, 2 * W0_BYTES));
   if (!t.w1) VAEX_CUDA(cudaMalloc(&t.w1, 2 * W1_BYTES));
-  if (!t.b0) VAEX_CUDA(cudaMalloc(&t.b0, HID * sizeof(float)));
   if (!t.b1) VAEX_CUDA(cudaMalloc(&t.b1, HID * sizeof(float)));
   VAEX_CUDA(cudaMemcpyAsync(t.w0, i0.data(), 2 * W0_BYTES, cudaMemcpyHostToDevice, st));
   VAEX_CUDA(cudaMemcpyAsync(t.w1, i1.data(), 2 * W1_BYTES, cudaMemcpyHostToDevice, st));
-  VAEX_CUDA(cudaMemcpyAsync(t.b0, m->host["segment_encoder.0.bias"].v.data(), HID * sizeof(float), cudaMemcpyHostToDevice, st));
   VAEX_CUDA(cudaMemcpyAsync(t.b1, m->host["segment_encoder.2.bias"].v.data(), HID * sizeof(float), cudaMemcpyHostToDevice, st));
   VAEX_CUDA(cudaStreamSynchronize(st));
   VAEX_CUDA(cudaFuncSetAttribute(segsum_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_DYN));
@@ -389,18 +478,19 @@ int segsum_tc_encode(vaex_model* m, const float* feats, const int32_t* off, int6
   VAEX_CHECK(m->tc.ready, "tcgen05 weights not packed");
   VAEX_CHECK(P < (1ll << 31) && R < (1ll << 31) - PAIR, "sizes exceed int32 row indexing");
   const int T = (int)cdiv(R, PAIR);
-  const int nprep = (int)std::max<int64_t>(P, T);
-  { int rc = m->tc_ws.ensure(sizeof(int32_t) * (size_t)std::max(T, 1) * 9); if (rc != VAEX_OK) return rc; }
+  const int nblk = 2 * T;
+  const int nprep = (int)std::max<int64_t>(P, nblk);
+  { int rc = m->tc_ws.ensure(sizeof(int32_t) * (size_t)std::max(T, 1) * 10); if (rc != VAEX_OK) return rc; }
   int32_t* first_prog = m->tc_ws.as<int32_t>();
-  uint32_t* rowmask = reinterpret_cast<uint32_t*>(first_prog + std::max(T, 1));
-  tc_prepare_kernel<<<(unsigned)cdiv(nprep, 256), 256, 0, st>>>(off, (int)P, T, first_prog, segsum);
+  uint32_t* rowmask = reinterpret_cast<uint32_t*>(first_prog + 2 * std::max(T, 1));
+  tc_prepare_kernel<<<(unsigned)cdiv(nprep, 256), 256, 0, st>>>(off, (int)P, nblk, first_prog, segsum);
   VAEX_LAUNCH_CHECK();
   if (T > 0) {
     TcParams prm;
     prm.feats = feats; prm.off = off; prm.first_prog = first_prog;
-    prm.w0 = m->tc.w0; prm.w1 = m->tc.w1; prm.b0 = m->tc.b0; prm.b1 = m->tc.b1;
+    prm.w0 = m->tc.w0; prm.w1 = m->tc.w1; prm.b1 = m->tc.b1;
     prm.out = segsum; prm.rowmask = rowmask; prm.n_rows = R; prm.P = (int)P; prm.T = T; prm.F = m->F;
-    prm.k0_steps = (m->F + 15) / 16;
+    prm.k0_steps = (m->F + 1 + 15) / 16;           // + the bias column
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
