@@ -147,6 +147,43 @@ __device__ __forceinline__ uint32_t load_convert_rows(const TcParams& p, uint32_
   return nzmask;
 }
 
+// Fast path (F % 4 == 0, 16-byte aligned rows): the swizzled A0 offset of every (slot, lane) unit
+// is the same for all tiles and, up to +2048*warp, for all warps -> a 1.5 KB table in shared
+// memory built once per CTA.  Per slot and lane: LDG.128, LDS.U16, 2 F2FP, STS.64 and the row's
+// non-zero bit (row = bits 7..10 of the offset); one REDUX.OR per tile merges the lanes' bits.
+constexpr int FAST_SLOTS = 24;                        // 16 rows * 47 units / 32 lanes
+__device__ __forceinline__ uint32_t load_convert_fast(const TcParams& p, uint32_t A0w, const uint16_t* tab, int64_t grow0,
+                                                      int lane) {
+  constexpr int ROWS = tc::TILE / tc::LOAD_WARPS;
+  constexpr int BATCH = 12;
+  const int total = ROWS * (p.F >> 2);
+  const int64_t vr = min((int64_t)ROWS, p.n_rows - grow0);
+  const int valid_units = vr > 0 ? (int)vr * (p.F >> 2) : 0;
+  const float4* src = reinterpret_cast<const float4*>(p.feats + grow0 * p.F) + lane;
+  uint32_t mask = 0;
+#pragma unroll
+  for (int s0 = 0; s0 < FAST_SLOTS; s0 += BATCH) {
+    float4 x[BATCH];
+    uint32_t o[BATCH];
+#pragma unroll
+    for (int j = 0; j < BATCH; ++j) {
+      const int idx = (s0 + j) * 32 + lane;
+      o[j] = tab[idx];
+      if (idx < valid_units) x[j] = ptx::ldg_stream_f4(reinterpret_cast<const float*>(src + (s0 + j) * 32));
+      else x[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int j = 0; j < BATCH; ++j) {
+      if ((s0 + j) * 32 + lane < total) {
+        ptx::sts_v2(A0w + o[j], ptx::cvt_h2_sat(x[j].x, x[j].y), ptx::cvt_h2_sat(x[j].z, x[j].w));
+        const uint32_t any = (__float_as_uint(x[j].x) | __float_as_uint(x[j].y) | __float_as_uint(x[j].z) | __float_as_uint(x[j].w)) << 1;
+        if (any) mask |= 1u << ((o[j] >> 7) & 15);
+      }
+    }
+  }
+  return __reduce_or_sync(0xffffffffu, mask);
+}
+
 template <int N>
 __device__ __forceinline__ float relu_sum(const uint32_t (&v)[N], float b1) {
   float a0 = 0.f, a1 = 0.f;
@@ -192,6 +229,7 @@ segsum_tc_kernel(const TcParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[B_COUNT];
   __shared__ uint32_t tmem_base_slot;
+  __shared__ uint16_t a0_tab[FAST_SLOTS * 32];
 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const uint32_t sbase = ptx::smem_u32(smem);
@@ -222,6 +260,13 @@ segsum_tc_kernel(const TcParams p) {
     uint4* s1 = reinterpret_cast<uint4*>(smem + W1_OFF);
     for (int i = threadIdx.x; i < W0_BYTES / 16; i += THREADS) s0[i] = __ldg(g0 + i);
     for (int i = threadIdx.x; i < W1_BYTES / 16; i += THREADS) s1[i] = __ldg(g1 + i);
+    if ((p.F & 3) == 0) {                                   // loader fast-path offset table
+      const int U = p.F >> 2;
+      for (int i = threadIdx.x; i < FAST_SLOTS * 32; i += THREADS) {
+        const int row = i / U, col = i - row * U;
+        a0_tab[i] = row < TILE / LOAD_WARPS ? (uint16_t)sw128_off(row, col * 4) : (uint16_t)0;
+      }
+    }
     uint4* a0 = reinterpret_cast<uint4*>(smem + A0_OFF);   // zero once: K padding columns stay 0
     for (int i = threadIdx.x; i < A0_BYTES / 16; i += THREADS) a0[i] = make_uint4(0, 0, 0, 0);
   }
@@ -255,7 +300,7 @@ segsum_tc_kernel(const TcParams p) {
       if (it > 0) ptx::mbar_wait(bar(B_A0_EMPTY), (it - 1) & 1);
       const int64_t row0 = (int64_t)t * PAIR + rank * TILE;
       uint32_t nzmask;
-      if (al16) nzmask = load_convert_rows<4>(p, A0, row0, warp * ROWS, lane);
+      if (al16) nzmask = load_convert_fast(p, A0 + 2048u * warp, a0_tab, row0 + warp * ROWS, lane);
       else if (al8) nzmask = load_convert_rows<2>(p, A0, row0, warp * ROWS, lane);
       else nzmask = load_convert_rows<1>(p, A0, row0, warp * ROWS, lane);
       // 16 flag bits per warp: two warps share one 32-bit word of the row mask
@@ -352,9 +397,10 @@ segsum_tc_kernel(const TcParams p) {
       if (lane == 0) ptx::mbar_arrive_cluster(bar(B_A1_FULL0 + g), 0);
 
       // ---- epi 1: segment sum over the 128-row block g of the tile (TMEM columns) ----
+      // all row indices are int32 and warp-uniform (n_rows < 2^31 - 256 is checked on the host)
       const int blk = 2 * t + g;
-      const int64_t Cb = (int64_t)blk * TILE;
-      const int64_t Ce = min(Cb + (int64_t)TILE, p.n_rows);
+      const int Cb = blk * TILE;                              // first row of the block
+      const int Ce = min(Cb + TILE, (int)p.n_rows);           // one past its last valid row
       int prog = 0, batch_base = 0, boff = 0, seg_begin = 0, seg_end = 0;
       auto off_at = [&](int idx) { return __shfl_sync(0xffffffffu, boff, idx - batch_base); };
       if (Cb < Ce) {
@@ -364,18 +410,20 @@ segsum_tc_kernel(const TcParams p) {
         seg_begin = off_at(prog);
         seg_end = off_at(prog + 1);
       }
+      float* dst = p.out + (size_t)prog * HID + hu;
+      const uint32_t tcol = tmem + lane_base + 256 + TILE * g - Cb;   // + row -> TMEM column of that row
       ptx::mbar_wait(bar(B_ACC1_FULL), it & 1);
       ptx::tc_fence_after();
-      int64_t r = Cb;
+      int r = Cb;
       while (r < Ce) {
-        const int e = (int)min((int64_t)seg_end, Ce);
-        const float s = segment_relu_sum(tmem + lane_base + 256 + (uint32_t)(r - (int64_t)t * PAIR), e - (int)r, b1);
-        float* dst = p.out + (size_t)prog * HID + hu;
+        const int e = min(seg_end, Ce);
+        const float s = segment_relu_sum(tcol + r, e - r, b1);
         if (seg_begin < Cb || seg_end > Ce) atomicAdd(dst, s); else *dst = s;
         r = e;
         if (seg_end <= Ce) {
           do {                                     // next program, skipping empty ones
             ++prog;
+            dst += HID;
             if (prog + 1 - batch_base > 31) { batch_base = prog; boff = p.off[min(batch_base + lane, p.P)]; }
             seg_begin = seg_end;
             seg_end = prog < p.P ? off_at(prog + 1) : INT32_MAX;
