@@ -22,12 +22,15 @@
 // the swizzled operand layout (the cast rules out a TMA tensor load of X).  b0 rides in a spare
 // K column of layer 0 (X gets a constant-1 column), so epi 0 has no bias add.
 //
-// Warp roles (17 warps): 0-7 loader, 8 MMA issuer (leader CTA), 9-16 epilogue in two groups of
-// four (one warp per TMEM lane quarter): group g runs epi 0 for hidden half g, then epi 1 for
-// 128-row block g of the tile.  All hand-offs are mbarriers; tcgen05.commit signals MMA completion.
+// Warp roles (17 warps): 0-7 front warps (epi 0 of tile i for hidden half w/4, then the load of
+// tile i+1: 16 rows each), 8 MMA issuer (leader CTA), 9-16 epi 1 in two groups of four (one warp
+// per TMEM lane quarter); group g drains layer-1 block g (N = 128 = rows [64g, 64g+64) of both
+// CTAs) while the tensor pipe runs the other block and the next tile's layer 0.  All hand-offs
+// are mbarriers; tcgen05.commit signals MMA completion.  Program boundaries come from a
+// per-sub-block descriptor list built by a pre-pass and read with warp-uniform loads.
 //
-// Programs cut by a 128-row block boundary receive two partial sums through atomicAdd on zeroed
-// rows (two addends: order-independent, so results are deterministic for S_i <= 128).
+// Programs cut by a 64-row sub-block boundary receive partial sums through atomicAdd on zeroed
+// rows (two addends when S_i <= 64: order-independent, so results are deterministic).
 #include <algorithm>
 #include <vector>
 
@@ -49,9 +52,11 @@ constexpr int A0_OFF = W1_OFF + W1_BYTES, A0_BYTES = 3 * ATOM;
 constexpr int A1_OFF = A0_OFF + A0_BYTES, A1_BYTES = 4 * ATOM;
 constexpr int SMEM_TILES = A1_OFF + A1_BYTES;          // 229376
 constexpr int SMEM_DYN = SMEM_TILES + 1024;            // + slack to align the base to 1024 B
-constexpr int LOAD_WARPS = 8, MMA_WARP = 8, EPI_WARP0 = 9, EPI_WARPS = 8;   // epilogue: 2 groups x 4 lane quarters
+constexpr int SUB = 64;              // rows per segment-descriptor sub-block (= rows one CTA feeds a layer-1 block)
+constexpr int LOAD_WARPS = 8, MMA_WARP = 8, EPI_WARP0 = 9, EPI_WARPS = 8;   // front (load + epi 0) and epi 1: 2 groups x 4 lane quarters
 constexpr int THREADS = 32 * (EPI_WARP0 + EPI_WARPS);   // 544
-enum { B_A0_FULL = 0, B_A0_EMPTY, B_ACC0_FULL0, B_ACC0_FULL1, B_A1_FULL0, B_A1_FULL1, B_ACC1_FULL, B_ACC1_EMPTY, B_COUNT };
+enum { B_A0_FULL = 0, B_A0_EMPTY, B_ACC0_FULL0, B_ACC0_FULL1, B_A1_FULL0, B_A1_FULL1, B_ACC1_FULL0, B_ACC1_FULL1,
+       B_ACC1_EMPTY0, B_ACC1_EMPTY1, B_COUNT };
 
 __host__ __device__ inline uint32_t sw128_off(int row, int k) {
   return (uint32_t)((k >> 6) * ATOM + (row >> 3) * 1024 + (row & 7) * 128 + ((((k & 63) >> 3) ^ (row & 7)) << 4) +
@@ -67,7 +72,7 @@ __host__ __device__ inline int hidden_of_col(int c) {
 struct TcParams {
   const float* feats;          // [n_rows, F]
   const int32_t* off;          // [P + 1]
-  const int32_t* first_prog;   // [2T] program holding the first row of 128-row block b
+  const uint2* desc;           // [4T][64] segment descriptors per 64-row sub-block: {program, col | len<<8 | partial<<16}
   const __half* w0;            // [2][W0_BYTES/2] swizzled images per CTA rank ([W0 | b0])
   const __half* w1;            // [2][W1_BYTES/2] (K permuted to the layer-0 column order)
   const float* b1;             // [256]
@@ -233,7 +238,8 @@ segsum_tc_kernel(const TcParams p) {
 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const uint32_t sbase = ptx::smem_u32(smem);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);   // warp-uniform for the compiler
+  const int lane = threadIdx.x & 31;
   const uint32_t rank = ptx::cluster_ctarank();
   const int cluster = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
   const uint32_t bar0 = ptx::smem_u32(&bars[0]);
@@ -247,8 +253,10 @@ segsum_tc_kernel(const TcParams p) {
     ptx::mbar_init(bar(B_ACC0_FULL1), 1);
     ptx::mbar_init(bar(B_A1_FULL0), 2 * 4);
     ptx::mbar_init(bar(B_A1_FULL1), 2 * 4);
-    ptx::mbar_init(bar(B_ACC1_FULL), 1);
-    ptx::mbar_init(bar(B_ACC1_EMPTY), 2 * EPI_WARPS);
+    ptx::mbar_init(bar(B_ACC1_FULL0), 1);
+    ptx::mbar_init(bar(B_ACC1_FULL1), 1);
+    ptx::mbar_init(bar(B_ACC1_EMPTY0), 2 * 4);
+    ptx::mbar_init(bar(B_ACC1_EMPTY1), 2 * 4);
     ptx::fence_mbar_init();
   }
   if (warp == EPI_WARP0) ptx::tmem_alloc_2cta(ptx::smem_u32(&tmem_base_slot), 512);
@@ -282,9 +290,9 @@ segsum_tc_kernel(const TcParams p) {
 
   // ---- roles ----------------------------------------------------------------------------------
   if (warp < LOAD_WARPS) {
-    // ===== loader: global fp32 rows -> fp16 swizzled A0 =====
-    const uint32_t A0 = sbase + A0_OFF;
+    // ===== front warps: epi 0 (acc0 -> ReLU -> fp16 -> A1) of tile i, then load tile i+1 =====
     constexpr int ROWS = TILE / LOAD_WARPS;
+    const uint32_t A0 = sbase + A0_OFF;
     const bool al16 = ((reinterpret_cast<uintptr_t>(p.feats) & 15) == 0) && (p.F % 4 == 0);
     const bool al8 = ((reinterpret_cast<uintptr_t>(p.feats) & 7) == 0) && (p.F % 2 == 0);
     auto prefetch = [&](int t) {
@@ -293,11 +301,7 @@ segsum_tc_kernel(const TcParams p) {
       const int64_t nr = min((int64_t)ROWS, p.n_rows - r0);
       if (nr > 0) ptx::prefetch_l2_bulk(p.feats + r0 * p.F, (uint32_t)(nr * p.F * 4));
     };
-    if (lane == 0) prefetch(cluster + n_clusters);
-    int it = 0;
-    for (int t = cluster; t < p.T; t += n_clusters, ++it) {
-      if (lane == 0) prefetch(t + 2 * n_clusters);
-      if (it > 0) ptx::mbar_wait(bar(B_A0_EMPTY), (it - 1) & 1);
+    auto load_tile = [&](int t) {
       const int64_t row0 = (int64_t)t * PAIR + rank * TILE;
       uint32_t nzmask;
       if (al16) nzmask = load_convert_fast(p, A0 + 2048u * warp, a0_tab, row0 + warp * ROWS, lane);
@@ -308,38 +312,80 @@ segsum_tc_kernel(const TcParams p) {
       ptx::fence_proxy_async();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_cluster(bar(B_A0_FULL), 0);
+    };
+    // epi 0 identity of this warp: TMEM lane quarter q, hidden half g
+    const int q = warp & 3, g = warp >> 2;
+    const uint32_t lane_base = (uint32_t)(32 * q) << 16;
+    const int row = 32 * q + lane;
+    const uint32_t a1_row = sbase + A1_OFF + (row >> 3) * 1024 + (row & 7) * 128;
+    const int sw = row & 7;
+
+    if (lane == 0) { prefetch(cluster + n_clusters); prefetch(cluster + 2 * n_clusters); }
+    if (cluster < p.T) load_tile(cluster);
+    int it = 0;
+    for (int t = cluster; t < p.T; t += n_clusters, ++it) {
+      if (lane == 0) prefetch(t + 3 * n_clusters);
+      // ---- epi 0: acc0 columns [128g, 128g+128) -> A1 atoms 2g, 2g+1 ----
+      ptx::mbar_wait(bar(B_ACC0_FULL0 + g), it & 1);
+      if (it > 0) ptx::mbar_wait(bar(B_ACC1_FULL1), (it - 1) & 1);   // layer 1 of the previous tile has read A1
+      ptx::tc_fence_after();
+#pragma unroll 1
+      for (int c = 4 * g; c < 4 * g + 4; ++c) {          // 32 columns per step
+        uint32_t v[32];
+        ptx::tmem_ld32(tmem + lane_base + 32 * c, v);
+        ptx::tmem_ld_wait();
+        const uint32_t base = a1_row + (c >> 1) * ATOM;
+#pragma unroll
+        for (int m = 0; m < 4; ++m)
+          ptx::sts_v4(base + ((((c & 1) * 4 + m) ^ sw) << 4),
+                      ptx::cvt_h2_relu_sat(__uint_as_float(v[8 * m]), __uint_as_float(v[8 * m + 1])),
+                      ptx::cvt_h2_relu_sat(__uint_as_float(v[8 * m + 2]), __uint_as_float(v[8 * m + 3])),
+                      ptx::cvt_h2_relu_sat(__uint_as_float(v[8 * m + 4]), __uint_as_float(v[8 * m + 5])),
+                      ptx::cvt_h2_relu_sat(__uint_as_float(v[8 * m + 6]), __uint_as_float(v[8 * m + 7])));
+      }
+      ptx::fence_proxy_async();
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive_cluster(bar(B_A1_FULL0 + g), 0);
+      // ---- load the next tile of this cluster ----
+      if (t + n_clusters < p.T) {
+        ptx::mbar_wait(bar(B_A0_EMPTY), it & 1);
+        load_tile(t + n_clusters);
+      }
     }
   } else if (warp == MMA_WARP) {
     // ===== MMA issuer: one thread of the leader CTA =====
     if (rank == 0) {
-      const uint32_t idesc_l0 = ptx::umma_idesc_f16(256, 128), idesc_l1 = ptx::umma_idesc_f16(256, 256);
+      const uint32_t idesc_n128 = ptx::umma_idesc_f16(256, 128);
       const uint64_t dW0 = ptx::umma_desc_sw128(sbase + W0_OFF), dW1 = ptx::umma_desc_sw128(sbase + W1_OFF);
       const uint64_t dA0 = ptx::umma_desc_sw128(sbase + A0_OFF), dA1 = ptx::umma_desc_sw128(sbase + A1_OFF);
       // +32 B per K=16 step inside an atom (encoded >>4 -> +2), +ATOM per 64 columns
       auto kadv = [](int k) -> uint64_t { return (uint64_t)(((k >> 2) * ATOM + (k & 3) * 32) >> 4); };
-      constexpr uint64_t half_rows = (64 * 128) >> 4;   // B rows 64.. of each CTA's W0 half
+      constexpr uint64_t rows64 = (64 * 128) >> 4;      // operand rows 64.. of a CTA (N = 128 halves)
       int it = 0;
       for (int t = cluster; t < p.T; t += n_clusters, ++it) {
+        // ---- layer 0: two hidden halves ----
         ptx::mbar_wait(bar(B_A0_FULL), it & 1);
         ptx::fence_acq_rel_cluster();
         ptx::tc_fence_after();
         if (lane == 0) {
           for (int k = 0; k < p.k0_steps; ++k)
-            ptx::umma_f16_2cta(tmem + 0, dA0 + kadv(k), dW0 + kadv(k), idesc_l0, k > 0);
+            ptx::umma_f16_2cta(tmem + 0, dA0 + kadv(k), dW0 + kadv(k), idesc_n128, k > 0);
           ptx::umma_commit_2cta(bar(B_ACC0_FULL0), 3);
           for (int k = 0; k < p.k0_steps; ++k)
-            ptx::umma_f16_2cta(tmem + 128, dA0 + kadv(k), dW0 + half_rows + kadv(k), idesc_l0, k > 0);
+            ptx::umma_f16_2cta(tmem + 128, dA0 + kadv(k), dW0 + rows64 + kadv(k), idesc_n128, k > 0);
           ptx::umma_commit_2cta(bar(B_ACC0_FULL1), 3);
           ptx::umma_commit_2cta(bar(B_A0_EMPTY), 3);
         }
         __syncwarp();
-        if (it > 0) ptx::mbar_wait(bar(B_ACC1_EMPTY), (it - 1) & 1);
+        // ---- layer 1, row block 0 (rows [0,64) of both CTAs): K half 0 then K half 1 ----
+        if (it > 0) ptx::mbar_wait(bar(B_ACC1_EMPTY0), (it - 1) & 1);
         ptx::mbar_wait(bar(B_A1_FULL0), it & 1);
         ptx::fence_acq_rel_cluster();
         ptx::tc_fence_after();
         if (lane == 0) {
 #pragma unroll
-          for (int k = 0; k < 8; ++k) ptx::umma_f16_2cta(tmem + 256, dW1 + kadv(k), dA1 + kadv(k), idesc_l1, k > 0);
+          for (int k = 0; k < 8; ++k) ptx::umma_f16_2cta(tmem + 256, dW1 + kadv(k), dA1 + kadv(k), idesc_n128, k > 0);
         }
         __syncwarp();
         ptx::mbar_wait(bar(B_A1_FULL1), it & 1);
@@ -347,92 +393,61 @@ segsum_tc_kernel(const TcParams p) {
         ptx::tc_fence_after();
         if (lane == 0) {
 #pragma unroll
-          for (int k = 8; k < 16; ++k) ptx::umma_f16_2cta(tmem + 256, dW1 + kadv(k), dA1 + kadv(k), idesc_l1, 1);
-          ptx::umma_commit_2cta(bar(B_ACC1_FULL), 3);
+          for (int k = 8; k < 16; ++k) ptx::umma_f16_2cta(tmem + 256, dW1 + kadv(k), dA1 + kadv(k), idesc_n128, 1);
+          ptx::umma_commit_2cta(bar(B_ACC1_FULL0), 3);
+        }
+        __syncwarp();
+        // ---- layer 1, row block 1 (rows [64,128) of both CTAs) ----
+        if (it > 0) ptx::mbar_wait(bar(B_ACC1_EMPTY1), (it - 1) & 1);
+        ptx::tc_fence_after();
+        if (lane == 0) {
+#pragma unroll
+          for (int k = 0; k < 16; ++k)
+            ptx::umma_f16_2cta(tmem + 384, dW1 + kadv(k), dA1 + rows64 + kadv(k), idesc_n128, k > 0);
+          ptx::umma_commit_2cta(bar(B_ACC1_FULL1), 3);
         }
         __syncwarp();
       }
     }
   } else {
-    // ===== epilogue group g: epi 0 for hidden half g, then epi 1 for 128-row block g =====
-    const int q = warp & 3;                       // TMEM lane quarter this warp may access
+    // ===== epi 1, group g: layer-1 block g = TMEM columns [256+128g, +128) =====
+    //   columns [0,64)   <-> rows [64g, 64g+64) of CTA 0  = sub-block 4t + g
+    //   columns [64,128) <-> rows [64g, 64g+64) of CTA 1  = sub-block 4t + 2 + g
+    const int q = warp & 3;
     const int g = (warp - EPI_WARP0) >> 2;
     const uint32_t lane_base = (uint32_t)(32 * q) << 16;
-    const int row = 32 * q + lane;                // epi 0: row of this CTA's half tile
-    const uint32_t a1_row = sbase + A1_OFF + (row >> 3) * 1024 + (row & 7) * 128;
-    const int sw = row & 7;
-    const int hu = rank * TILE + 32 * q + lane;   // epi 1: hidden unit of this lane
+    const int hu = rank * TILE + 32 * q + lane;   // hidden unit of this lane
     const float b1 = p.b1[hu];
+    float* const out_h = p.out + hu;
     int it = 0;
     for (int t = cluster; t < p.T; t += n_clusters, ++it) {
-      // ---- epi 0: acc0 columns [128g, 128g+128) -> ReLU -> fp16 -> A1 atoms 2g, 2g+1 ----
-      // (A1 is free: this warp already waited for layer 1 of the previous tile in its epi 1)
-      ptx::mbar_wait(bar(B_ACC0_FULL0 + g), it & 1);
+      const uint2* d0 = p.desc + (size_t)(4 * t + g) * SUB;
+      const uint2* d1 = p.desc + (size_t)(4 * t + 2 + g) * SUB;
+      uint2 nxt = __ldg(d0);                                    // warp-uniform load
+      ptx::mbar_wait(bar(B_ACC1_FULL0 + g), it & 1);
       ptx::tc_fence_after();
 #pragma unroll 1
-      for (int cc = 2 * g; cc < 2 * g + 2; ++cc) {
-        uint32_t v[32], w[32];
-        ptx::tmem_ld32(tmem + lane_base + 64 * cc, v);
-        ptx::tmem_ld32(tmem + lane_base + 64 * cc + 32, w);
-        ptx::tmem_ld_wait();
-        const uint32_t base = a1_row + cc * ATOM;
-#pragma unroll
-        for (int m = 0; m < 4; ++m)
-          ptx::sts_v4(base + ((m ^ sw) << 4),
-                      ptx::cvt_h2_relu_sat(__uint_as_float(v[8 * m]), __uint_as_float(v[8 * m + 1])),
-                      ptx::cvt_h2_relu_sat(__uint_as_float(v[8 * m + 2]), __uint_as_float(v[8 * m + 3])),
-                      ptx::cvt_h2_relu_sat(__uint_as_float(v[8 * m + 4]), __uint_as_float(v[8 * m + 5])),
-                      ptx::cvt_h2_relu_sat(__uint_as_float(v[8 * m + 6]), __uint_as_float(v[8 * m + 7])));
-#pragma unroll
-        for (int m = 0; m < 4; ++m)
-          ptx::sts_v4(base + (((m + 4) ^ sw) << 4),
-                      ptx::cvt_h2_relu_sat(__uint_as_float(w[8 * m]), __uint_as_float(w[8 * m + 1])),
-                      ptx::cvt_h2_relu_sat(__uint_as_float(w[8 * m + 2]), __uint_as_float(w[8 * m + 3])),
-                      ptx::cvt_h2_relu_sat(__uint_as_float(w[8 * m + 4]), __uint_as_float(w[8 * m + 5])),
-                      ptx::cvt_h2_relu_sat(__uint_as_float(w[8 * m + 6]), __uint_as_float(w[8 * m + 7])));
-      }
-      ptx::fence_proxy_async();
-      ptx::tc_fence_before();
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive_cluster(bar(B_A1_FULL0 + g), 0);
-
-      // ---- epi 1: segment sum over the 128-row block g of the tile (TMEM columns) ----
-      // all row indices are int32 and warp-uniform (n_rows < 2^31 - 256 is checked on the host)
-      const int blk = 2 * t + g;
-      const int Cb = blk * TILE;                              // first row of the block
-      const int Ce = min(Cb + TILE, (int)p.n_rows);           // one past its last valid row
-      int prog = 0, batch_base = 0, boff = 0, seg_begin = 0, seg_end = 0;
-      auto off_at = [&](int idx) { return __shfl_sync(0xffffffffu, boff, idx - batch_base); };
-      if (Cb < Ce) {
-        prog = p.first_prog[blk];
-        batch_base = prog;
-        boff = p.off[min(batch_base + lane, p.P)];
-        seg_begin = off_at(prog);
-        seg_end = off_at(prog + 1);
-      }
-      float* dst = p.out + (size_t)prog * HID + hu;
-      const uint32_t tcol = tmem + lane_base + 256 + TILE * g - Cb;   // + row -> TMEM column of that row
-      ptx::mbar_wait(bar(B_ACC1_FULL), it & 1);
-      ptx::tc_fence_after();
-      int r = Cb;
-      while (r < Ce) {
-        const int e = min(seg_end, Ce);
-        const float s = segment_relu_sum(tcol + r, e - r, b1);
-        if (seg_begin < Cb || seg_end > Ce) atomicAdd(dst, s); else *dst = s;
-        r = e;
-        if (seg_end <= Ce) {
-          do {                                     // next program, skipping empty ones
-            ++prog;
-            dst += HID;
-            if (prog + 1 - batch_base > 31) { batch_base = prog; boff = p.off[min(batch_base + lane, p.P)]; }
-            seg_begin = seg_end;
-            seg_end = prog < p.P ? off_at(prog + 1) : INT32_MAX;
-          } while (prog < p.P && seg_end == seg_begin);
+      for (int half = 0; half < 2; ++half) {
+        const uint2* dl = half ? d1 : d0;
+        const int sub_row0 = (4 * t + 2 * half + g) * SUB;
+        const int nvalid = min(SUB, (int)p.n_rows - sub_row0);
+        const uint32_t tcol = tmem + lane_base + 256 + 128 * g + 64 * half;
+        if (half) nxt = __ldg(d1);
+        int covered = 0, k = 0;
+        while (covered < nvalid) {
+          const uint2 d = nxt;
+          ++k;
+          if (k < SUB) nxt = __ldg(dl + k);
+          const int c0 = d.y & 0xff, n = (d.y >> 8) & 0xff;
+          const float s = segment_relu_sum(tcol + c0, n, b1);
+          float* dst = out_h + (size_t)d.x * HID;
+          if (d.y >> 16) atomicAdd(dst, s); else *dst = s;
+          covered += n;
         }
       }
       ptx::tc_fence_before();
       __syncwarp();
-      if (lane == 0) ptx::mbar_arrive_cluster(bar(B_ACC1_EMPTY), 0);
+      if (lane == 0) ptx::mbar_arrive_cluster(bar(B_ACC1_EMPTY0 + g), 0);
     }
   }
 
@@ -444,26 +459,38 @@ segsum_tc_kernel(const TcParams p) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// pre-pass: first program of every 128-row block; zero the output rows that receive atomics
-// (programs cut by a block boundary) or nothing at all (empty programs).
-__global__ void tc_prepare_kernel(const int32_t* __restrict__ off, int P, int nblk, int32_t* __restrict__ first_prog,
+// pre-pass, one thread per 64-row sub-block: the list of (program, first column, length, partial)
+// pieces that tile the sub-block; and one thread per program: zero the output rows that receive
+// atomics (programs cut by a sub-block boundary) or nothing at all (empty programs).
+__global__ void tc_prepare_kernel(const int32_t* __restrict__ off, int P, int n_rows, int nsub, uint2* __restrict__ desc,
                                   float* __restrict__ out) {
   const int gid = blockIdx.x * blockDim.x + threadIdx.x;
-  if (gid < nblk) {
-    const int target = gid * tc::TILE;            // last p in [0, P) with off[p] <= target
-    int lo = 0, hi = P;                           // invariant: off[lo] <= target, answer in [lo, hi)
+  if (gid < nsub) {
+    const int r0 = gid * tc::SUB, r1 = min(r0 + tc::SUB, n_rows);
+    int lo = 0, hi = P;                           // last p in [0, P) with off[p] <= r0
     while (hi - lo > 1) {
       const int mid = (lo + hi) >> 1;
-      if (off[mid] <= target) lo = mid; else hi = mid;
+      if (off[mid] <= r0) lo = mid; else hi = mid;
     }
-    first_prog[gid] = lo;
+    uint2* d = desc + (size_t)gid * tc::SUB;
+    int p = lo, r = r0, k = 0;
+    while (r < r1) {
+      const int s = off[p], e = off[p + 1];
+      if (e > r) {                                // skips empty programs
+        const int ee = min(e, r1);
+        const unsigned partial = (s < r0 || e > r1) ? 1u : 0u;
+        d[k++] = make_uint2((unsigned)p, (unsigned)(r - r0) | ((unsigned)(ee - r) << 8) | (partial << 16));
+        r = ee;
+      }
+      ++p;
+    }
   }
   const int lane = threadIdx.x & 31;
   const int pbase = gid - lane;                   // 32 programs per warp
   int need = 0;
   if (gid < P) {
     const int s = off[gid], e = off[gid + 1];
-    need = (e == s) || (s / tc::TILE != (e - 1) / tc::TILE);
+    need = (e == s) || (s / tc::SUB != (e - 1) / tc::SUB);
   }
   unsigned m = __ballot_sync(0xffffffffu, need);
   while (m) {
@@ -526,16 +553,17 @@ int segsum_tc_encode(vaex_model* m, const float* feats, const int32_t* off, int6
   VAEX_CHECK(m->tc.ready, "tcgen05 weights not packed");
   VAEX_CHECK(P < (1ll << 31) && R < (1ll << 31) - PAIR, "sizes exceed int32 row indexing");
   const int T = (int)cdiv(R, PAIR);
-  const int nblk = 2 * T;
-  const int nprep = (int)std::max<int64_t>(P, nblk);
-  { int rc = m->tc_ws.ensure(sizeof(int32_t) * (size_t)std::max(T, 1) * 10); if (rc != VAEX_OK) return rc; }
-  int32_t* first_prog = m->tc_ws.as<int32_t>();
-  uint32_t* rowmask = reinterpret_cast<uint32_t*>(first_prog + 2 * std::max(T, 1));
-  tc_prepare_kernel<<<(unsigned)cdiv(nprep, 256), 256, 0, st>>>(off, (int)P, nblk, first_prog, segsum);
+  const int nsub = 4 * T;
+  const int nprep = (int)std::max<int64_t>(P, nsub);
+  const size_t desc_bytes = sizeof(uint2) * (size_t)std::max(nsub, 1) * SUB;
+  { int rc = m->tc_ws.ensure(desc_bytes + sizeof(uint32_t) * (size_t)std::max(T, 1) * 8); if (rc != VAEX_OK) return rc; }
+  uint2* desc = m->tc_ws.as<uint2>();
+  uint32_t* rowmask = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(desc) + desc_bytes);
+  tc_prepare_kernel<<<(unsigned)cdiv(nprep, 256), 256, 0, st>>>(off, (int)P, (int)R, nsub, desc, segsum);
   VAEX_LAUNCH_CHECK();
   if (T > 0) {
     TcParams prm;
-    prm.feats = feats; prm.off = off; prm.first_prog = first_prog;
+    prm.feats = feats; prm.off = off; prm.desc = desc;
     prm.w0 = m->tc.w0; prm.w1 = m->tc.w1; prm.b1 = m->tc.b1;
     prm.out = segsum; prm.rowmask = rowmask; prm.n_rows = R; prm.P = (int)P; prm.T = T; prm.F = m->F;
     prm.k0_steps = (m->F + 1 + 15) / 16;           // + the bias column
