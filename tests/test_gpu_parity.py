@@ -142,13 +142,15 @@ def test_segsum_mlp_properties_large():
         b = net(torch.from_numpy(sizes[order[:5000]]).cuda(), feats[torch.from_numpy(row_idx).cuda()])
         c = net(st, feats)
     assert torch.equal(a, c), "not deterministic run to run"
-    # position in the batch only changes where a 256-row tile cuts a program, i.e. the fp32
-    # association of its segment sum: scores agree to fp32 rounding, not to fp16 rounding
+    # position in the batch changes where a 64-row sub-block cuts a program, i.e. the fp32
+    # association of its segment sum (1e-7); the head then rounds the sums to fp16 operands, so
+    # a flipped rounding moves a score by up to the tcgen05 tolerance -- never more
     pa = a[torch.from_numpy(order[:5000]).cuda()]
-    assert (pa - b).abs().max().item() < 2e-6 * max(1.0, pa.abs().max().item()), "score depends on batch position"
+    assert l2_err(b.cpu().numpy(), pa.cpu().numpy()) < 2e-4, "score depends on batch position"
+    assert rel_err(b.cpu().numpy(), pa.cpu().numpy()) < TC_RTOL
     # host path (chunked, two streams) vs device path: same property
     h = vaex_b200.predict_flat(net, feats[: offs[50000]].cpu().numpy(), sizes[:50000])
-    np.testing.assert_allclose(h, a[:50000].cpu().numpy(), rtol=0, atol=2e-6 * max(1.0, float(a.abs().max())))
+    assert l2_err(h, a[:50000].cpu().numpy()) < 2e-4 and rel_err(h, a[:50000].cpu().numpy()) < TC_RTOL
 
 
 def test_segment_offsets_scan():

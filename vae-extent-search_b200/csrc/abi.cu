@@ -92,6 +92,7 @@ static int pack_segsum_mlp(vaex_model* m, const float* norm, cudaStream_t st) {
     TRY(upload(m, "norm.shift", c.data(), H, st));
   }
   TRY(tc_pack(m, w0, st));
+  TRY(head_tc_pack(m, st));
   return VAEX_OK;
 }
 
@@ -202,6 +203,8 @@ int vaex_model_destroy(vaex_model_t h) {
   if (h->tc.w1) cudaFree(h->tc.w1);
   if (h->tc.b0) cudaFree(h->tc.b0);
   if (h->tc.b1) cudaFree(h->tc.b1);
+  if (h->tc.wl0) cudaFree(h->tc.wl0);
+  if (h->tc.wl1) cudaFree(h->tc.wl1);
   for (auto& sl : h->slots) { if (sl.feats) cudaFree(sl.feats); if (sl.off) cudaFree(sl.off); if (sl.scores) cudaFree(sl.scores); }
   for (auto& s : h->copy_streams) if (s) cudaStreamDestroy(s);
   for (auto& e : h->events) if (e) cudaEventDestroy(e);

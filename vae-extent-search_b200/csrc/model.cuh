@@ -20,8 +20,11 @@ struct TcPack {
   __half* w1 = nullptr;   // [256][256]
   float* b0 = nullptr;    // [256]
   float* b1 = nullptr;    // [256]
+  __half* wl0 = nullptr;  // head: [2][128 x 256] per CTA rank
+  __half* wl1 = nullptr;
   int F = 0, K0P = 0;
   bool ready = false;
+  bool head_ready = false;
 };
 
 struct DevBuf {
@@ -59,6 +62,10 @@ struct vaex_model {
 namespace vaex {
 // segsum_tc.cu
 int tc_pack(vaex_model* m, const std::vector<float>& w0_folded, cudaStream_t st);
+// head_tc.cu
+int head_tc_pack(vaex_model* m, cudaStream_t st);
+int head_tc_forward(vaex_model* m, const float* S, int64_t P, const uint8_t* valid, float* scores, cudaStream_t st);
+// segsum_tc.cu
 int segsum_tc_encode(vaex_model* m, const float* feats, const int32_t* off, int64_t n_programs,
                      int64_t n_rows, float* segsum, uint8_t* valid, cudaStream_t st);
 }  // namespace vaex

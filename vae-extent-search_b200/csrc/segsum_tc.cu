@@ -421,33 +421,36 @@ segsum_tc_kernel(const TcParams p) {
     float* const out_h = p.out + hu;
     int it = 0;
     for (int t = cluster; t < p.T; t += n_clusters, ++it) {
+      // descriptors of both sub-blocks: lane j holds entries j and j+32 (two coalesced 256 B loads
+      // per sub-block, issued before the wait); the walk below broadcasts them with shuffles.
       const uint2* d0 = p.desc + (size_t)(4 * t + g) * SUB;
       const uint2* d1 = p.desc + (size_t)(4 * t + 2 + g) * SUB;
-      uint2 nxt = __ldg(d0);                                    // warp-uniform load
+      const uint2 e00 = __ldg(d0 + lane), e01 = __ldg(d0 + lane + 32);
+      const uint2 e10 = __ldg(d1 + lane), e11 = __ldg(d1 + lane + 32);
       ptx::mbar_wait(bar(B_ACC1_FULL0 + g), it & 1);
       ptx::tc_fence_after();
 #pragma unroll 1
       for (int half = 0; half < 2; ++half) {
-        const uint2* dl = half ? d1 : d0;
         const int sub_row0 = (4 * t + 2 * half + g) * SUB;
         const int nvalid = min(SUB, (int)p.n_rows - sub_row0);
         const uint32_t tcol = tmem + lane_base + 256 + 128 * g + 64 * half;
-        if (half) nxt = __ldg(d1);
+        const uint2 lo = half ? e10 : e00, hi = half ? e11 : e01;
         int covered = 0, k = 0;
         while (covered < nvalid) {
-          const uint2 d = nxt;
+          const uint2 sel = k < 32 ? lo : hi;
+          const unsigned dx = __shfl_sync(0xffffffffu, sel.x, k & 31);
+          const unsigned dy = __shfl_sync(0xffffffffu, sel.y, k & 31);
           ++k;
-          if (k < SUB) nxt = __ldg(dl + k);
-          const int c0 = d.y & 0xff, n = (d.y >> 8) & 0xff;
+          const int c0 = dy & 0xff, n = (dy >> 8) & 0xff;
           const float s = segment_relu_sum(tcol + c0, n, b1);
-          float* dst = out_h + (size_t)d.x * HID;
-          if (d.y >> 16) atomicAdd(dst, s); else *dst = s;
+          float* dst = out_h + (size_t)dx * HID;
+          if (dy >> 16) atomicAdd(dst, s); else *dst = s;
           covered += n;
         }
       }
       ptx::tc_fence_before();
       __syncwarp();
-      if (lane == 0) ptx::mbar_arrive_cluster(bar(B_ACC1_EMPTY0 + g), 0);
+      if (lane == 0) ptx::mbar_arrive_cluster_relaxed(bar(B_ACC1_EMPTY0 + g), 0);
     }
   }
 

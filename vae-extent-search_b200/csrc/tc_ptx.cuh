@@ -67,6 +67,18 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar, uint32_t rank)
       : "memory");
 }
 
+// same, without release semantics: for barriers that publish no data (e.g. "TMEM drained", which is
+// ordered by tcgen05.wait::ld + tcgen05.fence::before_thread_sync); avoids a MEMBAR that would wait
+// for the warp's outstanding global stores.
+__device__ __forceinline__ void mbar_arrive_cluster_relaxed(uint32_t bar, uint32_t rank) {
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [ra];\n\t}"
+      ::"r"(bar), "r"(rank)
+      : "memory");
+}
+
 // ---- proxies / tcgen05 fences --------------------------------------------------------------
 __device__ __forceinline__ void fence_proxy_async() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
