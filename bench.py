@@ -170,7 +170,7 @@ def main_vaex(args):
     import torch
     import torch.distributed as dist
     import vaex_b200
-    from vaex_b200 import _lib
+    from vaex_b200 import _lib, shard
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -193,8 +193,7 @@ def main_vaex(args):
     segsum = None
     top_v, top_i = torch.empty(TOPK, device=dev), torch.empty(TOPK, dtype=torch.int64, device=dev)
     n_out = torch.zeros(1, dtype=torch.int32, device=dev)
-    gath_v = torch.empty(world * TOPK, device=dev)
-    gath_i = torch.empty(world * TOPK, dtype=torch.int64, device=dev)
+    merged = [None]
     stream = torch.cuda.current_stream()
     st = stream.cuda_stream
     flags = _lib.F_MASK_INVALID
@@ -203,10 +202,8 @@ def main_vaex(args):
         _lib.check(lib.vaex_segment_offsets(_lib.ptr(sizes_d), P, _lib.ptr(offsets), st))
         _lib.check(lib.vaex_segsum_mlp_forward(model.h, _lib.ptr(feats), _lib.ptr(offsets), P, rows, _lib.ptr(scores), flags, st))
         _lib.check(lib.vaex_topk(_lib.ptr(scores), P, TOPK, None, _lib.ptr(top_v), _lib.ptr(top_i), _lib.ptr(n_out), st))
-        if world > 1:
-            dist.all_gather_into_tensor(gath_v, top_v)
-            dist.all_gather_into_tensor(gath_i, top_i + rank * P)
-            _lib.check(lib.vaex_topk(_lib.ptr(gath_v), world * TOPK, TOPK, None, _lib.ptr(top_v), _lib.ptr(top_i), _lib.ptr(n_out), st))
+        if world > 1:       # candidate merge: the path's only exchange (vaex_b200/shard.py)
+            merged[0] = shard.merge_topk(top_v, top_i, rank * P, TOPK)
 
     def barrier():
         if world > 1:

@@ -1,0 +1,92 @@
+"""N>1 host logic on CPU: block partition, row-balanced partition and the top-k merge over a
+world_size-2 gloo group (the CUDA radix select is replaced by the oracle's top-k here; the GPU
+version of the same merge is covered by bench.py --gpus N)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import vaex_b200
+from vaex_b200 import shard
+from oracle import torch_oracle as O
+
+
+def test_shard_range_covers_everything():
+    for n in (0, 1, 7, 8, 9, 1000003):
+        for world in (1, 2, 3, 8):
+            spans = [shard.shard_range(n, r, world) for r in range(world)]
+            assert spans[0][0] == 0 and spans[-1][1] == n
+            assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+            lens = [b - a for a, b in spans]
+            assert max(lens) - min(lens) <= 1
+    with pytest.raises(ValueError):
+        shard.shard_range(10, 2, 2)
+
+
+def test_shard_by_rows_balances_rows():
+    rng = np.random.default_rng(0)
+    sizes = rng.integers(1, 33, size=20000)
+    for world in (1, 2, 4, 8):
+        cuts = shard.shard_by_rows(sizes, world)
+        assert cuts[0] == 0 and cuts[-1] == len(sizes) and np.all(np.diff(cuts) >= 0)
+        rows = np.add.reduceat(sizes, cuts[:-1])
+        assert rows.sum() == sizes.sum()
+        assert rows.max() - rows.min() <= 64          # within two maximal programs
+    # degenerate: fewer programs than ranks
+    cuts = shard.shard_by_rows([5, 5], 4)
+    assert cuts[0] == 0 and cuts[-1] == 2 and np.all(np.diff(cuts) >= 0)
+
+
+def _oracle_topk(values, k, mask):
+    v = values.numpy().copy()
+    keep = np.nonzero(mask.numpy())[0]
+    vals, pos = O.topk_desc(v[keep], k)
+    return torch.from_numpy(vals.copy()), torch.from_numpy(keep[pos])
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, n, k, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        rng = np.random.default_rng(5)
+        scores = rng.standard_normal(n).astype(np.float32)
+        scores[rng.integers(0, n, size=n // 4)] = 0.5            # many exact ties across ranks
+        scores[rng.integers(0, n, size=n // 50)] = -np.inf       # invalid programs
+        lo, hi = shard.shard_range(n, rank, world)
+        lv, li = O.topk_desc(scores[lo:hi], k)
+        vals, idx = shard.merge_topk(torch.from_numpy(lv.copy()), torch.from_numpy(li), lo, k, topk_fn=_oracle_topk)
+        np.savez(os.path.join(out_dir, "r%d.npz" % rank), vals=vals.numpy(), idx=idx.numpy(), scores=scores)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n,k", [(5000, 320), (300, 320), (7, 4)])
+def test_merge_topk_world2_gloo(tmp_path, n, k):
+    world = 2
+    mp.spawn(_worker, args=(world, _free_port(), n, k, str(tmp_path)), nprocs=world, join=True)
+    r0, r1 = (np.load(tmp_path / ("r%d.npz" % r)) for r in range(world))
+    want_v, want_i = O.topk_desc(r0["scores"], k)            # single-process answer over the whole pool
+    for r in (r0, r1):
+        assert np.array_equal(r["idx"], want_i)              # bit-exact incl. tie order
+        assert np.array_equal(r["vals"], want_v)
+
+
+def test_merge_topk_single_process_is_identity():
+    v = torch.tensor([3.0, 2.0, 2.0])
+    i = torch.tensor([4, 1, 9])
+    vals, idx = shard.merge_topk(v, i, 100, 5, topk_fn=_oracle_topk)
+    assert idx.tolist() == [104, 101, 109] and vals.tolist() == [3.0, 2.0, 2.0]
+    with pytest.raises(ValueError):
+        shard.merge_topk(v, i, 0, 2, topk_fn=_oracle_topk)

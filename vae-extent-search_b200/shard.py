@@ -1,0 +1,76 @@
+"""Multi-GPU sharding of the scoring path.
+
+Programs are independent, so the path shards by contiguous blocks of programs with the weights
+replicated and *no data-path collective*.  The only exchange is the candidate merge: every rank
+contributes its k best (score, global index) pairs, one all-gather, one more top-k.  The merge
+keeps the library's deterministic order (score desc, global index asc): ranks own ascending
+blocks and every local list is already in that order, so "position in the gathered array" and
+"global index" break ties identically.
+
+The reference is single-GPU (utils/select.py:54-81 sorts one numpy array); this module is what
+replaces that sort when the pool is spread over ranks."""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def shard_range(n, rank, world):
+    """Contiguous balanced block [lo, hi) of n items for `rank` (first n % world ranks get one more)."""
+    if not (0 <= rank < world):
+        raise ValueError("rank %d outside world of %d" % (rank, world))
+    base, extra = divmod(int(n), int(world))
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def shard_by_rows(sizes, world):
+    """Program boundaries [world+1] that balance the number of feature *rows* per rank (the
+    row encoder's work is per row, not per program).  Contiguous, monotone, covers everything."""
+    sizes = np.asarray(sizes, dtype=np.int64)
+    ends = np.cumsum(sizes)
+    total = int(ends[-1]) if len(ends) else 0
+    cuts = [0]
+    for r in range(1, world):
+        target = total * r / world
+        c = int(np.searchsorted(ends, target, side="left"))
+        # pick the nearer side of the target, keep monotone
+        if c < len(ends) and c > 0 and abs(ends[c - 1] - target) <= abs(ends[c] - target):
+            c -= 1
+        cuts.append(max(cuts[-1], min(c + 1, len(sizes))))
+    cuts.append(len(sizes))
+    return np.asarray(cuts, dtype=np.int64)
+
+
+def _default_topk(values, k, mask):
+    from . import vae_model
+    return vae_model.topk(values, k, mask)
+
+
+def merge_topk(local_values, local_indices, index_base, k, group=None, topk_fn=None):
+    """Global top-k from per-rank winners.
+
+    local_values [m<=k] (score desc, index asc) and local_indices [m] (rank-local int64) are
+    this rank's winners; index_base is the global index of the rank's first program.  Returns
+    (values, global_indices) of the k best over all ranks, identical on every rank.  Ranks
+    with fewer than k winners pad with index -1; padding is masked out of the merge, so it never
+    displaces a real entry (not even a real -inf score).  `topk_fn(values, k, mask) -> (values,
+    positions)` defaults to the CUDA radix select (tests on CPU inject the oracle's)."""
+    topk_fn = topk_fn or _default_topk
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    dev = local_values.device
+    m = int(local_values.shape[0])
+    if m > k:
+        raise ValueError("more local winners (%d) than k (%d)" % (m, k))
+    v = torch.full((k,), float("-inf"), dtype=torch.float32, device=dev)
+    i = torch.full((k,), -1, dtype=torch.int64, device=dev)
+    v[:m] = local_values
+    i[:m] = local_indices.to(torch.int64) + int(index_base)
+    if world > 1:
+        gv = torch.empty(world * k, dtype=torch.float32, device=dev)
+        gi = torch.empty(world * k, dtype=torch.int64, device=dev)
+        dist.all_gather_into_tensor(gv, v, group=group)
+        dist.all_gather_into_tensor(gi, i, group=group)
+    else:
+        gv, gi = v, i
+    vals, pos = topk_fn(gv, k, (gi >= 0).to(torch.uint8))
+    return vals, gi[pos]
