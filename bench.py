@@ -203,7 +203,7 @@ def main_vaex(args):
         _lib.check(lib.vaex_segsum_mlp_forward(model.h, _lib.ptr(feats), _lib.ptr(offsets), P, rows, _lib.ptr(scores), flags, st))
         _lib.check(lib.vaex_topk(_lib.ptr(scores), P, TOPK, None, _lib.ptr(top_v), _lib.ptr(top_i), _lib.ptr(n_out), st))
         if world > 1:       # candidate merge: the path's only exchange (vaex_b200/shard.py)
-            merged[0] = shard.merge_topk(top_v, top_i, rank * P, TOPK)
+            merged[0] = shard.merge_topk(top_v, top_i, rank * P, TOPK, n_local=n_out, sync=False)
 
     def barrier():
         if world > 1:

@@ -45,7 +45,10 @@ def _oracle_topk(values, k, mask):
     v = values.numpy().copy()
     keep = np.nonzero(mask.numpy())[0]
     vals, pos = O.topk_desc(v[keep], k)
-    return torch.from_numpy(vals.copy()), torch.from_numpy(keep[pos])
+    n = len(pos)                                    # k-sized outputs + count, like the CUDA call with sync=False
+    ov, op = np.zeros(min(k, len(v)), np.float32), np.zeros(min(k, len(v)), np.int64)
+    ov[:n], op[:n] = vals, keep[pos]
+    return torch.from_numpy(ov), torch.from_numpy(op), torch.tensor([n], dtype=torch.int32)
 
 
 def _free_port():
@@ -90,3 +93,10 @@ def test_merge_topk_single_process_is_identity():
     assert idx.tolist() == [104, 101, 109] and vals.tolist() == [3.0, 2.0, 2.0]
     with pytest.raises(ValueError):
         shard.merge_topk(v, i, 0, 2, topk_fn=_oracle_topk)
+
+
+def test_merge_topk_device_count_and_nosync():
+    v = torch.tensor([3.0, 2.0, 9.0, 9.0])          # last two are unspecified padding of the local top-k
+    i = torch.tensor([4, 1, 7, 7])
+    vals, idx = shard.merge_topk(v, i, 10, 4, topk_fn=_oracle_topk, n_local=torch.tensor([2], dtype=torch.int32), sync=False)
+    assert idx.tolist() == [14, 11, -1, -1] and vals[:2].tolist() == [3.0, 2.0]

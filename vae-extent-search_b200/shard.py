@@ -43,28 +43,37 @@ def shard_by_rows(sizes, world):
 
 def _default_topk(values, k, mask):
     from . import vae_model
-    return vae_model.topk(values, k, mask)
+    return vae_model.topk(values, k, mask, sync=False)
 
 
-def merge_topk(local_values, local_indices, index_base, k, group=None, topk_fn=None):
+def merge_topk(local_values, local_indices, index_base, k, group=None, topk_fn=None, n_local=None, sync=True):
     """Global top-k from per-rank winners.
 
     local_values [m<=k] (score desc, index asc) and local_indices [m] (rank-local int64) are
-    this rank's winners; index_base is the global index of the rank's first program.  Returns
-    (values, global_indices) of the k best over all ranks, identical on every rank.  Ranks
-    with fewer than k winners pad with index -1; padding is masked out of the merge, so it never
-    displaces a real entry (not even a real -inf score).  `topk_fn(values, k, mask) -> (values,
-    positions)` defaults to the CUDA radix select (tests on CPU inject the oracle's)."""
+    this rank's winners; index_base is the global index of the rank's first program.  When the
+    winner count is only known on the device pass k-sized tensors and n_local (int32 tensor).
+    Returns (values, global_indices) of the k best over all ranks, identical on every rank.
+    Ranks with fewer than k winners pad with index -1; padding is masked out of the merge, so it
+    never displaces a real entry (not even a real -inf score).  sync=False returns k-sized
+    tensors whose unused tail has index -1 and does not wait for the GPU.
+    `topk_fn(values, k, mask) -> (values, positions, count)` defaults to the CUDA radix select
+    (tests on CPU inject the oracle's)."""
     topk_fn = topk_fn or _default_topk
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     dev = local_values.device
     m = int(local_values.shape[0])
     if m > k:
         raise ValueError("more local winners (%d) than k (%d)" % (m, k))
-    v = torch.full((k,), float("-inf"), dtype=torch.float32, device=dev)
-    i = torch.full((k,), -1, dtype=torch.int64, device=dev)
-    v[:m] = local_values
-    i[:m] = local_indices.to(torch.int64) + int(index_base)
+    gi_local = local_indices.to(torch.int64) + int(index_base)
+    if n_local is not None:
+        gi_local = torch.where(torch.arange(m, device=dev) < n_local.to(dev), gi_local, gi_local.new_full((), -1))
+    if m < k:
+        v = torch.full((k,), float("-inf"), dtype=torch.float32, device=dev)
+        i = torch.full((k,), -1, dtype=torch.int64, device=dev)
+        v[:m] = local_values
+        i[:m] = gi_local
+    else:
+        v, i = local_values.to(torch.float32).contiguous(), gi_local
     if world > 1:
         gv = torch.empty(world * k, dtype=torch.float32, device=dev)
         gi = torch.empty(world * k, dtype=torch.int64, device=dev)
@@ -72,5 +81,11 @@ def merge_topk(local_values, local_indices, index_base, k, group=None, topk_fn=N
         dist.all_gather_into_tensor(gi, i, group=group)
     else:
         gv, gi = v, i
-    vals, pos = topk_fn(gv, k, (gi >= 0).to(torch.uint8))
-    return vals, gi[pos]
+    vals, pos, count = topk_fn(gv, k, (gi >= 0).to(torch.uint8))
+    kk = vals.shape[0]
+    live = torch.arange(kk, device=dev) < count.to(dev)
+    idx = torch.where(live, gi[pos.clamp(0, gi.shape[0] - 1)], gi.new_full((), -1))
+    if not sync:
+        return vals, idx
+    n = int(count.item())
+    return vals[:n], idx[:n]

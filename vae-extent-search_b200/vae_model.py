@@ -241,8 +241,10 @@ class VAECostPredictor(_Packed, nn.Module):
         return z, cost
 
 
-def topk(scores, k, mask=None):
-    """GPU top-k with the deterministic (score desc, index asc) order -> (values, int64 indices)."""
+def topk(scores, k, mask=None, sync=True):
+    """GPU top-k with the deterministic (score desc, index asc) order -> (values, int64 indices).
+    sync=False skips the host read of the winner count and returns (values[k], indices[k],
+    count) with count a device int32 tensor; entries past count are unspecified."""
     s = _need_cuda(scores)
     k = int(min(k, s.shape[0]))
     vals = torch.empty(k, device=s.device)
@@ -251,5 +253,7 @@ def topk(scores, k, mask=None):
     mk = None if mask is None else mask.to(device=s.device, dtype=torch.uint8).contiguous()
     _lib.check(_lib.load().vaex_topk(_lib.ptr(s), s.shape[0], k, _lib.ptr(mk), _lib.ptr(vals), _lib.ptr(idx), _lib.ptr(n_out),
                                     _lib.stream_ptr()))
+    if not sync:
+        return vals, idx, n_out
     m = int(n_out.item())
     return vals[:m], idx[:m]
