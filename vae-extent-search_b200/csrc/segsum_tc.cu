@@ -22,12 +22,16 @@
 // the swizzled operand layout (the cast rules out a TMA tensor load of X).  b0 rides in a spare
 // K column of layer 0 (X gets a constant-1 column), so epi 0 has no bias add.
 //
-// Warp roles (17 warps): 0-7 front warps (epi 0 of tile i for hidden half w/4, then the load of
-// tile i+1: 16 rows each), 8 MMA issuer (leader CTA), 9-16 epi 1 in two groups of four (one warp
-// per TMEM lane quarter); group g drains layer-1 block g (N = 128 = rows [64g, 64g+64) of both
-// CTAs) while the tensor pipe runs the other block and the next tile's layer 0.  All hand-offs
-// are mbarriers; tcgen05.commit signals MMA completion.  Program boundaries come from a
-// per-sub-block descriptor list built by a pre-pass and read with warp-uniform loads.
+// Warp roles (21 warps): 0-7 loaders (16 rows each; the first half of the next tile is already
+// in registers when the tensor pipe releases A0), 8-11 epi 0 (one warp per TMEM lane quarter;
+// hidden half 0 while the MMAs of half 1 run), 12-19 epi 1 in two groups of four (group g drains
+// layer-1 block g while the tensor pipe fills the other block and runs the next tile's layer 0),
+// 20 MMA issuer (leader CTA).  All hand-offs are mbarriers; tcgen05.commit signals MMA completion.
+//
+// epi 1 walks the 64 accumulator columns of a sub-block with a *static* register index and a
+// warp-uniform 64-bit "last row of a piece" mask built by a pre-pass: no per-segment TMEM
+// round trip.  When F <= 174, b1 rides in the spare k-step (columns 176/177) of the resident
+// W0 / A0 images as a 17th K step of layer 1 (hi + lo fp16 halves, so the bias keeps ~22 bits).
 //
 // Programs cut by a 64-row sub-block boundary receive partial sums through atomicAdd on zeroed
 // rows (two addends when S_i <= 64: order-independent, so results are deterministic).
@@ -53,8 +57,9 @@ constexpr int A1_OFF = A0_OFF + A0_BYTES, A1_BYTES = 4 * ATOM;
 constexpr int SMEM_TILES = A1_OFF + A1_BYTES;          // 229376
 constexpr int SMEM_DYN = SMEM_TILES + 1024;            // + slack to align the base to 1024 B
 constexpr int SUB = 64;              // rows per segment-descriptor sub-block (= rows one CTA feeds a layer-1 block)
-constexpr int LOAD_WARPS = 8, MMA_WARP = 8, EPI_WARP0 = 9, EPI_WARPS = 8;   // front (load + epi 0) and epi 1: 2 groups x 4 lane quarters
-constexpr int THREADS = 32 * (EPI_WARP0 + EPI_WARPS);   // 544
+constexpr int LOAD_WARPS = 8, EPI1_WARP0 = 12, MMA_WARP = 20;   // 0-7 loaders, 8-11 epi 0, 12-19 epi 1, 20 MMA issuer
+constexpr int THREADS = 32 * (MMA_WARP + 1);   // 672
+constexpr int B1_COL = 176;          // k columns of the b1 hi/lo halves (spare k-step 11 of the W0 / A0 images)
 enum { B_A0_FULL = 0, B_A0_EMPTY, B_ACC0_FULL0, B_ACC0_FULL1, B_A1_FULL0, B_A1_FULL1, B_ACC1_FULL0, B_ACC1_FULL1,
        B_ACC1_EMPTY0, B_ACC1_EMPTY1, B_COUNT };
 
@@ -72,7 +77,8 @@ __host__ __device__ inline int hidden_of_col(int c) {
 struct TcParams {
   const float* feats;          // [n_rows, F]
   const int32_t* off;          // [P + 1]
-  const uint2* desc;           // [4T][64] segment descriptors per 64-row sub-block: {program, col | len<<8 | partial<<16}
+  const uint4* meta;           // [4T][2] per 64-row sub-block: {endmask lo, hi, partialmask lo, hi}, {first program, flags, -, -}
+  const uint2* desc;           // [4T][64] piece list {program, col | len<<8 | partial<<16}; only written for irregular sub-blocks
   const __half* w0;            // [2][W0_BYTES/2] swizzled images per CTA rank ([W0 | b0])
   const __half* w1;            // [2][W1_BYTES/2] (K permuted to the layer-0 column order)
   const float* b1;             // [256]
@@ -156,78 +162,115 @@ __device__ __forceinline__ uint32_t load_convert_rows(const TcParams& p, uint32_
 // is the same for all tiles and, up to +2048*warp, for all warps -> a 1.5 KB table in shared
 // memory built once per CTA.  Per slot and lane: LDG.128, LDS.U16, 2 F2FP, STS.64 and the row's
 // non-zero bit (row = bits 7..10 of the offset); one REDUX.OR per tile merges the lanes' bits.
+// The 24 slots of a lane are split in two batches: issue() puts 12 LDG.128 in flight, commit()
+// converts and stores them, so batch 0 of the next tile can be fetched before A0 is released.
 constexpr int FAST_SLOTS = 24;                        // 16 rows * 47 units / 32 lanes
-__device__ __forceinline__ uint32_t load_convert_fast(const TcParams& p, uint32_t A0w, const uint16_t* tab, int64_t grow0,
-                                                      int lane) {
-  constexpr int ROWS = tc::TILE / tc::LOAD_WARPS;
-  constexpr int BATCH = 12;
-  const int total = ROWS * (p.F >> 2);
-  const int64_t vr = min((int64_t)ROWS, p.n_rows - grow0);
-  const int valid_units = vr > 0 ? (int)vr * (p.F >> 2) : 0;
-  const float4* src = reinterpret_cast<const float4*>(p.feats + grow0 * p.F) + lane;
-  uint32_t mask = 0;
+constexpr int FAST_BATCH = 12;
+struct FastLoader {
+  const float4* src;
+  int valid_units, total;
+  __device__ __forceinline__ void open(const TcParams& p, int64_t grow0, int lane) {
+    constexpr int ROWS = tc::TILE / tc::LOAD_WARPS;
+    total = ROWS * (p.F >> 2);
+    const int64_t vr = min((int64_t)ROWS, p.n_rows - grow0);
+    valid_units = vr > 0 ? (int)vr * (p.F >> 2) : 0;
+    src = reinterpret_cast<const float4*>(p.feats + (vr > 0 ? grow0 : 0) * p.F) + lane;
+  }
+  __device__ __forceinline__ void issue(int s0, int lane, float4 (&x)[FAST_BATCH]) const {
 #pragma unroll
-  for (int s0 = 0; s0 < FAST_SLOTS; s0 += BATCH) {
-    float4 x[BATCH];
-    uint32_t o[BATCH];
-#pragma unroll
-    for (int j = 0; j < BATCH; ++j) {
+    for (int j = 0; j < FAST_BATCH; ++j) {
       const int idx = (s0 + j) * 32 + lane;
-      o[j] = tab[idx];
       if (idx < valid_units) x[j] = ptx::ldg_stream_f4(reinterpret_cast<const float*>(src + (s0 + j) * 32));
       else x[j] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
+  }
+  __device__ __forceinline__ uint32_t commit(int s0, int lane, const float4 (&x)[FAST_BATCH], uint32_t A0w,
+                                             const uint16_t* tab) const {
+    uint32_t mask = 0;
 #pragma unroll
-    for (int j = 0; j < BATCH; ++j) {
-      if ((s0 + j) * 32 + lane < total) {
-        ptx::sts_v2(A0w + o[j], ptx::cvt_h2_sat(x[j].x, x[j].y), ptx::cvt_h2_sat(x[j].z, x[j].w));
+    for (int j = 0; j < FAST_BATCH; ++j) {
+      const int idx = (s0 + j) * 32 + lane;
+      if (idx < total) {
+        const uint32_t o = tab[idx];
+        ptx::sts_v2(A0w + o, ptx::cvt_h2_sat(x[j].x, x[j].y), ptx::cvt_h2_sat(x[j].z, x[j].w));
         const uint32_t any = (__float_as_uint(x[j].x) | __float_as_uint(x[j].y) | __float_as_uint(x[j].z) | __float_as_uint(x[j].w)) << 1;
-        if (any) mask |= 1u << ((o[j] >> 7) & 15);
+        if (any) mask |= 1u << ((o >> 7) & 15);
       }
     }
+    return mask;
   }
-  return __reduce_or_sync(0xffffffffu, mask);
-}
+};
 
-template <int N>
-__device__ __forceinline__ float relu_sum(const uint32_t (&v)[N], float b1) {
-  float a0 = 0.f, a1 = 0.f;
+// ---------------------------------------------------------------------------------------------
+// epi 1 building block: 16 accumulator columns (static register index).  m: bit j = column j is
+// the last row of a piece, pm: that piece is partial (cut by the sub-block boundary -> atomicAdd).
+// a0/a1 are the running even/odd-column sums of the open piece; dst walks the output rows (the
+// pieces of a regular sub-block belong to consecutive programs).
+__device__ __forceinline__ void flush_piece(float* dst, float s, uint32_t partial) {
+  // one pointer, two predicated instructions: keeps the (cold) boundary code small
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0;\n\t@p red.global.add.f32 [%0], %1;\n\t@!p st.global.f32 [%0], %1;\n\t}"
+      :: "l"(dst), "f"(s), "r"(partial) : "memory");
+}
+template <bool FOLD>
+__device__ __forceinline__ void sum_chunk(const uint32_t (&v)[16], uint32_t m, uint32_t pm, float b1, float& a0, float& a1,
+                                          float*& dst) {
+  auto act = [&](uint32_t u) { return FOLD ? fmaxf(__uint_as_float(u), 0.f) : fmaxf(__uint_as_float(u) + b1, 0.f); };
 #pragma unroll
-  for (int j = 0; j < N; j += 2) {
-    a0 += fmaxf(__uint_as_float(v[j]) + b1, 0.f);
-    if (j + 1 < N) a1 += fmaxf(__uint_as_float(v[j + 1]) + b1, 0.f);
+  for (int j = 0; j < 16; j += 4) {
+    const float x0 = act(v[j]), x1 = act(v[j + 1]), x2 = act(v[j + 2]), x3 = act(v[j + 3]);
+    if ((m >> j) & 15u) {                                 // warp-uniform, ~22 % of the 4-column groups
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float x = i == 0 ? x0 : i == 1 ? x1 : i == 2 ? x2 : x3;
+        if (i & 1) a1 += x; else a0 += x;
+        if ((m >> (j + i)) & 1u) {
+          flush_piece(dst, a0 + a1, (pm >> (j + i)) & 1u);
+          dst += tc::HID;
+          a0 = 0.f;
+          a1 = 0.f;
+        }
+      }
+    } else {
+      a0 += x0;
+      a1 += x1;
+      a0 += x2;
+      a1 += x3;
+    }
   }
-  return a0 + a1;
 }
 
-// sum_{c in [c0, c0+n)} relu(acc1[lane, c] + b1): the segment is fetched with x32 loads plus one
-// power-of-two load per set bit of the remainder, all issued before a single wait.
-__device__ __forceinline__ float segment_relu_sum(uint32_t taddr, int n, float b1) {
-  float acc = 0.f;
-  while (n >= 32) {
-    uint32_t v[32];
-    ptx::tmem_ld32(taddr, v);
-    ptx::tmem_ld_wait();
-    acc += relu_sum<32>(v, b1);
-    taddr += 32;
-    n -= 32;
+// irregular sub-block (an empty program sits between two pieces; rare): per-piece TMEM walk,
+// kept small on purpose (8-column loads, then single columns)
+__device__ __forceinline__ void sum_irregular(uint32_t tcol, const uint2* __restrict__ d, int nvalid, float b1, float* out_h) {
+  int covered = 0, k = 0;
+  while (covered < nvalid) {
+    const uint2 e = __ldg(d + k);
+    ++k;
+    uint32_t c = tcol + (e.y & 0xff);
+    int n = (e.y >> 8) & 0xff;
+    covered += n;
+    float s = 0.f;
+    for (; n >= 8; n -= 8, c += 8) {
+      uint32_t v[8];
+      ptx::tmem_ld8(c, v);
+      ptx::tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s += fmaxf(__uint_as_float(v[j]) + b1, 0.f);
+    }
+    for (; n > 0; --n, ++c) {
+      uint32_t v;
+      ptx::tmem_ld1(c, v);
+      ptx::tmem_ld_wait();
+      s += fmaxf(__uint_as_float(v) + b1, 0.f);
+    }
+    float* dst = out_h + (size_t)e.x * tc::HID;
+    if (e.y >> 16) atomicAdd(dst, s); else *dst = s;
   }
-  uint32_t v16[16], v8[8], v4[4], v2[2], v1;
-  if (n & 16) { ptx::tmem_ld16(taddr, v16); taddr += 16; }
-  if (n & 8) { ptx::tmem_ld8(taddr, v8); taddr += 8; }
-  if (n & 4) { ptx::tmem_ld4(taddr, v4); taddr += 4; }
-  if (n & 2) { ptx::tmem_ld2(taddr, v2); taddr += 2; }
-  if (n & 1) { ptx::tmem_ld1(taddr, v1); }
-  ptx::tmem_ld_wait();
-  if (n & 16) acc += relu_sum<16>(v16, b1);
-  if (n & 8) acc += relu_sum<8>(v8, b1);
-  if (n & 4) acc += relu_sum<4>(v4, b1);
-  if (n & 2) acc += relu_sum<2>(v2, b1);
-  if (n & 1) acc += fmaxf(__uint_as_float(v1) + b1, 0.f);
-  return acc;
 }
 
 // ---------------------------------------------------------------------------------------------
+template <bool FOLD>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(tc::THREADS, 1)
 segsum_tc_kernel(const TcParams p) {
   using namespace tc;
@@ -259,7 +302,7 @@ segsum_tc_kernel(const TcParams p) {
     ptx::mbar_init(bar(B_ACC1_EMPTY1), 2 * 4);
     ptx::fence_mbar_init();
   }
-  if (warp == EPI_WARP0) ptx::tmem_alloc_2cta(ptx::smem_u32(&tmem_base_slot), 512);
+  if (warp == EPI1_WARP0) ptx::tmem_alloc_2cta(ptx::smem_u32(&tmem_base_slot), 512);
   {
     // resident weights: already in the exact swizzled byte layout -> straight 16-byte copies
     const uint4* g0 = reinterpret_cast<const uint4*>(p.w0) + (size_t)rank * (W0_BYTES / 16);
@@ -279,8 +322,14 @@ segsum_tc_kernel(const TcParams p) {
     for (int i = threadIdx.x; i < A0_BYTES / 16; i += THREADS) a0[i] = make_uint4(0, 0, 0, 0);
   }
   __syncthreads();
-  // constant-1 column at k = F multiplies the b0 column of the W0 image (bias inside the MMA)
-  if (threadIdx.x < TILE) *reinterpret_cast<uint16_t*>(smem + A0_OFF + sw128_off(threadIdx.x, p.F)) = 0x3C00;
+  // constant-1 columns: k = F, F+1 multiply the b0 hi/lo columns of the W0 image (bias inside the
+  // MMA); k = 176, 177 multiply the b1 hi/lo columns in the extra K step of layer 1
+  if (threadIdx.x < TILE) {
+    auto one = [&](int k) { *reinterpret_cast<uint16_t*>(smem + A0_OFF + sw128_off(threadIdx.x, k)) = 0x3C00; };
+    one(p.F);
+    if (p.F + 1 < K0P) one(p.F + 1);
+    if (FOLD) { one(B1_COL); one(B1_COL + 1); }
+  }
   ptx::fence_proxy_async();
   ptx::tc_fence_before();
   __syncthreads();
@@ -290,7 +339,7 @@ segsum_tc_kernel(const TcParams p) {
 
   // ---- roles ----------------------------------------------------------------------------------
   if (warp < LOAD_WARPS) {
-    // ===== front warps: epi 0 (acc0 -> ReLU -> fp16 -> A1) of tile i, then load tile i+1 =====
+    // ===== loaders: fp32 rows -> fp16 swizzled A0; 16 rows per warp =====
     constexpr int ROWS = TILE / LOAD_WARPS;
     const uint32_t A0 = sbase + A0_OFF;
     const bool al16 = ((reinterpret_cast<uintptr_t>(p.feats) & 15) == 0) && (p.F % 4 == 0);
@@ -301,59 +350,159 @@ segsum_tc_kernel(const TcParams p) {
       const int64_t nr = min((int64_t)ROWS, p.n_rows - r0);
       if (nr > 0) ptx::prefetch_l2_bulk(p.feats + r0 * p.F, (uint32_t)(nr * p.F * 4));
     };
-    auto load_tile = [&](int t) {
-      const int64_t row0 = (int64_t)t * PAIR + rank * TILE;
-      uint32_t nzmask;
-      if (al16) nzmask = load_convert_fast(p, A0 + 2048u * warp, a0_tab, row0 + warp * ROWS, lane);
-      else if (al8) nzmask = load_convert_rows<2>(p, A0, row0, warp * ROWS, lane);
-      else nzmask = load_convert_rows<1>(p, A0, row0, warp * ROWS, lane);
+    auto publish = [&](int t, uint32_t nzmask) {
       // 16 flag bits per warp: two warps share one 32-bit word of the row mask
       if (lane == 0) reinterpret_cast<uint16_t*>(p.rowmask)[((size_t)t * 8 + rank * 4) * 2 + warp] = (uint16_t)nzmask;
       ptx::fence_proxy_async();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_cluster(bar(B_A0_FULL), 0);
     };
-    // epi 0 identity of this warp: TMEM lane quarter q, hidden half g
-    const int q = warp & 3, g = warp >> 2;
+    if (lane == 0) { prefetch(cluster + n_clusters); prefetch(cluster + 2 * n_clusters); }
+    if (al16) {
+      FastLoader ld;
+      float4 x[FAST_BATCH];
+      const uint32_t A0w = A0 + 2048u * warp;
+      if (cluster < p.T) {
+        ld.open(p, (int64_t)cluster * PAIR + rank * TILE + warp * ROWS, lane);
+        ld.issue(0, lane, x);
+      }
+      int it = 0;
+      for (int t = cluster; t < p.T; t += n_clusters, ++it) {
+        if (lane == 0) prefetch(t + 3 * n_clusters);
+        if (it > 0) ptx::mbar_wait(bar(B_A0_EMPTY), (it - 1) & 1);      // layer 0 of the previous tile has read A0
+        uint32_t nz = ld.commit(0, lane, x, A0w, a0_tab);
+        ld.issue(FAST_BATCH, lane, x);
+        nz |= ld.commit(FAST_BATCH, lane, x, A0w, a0_tab);
+        publish(t, __reduce_or_sync(0xffffffffu, nz));
+        if (t + n_clusters < p.T) {                                     // batch 0 of the next tile rides in registers
+          ld.open(p, (int64_t)(t + n_clusters) * PAIR + rank * TILE + warp * ROWS, lane);
+          ld.issue(0, lane, x);
+        }
+      }
+    } else {
+      int it = 0;
+      for (int t = cluster; t < p.T; t += n_clusters, ++it) {
+        if (it > 0) ptx::mbar_wait(bar(B_A0_EMPTY), (it - 1) & 1);
+        const int64_t row0 = (int64_t)t * PAIR + rank * TILE;
+        publish(t, al8 ? load_convert_rows<2>(p, A0, row0, warp * ROWS, lane) : load_convert_rows<1>(p, A0, row0, warp * ROWS, lane));
+      }
+    }
+  } else if (warp < EPI1_WARP0) {
+    // ===== epi 0: acc0 -> ReLU -> fp16 -> A1 (K-major, 128B swizzle); lane = tile row =====
+    const int q = warp & 3;
     const uint32_t lane_base = (uint32_t)(32 * q) << 16;
     const int row = 32 * q + lane;
     const uint32_t a1_row = sbase + A1_OFF + (row >> 3) * 1024 + (row & 7) * 128;
     const int sw = row & 7;
-
-    if (lane == 0) { prefetch(cluster + n_clusters); prefetch(cluster + 2 * n_clusters); }
-    if (cluster < p.T) load_tile(cluster);
+    auto pack32 = [&](const uint32_t (&v)[32], int c) {   // accumulator columns [32c, 32c+32) -> 64 B of A1
+      const uint32_t base = a1_row + (c >> 1) * ATOM;
+#pragma unroll
+      for (int m = 0; m < 4; ++m)
+        ptx::sts_v4(base + ((((c & 1) * 4 + m) ^ sw) << 4),
+                    ptx::cvt_h2_relu_sat(__uint_as_float(v[8 * m]), __uint_as_float(v[8 * m + 1])),
+                    ptx::cvt_h2_relu_sat(__uint_as_float(v[8 * m + 2]), __uint_as_float(v[8 * m + 3])),
+                    ptx::cvt_h2_relu_sat(__uint_as_float(v[8 * m + 4]), __uint_as_float(v[8 * m + 5])),
+                    ptx::cvt_h2_relu_sat(__uint_as_float(v[8 * m + 6]), __uint_as_float(v[8 * m + 7])));
+    };
     int it = 0;
     for (int t = cluster; t < p.T; t += n_clusters, ++it) {
-      if (lane == 0) prefetch(t + 3 * n_clusters);
-      // ---- epi 0: acc0 columns [128g, 128g+128) -> A1 atoms 2g, 2g+1 ----
-      ptx::mbar_wait(bar(B_ACC0_FULL0 + g), it & 1);
-      if (it > 0) ptx::mbar_wait(bar(B_ACC1_FULL1), (it - 1) & 1);   // layer 1 of the previous tile has read A1
-      ptx::tc_fence_after();
 #pragma unroll 1
-      for (int c = 4 * g; c < 4 * g + 4; ++c) {          // 32 columns per step
-        uint32_t v[32];
-        ptx::tmem_ld32(tmem + lane_base + 32 * c, v);
+      for (int g = 0; g < 2; ++g) {                        // hidden half g = acc0 columns [128g, 128g+128)
+        ptx::mbar_wait(bar(B_ACC0_FULL0 + g), it & 1);
+        if (g == 0 && it > 0) ptx::mbar_wait(bar(B_ACC1_FULL1), (it - 1) & 1);   // layer 1 of the previous tile has read A1
+        ptx::tc_fence_after();
+        const uint32_t tcol = tmem + lane_base + 128 * g;
+        uint32_t va[32], vb[32];
+        ptx::tmem_ld32(tcol, va);
         ptx::tmem_ld_wait();
-        const uint32_t base = a1_row + (c >> 1) * ATOM;
-#pragma unroll
-        for (int m = 0; m < 4; ++m)
-          ptx::sts_v4(base + ((((c & 1) * 4 + m) ^ sw) << 4),
-                      ptx::cvt_h2_relu_sat(__uint_as_float(v[8 * m]), __uint_as_float(v[8 * m + 1])),
-                      ptx::cvt_h2_relu_sat(__uint_as_float(v[8 * m + 2]), __uint_as_float(v[8 * m + 3])),
-                      ptx::cvt_h2_relu_sat(__uint_as_float(v[8 * m + 4]), __uint_as_float(v[8 * m + 5])),
-                      ptx::cvt_h2_relu_sat(__uint_as_float(v[8 * m + 6]), __uint_as_float(v[8 * m + 7])));
-      }
-      ptx::fence_proxy_async();
-      ptx::tc_fence_before();
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive_cluster(bar(B_A1_FULL0 + g), 0);
-      // ---- load the next tile of this cluster ----
-      if (t + n_clusters < p.T) {
-        ptx::mbar_wait(bar(B_A0_EMPTY), it & 1);
-        load_tile(t + n_clusters);
+        ptx::tmem_ld32(tcol + 32, vb);
+        pack32(va, 4 * g);
+        ptx::tmem_ld_wait();
+        ptx::tmem_ld32(tcol + 64, va);
+        pack32(vb, 4 * g + 1);
+        ptx::tmem_ld_wait();
+        ptx::tmem_ld32(tcol + 96, vb);
+        pack32(va, 4 * g + 2);
+        ptx::tmem_ld_wait();
+        pack32(vb, 4 * g + 3);
+        ptx::fence_proxy_async();
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive_cluster(bar(B_A1_FULL0 + g), 0);
       }
     }
-  } else if (warp == MMA_WARP) {
+  } else if (warp < MMA_WARP) {
+    // ===== epi 1: layer-1 block g = TMEM columns [256+128g, +128) =====
+    //   columns [0,64)   <-> rows [64g, 64g+64) of CTA 0  = sub-block 4t + g
+    //   columns [64,128) <-> rows [64g, 64g+64) of CTA 1  = sub-block 4t + 2 + g
+    // Two groups of four warps (one per TMEM lane quarter); group g drains block g while the
+    // tensor pipe fills the other one.  One loop body per 32 columns (two instantiations of the
+    // statically indexed 16-column code, ping-pong TMEM loads), four steps per block.
+    const int q = warp & 3;
+    const int g = (warp - EPI1_WARP0) >> 2;
+    const uint32_t lane_base = (uint32_t)(32 * q) << 16;
+    const int hu = rank * TILE + 32 * q + lane;   // hidden unit of this lane
+    const float b1 = FOLD ? 0.f : p.b1[hu];
+    float* const out_h = p.out + hu;
+    const uint32_t tbase = tmem + lane_base + 256 + 128 * g;
+    uint32_t va[16], vb[16];
+    // sub-block metadata of this tile (na, nb: h = 0; nc, nd: h = 1), fetched one tile ahead
+    uint4 na = make_uint4(0, 0, 0, 0), nc = na;
+    uint2 nb = make_uint2(0, 0), nd = nb;
+    auto fetch_meta = [&](int t) {
+      if (t >= p.T) return;
+      const uint4* m = p.meta + 2 * (size_t)(4 * t + g);
+      na = __ldg(m);
+      nb = __ldg(reinterpret_cast<const uint2*>(m + 1));
+      nc = __ldg(m + 4);
+      nd = __ldg(reinterpret_cast<const uint2*>(m + 5));
+    };
+    fetch_meta(cluster);
+    int it = 0;
+    for (int t = cluster; t < p.T; t += n_clusters, ++it) {
+      const uint4 ma = na, mc = nc;
+      const uint2 mb = nb, md = nd;
+      fetch_meta(t + n_clusters);
+      ptx::mbar_wait(bar(B_ACC1_FULL0 + g), it & 1);
+      ptx::tc_fence_after();
+      ptx::tmem_ld16(tbase, va);
+      float* dst = out_h;
+      float a0 = 0.f, a1 = 0.f;
+      uint32_t em = 0, pm = 0;
+      bool regular = true;
+#pragma unroll 1
+      for (int s = 0; s < 4; ++s) {                        // columns [32s, 32s+32) of the block
+        if ((s & 1) == 0) {                                // a new sub-block: 4t + 2h + g, h = s >> 1
+          const bool h = s != 0;
+          regular = (h ? md.y : mb.y) == 0u;
+          dst = out_h + (size_t)(h ? md.x : mb.x) * HID;
+          em = h ? mc.x : ma.x;
+          pm = h ? mc.z : ma.z;
+          a0 = 0.f;
+          a1 = 0.f;
+        } else {
+          const bool h = s == 3;
+          em = h ? mc.y : ma.y;
+          pm = h ? mc.w : ma.w;
+        }
+        const uint32_t tcol = tbase + 32 * s;
+        ptx::tmem_ld_wait();
+        ptx::tmem_ld16(tcol + 16, vb);
+        if (__builtin_expect(regular, 1)) {
+          sum_chunk<FOLD>(va, em, pm, b1, a0, a1, dst);
+        } else if ((s & 1) == 0) {
+          const int sub = 4 * t + (s & 2) + g;
+          sum_irregular(tcol, p.desc + (size_t)sub * SUB, min(SUB, (int)p.n_rows - sub * SUB), b1, out_h);
+        }
+        ptx::tmem_ld_wait();
+        if (s != 3) ptx::tmem_ld16(tcol + 32, va);
+        if (__builtin_expect(regular, 1)) sum_chunk<FOLD>(vb, em >> 16, pm >> 16, b1, a0, a1, dst);
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive_cluster_relaxed(bar(B_ACC1_EMPTY0 + g), 0);
+    }
+  } else {
     // ===== MMA issuer: one thread of the leader CTA =====
     if (rank == 0) {
       const uint32_t idesc_n128 = ptx::umma_idesc_f16(256, 128);
@@ -362,6 +511,7 @@ segsum_tc_kernel(const TcParams p) {
       // +32 B per K=16 step inside an atom (encoded >>4 -> +2), +ATOM per 64 columns
       auto kadv = [](int k) -> uint64_t { return (uint64_t)(((k >> 2) * ATOM + (k & 3) * 32) >> 4); };
       constexpr uint64_t rows64 = (64 * 128) >> 4;      // operand rows 64.. of a CTA (N = 128 halves)
+      constexpr int KB1 = B1_COL / 16;                  // the b1 k-step of the W0 / A0 images
       int it = 0;
       for (int t = cluster; t < p.T; t += n_clusters, ++it) {
         // ---- layer 0: two hidden halves ----
@@ -384,8 +534,10 @@ segsum_tc_kernel(const TcParams p) {
         ptx::fence_acq_rel_cluster();
         ptx::tc_fence_after();
         if (lane == 0) {
+          if (FOLD) ptx::umma_f16_2cta(tmem + 256, dW0 + kadv(KB1), dA0 + kadv(KB1), idesc_n128, 0);
 #pragma unroll
-          for (int k = 0; k < 8; ++k) ptx::umma_f16_2cta(tmem + 256, dW1 + kadv(k), dA1 + kadv(k), idesc_n128, k > 0);
+          for (int k = 0; k < 8; ++k)
+            ptx::umma_f16_2cta(tmem + 256, dW1 + kadv(k), dA1 + kadv(k), idesc_n128, FOLD || k > 0);
         }
         __syncwarp();
         ptx::mbar_wait(bar(B_A1_FULL1), it & 1);
@@ -401,56 +553,14 @@ segsum_tc_kernel(const TcParams p) {
         if (it > 0) ptx::mbar_wait(bar(B_ACC1_EMPTY1), (it - 1) & 1);
         ptx::tc_fence_after();
         if (lane == 0) {
+          if (FOLD) ptx::umma_f16_2cta(tmem + 384, dW0 + kadv(KB1), dA0 + rows64 + kadv(KB1), idesc_n128, 0);
 #pragma unroll
           for (int k = 0; k < 16; ++k)
-            ptx::umma_f16_2cta(tmem + 384, dW1 + kadv(k), dA1 + rows64 + kadv(k), idesc_n128, k > 0);
+            ptx::umma_f16_2cta(tmem + 384, dW1 + kadv(k), dA1 + rows64 + kadv(k), idesc_n128, FOLD || k > 0);
           ptx::umma_commit_2cta(bar(B_ACC1_FULL1), 3);
         }
         __syncwarp();
       }
-    }
-  } else {
-    // ===== epi 1, group g: layer-1 block g = TMEM columns [256+128g, +128) =====
-    //   columns [0,64)   <-> rows [64g, 64g+64) of CTA 0  = sub-block 4t + g
-    //   columns [64,128) <-> rows [64g, 64g+64) of CTA 1  = sub-block 4t + 2 + g
-    const int q = warp & 3;
-    const int g = (warp - EPI_WARP0) >> 2;
-    const uint32_t lane_base = (uint32_t)(32 * q) << 16;
-    const int hu = rank * TILE + 32 * q + lane;   // hidden unit of this lane
-    const float b1 = p.b1[hu];
-    float* const out_h = p.out + hu;
-    int it = 0;
-    for (int t = cluster; t < p.T; t += n_clusters, ++it) {
-      // descriptors of both sub-blocks: lane j holds entries j and j+32 (two coalesced 256 B loads
-      // per sub-block, issued before the wait); the walk below broadcasts them with shuffles.
-      const uint2* d0 = p.desc + (size_t)(4 * t + g) * SUB;
-      const uint2* d1 = p.desc + (size_t)(4 * t + 2 + g) * SUB;
-      const uint2 e00 = __ldg(d0 + lane), e01 = __ldg(d0 + lane + 32);
-      const uint2 e10 = __ldg(d1 + lane), e11 = __ldg(d1 + lane + 32);
-      ptx::mbar_wait(bar(B_ACC1_FULL0 + g), it & 1);
-      ptx::tc_fence_after();
-#pragma unroll 1
-      for (int half = 0; half < 2; ++half) {
-        const int sub_row0 = (4 * t + 2 * half + g) * SUB;
-        const int nvalid = min(SUB, (int)p.n_rows - sub_row0);
-        const uint32_t tcol = tmem + lane_base + 256 + 128 * g + 64 * half;
-        const uint2 lo = half ? e10 : e00, hi = half ? e11 : e01;
-        int covered = 0, k = 0;
-        while (covered < nvalid) {
-          const uint2 sel = k < 32 ? lo : hi;
-          const unsigned dx = __shfl_sync(0xffffffffu, sel.x, k & 31);
-          const unsigned dy = __shfl_sync(0xffffffffu, sel.y, k & 31);
-          ++k;
-          const int c0 = dy & 0xff, n = (dy >> 8) & 0xff;
-          const float s = segment_relu_sum(tcol + c0, n, b1);
-          float* dst = out_h + (size_t)dx * HID;
-          if (dy >> 16) atomicAdd(dst, s); else *dst = s;
-          covered += n;
-        }
-      }
-      ptx::tc_fence_before();
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive_cluster_relaxed(bar(B_ACC1_EMPTY0 + g), 0);
     }
   }
 
@@ -458,15 +568,15 @@ segsum_tc_kernel(const TcParams p) {
   ptx::tc_fence_before();
   __syncthreads();
   ptx::cluster_sync();
-  if (warp == EPI_WARP0) ptx::tmem_dealloc_2cta(tmem, 512);
+  if (warp == EPI1_WARP0) ptx::tmem_dealloc_2cta(tmem, 512);
 }
 
 // ---------------------------------------------------------------------------------------------
-// pre-pass, one thread per 64-row sub-block: the list of (program, first column, length, partial)
-// pieces that tile the sub-block; and one thread per program: zero the output rows that receive
-// atomics (programs cut by a sub-block boundary) or nothing at all (empty programs).
-__global__ void tc_prepare_kernel(const int32_t* __restrict__ off, int P, int n_rows, int nsub, uint2* __restrict__ desc,
-                                  float* __restrict__ out) {
+// pre-pass, one thread per 64-row sub-block: bit masks of the last rows of the pieces that tile the
+// sub-block and of the partial ones, the first program, and (irregular sub-blocks only) the explicit
+// piece list; and one thread per program: zero the output rows that receive atomics (programs cut by a sub-block boundary) or nothing at all (empty programs).
+__global__ void tc_prepare_kernel(const int32_t* __restrict__ off, int P, int n_rows, int nsub, uint4* __restrict__ meta,
+                                  uint2* __restrict__ desc, float* __restrict__ out) {
   const int gid = blockIdx.x * blockDim.x + threadIdx.x;
   if (gid < nsub) {
     const int r0 = gid * tc::SUB, r1 = min(r0 + tc::SUB, n_rows);
@@ -475,18 +585,32 @@ __global__ void tc_prepare_kernel(const int32_t* __restrict__ off, int P, int n_
       const int mid = (lo + hi) >> 1;
       if (off[mid] <= r0) lo = mid; else hi = mid;
     }
-    uint2* d = desc + (size_t)gid * tc::SUB;
-    int p = lo, r = r0, k = 0;
-    while (r < r1) {
-      const int s = off[p], e = off[p + 1];
-      if (e > r) {                                // skips empty programs
-        const int ee = min(e, r1);
-        const unsigned partial = (s < r0 || e > r1) ? 1u : 0u;
-        d[k++] = make_uint2((unsigned)p, (unsigned)(r - r0) | ((unsigned)(ee - r) << 8) | (partial << 16));
-        r = ee;
+    uint64_t ends = 0, parts = 0;
+    int first = -1, last = -1, k = 0;
+    for (int pass = 0; pass < 2; ++pass) {        // pass 1 only for irregular sub-blocks: the explicit piece list
+      uint2* d = desc + (size_t)gid * tc::SUB;
+      int p = lo, r = r0;
+      k = 0;
+      while (r < r1) {
+        const int s = off[p], e = off[p + 1];
+        if (e > r) {                              // skips empty programs
+          const int ee = min(e, r1);
+          const unsigned partial = (s < r0 || e > r1) ? 1u : 0u;
+          if (pass) d[k] = make_uint2((unsigned)p, (unsigned)(r - r0) | ((unsigned)(ee - r) << 8) | (partial << 16));
+          ++k;
+          ends |= 1ull << (ee - 1 - r0);
+          parts |= (uint64_t)partial << (ee - 1 - r0);
+          if (first < 0) first = p;
+          last = p;
+          r = ee;
+        }
+        ++p;
       }
-      ++p;
+      if (k == 0 || last - first + 1 == k) break; // regular: pieces belong to consecutive programs
     }
+    const unsigned irregular = (k > 0 && last - first + 1 != k) ? 1u : 0u;
+    meta[2 * (size_t)gid] = make_uint4((unsigned)ends, (unsigned)(ends >> 32), (unsigned)parts, (unsigned)(parts >> 32));
+    meta[2 * (size_t)gid + 1] = make_uint4((unsigned)max(first, 0), irregular, 0u, 0u);
   }
   const int lane = threadIdx.x & 31;
   const int pbase = gid - lane;                   // 32 programs per warp
@@ -526,13 +650,23 @@ int tc_pack(vaex_model* m, const std::vector<float>& w0, cudaStream_t st) {
   std::vector<__half> i0(2 * W0_BYTES / 2, __float2half_rn(0.f)), i1(2 * W1_BYTES / 2);
   const std::vector<float>& w1 = m->host["segment_encoder.2.weight"].v;
   const std::vector<float>& b0 = m->host["segment_encoder.0.bias"].v;
+  const std::vector<float>& b1 = m->host["segment_encoder.2.bias"].v;
+  const bool fold = F + 2 <= B1_COL;                            // b1 as a 17th K step of layer 1
   for (int r = 0; r < 2; ++r)
     for (int row = 0; row < TILE; ++row) {
       const int h = r * TILE + row;
       __half* d0 = i0.data() + (size_t)r * (W0_BYTES / 2);
       __half* d1 = i1.data() + (size_t)r * (W1_BYTES / 2);
       for (int k = 0; k < F; ++k) d0[sw128_off(row, k) / 2] = h_clamp(w0[(size_t)h * F + k]);
-      d0[sw128_off(row, F) / 2] = h_clamp(b0[h]);            // bias column (X supplies the 1)
+      // bias columns (X supplies the 1s): hi + lo fp16 halves keep ~22 bits of the fp32 bias
+      const __half b0h = h_clamp(b0[h]);
+      d0[sw128_off(row, F) / 2] = b0h;
+      if (F + 1 < K0P) d0[sw128_off(row, F + 1) / 2] = h_clamp(b0[h] - __half2float(b0h));
+      if (fold) {
+        const __half b1h = h_clamp(b1[h]);
+        d0[sw128_off(row, B1_COL) / 2] = b1h;
+        d0[sw128_off(row, B1_COL + 1) / 2] = h_clamp(b1[h] - __half2float(b1h));
+      }
       for (int c = 0; c < HID; ++c) d1[sw128_off(row, c) / 2] = h_clamp(w1[(size_t)h * HID + hidden_of_col(c)]);
     }
   TcPack& t = m->tc;
@@ -543,7 +677,8 @@ int tc_pack(vaex_model* m, const std::vector<float>& w0, cudaStream_t st) {
   VAEX_CUDA(cudaMemcpyAsync(t.w1, i1.data(), 2 * W1_BYTES, cudaMemcpyHostToDevice, st));
   VAEX_CUDA(cudaMemcpyAsync(t.b1, m->host["segment_encoder.2.bias"].v.data(), HID * sizeof(float), cudaMemcpyHostToDevice, st));
   VAEX_CUDA(cudaStreamSynchronize(st));
-  VAEX_CUDA(cudaFuncSetAttribute(segsum_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_DYN));
+  VAEX_CUDA(cudaFuncSetAttribute(segsum_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_DYN));
+  VAEX_CUDA(cudaFuncSetAttribute(segsum_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_DYN));
   t.F = F;
   t.K0P = K0P;
   t.ready = true;
@@ -558,23 +693,27 @@ int segsum_tc_encode(vaex_model* m, const float* feats, const int32_t* off, int6
   const int T = (int)cdiv(R, PAIR);
   const int nsub = 4 * T;
   const int nprep = (int)std::max<int64_t>(P, nsub);
+  const size_t meta_bytes = 2 * sizeof(uint4) * (size_t)std::max(nsub, 1);
   const size_t desc_bytes = sizeof(uint2) * (size_t)std::max(nsub, 1) * SUB;
-  { int rc = m->tc_ws.ensure(desc_bytes + sizeof(uint32_t) * (size_t)std::max(T, 1) * 8); if (rc != VAEX_OK) return rc; }
-  uint2* desc = m->tc_ws.as<uint2>();
+  { int rc = m->tc_ws.ensure(meta_bytes + desc_bytes + sizeof(uint32_t) * (size_t)std::max(T, 1) * 8); if (rc != VAEX_OK) return rc; }
+  uint4* meta = m->tc_ws.as<uint4>();
+  uint2* desc = reinterpret_cast<uint2*>(reinterpret_cast<uint8_t*>(meta) + meta_bytes);
   uint32_t* rowmask = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(desc) + desc_bytes);
-  tc_prepare_kernel<<<(unsigned)cdiv(nprep, 256), 256, 0, st>>>(off, (int)P, (int)R, nsub, desc, segsum);
+  tc_prepare_kernel<<<(unsigned)cdiv(nprep, 256), 256, 0, st>>>(off, (int)P, (int)R, nsub, meta, desc, segsum);
   VAEX_LAUNCH_CHECK();
   if (T > 0) {
     TcParams prm;
-    prm.feats = feats; prm.off = off; prm.desc = desc;
+    prm.feats = feats; prm.off = off; prm.desc = desc; prm.meta = meta;
     prm.w0 = m->tc.w0; prm.w1 = m->tc.w1; prm.b1 = m->tc.b1;
     prm.out = segsum; prm.rowmask = rowmask; prm.n_rows = R; prm.P = (int)P; prm.T = T; prm.F = m->F;
-    prm.k0_steps = (m->F + 1 + 15) / 16;           // + the bias column
+    prm.k0_steps = (m->F + (m->F + 1 < K0P ? 2 : 1) + 15) / 16;   // + the bias hi/lo columns
+    const bool fold = m->F + 2 <= B1_COL;
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int clusters = std::max(1, std::min(sms / 2, T));
-    segsum_tc_kernel<<<2 * clusters, THREADS, SMEM_DYN, st>>>(prm);
+    if (fold) segsum_tc_kernel<true><<<2 * clusters, THREADS, SMEM_DYN, st>>>(prm);
+    else segsum_tc_kernel<false><<<2 * clusters, THREADS, SMEM_DYN, st>>>(prm);
     VAEX_LAUNCH_CHECK();
   }
   if (valid) {
