@@ -355,7 +355,7 @@ segsum_tc_kernel(const TcParams p) {
       if (lane == 0) reinterpret_cast<uint16_t*>(p.rowmask)[((size_t)t * 8 + rank * 4) * 2 + warp] = (uint16_t)nzmask;
       ptx::fence_proxy_async();
       __syncwarp();
-      if (lane == 0) ptx::mbar_arrive_cluster(bar(B_A0_FULL), 0);
+      if (lane == 0) ptx::mbar_arrive_cluster_relaxed(bar(B_A0_FULL), 0);
     };
     if (lane == 0) { prefetch(cluster + n_clusters); prefetch(cluster + 2 * n_clusters); }
     if (al16) {
@@ -428,7 +428,7 @@ segsum_tc_kernel(const TcParams p) {
         ptx::fence_proxy_async();
         ptx::tc_fence_before();
         __syncwarp();
-        if (lane == 0) ptx::mbar_arrive_cluster(bar(B_A1_FULL0 + g), 0);
+        if (lane == 0) ptx::mbar_arrive_cluster_relaxed(bar(B_A1_FULL0 + g), 0);
       }
     }
   } else if (warp < MMA_WARP) {
@@ -516,9 +516,8 @@ segsum_tc_kernel(const TcParams p) {
       for (int t = cluster; t < p.T; t += n_clusters, ++it) {
         // ---- layer 0: two hidden halves ----
         ptx::mbar_wait(bar(B_A0_FULL), it & 1);
-        ptx::fence_acq_rel_cluster();
         ptx::tc_fence_after();
-        if (lane == 0) {
+        if (ptx::elect_one()) {
           for (int k = 0; k < p.k0_steps; ++k)
             ptx::umma_f16_2cta(tmem + 0, dA0 + kadv(k), dW0 + kadv(k), idesc_n128, k > 0);
           ptx::umma_commit_2cta(bar(B_ACC0_FULL0), 3);
@@ -531,9 +530,8 @@ segsum_tc_kernel(const TcParams p) {
         // ---- layer 1, row block 0 (rows [0,64) of both CTAs): K half 0 then K half 1 ----
         if (it > 0) ptx::mbar_wait(bar(B_ACC1_EMPTY0), (it - 1) & 1);
         ptx::mbar_wait(bar(B_A1_FULL0), it & 1);
-        ptx::fence_acq_rel_cluster();
         ptx::tc_fence_after();
-        if (lane == 0) {
+        if (ptx::elect_one()) {
           if (FOLD) ptx::umma_f16_2cta(tmem + 256, dW0 + kadv(KB1), dA0 + kadv(KB1), idesc_n128, 0);
 #pragma unroll
           for (int k = 0; k < 8; ++k)
@@ -541,9 +539,8 @@ segsum_tc_kernel(const TcParams p) {
         }
         __syncwarp();
         ptx::mbar_wait(bar(B_A1_FULL1), it & 1);
-        ptx::fence_acq_rel_cluster();
         ptx::tc_fence_after();
-        if (lane == 0) {
+        if (ptx::elect_one()) {
 #pragma unroll
           for (int k = 8; k < 16; ++k) ptx::umma_f16_2cta(tmem + 256, dW1 + kadv(k), dA1 + kadv(k), idesc_n128, 1);
           ptx::umma_commit_2cta(bar(B_ACC1_FULL0), 3);
@@ -552,7 +549,7 @@ segsum_tc_kernel(const TcParams p) {
         // ---- layer 1, row block 1 (rows [64,128) of both CTAs) ----
         if (it > 0) ptx::mbar_wait(bar(B_ACC1_EMPTY1), (it - 1) & 1);
         ptx::tc_fence_after();
-        if (lane == 0) {
+        if (ptx::elect_one()) {
           if (FOLD) ptx::umma_f16_2cta(tmem + 384, dW0 + kadv(KB1), dA0 + rows64 + kadv(KB1), idesc_n128, 0);
 #pragma unroll
           for (int k = 0; k < 16; ++k)

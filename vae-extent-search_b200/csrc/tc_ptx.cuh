@@ -51,6 +51,17 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     if (++spins > (1u << 28)) __trap();
   }
 }
+// one lane of a converged warp (ptxas then treats the guarded code as single-threaded: no
+// per-instruction ELECT loops around tcgen05.mma)
+__device__ __forceinline__ bool elect_one() {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok));
+  return ok != 0;
+}
 __device__ __forceinline__ void fence_acq_rel_cluster() {
   asm volatile("fence.acq_rel.cluster;" ::: "memory");
 }
