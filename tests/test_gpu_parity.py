@@ -153,6 +153,35 @@ def test_segsum_mlp_properties_large():
     assert l2_err(h, a[:50000].cpu().numpy()) < 2e-4 and rel_err(h, a[:50000].cpu().numpy()) < TC_RTOL
 
 
+def test_segment_sums_tc_vs_simt_stress():
+    """The tcgen05 kernel's hand-offs (mbarriers, relaxed cluster arrivals, proxy fences) under
+    load: per-program segment sums against the fp32 SIMT kernels element by element, several
+    size mixes (many boundaries / long programs / empty programs), repeated launches bit-equal."""
+    torch.manual_seed(11)
+    net = vaex_b200.SegmentSumMLPModule(164, 256, 1).cuda().eval()
+    rng = np.random.default_rng(11)
+    mixes = {
+        "u1_32": rng.integers(1, 33, size=120000),
+        "tiny": rng.integers(1, 4, size=300000),
+        "with_empty": rng.integers(0, 9, size=200000),
+        "long": rng.integers(40, 300, size=6000),
+    }
+    for name, sizes in mixes.items():
+        sizes = sizes.astype(np.int32)
+        feats = torch.rand(int(sizes.sum()), 164, device="cuda", generator=torch.Generator("cuda").manual_seed(1))
+        feats = feats * (torch.rand(164, device="cuda") > 0.15)
+        st = torch.from_numpy(sizes).cuda()
+        ref = net.segment_sums(st, feats, flags=_lib.F_FORCE_SIMT)
+        got = net.segment_sums(st, feats)
+        scale = ref.abs().mean(dim=1, keepdim=True).clamp_min(1e-3)
+        err = ((got - ref).abs() / scale).max().item()
+        assert err < 5e-3, (name, err)                       # fp16 operands, element-wise vs the row's mean |S|
+        assert (got[torch.from_numpy(sizes == 0).cuda()] == 0).all(), name
+        if sizes.max() <= 64:                                # <= 2 addends per element: order-independent
+            for _ in range(4):
+                assert torch.equal(net.segment_sums(st, feats), got), name + ": not deterministic"
+
+
 def test_segment_offsets_scan():
     lib = _lib.load()
     for n in [0, 1, 5, 2048, 2049, 1000003]:

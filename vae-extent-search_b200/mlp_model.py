@@ -185,6 +185,24 @@ class SegmentSumMLPModule(torch.nn.Module):
                                                 _lib.ptr(scores), flags, st))
         return scores.squeeze()
 
+    def segment_sums(self, segment_sizes, features, flags=0, fea_norm_vec=None):
+        """[n_programs, hidden] per-program sums of the row encoder's output -- the tensor
+        `scatter_add(...)` produces at mlp_model.py:200-208 (and SegmentVAE.segment_sum,
+        scripts/vae_experiments/models/vae.py:68-85)."""
+        if not features.is_cuda:
+            raise _lib.VaexError("SegmentSumMLPModule.segment_sums needs CUDA tensors (no CPU fallback)")
+        lib = _lib.load()
+        m = self.packed(fea_norm_vec)
+        feats = features.detach().contiguous().float()
+        sizes = segment_sizes.detach().to(device=feats.device, dtype=torch.int32).contiguous()
+        n = sizes.shape[0]
+        offsets = torch.empty(n + 1, dtype=torch.int32, device=feats.device)
+        out = torch.empty(n, self.segment_encoder[0].out_features, dtype=torch.float32, device=feats.device)
+        st = _lib.stream_ptr()
+        _lib.check(lib.vaex_segment_offsets(_lib.ptr(sizes), n, _lib.ptr(offsets), st))
+        _lib.check(lib.vaex_segsum_encode(m.h, _lib.ptr(feats), _lib.ptr(offsets), n, feats.shape[0], _lib.ptr(out), flags, st))
+        return out
+
 
 def make_net(params):
     if params["type"] == "SegmentSumMLP":
