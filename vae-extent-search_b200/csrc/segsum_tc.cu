@@ -369,7 +369,7 @@ segsum_tc_kernel(const TcParams p) {
       int it = 0;
       for (int t = cluster; t < p.T; t += n_clusters, ++it) {
         if (lane == 0) prefetch(t + 3 * n_clusters);
-        if (it > 0) ptx::mbar_wait(bar(B_A0_EMPTY), (it - 1) & 1);      // layer 0 of the previous tile has read A0
+        if (it > 0) ptx::mbar_wait_role(bar(B_A0_EMPTY), (it - 1) & 1, warp == 0, 1, 32 * LOAD_WARPS);   // layer 0 of the previous tile has read A0
         uint32_t nz = ld.commit(0, lane, x, A0w, a0_tab);
         ld.issue(FAST_BATCH, lane, x);
         nz |= ld.commit(FAST_BATCH, lane, x, A0w, a0_tab);
@@ -382,7 +382,7 @@ segsum_tc_kernel(const TcParams p) {
     } else {
       int it = 0;
       for (int t = cluster; t < p.T; t += n_clusters, ++it) {
-        if (it > 0) ptx::mbar_wait(bar(B_A0_EMPTY), (it - 1) & 1);
+        if (it > 0) ptx::mbar_wait_role(bar(B_A0_EMPTY), (it - 1) & 1, warp == 0, 1, 32 * LOAD_WARPS);
         const int64_t row0 = (int64_t)t * PAIR + rank * TILE;
         publish(t, al8 ? load_convert_rows<2>(p, A0, row0, warp * ROWS, lane) : load_convert_rows<1>(p, A0, row0, warp * ROWS, lane));
       }
@@ -408,8 +408,11 @@ segsum_tc_kernel(const TcParams p) {
     for (int t = cluster; t < p.T; t += n_clusters, ++it) {
 #pragma unroll 1
       for (int g = 0; g < 2; ++g) {                        // hidden half g = acc0 columns [128g, 128g+128)
-        ptx::mbar_wait(bar(B_ACC0_FULL0 + g), it & 1);
-        if (g == 0 && it > 0) ptx::mbar_wait(bar(B_ACC1_FULL1), (it - 1) & 1);   // layer 1 of the previous tile has read A1
+        if (q == 0) {
+          ptx::mbar_wait(bar(B_ACC0_FULL0 + g), it & 1);
+          if (g == 0 && it > 0) ptx::mbar_wait(bar(B_ACC1_FULL1), (it - 1) & 1);   // layer 1 of the previous tile has read A1
+        }
+        ptx::bar_sync(2, 128);
         ptx::tc_fence_after();
         const uint32_t tcol = tmem + lane_base + 128 * g;
         uint32_t va[32], vb[32];
@@ -463,7 +466,7 @@ segsum_tc_kernel(const TcParams p) {
       const uint4 ma = na, mc = nc;
       const uint2 mb = nb, md = nd;
       fetch_meta(t + n_clusters);
-      ptx::mbar_wait(bar(B_ACC1_FULL0 + g), it & 1);
+      ptx::mbar_wait_role(bar(B_ACC1_FULL0 + g), it & 1, q == 0, 3 + g, 128);
       ptx::tc_fence_after();
       ptx::tmem_ld16(tbase, va);
       float* dst = out_h;

@@ -62,6 +62,17 @@ __device__ __forceinline__ bool elect_one() {
       : "=r"(ok));
   return ok != 0;
 }
+// named CTA barrier among `nthreads` threads (ids 1..15; 0 is __syncthreads)
+__device__ __forceinline__ void bar_sync(uint32_t id, uint32_t nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+// One warp of a role polls the mbarrier, the role's other warps park on a named barrier: a
+// sleeping mbarrier waiter is woken by every barrier event of the CTA and burns issue slots on
+// each re-check, a bar.sync waiter does not.
+__device__ __forceinline__ void mbar_wait_role(uint32_t bar, uint32_t parity, bool poller, uint32_t id, uint32_t nthreads) {
+  if (poller) mbar_wait(bar, parity);
+  bar_sync(id, nthreads);
+}
 __device__ __forceinline__ void fence_acq_rel_cluster() {
   asm volatile("fence.acq_rel.cluster;" ::: "memory");
 }
