@@ -6,11 +6,19 @@
 //   score = y2 . wd + bd               (+ sigmoid, + -inf for invalid programs)
 //   (SegmentSumMLPModule.forward, python/tvm/auto_scheduler/cost_model/mlp_model.py:210-221)
 //
-// One CTA pair (cta_group::2) per 256 programs: each CTA owns 128 programs (TMEM lanes) and half
-// of the output units of both 256x256 weights (resident, 128 KB fp16).  The A operand buffer
-// (64 KB) first holds fp16(y0), then fp16(y1); fp32 y1 is parked in TMEM (over the dead layer-0
-// accumulator) for the second residual, so no intermediate touches HBM.  This kernel is ~7 % of
-// the path's FLOPs; phases are separated by cluster barriers instead of a warp-specialised pipe.
+// One persistent CTA pair (cta_group::2) per 256 programs per step: each CTA owns 128 programs
+// (TMEM lanes) and half of the output units of both 256x256 weights (resident, 128 KB fp16).
+// A worker thread owns one program row and one 128-column half of it end to end:
+//   A. its 512 B of S arrive as 16 LDG.256 (issued during the previous step's second GEMM),
+//      go as fp32 into TMEM columns [0,256) (the residual) and as fp16 into the A operand (64 KB)
+//   B. GEMM 0 -> TMEM columns [256,512)
+//   C. y1 = relu(acc + bl0) + residual: fp32 back over the residual, fp16 over the A operand
+//   D. GEMM 1 -> the same accumulator columns
+//   E. y2 = relu(acc + bl1) + residual, dotted with wd in registers
+// so no intermediate touches HBM and S is read exactly once.  Warps 0-7 are workers (lane
+// quarter = warp % 4, column half = warp / 4), warp 8 of the leader CTA issues the MMAs; hand-offs
+// are mbarriers (warp arrivals -> issuer, tcgen05.commit multicast -> workers), no cluster barrier
+// inside the loop.
 #include <algorithm>
 #include <vector>
 
@@ -26,7 +34,8 @@ constexpr int W_BYTES = 4 * ATOM;                 // [128 units x 256 k] fp16, K
 constexpr int WL0_OFF = 0, WL1_OFF = W_BYTES, A_OFF = 2 * W_BYTES;
 constexpr int SMEM_TILES = 3 * W_BYTES;           // 196608
 constexpr int SMEM_DYN = SMEM_TILES + 1024;
-constexpr int THREADS = 256;
+constexpr int WORKERS = 256, THREADS = 288;     // 8 worker warps + the MMA issuer
+enum { B_Y0 = 0, B_ACC0, B_Y1, B_ACC1, B_COUNT };
 
 __host__ __device__ inline uint32_t sw128_off(int row, int k) {
   return (uint32_t)((k >> 6) * ATOM + (row >> 3) * 1024 + (row & 7) * 128 + ((((k & 63) >> 3) ^ (row & 7)) << 4) +
@@ -61,14 +70,22 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&v)[32
       : "memory");
 }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+struct F8 { float v[8]; };
+__device__ __forceinline__ F8 ldg_stream_f8(const float* p) {   // one full 32 B sector per lane
+  F8 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(r.v[0]), "=f"(r.v[1]), "=f"(r.v[2]), "=f"(r.v[3]), "=f"(r.v[4]), "=f"(r.v[5]), "=f"(r.v[6]), "=f"(r.v[7])
+               : "l"(p));
+  return r;
+}
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(hd::THREADS, 1)
 head_tc_kernel(const HeadParams p) {
   using namespace hd;
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bars[2];
+  __shared__ __align__(8) uint64_t bars[B_COUNT];
   __shared__ uint32_t tmem_base_slot;
-  __shared__ float s_bl0[HID], s_bl1[HID], s_wd[HID], s_ns[HID], s_nb[HID];
+  __shared__ __align__(16) float s_bl0[HID], s_bl1[HID], s_wd[HID], s_ns[HID], s_nb[HID];
   __shared__ float s_dot[TILE];
 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -76,12 +93,15 @@ head_tc_kernel(const HeadParams p) {
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   const uint32_t rank = ptx::cluster_ctarank();
   const int cluster = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
-  const uint32_t bar_l0 = ptx::smem_u32(&bars[0]), bar_l1 = ptx::smem_u32(&bars[1]);
+  const uint32_t bar0 = ptx::smem_u32(&bars[0]);
+  auto bar = [&](int i) { return bar0 + 8u * i; };
   const bool has_norm = p.nscale != nullptr;
 
   if (threadIdx.x == 0) {
-    ptx::mbar_init(bar_l0, 1);
-    ptx::mbar_init(bar_l1, 1);
+    ptx::mbar_init(bar(B_Y0), 16);      // 8 worker warps x 2 CTAs
+    ptx::mbar_init(bar(B_ACC0), 1);
+    ptx::mbar_init(bar(B_Y1), 16);
+    ptx::mbar_init(bar(B_ACC1), 1);
     ptx::fence_mbar_init();
   }
   if (warp == 1) ptx::tmem_alloc_2cta(ptx::smem_u32(&tmem_base_slot), 512);
@@ -104,119 +124,158 @@ head_tc_kernel(const HeadParams p) {
   ptx::tc_fence_after();
   const uint32_t tmem = tmem_base_slot;
 
-  const uint32_t idesc = ptx::umma_idesc_f16(256, 256);
-  const uint64_t dWl0 = ptx::umma_desc_sw128(sbase + WL0_OFF), dWl1 = ptx::umma_desc_sw128(sbase + WL1_OFF);
-  const uint64_t dA = ptx::umma_desc_sw128(sbase + A_OFF);
-  auto kadv = [](int k) -> uint64_t { return (uint64_t)(((k >> 2) * ATOM + (k & 3) * 32) >> 4); };
+  if (warp < 8) {
+    // ===== workers =====
+    const int q = warp & 3, ch = warp >> 2;          // TMEM lane quarter, column half
+    const uint32_t lane_base = (uint32_t)(32 * q) << 16;
+    const int row = 32 * q + lane;                   // program row (TMEM lane) of this thread
+    const uint32_t a_row = sbase + A_OFF + (row >> 3) * 1024 + (row & 7) * 128;
+    const int sw = row & 7;
+    const int col0 = 128 * ch;
+    const uint32_t t_res = tmem + lane_base + col0, t_acc = tmem + lane_base + 256 + col0;
+    const float bd = p.bd[0];
+    F8 pf[16];                                       // this thread's 128 floats of the next step
 
-  const int q = warp & 3, ch = warp >> 2;          // TMEM lane quarter, column half of the epilogues
-  const uint32_t lane_base = (uint32_t)(32 * q) << 16;
-  const int erow = 32 * q + lane;                  // program row (TMEM lane) of this thread in the epilogues
-  const uint32_t a_row = sbase + A_OFF + (erow >> 3) * 1024 + (erow & 7) * 128;
-  const int sw = erow & 7;
-  const float bd = p.bd[0];
-
-  int it = 0;
-  for (int t = cluster; t < p.T; t += n_clusters, ++it) {
-    const int64_t prog0 = (int64_t)t * PAIR + rank * TILE;
-    // ---- 1. y0 = norm(S) -> fp16 A operand: warp w converts rows [16w, 16w+16), 8 B stores ----
-#pragma unroll 4
-    for (int r = 0; r < 16; ++r) {
-      const int row = warp * 16 + r;
-      const int64_t prog = prog0 + row;
+    auto fetch = [&](int t) {
+      const int64_t prog = (int64_t)t * PAIR + rank * TILE + row;
+      if (t < p.T && prog < p.P) {
+        const float* src = p.S + prog * HID + col0;
 #pragma unroll
-      for (int hh = 0; hh < 2; ++hh) {
-        const int c = (lane + 32 * hh) * 4;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (prog < p.P) v = __ldg(reinterpret_cast<const float4*>(p.S + prog * HID + c));
-        if (has_norm) {
-          v.x = v.x * s_ns[c] + s_nb[c]; v.y = v.y * s_ns[c + 1] + s_nb[c + 1];
-          v.z = v.z * s_ns[c + 2] + s_nb[c + 2]; v.w = v.w * s_ns[c + 3] + s_nb[c + 3];
-        }
-        ptx::sts_v2(sbase + A_OFF + sw128_off(row, c), ptx::cvt_h2_sat(v.x, v.y), ptx::cvt_h2_sat(v.z, v.w));
+        for (int j = 0; j < 16; ++j) pf[j] = ldg_stream_f8(src + 8 * j);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+#pragma unroll
+          for (int e = 0; e < 8; ++e) pf[j].v[e] = 0.f;
       }
-    }
-    ptx::fence_proxy_async();
-    ptx::tc_fence_before();
-    ptx::cluster_sync();
-    // ---- 2. layer l0 ----
-    if (rank == 0 && threadIdx.x == 0) {
-      ptx::tc_fence_after();
-#pragma unroll
-      for (int k = 0; k < 16; ++k) ptx::umma_f16_2cta(tmem, dA + kadv(k), dWl0 + kadv(k), idesc, k > 0);
-      ptx::umma_commit_2cta(bar_l0, 3);
-    }
-    ptx::mbar_wait(bar_l0, it & 1);
-    ptx::tc_fence_after();
-    // ---- 3. y1 = relu(acc0 + bl0) + y0 -> fp32 back into TMEM, fp16 into A ----
-    const int64_t eprog = prog0 + erow;
-    const float* srow = p.S + (eprog < p.P ? eprog : 0) * HID;
-#pragma unroll 1
-    for (int c4 = 0; c4 < 4; ++c4) {
-      const int c = ch * 4 + c4;                    // 32-column chunk
-      uint32_t v[32];
-      ptx::tmem_ld32(tmem + lane_base + 32 * c, v);
-      ptx::tmem_ld_wait();
-#pragma unroll
-      for (int j4 = 0; j4 < 8; ++j4) {
-        float4 y0 = __ldg(reinterpret_cast<const float4*>(srow + 32 * c + 4 * j4));
-        const float yy[4] = {y0.x, y0.y, y0.z, y0.w};
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const int col = 32 * c + 4 * j4 + e;
-          float r0 = yy[e];
-          if (has_norm) r0 = r0 * s_ns[col] + s_nb[col];
-          v[4 * j4 + e] = __float_as_uint(fmaxf(__uint_as_float(v[4 * j4 + e]) + s_bl0[col], 0.f) + r0);
-        }
-      }
-      tmem_st32(tmem + lane_base + 32 * c, v);
-      const uint32_t base = a_row + (c >> 1) * ATOM;
+    };
+    auto prefetch_l2 = [&](int t) {                  // this warp's 16 KB slice of a later step
+      if (lane != 0 || t >= p.T) return;
+      const int64_t r0 = (int64_t)t * PAIR + rank * TILE + warp * 16;
+      const int64_t nr = min((int64_t)16, (int64_t)p.P - r0);
+      if (nr > 0) ptx::prefetch_l2_bulk(p.S + r0 * HID, (uint32_t)(nr * HID * 4));
+    };
+    // fp32 values of 32 columns -> 64 B of the fp16 A operand (columns [col0 + 32c, +32))
+    auto pack32 = [&](const uint32_t (&v)[32], int c) {
+      const int cc = 4 * ch + c;                     // 32-column chunk of the row
+      const uint32_t base = a_row + (cc >> 1) * ATOM;
 #pragma unroll
       for (int m = 0; m < 4; ++m)
-        ptx::sts_v4(base + ((((c & 1) * 4 + m) ^ sw) << 4),
+        ptx::sts_v4(base + ((((cc & 1) * 4 + m) ^ sw) << 4),
                     ptx::cvt_h2_sat(__uint_as_float(v[8 * m]), __uint_as_float(v[8 * m + 1])),
                     ptx::cvt_h2_sat(__uint_as_float(v[8 * m + 2]), __uint_as_float(v[8 * m + 3])),
                     ptx::cvt_h2_sat(__uint_as_float(v[8 * m + 4]), __uint_as_float(v[8 * m + 5])),
                     ptx::cvt_h2_sat(__uint_as_float(v[8 * m + 6]), __uint_as_float(v[8 * m + 7])));
-    }
-    tmem_st_wait();
-    ptx::fence_proxy_async();
-    ptx::tc_fence_before();
-    ptx::cluster_sync();
-    // ---- 4. layer l1 ----
-    if (rank == 0 && threadIdx.x == 0) {
+    };
+    auto publish = [&](int b) {                      // operand + TMEM writes of this warp -> issuer
+      tmem_st_wait();
+      ptx::fence_proxy_async();
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive_cluster_relaxed(bar(b), 0);
+    };
+
+    prefetch_l2(cluster + n_clusters);
+    fetch(cluster);
+    int it = 0;
+    for (int t = cluster; t < p.T; t += n_clusters, ++it) {
+      prefetch_l2(t + 2 * n_clusters);
+      // ---- A. y0 = norm(S): fp32 -> TMEM residual, fp16 -> A operand ----
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          float x = pf[4 * c + (j >> 3)].v[j & 7];
+          if (has_norm) x = x * s_ns[col0 + 32 * c + j] + s_nb[col0 + 32 * c + j];
+          v[j] = __float_as_uint(x);
+        }
+        tmem_st32(t_res + 32 * c, v);
+        pack32(v, c);
+      }
+      publish(B_Y0);
+      // ---- C. y1 = relu(acc + bl0) + y0 -> residual (fp32) and A operand (fp16) ----
+      ptx::mbar_wait(bar(B_ACC0), it & 1);
       ptx::tc_fence_after();
-#pragma unroll
-      for (int k = 0; k < 16; ++k) ptx::umma_f16_2cta(tmem + 256, dA + kadv(k), dWl1 + kadv(k), idesc, k > 0);
-      ptx::umma_commit_2cta(bar_l1, 3);
-    }
-    ptx::mbar_wait(bar_l1, it & 1);
-    ptx::tc_fence_after();
-    // ---- 5. y2 = relu(acc1 + bl1) + y1; score = y2 . wd + bd ----
-    float dot = 0.f;
 #pragma unroll 1
-    for (int c4 = 0; c4 < 4; ++c4) {
-      const int c = ch * 4 + c4;
-      uint32_t v[32], y1[32];
-      ptx::tmem_ld32(tmem + lane_base + 256 + 32 * c, v);
-      ptx::tmem_ld32(tmem + lane_base + 32 * c, y1);
-      ptx::tmem_ld_wait();
+      for (int c = 0; c < 4; ++c) {
+        uint32_t v[32], r[32];
+        ptx::tmem_ld32(t_acc + 32 * c, v);
+        ptx::tmem_ld32(t_res + 32 * c, r);
+        ptx::tmem_ld_wait();
+        const float4* b4 = reinterpret_cast<const float4*>(s_bl0 + col0 + 32 * c);
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        const float y2 = fmaxf(__uint_as_float(v[j]) + s_bl1[32 * c + j], 0.f) + __uint_as_float(y1[j]);
-        dot = fmaf(y2, s_wd[32 * c + j], dot);
+        for (int j4 = 0; j4 < 8; ++j4) {
+          const float4 b = b4[j4];
+          v[4 * j4 + 0] = __float_as_uint(fmaxf(__uint_as_float(v[4 * j4 + 0]) + b.x, 0.f) + __uint_as_float(r[4 * j4 + 0]));
+          v[4 * j4 + 1] = __float_as_uint(fmaxf(__uint_as_float(v[4 * j4 + 1]) + b.y, 0.f) + __uint_as_float(r[4 * j4 + 1]));
+          v[4 * j4 + 2] = __float_as_uint(fmaxf(__uint_as_float(v[4 * j4 + 2]) + b.z, 0.f) + __uint_as_float(r[4 * j4 + 2]));
+          v[4 * j4 + 3] = __float_as_uint(fmaxf(__uint_as_float(v[4 * j4 + 3]) + b.w, 0.f) + __uint_as_float(r[4 * j4 + 3]));
+        }
+        tmem_st32(t_res + 32 * c, v);
+        pack32(v, c);
+      }
+      publish(B_Y1);
+      // the next step's rows stream in while GEMM 1 runs
+      fetch(t + n_clusters);
+      // ---- E. y2 = relu(acc + bl1) + y1; score = y2 . wd + bd ----
+      ptx::mbar_wait(bar(B_ACC1), it & 1);
+      ptx::tc_fence_after();
+      float dot0 = 0.f, dot1 = 0.f;
+#pragma unroll 1
+      for (int c = 0; c < 8; ++c) {
+        uint32_t v[16], r[16];
+        ptx::tmem_ld16(t_acc + 16 * c, v);
+        ptx::tmem_ld16(t_res + 16 * c, r);
+        ptx::tmem_ld_wait();
+        const float4* b4 = reinterpret_cast<const float4*>(s_bl1 + col0 + 16 * c);
+        const float4* w4 = reinterpret_cast<const float4*>(s_wd + col0 + 16 * c);
+#pragma unroll
+        for (int j4 = 0; j4 < 4; ++j4) {
+          const float4 b = b4[j4], w = w4[j4];
+          dot0 = fmaf(fmaxf(__uint_as_float(v[4 * j4 + 0]) + b.x, 0.f) + __uint_as_float(r[4 * j4 + 0]), w.x, dot0);
+          dot1 = fmaf(fmaxf(__uint_as_float(v[4 * j4 + 1]) + b.y, 0.f) + __uint_as_float(r[4 * j4 + 1]), w.y, dot1);
+          dot0 = fmaf(fmaxf(__uint_as_float(v[4 * j4 + 2]) + b.z, 0.f) + __uint_as_float(r[4 * j4 + 2]), w.z, dot0);
+          dot1 = fmaf(fmaxf(__uint_as_float(v[4 * j4 + 3]) + b.w, 0.f) + __uint_as_float(r[4 * j4 + 3]), w.w, dot1);
+        }
+      }
+      const float dot = dot0 + dot1;
+      if (ch == 1) s_dot[row] = dot;
+      ptx::tc_fence_before();
+      ptx::bar_sync(1, WORKERS);
+      const int64_t prog = (int64_t)t * PAIR + rank * TILE + row;
+      if (ch == 0 && prog < p.P) {
+        float s = dot + s_dot[row] + bd;
+        if (p.sigmoid) s = 1.f / (1.f + expf(-s));
+        if (p.valid && !p.valid[prog]) s = -INFINITY;
+        p.scores[prog] = s;
       }
     }
-    if (ch == 1) s_dot[erow] = dot;
-    ptx::tc_fence_before();
-    __syncthreads();
-    if (ch == 0 && eprog < p.P) {
-      float s = dot + s_dot[erow] + bd;
-      if (p.sigmoid) s = 1.f / (1.f + expf(-s));
-      if (p.valid && !p.valid[eprog]) s = -INFINITY;
-      p.scores[eprog] = s;
+  } else if (rank == 0) {
+    // ===== MMA issuer (leader CTA) =====
+    const uint32_t idesc = ptx::umma_idesc_f16(256, 256);
+    const uint64_t dWl0 = ptx::umma_desc_sw128(sbase + WL0_OFF), dWl1 = ptx::umma_desc_sw128(sbase + WL1_OFF);
+    const uint64_t dA = ptx::umma_desc_sw128(sbase + A_OFF);
+    auto kadv = [](int k) -> uint64_t { return (uint64_t)(((k >> 2) * ATOM + (k & 3) * 32) >> 4); };
+    int it = 0;
+    for (int t = cluster; t < p.T; t += n_clusters, ++it) {
+      ptx::mbar_wait(bar(B_Y0), it & 1);
+      ptx::tc_fence_after();
+      if (ptx::elect_one()) {
+#pragma unroll
+        for (int k = 0; k < 16; ++k) ptx::umma_f16_2cta(tmem + 256, dA + kadv(k), dWl0 + kadv(k), idesc, k > 0);
+        ptx::umma_commit_2cta(bar(B_ACC0), 3);
+      }
+      __syncwarp();
+      ptx::mbar_wait(bar(B_Y1), it & 1);
+      ptx::tc_fence_after();
+      if (ptx::elect_one()) {
+#pragma unroll
+        for (int k = 0; k < 16; ++k) ptx::umma_f16_2cta(tmem + 256, dA + kadv(k), dWl1 + kadv(k), idesc, k > 0);
+        ptx::umma_commit_2cta(bar(B_ACC1), 3);
+      }
+      __syncwarp();
     }
-    // the next tile's first cluster barrier orders these TMEM / smem reads before its MMAs
   }
 
   ptx::tc_fence_before();
