@@ -302,6 +302,13 @@ def main_vaex(args):
         if not peak:
             peak, peak_src = 1400.0, "fallback (B200_PROFILING.md: ~1.4 PFLOP/s sustained)"
         ach = rows * FLOP_PER_ROW / (kms * 1e-3) / 1e12
+        traffic = None          # dram read+write bytes per launch of the same kernel/workload from the committed ncu capture
+        try:
+            tr = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))["segsum_tc_kernel"]
+            if tr["rows"] == rows and tr["programs"] == P:
+                traffic = tr["dram_bytes_read"] + tr["dram_bytes_write"]
+        except Exception:
+            pass
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_max, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16xf16->f32",
@@ -311,7 +318,7 @@ def main_vaex(args):
                        "parallelism": "programs sharded over %d GPU(s); top-k all-gather only" % world},
             "e2e": e2e, "gpu_launches": int(launches), "clocks": sampler.summary(),
             "roofline": {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
-                         "traffic": None, "kernel": "segsum_tc_kernel (fused row encoder + segment sum)",
+                         "traffic": traffic, "kernel": "segsum_tc_kernel (fused row encoder + segment sum)",
                          "kernel_ms": kms, "flop_per_launch": rows * FLOP_PER_ROW, "peak_source": peak_src,
                          "hbm_gbs_algorithmic": (rows * F * 4 + P * H * 4) / (kms * 1e-3) / 1e9},
         }
