@@ -46,7 +46,12 @@ enum {
   VAEX_KIND_EXTENT_VAE = 2,
   /* VAECostPredictor (extent family), utils/model.py:86-273.
    * dims = {input_dim D, hidden H, latent L, predictor_hidden PH} */
-  VAEX_KIND_COST_PREDICTOR = 3
+  VAEX_KIND_COST_PREDICTOR = 3,
+  /* SegmentVAE, scripts/vae_experiments/models/vae.py:16-137.  dims = {input_dim F, hidden H, latent L} */
+  VAEX_KIND_SEGMENT_VAE = 4,
+  /* VAECostPredictor (segment family), scripts/vae_experiments/models/regression.py:11-185.
+   * dims = {input_dim F, hidden H, latent L, predictor_hidden PH, predictor_layers} */
+  VAEX_KIND_SEGMENT_COST = 5
 };
 
 /* flags for vaex_segsum_mlp_forward */
@@ -133,6 +138,19 @@ int vaex_cost_grad_z(vaex_model_t h, const float* z_dev, int64_t n, float* cost_
 /* multi-step ascent z += lr * dcost/dz (new surface, BASELINE config 3) */
 int vaex_latent_ascent(vaex_model_t h, float* z_inout_dev, int64_t n, int32_t steps, float lr,
                        float* cost_dev, void* stream);
+
+/* ---- segment-VAE family (eval mode: BatchNorm folded to affines, Dropout = identity) -------- */
+/* SegmentVAE.forward steps 1-3 (vae.py:113-128) / VAECostPredictor.encode (regression.py:82-101):
+ * row encoder -> segment sum -> norm -> residual l0, l1 -> fc_mean, fc_logvar.
+ * mean_dev, logvar_dev fp32 [n_programs, L]; segsum_dev_or_null fp32 [n_programs, H] receives the
+ * raw segment sums (the reference returns them as `segment_sum_vec`).  Kinds 4 and 5. */
+int vaex_segvae_encode(vaex_model_t h, const float* feats_dev, const int32_t* seg_offsets_dev,
+                       int64_t n_programs, int64_t n_rows, float* mean_dev, float* logvar_dev_or_null,
+                       float* segsum_dev_or_null, int flags, void* stream);
+/* SegmentVAE.decode (vae.py:109-111): z [n, L] -> reconstructed segment-sum vector [n, H].  Kind 4. */
+int vaex_segvae_decode(vaex_model_t h, const float* z_dev, int64_t n, float* recon_dev, void* stream);
+/* VAECostPredictor.predict_cost (regression.py:109-111): z [n, L] -> cost [n].  Kind 5. */
+int vaex_segcost_predict(vaex_model_t h, const float* z_dev, int64_t n, float* cost_dev, void* stream);
 
 /* ---- top-k (util_select_topk, utils/select.py:54-81) -------------------------------------- */
 /* k largest of scores[n] restricted to mask (uint8, 1 = eligible; NULL = all), ordered by

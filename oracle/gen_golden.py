@@ -150,6 +150,55 @@ def gen_select(ns):
         rem_prog=np.array(sorted(rem_prog), np.int64), **sd_np(reg, "reg."))
 
 
+def gen_segment_family(ns):
+    """a7/a8 with the reference's *shipped trained* checkpoints (real BatchNorm running stats):
+    SegmentVAE = model_final/checkpoints/vae_small/vae_rank10_h256_l32_*.pt, segment
+    VAECostPredictor = for_inference/vae_latent_augmented_best.pth (carries its fea_norm_vec)."""
+    ref = os.environ.get("VAEX_REFERENCE_ROOT", "/root/reference")
+    rng = np.random.default_rng(2024)
+    progs = synth_programs(rng, 67, zero_frac=0.0)
+    sizes = np.array([len(p) for p in progs], np.int32)
+    raw = np.concatenate(progs, 0)
+    # --- SegmentVAE
+    ck = torch.load(os.path.join(ref, "scripts/pre_experiments/model_final/checkpoints/vae_small/"
+                                      "vae_rank10_h256_l32_b5e-04_lr5e-04.pt"), map_location="cpu", weights_only=False)
+    cfg = ck["config"]
+    vae = ns.seg_vae.SegmentVAE(164, hidden_dim=cfg["hidden_dim"], latent_dim=cfg["latent_dim"])
+    vae.load_state_dict(ck["model_state_dict"])
+    vae.eval()
+    feats = torch.from_numpy(raw / 25.0)
+    with torch.no_grad():
+        h = vae.segment_encoder(feats)
+        S = vae.segment_sum(torch.from_numpy(sizes), h)
+        mean, logvar = vae.encode(S)
+        recon = vae.decode(mean)
+        torch.manual_seed(5)
+        fm, fl, fz, frecon, fS = vae(torch.from_numpy(sizes), feats, use_mean=True)   # z = mean + eps (logvar forced to 0)
+    np.savez_compressed(os.path.join(OUT, "segment_vae.npz"), feats=feats.numpy(), sizes=sizes, segsum=S.numpy(),
+                        mean=mean.numpy(), logvar=logvar.numpy(), recon=recon.numpy(),
+                        fwd_eps=(fz - fm).numpy(), fwd_logvar=fl.numpy(), fwd_recon=frecon.numpy(),
+                        hidden=cfg["hidden_dim"], latent=cfg["latent_dim"], **sd_np(vae))
+    # --- segment VAECostPredictor
+    ck = torch.load(os.path.join(ref, "scripts/pre_experiments/for_inference/vae_latent_augmented_best.pth"),
+                    map_location="cpu", weights_only=False)
+    cfg = ck["config"]
+    reg = ns.seg_reg.VAECostPredictor(cfg["input_dim"], cfg["hidden_dim"], cfg["latent_dim"], cfg["predictor_hidden"],
+                                      cfg["predictor_layers"], cfg["dropout"])
+    reg.load_state_dict(ck["model_state_dict"])
+    reg.eval()
+    norm = np.asarray(ck["fea_norm_vec"], np.float32).reshape(-1)
+    norm = np.where(norm == 0, 1.0, norm).astype(np.float32)
+    featn = torch.from_numpy(raw / norm)
+    with torch.no_grad():
+        cost, mean, logvar, z = reg(torch.from_numpy(sizes), featn, use_mean=True)
+        zt = torch.randn(33, cfg["latent_dim"], generator=torch.Generator().manual_seed(6))
+        cost_z = reg.predict_cost(zt)
+    np.savez_compressed(os.path.join(OUT, "segment_cost.npz"), raw=raw, norm=norm, sizes=sizes, cost=cost.numpy(),
+                        mean=mean.numpy(), logvar=logvar.numpy(), z_test=zt.numpy(), cost_z=cost_z.numpy(),
+                        dims=np.array([cfg["input_dim"], cfg["hidden_dim"], cfg["latent_dim"], cfg["predictor_hidden"],
+                                       cfg["predictor_layers"]]), **sd_np(reg))
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     ns = load_reference()
@@ -157,6 +206,7 @@ def main():
     gen_extent_vae(ns)
     gen_snap(ns)
     gen_select(ns)
+    gen_segment_family(ns)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

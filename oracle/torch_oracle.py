@@ -99,6 +99,34 @@ def segsum_mlp_forward(P, sizes, feats, add_sigmoid=False):
 
 
 # --------------------------------------------------------------------------------------
+# a7/a8  SegmentVAE (scripts/vae_experiments/models/vae.py:87-137) and the segment VAECostPredictor
+#        (models/regression.py:82-135), eval mode (BatchNorm running stats, Dropout = identity)
+# --------------------------------------------------------------------------------------
+def segvae_encode(P, sizes, feats):
+    """-> (mean, logvar, segment_sum_vec): vae.py:118-128 / regression.py:82-101."""
+    S = segment_sum(segsum_mlp_encode_rows(P, feats), sizes)
+    h = segsum_mlp_head(P, S)
+    return _lin(h, P["fc_mean.weight"], P["fc_mean.bias"]), _lin(h, P["fc_logvar.weight"], P["fc_logvar.bias"]), S
+
+
+def segvae_decode(P, z):
+    """vae.py:57-66,109-111: Linear, BN, ReLU, Dropout, Linear, BN, ReLU, Linear."""
+    h = torch.relu(_bn_eval(_lin(_t(z), P["decoder.0.weight"], P["decoder.0.bias"]), P, "decoder.1"))
+    h = torch.relu(_bn_eval(_lin(h, P["decoder.4.weight"], P["decoder.4.bias"]), P, "decoder.5"))
+    return _lin(h, P["decoder.7.weight"], P["decoder.7.bias"])
+
+
+def segcost_predict(P, z, n_layers=3):
+    """regression.py:47-61,109-111: n x [Linear, BN, ReLU, Dropout] + Linear -> squeeze."""
+    h = _t(z)
+    for i in range(n_layers):
+        pre = "cost_predictor.%d" % (4 * i)
+        h = torch.relu(_bn_eval(_lin(h, P[pre + ".weight"], P[pre + ".bias"]), P, "cost_predictor.%d" % (4 * i + 1)))
+    pre = "cost_predictor.%d" % (4 * n_layers)
+    return _lin(h, P[pre + ".weight"], P[pre + ".bias"]).squeeze(-1)
+
+
+# --------------------------------------------------------------------------------------
 # a3  MLPModelInternal._predict_a_task (mlp_model.py:669-681) + MLPModel.predict (:832-846)
 # --------------------------------------------------------------------------------------
 def predict_programs(P, programs, norm_vec=None, task_embedding=None, batch=4096,

@@ -319,3 +319,54 @@ def test_errors_are_loud():
         m.load_state({})
     x = torch.zeros(4, device="cuda")
     assert lib.vaex_topk(_lib.ptr(x), 4, 5000, None, _lib.ptr(x), _lib.ptr(x), None, None) == -1
+
+
+def _seg_close(got, want, rel):
+    got, want = np.asarray(got, np.float64), np.asarray(want, np.float64)
+    return np.abs(got - want).max() <= rel * max(1e-6, np.abs(want).max())
+
+
+@pytest.mark.parametrize("flags", [_lib.F_FORCE_SIMT, 0])
+def test_segment_vae_checkpoint_golden(flags):
+    """a7: SegmentVAE mirror (shipped trained checkpoint) against the reference's outputs.  fp32
+    SIMT path 1e-4 of the tensor's largest magnitude; tcgen05 row encoder 2e-3 (fp16 operands)."""
+    g = load_golden("segment_vae.npz")
+    vae = vaex_b200.SegmentVAE(164, hidden_dim=int(g["hidden"]), latent_dim=int(g["latent"]))
+    vae.load_state_dict(split_sd(g, "w."))
+    vae = vae.cuda().eval()
+    rel = 1e-4 if flags else 2e-3
+    sizes, feats = torch.from_numpy(g["sizes"]).cuda(), torch.from_numpy(g["feats"]).cuda()
+    mean, logvar, S = vae.encode_segments(sizes, feats, flags=flags)
+    assert _seg_close(S.cpu(), g["segsum"], rel)
+    assert _seg_close(mean.cpu(), g["mean"], rel) and _seg_close(logvar.cpu(), g["logvar"], rel)
+    assert _seg_close(vae.decode(torch.from_numpy(g["mean"]).cuda()).cpu(), g["recon"], 1e-4)
+    fm, fl, fz, frecon, fS = vae(sizes, feats, use_mean=True, eps=torch.from_numpy(g["fwd_eps"]).cuda(), flags=flags)
+    assert not fl.any() and _seg_close((fz - fm).cpu(), g["fwd_eps"], 1e-5)
+    assert _seg_close(frecon.cpu(), g["fwd_recon"], 5 * rel)
+    vae.train()
+    with pytest.raises(NotImplementedError):
+        vae(sizes, feats)
+
+
+@pytest.mark.parametrize("flags", [_lib.F_FORCE_SIMT, 0])
+def test_segment_cost_predictor_checkpoint_golden(flags):
+    """a8: segment VAECostPredictor mirror on the shipped for_inference checkpoint; raw features with
+    the checkpoint's fea_norm_vec folded into W0 at pack time."""
+    g = load_golden("segment_cost.npz")
+    d = [int(x) for x in g["dims"]]
+    reg = vaex_b200.seg_models.VAECostPredictor(d[0], d[1], d[2], d[3], d[4])
+    reg.load_state_dict(split_sd(g, "w."))
+    reg = reg.cuda().eval()
+    rel = 1e-4 if flags else 2e-3
+    sizes, raw = torch.from_numpy(g["sizes"]).cuda(), torch.from_numpy(g["raw"]).cuda()
+    cost, mean, logvar, z = reg(sizes, raw, use_mean=True, flags=flags, fea_norm_vec=torch.from_numpy(g["norm"]))
+    assert z is mean
+    assert _seg_close(mean.cpu(), g["mean"], rel) and _seg_close(logvar.cpu(), g["logvar"], rel)
+    assert _seg_close(cost.cpu(), g["cost"], 2 * rel)
+    assert _seg_close(reg.predict_cost(torch.from_numpy(g["z_test"]).cuda()).cpu(), g["cost_z"], 1e-4)
+    # the same encoder through load_pretrained_encoder of a SegmentVAE-style state dict
+    reg2 = vaex_b200.seg_models.VAECostPredictor(d[0], d[1], d[2], d[3], d[4])
+    reg2.load_pretrained_encoder({"model_state_dict": split_sd(g, "w.")})
+    reg2 = reg2.cuda().eval()
+    m2, _, _ = reg2.encode(sizes, raw, flags=flags, fea_norm_vec=torch.from_numpy(g["norm"]))
+    assert torch.equal(m2, mean)

@@ -8,7 +8,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libvaex_b200.so")
 
-KIND_SEGSUM_MLP, KIND_EXTENT_VAE, KIND_COST_PREDICTOR = 1, 2, 3
+KIND_SEGSUM_MLP, KIND_EXTENT_VAE, KIND_COST_PREDICTOR, KIND_SEGMENT_VAE, KIND_SEGMENT_COST = 1, 2, 3, 4, 5
 F_MASK_INVALID, F_FORCE_SIMT = 1, 2
 SNAP_EXP, SNAP_EXPM1, SNAP_DIVISOR = 0, 1, 4
 
@@ -37,6 +37,9 @@ SIGNATURES = {
     "vaex_predict_cost": ([vp, vp, i64, vp, vp, u64, f32, vp], ctypes.c_int),
     "vaex_cost_grad_z": ([vp, vp, i64, vp, vp, vp, vp], ctypes.c_int),
     "vaex_latent_ascent": ([vp, vp, i64, i32, f32, vp, vp], ctypes.c_int),
+    "vaex_segvae_encode": ([vp, vp, vp, i64, i64, vp, vp, vp, ctypes.c_int, vp], ctypes.c_int),
+    "vaex_segvae_decode": ([vp, vp, i64, vp, vp], ctypes.c_int),
+    "vaex_segcost_predict": ([vp, vp, i64, vp, vp], ctypes.c_int),
     "vaex_topk": ([vp, i64, i32, vp, vp, vp, vp, vp], ctypes.c_int),
 }
 

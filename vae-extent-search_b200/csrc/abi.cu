@@ -65,6 +65,23 @@ static int pack_linear(vaex_model* m, const std::string& pre, int out, int in, c
   return VAEX_OK;
 }
 
+// Linear followed by eval-mode BatchNorm1d: W' = diag(a) W, b' = a*b + (beta - a*mean), a = gamma/sqrt(var+eps)
+static int pack_linear_bn(vaex_model* m, const std::string& lin, const std::string& bn, const std::string& out_name,
+                          int out, int in, cudaStream_t st) {
+  TRY(need(m, (lin + ".weight").c_str(), out, in));
+  TRY(need(m, (lin + ".bias").c_str(), 1, out));
+  for (const char* k : {".weight", ".bias", ".running_mean", ".running_var"}) TRY(need(m, (bn + k).c_str(), 1, out));
+  std::vector<float> w = m->host[lin + ".weight"].v, b = m->host[lin + ".bias"].v;
+  for (int j = 0; j < out; ++j) {
+    const float a = m->host[bn + ".weight"].v[j] / std::sqrt(m->host[bn + ".running_var"].v[j] + 1e-5f);
+    for (int c = 0; c < in; ++c) w[(size_t)j * in + c] *= a;
+    b[j] = a * b[j] + (m->host[bn + ".bias"].v[j] - a * m->host[bn + ".running_mean"].v[j]);
+  }
+  TRY(upload(m, out_name + ".weight", w.data(), w.size(), st));
+  TRY(upload(m, out_name + ".bias", b.data(), b.size(), st));
+  return VAEX_OK;
+}
+
 static int pack_segsum_mlp(vaex_model* m, const float* norm, cudaStream_t st) {
   const int F = m->F, H = m->H;
   TRY(need(m, "segment_encoder.0.weight", H, F));
@@ -79,7 +96,7 @@ static int pack_segsum_mlp(vaex_model* m, const float* norm, cudaStream_t st) {
   TRY(pack_linear(m, "segment_encoder.2", H, H, st));
   TRY(pack_linear(m, "l0.0", H, H, st));
   TRY(pack_linear(m, "l1.0", H, H, st));
-  TRY(pack_linear(m, "decoder", 1, H, st));
+  if (m->kind == VAEX_KIND_SEGSUM_MLP) TRY(pack_linear(m, "decoder", 1, H, st));
   if (m->use_norm) {  // eval-mode BatchNorm1d -> per-column affine y = s*a + c
     for (const char* k : {"norm.weight", "norm.bias", "norm.running_mean", "norm.running_var"}) TRY(need(m, k, 1, H));
     std::vector<float> a(H), c(H);
@@ -92,7 +109,7 @@ static int pack_segsum_mlp(vaex_model* m, const float* norm, cudaStream_t st) {
     TRY(upload(m, "norm.shift", c.data(), H, st));
   }
   TRY(tc_pack(m, w0, st));
-  TRY(head_tc_pack(m, st));
+  if (m->kind == VAEX_KIND_SEGSUM_MLP) TRY(head_tc_pack(m, st));
   return VAEX_OK;
 }
 
@@ -127,6 +144,25 @@ static int pack_model(vaex_model* m, const float* norm, cudaStream_t st) {
       auto t0 = transpose(m->host["cost_predictor.0.weight"]);
       TRY(upload(m, "cost_predictor.3.weight_t", t3.data(), t3.size(), st));
       TRY(upload(m, "cost_predictor.0.weight_t", t0.data(), t0.size(), st));
+      return VAEX_OK;
+    }
+    case VAEX_KIND_SEGMENT_VAE: {
+      TRY(pack_segsum_mlp(m, norm, st));                      // row encoder, norm, l0, l1 (+ tcgen05 images)
+      TRY(pack_linear(m, "fc_mean", m->L, m->H, st));
+      TRY(pack_linear(m, "fc_logvar", m->L, m->H, st));
+      TRY(pack_linear_bn(m, "decoder.0", "decoder.1", "dec0", m->H, m->L, st));
+      TRY(pack_linear_bn(m, "decoder.4", "decoder.5", "dec1", m->H, m->H, st));
+      TRY(pack_linear(m, "decoder.7", m->H, m->H, st));
+      return VAEX_OK;
+    }
+    case VAEX_KIND_SEGMENT_COST: {
+      TRY(pack_segsum_mlp(m, norm, st));
+      TRY(pack_linear(m, "fc_mean", m->L, m->H, st));
+      TRY(pack_linear(m, "fc_logvar", m->L, m->H, st));
+      for (int i = 0; i < m->n_pred; ++i)
+        TRY(pack_linear_bn(m, "cost_predictor." + std::to_string(4 * i), "cost_predictor." + std::to_string(4 * i + 1),
+                           "pred" + std::to_string(i), m->PH, i == 0 ? m->L : m->PH, st));
+      TRY(pack_linear(m, "cost_predictor." + std::to_string(4 * m->n_pred), 1, m->PH, st));
       return VAEX_OK;
     }
   }
@@ -165,6 +201,12 @@ int vaex_model_create(int kind, const int32_t* dims, int ndims, vaex_model_t* ou
   } else if (kind == VAEX_KIND_COST_PREDICTOR && ndims == 4) {
     m->D = dims[0]; m->H = dims[1]; m->L = dims[2]; m->PH = dims[3];
     if (m->D < 1 || m->H < 1 || m->L < 1 || m->PH < 1) rc = VAEX_E_INVALID;
+  } else if (kind == VAEX_KIND_SEGMENT_VAE && ndims == 3) {
+    m->F = dims[0]; m->H = dims[1]; m->L = dims[2]; m->use_norm = 1;
+    if (m->F < 1 || m->H < 1 || m->L < 1) rc = VAEX_E_INVALID;
+  } else if (kind == VAEX_KIND_SEGMENT_COST && ndims == 5) {
+    m->F = dims[0]; m->H = dims[1]; m->L = dims[2]; m->PH = dims[3]; m->n_pred = dims[4]; m->use_norm = 1;
+    if (m->F < 1 || m->H < 1 || m->L < 1 || m->PH < 1 || m->n_pred < 1 || m->n_pred > 8) rc = VAEX_E_INVALID;
   } else {
     rc = VAEX_E_INVALID;
   }
@@ -216,3 +258,4 @@ int vaex_model_destroy(vaex_model_t h) {
 
 #include "abi_segsum.inc"
 #include "abi_vae.inc"
+#include "abi_segvae.inc"

@@ -39,7 +39,7 @@ struct DevBuf {
 
 struct vaex_model {
   int kind = 0;
-  int F = 0, H = 0, L = 0, D = 0, PH = 0;
+  int F = 0, H = 0, L = 0, D = 0, PH = 0, n_pred = 0;
   int use_norm = 0, add_sigmoid = 0;
   bool packed = false;
   std::map<std::string, vaex::HostTensor> host;
