@@ -67,7 +67,16 @@ enum {
   VAEX_SNAP_DIVISOR = 4 /* OR-able: then legalise to tile factors (utils.cc:433-463 semantics) */
 };
 
+/* losses of MLPModelInternal (mlp_model.py:369-392) */
+enum {
+  VAEX_LOSS_MSE = 0,        /* 'rmse': torch.nn.MSELoss on sigmoid outputs */
+  VAEX_LOSS_RANKNET = 1,    /* RankNetLoss, mlp_model.py:869-876 */
+  VAEX_LOSS_LAMBDARANK = 2, /* LambdaRankLoss, :879-925 (the default) */
+  VAEX_LOSS_LISTNET = 3     /* ListNetLoss, :928-944 */
+};
+
 typedef struct vaex_model* vaex_model_t;
+typedef struct vaex_trainer* vaex_trainer_t;
 
 const char* vaex_last_error(void);
 int vaex_abi_version(void);
@@ -151,6 +160,40 @@ int vaex_segvae_encode(vaex_model_t h, const float* feats_dev, const int32_t* se
 int vaex_segvae_decode(vaex_model_t h, const float* z_dev, int64_t n, float* recon_dev, void* stream);
 /* VAECostPredictor.predict_cost (regression.py:109-111): z [n, L] -> cost [n].  Kind 5. */
 int vaex_segcost_predict(vaex_model_t h, const float* z_dev, int64_t n, float* cost_dev, void* stream);
+
+/* ---- training of the SegmentSumMLP (MLPModelInternal._fit_a_model / _fine_tune_a_model,
+ *      mlp_model.py:512-600,609-651).  Parameters, gradients and the Adam moments are flat fp32
+ *      device buffers owned by the caller, laid out in state_dict order (vaex_trainer_param_offset);
+ *      data-parallel training all-reduces `grads` between the two calls. ------------------------ */
+int vaex_trainer_create(int32_t in_dim, int32_t hidden, int32_t add_sigmoid, vaex_trainer_t* out);
+int vaex_trainer_destroy(vaex_trainer_t t);
+int64_t vaex_trainer_param_count(vaex_trainer_t t);
+/* offset / element count of a reference state_dict key inside the flat buffers */
+int vaex_trainer_param_offset(vaex_trainer_t t, const char* name, int64_t* offset, int64_t* count);
+/* shuffled mini-batch assembly on the device (SegmentDataLoader._fetch_indices, :129-141): packs the
+ * rows (and labels) of programs indices_dev[0..n) of a resident data set; out_offsets_dev int32[n+1],
+ * out_feats_dev fp32 [sum of their sizes, F] (the caller knows that sum from its host copy of the sizes). */
+int vaex_gather_segments(const float* feats_dev, int32_t in_dim, const int32_t* seg_offsets_dev,
+                         const int64_t* indices_dev, int64_t n, int32_t* out_offsets_dev,
+                         float* out_feats_dev, const float* labels_dev_or_null,
+                         float* out_labels_dev_or_null, void* stream);
+/* one batch (<= 4096 programs): forward, loss (VAEX_LOSS_*) and the full backward pass.
+ * grads_dev is overwritten; *loss_dev receives the loss; preds_dev_or_null the predictions. */
+int vaex_trainer_forward_backward(vaex_trainer_t t, const float* params_dev, float* grads_dev,
+                                  const float* feats_dev, const int32_t* seg_offsets_dev,
+                                  const float* labels_dev, int64_t n_programs, int64_t n_rows,
+                                  int loss_type, float* loss_dev, float* preds_dev_or_null, void* stream);
+/* loss value (and optionally d loss / d pred) of n <= 4096 predictions (_validate, :653-661) */
+int vaex_loss_eval(int loss_type, const float* preds_dev, const float* labels_dev, int64_t n,
+                   float* loss_dev, float* dpred_dev_or_null, void* stream);
+/* g = grad_scale * grads; clip_grad_norm_(clip_norm) if clip_norm > 0 (pre-clip norm -> *gnorm_dev);
+ * torch.optim.Adam step `step` (1-based) with L2 weight decay, in place. */
+int vaex_adam_step(float* params_dev, const float* grads_dev, float* m_dev, float* v_dev, int64_t n,
+                   int64_t step, float lr, float beta1, float beta2, float eps, float weight_decay,
+                   float clip_norm, float grad_scale, float* gnorm_dev_or_null, void* stream);
+/* torch.optim.SGD step without momentum (fine-tuning, :626) */
+int vaex_sgd_step(float* params_dev, const float* grads_dev, int64_t n, float lr, float weight_decay,
+                  float grad_scale, void* stream);
 
 /* ---- top-k (util_select_topk, utils/select.py:54-81) -------------------------------------- */
 /* k largest of scores[n] restricted to mask (uint8, 1 = eligible; NULL = all), ordered by

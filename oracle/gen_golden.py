@@ -199,6 +199,57 @@ def gen_segment_family(ns):
                                        cfg["predictor_layers"]]), **sd_np(reg))
 
 
+def gen_train(ns):
+    """a4: the reference's loss classes (value + autograd gradient) and short optimisation
+    trajectories with its own make_net / Adam / clip_grad_norm_ (mlp_model.py:541-565)."""
+    M = ns.mlp_model
+    rng = np.random.default_rng(77)
+    out = {}
+    ref_losses = {"rmse": torch.nn.MSELoss(), "rankNetLoss": M.RankNetLoss(), "lambdaRankLoss": M.LambdaRankLoss(),
+                  "listNetLoss": M.ListNetLoss()}
+    for n in (64, 257):
+        preds = torch.from_numpy(rng.standard_normal(n).astype(np.float32))
+        labels = torch.from_numpy(rng.random(n).astype(np.float32))
+        labels[::7] = 0.0                                  # failed measurements: throughput 0, ties in the labels
+        out["loss_preds_%d" % n], out["loss_labels_%d" % n] = preds.numpy(), labels.numpy()
+        for name, fn in ref_losses.items():
+            p = (torch.sigmoid(preds) if name == "rmse" else preds).clone().requires_grad_(True)
+            kw = {"device": "cpu"} if name == "lambdaRankLoss" else {}
+            loss = fn(p, labels, **kw)
+            (g,) = torch.autograd.grad(loss, p)
+            out["loss_%s_%d" % (name, n)], out["grad_%s_%d" % (name, n)] = np.float32(loss.item()), g.numpy()
+    # optimisation trajectories (hidden_dim 64 keeps the fixture small)
+    progs = synth_programs(rng, 3 * 48, smax=8, zero_frac=0.0)
+    sizes = np.array([len(p) for p in progs], np.int32)
+    feats = np.concatenate(progs, 0) / 25.0
+    labels = rng.random(len(progs)).astype(np.float32)
+    offs = np.concatenate([[0], np.cumsum(sizes)])
+    out.update(train_feats=feats.astype(np.float32), train_sizes=sizes, train_labels=labels)
+    for name in ("lambdaRankLoss", "rmse", "rankNetLoss", "listNetLoss"):
+        torch.manual_seed(11)
+        net = M.make_net({"type": "SegmentSumMLP", "in_dim": 164, "hidden_dim": 64, "out_dim": 1, "add_sigmoid": name == "rmse"})
+        net.train()
+        for k, v in net.state_dict().items():
+            out["init.%s" % k] = v.detach().numpy().copy()
+        opt = torch.optim.Adam(net.parameters(), lr=7e-4, weight_decay=1e-6)
+        losses, norms = [], []
+        for step in range(6):
+            b = step % 3
+            s, e = 48 * b, 48 * (b + 1)
+            opt.zero_grad()
+            kw = {"device": "cpu"} if name == "lambdaRankLoss" else {}
+            loss = ref_losses[name](net(torch.from_numpy(sizes[s:e]), torch.from_numpy(feats[offs[s]:offs[e]].astype(np.float32))),
+                                    torch.from_numpy(labels[s:e]), **kw)
+            loss.backward()
+            norms.append(float(torch.nn.utils.clip_grad_norm_(net.parameters(), 0.5)))
+            opt.step()
+            losses.append(float(loss))
+        out["traj_losses_%s" % name], out["traj_norms_%s" % name] = np.array(losses, np.float64), np.array(norms, np.float64)
+        for k, v in net.state_dict().items():
+            out["final_%s.%s" % (name, k)] = v.detach().numpy().copy()
+    np.savez_compressed(os.path.join(OUT, "train.npz"), **out)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     ns = load_reference()
@@ -207,6 +258,7 @@ def main():
     gen_snap(ns)
     gen_select(ns)
     gen_segment_family(ns)
+    gen_train(ns)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

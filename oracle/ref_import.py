@@ -14,6 +14,7 @@ Modules loaded:
   scripts/pre_experiments/model_myself/utils/{model,select,common}.py
   scripts/vae_experiments/models/{vae,regression}.py
 """
+import importlib.machinery
 import importlib.util
 import os
 import sys
@@ -33,6 +34,7 @@ def available():
 
 def _stub(name, **attrs):
     m = types.ModuleType(name)
+    m.__spec__ = importlib.machinery.ModuleSpec(name, None)   # torch._dynamo calls find_spec on every loaded module
     m.__dict__.update(attrs)
     m.__path__ = []  # behave like a package
     sys.modules[name] = m

@@ -127,6 +127,80 @@ def segcost_predict(P, z, n_layers=3):
 
 
 # --------------------------------------------------------------------------------------
+# a4  losses (mlp_model.py:863-944) and the optimisation step of _fit_a_model (:541-565)
+#     restated with torch autograd on the CPU
+# --------------------------------------------------------------------------------------
+def loss_mse(preds, labels):
+    return torch.mean((preds - labels) ** 2)
+
+
+def loss_ranknet(preds, labels):
+    """RankNetLoss, :863-876."""
+    s_ij = preds - preds.unsqueeze(1)
+    p_ij = torch.triu(1 / (torch.exp(s_ij) + 1), diagonal=1)
+    y_ij = torch.triu((labels.unsqueeze(1) > labels).float(), diagonal=1)
+    return torch.nn.functional.binary_cross_entropy(p_ij, y_ij)
+
+
+def loss_lambdarank(preds, labels, eps=1e-10, sigma=1.0):
+    """LambdaRankLoss.forward with k=None, :887-925."""
+    y_pred, y_true = preds[None, :], labels[None, :]
+    y_pred_sorted, idx = y_pred.sort(descending=True, dim=-1)
+    y_true_sorted, _ = y_true.sort(descending=True, dim=-1)
+    t = torch.gather(y_true, 1, idx)
+    diffs = t[:, :, None] - t[:, None, :]
+    mask = torch.isfinite(diffs) & (diffs > 0)
+    t = t.clamp(min=0.0)
+    y_true_sorted = y_true_sorted.clamp(min=0.0)
+    D = torch.log2(1.0 + torch.arange(1, y_pred.shape[1] + 1).float())[None, :]
+    max_dcg = torch.sum((torch.pow(2, y_true_sorted) - 1) / D, dim=-1).clamp(min=eps)
+    G = (torch.pow(2, t) - 1) / max_dcg[:, None]
+    w = torch.abs(torch.pow(D[:, :, None], -1.0) - torch.pow(D[:, None, :], -1.0)) * torch.abs(G[:, :, None] - G[:, None, :])
+    sd = (y_pred_sorted[:, :, None] - y_pred_sorted[:, None, :]).clamp(min=-1e8, max=1e8)
+    sd = torch.where(torch.isnan(sd), torch.zeros_like(sd), sd)
+    wp = (torch.sigmoid(sigma * sd).clamp(min=eps) ** w).clamp(min=eps)
+    return -torch.sum(torch.log2(wp)[mask])
+
+
+def loss_listnet(preds, labels, eps=1e-10):
+    """ListNetLoss, :928-944."""
+    q = torch.softmax(preds[None, :], dim=1) + eps
+    return torch.mean(-torch.sum(torch.softmax(labels[None, :], dim=1) * torch.log(q), dim=1))
+
+
+LOSSES = {"rmse": loss_mse, "rankNetLoss": loss_ranknet, "lambdaRankLoss": loss_lambdarank, "listNetLoss": loss_listnet}
+PARAM_ORDER = ["segment_encoder.0.weight", "segment_encoder.0.bias", "segment_encoder.2.weight", "segment_encoder.2.bias",
+               "l0.0.weight", "l0.0.bias", "l1.0.weight", "l1.0.bias", "decoder.weight", "decoder.bias"]
+
+
+def loss_and_grad(loss_type, preds, labels):
+    p = _t(preds).clone().requires_grad_(True)
+    loss = LOSSES[loss_type](p, _t(labels))
+    (g,) = torch.autograd.grad(loss, p)
+    return loss.detach(), g
+
+
+def train_steps(P0, batches, loss_type, lr=7e-4, wd=1e-6, grad_clip=0.5, optimizer="adam"):
+    """batches: list of (sizes, feats, labels).  Runs optimizer.zero_grad / loss.backward /
+    clip_grad_norm_ / optimizer.step per batch (mlp_model.py:559-565; SGD variant :636-638).
+    -> (final params dict, [loss per step], [pre-clip grad norm per step])"""
+    P = {k: _t(P0[k]).clone().requires_grad_(True) for k in PARAM_ORDER}
+    params = [P[k] for k in PARAM_ORDER]
+    opt = torch.optim.Adam(params, lr=lr, weight_decay=wd) if optimizer == "adam" else torch.optim.SGD(params, lr=lr, weight_decay=wd)
+    losses, norms = [], []
+    for sizes, feats, labels in batches:
+        opt.zero_grad()
+        out = segsum_mlp_forward(P, sizes, _t(feats), add_sigmoid=(loss_type == "rmse"))
+        loss = LOSSES[loss_type](out, _t(labels))
+        loss.backward()
+        if grad_clip:
+            norms.append(float(torch.nn.utils.clip_grad_norm_(params, grad_clip)))
+        opt.step()
+        losses.append(float(loss))
+    return {k: v.detach() for k, v in P.items()}, losses, norms
+
+
+# --------------------------------------------------------------------------------------
 # a3  MLPModelInternal._predict_a_task (mlp_model.py:669-681) + MLPModel.predict (:832-846)
 # --------------------------------------------------------------------------------------
 def predict_programs(P, programs, norm_vec=None, task_embedding=None, batch=4096,

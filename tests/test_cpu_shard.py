@@ -100,3 +100,24 @@ def test_merge_topk_device_count_and_nosync():
     i = torch.tensor([4, 1, 7, 7])
     vals, idx = shard.merge_topk(v, i, 10, 4, topk_fn=_oracle_topk, n_local=torch.tensor([2], dtype=torch.int32), sync=False)
     assert idx.tolist() == [14, 11, -1, -1] and vals[:2].tolist() == [3.0, 2.0]
+
+
+def _grad_worker(rank, world, port, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        g = torch.arange(1000, dtype=torch.float32) * (rank + 1)      # rank-local gradient buffer
+        scale = shard.reduce_gradients(g)
+        np.savez(os.path.join(out_dir, "g%d.npz" % rank), g=g.numpy(), scale=scale)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_reduce_gradients_world2_gloo(tmp_path):
+    """training's only collective: sum all-reduce of the flat gradient buffer + the 1/world factor"""
+    mp.spawn(_grad_worker, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
+    want = np.arange(1000, dtype=np.float32) * 3
+    for r in range(2):
+        z = np.load(tmp_path / ("g%d.npz" % r))
+        assert np.array_equal(z["g"], want) and float(z["scale"]) == 0.5
+    assert shard.reduce_gradients(torch.ones(4)) == 1.0                # no process group: identity

@@ -1,0 +1,152 @@
+"""GPU parity of the training row: CUDA losses, backward pass, clip + Adam / SGD against
+the reference-generated goldens (tests/golden/train.npz) and the torch-autograd oracle."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_golden, split_sd
+from oracle import torch_oracle as O
+
+import vaex_b200
+from vaex_b200 import _lib, train
+
+pytestmark = pytest.mark.gpu
+
+
+def _offsets(sizes):
+    return torch.from_numpy(np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)).cuda()
+
+
+@pytest.mark.parametrize("n", [64, 257])
+def test_losses_and_gradients_vs_reference(n):
+    g = load_golden("train.npz")
+    lib = _lib.load()
+    preds, labels = g["loss_preds_%d" % n], g["loss_labels_%d" % n]
+    for name, lid in _lib.LOSS_IDS.items():
+        p = torch.from_numpy(preds).cuda()
+        if name == "rmse":
+            p = torch.sigmoid(p)
+        loss, grad = torch.zeros(1, device="cuda"), torch.zeros(n, device="cuda")
+        _lib.check(lib.vaex_loss_eval(lid, _lib.ptr(p), _lib.ptr(torch.from_numpy(labels).cuda()), n, _lib.ptr(loss),
+                                      _lib.ptr(grad), _lib.stream_ptr()))
+        np.testing.assert_allclose(loss.item(), g["loss_%s_%d" % (name, n)], rtol=2e-5, err_msg=name)
+        want = g["grad_%s_%d" % (name, n)]
+        np.testing.assert_allclose(grad.cpu().numpy(), want, rtol=2e-4, atol=2e-6 * np.abs(want).max(), err_msg=name)
+
+
+def test_loss_edge_cases():
+    lib = _lib.load()
+    for n in (1, 2, 1000, 4096):                       # single element, non-power-of-two, the 4096 limit
+        rng = np.random.default_rng(n)
+        p, y = rng.standard_normal(n).astype(np.float32), rng.random(n).astype(np.float32)
+        for name, lid in _lib.LOSS_IDS.items():
+            loss, grad = torch.zeros(1, device="cuda"), torch.zeros(n, device="cuda")
+            _lib.check(lib.vaex_loss_eval(lid, _lib.ptr(torch.from_numpy(p).cuda()), _lib.ptr(torch.from_numpy(y).cuda()), n,
+                                          _lib.ptr(loss), _lib.ptr(grad), _lib.stream_ptr()))
+            wl, wg = O.loss_and_grad(name, p, y)
+            np.testing.assert_allclose(loss.item(), float(wl), rtol=2e-4, atol=1e-6, err_msg="%s n=%d" % (name, n))
+            np.testing.assert_allclose(grad.cpu().numpy(), wg.numpy(), rtol=1e-3, atol=1e-5 * max(1e-3, float(wg.abs().max())),
+                                       err_msg="%s n=%d" % (name, n))
+    loss = torch.zeros(1, device="cuda")
+    with pytest.raises(_lib.VaexError):
+        _lib.check(lib.vaex_loss_eval(2, _lib.ptr(loss), _lib.ptr(loss), 4097, _lib.ptr(loss), None, None))
+
+
+@pytest.mark.parametrize("name", ["lambdaRankLoss", "rmse", "rankNetLoss", "listNetLoss"])
+def test_train_trajectory_vs_reference(name):
+    """six Adam steps (lr 7e-4, L2 1e-6, clip 0.5) on fixed batches: losses, pre-clip gradient norms and
+    final parameters against the reference's own make_net / loss / torch.optim.Adam run."""
+    g = load_golden("train.npz")
+    sizes, feats, labels = g["train_sizes"], g["train_feats"], g["train_labels"]
+    offs = np.concatenate([[0], np.cumsum(sizes)])
+    net = vaex_b200.SegmentSumMLPModule(164, 64, 1, add_sigmoid=(name == "rmse"))
+    net.load_state_dict(split_sd(g, "init."))
+    tr = train.Trainer(net.cuda(), name)
+    losses, norms = [], []
+    for b in (0, 1, 2, 0, 1, 2):
+        s, e = 48 * b, 48 * (b + 1)
+        loss = tr.step(_offsets(sizes[s:e]), torch.from_numpy(feats[offs[s]:offs[e]]).cuda(), torch.from_numpy(labels[s:e]).cuda(),
+                       7e-4, 1e-6, 0.5)
+        losses.append(loss.item())
+        norms.append(tr.gnorm.item())
+    np.testing.assert_allclose(losses, g["traj_losses_%s" % name], rtol=2e-4)
+    np.testing.assert_allclose(norms, g["traj_norms_%s" % name], rtol=2e-3)
+    net = tr.export_params()
+    for k, v in split_sd(g, "final_%s." % name).items():
+        got = net.state_dict()[k].cpu().numpy()
+        # Adam's first steps move every weight by ~lr regardless of the gradient's size, so compare the *update*
+        init = g["init." + k]
+        np.testing.assert_allclose(got - init, v.numpy() - init, rtol=0.02, atol=2e-5, err_msg=k)
+
+
+def test_backward_h256_vs_autograd_and_sgd():
+    """full-size model (F=164, H=256, 300 programs): every gradient tensor against torch autograd, then one
+    SGD fine-tune step (mlp_model.py:626,636-638)."""
+    torch.manual_seed(21)
+    rng = np.random.default_rng(21)
+    net = vaex_b200.SegmentSumMLPModule(164, 256, 1)
+    P0 = {k: v.detach().clone() for k, v in net.state_dict().items()}
+    sizes = rng.integers(1, 33, size=300).astype(np.int32)
+    feats = (rng.random((int(sizes.sum()), 164), dtype=np.float32) * (rng.random(164) > 0.15)).astype(np.float32)
+    labels = rng.random(300).astype(np.float32)
+    tr = train.Trainer(net.cuda(), "lambdaRankLoss")
+    tr.forward_backward(_offsets(sizes), torch.from_numpy(feats).cuda(), torch.from_numpy(labels).cuda())
+    P = {k: v.clone().requires_grad_(True) for k, v in P0.items()}
+    loss = O.loss_lambdarank(O.segsum_mlp_forward(P, sizes, torch.from_numpy(feats)), torch.from_numpy(labels))
+    grads = torch.autograd.grad(loss, [P[k] for k in O.PARAM_ORDER])
+    np.testing.assert_allclose(tr.loss.item(), float(loss), rtol=1e-4)
+    for k, gw in zip(O.PARAM_ORDER, grads):
+        o, c = tr.slices[k]
+        got = tr.grads[o:o + c].cpu().numpy().reshape(gw.shape)
+        assert np.abs(got - gw.numpy()).max() <= 2e-4 * np.abs(gw.numpy()).max() + 1e-7, k
+    tr.sgd_step(4e-2, 0.0)
+    net = tr.export_params()
+    for k, gw in zip(O.PARAM_ORDER, grads):
+        want = P0[k] - 4e-2 * gw
+        np.testing.assert_allclose(net.state_dict()[k].cpu().numpy(), want.numpy(), rtol=1e-4, atol=2e-6, err_msg=k)
+    # determinism: the same batch twice gives bit-identical gradients (two-pass reductions, no atomics)
+    g1 = tr.grads.clone()
+    tr.import_params()
+    tr.forward_backward(_offsets(sizes), torch.from_numpy(feats).cuda(), torch.from_numpy(labels).cuda())
+    g2 = tr.grads.clone()
+    tr.forward_backward(_offsets(sizes), torch.from_numpy(feats).cuda(), torch.from_numpy(labels).cuda())
+    assert torch.equal(g2, tr.grads) and not torch.equal(g1, g2)
+
+
+def test_gather_segments_and_fit_base_learns():
+    """the device mini-batch gather against numpy, then MLPModelInternal.fit_base on a learnable synthetic
+    task: the ranking loss falls and held-out predictions rank the programs."""
+    rng = np.random.default_rng(5)
+    n = 3000
+    sizes = rng.integers(1, 17, size=n)
+    w = rng.standard_normal(164).astype(np.float32)
+    feats, labels = np.empty(n, dtype=object), np.empty(n, np.float32)
+    for i in range(n):
+        f = rng.random((sizes[i], 164), dtype=np.float32)
+        feats[i] = f
+        labels[i] = 1.0 / (1.0 + np.exp(-(f.mean(0) @ w)))                  # "throughput" in (0, 1)
+    task = vaex_b200.LearningTask("wk", "cuda")
+    ds = vaex_b200.Dataset.create_one_task(task, feats[:2500], labels[:2500])
+    test = vaex_b200.Dataset.create_one_task(task, feats[2500:], labels[2500:])
+    m = vaex_b200.MLPModelInternal(device="cuda:0", use_workload_embedding=False)
+    # gather kernel
+    loader = vaex_b200.SegmentDataLoader(ds, 512, "cuda:0", False, False, {})
+    rs = train.ResidentSet(loader, "cuda:0")
+    idx = torch.randperm(2500)[:77]
+    off, bf, bl = rs.batch(idx.numpy(), idx.cuda())
+    want = np.concatenate([feats[i] for i in idx.numpy()], 0)
+    assert np.array_equal(bf.cpu().numpy(), want) and np.array_equal(bl.cpu().numpy(), labels[idx.numpy()])
+    assert np.array_equal(off.cpu().numpy(), np.concatenate([[0], np.cumsum(sizes[idx.numpy()])]))
+    # training
+    m.n_epoch, m.print_per_epoches = 12, 4
+    torch.manual_seed(0)
+    m.fit_base(ds, valid_set=test)
+    pred = m.predict(test)[task]
+    from scipy.stats import spearmanr
+    rho = spearmanr(pred, labels[2500:]).statistic
+    assert rho > 0.8, rho
+    # fine-tuning path (SGD) runs and keeps the model usable
+    m.few_shot_learning = "fine_tune_mix_task"
+    m.fine_tune_num_steps = 2
+    m.fit_local(ds)
+    assert np.isfinite(m.predict(test)[task]).all()

@@ -11,6 +11,7 @@ LIB_PATH = os.path.join(_HERE, "libvaex_b200.so")
 KIND_SEGSUM_MLP, KIND_EXTENT_VAE, KIND_COST_PREDICTOR, KIND_SEGMENT_VAE, KIND_SEGMENT_COST = 1, 2, 3, 4, 5
 F_MASK_INVALID, F_FORCE_SIMT = 1, 2
 SNAP_EXP, SNAP_EXPM1, SNAP_DIVISOR = 0, 1, 4
+LOSS_IDS = {"rmse": 0, "rankNetLoss": 1, "lambdaRankLoss": 2, "listNetLoss": 3}
 
 c_i32p = ctypes.POINTER(ctypes.c_int32)
 c_f32p = ctypes.POINTER(ctypes.c_float)
@@ -40,6 +41,15 @@ SIGNATURES = {
     "vaex_segvae_encode": ([vp, vp, vp, i64, i64, vp, vp, vp, ctypes.c_int, vp], ctypes.c_int),
     "vaex_segvae_decode": ([vp, vp, i64, vp, vp], ctypes.c_int),
     "vaex_segcost_predict": ([vp, vp, i64, vp, vp], ctypes.c_int),
+    "vaex_trainer_create": ([i32, i32, i32, ctypes.POINTER(vp)], ctypes.c_int),
+    "vaex_trainer_destroy": ([vp], ctypes.c_int),
+    "vaex_trainer_param_count": ([vp], i64),
+    "vaex_trainer_param_offset": ([vp, ctypes.c_char_p, ctypes.POINTER(i64), ctypes.POINTER(i64)], ctypes.c_int),
+    "vaex_gather_segments": ([vp, i32, vp, vp, i64, vp, vp, vp, vp, vp], ctypes.c_int),
+    "vaex_trainer_forward_backward": ([vp, vp, vp, vp, vp, vp, i64, i64, ctypes.c_int, vp, vp, vp], ctypes.c_int),
+    "vaex_loss_eval": ([ctypes.c_int, vp, vp, i64, vp, vp, vp], ctypes.c_int),
+    "vaex_adam_step": ([vp, vp, vp, vp, i64, i64, f32, f32, f32, f32, f32, f32, f32, vp, vp], ctypes.c_int),
+    "vaex_sgd_step": ([vp, vp, i64, f32, f32, f32, vp], ctypes.c_int),
     "vaex_topk": ([vp, i64, i32, vp, vp, vp, vp, vp], ctypes.c_int),
 }
 

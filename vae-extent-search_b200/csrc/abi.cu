@@ -55,7 +55,6 @@ static std::vector<float> transpose(const HostTensor& t) {
   return o;
 }
 
-#define TRY(x) do { int rc_ = (x); if (rc_ != VAEX_OK) return rc_; } while (0)
 
 static int pack_linear(vaex_model* m, const std::string& pre, int out, int in, cudaStream_t st) {
   TRY(need(m, (pre + ".weight").c_str(), out, in));

@@ -36,6 +36,8 @@ void count_launch(int n = 1);
     VAEX_CUDA(cudaGetLastError());                                                          \
   } while (0)
 
+#define TRY(x) do { int rc_ = (x); if (rc_ != VAEX_OK) return rc_; } while (0)
+
 static inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
 // epilogues of the SIMT linear kernel
@@ -43,7 +45,8 @@ enum Epi {
   EPI_NONE = 0,
   EPI_RELU = 1,
   EPI_RELU_RESIDUAL = 2,  // y = relu(acc+b) + aux[n,m]
-  EPI_MUL_MASK = 3        // y = (acc) * (aux[n,m] > 0)      (ReLU backward)
+  EPI_MUL_MASK = 3,       // y = (acc) * (aux[n,m] > 0)      (ReLU backward)
+  EPI_ADD_AUX = 4         // y = acc + b + aux[n,m]          (residual branch of a backward pass)
 };
 
 // Y[n, m] = epi(sum_k X[n, k] * W[m, k] + b[m]);  X [N, K] (ldx), W [M, K] row-major.

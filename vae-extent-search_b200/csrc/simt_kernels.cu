@@ -76,6 +76,7 @@ linear_kernel(const float* __restrict__ X, int64_t ldx, const float* __restrict_
       if (EPI == EPI_RELU) v = fmaxf(v, 0.f);
       if (EPI == EPI_RELU_RESIDUAL) v = fmaxf(v, 0.f) + aux[n * ldaux + m];
       if (EPI == EPI_MUL_MASK) v = aux[n * ldaux + m] > 0.f ? v : 0.f;
+      if (EPI == EPI_ADD_AUX) v += aux[n * ldaux + m];
       Y[n * ldy + m] = v;
     }
   }
@@ -91,6 +92,7 @@ int linear_simt(const float* X, int64_t ldx, const float* W, const float* b, flo
     case EPI_RELU: linear_kernel<EPI_RELU><<<grid, 256, 0, st>>>(X, ldx, W, b, Y, ldy, N, M, K, aux, ldaux); break;
     case EPI_RELU_RESIDUAL: linear_kernel<EPI_RELU_RESIDUAL><<<grid, 256, 0, st>>>(X, ldx, W, b, Y, ldy, N, M, K, aux, ldaux); break;
     case EPI_MUL_MASK: linear_kernel<EPI_MUL_MASK><<<grid, 256, 0, st>>>(X, ldx, W, b, Y, ldy, N, M, K, aux, ldaux); break;
+    case EPI_ADD_AUX: linear_kernel<EPI_ADD_AUX><<<grid, 256, 0, st>>>(X, ldx, W, b, Y, ldy, N, M, K, aux, ldaux); break;
     default: set_error("bad epilogue"); return VAEX_E_INVALID;
   }
   VAEX_LAUNCH_CHECK();

@@ -1,4 +1,4 @@
-"""Drop-in mirror of the TenSet MLP cost model's inference interface
+"""Drop-in mirror of the TenSet MLP cost model
 (reference: python/tvm/auto_scheduler/cost_model/mlp_model.py).
 
 Same class names, constructor arguments, attribute names, state_dict keys and pickle tuple as
@@ -8,12 +8,15 @@ calls raise.
 
   SegmentDataLoader   mlp_model.py:26-144   -> flatten_features() + on-device offsets
   SegmentSumMLPModule mlp_model.py:147-221  -> vaex_segsum_mlp_forward
-  MLPModelInternal    mlp_model.py:340-804  -> predict / save / load (fit_*: next round)
+  MLPModelInternal    mlp_model.py:340-804  -> predict / save / load; fit_base / fit_local / fine-tune on the
+                                             CUDA training kernels (train.py)
   MLPModel            mlp_model.py:814-860  -> predict with the -inf rule (:842-844)
 """
 import io
 import logging
 import pickle
+
+import time
 
 import numpy as np
 import torch
@@ -257,13 +260,156 @@ class MLPModelInternal:
         if target not in self.target_id_dict:
             self.target_id_dict[target] = len(self.target_id_dict)
 
+    # -- training (mlp_model.py:420-489,512-661) on the CUDA training kernels -----------------------
     def fit_base(self, train_set, valid_set=None, valid_train_set=None):
-        raise NotImplementedError("training (mlp_model.py:512-600) is the next hot-path row (SURVEY 8a a4)")
+        if self.few_shot_learning == "local_only":
+            self.base_model = None
+        elif self.few_shot_learning == "MAML":
+            raise NotImplementedError("MAML raises NotImplemented in the reference as well (mlp_model.py:424-428)")
+        else:
+            self.base_model = self._fit_a_model(train_set, valid_set, valid_train_set)
 
     def fit_local(self, train_set, valid_set=None):
-        if self.few_shot_learning == "base_only":
+        fsl = self.few_shot_learning
+        if fsl == "base_only":
             return
-        raise NotImplementedError("training (mlp_model.py:456-489) is the next hot-path row")
+        if fsl == "local_only_mix_task":
+            local_model = self._fit_a_model(train_set, valid_set)
+            for task in train_set.tasks():
+                self.local_model[task] = local_model
+        elif fsl == "local_only_per_task":
+            for task in train_set.tasks():
+                self.local_model[task] = self._fit_a_model(train_set.extract_subset([task]), valid_set)
+        elif fsl in ("plus_mix_task", "plus_per_task"):
+            if fsl == "plus_mix_task":
+                self.net_params["hidden_dim"] = 128
+                self.loss_type = 'rmse'
+                self.net_params['add_sigmoid'] = True
+
+            def diff_set(ds):
+                base = self._predict_a_dataset(self.base_model, ds)
+                out = Dataset()
+                for task in ds.tasks():
+                    out.load_task_data(task, ds.features[task], ds.throughputs[task] - base[task])
+                return out
+            if fsl == "plus_mix_task":
+                diff_model = self._fit_a_model(diff_set(train_set), diff_set(valid_set) if valid_set else None)
+                for task in train_set.tasks():
+                    self.local_model[task] = diff_model
+            else:
+                for task in train_set.tasks():
+                    self.local_model[task] = self._fit_a_model(diff_set(train_set.extract_subset([task])), valid_set)
+        elif fsl == "fine_tune_mix_task":
+            self.base_model = self._fine_tune_a_model(self.base_model, train_set, valid_set)
+        else:
+            raise ValueError("Invalid few-shot learning method: " + fsl)
+
+    def _loaders(self, train_set, valid_set, batch_size, shuffle):
+        for task in train_set.tasks():
+            self.register_new_task(task)
+        train_loader = SegmentDataLoader(train_set, batch_size, self.device, self.use_workload_embedding,
+                                         self.use_target_embedding, self.target_id_dict, shuffle=shuffle)
+        if self.fea_norm_vec is None:
+            self.fea_norm_vec = train_loader.normalize()
+        else:
+            train_loader.normalize(self.fea_norm_vec)
+        valid_loader = None
+        if valid_set:
+            for task in valid_set.tasks():
+                self.register_new_task(task)
+            valid_loader = SegmentDataLoader(valid_set, self.infer_batch_size, self.device, self.use_workload_embedding,
+                                             self.use_target_embedding, self.target_id_dict, fea_norm_vec=self.fea_norm_vec)
+        return train_loader, valid_loader
+
+    def _epoch(self, trainer, data, batch_size, shuffle, lr, wd, clip, optimizer, avg):
+        """One pass over the resident set; the running loss (moving_average, momentum 0.95) stays on
+        the device and is read back once by the caller."""
+        order = torch.randperm(data.n) if shuffle else torch.arange(data.n)       # same CPU stream as the reference
+        order_dev = order.to(data.device)
+        order_host = order.numpy()
+        n_batches = 0
+        for s in range(0, data.n, batch_size):
+            e = min(s + batch_size, data.n)
+            off, feats, labels = data.batch(order_host[s:e], order_dev[s:e])
+            loss = trainer.step(off, feats, labels, lr, wd, clip, optimizer)
+            if avg is None:
+                avg = loss.clone()
+            else:
+                avg.mul_(0.95).add_(loss, alpha=0.05)
+            n_batches += 1
+        return avg, n_batches
+
+    def _fit_a_model(self, train_set, valid_set=None, valid_train_set=None, n_epoch=None):
+        from . import train as _train
+        print("=" * 60 + "\nFit a net. Train size: %d" % len(train_set))
+        train_loader, valid_loader = self._loaders(train_set, valid_set, self.batch_size, True)
+        n_epoch = n_epoch or self.n_epoch
+        early_stop = n_epoch // 6
+        net = make_net(self.net_params).to(self.device)
+        trainer = _train.Trainer(net, self.loss_type, self.device)
+        data = _train.ResidentSet(train_loader, self.device)
+        train_loss, best_epoch, best_train_loss = None, None, 1e10
+        for epoch in range(n_epoch):
+            tic = time.time()
+            train_loss, batch = self._epoch(trainer, data, self.batch_size, True, self.lr, self.wd, self.grad_clip, "adam",
+                                            train_loss)
+            loss_now = float(train_loss.item())                       # the only device read of the epoch
+            train_time = time.time() - tic
+            if epoch % self.print_per_epoches == 0 or epoch == n_epoch - 1:
+                valid_loss = self._validate(trainer.export_params(), valid_loader, trainer) if valid_loader else 0.0
+                if self.loss_type == "rmse":
+                    loss_msg = "Train RMSE: %.4f\tValid RMSE: %.4f" % (np.sqrt(loss_now), np.sqrt(valid_loss))
+                else:
+                    loss_msg = "Train Loss: %.4f\tValid Loss: %.4f" % (loss_now, valid_loss)
+                print("Epoch: %d\tBatch: %d\t%s\tTrain Speed: %.0f" % (epoch, batch - 1, loss_msg, len(train_loader) / train_time))
+            if loss_now < best_train_loss:
+                best_train_loss, best_epoch = loss_now, epoch
+            elif epoch - best_epoch >= early_stop:
+                print("Early stop. Best epoch: %d" % best_epoch)
+                break
+        net = trainer.export_params()
+        trainer.close()
+        return net.eval()
+
+    def _fine_tune_a_model(self, model, train_set, valid_set=None, verbose=1):
+        from . import train as _train
+        if verbose >= 1:
+            print("=" * 60 + "\nFine-tune a net. Train size: %d" % len(train_set))
+        bs = self.fine_tune_batch_size or len(train_set)
+        train_loader, valid_loader = self._loaders(train_set, valid_set, bs, False)
+        trainer = _train.Trainer(model.to(self.device), self.loss_type, self.device)
+        data = _train.ResidentSet(train_loader, self.device)
+        tic = time.time()
+        for step in range(self.fine_tune_num_steps):
+            train_loss, _ = self._epoch(trainer, data, bs, False, self.fine_tune_lr, self.fine_tune_wd, 0.0, "sgd", None)
+            if verbose >= 1:
+                valid_loss = self._validate(trainer.export_params(), valid_loader, trainer) if valid_loader else 0
+                loss_now = float(train_loss.item())
+                if self.loss_type == "rmse":
+                    loss_msg = "Train RMSE: %.4f\tValid RMSE: %.4f" % (np.sqrt(loss_now), np.sqrt(valid_loss))
+                else:
+                    loss_msg = "Train Loss: %.4f\tValid Loss: %.4f" % (loss_now, valid_loss)
+                print("Fine-tune step: %d\t%s\tTime: %.1f" % (step, loss_msg, time.time() - tic))
+        model = trainer.export_params()
+        trainer.close()
+        return model.eval()
+
+    def _validate(self, model, valid_loader, trainer=None):
+        """mlp_model.py:653-661: mean over infer_batch_size batches of loss_func(model(batch), labels);
+        the forward is the fp32 check path so the validation loss is comparable with the training loss."""
+        from . import train as _train
+        own = trainer is None
+        if own:
+            trainer = _train.Trainer(model, self.loss_type, self.device)
+        model.eval()
+        losses = []
+        for segment_sizes, features, labels in valid_loader:
+            with torch.no_grad():
+                preds = model(segment_sizes, features, flags=_lib.F_FORCE_SIMT)
+            losses.append(trainer.loss_value(preds.reshape(-1), labels))
+        if own:
+            trainer.close()
+        return float(torch.cat(losses).mean().item()) if losses else 0.0
 
     # -- inference ---------------------------------------------------------------------------
     def _task_embedding(self, task):

@@ -41,6 +41,16 @@ def shard_by_rows(sizes, world):
     return np.asarray(cuts, dtype=np.int64)
 
 
+def reduce_gradients(flat_grads, group=None):
+    """Data-parallel training: one sum all-reduce of the flat fp32 gradient buffer
+    (NCCL over NVLink on GPUs, 0.96 MB for the SegmentSumMLP); returns the factor 1 / world that the
+    optimizer kernel folds in, so every rank applies the mean gradient of the global batch."""
+    world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+    if world > 1:
+        dist.all_reduce(flat_grads, op=dist.ReduceOp.SUM, group=group)
+    return 1.0 / world
+
+
 def _default_topk(values, k, mask):
     from . import vae_model
     return vae_model.topk(values, k, mask, sync=False)
