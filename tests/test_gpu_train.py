@@ -27,8 +27,8 @@ def test_losses_and_gradients_vs_reference(n):
         if name == "rmse":
             p = torch.sigmoid(p)
         loss, grad = torch.zeros(1, device="cuda"), torch.zeros(n, device="cuda")
-        _lib.check(lib.vaex_loss_eval(lid, _lib.ptr(p), _lib.ptr(torch.from_numpy(labels).cuda()), n, _lib.ptr(loss),
-                                      _lib.ptr(grad), _lib.stream_ptr()))
+        yd = torch.from_numpy(labels).cuda()
+        _lib.check(lib.vaex_loss_eval(lid, _lib.ptr(p), _lib.ptr(yd), n, _lib.ptr(loss), _lib.ptr(grad), _lib.stream_ptr()))
         np.testing.assert_allclose(loss.item(), g["loss_%s_%d" % (name, n)], rtol=2e-5, err_msg=name)
         want = g["grad_%s_%d" % (name, n)]
         np.testing.assert_allclose(grad.cpu().numpy(), want, rtol=2e-4, atol=2e-6 * np.abs(want).max(), err_msg=name)
