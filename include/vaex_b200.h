@@ -97,6 +97,11 @@ int vaex_model_load_weights(vaex_model_t h, const char* name, const float* data_
  * copies for the backward pass. */
 int vaex_model_pack(vaex_model_t h, const float* fea_norm_vec_host, void* stream);
 int vaex_model_destroy(vaex_model_t h);
+/* per-model options.  VAEX_OPT_TENSOR_CORES (default 1): extent-VAE decode / predict_cost run the fused
+ * tcgen05 chains (fp16 operands, fp32 accumulate: 1e-3 relative) when the shapes allow; 0 = fp32 SIMT
+ * kernels (1e-5).  The SegmentSumMLP entry points take VAEX_F_FORCE_SIMT per call instead. */
+enum { VAEX_OPT_TENSOR_CORES = 1 };
+int vaex_model_set_option(vaex_model_t h, int option, int value);
 
 /* ---- SegmentSumMLP scoring (replaces SegmentSumMLPModule.forward, mlp_model.py:179-221,
  *      and the batch loop of MLPModelInternal._predict_a_task, :669-681) --------------------- */
@@ -136,6 +141,14 @@ int vaex_snap_extents(const float* x_dev, int64_t n, int32_t d, const float* mea
                       const float* scale_dev, int mode, const int32_t* slot_extent_dev,
                       const uint8_t* slot_last_dev, int32_t max_innermost, int32_t* extents_dev,
                       void* stream);
+/* decode + snap in one call (the scoring path of BASELINE configs 3/5): z [n, L] -> continuous extents
+ * x_dev_or_null fp32 [n, D] and integer extents_dev_or_null int32 [n, D]; with tensor cores enabled the
+ * snap runs in the decoder kernel's epilogue (x never touches HBM unless asked for).  Arguments as in
+ * vaex_vae_decode / vaex_snap_extents. */
+int vaex_decode_snap(vaex_model_t h, const float* z_dev, int64_t n, float* x_dev_or_null,
+                     int32_t* extents_dev_or_null, const float* mean_dev, const float* scale_dev, int mode,
+                     const int32_t* slot_extent_dev, const uint8_t* slot_last_dev, int32_t max_innermost,
+                     void* stream);
 /* VAECostPredictor.predict_cost (utils/model.py:168-170); drop_mask_dev (uint8 [n, PH], 1=keep)
  * or drop_seed != 0 activates Dropout(p) after the first ReLU (mc_predict, :241-273). */
 int vaex_predict_cost(vaex_model_t h, const float* z_dev, int64_t n, float* cost_dev,

@@ -199,6 +199,7 @@ def test_extent_vae_golden():
     reg = vaex_b200.VAECostPredictor(48, hidden_dim=256, latent_dim=64)
     reg.load_state_dict(split_sd(g, "reg."))
     vae, reg = vae.cuda().eval(), reg.cuda().eval()
+    vae.set_tensor_cores(False), reg.set_tensor_cores(False)      # fp32 kernels: 1e-5 parity (the tcgen05 chain is tested below)
     x, z = torch.from_numpy(g["x"]).cuda(), torch.from_numpy(g["z"]).cuda()
     tol = dict(rtol=2e-5, atol=2e-6)
     mu, logvar = vae.encode(x)
@@ -232,6 +233,61 @@ def test_extent_vae_golden():
     eps = torch.randn(300, 64, device="cuda")
     np.testing.assert_allclose(reg.reparameterize(mu, logvar, eps=eps).cpu().numpy(),
                                O.reparameterize(mu.cpu(), logvar.cpu(), eps.cpu()).numpy(), rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("n", [1, 127, 128, 129, 300, 70001])
+def test_extent_chain_tensor_cores(n):
+    """the fused tcgen05 chains (decoder 64-256-256-256-48 [+ snap epilogue]; predictor 64-256-256-1) against the
+    oracle at the fp16-operand tolerance, on ragged batch sizes around the 128-row tile; the fused snap must be
+    bit-identical to snapping the kernel's own fp32 x, and agree with the oracle's extents except where x sits
+    on a rounding boundary."""
+    g = load_golden("extent_vae.npz")
+    vae = vaex_b200.VAE_feature_head(48, None, 64, 256)
+    vae.load_state_dict(split_sd(g, "vae."))
+    reg = vaex_b200.VAECostPredictor(48, hidden_dim=256, latent_dim=64)
+    reg.load_state_dict(split_sd(g, "reg."))
+    vae, reg = vae.cuda().eval(), reg.cuda().eval()
+    rng = np.random.default_rng(n)
+    if n <= 300:
+        z = g["z"][:n].copy()
+    else:
+        z = (rng.standard_normal((n, 64)) * g["z"].std()).astype(np.float32)
+    zd = torch.from_numpy(z).cuda()
+    want_x = O.vae_decode(split_sd(g, "vae."), z).numpy()
+    want_c = O.predict_cost(split_sd(g, "reg."), z).numpy()
+    got_x = vae.decode(zd).cpu().numpy()
+    assert l2_err(got_x, want_x) < TC_RTOL, l2_err(got_x, want_x)
+    assert rel_err(got_x, want_x) < 4 * TC_RTOL, rel_err(got_x, want_x)
+    got_c = reg.predict_cost(zd).cpu().numpy()
+    assert got_c.shape == (n,)
+    assert l2_err(got_c, want_c) < TC_RTOL, l2_err(got_c, want_c)
+    assert rel_err(got_c, want_c) < 4 * TC_RTOL, rel_err(got_c, want_c)
+    if n <= 300:
+        np.testing.assert_allclose(got_x, g["dec"][:n], rtol=0, atol=4 * TC_RTOL * np.sqrt(np.mean(g["dec"] ** 2)))
+    # fused snap epilogue
+    mean = rng.uniform(0.5, 3, 48).astype(np.float32)
+    std = rng.uniform(0.3, 1.5, 48).astype(np.float32)
+    x2, ext = vae.decode_and_snap(zd, mean, std)
+    assert np.array_equal(x2.cpu().numpy(), got_x)
+    assert torch.equal(ext, vaex_b200.snap_extents(x2, mean, std))
+    assert torch.equal(vae.decode_snap(zd, mean, std), ext)
+    want_ext = O.snap_round_clamp(want_x, mean, std).numpy()
+    diff = ext.cpu().numpy() != want_ext
+    assert diff.mean() < 0.01, diff.mean()
+    assert np.abs(ext.cpu().numpy().astype(np.int64) - want_ext)[diff].max(initial=0) <= np.maximum(1, 0.01 * want_ext[diff]).max(initial=1)
+    bounds = [1, 3, 4, 28, 56, 57, 64, 128, 960, 4096]
+    sext, last = [], []
+    while len(sext) < 44:
+        sext += [bounds[rng.integers(len(bounds))]] * 4
+        last += [0, 0, 0, 1]
+    sext, last = sext + [0] * 4, last + [0] * 4
+    leg = vae.decode_snap(zd, mean, std, slot_extent=sext, slot_last=last)
+    assert np.array_equal(leg.cpu().numpy(), O.legalise_divisor(ext.cpu().numpy(), sext, last))
+    # the fp32 switch gives the SIMT result back
+    vae.set_tensor_cores(False)
+    assert rel_err(vae.decode(zd).cpu().numpy(), want_x) < 2e-5
+    x3, ext3 = vae.decode_and_snap(zd, mean, std)
+    assert torch.equal(ext3, vaex_b200.snap_extents(x3, mean, std))
 
 
 def test_snap_bit_exact_and_legalise():

@@ -10,6 +10,7 @@ LIB_PATH = os.path.join(_HERE, "libvaex_b200.so")
 
 KIND_SEGSUM_MLP, KIND_EXTENT_VAE, KIND_COST_PREDICTOR, KIND_SEGMENT_VAE, KIND_SEGMENT_COST = 1, 2, 3, 4, 5
 F_MASK_INVALID, F_FORCE_SIMT = 1, 2
+OPT_TENSOR_CORES = 1
 SNAP_EXP, SNAP_EXPM1, SNAP_DIVISOR = 0, 1, 4
 LOSS_IDS = {"rmse": 0, "rankNetLoss": 1, "lambdaRankLoss": 2, "listNetLoss": 3}
 
@@ -27,6 +28,7 @@ SIGNATURES = {
     "vaex_model_load_weights": ([vp, ctypes.c_char_p, vp, i32, i32], ctypes.c_int),
     "vaex_model_pack": ([vp, vp, vp], ctypes.c_int),
     "vaex_model_destroy": ([vp], ctypes.c_int),
+    "vaex_model_set_option": ([vp, ctypes.c_int, ctypes.c_int], ctypes.c_int),
     "vaex_segment_offsets": ([vp, i64, vp, vp], ctypes.c_int),
     "vaex_segsum_mlp_forward": ([vp, vp, vp, i64, i64, vp, ctypes.c_int, vp], ctypes.c_int),
     "vaex_segsum_encode": ([vp, vp, vp, i64, i64, vp, ctypes.c_int, vp], ctypes.c_int),
@@ -34,6 +36,7 @@ SIGNATURES = {
     "vaex_vae_encode": ([vp, vp, i64, vp, vp, vp], ctypes.c_int),
     "vaex_reparam": ([vp, vp, vp, u64, u64, vp, i64, i32, vp], ctypes.c_int),
     "vaex_vae_decode": ([vp, vp, i64, vp, vp], ctypes.c_int),
+    "vaex_decode_snap": ([vp, vp, i64, vp, vp, vp, vp, ctypes.c_int, vp, vp, i32, vp], ctypes.c_int),
     "vaex_snap_extents": ([vp, i64, i32, vp, vp, ctypes.c_int, vp, vp, i32, vp, vp], ctypes.c_int),
     "vaex_predict_cost": ([vp, vp, i64, vp, vp, u64, f32, vp], ctypes.c_int),
     "vaex_cost_grad_z": ([vp, vp, i64, vp, vp, vp, vp], ctypes.c_int),
@@ -126,6 +129,9 @@ class Model:
                 norm_vec = norm_vec.detach().to("cpu").float().numpy()
             nv = np.ascontiguousarray(np.asarray(norm_vec, dtype=np.float32))
         check(self.lib.vaex_model_pack(self.h, nv.ctypes.data if nv is not None else None, None))
+
+    def set_option(self, option, value):
+        check(self.lib.vaex_model_set_option(self.h, int(option), int(value)))
 
     def close(self):
         if self.h:

@@ -122,6 +122,14 @@ static int pack_encoder(vaex_model* m, cudaStream_t st) {
   return VAEX_OK;
 }
 
+struct ChainLayer { const std::vector<float>* w; const std::vector<float>* b; int out, in; };
+int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode, cudaStream_t st);
+
+static ChainLayer chain_layer(vaex_model* m, const std::string& pre) {
+  HostTensor& w = m->host[pre + ".weight"];
+  return ChainLayer{&w.v, &m->host[pre + ".bias"].v, w.rows, w.cols};
+}
+
 static int pack_model(vaex_model* m, const float* norm, cudaStream_t st) {
   switch (m->kind) {
     case VAEX_KIND_SEGSUM_MLP: return pack_segsum_mlp(m, norm, st);
@@ -131,6 +139,8 @@ static int pack_model(vaex_model* m, const float* norm, cudaStream_t st) {
       TRY(pack_linear(m, "decoder.2", m->H, m->H, st));
       TRY(pack_linear(m, "decoder.4", m->H, m->H, st));
       TRY(pack_linear(m, "decoder.6", m->D, m->H, st));
+      TRY(chain_tc_pack(m->dec_chain, {chain_layer(m, "decoder.0"), chain_layer(m, "decoder.2"), chain_layer(m, "decoder.4"),
+                                       chain_layer(m, "decoder.6")}, 0, st));
       return VAEX_OK;
     }
     case VAEX_KIND_COST_PREDICTOR: {
@@ -143,6 +153,8 @@ static int pack_model(vaex_model* m, const float* norm, cudaStream_t st) {
       auto t0 = transpose(m->host["cost_predictor.0.weight"]);
       TRY(upload(m, "cost_predictor.3.weight_t", t3.data(), t3.size(), st));
       TRY(upload(m, "cost_predictor.0.weight_t", t0.data(), t0.size(), st));
+      TRY(chain_tc_pack(m->pred_chain, {chain_layer(m, "cost_predictor.0"), chain_layer(m, "cost_predictor.3"),
+                                        chain_layer(m, "cost_predictor.6")}, 1, st));
       return VAEX_OK;
     }
     case VAEX_KIND_SEGMENT_VAE: {
@@ -212,6 +224,13 @@ int vaex_model_create(int kind, const int32_t* dims, int ndims, vaex_model_t* ou
   if (rc != VAEX_OK) { delete m; set_error("bad kind/dims for vaex_model_create"); return rc; }
   *out = m;
   return VAEX_OK;
+}
+
+int vaex_model_set_option(vaex_model_t h, int option, int value) {
+  VAEX_CHECK(h, "null handle");
+  if (option == VAEX_OPT_TENSOR_CORES) { h->use_tensor = value ? 1 : 0; return VAEX_OK; }
+  set_error("unknown option");
+  return VAEX_E_INVALID;
 }
 
 int vaex_model_load_weights(vaex_model_t h, const char* name, const float* data, int32_t rows, int32_t cols) {

@@ -2,6 +2,7 @@
 // ReLU-mask products for the fused backward, z update.
 #include "common.cuh"
 #include "simt_kernels.cuh"
+#include "snap.cuh"
 
 namespace vaex {
 
@@ -151,23 +152,6 @@ int reparam(const float* mu, const float* logvar, const float* eps, uint64_t see
 }
 
 // ------------------------------------------------------------------ snap + legalise
-// torch: clamp(round(exp(v)).int(), min=1); round = half-to-even; out-of-range float->int32
-// follows x86 cvttss2si (INT_MIN), which the clamp then maps to 1.
-// unfused mul/add (no FMA contraction) keeps v bit-identical with torch's x*(std+1e-8)+mean.
-__device__ __forceinline__ int32_t snap_one(float x, float mean, float scale, int mode) {
-  float e;
-  if ((mode & 3) == VAEX_SNAP_EXPM1) {
-    const float v = __fadd_rn(__fmul_rn(x, scale), mean);
-    e = (float)expm1((double)v);
-  } else {
-    const float v = __fadd_rn(__fmul_rn(x, __fadd_rn(scale, 1e-8f)), mean);
-    e = (float)exp((double)v);
-  }
-  const float r = rintf(e);
-  int32_t q = (r >= -2147483648.f && r < 2147483648.f) ? (int32_t)r : INT32_MIN;
-  return q < 1 ? 1 : q;
-}
-
 __device__ __forceinline__ int nearest_divisor(int rem, int v, int cap) {
   int bound = rem;
   if (cap > 0 && cap < bound) bound = cap;
@@ -204,6 +188,14 @@ __global__ void legalise_kernel(int32_t* __restrict__ ext, int64_t n, int d,
     rem /= q;
     if (last) rem = 0;
   }
+}
+
+int legalise_extents(int32_t* ext, int64_t n, int d, const int32_t* slot_extent, const uint8_t* slot_last, int max_innermost,
+                     cudaStream_t st) {
+  if (n == 0) return VAEX_OK;
+  legalise_kernel<<<(unsigned)cdiv(n, 128), 128, 0, st>>>(ext, n, d, slot_extent, slot_last, max_innermost);
+  VAEX_LAUNCH_CHECK();
+  return VAEX_OK;
 }
 
 int snap_extents(const float* x, int64_t n, int d, const float* mean, const float* scale, int mode,

@@ -27,6 +27,15 @@ struct TcPack {
   bool head_ready = false;
 };
 
+// packed weights of a fused tcgen05 MLP chain (chain_tc.cu)
+struct ChainPack {
+  __half* w = nullptr;
+  __half* bias = nullptr;
+  int smem_bytes = 0;
+  bool ready = false;
+  alignas(8) unsigned char params_storage[320] = {};   // shape part of ChainParams
+};
+
 struct DevBuf {
   void* p = nullptr;
   size_t bytes = 0;
@@ -45,6 +54,8 @@ struct vaex_model {
   std::map<std::string, vaex::HostTensor> host;
   std::map<std::string, float*> dev;   // packed fp32 device tensors, by name
   vaex::TcPack tc;
+  vaex::ChainPack dec_chain, pred_chain;   // extent-VAE decoder / cost predictor on tensor cores
+  int use_tensor = 1;                      // VAEX_OPT_TENSOR_CORES
   vaex::DevBuf ws[6];                  // activations / staging
   vaex::DevBuf topk_ws;
   vaex::DevBuf tc_ws;                  // first_prog + rowmask of the tcgen05 kernel
@@ -65,6 +76,10 @@ int tc_pack(vaex_model* m, const std::vector<float>& w0_folded, cudaStream_t st)
 // head_tc.cu
 int head_tc_pack(vaex_model* m, cudaStream_t st);
 int head_tc_forward(vaex_model* m, const float* S, int64_t P, const uint8_t* valid, float* scores, cudaStream_t st);
+// chain_tc.cu
+struct ChainLayer;
+int chain_tc_run(const ChainPack& cp, const float* X, int64_t n, float* out, int32_t* extents, const float* mean,
+                 const float* scale, int snap_mode, const float* wd, const float* bd, cudaStream_t st);
 // segsum_tc.cu
 int segsum_tc_encode(vaex_model* m, const float* feats, const int32_t* off, int64_t n_programs,
                      int64_t n_rows, float* segsum, uint8_t* valid, cudaStream_t st);

@@ -17,6 +17,8 @@ int reparam(const float* mu, const float* logvar, const float* eps, uint64_t see
 int snap_extents(const float* x, int64_t n, int d, const float* mean, const float* scale, int mode,
                  const int32_t* slot_extent, const uint8_t* slot_last, int max_innermost,
                  int32_t* out, cudaStream_t st);
+int legalise_extents(int32_t* ext, int64_t n, int d, const int32_t* slot_extent, const uint8_t* slot_last, int max_innermost,
+                     cudaStream_t st);
 int dropout_apply(float* h, int64_t n, int cols, const uint8_t* mask, uint64_t seed, float p,
                   cudaStream_t st);
 int relu_mask_rowvec(const float* h, const float* w, float* out, int64_t n, int cols, cudaStream_t st);

@@ -39,8 +39,18 @@ class _Packed:
             return cached[0]
         m = _lib.Model(self._kind, self._dims())
         m.load_state({k: v for k, v in self.state_dict().items() if not k.startswith("feature_predictor")})
+        m.set_option(_lib.OPT_TENSOR_CORES, int(self.__dict__.get("_tensor_cores", True)))
         self.__dict__["_packed_cache"] = (m, key)
         return m
+
+    def set_tensor_cores(self, on=True):
+        """True (default): decoder / cost predictor on the fused tcgen05 chain (fp16 operands, fp32
+        accumulate: ~1e-3 of the reference's fp32); False: the fp32 SIMT kernels (1e-5)."""
+        self.__dict__["_tensor_cores"] = bool(on)
+        cached = self.__dict__.get("_packed_cache")
+        if cached is not None:
+            cached[0].set_option(_lib.OPT_TENSOR_CORES, int(bool(on)))
+        return self
 
     def __getstate__(self):
         d = self.__dict__.copy()
@@ -97,7 +107,25 @@ class VAE_feature_head(_Packed, nn.Module):
     def decode_snap(self, z, mean, scale, log1p=False, slot_extent=None, slot_last=None, max_innermost=64):
         """decode -> postprocess (vae_sch_extent.ipynb:1374-1383) -> clamp(min=1) (:1457), and,
         when slot tables are given, legalise to tile factors (utils.cc:433-463 semantics)."""
-        return snap_extents(self.decode(z), mean, scale, log1p, slot_extent, slot_last, max_innermost)
+        return self.decode_and_snap(z, mean, scale, log1p, slot_extent, slot_last, max_innermost, want_x=False)[1]
+
+    def decode_and_snap(self, z, mean, scale, log1p=False, slot_extent=None, slot_last=None, max_innermost=64, want_x=True):
+        """One launch: (x fp32 or None, extents int32).  The snap runs in the decoder kernel's epilogue."""
+        z = _need_cuda(z)
+        dev, n, D = z.device, z.shape[0], self.decoder[-1].out_features
+        mean = torch.as_tensor(mean, dtype=torch.float32).to(dev).contiguous()
+        scale = torch.as_tensor(scale, dtype=torch.float32).to(dev).contiguous()
+        x = torch.empty(n, D, device=dev) if want_x else None
+        out = torch.empty(n, D, dtype=torch.int32, device=dev)
+        mode = _lib.SNAP_EXPM1 if log1p else _lib.SNAP_EXP
+        se = sl = None
+        if slot_extent is not None:
+            mode |= _lib.SNAP_DIVISOR
+            se = torch.as_tensor(slot_extent, dtype=torch.int32).to(dev).contiguous()
+            sl = torch.as_tensor(slot_last, dtype=torch.uint8).to(dev).contiguous()
+        _lib.check(_lib.load().vaex_decode_snap(self.packed().h, _lib.ptr(z), n, _lib.ptr(x), _lib.ptr(out), _lib.ptr(mean),
+                                               _lib.ptr(scale), mode, _lib.ptr(se), _lib.ptr(sl), max_innermost, _lib.stream_ptr()))
+        return x, out
 
     def predict_feature(self, z):
         raise NotImplementedError("feature_predictor head (alpha_feature experiments) is outside the hot path")
