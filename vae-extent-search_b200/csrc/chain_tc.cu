@@ -6,11 +6,22 @@
 //             (VAECostPredictor.predict_cost, utils/model.py:128-141,168-170; eval mode, Dropout = identity)
 //
 // One persistent CTA pair (cta_group::2) per 256 rows per step; all layer weights stay resident
-// in shared memory (each CTA holds the half of every layer's output units: 160 KB for the decoder),
+// in shared memory (each CTA holds half of every layer's output units: 160 KB for the decoder),
 // the 64 KB A operand is rewritten in place by each layer's epilogue (bias + ReLU + fp16 pack),
-// the accumulator lives in TMEM: activations never touch HBM -- per row the kernel reads 4*L
-// bytes and writes 4*D (or 4).  Same worker layout as head_tc.cu: a thread owns one row and one
-// half of the columns; warp 8 of the leader CTA issues the MMAs; hand-offs are two mbarriers.
+// the accumulators live in TMEM: activations never touch HBM -- per row the kernel reads 4*L
+// bytes and writes 4*D (or 4).
+//
+// Pipelining inside a tile (v2).  A 256-wide layer is issued as four MMA pieces, K-half major:
+//   (n-half 0, k 0..127) (n-half 1, k 0..127) (n-half 0, k 128..255) -> commit ACC[0]
+//   (n-half 1, k 128..255) -> commit ACC[1]
+// The epilogue of n-half h produces exactly the A atoms of k-half h of the next layer, so the
+// next layer's first two pieces run on the tensor pipe while the workers are still draining
+// n-half 1 of this one (accumulators are double-buffered: 2 x 256 TMEM columns); pieces of k-half
+// h wait for mbarrier IN[h].  In-place A is safe: an epilogue only overwrites atoms whose readers
+// (all earlier pieces) are covered by the commit it waited for.  z of the next tile is packed into
+// atom 3 (the last one the layer-0 epilogue rewrites) right after the last layer's commit, so
+// layer 0 of tile t+1 runs behind the output epilogue of tile t.
+// Workers: 16 warps, thread = (row, 32-column group of the n-half); warp 16 of the leader CTA issues.
 #include <algorithm>
 #include <vector>
 
@@ -23,9 +34,9 @@ namespace vaex {
 
 namespace ch {
 constexpr int TILE = 128, PAIR = 256, ATOM = 128 * 128, HID = 256, K0 = 64;
-constexpr int WORKERS = 256, THREADS = 288;
+constexpr int WORKER_WARPS = 16, WORKERS = 32 * WORKER_WARPS, THREADS = WORKERS + 32;
 constexpr int MAX_LAYERS = 4;
-enum { B_IN = 0, B_ACC = 1 };
+enum { B_IN0 = 0, B_IN1 = 1, B_ACC0 = 2, B_ACC1 = 3 };
 enum { MODE_VECTOR = 0, MODE_DOT = 1 };
 constexpr int SMEM_MAX = 232448;
 
@@ -38,7 +49,7 @@ __host__ __device__ inline uint32_t sw_off(int rows, int u, int k) {
 struct ChainParams {
   const float* X;            // [n, in_dim] fp32
   const __half* w;           // all layer images, rank-major: [2][w_bytes / 2]
-  const __half* bias;        // fp16 biases of the MMA layers, concatenated
+  const float* bias;         // fp32 biases of the MMA layers, concatenated (zero padded to N) [+ MODE_DOT: wd[256], bd]
   float* out;                // MODE_VECTOR: [n, out_dim] fp32 (nullable); MODE_DOT: [n]
   int32_t* extents;          // MODE_VECTOR: [n, out_dim] int32 (nullable): fused snap
   const float* snap_mean;    // [out_dim]
@@ -48,7 +59,7 @@ struct ChainParams {
   int64_t n;
   int32_t T, in_dim, out_dim, mode, snap_mode, n_mma;
   int32_t K[ch::MAX_LAYERS], N[ch::MAX_LAYERS], w_off[ch::MAX_LAYERS], b_off[ch::MAX_LAYERS];
-  int32_t w_bytes, a_off, bias_off, bias_count, bar_off;
+  int32_t w_bytes, a_off, bias_off, bias_count, wd_off, bar_off;
 };
 
 __global__ void smem_base_probe_kernel(uint32_t* out) {
@@ -65,26 +76,26 @@ chain_tc_kernel(const ChainParams p) {
   const uint32_t rank = ptx::cluster_ctarank();
   const int cluster = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + p.bar_off);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + p.bar_off + 16);
-  float* s_dot = reinterpret_cast<float*>(smem + p.a_off);      // MODE_DOT: the A operand is dead during the last epilogue
-  const __half* s_bias = reinterpret_cast<const __half*>(smem + p.bias_off);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + p.bar_off + 32);
+  float* s_dot = reinterpret_cast<float*>(smem + p.bar_off + 64);     // MODE_DOT: [3][128] partial dots
+  const float* s_bias = reinterpret_cast<const float*>(smem + p.bias_off);
   const uint32_t bar0 = ptx::smem_u32(bars);
   auto bar = [&](int i) { return bar0 + 8u * i; };
 
   if (threadIdx.x == 0) {
-    ptx::mbar_init(bar(B_IN), 16);      // 8 worker warps x 2 CTAs
-    ptx::mbar_init(bar(B_ACC), 1);
+    ptx::mbar_init(bar(B_IN0), 2 * WORKER_WARPS);      // worker warps x 2 CTAs
+    ptx::mbar_init(bar(B_IN1), 2 * WORKER_WARPS);
+    ptx::mbar_init(bar(B_ACC0), 1);
+    ptx::mbar_init(bar(B_ACC1), 1);
     ptx::fence_mbar_init();
   }
-  if (warp == 1) ptx::tmem_alloc_2cta(ptx::smem_u32(tmem_slot), 256);
+  if (warp == 1) ptx::tmem_alloc_2cta(ptx::smem_u32(tmem_slot), 512);
   {
     const uint4* g = reinterpret_cast<const uint4*>(p.w) + (size_t)rank * (p.w_bytes / 16);
     uint4* s = reinterpret_cast<uint4*>(smem);
     for (int i = threadIdx.x; i < p.w_bytes / 16; i += THREADS) s[i] = __ldg(g + i);
-    __half* sb = reinterpret_cast<__half*>(smem + p.bias_off);
+    float* sb = reinterpret_cast<float*>(smem + p.bias_off);
     for (int i = threadIdx.x; i < p.bias_count; i += THREADS) sb[i] = p.bias[i];
-    uint4* a = reinterpret_cast<uint4*>(smem + p.a_off);   // K padding of the first layer stays zero
-    for (int i = threadIdx.x; i < ATOM / 16; i += THREADS) a[i] = make_uint4(0, 0, 0, 0);
   }
   ptx::fence_proxy_async();
   ptx::tc_fence_before();
@@ -93,135 +104,161 @@ chain_tc_kernel(const ChainParams p) {
   ptx::tc_fence_after();
   const uint32_t tmem = *tmem_slot;
 
-  if (warp < 8) {
-    // ===== workers: thread = (row, column half) =====
-    const int q = warp & 3, chh = warp >> 2;
-    const uint32_t lane_base = (uint32_t)(32 * q) << 16;
+  if (warp < WORKER_WARPS) {
+    // ===== workers: thread = (row, column group cg of 4) =====
+    const int q = warp & 3, cg = warp >> 2;
     const int row = 32 * q + lane;
     const uint32_t a_row = sbase + p.a_off + (row >> 3) * 1024 + (row & 7) * 128;
     const int sw = row & 7;
-    const uint32_t t_acc = tmem + lane_base;
-    float xin[32];                                   // this thread's half of the next input row
+    const uint32_t t_lane = tmem + ((uint32_t)(32 * q) << 16);
+    float xin[16];                                   // this thread's 16 columns of the next input row
 
     auto fetch = [&](int t) {
       const int64_t r = (int64_t)t * PAIR + rank * TILE + row;
       const bool ok = t < p.T && r < p.n;
       const float* src = p.X + (ok ? r : 0) * p.in_dim;
-      if (ok && (p.in_dim & 7) == 0 && ((reinterpret_cast<uintptr_t>(p.X) & 31) == 0)) {
+      if (ok && (p.in_dim & 3) == 0 && ((reinterpret_cast<uintptr_t>(p.X) & 15) == 0)) {
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          const int c = 32 * chh + 8 * j;
-          if (c < p.in_dim) {
-            float4 a = ptx::ldg_stream_f4(src + c), b = ptx::ldg_stream_f4(src + c + 4);
-            xin[8 * j] = a.x; xin[8 * j + 1] = a.y; xin[8 * j + 2] = a.z; xin[8 * j + 3] = a.w;
-            xin[8 * j + 4] = b.x; xin[8 * j + 5] = b.y; xin[8 * j + 6] = b.z; xin[8 * j + 7] = b.w;
-          } else {
-#pragma unroll
-            for (int e = 0; e < 8; ++e) xin[8 * j + e] = 0.f;
-          }
+          const int c = 16 * cg + 4 * j;
+          float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (c < p.in_dim) a = ptx::ldg_stream_f4(src + c);
+          xin[4 * j] = a.x; xin[4 * j + 1] = a.y; xin[4 * j + 2] = a.z; xin[4 * j + 3] = a.w;
         }
       } else {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int c = 32 * chh + j;
+        for (int j = 0; j < 16; ++j) {
+          const int c = 16 * cg + j;
           xin[j] = (ok && c < p.in_dim) ? __ldg(src + c) : 0.f;
         }
       }
     };
-    // 32 fp32 values -> 64 B of the fp16 A operand, 32-column chunk cc of the row
-    auto pack32 = [&](const float (&v)[32], int cc) {
-      const uint32_t base = a_row + (cc >> 1) * ATOM;
+    // z: 16 fp32 -> 32 B of atom 3 (the layer-0 A operand)
+    auto pack_z = [&]() {
+      const uint32_t base = a_row + 3 * ATOM;
 #pragma unroll
-      for (int m = 0; m < 4; ++m)
-        ptx::sts_v4(base + ((((cc & 1) * 4 + m) ^ sw) << 4),
-                    ptx::cvt_h2_sat(v[8 * m], v[8 * m + 1]), ptx::cvt_h2_sat(v[8 * m + 2], v[8 * m + 3]),
-                    ptx::cvt_h2_sat(v[8 * m + 4], v[8 * m + 5]), ptx::cvt_h2_sat(v[8 * m + 6], v[8 * m + 7]));
+      for (int m = 0; m < 2; ++m)
+        ptx::sts_v4(base + (((2 * cg + m) ^ sw) << 4),
+                    ptx::cvt_h2_sat(xin[8 * m], xin[8 * m + 1]), ptx::cvt_h2_sat(xin[8 * m + 2], xin[8 * m + 3]),
+                    ptx::cvt_h2_sat(xin[8 * m + 4], xin[8 * m + 5]), ptx::cvt_h2_sat(xin[8 * m + 6], xin[8 * m + 7]));
     };
-    auto publish = [&]() {
+    auto publish = [&](int b) {
       ptx::fence_proxy_async();
       ptx::tc_fence_before();
       __syncwarp();
-      if (lane == 0) ptx::mbar_arrive_cluster_relaxed(bar(B_IN), 0);
+      if (lane == 0) ptx::mbar_arrive_cluster_relaxed(bar(b), 0);
     };
-    auto bias32 = [&](int boff, float (&b)[32]) {     // 32 consecutive fp16 biases (64-byte aligned)
-      const uint4* src = reinterpret_cast<const uint4*>(s_bias + boff);
-#pragma unroll
-      for (int m = 0; m < 4; ++m) {
-        const uint4 u = src[m];
-        const uint32_t w[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[e]));
-          b[8 * m + 2 * e] = f.x;
-          b[8 * m + 2 * e + 1] = f.y;
-        }
-      }
-    };
-
+    const bool vec_ok = (p.out_dim & 3) == 0 &&
+        ((reinterpret_cast<uintptr_t>(p.out) | reinterpret_cast<uintptr_t>(p.extents) | reinterpret_cast<uintptr_t>(p.snap_mean) |
+          reinterpret_cast<uintptr_t>(p.snap_scale)) & 15) == 0;
+    uint32_t acc_use0 = 0, acc_use1 = 0, lc = 0;
     fetch(cluster);
-    uint32_t use = 0;
+    if (cluster < p.T) {
+      pack_z();
+      publish(B_IN0);
+    }
     for (int t = cluster; t < p.T; t += n_clusters) {
-      pack32(xin, chh);                              // z -> fp16, columns [32 chh, +32) of atom 0
-      publish();
+      const int64_t r = (int64_t)t * PAIR + rank * TILE + row;
       for (int l = 0; l < p.n_mma; ++l) {
         const bool last = l + 1 == p.n_mma;
-        if (last) fetch(t + n_clusters);             // the next rows stream in behind the last GEMM
-        ptx::mbar_wait(bar(B_ACC), use & 1);
-        ++use;
-        ptx::tc_fence_after();
+        const uint32_t t_acc = t_lane + 256u * (lc & 1);
+        ++lc;
+        if (last) {
+          fetch(t + n_clusters);                     // the next rows stream in behind the last GEMM
+          const int64_t r2 = (int64_t)(t + 2 * n_clusters) * PAIR + rank * TILE + row;
+          if (cg < 2 && 32 * cg < p.in_dim && r2 < p.n) ptx::prefetch_l2(p.X + r2 * p.in_dim + 32 * cg);   // and the rows after those reach L2
+        }
         if (!last || p.mode == MODE_DOT) {
-          // hidden layer: 128 columns of this row, bias + ReLU (+ fp16 pack | + dot)
+          // hidden layer: n-half nh -> 32 columns of this row: bias + ReLU (+ fp16 pack | + dot)
           float dot0 = 0.f, dot1 = 0.f;
 #pragma unroll 1
-          for (int c = 0; c < 4; ++c) {
+          for (int nh = 0; nh < 2; ++nh) {
+            const int col = 128 * nh + 32 * cg;
+            const float4* b = reinterpret_cast<const float4*>(s_bias + p.b_off[l] + col);
+            if (nh == 0) { ptx::mbar_wait(bar(B_ACC0), acc_use0 & 1); ++acc_use0; }
+            else         { ptx::mbar_wait(bar(B_ACC1), acc_use1 & 1); ++acc_use1; }
+            ptx::tc_fence_after();
             uint32_t v[32];
-            float b[32], y[32];
-            ptx::tmem_ld32(t_acc + 128 * chh + 32 * c, v);
-            bias32(p.b_off[l] + 128 * chh + 32 * c, b);
+            ptx::tmem_ld32(t_acc + col, v);
             ptx::tmem_ld_wait();
-#pragma unroll
-            for (int j = 0; j < 32; ++j) y[j] = fmaxf(__uint_as_float(v[j]) + b[j], 0.f);
             if (!last) {
-              pack32(y, 4 * chh + c);
-            } else {
-              const float4* w4 = reinterpret_cast<const float4*>(p.wd + 128 * chh + 32 * c);
+              const int cc = 4 * nh + cg;
+              const uint32_t base = a_row + (cc >> 1) * ATOM;
 #pragma unroll
-              for (int j4 = 0; j4 < 8; ++j4) {
-                const float4 w = __ldg(w4 + j4);
-                dot0 = fmaf(y[4 * j4], w.x, dot0);
-                dot1 = fmaf(y[4 * j4 + 1], w.y, dot1);
-                dot0 = fmaf(y[4 * j4 + 2], w.z, dot0);
-                dot1 = fmaf(y[4 * j4 + 3], w.w, dot1);
+              for (int m = 0; m < 4; ++m) {
+                const float4 b0 = b[2 * m], b1 = b[2 * m + 1];
+                ptx::sts_v4(base + ((((cc & 1) * 4 + m) ^ sw) << 4),
+                            ptx::cvt_h2_relu_sat(__uint_as_float(v[8 * m]) + b0.x, __uint_as_float(v[8 * m + 1]) + b0.y),
+                            ptx::cvt_h2_relu_sat(__uint_as_float(v[8 * m + 2]) + b0.z, __uint_as_float(v[8 * m + 3]) + b0.w),
+                            ptx::cvt_h2_relu_sat(__uint_as_float(v[8 * m + 4]) + b1.x, __uint_as_float(v[8 * m + 5]) + b1.y),
+                            ptx::cvt_h2_relu_sat(__uint_as_float(v[8 * m + 6]) + b1.z, __uint_as_float(v[8 * m + 7]) + b1.w));
+              }
+              publish(nh == 0 ? B_IN0 : B_IN1);
+            } else {
+              const float4* w4 = reinterpret_cast<const float4*>(s_bias + p.wd_off + col);
+#pragma unroll
+              for (int m = 0; m < 8; ++m) {
+                const float4 w = w4[m], bm = b[m];
+                dot0 = fmaf(fmaxf(__uint_as_float(v[4 * m]) + bm.x, 0.f), w.x, dot0);
+                dot1 = fmaf(fmaxf(__uint_as_float(v[4 * m + 1]) + bm.y, 0.f), w.y, dot1);
+                dot0 = fmaf(fmaxf(__uint_as_float(v[4 * m + 2]) + bm.z, 0.f), w.z, dot0);
+                dot1 = fmaf(fmaxf(__uint_as_float(v[4 * m + 3]) + bm.w, 0.f), w.w, dot1);
               }
             }
           }
-          if (!last) {
-            publish();
-          } else {
-            const float dot = dot0 + dot1;
-            if (chh == 1) s_dot[row] = dot;
+          if (last) {
+            // every MMA of this tile has completed: z of the next tile goes in first, then the scalar head
             ptx::tc_fence_before();
+            if (t + n_clusters < p.T) {
+              pack_z();
+              publish(B_IN0);
+            }
+            const float dot = dot0 + dot1;
+            if (cg) s_dot[(cg - 1) * TILE + row] = dot;
             ptx::bar_sync(1, WORKERS);
-            const int64_t r = (int64_t)t * PAIR + rank * TILE + row;
-            if (chh == 0 && r < p.n) p.out[r] = dot + s_dot[row] + __ldg(p.bd);
-            ptx::bar_sync(1, WORKERS);               // s_dot aliases the A operand the next step rewrites
+            if (cg == 0 && r < p.n) p.out[r] = ((dot + s_dot[row]) + (s_dot[TILE + row] + s_dot[2 * TILE + row])) + s_bias[p.wd_off + HID];
           }
         } else {
-          // output layer (N = 64): 32 columns of this row -> fp32 x and / or snapped extents
-          uint32_t v[32];
-          float b[32];
-          ptx::tmem_ld32(t_acc + 32 * chh, v);
-          bias32(p.b_off[l] + 32 * chh, b);
+          // output layer (N = 64): 16 columns of this row -> fp32 x and / or snapped extents
+          const int c0 = 16 * cg;
+          const float4* b = reinterpret_cast<const float4*>(s_bias + p.b_off[l] + c0);
+          ptx::mbar_wait(bar(B_ACC0), acc_use0 & 1);
+          ++acc_use0;
+          ptx::tc_fence_after();
+          uint32_t v[16];
+          ptx::tmem_ld16(t_acc + c0, v);
+          if (t + n_clusters < p.T) {
+            pack_z();
+            publish(B_IN0);
+          }
           ptx::tmem_ld_wait();
-          const int64_t r = (int64_t)t * PAIR + rank * TILE + row;
-          if (r < p.n) {
+          if (r < p.n && c0 < p.N[l]) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const int c = 32 * chh + j;
-              if (c < p.out_dim) {
-                const float x = __uint_as_float(v[j]) + b[j];
-                if (p.out) p.out[r * p.out_dim + c] = x;
-                if (p.extents) p.extents[r * p.out_dim + c] = snap_one(x, __ldg(p.snap_mean + c), __ldg(p.snap_scale + c), p.snap_mode);
+            for (int m = 0; m < 4; ++m) {
+              const int c = c0 + 4 * m;
+              const float4 bm = b[m];
+              const float y0 = __uint_as_float(v[4 * m]) + bm.x, y1 = __uint_as_float(v[4 * m + 1]) + bm.y;
+              const float y2 = __uint_as_float(v[4 * m + 2]) + bm.z, y3 = __uint_as_float(v[4 * m + 3]) + bm.w;
+              if (vec_ok) {
+                if (c < p.out_dim) {
+                  if (p.out) *reinterpret_cast<float4*>(p.out + r * p.out_dim + c) = make_float4(y0, y1, y2, y3);
+                  if (p.extents) {
+                    const float4 mu = __ldg(reinterpret_cast<const float4*>(p.snap_mean + c));
+                    const float4 sc = __ldg(reinterpret_cast<const float4*>(p.snap_scale + c));
+                    *reinterpret_cast<int4*>(p.extents + r * p.out_dim + c) =
+                        make_int4(snap_one(y0, mu.x, sc.x, p.snap_mode), snap_one(y1, mu.y, sc.y, p.snap_mode),
+                                  snap_one(y2, mu.z, sc.z, p.snap_mode), snap_one(y3, mu.w, sc.w, p.snap_mode));
+                  }
+                }
+              } else {
+                const float y[4] = {y0, y1, y2, y3};
+#pragma unroll
+                for (int e = 0; e < 4; ++e)
+                  if (c + e < p.out_dim) {
+                    if (p.out) p.out[r * p.out_dim + c + e] = y[e];
+                    if (p.extents)
+                      p.extents[r * p.out_dim + c + e] = snap_one(y[e], __ldg(p.snap_mean + c + e), __ldg(p.snap_scale + c + e), p.snap_mode);
+                  }
               }
             }
           }
@@ -231,23 +268,35 @@ chain_tc_kernel(const ChainParams p) {
     }
   } else if (rank == 0) {
     // ===== MMA issuer (leader CTA) =====
-    const uint64_t dA = ptx::umma_desc_sw128(sbase + p.a_off);
-    uint32_t use = 0;
+    uint32_t in_use0 = 0, in_use1 = 0, lc = 0;
     for (int t = cluster; t < p.T; t += n_clusters) {
       for (int l = 0; l < p.n_mma; ++l) {
-        ptx::mbar_wait(bar(B_IN), use & 1);
-        ++use;
-        ptx::tc_fence_after();
-        if (ptx::elect_one()) {
-          const uint32_t idesc = ptx::umma_idesc_f16(256, p.N[l]);
-          const uint64_t dW = ptx::umma_desc_sw128(sbase + p.w_off[l]);
-          const int w_atom = (p.N[l] / 2) * 128;
-          for (int k = 0; k < p.K[l] / 16; ++k)
-            ptx::umma_f16_2cta(tmem, dA + (uint64_t)(((k >> 2) * ATOM + (k & 3) * 32) >> 4),
-                               dW + (uint64_t)(((k >> 2) * w_atom + (k & 3) * 32) >> 4), idesc, k > 0);
-          ptx::umma_commit_2cta(bar(B_ACC), 3);
+        const int K = p.K[l], N = p.N[l];
+        const int n_kh = K == HID ? 2 : 1, n_nh = N == HID ? 2 : 1;
+        const int n_piece = N == HID ? 128 : N;                 // columns per MMA
+        const int w_atom = (N / 2) * 128;                       // bytes per 64-column atom of the W image
+        const uint32_t idesc = ptx::umma_idesc_f16(256, n_piece);
+        const uint32_t acc = tmem + 256u * (lc & 1);
+        ++lc;
+        const uint64_t dA = ptx::umma_desc_sw128(sbase + p.a_off + (K == HID ? 0 : 3 * ATOM));
+        for (int kh = 0; kh < n_kh; ++kh) {
+          if (kh == 0) { ptx::mbar_wait(bar(B_IN0), in_use0 & 1); ++in_use0; }
+          else         { ptx::mbar_wait(bar(B_IN1), in_use1 & 1); ++in_use1; }
+          ptx::tc_fence_after();
+          if (ptx::elect_one()) {
+            const int steps = K == HID ? 8 : 4;
+            for (int nh = 0; nh < n_nh; ++nh) {
+              const uint64_t dW = ptx::umma_desc_sw128(sbase + p.w_off[l] + nh * 64 * 128);
+              for (int i = 0; i < steps; ++i) {
+                const int k = steps * kh + i;
+                ptx::umma_f16_2cta(acc + 128u * nh, dA + (uint64_t)(((k >> 2) * ATOM + (k & 3) * 32) >> 4),
+                                   dW + (uint64_t)(((k >> 2) * w_atom + (k & 3) * 32) >> 4), idesc, k > 0);
+              }
+              if (kh == n_kh - 1) ptx::umma_commit_2cta(bar(nh == 0 ? B_ACC0 : B_ACC1), 3);
+            }
+          }
+          __syncwarp();
         }
-        __syncwarp();
       }
     }
   }
@@ -255,7 +304,7 @@ chain_tc_kernel(const ChainParams p) {
   ptx::tc_fence_before();
   __syncthreads();
   ptx::cluster_sync();
-  if (warp == 1) ptx::tmem_dealloc_2cta(tmem, 256);
+  if (warp == 1) ptx::tmem_dealloc_2cta(tmem, 512);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -279,7 +328,7 @@ int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode
     const ChainLayer& L = layers[l];
     const int K = l == 0 ? K0 : HID;
     const bool out_layer = mode == MODE_VECTOR && l == n_mma - 1;
-    const int N = out_layer ? 64 : HID;
+    const int N = out_layer ? std::max(16, (L.out + 15) / 16 * 16) : HID;
     if ((l == 0 ? L.in > K0 : L.in != HID) || (out_layer ? L.out > 64 : L.out != HID)) return VAEX_OK;   // shape outside this kernel
     P.K[l] = K; P.N[l] = N; P.w_off[l] = woff; P.b_off[l] = boff;
     woff += (N / 2) * K * 2;
@@ -289,10 +338,15 @@ int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode
   P.out_dim = mode == MODE_VECTOR ? layers[n_mma - 1].out : 1;
   P.w_bytes = woff;
   P.a_off = woff;
+  P.wd_off = boff;
+  if (mode == MODE_DOT) {
+    if (layers[n_mma].in != HID || layers[n_mma].out != 1) return VAEX_OK;
+    boff += HID + 4;
+  }
   P.bias_off = P.a_off + 4 * ATOM;
   P.bias_count = boff;
-  P.bar_off = (P.bias_off + boff * 2 + 15) & ~15;
-  cp.smem_bytes = P.bar_off + 32;
+  P.bar_off = P.bias_off + boff * 4;
+  cp.smem_bytes = P.bar_off + 64 + (mode == MODE_DOT ? 3 * TILE * 4 : 0);
   if (cp.smem_bytes > SMEM_MAX) return VAEX_OK;
   // the kernel relies on a 1024-byte aligned dynamic shared-memory base (no static shared memory)
   {
@@ -307,26 +361,31 @@ int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode
     if (h & 1023u) return VAEX_OK;                     // stay on the SIMT path
   }
   std::vector<__half> img((size_t)woff, __float2half_rn(0.f));   // 2 ranks x (woff bytes / 2) halves
-  std::vector<__half> bias((size_t)boff, __float2half_rn(0.f));
+  std::vector<float> bias((size_t)boff, 0.f);
   for (int l = 0; l < n_mma; ++l) {
     const ChainLayer& L = layers[l];
     const int nh = P.N[l] / 2;
     for (int r = 0; r < 2; ++r)
       for (int u = 0; u < nh; ++u) {
-        const int unit = r * nh + u;
+        // a 256-wide layer is issued as two 128-column MMAs: image rows [64 h, +64) of rank r = units 128 h + 64 r + [0, 64)
+        const int unit = P.N[l] == HID ? 128 * (u >> 6) + 64 * r + (u & 63) : r * nh + u;
         if (unit >= L.out) continue;
         __half* dst = img.data() + (size_t)r * (woff / 2) + P.w_off[l] / 2;
         for (int k = 0; k < L.in; ++k) dst[sw_off(nh, u, k) / 2] = c_clamp((*L.w)[(size_t)unit * L.in + k]);
       }
-    for (int j = 0; j < L.out; ++j) bias[P.b_off[l] + j] = c_clamp((*L.b)[j]);
+    for (int j = 0; j < L.out; ++j) bias[P.b_off[l] + j] = (*L.b)[j];
+  }
+  if (mode == MODE_DOT) {
+    for (int k = 0; k < HID; ++k) bias[P.wd_off + k] = (*layers[n_mma].w)[k];
+    bias[P.wd_off + HID] = (*layers[n_mma].b)[0];
   }
   if (cp.w) cudaFree(cp.w);
   if (cp.bias) cudaFree(cp.bias);
   cp.w = nullptr; cp.bias = nullptr;
   VAEX_CUDA(cudaMalloc(&cp.w, img.size() * sizeof(__half)));
-  VAEX_CUDA(cudaMalloc(&cp.bias, std::max<size_t>(bias.size(), 1) * sizeof(__half)));
+  VAEX_CUDA(cudaMalloc(&cp.bias, std::max<size_t>(bias.size(), 1) * sizeof(float)));
   VAEX_CUDA(cudaMemcpyAsync(cp.w, img.data(), img.size() * sizeof(__half), cudaMemcpyHostToDevice, st));
-  VAEX_CUDA(cudaMemcpyAsync(cp.bias, bias.data(), bias.size() * sizeof(__half), cudaMemcpyHostToDevice, st));
+  VAEX_CUDA(cudaMemcpyAsync(cp.bias, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice, st));
   VAEX_CUDA(cudaStreamSynchronize(st));
   VAEX_CUDA(cudaFuncSetAttribute(chain_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_MAX));
   cp.ready = true;

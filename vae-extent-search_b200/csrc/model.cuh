@@ -30,7 +30,7 @@ struct TcPack {
 // packed weights of a fused tcgen05 MLP chain (chain_tc.cu)
 struct ChainPack {
   __half* w = nullptr;
-  __half* bias = nullptr;
+  float* bias = nullptr;
   int smem_bytes = 0;
   bool ready = false;
   alignas(8) unsigned char params_storage[320] = {};   // shape part of ChainParams

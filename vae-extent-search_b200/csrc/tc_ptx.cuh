@@ -185,6 +185,10 @@ __device__ __forceinline__ void sts_b32(uint32_t addr, uint32_t a) {
 __device__ __forceinline__ void sts_b16(uint32_t addr, uint32_t a) {
   asm volatile("st.shared.b16 [%0], %1;" ::"r"(addr), "h"((uint16_t)a) : "memory");
 }
+// ask the L2 to fetch the 128-byte line holding p
+__device__ __forceinline__ void prefetch_l2(const void* p) {
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
 // ask the L2 to fetch [p, p + bytes) (16-byte aligned, bytes % 16 == 0)
 __device__ __forceinline__ void prefetch_l2_bulk(const void* p, uint32_t bytes) {
   asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
