@@ -230,7 +230,7 @@ def test_extent_vae_golden():
     big_mu, big_lv = torch.zeros(200000, 64, device="cuda"), torch.full((200000, 64), np.log(4.0), device="cuda")
     zs = reg.reparameterize(big_mu, big_lv, seed=11)
     assert abs(zs.mean().item()) < 0.01 and abs(zs.std().item() - 2.0) < 0.01
-    eps = torch.randn(300, 64, device="cuda")
+    eps = torch.randn(300, 64, generator=torch.Generator().manual_seed(3)).cuda()
     np.testing.assert_allclose(reg.reparameterize(mu, logvar, eps=eps).cpu().numpy(),
                                O.reparameterize(mu.cpu(), logvar.cpu(), eps.cpu()).numpy(), rtol=1e-5, atol=1e-6)
 
@@ -301,6 +301,24 @@ def test_snap_bit_exact_and_legalise():
     std = rng.uniform(0.3, 1.5, 48).astype(np.float32)
     want = O.snap_round_clamp(xb, mean, std).numpy()
     assert np.array_equal(vaex_b200.snap_extents(torch.from_numpy(xb).cuda(), mean, std).cpu().numpy(), want)
+    # adversarial: exp(v) within a few ulp of every rounding boundary k + 0.5 (the kernel's fp32 fast path must hand
+    # these to its exact path); expected = correctly rounded exp.  mean 0, std 1 (1 + 1e-8 == 1 in fp32) -> v = x
+    k = np.arange(1, 200001, dtype=np.float64)
+    base = np.log(k + 0.5).astype(np.float32)
+    adv = np.stack([np.nextafter(base, np.float32(np.inf)) if d > 0 else np.nextafter(base, np.float32(-np.inf)) if d < 0 else base
+                    for d in (-1, 0, 1)], 1)
+    for _ in range(2):
+        adv = np.concatenate([adv, np.nextafter(adv[:, :1], np.float32(-np.inf)), np.nextafter(adv[:, -1:], np.float32(np.inf))], 1)
+    adv = np.ascontiguousarray(adv.astype(np.float32))                          # [200000, 7]: base -3 .. +3 ulp
+    zero, one = np.zeros(adv.shape[1], np.float32), np.ones(adv.shape[1], np.float32)
+    exact = np.maximum(np.rint(np.exp(adv.astype(np.float64)).astype(np.float32)), 1).astype(np.int32)
+    got = vaex_b200.snap_extents(torch.from_numpy(adv).cuda(), zero, one).cpu().numpy()
+    assert np.array_equal(got, exact)
+    exact1 = np.maximum(np.rint(np.expm1(adv.astype(np.float64)).astype(np.float32)), 1).astype(np.int32)
+    got1 = vaex_b200.snap_extents(torch.from_numpy(adv).cuda(), zero, one, log1p=True).cpu().numpy()
+    assert np.array_equal(got1, exact1)
+    # (torch's vectorised CPU expf is a 1-ulp routine, so on boundary cases it may itself differ from the exact result)
+    assert (O.snap_round_clamp(adv, zero, one).numpy() != exact).mean() < 0.02
     # divisor legalisation against the utils.cc:446-463 restatement; task-1264-like loop bounds
     bounds = [1, 3, 4, 28, 56, 57, 64, 128, 960, 4096]
     ext, last = [], []
