@@ -123,6 +123,23 @@ int vaex_segsum_encode(vaex_model_t h, const float* feats_dev, const int32_t* se
 int vaex_segsum_mlp_predict_host(vaex_model_t h, const float* feats_host, const int32_t* sizes_host,
                                  int64_t n_programs, int64_t n_rows, float* scores_host, int flags);
 
+/* ---- Ansor's packed per-store feature blob (SerializeFeatures, src/auto_scheduler/feature.cc:1562-1622;
+ *      replaces unpack_feature, python/tvm/auto_scheduler/feature.py:49-158).  Host functions. ---- */
+/* validates the blob and returns counts[5] = {records, feature rows (a record that failed lowering counts as
+ * one zero row, feature.py:114-116), throughputs, task ids, min costs} */
+int vaex_feature_blob_scan(const void* blob_host, int64_t nbytes, int32_t vec_len, int64_t* counts);
+/* feats_host fp32 [rows, vec_len], sizes_host int32[records] (rows per record), lowered_host uint8[records]
+ * (0 where the record had size 0; nullable), trailers nullable.  Same errors as the reference's assertions. */
+int vaex_feature_blob_unpack(const void* blob_host, int64_t nbytes, int32_t vec_len, float* feats_host,
+                             int32_t* sizes_host, uint8_t* lowered_host_or_null, float* throughputs_host_or_null,
+                             int32_t* task_ids_host_or_null, float* min_costs_host_or_null);
+/* MLPModel.predict from the bytes TVM's GetPerStoreFeaturesFromStates returns (mlp_model.py:832-846 with
+ * feature.py:224-246): parse -> pinned staging -> chunked H2D overlapped with the kernels -> scores_host
+ * [records].  The model's input width must equal the blob's vec_len (a constant task embedding is folded into
+ * the first bias by the caller).  Synchronous. */
+int vaex_segsum_mlp_predict_blob(vaex_model_t h, const void* blob_host, int64_t nbytes, float* scores_host,
+                                 int64_t n_scores, int flags);
+
 /* ---- extent-VAE family ----------------------------------------------------------------- */
 /* VAE_feature_head.encode / VAECostPredictor.encode (utils/model.py:52-56, :145-160) */
 int vaex_vae_encode(vaex_model_t h, const float* x_dev, int64_t n, float* mu_dev,

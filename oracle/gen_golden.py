@@ -250,6 +250,34 @@ def gen_train(ns):
     np.savez_compressed(os.path.join(OUT, "train.npz"), **out)
 
 
+def gen_feature_blob(ns):
+    """A packed per-store feature blob (layout of SerializeFeatures, feature.cc:1562-1622, written by
+    oracle/feature_blob.serialize_features) through the reference's own unpack_feature (feature.py:49-158)."""
+    from oracle import feature_blob as FB
+    from oracle.ref_import import load_reference_feature
+    ref = load_reference_feature()
+    rng = np.random.default_rng(77)
+    feats = []
+    for i in range(41):
+        if i in (0, 7, 40):
+            feats.append(None)                              # failed lowering -> size 0
+        elif i == 13:
+            feats.append(np.zeros((3, 164), np.float32))    # lowered, but all-zero features
+        else:
+            f = (rng.random((int(rng.integers(1, 33)), 164)) * 24).astype(np.float32)
+            f[:, rng.random(164) < 0.3] = 0
+            feats.append(f)
+    thr = rng.random(41).astype(np.float32)
+    task_ids = rng.integers(0, 5, 41).astype(np.int32)
+    min_costs = rng.random(5).astype(np.float32)
+    blob = FB.serialize_features(feats, thr, task_ids, min_costs)
+    f_ref, thr_ref, ids_ref, min_ref = ref.unpack_feature(bytearray(blob))
+    out = {"blob": np.frombuffer(blob, np.uint8), "thr": np.asarray(thr_ref), "task_ids": np.asarray(ids_ref),
+           "min_costs": np.asarray(min_ref), "sizes": np.array([len(f) for f in f_ref], np.int32),
+           "flat": np.concatenate([np.asarray(f, np.float64) for f in f_ref], 0)}
+    np.savez_compressed(os.path.join(OUT, "feature_blob.npz"), **out)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     ns = load_reference()
@@ -259,6 +287,7 @@ def main():
     gen_select(ns)
     gen_segment_family(ns)
     gen_train(ns)
+    gen_feature_blob(ns)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

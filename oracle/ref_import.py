@@ -13,6 +13,7 @@ Modules loaded:
   python/tvm/auto_scheduler/cost_model/mlp_model.py
   scripts/pre_experiments/model_myself/utils/{model,select,common}.py
   scripts/vae_experiments/models/{vae,regression}.py
+  python/tvm/auto_scheduler/feature.py (unpack_feature only; load_reference_feature())
 """
 import importlib.machinery
 import importlib.util
@@ -108,3 +109,20 @@ def load_reference():
         ns.seg_reg_error = repr(e)
     _CACHE["ns"] = ns
     return ns
+
+
+def load_reference_feature():
+    """The reference's python/tvm/auto_scheduler/feature.py (for unpack_feature, :49-158) under the stub
+    package; its C++ entry points (_ffi_api) are placeholders that raise."""
+    if "feature" in _CACHE:
+        return _CACHE["feature"]
+    load_reference()
+
+    class _Dummy:
+        pass
+
+    _stub("tvm.auto_scheduler.loop_state", State=_Dummy, StateObject=_Dummy)
+    _stub("tvm.auto_scheduler._ffi_api")
+    mod = _load("tvm.auto_scheduler._ref_feature", "python/tvm/auto_scheduler/feature.py")
+    _CACHE["feature"] = mod
+    return mod

@@ -36,6 +36,9 @@ SIGNATURES = {
     "vaex_vae_encode": ([vp, vp, i64, vp, vp, vp], ctypes.c_int),
     "vaex_reparam": ([vp, vp, vp, u64, u64, vp, i64, i32, vp], ctypes.c_int),
     "vaex_vae_decode": ([vp, vp, i64, vp, vp], ctypes.c_int),
+    "vaex_feature_blob_scan": ([vp, i64, i32, vp], ctypes.c_int),
+    "vaex_feature_blob_unpack": ([vp, i64, i32, vp, vp, vp, vp, vp, vp], ctypes.c_int),
+    "vaex_segsum_mlp_predict_blob": ([vp, vp, i64, vp, i64, ctypes.c_int], ctypes.c_int),
     "vaex_decode_snap": ([vp, vp, i64, vp, vp, vp, vp, ctypes.c_int, vp, vp, i32, vp], ctypes.c_int),
     "vaex_snap_extents": ([vp, i64, i32, vp, vp, ctypes.c_int, vp, vp, i32, vp, vp], ctypes.c_int),
     "vaex_predict_cost": ([vp, vp, i64, vp, vp, u64, f32, vp], ctypes.c_int),

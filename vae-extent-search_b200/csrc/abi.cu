@@ -266,6 +266,7 @@ int vaex_model_destroy(vaex_model_t h) {
   if (h->tc.wl0) cudaFree(h->tc.wl0);
   if (h->tc.wl1) cudaFree(h->tc.wl1);
   for (auto& sl : h->slots) { if (sl.feats) cudaFree(sl.feats); if (sl.off) cudaFree(sl.off); if (sl.scores) cudaFree(sl.scores); }
+  for (auto& pn : h->pinned) if (pn.p) cudaFreeHost(pn.p);
   for (auto& s : h->copy_streams) if (s) cudaStreamDestroy(s);
   for (auto& e : h->events) if (e) cudaEventDestroy(e);
   delete h;

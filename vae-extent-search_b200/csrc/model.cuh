@@ -60,7 +60,9 @@ struct vaex_model {
   vaex::DevBuf topk_ws;
   vaex::DevBuf tc_ws;                  // first_prog + rowmask of the tcgen05 kernel
   struct HostSlot { float* feats = nullptr; int32_t* off = nullptr; float* scores = nullptr; size_t rows = 0, progs = 0; };
-  HostSlot slots[2];                   // device staging of vaex_segsum_mlp_predict_host
+  HostSlot slots[2];                   // device staging of vaex_segsum_mlp_predict_host / _blob
+  struct PinnedSlot { void* p = nullptr; size_t bytes = 0; };
+  PinnedSlot pinned[2];                // host staging of vaex_segsum_mlp_predict_blob
   cudaStream_t copy_streams[2] = {nullptr, nullptr};
   cudaEvent_t events[4] = {nullptr, nullptr, nullptr, nullptr};
 
