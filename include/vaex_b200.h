@@ -174,6 +174,13 @@ int vaex_predict_cost(vaex_model_t h, const float* z_dev, int64_t n, float* cost
 /* select_topk_z_grad's autograd.grad(cost.sum(), z) (utils/select.py:128-135) */
 int vaex_cost_grad_z(vaex_model_t h, const float* z_dev, int64_t n, float* cost_dev,
                      float* grad_z_dev, float* grad_norm_dev_or_null, void* stream);
+/* select_topk_latent_diversity (utils/select.py:185-270): k-center greedy on the L2-normalised rows
+ * z[cand] with z[used] as the initial centres; out_sel_dev int64[k] = the chosen entries of cand_dev in
+ * selection order.  z_dev fp32 [n, L]; cand_dev int64[M]; used_dev int64[U] (U may be 0).  Returns after the
+ * selection is complete (it reads one status word back). */
+int vaex_kcenter_select(const float* z_dev, int64_t n, int32_t L, const int64_t* cand_dev, int64_t M,
+                        const int64_t* used_dev, int64_t U, int32_t k, float eps, int64_t* out_sel_dev,
+                        void* stream);
 /* multi-step ascent z += lr * dcost/dz (new surface, BASELINE config 3) */
 int vaex_latent_ascent(vaex_model_t h, float* z_inout_dev, int64_t n, int32_t steps, float lr,
                        float* cost_dev, void* stream);

@@ -250,6 +250,34 @@ def gen_train(ns):
     np.savez_compressed(os.path.join(OUT, "train.npz"), **out)
 
 
+def gen_kcenter(ns):
+    """n2: select_topk_latent_diversity (select.py:185-270) on seeded latents, and select_programs with a
+    diversity budget.  The candidate order the reference iterates (list(set)) is stored with the result."""
+    g = torch.Generator().manual_seed(21)
+    z = torch.randn(2000, 64, generator=g) * torch.rand(2000, 1, generator=g) * 3
+    out = {"z": z.numpy()}
+    rng = np.random.default_rng(22)
+    perm = rng.permutation(2000)
+    cases = {"a": (perm[:320], perm[320:620], 24), "b": (perm[700:800], np.zeros(0, np.int64), 10),
+             "c": (perm[900:916], perm[1000:1003], 16)}
+    for tag, (cand, used, k) in cases.items():
+        cset = set(cand.tolist())
+        order = np.array(list(cset), dtype=np.int64)
+        sel, rest = ns.select.select_topk_latent_diversity(z, set(cset), set(used.tolist()), k)
+        out.update({"cand_" + tag: order, "used_" + tag: np.array(list(set(used.tolist())), np.int64), "k_" + tag: np.int64(k),
+                    "sel_" + tag: sel, "rest_" + tag: np.array(sorted(rest), np.int64)})
+    sel_ref = np.load(os.path.join(OUT, "select.npz"))
+    torch.manual_seed(11)
+    reg = ns.vae_model.VAECostPredictor(48, hidden_dim=256, latent_dim=64).eval()
+    reg.load_state_dict({k[4:]: torch.from_numpy(sel_ref[k]) for k in sel_ref.files if k.startswith("reg.")})
+    sel_prog, rem_prog = ns.select.select_programs(
+        reg, sel_ref["x"], set(sel_ref["used"].tolist()), set(sel_ref["remaining"].tolist()), num_select=64, T_mc=4,
+        uncertainty_topk=10 ** 9, w_cost=0.5, w_unc=0.0, w_div=0.5, grad_num=2, rand_num=0,
+        rng=np.random.default_rng(42), device=torch.device("cpu"), topk_factor=5)
+    out.update({"sel_prog_div": sel_prog, "rem_prog_div": np.array(sorted(rem_prog), np.int64)})
+    np.savez_compressed(os.path.join(OUT, "kcenter.npz"), **out)
+
+
 def gen_feature_blob(ns):
     """A packed per-store feature blob (layout of SerializeFeatures, feature.cc:1562-1622, written by
     oracle/feature_blob.serialize_features) through the reference's own unpack_feature (feature.py:49-158)."""
@@ -288,6 +316,7 @@ def main():
     gen_segment_family(ns)
     gen_train(ns)
     gen_feature_blob(ns)
+    gen_kcenter(ns)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

@@ -367,3 +367,23 @@ def latent_ascent(P, z0, steps, lr):
         _, g = cost_grad_z(P, z)
         z = z + lr * g
     return z, predict_cost(P, z).detach()
+
+
+def kcenter_select(z, cand, used, k, eps=1e-12):
+    """select_topk_latent_diversity (utils/select.py:185-270) on an explicit candidate order: k-center greedy
+    over L2-normalised rows, centres initialised with `used`; returns the chosen entries of cand in order."""
+    z = _t(z)
+    zn = z / (z.norm(dim=1, keepdim=True) + eps)
+    cand = np.asarray(cand, dtype=np.int64)
+    zc = zn[torch.from_numpy(cand)]
+    if len(used):
+        min_d = torch.cdist(zc, zn[torch.from_numpy(np.asarray(used, dtype=np.int64))], p=2).min(dim=1).values
+    else:
+        min_d = torch.full((len(cand),), float("inf"))
+    sel = []
+    for _ in range(int(k)):
+        j = int(torch.argmax(min_d))
+        sel.append(cand[j])
+        min_d[j] = -float("inf")
+        min_d = torch.minimum(min_d, torch.cdist(zc, zc[j:j + 1], p=2).squeeze(1))
+    return np.array(sel, dtype=np.int64)

@@ -494,3 +494,51 @@ def test_predict_blob_and_embedding_fold():
         check_scores(got[~invalid], want[~invalid], 0)
         simt = m._predict_a_task(m.base_model, task, objs, flags=_lib.F_FORCE_SIMT)
         check_scores(simt[~invalid], want[~invalid], _lib.F_FORCE_SIMT)
+
+
+def test_kcenter_select_matches_reference():
+    """n2: vaex_kcenter_select against the reference's select_topk_latent_diversity picks (tests/golden/kcenter.npz),
+    through the C ABI with the reference's candidate order and through the Python mirror with sets; then
+    select_programs with a diversity budget."""
+    g = load_golden("kcenter.npz")
+    z = torch.from_numpy(g["z"]).cuda()
+    lib = _lib.load()
+    for tag in "abc":
+        cand, used, k = g["cand_" + tag], g["used_" + tag], int(g["k_" + tag])
+        cd = torch.from_numpy(cand).cuda()
+        ud = torch.from_numpy(used).cuda() if len(used) else None
+        sel = torch.empty(k, dtype=torch.int64, device="cuda")
+        _lib.check(lib.vaex_kcenter_select(_lib.ptr(z), z.shape[0], 64, _lib.ptr(cd), len(cand), _lib.ptr(ud), len(used), k,
+                                           1e-12, _lib.ptr(sel), _lib.stream_ptr()))
+        assert np.array_equal(sel.cpu().numpy(), g["sel_" + tag]), tag
+        cset = set(cand.tolist())
+        if list(cset) == cand.tolist():                     # same set iteration order as the generating interpreter
+            got, rest = vaex_b200.select.select_topk_latent_diversity(z, set(cset), set(used.tolist()), k)
+            assert np.array_equal(got, g["sel_" + tag]) and np.array_equal(sorted(rest), g["rest_" + tag])
+    # a larger, seeded case against the oracle (more centres than candidates, k = 64)
+    rng = np.random.default_rng(8)
+    zz = rng.standard_normal((20000, 64)).astype(np.float32)
+    perm = rng.permutation(20000)
+    cand, used = perm[:1500].astype(np.int64), perm[1500:6500].astype(np.int64)
+    sel = torch.empty(64, dtype=torch.int64, device="cuda")
+    zd, cd, ud = torch.from_numpy(zz).cuda(), torch.from_numpy(cand).cuda(), torch.from_numpy(used).cuda()
+    _lib.check(lib.vaex_kcenter_select(_lib.ptr(zd), 20000, 64, _lib.ptr(cd), 1500, _lib.ptr(ud), 5000, 64, 1e-12, _lib.ptr(sel),
+                                       _lib.stream_ptr()))
+    assert np.array_equal(sel.cpu().numpy(), O.kcenter_select(zz, cand, used, 64))
+    bad = torch.tensor([5, 20000], dtype=torch.int64, device="cuda")
+    with pytest.raises(_lib.VaexError, match="out of range"):
+        _lib.check(lib.vaex_kcenter_select(_lib.ptr(zd), 20000, 64, _lib.ptr(bad), 2, None, 0, 1, 1e-12, _lib.ptr(sel), _lib.stream_ptr()))
+    with pytest.raises(_lib.VaexError, match="more points"):
+        _lib.check(lib.vaex_kcenter_select(_lib.ptr(zd), 20000, 64, _lib.ptr(cd), 3, None, 0, 4, 1e-12, _lib.ptr(sel), _lib.stream_ptr()))
+    # full selection with a diversity budget
+    gs = load_golden("select.npz")
+    reg = vaex_b200.VAECostPredictor(48, hidden_dim=256, latent_dim=64)
+    reg.load_state_dict(split_sd(gs, "reg."))
+    reg = reg.cuda().eval()
+    reg.set_tensor_cores(False)
+    sel_prog, rem_prog = vaex_b200.select_programs(
+        reg, gs["x"], set(gs["used"].tolist()), set(gs["remaining"].tolist()), num_select=64, T_mc=4, uncertainty_topk=10 ** 9,
+        w_cost=0.5, w_unc=0.0, w_div=0.5, grad_num=2, rand_num=0, rng=np.random.default_rng(42),
+        device=torch.device("cuda"), topk_factor=5)
+    assert np.array_equal(sel_prog, g["sel_prog_div"])
+    assert np.array_equal(np.array(sorted(rem_prog)), g["rem_prog_div"])

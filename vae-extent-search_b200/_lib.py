@@ -56,6 +56,7 @@ SIGNATURES = {
     "vaex_loss_eval": ([ctypes.c_int, vp, vp, i64, vp, vp, vp], ctypes.c_int),
     "vaex_adam_step": ([vp, vp, vp, vp, i64, i64, f32, f32, f32, f32, f32, f32, f32, vp, vp], ctypes.c_int),
     "vaex_sgd_step": ([vp, vp, i64, f32, f32, f32, vp], ctypes.c_int),
+    "vaex_kcenter_select": ([vp, i64, i32, vp, i64, vp, i64, i32, f32, vp, vp], ctypes.c_int),
     "vaex_topk": ([vp, i64, i32, vp, vp, vp, vp, vp], ctypes.c_int),
 }
 

@@ -6,7 +6,7 @@ np.argsort(pred[list(set)])[-k:] on the host (select.py:54-81)."""
 import numpy as np
 import torch
 
-from . import vae_model
+from . import _lib, vae_model
 
 
 def _mask_from(indices, n, device):
@@ -68,26 +68,21 @@ def select_topk_uncertainty(model, input_tensor, remaining_indices, num_select, 
 
 def select_topk_latent_diversity(z, candidate_indices, used_indices, select_n_div, chunk_size=1024, eps=1e-12):
     """select.py:185-270: k-center greedy on L2-normalised latents, centres = used_indices.
-    M <= 320 candidates: a handful of tiny device ops (SURVEY 8f row n2 moves it into one CTA)."""
+    One call: normalise, min distance to the centres, then all k greedy steps in a single CTA (vaex_kcenter_select)."""
     if select_n_div == 0 or len(candidate_indices) == 0:
         return np.array([], dtype=np.int64), candidate_indices
-    with torch.no_grad():
-        zn = z.detach() / (z.detach().norm(dim=1, keepdim=True) + eps)
-        cand = np.array(list(candidate_indices), dtype=np.int64)
-        k = min(select_n_div, len(cand))
-        zc = zn[torch.from_numpy(cand).to(z.device)]
-        used = np.array(list(used_indices), dtype=np.int64)
-        if len(used):
-            min_d = torch.cdist(zc, zn[torch.from_numpy(used).to(z.device)]).min(dim=1).values
-        else:
-            min_d = torch.full((len(cand),), float("inf"), device=z.device)
-        selected = []
-        for _ in range(k):
-            j = int(torch.argmax(min_d).item())
-            selected.append(cand[j])
-            min_d[j] = -float("inf")
-            min_d = torch.minimum(min_d, torch.cdist(zc, zc[j:j + 1]).squeeze(1))
-    diverse = np.array(selected, dtype=np.int64)
+    if not z.is_cuda:
+        raise _lib.VaexError("vaex_b200 needs CUDA tensors (no CPU fallback)")
+    zc = z.detach().contiguous().float()
+    cand = np.array(list(candidate_indices), dtype=np.int64)
+    k = min(select_n_div, len(cand))
+    used = np.array(list(used_indices), dtype=np.int64)
+    cand_d = torch.from_numpy(cand).to(z.device)
+    used_d = torch.from_numpy(used).to(z.device) if len(used) else None
+    sel = torch.empty(k, dtype=torch.int64, device=z.device)
+    _lib.check(_lib.load().vaex_kcenter_select(_lib.ptr(zc), zc.shape[0], zc.shape[1], _lib.ptr(cand_d), len(cand),
+                                              _lib.ptr(used_d), len(used), k, float(eps), _lib.ptr(sel), _lib.stream_ptr()))
+    diverse = sel.cpu().numpy()
     candidate_indices = set(candidate_indices)
     candidate_indices.difference_update(diverse.tolist())
     return diverse, candidate_indices
