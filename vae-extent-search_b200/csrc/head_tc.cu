@@ -7,18 +7,21 @@
 //   (SegmentSumMLPModule.forward, python/tvm/auto_scheduler/cost_model/mlp_model.py:210-221)
 //
 // One persistent CTA pair (cta_group::2) per 256 programs per step: each CTA owns 128 programs
-// (TMEM lanes) and half of the output units of both 256x256 weights (resident, 128 KB fp16).
-// A worker thread owns one program row and one 128-column half of it end to end:
-//   A. its 512 B of S arrive as 16 LDG.256 (issued during the previous step's second GEMM),
-//      go as fp32 into TMEM columns [0,256) (the residual) and as fp16 into the A operand (64 KB)
-//   B. GEMM 0 -> TMEM columns [256,512)
-//   C. y1 = relu(acc + bl0) + residual: fp32 back over the residual, fp16 over the A operand
-//   D. GEMM 1 -> the same accumulator columns
-//   E. y2 = relu(acc + bl1) + residual, dotted with wd in registers
-// so no intermediate touches HBM and S is read exactly once.  Warps 0-7 are workers (lane
-// quarter = warp % 4, column half = warp / 4), warp 8 of the leader CTA issues the MMAs; hand-offs
-// are mbarriers (warp arrivals -> issuer, tcgen05.commit multicast -> workers), no cluster barrier
-// inside the loop.
+// (TMEM lanes) and half of the output units of both 256x256 weights (resident, 128 KB fp16); the
+// 64 KB A operand holds fp16(y0) and is rewritten in place with fp16(y1).  TMEM: columns [0,256)
+// = fp32 y0 (the residual of layer 0), [256,512) = the accumulator.  Nothing intermediate touches
+// HBM and S is read exactly once.
+//
+// v3 (same piece pipeline as chain_tc.cu): every GEMM is issued as four MMA pieces (n-half, k-half),
+// k-half major, with one commit per n-half; the epilogue of n-half h writes exactly k-half h of the
+// next GEMM's operand, so pieces start as soon as their half is published (mbarriers IN0/IN1) and
+// their accumulator half has been drained.  score = wd.relu(acc1 + bl1) + wd.y1 + bd, and wd.y1 is
+// accumulated while y1 is formed, so y1 never goes back to TMEM and the last epilogue reads only
+// the accumulator.  16 worker warps: thread = (program row, 32-column group of the half).  The
+// residual columns double as the staging buffer of the next step: they are free once the layer-0
+// epilogue has read them, so the next rows are loaded and stored there (fp32) behind GEMM 1, and
+// the step boundary only converts them into the operand (tcgen05.ld -> fp16 -> st.shared).
+// Warp 16 of the leader CTA issues the MMAs.
 #include <algorithm>
 #include <vector>
 
@@ -34,8 +37,8 @@ constexpr int W_BYTES = 4 * ATOM;                 // [128 units x 256 k] fp16, K
 constexpr int WL0_OFF = 0, WL1_OFF = W_BYTES, A_OFF = 2 * W_BYTES;
 constexpr int SMEM_TILES = 3 * W_BYTES;           // 196608
 constexpr int SMEM_DYN = SMEM_TILES + 1024;
-constexpr int WORKERS = 256, THREADS = 288;     // 8 worker warps + the MMA issuer
-enum { B_Y0 = 0, B_ACC0, B_Y1, B_ACC1, B_COUNT };
+constexpr int WORKER_WARPS = 16, WORKERS = 32 * WORKER_WARPS, THREADS = WORKERS + 32;
+enum { B_IN0 = 0, B_IN1, B_ACC0, B_ACC1, B_COUNT };
 
 __host__ __device__ inline uint32_t sw128_off(int row, int k) {
   return (uint32_t)((k >> 6) * ATOM + (row >> 3) * 1024 + (row & 7) * 128 + ((((k & 63) >> 3) ^ (row & 7)) << 4) +
@@ -70,6 +73,7 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&v)[32
       : "memory");
 }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
 struct F8 { float v[8]; };
 __device__ __forceinline__ F8 ldg_stream_f8(const float* p) {   // one full 32 B sector per lane
   F8 r;
@@ -86,7 +90,7 @@ head_tc_kernel(const HeadParams p) {
   __shared__ __align__(8) uint64_t bars[B_COUNT];
   __shared__ uint32_t tmem_base_slot;
   __shared__ __align__(16) float s_bl0[HID], s_bl1[HID], s_wd[HID], s_ns[HID], s_nb[HID];
-  __shared__ float s_dot[TILE];
+  __shared__ float s_dot[3 * TILE];
 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const uint32_t sbase = ptx::smem_u32(smem);
@@ -98,9 +102,9 @@ head_tc_kernel(const HeadParams p) {
   const bool has_norm = p.nscale != nullptr;
 
   if (threadIdx.x == 0) {
-    ptx::mbar_init(bar(B_Y0), 16);      // 8 worker warps x 2 CTAs
+    ptx::mbar_init(bar(B_IN0), 2 * WORKER_WARPS);      // worker warps x 2 CTAs
+    ptx::mbar_init(bar(B_IN1), 2 * WORKER_WARPS);
     ptx::mbar_init(bar(B_ACC0), 1);
-    ptx::mbar_init(bar(B_Y1), 16);
     ptx::mbar_init(bar(B_ACC1), 1);
     ptx::fence_mbar_init();
   }
@@ -124,40 +128,39 @@ head_tc_kernel(const HeadParams p) {
   ptx::tc_fence_after();
   const uint32_t tmem = tmem_base_slot;
 
-  if (warp < 8) {
+  if (warp < WORKER_WARPS) {
     // ===== workers =====
-    const int q = warp & 3, ch = warp >> 2;          // TMEM lane quarter, column half
-    const uint32_t lane_base = (uint32_t)(32 * q) << 16;
+    const int q = warp & 3, cg = warp >> 2;          // TMEM lane quarter, 32-column group of a half
     const int row = 32 * q + lane;                   // program row (TMEM lane) of this thread
     const uint32_t a_row = sbase + A_OFF + (row >> 3) * 1024 + (row & 7) * 128;
     const int sw = row & 7;
-    const int col0 = 128 * ch;
-    const uint32_t t_res = tmem + lane_base + col0, t_acc = tmem + lane_base + 256 + col0;
+    const uint32_t t_res = tmem + ((uint32_t)(32 * q) << 16), t_acc = t_res + 256;
     const float bd = p.bd[0];
-    F8 pf[16];                                       // this thread's 128 floats of the next step
+    float4 x[8];                                     // 32 floats of the next step's row (one half at a time)
 
-    auto fetch = [&](int t) {
+    auto load_half = [&](int t, int h) {
       const int64_t prog = (int64_t)t * PAIR + rank * TILE + row;
       if (t < p.T && prog < p.P) {
-        const float* src = p.S + prog * HID + col0;
+        const float* src = p.S + prog * HID + 128 * h + 32 * cg;
 #pragma unroll
-        for (int j = 0; j < 16; ++j) pf[j] = ldg_stream_f8(src + 8 * j);
+        for (int j = 0; j < 4; ++j) {
+          const F8 f = ldg_stream_f8(src + 8 * j);
+          x[2 * j] = make_float4(f.v[0], f.v[1], f.v[2], f.v[3]);
+          x[2 * j + 1] = make_float4(f.v[4], f.v[5], f.v[6], f.v[7]);
+        }
       } else {
 #pragma unroll
-        for (int j = 0; j < 16; ++j)
-#pragma unroll
-          for (int e = 0; e < 8; ++e) pf[j].v[e] = 0.f;
+        for (int j = 0; j < 8; ++j) x[j] = make_float4(0.f, 0.f, 0.f, 0.f);
       }
     };
-    auto prefetch_l2 = [&](int t) {                  // this warp's 16 KB slice of a later step
+    auto prefetch_l2 = [&](int t) {                  // this warp's 8 KB slice of a later step
       if (lane != 0 || t >= p.T) return;
-      const int64_t r0 = (int64_t)t * PAIR + rank * TILE + warp * 16;
-      const int64_t nr = min((int64_t)16, (int64_t)p.P - r0);
+      const int64_t r0 = (int64_t)t * PAIR + rank * TILE + warp * 8;
+      const int64_t nr = min((int64_t)8, (int64_t)p.P - r0);
       if (nr > 0) ptx::prefetch_l2_bulk(p.S + r0 * HID, (uint32_t)(nr * HID * 4));
     };
-    // fp32 values of 32 columns -> 64 B of the fp16 A operand (columns [col0 + 32c, +32))
-    auto pack32 = [&](const uint32_t (&v)[32], int c) {
-      const int cc = 4 * ch + c;                     // 32-column chunk of the row
+    // 32 fp32 values -> 64 B of the fp16 A operand, 32-column chunk cc of the row
+    auto pack32 = [&](const uint32_t (&v)[32], int cc) {
       const uint32_t base = a_row + (cc >> 1) * ATOM;
 #pragma unroll
       for (int m = 0; m < 4; ++m)
@@ -168,84 +171,115 @@ head_tc_kernel(const HeadParams p) {
                     ptx::cvt_h2_sat(__uint_as_float(v[8 * m + 6]), __uint_as_float(v[8 * m + 7])));
     };
     auto publish = [&](int b) {                      // operand + TMEM writes of this warp -> issuer
-      tmem_st_wait();
       ptx::fence_proxy_async();
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_cluster_relaxed(bar(b), 0);
     };
-
-    prefetch_l2(cluster + n_clusters);
-    fetch(cluster);
-    int it = 0;
-    for (int t = cluster; t < p.T; t += n_clusters, ++it) {
-      prefetch_l2(t + 2 * n_clusters);
-      // ---- A. y0 = norm(S): fp32 -> TMEM residual, fp16 -> A operand ----
+    // y0 half h of the loaded row: norm -> fp32 residual columns of TMEM.  The residual doubles as the staging
+    // buffer of the next step: it is free as soon as the layer-0 epilogue has read it, long before the operand is.
+    auto commit_half = [&](int h) {
+      const int col = 128 * h + 32 * cg;
+      uint32_t v[32];
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        uint32_t v[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          float x = pf[4 * c + (j >> 3)].v[j & 7];
-          if (has_norm) x = x * s_ns[col0 + 32 * c + j] + s_nb[col0 + 32 * c + j];
-          v[j] = __float_as_uint(x);
+      for (int j = 0; j < 8; ++j) {
+        float4 a = x[j];
+        if (has_norm) {
+          const float4 sc = *reinterpret_cast<const float4*>(s_ns + col + 4 * j), sh = *reinterpret_cast<const float4*>(s_nb + col + 4 * j);
+          a.x = a.x * sc.x + sh.x; a.y = a.y * sc.y + sh.y; a.z = a.z * sc.z + sh.z; a.w = a.w * sc.w + sh.w;
         }
-        tmem_st32(t_res + 32 * c, v);
-        pack32(v, c);
+        v[4 * j] = __float_as_uint(a.x); v[4 * j + 1] = __float_as_uint(a.y);
+        v[4 * j + 2] = __float_as_uint(a.z); v[4 * j + 3] = __float_as_uint(a.w);
       }
-      publish(B_Y0);
-      // ---- C. y1 = relu(acc + bl0) + y0 -> residual (fp32) and A operand (fp16) ----
-      ptx::mbar_wait(bar(B_ACC0), it & 1);
-      ptx::tc_fence_after();
+      tmem_st32(t_res + col, v);
+    };
+    // residual half h -> fp16 operand k-half h, publish
+    auto pack_half = [&](int h) {
+      uint32_t v[32];
+      ptx::tmem_ld32(t_res + 128 * h + 32 * cg, v);
+      ptx::tmem_ld_wait();
+      pack32(v, 4 * h + cg);
+      publish(h == 0 ? B_IN0 : B_IN1);
+    };
+
+    uint32_t acc_use0 = 0, acc_use1 = 0;
+    prefetch_l2(cluster + n_clusters);
+    load_half(cluster, 0);
+    commit_half(0);
+    load_half(cluster, 1);
+    commit_half(1);
+    tmem_st_wait();
+    pack_half(0);
+    pack_half(1);
+    for (int t = cluster; t < p.T; t += n_clusters) {
+      prefetch_l2(t + 2 * n_clusters);
+      float dot0 = 0.f, dot1 = 0.f;
+      // ---- layer 0: y1 = relu(acc + bl0) + y0 -> operand (fp16); wd . y1 accumulated ----
 #pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
+      for (int h = 0; h < 2; ++h) {
+        const int col = 128 * h + 32 * cg;
+        if (h == 0) { ptx::mbar_wait(bar(B_ACC0), acc_use0 & 1); ++acc_use0; }
+        else        { ptx::mbar_wait(bar(B_ACC1), acc_use1 & 1); ++acc_use1; }
+        ptx::tc_fence_after();
         uint32_t v[32], r[32];
-        ptx::tmem_ld32(t_acc + 32 * c, v);
-        ptx::tmem_ld32(t_res + 32 * c, r);
+        ptx::tmem_ld32(t_acc + col, v);
+        ptx::tmem_ld32(t_res + col, r);
         ptx::tmem_ld_wait();
-        const float4* b4 = reinterpret_cast<const float4*>(s_bl0 + col0 + 32 * c);
+        const float4* b4 = reinterpret_cast<const float4*>(s_bl0 + col);
+        const float4* w4 = reinterpret_cast<const float4*>(s_wd + col);
 #pragma unroll
         for (int j4 = 0; j4 < 8; ++j4) {
-          const float4 b = b4[j4];
-          v[4 * j4 + 0] = __float_as_uint(fmaxf(__uint_as_float(v[4 * j4 + 0]) + b.x, 0.f) + __uint_as_float(r[4 * j4 + 0]));
-          v[4 * j4 + 1] = __float_as_uint(fmaxf(__uint_as_float(v[4 * j4 + 1]) + b.y, 0.f) + __uint_as_float(r[4 * j4 + 1]));
-          v[4 * j4 + 2] = __float_as_uint(fmaxf(__uint_as_float(v[4 * j4 + 2]) + b.z, 0.f) + __uint_as_float(r[4 * j4 + 2]));
-          v[4 * j4 + 3] = __float_as_uint(fmaxf(__uint_as_float(v[4 * j4 + 3]) + b.w, 0.f) + __uint_as_float(r[4 * j4 + 3]));
-        }
-        tmem_st32(t_res + 32 * c, v);
-        pack32(v, c);
-      }
-      publish(B_Y1);
-      // the next step's rows stream in while GEMM 1 runs
-      fetch(t + n_clusters);
-      // ---- E. y2 = relu(acc + bl1) + y1; score = y2 . wd + bd ----
-      ptx::mbar_wait(bar(B_ACC1), it & 1);
-      ptx::tc_fence_after();
-      float dot0 = 0.f, dot1 = 0.f;
-#pragma unroll 1
-      for (int c = 0; c < 8; ++c) {
-        uint32_t v[16], r[16];
-        ptx::tmem_ld16(t_acc + 16 * c, v);
-        ptx::tmem_ld16(t_res + 16 * c, r);
-        ptx::tmem_ld_wait();
-        const float4* b4 = reinterpret_cast<const float4*>(s_bl1 + col0 + 16 * c);
-        const float4* w4 = reinterpret_cast<const float4*>(s_wd + col0 + 16 * c);
-#pragma unroll
-        for (int j4 = 0; j4 < 4; ++j4) {
           const float4 b = b4[j4], w = w4[j4];
-          dot0 = fmaf(fmaxf(__uint_as_float(v[4 * j4 + 0]) + b.x, 0.f) + __uint_as_float(r[4 * j4 + 0]), w.x, dot0);
-          dot1 = fmaf(fmaxf(__uint_as_float(v[4 * j4 + 1]) + b.y, 0.f) + __uint_as_float(r[4 * j4 + 1]), w.y, dot1);
-          dot0 = fmaf(fmaxf(__uint_as_float(v[4 * j4 + 2]) + b.z, 0.f) + __uint_as_float(r[4 * j4 + 2]), w.z, dot0);
-          dot1 = fmaf(fmaxf(__uint_as_float(v[4 * j4 + 3]) + b.w, 0.f) + __uint_as_float(r[4 * j4 + 3]), w.w, dot1);
+          const float y0 = fmaxf(__uint_as_float(v[4 * j4 + 0]) + b.x, 0.f) + __uint_as_float(r[4 * j4 + 0]);
+          const float y1 = fmaxf(__uint_as_float(v[4 * j4 + 1]) + b.y, 0.f) + __uint_as_float(r[4 * j4 + 1]);
+          const float y2 = fmaxf(__uint_as_float(v[4 * j4 + 2]) + b.z, 0.f) + __uint_as_float(r[4 * j4 + 2]);
+          const float y3 = fmaxf(__uint_as_float(v[4 * j4 + 3]) + b.w, 0.f) + __uint_as_float(r[4 * j4 + 3]);
+          dot0 = fmaf(y0, w.x, dot0); dot1 = fmaf(y1, w.y, dot1); dot0 = fmaf(y2, w.z, dot0); dot1 = fmaf(y3, w.w, dot1);
+          v[4 * j4 + 0] = __float_as_uint(y0); v[4 * j4 + 1] = __float_as_uint(y1);
+          v[4 * j4 + 2] = __float_as_uint(y2); v[4 * j4 + 3] = __float_as_uint(y3);
         }
+        pack32(v, 4 * h + cg);
+        publish(h == 0 ? B_IN0 : B_IN1);
+      }
+      // the next step's rows stream into the (now free) residual columns behind GEMM 1
+      load_half(t + n_clusters, 0);
+      commit_half(0);
+      load_half(t + n_clusters, 1);
+      // ---- layer 1: wd . relu(acc + bl1) ----
+#pragma unroll 1
+      for (int h = 0; h < 2; ++h) {
+        const int col = 128 * h + 32 * cg;
+        if (h == 0) { ptx::mbar_wait(bar(B_ACC0), acc_use0 & 1); ++acc_use0; }
+        else        { ptx::mbar_wait(bar(B_ACC1), acc_use1 & 1); ++acc_use1; }
+        ptx::tc_fence_after();
+        uint32_t v[32];
+        ptx::tmem_ld32(t_acc + col, v);
+        ptx::tmem_ld_wait();
+        const float4* b4 = reinterpret_cast<const float4*>(s_bl1 + col);
+        const float4* w4 = reinterpret_cast<const float4*>(s_wd + col);
+#pragma unroll
+        for (int j4 = 0; j4 < 8; ++j4) {
+          const float4 b = b4[j4], w = w4[j4];
+          dot0 = fmaf(fmaxf(__uint_as_float(v[4 * j4 + 0]) + b.x, 0.f), w.x, dot0);
+          dot1 = fmaf(fmaxf(__uint_as_float(v[4 * j4 + 1]) + b.y, 0.f), w.y, dot1);
+          dot0 = fmaf(fmaxf(__uint_as_float(v[4 * j4 + 2]) + b.z, 0.f), w.z, dot0);
+          dot1 = fmaf(fmaxf(__uint_as_float(v[4 * j4 + 3]) + b.w, 0.f), w.w, dot1);
+        }
+        if (h == 0) commit_half(1);
+      }
+      // every MMA of this step has completed: the operand is free, the next y0 is already in the residual columns
+      tmem_st_wait();
+      ptx::tc_fence_before();
+      if (t + n_clusters < p.T) {
+        pack_half(0);
+        pack_half(1);
       }
       const float dot = dot0 + dot1;
-      if (ch == 1) s_dot[row] = dot;
-      ptx::tc_fence_before();
+      if (cg) s_dot[(cg - 1) * TILE + row] = dot;
       ptx::bar_sync(1, WORKERS);
       const int64_t prog = (int64_t)t * PAIR + rank * TILE + row;
-      if (ch == 0 && prog < p.P) {
-        float s = dot + s_dot[row] + bd;
+      if (cg == 0 && prog < p.P) {
+        float s = ((dot + s_dot[row]) + (s_dot[TILE + row] + s_dot[2 * TILE + row])) + bd;
         if (p.sigmoid) s = 1.f / (1.f + expf(-s));
         if (p.valid && !p.valid[prog]) s = -INFINITY;
         p.scores[prog] = s;
@@ -253,26 +287,44 @@ head_tc_kernel(const HeadParams p) {
     }
   } else if (rank == 0) {
     // ===== MMA issuer (leader CTA) =====
-    const uint32_t idesc = ptx::umma_idesc_f16(256, 256);
-    const uint64_t dWl0 = ptx::umma_desc_sw128(sbase + WL0_OFF), dWl1 = ptx::umma_desc_sw128(sbase + WL1_OFF);
+    const uint32_t idesc = ptx::umma_idesc_f16(256, 128);
     const uint64_t dA = ptx::umma_desc_sw128(sbase + A_OFF);
     auto kadv = [](int k) -> uint64_t { return (uint64_t)(((k >> 2) * ATOM + (k & 3) * 32) >> 4); };
-    int it = 0;
-    for (int t = cluster; t < p.T; t += n_clusters, ++it) {
-      ptx::mbar_wait(bar(B_Y0), it & 1);
-      ptx::tc_fence_after();
-      if (ptx::elect_one()) {
+    uint32_t in_use0 = 0, in_use1 = 0;
+    // piece (n-half nh, k-half kh) of the GEMM with weights at w_off
+    auto piece = [&](uint32_t w_off, int nh, int kh) {
+      const uint64_t dW = ptx::umma_desc_sw128(sbase + w_off + nh * 64 * 128);
 #pragma unroll
-        for (int k = 0; k < 16; ++k) ptx::umma_f16_2cta(tmem + 256, dA + kadv(k), dWl0 + kadv(k), idesc, k > 0);
-        ptx::umma_commit_2cta(bar(B_ACC0), 3);
+      for (int i = 0; i < 8; ++i) {
+        const int k = 8 * kh + i;
+        ptx::umma_f16_2cta(tmem + 256 + 128 * nh, dA + kadv(k), dW + kadv(k), idesc, k > 0);
+      }
+    };
+    auto wait_in = [&](int h) {
+      if (h == 0) { ptx::mbar_wait(bar(B_IN0), in_use0 & 1); ++in_use0; }
+      else        { ptx::mbar_wait(bar(B_IN1), in_use1 & 1); ++in_use1; }
+      ptx::tc_fence_after();
+    };
+    for (int t = cluster; t < p.T; t += n_clusters) {
+      // GEMM 0: both accumulator halves are free once the operand is there
+      wait_in(0);
+      if (ptx::elect_one()) { piece(WL0_OFF, 0, 0); piece(WL0_OFF, 1, 0); }
+      __syncwarp();
+      wait_in(1);
+      if (ptx::elect_one()) {
+        piece(WL0_OFF, 0, 1); ptx::umma_commit_2cta(bar(B_ACC0), 3);
+        piece(WL0_OFF, 1, 1); ptx::umma_commit_2cta(bar(B_ACC1), 3);
       }
       __syncwarp();
-      ptx::mbar_wait(bar(B_Y1), it & 1);
-      ptx::tc_fence_after();
+      // GEMM 1: accumulator half h is free when the layer-0 epilogue of half h has published
+      wait_in(0);
+      if (ptx::elect_one()) piece(WL1_OFF, 0, 0);
+      __syncwarp();
+      wait_in(1);
       if (ptx::elect_one()) {
-#pragma unroll
-        for (int k = 0; k < 16; ++k) ptx::umma_f16_2cta(tmem + 256, dA + kadv(k), dWl1 + kadv(k), idesc, k > 0);
-        ptx::umma_commit_2cta(bar(B_ACC1), 3);
+        piece(WL1_OFF, 1, 0);
+        piece(WL1_OFF, 0, 1); ptx::umma_commit_2cta(bar(B_ACC0), 3);
+        piece(WL1_OFF, 1, 1); ptx::umma_commit_2cta(bar(B_ACC1), 3);
       }
       __syncwarp();
     }
@@ -299,7 +351,8 @@ int head_tc_pack(vaex_model* m, cudaStream_t st) {
     for (int r = 0; r < 2; ++r)
       for (int row = 0; row < TILE; ++row)
         for (int k = 0; k < HID; ++k)
-          img[l][(size_t)r * (W_BYTES / 2) + sw128_off(row, k) / 2] = hh_clamp(w[(size_t)(r * TILE + row) * HID + k]);
+          // each GEMM is issued as two 128-column MMAs: image rows [64 h, +64) of rank r = units 128 h + 64 r + [0, 64)
+          img[l][(size_t)r * (W_BYTES / 2) + sw128_off(row, k) / 2] = hh_clamp(w[(size_t)(128 * (row >> 6) + 64 * r + (row & 63)) * HID + k]);
   }
   TcPack& t = m->tc;
   if (!t.wl0) VAEX_CUDA(cudaMalloc(&t.wl0, 2 * W_BYTES));
