@@ -117,13 +117,18 @@ chain_tc_kernel(const ChainParams p) {
       const int64_t r = (int64_t)t * PAIR + rank * TILE + row;
       const bool ok = t < p.T && r < p.n;
       const float* src = p.X + (ok ? r : 0) * p.in_dim;
-      if (ok && (p.in_dim & 3) == 0 && ((reinterpret_cast<uintptr_t>(p.X) & 15) == 0)) {
+      if (ok && (p.in_dim & 7) == 0 && ((reinterpret_cast<uintptr_t>(p.X) & 31) == 0)) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const int c = 16 * cg + 4 * j;
-          float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (c < p.in_dim) a = ptx::ldg_stream_f4(src + c);
-          xin[4 * j] = a.x; xin[4 * j + 1] = a.y; xin[4 * j + 2] = a.z; xin[4 * j + 3] = a.w;
+        for (int j = 0; j < 2; ++j) {                // full 32 B sectors per lane
+          const int c = 16 * cg + 8 * j;
+          if (c < p.in_dim) {
+            const ptx::F8 f = ptx::ldg_stream_f8(src + c);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) xin[8 * j + e] = f.v[e];
+          } else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) xin[8 * j + e] = 0.f;
+          }
         }
       } else {
 #pragma unroll
@@ -151,6 +156,7 @@ chain_tc_kernel(const ChainParams p) {
     const bool vec_ok = (p.out_dim & 3) == 0 &&
         ((reinterpret_cast<uintptr_t>(p.out) | reinterpret_cast<uintptr_t>(p.extents) | reinterpret_cast<uintptr_t>(p.snap_mean) |
           reinterpret_cast<uintptr_t>(p.snap_scale)) & 15) == 0;
+    const bool vec8_ok = (p.out_dim & 7) == 0 && ((reinterpret_cast<uintptr_t>(p.out) | reinterpret_cast<uintptr_t>(p.extents)) & 31) == 0;
     uint32_t acc_use0 = 0, acc_use1 = 0, lc = 0;
     fetch(cluster);
     if (cluster < p.T) {
@@ -232,7 +238,30 @@ chain_tc_kernel(const ChainParams p) {
             publish(B_IN0);
           }
           ptx::tmem_ld_wait();
-          if (r < p.n && c0 < p.N[l]) {
+          if (r < p.n && c0 < p.N[l] && vec8_ok) {
+            // two 256-bit stores per output: full sectors for the lane-per-row pattern
+            float y[16];
+#pragma unroll
+            for (int m = 0; m < 4; ++m) {
+              const float4 bm = b[m];
+              y[4 * m] = __uint_as_float(v[4 * m]) + bm.x; y[4 * m + 1] = __uint_as_float(v[4 * m + 1]) + bm.y;
+              y[4 * m + 2] = __uint_as_float(v[4 * m + 2]) + bm.z; y[4 * m + 3] = __uint_as_float(v[4 * m + 3]) + bm.w;
+            }
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+              const int c = c0 + 8 * j;
+              if (c < p.out_dim) {
+                if (p.out) ptx::stg_f8(p.out + r * p.out_dim + c, y[8 * j], y[8 * j + 1], y[8 * j + 2], y[8 * j + 3], y[8 * j + 4],
+                                       y[8 * j + 5], y[8 * j + 6], y[8 * j + 7]);
+                if (p.extents) {
+                  int q[8];
+#pragma unroll
+                  for (int e = 0; e < 8; ++e) q[e] = snap_one(y[8 * j + e], __ldg(p.snap_mean + c + e), __ldg(p.snap_scale + c + e), p.snap_mode);
+                  ptx::stg_i8(p.extents + r * p.out_dim + c, q[0], q[1], q[2], q[3], q[4], q[5], q[6], q[7]);
+                }
+              }
+            }
+          } else if (r < p.n && c0 < p.N[l]) {
 #pragma unroll
             for (int m = 0; m < 4; ++m) {
               const int c = c0 + 4 * m;

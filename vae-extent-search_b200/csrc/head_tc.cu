@@ -74,15 +74,6 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&v)[32
 }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
-struct F8 { float v[8]; };
-__device__ __forceinline__ F8 ldg_stream_f8(const float* p) {   // one full 32 B sector per lane
-  F8 r;
-  asm volatile("ld.global.nc.L1::no_allocate.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-               : "=f"(r.v[0]), "=f"(r.v[1]), "=f"(r.v[2]), "=f"(r.v[3]), "=f"(r.v[4]), "=f"(r.v[5]), "=f"(r.v[6]), "=f"(r.v[7])
-               : "l"(p));
-  return r;
-}
-
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(hd::THREADS, 1)
 head_tc_kernel(const HeadParams p) {
   using namespace hd;
@@ -144,7 +135,7 @@ head_tc_kernel(const HeadParams p) {
         const float* src = p.S + prog * HID + 128 * h + 32 * cg;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          const F8 f = ldg_stream_f8(src + 8 * j);
+          const ptx::F8 f = ptx::ldg_stream_f8(src + 8 * j);
           x[2 * j] = make_float4(f.v[0], f.v[1], f.v[2], f.v[3]);
           x[2 * j + 1] = make_float4(f.v[4], f.v[5], f.v[6], f.v[7]);
         }
