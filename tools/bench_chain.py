@@ -28,6 +28,7 @@ def main():
     vae = vaex_b200.VAE_feature_head(48, None, 64, 256).cuda().eval()
     reg = vaex_b200.VAECostPredictor(48, hidden_dim=256, latent_dim=64).cuda().eval()
     z = torch.randn(n, 64, device="cuda")
+    xin = torch.randn(n, 48, device="cuda")
     mean = np.random.default_rng(0).uniform(0.5, 3, 48).astype(np.float32)
     std = np.random.default_rng(1).uniform(0.3, 1.5, 48).astype(np.float32)
     md, sd = torch.from_numpy(mean).cuda(), torch.from_numpy(std).cuda()
@@ -36,6 +37,8 @@ def main():
         vae.set_tensor_cores(tc), reg.set_tensor_cores(tc)
         tag = "tc" if tc else "simt"
         iters = 20 if tc else 3
+        out["encode_mean_ms_" + tag] = timed(lambda: vae.encode(xin, use_mean=True), iters)
+        out["encode_ms_" + tag] = timed(lambda: vae.encode(xin), iters)
         out["decode_ms_" + tag] = timed(lambda: vae.decode(z), iters)
         out["decode_snap_ms_" + tag] = timed(lambda: vae.decode_and_snap(z, md, sd, want_x=False), iters)
         out["predict_cost_ms_" + tag] = timed(lambda: reg.predict_cost(z), iters)

@@ -130,6 +130,17 @@ static ChainLayer chain_layer(vaex_model* m, const std::string& pre) {
   return ChainLayer{&w.v, &m->host[pre + ".bias"].v, w.rows, w.cols};
 }
 
+// x -> 256 -> 256 -> 256 -> mu (and the same trunk -> logvar): the trunk plus one 64-wide latent head is exactly
+// the decoder's shape (156 KB of weights per CTA beside the 64 KB operand); both heads at once would not fit, so
+// logvar, when asked for, is a second pass of the same kernel.
+static int pack_encoder_chains(vaex_model* m, cudaStream_t st) {
+  TRY(chain_tc_pack(m->enc_mu_chain, {chain_layer(m, "encoder.0"), chain_layer(m, "encoder.2"), chain_layer(m, "encoder.4"),
+                                      chain_layer(m, "fc_mu")}, 0, st));
+  TRY(chain_tc_pack(m->enc_lv_chain, {chain_layer(m, "encoder.0"), chain_layer(m, "encoder.2"), chain_layer(m, "encoder.4"),
+                                      chain_layer(m, "fc_logvar")}, 0, st));
+  return VAEX_OK;
+}
+
 static int pack_model(vaex_model* m, const float* norm, cudaStream_t st) {
   switch (m->kind) {
     case VAEX_KIND_SEGSUM_MLP: return pack_segsum_mlp(m, norm, st);
@@ -141,6 +152,7 @@ static int pack_model(vaex_model* m, const float* norm, cudaStream_t st) {
       TRY(pack_linear(m, "decoder.6", m->D, m->H, st));
       TRY(chain_tc_pack(m->dec_chain, {chain_layer(m, "decoder.0"), chain_layer(m, "decoder.2"), chain_layer(m, "decoder.4"),
                                        chain_layer(m, "decoder.6")}, 0, st));
+      TRY(pack_encoder_chains(m, st));
       return VAEX_OK;
     }
     case VAEX_KIND_COST_PREDICTOR: {
@@ -155,6 +167,7 @@ static int pack_model(vaex_model* m, const float* norm, cudaStream_t st) {
       TRY(upload(m, "cost_predictor.0.weight_t", t0.data(), t0.size(), st));
       TRY(chain_tc_pack(m->pred_chain, {chain_layer(m, "cost_predictor.0"), chain_layer(m, "cost_predictor.3"),
                                         chain_layer(m, "cost_predictor.6")}, 1, st));
+      TRY(pack_encoder_chains(m, st));
       return VAEX_OK;
     }
     case VAEX_KIND_SEGMENT_VAE: {
@@ -266,6 +279,10 @@ int vaex_model_destroy(vaex_model_t h) {
   if (h->tc.wl0) cudaFree(h->tc.wl0);
   if (h->tc.wl1) cudaFree(h->tc.wl1);
   for (auto& sl : h->slots) { if (sl.feats) cudaFree(sl.feats); if (sl.off) cudaFree(sl.off); if (sl.scores) cudaFree(sl.scores); }
+  for (ChainPack* cp : {&h->dec_chain, &h->pred_chain, &h->enc_mu_chain, &h->enc_lv_chain}) {
+    if (cp->w) cudaFree(cp->w);
+    if (cp->bias) cudaFree(cp->bias);
+  }
   for (auto& pn : h->pinned) if (pn.p) cudaFreeHost(pn.p);
   for (auto& s : h->copy_streams) if (s) cudaStreamDestroy(s);
   for (auto& e : h->events) if (e) cudaEventDestroy(e);

@@ -60,6 +60,8 @@ struct ChainParams {
   int32_t T, in_dim, out_dim, mode, snap_mode, n_mma;
   int32_t K[ch::MAX_LAYERS], N[ch::MAX_LAYERS], w_off[ch::MAX_LAYERS], b_off[ch::MAX_LAYERS];
   int32_t w_bytes, a_off, bias_off, bias_count, wd_off, bar_off;
+  int32_t ones_col;          // >= 0: input columns ones_col, ones_col + 1 are the constant 1 that carries layer 0's bias (hi, lo) in W0
+  float b_scale[ch::MAX_LAYERS];   // 1: add the stored bias; 0: the bias rides in the MMA
 };
 
 __global__ void smem_base_probe_kernel(uint32_t* out) {
@@ -137,6 +139,11 @@ chain_tc_kernel(const ChainParams p) {
           xin[j] = (ok && c < p.in_dim) ? __ldg(src + c) : 0.f;
         }
       }
+      if (p.ones_col >= 0) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+          if ((unsigned)(16 * cg + j - p.ones_col) < 2u) xin[j] = 1.f;
+      }
     };
     // z: 16 fp32 -> 32 B of atom 3 (the layer-0 A operand)
     auto pack_z = [&]() {
@@ -181,6 +188,7 @@ chain_tc_kernel(const ChainParams p) {
           for (int nh = 0; nh < 2; ++nh) {
             const int col = 128 * nh + 32 * cg;
             const float4* b = reinterpret_cast<const float4*>(s_bias + p.b_off[l] + col);
+            const float bs = p.b_scale[l];             // fmaf(1, b, acc) == acc + b bit for bit; 0 skips a folded bias
             if (nh == 0) { ptx::mbar_wait(bar(B_ACC0), acc_use0 & 1); ++acc_use0; }
             else         { ptx::mbar_wait(bar(B_ACC1), acc_use1 & 1); ++acc_use1; }
             ptx::tc_fence_after();
@@ -194,10 +202,10 @@ chain_tc_kernel(const ChainParams p) {
               for (int m = 0; m < 4; ++m) {
                 const float4 b0 = b[2 * m], b1 = b[2 * m + 1];
                 ptx::sts_v4(base + ((((cc & 1) * 4 + m) ^ sw) << 4),
-                            ptx::cvt_h2_relu_sat(__uint_as_float(v[8 * m]) + b0.x, __uint_as_float(v[8 * m + 1]) + b0.y),
-                            ptx::cvt_h2_relu_sat(__uint_as_float(v[8 * m + 2]) + b0.z, __uint_as_float(v[8 * m + 3]) + b0.w),
-                            ptx::cvt_h2_relu_sat(__uint_as_float(v[8 * m + 4]) + b1.x, __uint_as_float(v[8 * m + 5]) + b1.y),
-                            ptx::cvt_h2_relu_sat(__uint_as_float(v[8 * m + 6]) + b1.z, __uint_as_float(v[8 * m + 7]) + b1.w));
+                            ptx::cvt_h2_relu_sat(fmaf(bs, b0.x, __uint_as_float(v[8 * m])), fmaf(bs, b0.y, __uint_as_float(v[8 * m + 1]))),
+                            ptx::cvt_h2_relu_sat(fmaf(bs, b0.z, __uint_as_float(v[8 * m + 2])), fmaf(bs, b0.w, __uint_as_float(v[8 * m + 3]))),
+                            ptx::cvt_h2_relu_sat(fmaf(bs, b1.x, __uint_as_float(v[8 * m + 4])), fmaf(bs, b1.y, __uint_as_float(v[8 * m + 5]))),
+                            ptx::cvt_h2_relu_sat(fmaf(bs, b1.z, __uint_as_float(v[8 * m + 6])), fmaf(bs, b1.w, __uint_as_float(v[8 * m + 7]))));
               }
               publish(nh == 0 ? B_IN0 : B_IN1);
             } else {
@@ -352,6 +360,22 @@ int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode
   static_assert(sizeof(ChainParams) <= sizeof(cp.params_storage), "ChainPack::params_storage too small");
   P.mode = mode;
   P.n_mma = n_mma;
+  // When the fp32 biases do not fit beside the weights and the operand (the encoder: 160 KB + 64 KB + 3.3 KB), layer 0's
+  // bias rides in its GEMM instead: two spare input columns hold the constant 1 and W0 gets fp16 hi / lo parts of b0.
+  auto smem_need = [&](bool fold0) {
+    int w = 0, b = 0;
+    for (int l = 0; l < n_mma; ++l) {
+      const bool out_layer = mode == MODE_VECTOR && l == n_mma - 1;
+      const int N = out_layer ? std::max(16, (layers[l].out + 15) / 16 * 16) : HID;
+      w += (N / 2) * (l == 0 ? K0 : HID) * 2;
+      if (!(fold0 && l == 0)) b += N;
+    }
+    if (mode == MODE_DOT) b += HID + 4;
+    return w + 4 * ATOM + b * 4 + 64 + (mode == MODE_DOT ? 3 * TILE * 4 : 0);
+  };
+  const bool fold0 = smem_need(false) > SMEM_MAX && n_mma > 1 && layers[0].in + 2 <= K0 && layers[0].out == HID &&
+                     smem_need(true) <= SMEM_MAX;
+  P.ones_col = fold0 ? layers[0].in : -1;
   int woff = 0, boff = 0;
   for (int l = 0; l < n_mma; ++l) {
     const ChainLayer& L = layers[l];
@@ -360,8 +384,9 @@ int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode
     const int N = out_layer ? std::max(16, (L.out + 15) / 16 * 16) : HID;
     if ((l == 0 ? L.in > K0 : L.in != HID) || (out_layer ? L.out > 64 : L.out != HID)) return VAEX_OK;   // shape outside this kernel
     P.K[l] = K; P.N[l] = N; P.w_off[l] = woff; P.b_off[l] = boff;
+    P.b_scale[l] = (fold0 && l == 0) ? 0.f : 1.f;
     woff += (N / 2) * K * 2;
-    boff += N;
+    if (!(fold0 && l == 0)) boff += N;
   }
   P.in_dim = layers[0].in;
   P.out_dim = mode == MODE_VECTOR ? layers[n_mma - 1].out : 1;
@@ -401,8 +426,14 @@ int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode
         if (unit >= L.out) continue;
         __half* dst = img.data() + (size_t)r * (woff / 2) + P.w_off[l] / 2;
         for (int k = 0; k < L.in; ++k) dst[sw_off(nh, u, k) / 2] = c_clamp((*L.w)[(size_t)unit * L.in + k]);
+        if (fold0 && l == 0) {
+          const __half hi = c_clamp((*L.b)[unit]);
+          dst[sw_off(nh, u, L.in) / 2] = hi;
+          dst[sw_off(nh, u, L.in + 1) / 2] = c_clamp((*L.b)[unit] - __half2float(hi));
+        }
       }
-    for (int j = 0; j < L.out; ++j) bias[P.b_off[l] + j] = (*L.b)[j];
+    if (!(fold0 && l == 0))
+      for (int j = 0; j < L.out; ++j) bias[P.b_off[l] + j] = (*L.b)[j];
   }
   if (mode == MODE_DOT) {
     for (int k = 0; k < HID; ++k) bias[P.wd_off + k] = (*layers[n_mma].w)[k];

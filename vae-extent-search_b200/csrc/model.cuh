@@ -54,7 +54,7 @@ struct vaex_model {
   std::map<std::string, vaex::HostTensor> host;
   std::map<std::string, float*> dev;   // packed fp32 device tensors, by name
   vaex::TcPack tc;
-  vaex::ChainPack dec_chain, pred_chain;   // extent-VAE decoder / cost predictor on tensor cores
+  vaex::ChainPack dec_chain, pred_chain, enc_mu_chain, enc_lv_chain;   // extent-VAE decoder / cost predictor / encoder on tensor cores
   int use_tensor = 1;                      // VAEX_OPT_TENSOR_CORES
   vaex::DevBuf ws[6];                  // activations / staging
   vaex::DevBuf topk_ws;
