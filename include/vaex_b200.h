@@ -232,6 +232,35 @@ int vaex_adam_step(float* params_dev, const float* grads_dev, float* m_dev, floa
 int vaex_sgd_step(float* params_dev, const float* grads_dev, int64_t n, float lr, float weight_decay,
                   float grad_scale, void* stream);
 
+/* ---- training of the extent-family VAECostPredictor (train_regression, vae_extent_search.py:1413-1440; losses
+ *      utils/training.py:133-226) ---------------------------------------------------------------------------- */
+/* pair_loss_fn (training.py:144-166): mean over i < j of max(0, -sign(t_j - t_i) (p_j - p_i) + margin); n <= 4096 */
+int vaex_pair_loss(const float* pred_dev, const float* target_dev, int64_t n, float margin, float* loss_dev,
+                   float* dpred_dev_or_null, void* stream);
+/* kld_loss_fn (training.py:181-186): -0.5 mean(1 + logvar - mu^2 - exp(logvar)) over `count` elements */
+int vaex_kld_loss(const float* mu_dev, const float* logvar_dev, int64_t count, float* loss_dev, float* dmu_dev_or_null,
+                  float* dlogvar_dev_or_null, void* stream);
+typedef struct vaex_reg_trainer* vaex_reg_trainer_t;
+/* flat fp32 parameter buffer in state_dict order of VAECostPredictor(input D, hidden H, latent L, predictor_hidden PH,
+ * predictor_layers 2) (utils/model.py:108-131); "@encoder_group" / "@predictor_group" name the two AdamW groups */
+int vaex_reg_trainer_create(int32_t D, int32_t H, int32_t L, int32_t PH, vaex_reg_trainer_t* out);
+int vaex_reg_trainer_destroy(vaex_reg_trainer_t t);
+int64_t vaex_reg_trainer_param_count(vaex_reg_trainer_t t);
+int vaex_reg_trainer_param_offset(vaex_reg_trainer_t t, const char* name, int64_t* offset, int64_t* count);
+/* One step's forward(use_mean=True) + compute_total_loss + backward.  x_dev [n, D], labels_dev [n], n <= 4096;
+ * drop_mask_dev uint8 [n, PH] (1 = keep) makes the main forward train-mode (NULL = eval); noise_dev [n, L] is
+ * noise_std * randn of smooth_loss_fn (NULL = 0); cfg_host[6] = {lambda_reg, lambda_pair, margin, gamma, beta, p_drop};
+ * losses_dev[5] = {total, reg, pair, smooth, kld}; grads_dev is overwritten; cost_dev_or_null [n] = cost_pred. */
+int vaex_reg_trainer_forward_backward(vaex_reg_trainer_t t, const float* params_dev, float* grads_dev, const float* x_dev,
+                                      const float* labels_dev, int64_t n, const uint8_t* drop_mask_dev_or_null,
+                                      const float* noise_dev_or_null, const float* cfg_host, float* losses_dev,
+                                      float* cost_dev_or_null, void* stream);
+/* torch.optim.AdamW on the group params[off, off + cnt); the clip coefficient uses the norm of the whole gradient
+ * buffer (clip_grad_norm_ over all parameters), recomputed into gnorm_dev when compute_norm != 0 */
+int vaex_adamw_step(float* params_dev, const float* grads_dev, float* m_dev, float* v_dev, int64_t n_total, int64_t off,
+                    int64_t cnt, int64_t step, float lr, float beta1, float beta2, float eps, float weight_decay,
+                    float clip_norm, float grad_scale, float* gnorm_dev_or_null, int compute_norm, void* stream);
+
 /* ---- top-k (util_select_topk, utils/select.py:54-81) -------------------------------------- */
 /* k largest of scores[n] restricted to mask (uint8, 1 = eligible; NULL = all), ordered by
  * (score desc, index asc).  out_vals fp32[k], out_idx int64[k]; *n_out_dev (int32) = number

@@ -250,6 +250,71 @@ def gen_train(ns):
     np.savez_compressed(os.path.join(OUT, "train.npz"), **out)
 
 
+def gen_reg_train(ns):
+    """a15: the reference's pair / kld / total loss (utils/training.py) and three train_regression steps
+    (vae_extent_search.py:1389-1440: AdamW two groups, clip 1.0) on a small seeded VAECostPredictor.
+    nn.Dropout is replaced on the instance by a fixed-mask twin (same h * mask / (1 - p) in train mode) and the
+    smooth-loss noise is reproduced by seeding right before compute_total_loss, so both are recorded."""
+    from oracle.ref_import import load_reference_training
+    T = load_reference_training()
+    D, H, L, PH, n, p = 48, 64, 16, 64, 96, 0.1
+    torch.manual_seed(31)
+    reg = ns.vae_model.VAECostPredictor(D, hidden_dim=H, latent_dim=L, predictor_hidden=PH, predictor_layers=2, dropout=p)
+
+    class FixedDrop(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.mask = None
+
+        def forward(self, h):
+            return h * self.mask / (1.0 - p) if self.training else h
+
+    drop = FixedDrop()
+    reg.cost_predictor[2] = drop
+    out = {k: v.copy() for k, v in sd_np(reg, "init.").items()}      # copies: the optimizer updates the tensors in place
+    g = torch.Generator().manual_seed(32)
+    cfg = {"lambda_reg": 0.5, "lambda_pair": 6.0, "margin": 0.3, "gamma": 2.0, "beta": 0.01, "noise_std": 0.5, "loss_type": "mse"}
+    out["cfg"] = np.array([cfg["lambda_reg"], cfg["lambda_pair"], cfg["margin"], cfg["gamma"], cfg["beta"], p], np.float32)
+    # stand-alone losses
+    pred, target = torch.randn(257, generator=g), torch.rand(257, generator=g)
+    target[5] = target[9]                                        # an equal-target pair (label 0 -> contributes the margin)
+    pr = pred.clone().requires_grad_(True)
+    lp = T.pair_loss_fn(pr, target, margin=0.3)
+    lp.backward()
+    mu, lv = torch.randn(40, 16, generator=g).requires_grad_(True), (0.3 * torch.randn(40, 16, generator=g)).requires_grad_(True)
+    lk = T.kld_loss_fn(mu, lv)
+    lk.backward()
+    out.update({"pair_pred": pred.numpy(), "pair_target": target.numpy(), "pair_loss": lp.detach().numpy(), "pair_grad": pr.grad.numpy(),
+                "kld_mu": mu.detach().numpy(), "kld_lv": lv.detach().numpy(), "kld_loss": lk.detach().numpy(),
+                "kld_dmu": mu.grad.numpy(), "kld_dlv": lv.grad.numpy()})
+    # three training steps
+    opt = torch.optim.AdamW([{"params": reg.get_encoder_params(), "lr": 3e-4},
+                             {"params": reg.get_cost_predictor_params(), "lr": 1e-3}], weight_decay=1e-5)
+    xs, ys, masks, noises, losses, norms = [], [], [], [], [], []
+    for step in range(3):
+        x, y = torch.randn(n, D, generator=g), 4.0 * torch.rand(n, generator=g)
+        drop.mask = (torch.rand(n, PH, generator=g) > p).float()
+        reg.train()
+        cost_pred, mean, logvar, z = reg(x, use_mean=True)
+        torch.manual_seed(100 + step)
+        noise = cfg["noise_std"] * torch.randn(n, L)
+        torch.manual_seed(100 + step)
+        total, comp = T.compute_total_loss(reg, cost_pred, mean, logvar, z, y, None, cfg)
+        opt.zero_grad()
+        total.backward()
+        if step == 0:
+            out.update({"grad0." + k: v.grad.detach().numpy().copy() for k, v in reg.named_parameters()})
+            out["cost0"] = cost_pred.detach().numpy()
+        norms.append(float(torch.nn.utils.clip_grad_norm_(reg.parameters(), max_norm=1.0)))
+        opt.step()
+        losses.append([float(total), comp["reg_loss"], comp["pair_loss"], comp["smooth_loss"], comp["kld_loss"]])
+        xs.append(x.numpy()); ys.append(y.numpy()); masks.append(drop.mask.numpy().astype(np.uint8)); noises.append(noise.numpy())
+    out.update({"x": np.stack(xs), "y": np.stack(ys), "mask": np.stack(masks), "noise": np.stack(noises),
+                "losses": np.array(losses, np.float64), "norms": np.array(norms, np.float64)})
+    out.update({"final." + k: v.detach().numpy() for k, v in reg.state_dict().items()})
+    np.savez_compressed(os.path.join(OUT, "reg_train.npz"), **out)
+
+
 def gen_kcenter(ns):
     """n2: select_topk_latent_diversity (select.py:185-270) on seeded latents, and select_programs with a
     diversity budget.  The candidate order the reference iterates (list(set)) is stored with the result."""
@@ -317,6 +382,7 @@ def main():
     gen_train(ns)
     gen_feature_blob(ns)
     gen_kcenter(ns)
+    gen_reg_train(ns)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

@@ -126,3 +126,18 @@ def load_reference_feature():
     mod = _load("tvm.auto_scheduler._ref_feature", "python/tvm/auto_scheduler/feature.py")
     _CACHE["feature"] = mod
     return mod
+
+
+def load_reference_training():
+    """The reference's utils/training.py (losses + compute_total_loss, :133-226) with `utils.model` / `utils.common`
+    bound to the already loaded reference modules."""
+    if "training" in _CACHE:
+        return _CACHE["training"]
+    ns = load_reference()
+    utils = _stub("utils")
+    sys.modules["utils.model"] = ns.vae_model
+    sys.modules["utils.common"] = ns.common
+    utils.model, utils.common = ns.vae_model, ns.common
+    mod = _load("_vaex_ref_utils_training", "scripts/pre_experiments/model_myself/utils/training.py")
+    _CACHE["training"] = mod
+    return mod

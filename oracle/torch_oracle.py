@@ -387,3 +387,74 @@ def kcenter_select(z, cand, used, k, eps=1e-12):
         min_d[j] = -float("inf")
         min_d = torch.minimum(min_d, torch.cdist(zc, zc[j:j + 1], p=2).squeeze(1))
     return np.array(sel, dtype=np.int64)
+
+
+# --------------------------------------------------------------------------------------
+# a15  regression losses and training step of the extent-family VAECostPredictor
+#      (utils/training.py:133-226; train_regression, vae_extent_search.py:1413-1440)
+# --------------------------------------------------------------------------------------
+REG_PARAM_ORDER = ["encoder.0.weight", "encoder.0.bias", "encoder.2.weight", "encoder.2.bias", "encoder.4.weight",
+                   "encoder.4.bias", "fc_mu.weight", "fc_mu.bias", "fc_logvar.weight", "fc_logvar.bias",
+                   "cost_predictor.0.weight", "cost_predictor.0.bias", "cost_predictor.3.weight", "cost_predictor.3.bias",
+                   "cost_predictor.6.weight", "cost_predictor.6.bias"]
+REG_ENCODER_KEYS = REG_PARAM_ORDER[:10]
+
+
+def pair_loss(pred, target, margin=0.1):
+    """pair_loss_fn, training.py:144-166: margin ranking over all pairs i < j."""
+    pred, target = _t(pred).view(-1), _t(target).view(-1)
+    n = pred.shape[0]
+    if n < 2:
+        return torch.tensor(0.0)
+    i, j = torch.triu_indices(n, n, offset=1)
+    y = torch.sign(target[j] - target[i])
+    return torch.clamp(-y * (pred[j] - pred[i]) + margin, min=0).mean()
+
+
+def kld_loss(mu, logvar):
+    """kld_loss_fn, training.py:181-186."""
+    mu, logvar = _t(mu), _t(logvar)
+    return -0.5 * torch.mean(1 + logvar - mu.pow(2) - logvar.exp())
+
+
+def reg_total_loss(P, x, labels, cfg, drop_mask=None, noise=None, p_drop=0.1):
+    """forward(x, use_mean=True) + compute_total_loss (training.py:200-226).  drop_mask [n, PH] = the Bernoulli
+    keep mask of the train-mode forward (None: eval); noise [n, L] = noise_std * randn of smooth_loss_fn, whose
+    two predictor passes run in eval mode and whose noisy input is detached.
+    -> (total, {reg, pair, smooth, kld}, cost_pred)"""
+    mu, logvar = vae_encode(P, x)
+    cost = predict_cost(P, mu, drop_mask, p_drop)
+    y = _t(labels).view(-1)
+    reg = torch.mean((cost - y) ** 2)
+    pair = pair_loss(cost, y, cfg.get("margin", 0.1))
+    z_noisy = (mu + (_t(noise) if noise is not None else 0.0)).detach()
+    smooth = torch.mean((predict_cost(P, mu) - predict_cost(P, z_noisy)) ** 2)
+    kld = kld_loss(mu, logvar)
+    total = cfg["lambda_reg"] * reg + cfg["lambda_pair"] * pair + cfg["gamma"] * smooth + cfg["beta"] * kld
+    return total, {"reg": reg, "pair": pair, "smooth": smooth, "kld": kld}, cost
+
+
+def reg_train_steps(P0, batches, cfg, encoder_lr, predictor_lr, weight_decay=1e-5, clip=1.0, p_drop=0.1, encoder_freeze=False):
+    """batches: list of (x, labels, drop_mask or None, noise or None).  zero_grad / backward / clip_grad_norm_(1.0) /
+    AdamW with the encoder and predictor groups (vae_extent_search.py:1395-1398, :1435-1438).
+    -> (final params, [[total, reg, pair, smooth, kld] per step], [pre-clip grad norm per step], first-step grads)"""
+    P = {k: _t(P0[k]).clone().requires_grad_(True) for k in REG_PARAM_ORDER}
+    enc = [P[k] for k in REG_ENCODER_KEYS]
+    pred = [P[k] for k in REG_PARAM_ORDER[10:]]
+    if encoder_freeze:          # vae_extent_search.py:1386-1391: requires_grad = False, predictor group only
+        for t in enc:
+            t.requires_grad_(False)
+        opt = torch.optim.AdamW([{"params": pred, "lr": predictor_lr}], weight_decay=weight_decay)
+    else:
+        opt = torch.optim.AdamW([{"params": enc, "lr": encoder_lr}, {"params": pred, "lr": predictor_lr}], weight_decay=weight_decay)
+    losses, norms, first = [], [], None
+    for x, labels, mask, noise in batches:
+        opt.zero_grad()
+        total, comp, _ = reg_total_loss(P, x, labels, cfg, mask, noise, p_drop)
+        total.backward()
+        if first is None:
+            first = {k: P[k].grad.detach().clone() for k in REG_PARAM_ORDER if P[k].grad is not None}
+        norms.append(float(torch.nn.utils.clip_grad_norm_(pred if encoder_freeze else enc + pred, clip)))
+        opt.step()
+        losses.append([float(total)] + [float(comp[k]) for k in ("reg", "pair", "smooth", "kld")])
+    return {k: v.detach() for k, v in P.items()}, losses, norms, first
