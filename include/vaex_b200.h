@@ -255,6 +255,19 @@ int vaex_reg_trainer_forward_backward(vaex_reg_trainer_t t, const float* params_
                                       const float* labels_dev, int64_t n, const uint8_t* drop_mask_dev_or_null,
                                       const float* noise_dev_or_null, const float* cfg_host, float* losses_dev,
                                       float* cost_dev_or_null, void* stream);
+/* VAE pre-training (vae_train's inner loop + vae_feature_loss, utils/training.py:14-32,70-88): flat parameter buffer in
+ * state_dict order of VAE_feature_head(input D, latent L, hidden H) without the feature head (utils/model.py:16-50). */
+typedef struct vaex_vae_trainer* vaex_vae_trainer_t;
+int vaex_vae_trainer_create(int32_t D, int32_t H, int32_t L, vaex_vae_trainer_t* out);
+int vaex_vae_trainer_destroy(vaex_vae_trainer_t t);
+int64_t vaex_vae_trainer_param_count(vaex_vae_trainer_t t);
+int vaex_vae_trainer_param_offset(vaex_vae_trainer_t t, const char* name, int64_t* offset, int64_t* count);
+/* forward(x, use_mean = (eps_dev == NULL)) + alpha_recon * mse(x_recon, x) + beta * kl + backward; eps_dev [n, L] is the
+ * randn of reparameterize (utils/model.py:58-61); losses_dev[3] = {total, recon, kl}; n <= 4096.  The optimizer is
+ * vaex_adam_step (torch.optim.Adam, no clipping, :65). */
+int vaex_vae_trainer_forward_backward(vaex_vae_trainer_t t, const float* params_dev, float* grads_dev, const float* x_dev,
+                                      int64_t n, const float* eps_dev_or_null, float alpha_recon, float beta,
+                                      float* losses_dev, void* stream);
 /* torch.optim.AdamW on the group params[off, off + cnt); the clip coefficient uses the norm of the whole gradient
  * buffer (clip_grad_norm_ over all parameters), recomputed into gnorm_dev when compute_norm != 0 */
 int vaex_adamw_step(float* params_dev, const float* grads_dev, float* m_dev, float* v_dev, int64_t n_total, int64_t off,

@@ -315,6 +315,38 @@ def gen_reg_train(ns):
     np.savez_compressed(os.path.join(OUT, "reg_train.npz"), **out)
 
 
+def gen_vae_train(ns):
+    """a15: three vae_train steps (utils/training.py:65-88: forward(use_mean=False), vae_feature_loss, Adam) of the
+    reference's VAE_feature_head; the reparameterisation noise is reproduced by seeding right before the forward."""
+    from oracle.ref_import import load_reference_training
+    T = load_reference_training()
+    D, H, L, n = 48, 64, 16, 80
+    torch.manual_seed(41)
+    vae = ns.vae_model.VAE_feature_head(input_dim=D, latent_dim=L, hidden_dim=H)
+    out = {k: v.copy() for k, v in sd_np(vae, "init.").items()}
+    opt = torch.optim.Adam(vae.parameters(), lr=1e-3)
+    g = torch.Generator().manual_seed(42)
+    xs, epss, losses = [], [], []
+    for step in range(3):
+        x = torch.randn(n, D, generator=g)
+        torch.manual_seed(200 + step)
+        eps = torch.randn(n, L)
+        torch.manual_seed(200 + step)
+        vae.train()
+        x_recon, mu, logvar, z, fp = vae(x, use_mean=False)
+        loss, recon, kl, _ = T.vae_feature_loss(x_recon, x, mu, logvar, fp, None, alpha_recon=1.0, alpha_feature=0.0, beta=0.01)
+        opt.zero_grad()
+        loss.backward()
+        if step == 0:
+            out.update({"grad0." + k: v.grad.detach().numpy().copy() for k, v in vae.named_parameters()})
+        opt.step()
+        losses.append([float(loss), float(recon), float(kl)])
+        xs.append(x.numpy()); epss.append(eps.numpy())
+    out.update({"x": np.stack(xs), "eps": np.stack(epss), "losses": np.array(losses, np.float64)})
+    out.update({"final." + k: v.detach().numpy() for k, v in vae.state_dict().items()})
+    np.savez_compressed(os.path.join(OUT, "vae_train.npz"), **out)
+
+
 def gen_kcenter(ns):
     """n2: select_topk_latent_diversity (select.py:185-270) on seeded latents, and select_programs with a
     diversity budget.  The candidate order the reference iterates (list(set)) is stored with the result."""
@@ -383,6 +415,7 @@ def main():
     gen_feature_blob(ns)
     gen_kcenter(ns)
     gen_reg_train(ns)
+    gen_vae_train(ns)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

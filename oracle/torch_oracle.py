@@ -458,3 +458,36 @@ def reg_train_steps(P0, batches, cfg, encoder_lr, predictor_lr, weight_decay=1e-
         opt.step()
         losses.append([float(total)] + [float(comp[k]) for k in ("reg", "pair", "smooth", "kld")])
     return {k: v.detach() for k, v in P.items()}, losses, norms, first
+
+
+VAE_PARAM_ORDER = ["encoder.0.weight", "encoder.0.bias", "encoder.2.weight", "encoder.2.bias", "encoder.4.weight", "encoder.4.bias",
+                   "fc_mu.weight", "fc_mu.bias", "fc_logvar.weight", "fc_logvar.bias", "decoder.0.weight", "decoder.0.bias",
+                   "decoder.2.weight", "decoder.2.bias", "decoder.4.weight", "decoder.4.bias", "decoder.6.weight", "decoder.6.bias"]
+
+
+def vae_loss(P, x, eps, alpha_recon=1.0, beta=0.01):
+    """forward(x, use_mean=False) with the given reparameterisation noise + vae_feature_loss (training.py:14-32,
+    no feature head) -> (total, recon, kl)."""
+    mu, logvar = vae_encode(P, x)
+    z = mu if eps is None else mu + _t(eps) * torch.exp(0.5 * logvar)
+    recon = torch.mean((vae_decode(P, z) - _t(x)) ** 2)
+    kl = kld_loss(mu, logvar)
+    return alpha_recon * recon + beta * kl, recon, kl
+
+
+def vae_train_steps(P0, batches, alpha_recon=1.0, beta=0.01, lr=1e-3):
+    """batches: list of (x, eps).  zero_grad / backward / Adam.step (training.py:65,84-88).
+    -> (final params, [[total, recon, kl] per step], first-step grads)"""
+    P = {k: _t(P0[k]).clone().requires_grad_(True) for k in VAE_PARAM_ORDER}
+    params = [P[k] for k in VAE_PARAM_ORDER]
+    opt = torch.optim.Adam(params, lr=lr)
+    losses, first = [], None
+    for x, eps in batches:
+        opt.zero_grad()
+        total, recon, kl = vae_loss(P, x, eps, alpha_recon, beta)
+        total.backward()
+        if first is None:
+            first = {k: P[k].grad.detach().clone() for k in VAE_PARAM_ORDER}
+        opt.step()
+        losses.append([float(total), float(recon), float(kl)])
+    return {k: v.detach() for k, v in P.items()}, losses, first

@@ -134,3 +134,42 @@ def test_train_regression_learns():
     pred = model(torch.from_numpy(x[1024:]).cuda(), use_mean=True)[0].cpu().numpy()
     rho = spearmanr(pred, y[1024:]).statistic
     assert rho > 0.9, rho
+
+
+def test_vae_pretraining_vs_reference():
+    """vae_train's step (forward(use_mean=False) + vae_feature_loss + Adam) against the reference's VAE_feature_head,
+    vae_feature_loss and torch.optim.Adam (tests/golden/vae_train.npz): first-step gradients, three losses, parameters."""
+    g = load_golden("vae_train.npz")
+    vae = vaex_b200.VAE_feature_head(48, None, 16, 64)
+    vae.load_state_dict(split_sd(g, "init."))
+    tr = training.VAETrainer(vae.cuda(), lr=1e-3, alpha_recon=1.0, beta=0.01)
+    tr.forward_backward(torch.from_numpy(g["x"][0]).cuda(), torch.from_numpy(g["eps"][0]).cuda())
+    np.testing.assert_allclose(tr.losses.cpu().numpy(), g["losses"][0], rtol=5e-5)
+    gmax = max(np.abs(g["grad0." + k]).max() for k in O.VAE_PARAM_ORDER)
+    for k in O.VAE_PARAM_ORDER:
+        o, c = tr.slices[k]
+        got, want = tr.grads[o:o + c].cpu().numpy().reshape(g["grad0." + k].shape), g["grad0." + k]
+        assert np.abs(got - want).max() <= 2e-4 * np.abs(want).max() + 2e-6 * gmax, k
+    losses = []
+    for i in range(3):
+        losses.append(tr.step(torch.from_numpy(g["x"][i]).cuda(), torch.from_numpy(g["eps"][i]).cuda()).cpu().numpy().copy())
+    np.testing.assert_allclose(np.array(losses), g["losses"], rtol=2e-4)
+    net = tr.export_params()
+    for k in O.VAE_PARAM_ORDER:
+        du, dw = net.state_dict()[k].cpu().numpy() - g["init." + k], g["final." + k] - g["init." + k]
+        assert np.abs(du - dw).max() < 0.75e-3, k
+        bad = int(np.sum(np.abs(du - dw) > 0.02 * np.abs(dw) + 2e-6))
+        assert bad <= max(2, 0.03 * du.size), (k, bad)
+    # use_mean path (eps = None) against the oracle, and the values-only loss mirror
+    tr.import_params()
+    tr.forward_backward(torch.from_numpy(g["x"][1]).cuda(), None)
+    P = {k: v.detach().cpu() for k, v in net.state_dict().items()}
+    wt, wr, wk = O.vae_loss(P, g["x"][1], None)
+    np.testing.assert_allclose(tr.losses.cpu().numpy(), [float(wt), float(wr), float(wk)], rtol=1e-4)
+    net = net.eval()
+    net.set_tensor_cores(False)
+    x = torch.from_numpy(g["x"][1]).cuda()
+    xr, mu, lv, z, fp = net(x, use_mean=True)
+    _, lv = net.encode(x)
+    loss, recon, kl, _ = training.vae_feature_loss(xr, x, mu, lv, None, None, alpha_recon=1.0, beta=0.01)
+    np.testing.assert_allclose([loss.item(), recon.item(), kl.item()], [float(wt), float(wr), float(wk)], rtol=1e-4)

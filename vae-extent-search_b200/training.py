@@ -196,3 +196,71 @@ def train_regression(vae_cost_model, trainer, train_loader, config, warmup_epoch
             cfg['lambda_pair'] = lambda_pair_warmup(epoch, warmup_epochs, lambda_pair_max) if warmup_epochs else lambda_pair_max
             trainer.step(x_batch.to(trainer.device), labels.to(trainer.device).squeeze(-1), cfg)
     return trainer.export_params()
+
+
+def vae_feature_loss(x_recon, x, mu, logvar, feature_pred=None, feature=None, alpha_recon=0, alpha_feature=0, beta=1.0):
+    """training.py:14-32, values only (no feature head on the hot path) -> (loss, recon_loss, kl, feature_loss)."""
+    xr, xx = _f(x_recon).reshape(-1), _f(x).reshape(-1)
+    recon = ((xr - xx) ** 2).mean()
+    kl = kld_loss_fn(mu, logvar)
+    return alpha_recon * recon + beta * kl, recon, kl, 0.0
+
+
+class VAETrainer:
+    """optimizer = torch.optim.Adam(vae.parameters(), lr) + the inner loop of vae_train (training.py:65,70-88):
+    forward(x, use_mean=False) -> vae_feature_loss -> backward -> Adam.step, as two CUDA calls."""
+
+    def __init__(self, vae, lr=1e-3, alpha_recon=1.0, beta=0.01, device="cuda:0", group=None):
+        if getattr(vae, "use_feature", False):
+            raise NotImplementedError("feature_predictor head (alpha_feature experiments) is outside the hot path")
+        self.lib, self.model, self.group = _lib.load(), vae, group
+        self.device = torch.device(device)
+        D, H, L = vae._dims()
+        self.L, self.lr, self.alpha_recon, self.beta = L, float(lr), float(alpha_recon), float(beta)
+        self.h = _lib.vp()
+        _lib.check(self.lib.vaex_vae_trainer_create(D, H, L, ctypes.byref(self.h)))
+        self.n = int(self.lib.vaex_vae_trainer_param_count(self.h))
+        self.slices = {}
+        for name in vae.state_dict():
+            o, c = _lib.i64(), _lib.i64()
+            _lib.check(self.lib.vaex_vae_trainer_param_offset(self.h, name.encode(), ctypes.byref(o), ctypes.byref(c)))
+            self.slices[name] = (o.value, c.value)
+        z = lambda: torch.zeros(self.n, device=self.device)   # noqa: E731
+        self.params, self.grads, self.m, self.v = z(), z(), z(), z()
+        self.losses = torch.zeros(3, device=self.device)
+        self.t = 0
+        self.import_params()
+
+    import_params = RegressionTrainer.import_params
+    export_params = RegressionTrainer.export_params
+
+    def forward_backward(self, x, eps=None):
+        """eps [n, L]: the randn of reparameterize; None = use_mean.  Fills self.grads and self.losses = [total, recon, kl]."""
+        x = _f(x)
+        e = None if eps is None else _f(eps)
+        _lib.check(self.lib.vaex_vae_trainer_forward_backward(self.h, _lib.ptr(self.params), _lib.ptr(self.grads), _lib.ptr(x),
+                                                              x.shape[0], _lib.ptr(e), self.alpha_recon, self.beta,
+                                                              _lib.ptr(self.losses), _lib.stream_ptr()))
+        return self.losses
+
+    def step(self, x, eps="auto"):
+        x = _f(x)
+        if isinstance(eps, str):
+            eps = torch.randn(x.shape[0], self.L, device=x.device)
+        self.forward_backward(x, eps)
+        scale = shard.reduce_gradients(self.grads, self.group)
+        self.t += 1
+        _lib.check(self.lib.vaex_adam_step(_lib.ptr(self.params), _lib.ptr(self.grads), _lib.ptr(self.m), _lib.ptr(self.v), self.n,
+                                           self.t, self.lr, 0.9, 0.999, 1e-8, 0.0, 0.0, scale, None, _lib.stream_ptr()))
+        return self.losses
+
+    def close(self):
+        if self.h:
+            self.lib.vaex_vae_trainer_destroy(self.h)
+            self.h = _lib.vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
