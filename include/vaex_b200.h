@@ -158,6 +158,14 @@ int vaex_snap_extents(const float* x_dev, int64_t n, int32_t d, const float* mea
                       const float* scale_dev, int mode, const int32_t* slot_extent_dev,
                       const uint8_t* slot_last_dev, int32_t max_innermost, int32_t* extents_dev,
                       void* stream);
+/* Divisor legalisation on its own, in place on int32 extents [n, d] (GetFactors / tile legality,
+ * src/auto_scheduler/search_policy/utils.cc:433-463; SplitStep lengths must multiply to a divisor of the
+ * step's extent, transform_step.cc:1015-1023).  slot_order_dev_or_null int32[n_order]: the order in which
+ * the slots are walked, so that the lengths of one SplitStep are consecutive even though the printed loop
+ * nest interleaves them (NULL = slot order 0..d-1); slots not listed are left as they are. */
+int vaex_legalise_extents(int32_t* extents_dev, int64_t n, int32_t d, const int32_t* slot_extent_dev,
+                          const uint8_t* slot_last_dev, const int32_t* slot_order_dev_or_null, int32_t n_order,
+                          int32_t max_innermost, void* stream);
 /* decode + snap in one call (the scoring path of BASELINE configs 3/5): z [n, L] -> continuous extents
  * x_dev_or_null fp32 [n, D] and integer extents_dev_or_null int32 [n, D]; with tensor cores enabled the
  * snap runs in the decoder kernel's epilogue (x never touches HBM unless asked for).  Arguments as in
@@ -273,6 +281,29 @@ int vaex_vae_trainer_forward_backward(vaex_vae_trainer_t t, const float* params_
 int vaex_adamw_step(float* params_dev, const float* grads_dev, float* m_dev, float* v_dev, int64_t n_total, int64_t off,
                     int64_t cnt, int64_t step, float lr, float beta1, float beta2, float eps, float weight_decay,
                     float clip_norm, float grad_scale, float* gnorm_dev_or_null, int compute_norm, void* stream);
+
+/* ---- extent parser + scaler ------------------------------------------------------ */
+/* state_to_records' numeric part (scripts/pre_experiments/model_myself/utils/extent.py:94-136, inlined again at
+ * vae_extent_search.py:165-176): text_host holds n printed Ansor states back to back, state i =
+ * bytes [str_offsets_host[i], str_offsets_host[i+1]).  Per state: schedule = strip(state) after its last
+ * "Placeholder" + 2 characters; every match of \(0,\s*(\d+)\) is an extent, every match of auto_unroll:\s*(\d+) an
+ * unroll value (one 0.0 when there is none); the row is extents followed by unrolls.  Host only, all host threads.
+ * scan: counts_host int32 [n, 2] = (#extents, #unrolls incl. the default). */
+int vaex_extent_text_scan(const char* text_host, const int64_t* str_offsets_host, int64_t n, int32_t* counts_host);
+/* parse: out_host fp32 [n, d] (rows zero-padded to d; a pinned buffer makes the H2D copy asynchronous),
+ * row_len_host_or_null int32[n] = values found per state.  VAEX_E_INVALID if a state holds more than d values
+ * (its first d are still written). */
+int vaex_extent_text_parse(const char* text_host, const int64_t* str_offsets_host, int64_t n, int32_t d,
+                           float* out_host, int32_t* row_len_host_or_null);
+/* np.log1p + sklearn StandardScaler.fit (vae_extent_search.py:394-397; sklearn's _incremental_mean_and_var and
+ * _handle_zeros_in_scale rules) on raw extents raw_dev fp32 [n, d], d <= 256: mean_dev, var_dev, scale_dev fp64 [d].
+ * Deterministic (block partials reduced in a fixed order).  scratch_dev: at least 2*d*592 doubles. */
+int vaex_scaler_fit(const float* raw_dev, int64_t n, int32_t d, double* mean_dev, double* var_dev, double* scale_dev,
+                    double* scratch_dev, int64_t scratch_doubles, void* stream);
+/* StandardScaler.transform(np.log1p(raw)) with sklearn's rounding (statistics cast to fp32, one fp32 subtract,
+ * one fp32 divide): out_dev fp32 [n, d].  The inverse is vaex_snap_extents(VAEX_SNAP_EXPM1). */
+int vaex_scaler_transform(const float* raw_dev, int64_t n, int32_t d, const double* mean_dev, const double* scale_dev,
+                          float* out_dev, void* stream);
 
 /* ---- top-k (util_select_topk, utils/select.py:54-81) -------------------------------------- */
 /* k largest of scores[n] restricted to mask (uint8, 1 = eligible; NULL = all), ordered by

@@ -403,6 +403,111 @@ def gen_feature_blob(ns):
     np.savez_compressed(os.path.join(OUT, "feature_blob.npz"), **out)
 
 
+README_STATE = """Placeholder: placeholder, placeholder, placeholder
+parallel ax0.0@ax1.0@ax2.0@ (0,4)
+  for i1 (0,57)
+    for i2 ((floormod(ax0.outer.outer.ax1.outer.outer.fused.ax2.outer.outer.fused, 4)*14),15)
+      for i3 (0,64)
+        PaddedInput = ...
+  for ax3.0 (0,2)
+    for ax2.1 (0,7)
+      for ax3.1 (0,8)
+        Conv2dOutput auto_unroll: 16
+        for rx.0 (0,3)
+          for rc.0 (0,4)
+            for ry.1 (0,3)
+              for rc.1 (0,16)
+                for yy.3 (0,28)
+                  vectorize ff.3 (0,8)
+                    Conv2dOutput = ...
+        for ax1.2 (0,28)
+          vectorize ax3.2 (0,8)
+            T_relu = ...
+"""   # the printed program of the reference README (:86-108), dedented
+
+
+def synth_states(rng, n, ragged):
+    """Printed Ansor states in PrintState's format (src/auto_scheduler/loop_state.cc:354-440): one conv-like sketch
+    with random tile extents; `ragged` adds the odd cases (no / several auto_unroll lines, trivial loops, non-zero
+    minimums, undefined ranges, blanks after the comma, very long digit strings, leading / trailing blanks)."""
+    ann = ["for", "parallel", "vectorize", "unroll", "blockIdx.x", "threadIdx.x", "vthread"]
+    div = [1, 2, 3, 4, 7, 8, 14, 16, 28, 32, 56, 57, 64, 128, 512]
+    out = []
+    for i in range(n):
+        lines = ["Placeholder: data, kernel" if i % 3 else "Placeholder: placeholder, placeholder, placeholder"]
+        ind = 0
+        depth = 14 if not ragged else int(rng.integers(3, 20))
+        for j in range(depth):
+            name = "%s.%d" % ("ijkxyc"[j % 6], j // 6)
+            e = int(rng.choice(div))
+            if ragged:
+                r = rng.random()
+                if r < 0.08:
+                    lines.append(" " * ind + "for %s (%d,%d)" % (name, int(rng.integers(1, 9)), e)); ind += 2; continue
+                if r < 0.12:
+                    lines.append(" " * ind + "for %s (None)" % name); ind += 2; continue
+                if r < 0.18:
+                    lines.append(" " * ind + "for %s (0, %d)" % (name, e)); ind += 2; continue
+                if r < 0.21:
+                    lines.append(" " * ind + "for %s (0,%d)" % (name, int(rng.integers(10 ** 9, 10 ** 18)))); ind += 2; continue
+                if r < 0.24:
+                    lines.append(" " * ind + "for %s (0,\t %d)" % (name, e)); ind += 2; continue
+                if r < 0.27:
+                    lines.append(""); continue
+                if r < 0.30 and ind >= 2:
+                    lines.append(" " * ind + "A.local = ..."); ind -= 2; continue
+            if j in (2, 5) or (ragged and rng.random() < 0.1):
+                e = 1                                             # trivial loops: j = 2, 5 are common to all states
+            lines.append(" " * ind + "%s %s (0,%d)" % (ann[int(rng.integers(0, len(ann)))] if j not in (2, 5) else "for", name, e))
+            ind += 2
+            if j == 8 and (not ragged or rng.random() < 0.6):
+                lines.append(" " * ind + "conv auto_unroll: %d" % int(rng.choice([16, 64, 512, 1024])))
+            if ragged and rng.random() < 0.05:
+                lines.append(" " * ind + "pad auto_unroll:  %d" % int(rng.choice([0, 16, 64])))
+        lines.append(" " * ind + "conv = ...")
+        txt = "\n".join(lines) + "\n"
+        if ragged and rng.random() < 0.3:
+            txt = "  \n" + txt + " \t"
+        out.append(txt)
+    return out
+
+
+def _pack_text(strs):
+    enc = [s.encode() for s in strs]
+    return (np.frombuffer(b"".join(enc), dtype=np.uint8).copy(),
+            np.concatenate([[0], np.cumsum([len(b) for b in enc])]).astype(np.int64))
+
+
+def gen_extent_text(ns):
+    """the reference's own state_to_records (utils/extent.py:94-136) on synthetic printed states and on the
+    README's program; sklearn StandardScaler (the routine the reference calls, vae_extent_search.py:394-397) on the
+    fixed-sketch pool."""
+    import contextlib
+    import io
+    from sklearn.preprocessing import StandardScaler
+    from oracle.ref_import import load_reference_extent
+    ext = load_reference_extent()
+    rng = np.random.default_rng(2023)
+    out = {}
+    for tag, strs in (("rag", synth_states(rng, 400, True) + [README_STATE, "no placeholder here (0,7) auto_unroll: 3", ""]),
+                      ("pool", synth_states(rng, 3000, False))):
+        with contextlib.redirect_stdout(io.StringIO()):
+            rec = ext.state_to_records(strs)          # list in, so the order is kept (the reference passes a set)
+        out[tag + "_text"], out[tag + "_offsets"] = _pack_text(strs)
+        out[tag + "_len"] = np.array([len(a) for a in rec["all"]], dtype=np.int32)
+        out[tag + "_n_ext"] = np.array([len(a) for a in rec["extents"]], dtype=np.int32)
+        out[tag + "_all"] = np.concatenate(rec["all"]).astype(np.float32)
+        out[tag + "_clean_text"], out[tag + "_clean_offsets"] = _pack_text(rec["cleaned_schedules"])
+    raw = np.array(rec["all"], dtype=np.float32)
+    raw = np.concatenate([raw, np.full((raw.shape[0], 1), 7.0, np.float32)], axis=1)   # + a constant column
+    x = np.log1p(raw)
+    sc = StandardScaler()
+    xs = sc.fit_transform(x)
+    out.update(scaler_raw=raw, scaler_mean=sc.mean_, scaler_var=sc.var_, scaler_scale=sc.scale_, scaler_out=xs.astype(np.float32))
+    out["readme_extents"] = np.array([4, 57, 64, 2, 7, 8, 3, 4, 3, 16, 28, 8, 28, 8, 16], dtype=np.float32)
+    np.savez_compressed(os.path.join(OUT, "extent_text.npz"), **out)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     ns = load_reference()
@@ -416,6 +521,7 @@ def main():
     gen_kcenter(ns)
     gen_reg_train(ns)
     gen_vae_train(ns)
+    gen_extent_text(ns)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

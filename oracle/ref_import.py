@@ -141,3 +141,13 @@ def load_reference_training():
     mod = _load("_vaex_ref_utils_training", "scripts/pre_experiments/model_myself/utils/training.py")
     _CACHE["training"] = mod
     return mod
+
+
+def load_reference_extent():
+    """The reference's utils/extent.py (state_to_records and the schedule clean-up, :8-136) under the stub tvm."""
+    if "extent" in _CACHE:
+        return _CACHE["extent"]
+    load_reference()
+    mod = _load("_vaex_ref_utils_extent", "scripts/pre_experiments/model_myself/utils/extent.py")
+    _CACHE["extent"] = mod
+    return mod

@@ -41,6 +41,11 @@ SIGNATURES = {
     "vaex_segsum_mlp_predict_blob": ([vp, vp, i64, vp, i64, ctypes.c_int], ctypes.c_int),
     "vaex_decode_snap": ([vp, vp, i64, vp, vp, vp, vp, ctypes.c_int, vp, vp, i32, vp], ctypes.c_int),
     "vaex_snap_extents": ([vp, i64, i32, vp, vp, ctypes.c_int, vp, vp, i32, vp, vp], ctypes.c_int),
+    "vaex_legalise_extents": ([vp, i64, i32, vp, vp, vp, i32, i32, vp], ctypes.c_int),
+    "vaex_extent_text_scan": ([vp, vp, i64, vp], ctypes.c_int),
+    "vaex_extent_text_parse": ([vp, vp, i64, i32, vp, vp], ctypes.c_int),
+    "vaex_scaler_fit": ([vp, i64, i32, vp, vp, vp, vp, i64, vp], ctypes.c_int),
+    "vaex_scaler_transform": ([vp, i64, i32, vp, vp, vp, vp], ctypes.c_int),
     "vaex_predict_cost": ([vp, vp, i64, vp, vp, u64, f32, vp], ctypes.c_int),
     "vaex_cost_grad_z": ([vp, vp, i64, vp, vp, vp, vp], ctypes.c_int),
     "vaex_latent_ascent": ([vp, vp, i64, i32, f32, vp, vp], ctypes.c_int),

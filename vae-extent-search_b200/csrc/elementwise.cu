@@ -174,11 +174,16 @@ __global__ void snap_kernel(const float* __restrict__ x, int64_t n, int d, const
 
 __global__ void legalise_kernel(int32_t* __restrict__ ext, int64_t n, int d,
                                 const int32_t* __restrict__ slot_extent,
-                                const uint8_t* __restrict__ slot_last, int max_innermost) {
+                                const uint8_t* __restrict__ slot_last, int max_innermost,
+                                const int32_t* __restrict__ order, int n_order) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   int rem = 0;
-  for (int j = 0; j < d; ++j) {
+  // walk order: the slots as printed (order == nullptr), or the caller's list in which the lengths of one
+  // SplitStep are consecutive (a printed loop nest interleaves the splits of different axes)
+  const int steps = order ? n_order : d;
+  for (int jj = 0; jj < steps; ++jj) {
+    const int j = order ? order[jj] : jj;
     const int se = slot_extent[j];
     if (se <= 0) { rem = 0; continue; }
     if (rem == 0) rem = se;
@@ -191,9 +196,9 @@ __global__ void legalise_kernel(int32_t* __restrict__ ext, int64_t n, int d,
 }
 
 int legalise_extents(int32_t* ext, int64_t n, int d, const int32_t* slot_extent, const uint8_t* slot_last, int max_innermost,
-                     cudaStream_t st) {
+                     cudaStream_t st, const int32_t* order, int n_order) {
   if (n == 0) return VAEX_OK;
-  legalise_kernel<<<(unsigned)cdiv(n, 128), 128, 0, st>>>(ext, n, d, slot_extent, slot_last, max_innermost);
+  legalise_kernel<<<(unsigned)cdiv(n, 128), 128, 0, st>>>(ext, n, d, slot_extent, slot_last, max_innermost, order, n_order);
   VAEX_LAUNCH_CHECK();
   return VAEX_OK;
 }
@@ -206,7 +211,7 @@ int snap_extents(const float* x, int64_t n, int d, const float* mean, const floa
   VAEX_LAUNCH_CHECK();
   if (mode & VAEX_SNAP_DIVISOR) {
     VAEX_CHECK(slot_extent && slot_last, "divisor mode needs slot tables");
-    legalise_kernel<<<(unsigned)cdiv(n, 128), 128, 0, st>>>(out, n, d, slot_extent, slot_last, max_innermost);
+    legalise_kernel<<<(unsigned)cdiv(n, 128), 128, 0, st>>>(out, n, d, slot_extent, slot_last, max_innermost, nullptr, 0);
     VAEX_LAUNCH_CHECK();
   }
   return VAEX_OK;

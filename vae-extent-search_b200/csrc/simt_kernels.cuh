@@ -18,7 +18,7 @@ int snap_extents(const float* x, int64_t n, int d, const float* mean, const floa
                  const int32_t* slot_extent, const uint8_t* slot_last, int max_innermost,
                  int32_t* out, cudaStream_t st);
 int legalise_extents(int32_t* ext, int64_t n, int d, const int32_t* slot_extent, const uint8_t* slot_last, int max_innermost,
-                     cudaStream_t st);
+                     cudaStream_t st, const int32_t* order = nullptr, int n_order = 0);
 int dropout_apply(float* h, int64_t n, int cols, const uint8_t* mask, uint64_t seed, float p,
                   cudaStream_t st);
 int relu_mask_rowvec(const float* h, const float* w, float* out, int64_t n, int cols, cudaStream_t st);
