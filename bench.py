@@ -97,9 +97,33 @@ class ClockSampler(threading.Thread):
         self.index, self.samples, self.reasons, self.stop_flag, self.max_mhz = index, [], set(), False, None
 
     def run(self):
+        """In-process NVML sampling every 5 ms (a query costs microseconds and takes no lock the launches need);
+        spawning nvidia-smi instead took ~100 ms per sample and could land inside a 40 ms timed region."""
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        try:
+            import pynvml as nv
+            import torch
+            nv.nvmlInit()
+            try:
+                uuid = str(torch.cuda.get_device_properties(self.index).uuid)
+                handle = nv.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+            except Exception:
+                handle = nv.nvmlDeviceGetHandleByIndex(self.index)
+            bits = {"hw_slowdown": nv.nvmlClocksThrottleReasonHwSlowdown, "hw_thermal_slowdown": nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+                    "sw_thermal_slowdown": nv.nvmlClocksThrottleReasonSwThermalSlowdown, "sw_power_cap": nv.nvmlClocksThrottleReasonSwPowerCap}
+            self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(handle, nv.NVML_CLOCK_SM))
+            while not self.stop_flag:
+                self.samples.append(float(nv.nvmlDeviceGetClockInfo(handle, nv.NVML_CLOCK_SM)))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(handle)
+                for n, b in bits.items():
+                    if r & b:
+                        self.reasons.add(n)
+                time.sleep(0.005)
+            return
+        except Exception:
+            pass
         q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         while not self.stop_flag:
             try:
                 out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
@@ -275,6 +299,7 @@ def main_vaex(args):
 
         e2e_step()
         barrier()
+        cnt0 = (model.counter(0), model.counter(1))
         t0 = time.perf_counter()
         for _ in range(n_e2e):
             e2e_step()
@@ -287,8 +312,14 @@ def main_vaex(args):
         assert np.array_equal(np.isfinite(out.numpy()), fin) and \
             np.abs(out.numpy()[fin] - sc[:Pe][fin]).max() < 1e-3 * max(1.0, np.abs(sc[:Pe][fin]).max()), \
             "host path disagrees with device path"
-        e2e = {"value": world * Pe / float(tt.item()), "unit": UNIT, "h2d_bytes_per_step": int(re_ * F * 4 + Pe * 4),
-               "d2h_bytes_per_step": int(Pe * 4), "programs_per_gpu": Pe, "steps": n_e2e}
+        # chunks that crossed PCIe narrowed to fp16 by the host cores vs as the caller's fp32 rows (same scores bit for bit)
+        nar, raw = model.counter(0) - cnt0[0], model.counter(1) - cnt0[1]
+        frac16 = nar / max(1, nar + raw)
+        e2e = {"value": world * Pe / float(tt.item()), "unit": UNIT,
+               "h2d_bytes_per_step": int(re_ * F * 4 * (1 - frac16) + re_ * F * 2 * frac16 + Pe * 4),
+               "d2h_bytes_per_step": int(Pe * 4), "programs_per_gpu": Pe, "steps": n_e2e,
+               "host_input_bytes_per_step": int(re_ * F * 4 + Pe * 4),
+               "chunks_fp16_narrowed_on_host": int(nar), "chunks_fp32_raw": int(raw)}
         del host
 
     if rank == 0:

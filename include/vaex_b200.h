@@ -57,7 +57,10 @@ enum {
 /* flags for vaex_segsum_mlp_forward */
 enum {
   VAEX_F_MASK_INVALID = 1, /* all-zero program -> -inf (MLPModel.predict, mlp_model.py:842-844) */
-  VAEX_F_FORCE_SIMT = 2    /* run the fp32 SIMT check kernels instead of the tcgen05 kernel */
+  VAEX_F_FORCE_SIMT = 2,   /* run the fp32 SIMT check kernels instead of the tcgen05 kernel */
+  VAEX_F_FEATS_F16 = 4,    /* feats_dev holds IEEE fp16 (saturated to +-65504) instead of fp32: the tcgen05 row encoder
+                              rounds to fp16 first in any case, so the scores are bit-identical; needs F % 4 == 0 */
+  VAEX_F_NO_HOST_PACK = 8  /* vaex_segsum_mlp_predict_host: copy the fp32 rows as they are (no fp16 narrowing on the host) */
 };
 
 /* snap modes for vaex_snap_extents / vaex_decode_snap */
@@ -119,9 +122,20 @@ int vaex_segsum_encode(vaex_model_t h, const float* feats_dev, const int32_t* se
                        void* stream);
 /* End-to-end host call (what MLPModel.predict costs a reference user, mlp_model.py:832-846):
  * host fp32 features + int32 sizes in, host fp32 scores out; chunked H2D on two streams
- * overlapped with compute.  Synchronous. */
+ * overlapped with compute.  Synchronous.  When the tcgen05 kernel serves the model, F % 4 == 0 and the host has
+ * AVX2 + F16C, the host threads narrow each 128 MiB chunk to fp16 while the previous one crosses PCIe (half the
+ * bytes on the bus; the kernel rounds to fp16 first in any case, so the scores do not change by one bit; a chunk
+ * holding a non-zero value that would round to zero travels as fp32 so that the all-zero-program rule stays exact).
+ * VAEX_F_NO_HOST_PACK switches that off. */
 int vaex_segsum_mlp_predict_host(vaex_model_t h, const float* feats_host, const int32_t* sizes_host,
                                  int64_t n_programs, int64_t n_rows, float* scores_host, int flags);
+/* The narrowing on its own, for callers that keep fp16 rows resident in HBM (VAEX_F_FEATS_F16): out_host[i] =
+ * fp16(clamp(feats_host[i], +-65504)), round to nearest even = cvt.rn.satfinite.f16.f32.  *lossy_zero_or_null = 1 when
+ * some non-zero input became a zero.  Host only (AVX2 + F16C). */
+int vaex_pack_features_f16(const float* feats_host, uint16_t* out_host, int64_t count, int32_t* lossy_zero_or_null);
+/* counters of a handle: which = 0 chunks vaex_segsum_mlp_predict_host sent narrowed to fp16, 1 = sent as fp32
+ * (only calls large enough to start the narrowing threads count) */
+int vaex_model_get_counter(vaex_model_t h, int which, int64_t* value);
 
 /* ---- Ansor's packed per-store feature blob (SerializeFeatures, src/auto_scheduler/feature.cc:1562-1622;
  *      replaces unpack_feature, python/tvm/auto_scheduler/feature.py:49-158).  Host functions. ---- */

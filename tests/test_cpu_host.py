@@ -124,3 +124,27 @@ def test_select_budget_arithmetic_cpu():
         if c + u + d < budget:
             c += budget - (c + u + d)
         assert c + u + d == budget
+
+
+def test_pack_features_f16_is_the_kernels_rounding():
+    """vaex_pack_features_f16 (host, AVX2 + F16C) == clamp to +-65504 then round-to-nearest-even, the function
+    cvt.rn.satfinite.f16.f32 computes in the row encoder: bitwise against numpy's float16 cast."""
+    from vaex_b200.mlp_model import pack_features_f16
+    rng = np.random.default_rng(11)
+    x = np.concatenate([
+        rng.standard_normal(100003).astype(np.float32) * 30,
+        np.float32([0.0, -0.0, 65504, 65519.9, 65520, 1e6, -1e6, np.inf, -np.inf, 6.1e-5, 5.96e-8, 3.1e-8, 1e-7, -2.5e-7]),
+        (rng.standard_normal(5000) * 1e-6).astype(np.float32),                     # fp16 subnormal range
+        np.float32(2048) + np.arange(64, dtype=np.float32),                        # ties
+    ])
+    for shift in (0, 1, 3, 7):                                                    # unaligned heads and tails
+        got, lossy = pack_features_f16(x[shift:])
+        want = np.clip(x[shift:], -65504, 65504).astype(np.float16)
+        assert got.dtype == np.float16 and np.array_equal(got.view(np.uint16), want.view(np.uint16))
+        assert lossy == bool(((x[shift:] != 0) & (want == 0)).any())
+    assert not pack_features_f16(x[:100017])[1] and pack_features_f16(x[100017:])[1]
+    got, lossy = pack_features_f16(np.float32([[1.0, 2.9e-8, 3.0]]))
+    assert lossy and got[0, 1] == 0                                               # 2^-25 = 2.98e-8 and below round to 0
+    got, lossy = pack_features_f16(np.float32([np.nan, 1.0]))
+    assert np.isnan(got[0]) and got[1] == 1.0
+    assert pack_features_f16(np.zeros((0, 164), np.float32))[0].shape == (0, 164)

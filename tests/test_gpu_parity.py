@@ -153,6 +153,50 @@ def test_segsum_mlp_properties_large():
     assert l2_err(h, a[:50000].cpu().numpy()) < 2e-4 and rel_err(h, a[:50000].cpu().numpy()) < TC_RTOL
 
 
+def test_host_narrowing_is_bit_identical():
+    """vaex_segsum_mlp_predict_host narrows chunks to fp16 on the host cores (half the PCIe bytes) or sends them raw,
+    whichever keeps the bus busy; the row encoder rounds to fp16 first either way, so every mix must give the same
+    bits -- including saturation, fp16 subnormals, negative values and the all-zero-program rule."""
+    rng = np.random.default_rng(9)
+    torch.manual_seed(9)
+    net = vaex_b200.SegmentSumMLPModule(164, 256, 1).cuda().eval()
+    n = 70000
+    sizes = rng.integers(1, 33, size=n).astype(np.int32)
+    offs = np.concatenate([[0], np.cumsum(sizes)])
+    feats = (rng.random((int(offs[-1]), 164), dtype=np.float32) * 24).astype(np.float32)
+    feats[rng.random(feats.shape[0]) < 0.01] *= -1.0
+    feats[5, 3], feats[6, 7], feats[9, 1] = 1e6, -3e38, 65519.0              # saturate / round to 65504
+    feats[20:40, 10:20] = 3e-6                                                # fp16 subnormals
+    for p in (0, 17, n - 1):                                                  # all-zero programs (first chunk, last chunk)
+        feats[offs[p]:offs[p + 1]] = 0.0
+    flags = _lib.F_MASK_INVALID
+    m = net.packed(None)
+    before = (m.counter(0), m.counter(1))
+    a = vaex_b200.predict_flat(net, feats, sizes, flags=flags)
+    narrowed, raw = m.counter(0) - before[0], m.counter(1) - before[1]
+    assert narrowed + raw >= 5 and raw >= 1, (narrowed, raw)                  # ~760 MB = 6 chunks; the first goes raw
+    b = vaex_b200.predict_flat(net, feats, sizes, flags=flags | _lib.F_NO_HOST_PACK)
+    assert np.array_equal(a.view(np.uint32), b.view(np.uint32)), "narrowed and raw chunks disagree"
+    assert np.isneginf(a[[0, 17, n - 1]]).all() and np.isfinite(np.delete(a, [0, 17, n - 1])).all()
+    # a value that would round to an fp16 zero keeps its chunk in fp32: the program is NOT all-zero
+    feats[offs[17]] = 0.0
+    feats[offs[17], 0] = 1e-9
+    c = vaex_b200.predict_flat(net, feats, sizes, flags=flags)
+    d = vaex_b200.predict_flat(net, feats, sizes, flags=flags | _lib.F_NO_HOST_PACK)
+    assert np.isfinite(c[17]) and np.array_equal(c.view(np.uint32), d.view(np.uint32))
+    # device entry point with rows that are already fp16 in HBM (VAEX_F_FEATS_F16)
+    sub = feats[: offs[5000]].copy()
+    sub[5, 3], sub[6, 7], sub[9, 1] = 60000.0, -60000.0, 1.0                  # torch's .half() does not saturate
+    from vaex_b200.mlp_model import pack_features_f16
+    half, lossy = pack_features_f16(sub)
+    assert lossy                                                              # the 1e-9 above
+    st = torch.from_numpy(sizes[:5000]).cuda()
+    with torch.no_grad():
+        e = net(st, torch.from_numpy(sub).cuda())
+        f = net(st, torch.from_numpy(half).cuda())
+    assert torch.equal(e, f)
+
+
 def test_segment_sums_tc_vs_simt_stress():
     """The tcgen05 kernel's hand-offs (mbarriers, relaxed cluster arrivals, proxy fences) under
     load: per-program segment sums against the fp32 SIMT kernels element by element, several

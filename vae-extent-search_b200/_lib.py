@@ -9,7 +9,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libvaex_b200.so")
 
 KIND_SEGSUM_MLP, KIND_EXTENT_VAE, KIND_COST_PREDICTOR, KIND_SEGMENT_VAE, KIND_SEGMENT_COST = 1, 2, 3, 4, 5
-F_MASK_INVALID, F_FORCE_SIMT = 1, 2
+F_MASK_INVALID, F_FORCE_SIMT, F_FEATS_F16, F_NO_HOST_PACK = 1, 2, 4, 8
 OPT_TENSOR_CORES = 1
 SNAP_EXP, SNAP_EXPM1, SNAP_DIVISOR = 0, 1, 4
 LOSS_IDS = {"rmse": 0, "rankNetLoss": 1, "lambdaRankLoss": 2, "listNetLoss": 3}
@@ -33,6 +33,8 @@ SIGNATURES = {
     "vaex_segsum_mlp_forward": ([vp, vp, vp, i64, i64, vp, ctypes.c_int, vp], ctypes.c_int),
     "vaex_segsum_encode": ([vp, vp, vp, i64, i64, vp, ctypes.c_int, vp], ctypes.c_int),
     "vaex_segsum_mlp_predict_host": ([vp, vp, vp, i64, i64, vp, ctypes.c_int], ctypes.c_int),
+    "vaex_pack_features_f16": ([vp, vp, i64, vp], ctypes.c_int),
+    "vaex_model_get_counter": ([vp, ctypes.c_int, ctypes.POINTER(i64)], ctypes.c_int),
     "vaex_vae_encode": ([vp, vp, i64, vp, vp, vp], ctypes.c_int),
     "vaex_reparam": ([vp, vp, vp, u64, u64, vp, i64, i32, vp], ctypes.c_int),
     "vaex_vae_decode": ([vp, vp, i64, vp, vp], ctypes.c_int),
@@ -154,6 +156,11 @@ class Model:
 
     def set_option(self, option, value):
         check(self.lib.vaex_model_set_option(self.h, int(option), int(value)))
+
+    def counter(self, which):
+        v = i64(0)
+        check(self.lib.vaex_model_get_counter(self.h, int(which), ctypes.byref(v)))
+        return int(v.value)
 
     def close(self):
         if self.h:

@@ -2,7 +2,10 @@
 #include <algorithm>
 #include <atomic>
 #include <cmath>
+#include <chrono>
 #include <cstring>
+#include <thread>
+#include <vector>
 
 #include "common.cuh"
 #include "model.cuh"
@@ -284,6 +287,7 @@ int vaex_model_destroy(vaex_model_t h) {
     if (cp->bias) cudaFree(cp->bias);
   }
   for (auto& pn : h->pinned) if (pn.p) cudaFreeHost(pn.p);
+  for (auto& pn : h->pack_stage) if (pn.p) cudaFreeHost(pn.p);
   for (auto& s : h->copy_streams) if (s) cudaStreamDestroy(s);
   for (auto& e : h->events) if (e) cudaEventDestroy(e);
   delete h;

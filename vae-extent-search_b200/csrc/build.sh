@@ -13,6 +13,10 @@ for f in abi simt_kernels elementwise topk segsum_tc head_tc chain_tc train feat
     pids+=($!)
   fi
 done
+if [ ! -f build/host_pack.o ] || [ host_pack.cpp -nt build/host_pack.o ]; then
+  ${CXX:-g++} -O3 -std=c++17 -fPIC -mavx2 -mf16c -c host_pack.cpp -o build/host_pack.o &
+  pids+=($!)
+fi
 for p in "${pids[@]}"; do wait $p; done
 $NVCC -shared -gencode arch=compute_100a,code=sm_100a build/*.o -o $OUT -lcuda
 echo "built $(readlink -f $OUT)"

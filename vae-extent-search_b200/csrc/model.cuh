@@ -63,6 +63,10 @@ struct vaex_model {
   HostSlot slots[2];                   // device staging of vaex_segsum_mlp_predict_host / _blob
   struct PinnedSlot { void* p = nullptr; size_t bytes = 0; };
   PinnedSlot pinned[2];                // host staging of vaex_segsum_mlp_predict_blob
+  PinnedSlot pack_stage[4];            // fp16 staging ring of vaex_segsum_mlp_predict_host
+  cudaEvent_t pack_events[4] = {nullptr, nullptr, nullptr, nullptr};   // H2D of ring slot i is over
+  cudaEvent_t h2d_events[2] = {nullptr, nullptr};                      // feature H2D of device slot i is over
+  int64_t pack_stats[2] = {0, 0};      // chunks sent narrowed / raw since the handle was created
   cudaStream_t copy_streams[2] = {nullptr, nullptr};
   cudaEvent_t events[4] = {nullptr, nullptr, nullptr, nullptr};
 
@@ -84,5 +88,8 @@ int chain_tc_run(const ChainPack& cp, const float* X, int64_t n, float* out, int
                  const float* scale, int snap_mode, const float* wd, const float* bd, cudaStream_t st);
 // segsum_tc.cu
 int segsum_tc_encode(vaex_model* m, const float* feats, const int32_t* off, int64_t n_programs,
-                     int64_t n_rows, float* segsum, uint8_t* valid, cudaStream_t st);
+                     int64_t n_rows, float* segsum, uint8_t* valid, cudaStream_t st, bool feats_f16 = false);
+// host_pack.cpp
+bool host_pack_supported();
+bool host_pack_f16(const float* in, uint16_t* out, size_t n);   // true: a non-zero value became zero
 }  // namespace vaex

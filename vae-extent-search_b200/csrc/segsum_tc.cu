@@ -40,6 +40,7 @@
 
 #include "common.cuh"
 #include "model.cuh"
+#include <type_traits>
 #include "tc_ptx.cuh"
 
 namespace vaex {
@@ -75,7 +76,7 @@ __host__ __device__ inline int hidden_of_col(int c) {
 }  // namespace tc
 
 struct TcParams {
-  const float* feats;          // [n_rows, F]
+  const float* feats;          // [n_rows, F] fp32, or fp16 (already saturated) for the HALF_IN instantiation
   const int32_t* off;          // [P + 1]
   const uint4* meta;           // [4T][2] per 64-row sub-block: {endmask lo, hi, partialmask lo, hi}, {first program, flags, -, -}
   const uint2* desc;           // [4T][64] piece list {program, col | len<<8 | partial<<16}; only written for irregular sub-blocks
@@ -201,6 +202,43 @@ struct FastLoader {
   }
 };
 
+// Same walk for features that are already fp16 in HBM (VAEX_F_FEATS_F16: the host path narrows them before the
+// PCIe copy): a unit is 4 halves = one LDG.64, stored as it is; the offset table is the fp32 one (a unit is
+// still 4 features).  Half the bytes per tile, no F2FP.
+struct FastLoaderH {
+  const uint2* src;
+  int valid_units, total;
+  __device__ __forceinline__ void open(const TcParams& p, int64_t grow0, int lane) {
+    constexpr int ROWS = tc::TILE / tc::LOAD_WARPS;
+    total = ROWS * (p.F >> 2);
+    const int64_t vr = min((int64_t)ROWS, p.n_rows - grow0);
+    valid_units = vr > 0 ? (int)vr * (p.F >> 2) : 0;
+    src = reinterpret_cast<const uint2*>(reinterpret_cast<const __half*>(p.feats) + (vr > 0 ? grow0 : 0) * p.F) + lane;
+  }
+  __device__ __forceinline__ void issue(int s0, int lane, uint2 (&x)[FAST_BATCH]) const {
+#pragma unroll
+    for (int j = 0; j < FAST_BATCH; ++j) {
+      const int idx = (s0 + j) * 32 + lane;
+      if (idx < valid_units) x[j] = ptx::ldg_stream_u2(src + (s0 + j) * 32);
+      else x[j] = make_uint2(0u, 0u);
+    }
+  }
+  __device__ __forceinline__ uint32_t commit(int s0, int lane, const uint2 (&x)[FAST_BATCH], uint32_t A0w,
+                                             const uint16_t* tab) const {
+    uint32_t mask = 0;
+#pragma unroll
+    for (int j = 0; j < FAST_BATCH; ++j) {
+      const int idx = (s0 + j) * 32 + lane;
+      if (idx < total) {
+        const uint32_t o = tab[idx];
+        ptx::sts_v2(A0w + o, x[j].x, x[j].y);
+        if ((x[j].x | x[j].y) & 0x7fff7fffu) mask |= 1u << ((o >> 7) & 15);
+      }
+    }
+    return mask;
+  }
+};
+
 // ---------------------------------------------------------------------------------------------
 // epi 1 building block: 16 accumulator columns (static register index).  m: bit j = column j is
 // the last row of a piece, pm: that piece is partial (cut by the sub-block boundary -> atomicAdd).
@@ -270,7 +308,7 @@ __device__ __forceinline__ void sum_irregular(uint32_t tcol, const uint2* __rest
 }
 
 // ---------------------------------------------------------------------------------------------
-template <bool FOLD>
+template <bool FOLD, bool HALF_IN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(tc::THREADS, 1)
 segsum_tc_kernel(const TcParams p) {
   using namespace tc;
@@ -342,13 +380,16 @@ segsum_tc_kernel(const TcParams p) {
     // ===== loaders: fp32 rows -> fp16 swizzled A0; 16 rows per warp =====
     constexpr int ROWS = TILE / LOAD_WARPS;
     const uint32_t A0 = sbase + A0_OFF;
-    const bool al16 = ((reinterpret_cast<uintptr_t>(p.feats) & 15) == 0) && (p.F % 4 == 0);
+    // HALF_IN: the host checked F % 4 == 0 and 16-byte alignment (a warp's 16-row run then starts 16-byte aligned)
+    const bool al16 = HALF_IN || (((reinterpret_cast<uintptr_t>(p.feats) & 15) == 0) && (p.F % 4 == 0));
     const bool al8 = ((reinterpret_cast<uintptr_t>(p.feats) & 7) == 0) && (p.F % 2 == 0);
     auto prefetch = [&](int t) {
       if (!al16 || t >= p.T) return;
       const int64_t r0 = (int64_t)t * PAIR + rank * TILE + warp * ROWS;
       const int64_t nr = min((int64_t)ROWS, p.n_rows - r0);
-      if (nr > 0) ptx::prefetch_l2_bulk(p.feats + r0 * p.F, (uint32_t)(nr * p.F * 4));
+      if (nr <= 0) return;
+      if (HALF_IN) ptx::prefetch_l2_bulk(reinterpret_cast<const __half*>(p.feats) + r0 * p.F, (uint32_t)(nr * p.F * 2) & ~15u);
+      else ptx::prefetch_l2_bulk(p.feats + r0 * p.F, (uint32_t)(nr * p.F * 4));
     };
     auto publish = [&](int t, uint32_t nzmask) {
       // 16 flag bits per warp: two warps share one 32-bit word of the row mask
@@ -359,8 +400,8 @@ segsum_tc_kernel(const TcParams p) {
     };
     if (lane == 0) { prefetch(cluster + n_clusters); prefetch(cluster + 2 * n_clusters); }
     if (al16) {
-      FastLoader ld;
-      float4 x[FAST_BATCH];
+      typename std::conditional<HALF_IN, FastLoaderH, FastLoader>::type ld;
+      typename std::conditional<HALF_IN, uint2, float4>::type x[FAST_BATCH];
       const uint32_t A0w = A0 + 2048u * warp;
       if (cluster < p.T) {
         ld.open(p, (int64_t)cluster * PAIR + rank * TILE + warp * ROWS, lane);
@@ -677,8 +718,10 @@ int tc_pack(vaex_model* m, const std::vector<float>& w0, cudaStream_t st) {
   VAEX_CUDA(cudaMemcpyAsync(t.w1, i1.data(), 2 * W1_BYTES, cudaMemcpyHostToDevice, st));
   VAEX_CUDA(cudaMemcpyAsync(t.b1, m->host["segment_encoder.2.bias"].v.data(), HID * sizeof(float), cudaMemcpyHostToDevice, st));
   VAEX_CUDA(cudaStreamSynchronize(st));
-  VAEX_CUDA(cudaFuncSetAttribute(segsum_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_DYN));
-  VAEX_CUDA(cudaFuncSetAttribute(segsum_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_DYN));
+  VAEX_CUDA(cudaFuncSetAttribute(segsum_tc_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_DYN));
+  VAEX_CUDA(cudaFuncSetAttribute(segsum_tc_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_DYN));
+  VAEX_CUDA(cudaFuncSetAttribute(segsum_tc_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_DYN));
+  VAEX_CUDA(cudaFuncSetAttribute(segsum_tc_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_DYN));
   t.F = F;
   t.K0P = K0P;
   t.ready = true;
@@ -686,7 +729,7 @@ int tc_pack(vaex_model* m, const std::vector<float>& w0, cudaStream_t st) {
 }
 
 int segsum_tc_encode(vaex_model* m, const float* feats, const int32_t* off, int64_t P, int64_t R, float* segsum,
-                     uint8_t* valid, cudaStream_t st) {
+                     uint8_t* valid, cudaStream_t st, bool feats_f16) {
   using namespace tc;
   VAEX_CHECK(m->tc.ready, "tcgen05 weights not packed");
   VAEX_CHECK(P < (1ll << 31) && R < (1ll << 31) - PAIR, "sizes exceed int32 row indexing");
@@ -712,8 +755,13 @@ int segsum_tc_encode(vaex_model* m, const float* feats, const int32_t* off, int6
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int clusters = std::max(1, std::min(sms / 2, T));
-    if (fold) segsum_tc_kernel<true><<<2 * clusters, THREADS, SMEM_DYN, st>>>(prm);
-    else segsum_tc_kernel<false><<<2 * clusters, THREADS, SMEM_DYN, st>>>(prm);
+    if (feats_f16) {
+      VAEX_CHECK(m->F % 4 == 0 && (reinterpret_cast<uintptr_t>(feats) & 15) == 0,
+                 "fp16 features need F % 4 == 0 and a 16-byte aligned pointer");
+      if (fold) segsum_tc_kernel<true, true><<<2 * clusters, THREADS, SMEM_DYN, st>>>(prm);
+      else segsum_tc_kernel<false, true><<<2 * clusters, THREADS, SMEM_DYN, st>>>(prm);
+    } else if (fold) segsum_tc_kernel<true, false><<<2 * clusters, THREADS, SMEM_DYN, st>>>(prm);
+    else segsum_tc_kernel<false, false><<<2 * clusters, THREADS, SMEM_DYN, st>>>(prm);
     VAEX_LAUNCH_CHECK();
   }
   if (valid) {

@@ -18,6 +18,8 @@ import pickle
 
 import time
 
+import ctypes
+
 import numpy as np
 import torch
 
@@ -203,7 +205,10 @@ class SegmentSumMLPModule(torch.nn.Module):
             raise _lib.VaexError("SegmentSumMLPModule.forward needs CUDA tensors (no CPU fallback)")
         lib = _lib.load()
         m = self.packed(fea_norm_vec)
-        feats = features.detach().contiguous().float()
+        if features.dtype == torch.float16:      # rows already narrowed (the tcgen05 kernel rounds to fp16 first anyway)
+            feats, flags = features.detach().contiguous(), flags | _lib.F_FEATS_F16
+        else:
+            feats = features.detach().contiguous().float()
         sizes = segment_sizes.detach().to(device=feats.device, dtype=torch.int32).contiguous()
         n = sizes.shape[0]
         offsets = torch.empty(n + 1, dtype=torch.int32, device=feats.device)
@@ -528,6 +533,17 @@ def predict_flat(model, flat, sizes, fea_norm_vec=None, flags=0, embedding=None)
     _lib.check(lib.vaex_segsum_mlp_predict_host(m.h, flat.ctypes.data, sizes.ctypes.data, len(sizes),
                                                  flat.shape[0], out.ctypes.data, flags))
     return out
+
+
+def pack_features_f16(flat):
+    """Host fp32 rows -> (np.float16 array of the same shape, lossy_zero flag): the rounding the tcgen05 row encoder
+    applies, done ahead of the copy (vaex_pack_features_f16).  Feed the result to SegmentSumMLPModule.forward as a
+    CUDA half tensor."""
+    flat = np.ascontiguousarray(flat, dtype=np.float32)
+    out = np.empty(flat.shape, dtype=np.float16)
+    lossy = ctypes.c_int32(0)
+    _lib.check(_lib.load().vaex_pack_features_f16(flat.ctypes.data, out.ctypes.data, flat.size, ctypes.addressof(lossy)))
+    return out, bool(lossy.value)
 
 
 class MLPModel:
