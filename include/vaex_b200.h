@@ -80,6 +80,7 @@ enum {
 
 typedef struct vaex_model* vaex_model_t;
 typedef struct vaex_trainer* vaex_trainer_t;
+typedef struct vaex_segvae_trainer* vaex_segvae_trainer_t;
 
 const char* vaex_last_error(void);
 int vaex_abi_version(void);
@@ -290,6 +291,26 @@ int vaex_vae_trainer_param_offset(vaex_vae_trainer_t t, const char* name, int64_
 int vaex_vae_trainer_forward_backward(vaex_vae_trainer_t t, const float* params_dev, float* grads_dev, const float* x_dev,
                                       int64_t n, const float* eps_dev_or_null, float alpha_recon, float beta,
                                       float* losses_dev, void* stream);
+/* ---- SegmentVAE training step (segment family; VAE_Trainer.train_vae, scripts/vae_experiments/trainer.py:23-118) ----
+ * Flat fp32 parameter / gradient buffers in SegmentVAE.parameters() order (scripts/vae_experiments/models/vae.py:32-66);
+ * vaex_segvae_trainer_param_offset maps a state_dict key to its slice. */
+int vaex_segvae_trainer_create(int32_t F, int32_t H, int32_t L, vaex_segvae_trainer_t* out);
+int vaex_segvae_trainer_destroy(vaex_segvae_trainer_t t);
+int64_t vaex_segvae_trainer_param_count(vaex_segvae_trainer_t t);
+int vaex_segvae_trainer_param_offset(vaex_segvae_trainer_t t, const char* name, int64_t* offset, int64_t* count);
+/* SegmentVAE.forward in train mode (vae.py:113-137: batch-statistics BatchNorm x3, decoder Dropout, reparameterisation)
+ * + vae_loss (trainer.py:270-280: sum-reduced MSE against the LIVE segment sums + beta * KL sum) + backward.
+ * feats_dev fp32 [n_rows, F], seg_offsets_dev int32 [n_programs + 1], 2 <= n_programs <= 4096.
+ * eps_dev_or_null fp32 [n_programs, L]: the reparameterisation noise (NULL = use_mean: logvar := 0, z = mean).
+ * Dropout: drop_mask_dev_or_null uint8 [n_programs, H] (1 = keep), else drop_seed != 0 (Philox), else none.
+ * bn_running_dev_or_null fp32 [3][2][H]: running_mean / running_var of norm, decoder.1, decoder.5, updated in place
+ * (momentum 0.1, unbiased variance).  losses_dev fp32 [3] = {total, recon, kld}.  mean / recon outputs optional. */
+int vaex_segvae_trainer_forward_backward(vaex_segvae_trainer_t t, const float* params_dev, float* grads_dev,
+                                         const float* feats_dev, const int32_t* seg_offsets_dev, int64_t n_programs,
+                                         int64_t n_rows, const float* eps_dev_or_null, const uint8_t* drop_mask_dev_or_null,
+                                         uint64_t drop_seed, float p_drop, float beta, float* bn_running_dev_or_null,
+                                         float* losses_dev, float* mean_out_dev_or_null, float* recon_out_dev_or_null,
+                                         void* stream);
 /* torch.optim.AdamW on the group params[off, off + cnt); the clip coefficient uses the norm of the whole gradient
  * buffer (clip_grad_norm_ over all parameters), recomputed into gnorm_dev when compute_norm != 0 */
 int vaex_adamw_step(float* params_dev, const float* grads_dev, float* m_dev, float* v_dev, int64_t n_total, int64_t off,

@@ -508,6 +508,69 @@ def gen_extent_text(ns):
     np.savez_compressed(os.path.join(OUT, "extent_text.npz"), **out)
 
 
+def gen_segvae_train(ns):
+    """SURVEY 8a a15, segment family: three training steps of the reference's SegmentVAE (models/vae.py) exactly as
+    VAE_Trainer.train_vae runs them (trainer.py:57-66): train-mode forward, VAE_Trainer.vae_loss, backward,
+    clip_grad_norm_(1.0), AdamW(lr, weight_decay=1e-5).  The reparameterisation noise and the dropout keep-mask of each
+    step are captured from the run so that the CUDA path can replay them."""
+    from oracle.ref_import import load_reference_seg_trainer
+    ref_tr = load_reference_seg_trainer()
+    torch.manual_seed(7)
+    rng = np.random.default_rng(7)
+    F, H, L, P = 164, 256, 64, 40
+    model = ns.seg_vae.SegmentVAE(F, H, L, dropout=0.1)
+    with torch.no_grad():
+        for bn in (model.norm, model.decoder[1], model.decoder[5]):
+            bn.weight.copy_(1 + 0.2 * torch.randn(H))
+            bn.bias.copy_(0.1 * torch.randn(H))
+            bn.running_mean.copy_(0.05 * torch.randn(H))
+            bn.running_var.copy_(1 + 0.1 * torch.rand(H))
+    out = {"w." + k: v.detach().clone().numpy() for k, v in model.state_dict().items()}
+    sizes = rng.integers(1, 13, size=P).astype(np.int64)
+    feats = (rng.random((int(sizes.sum()), F), dtype=np.float32) * 1.5).astype(np.float32)
+    feats[:, rng.random(F) < 0.15] = 0.0
+    out["sizes"], out["feats"] = sizes.astype(np.int32), feats
+    beta, lr = 0.1, 1e-3
+    out["hyper"] = np.array([beta, lr, 1e-5, 1.0, 0.1], dtype=np.float64)       # beta, lr, weight_decay, max_norm, p_drop
+    opt = torch.optim.AdamW(model.parameters(), lr=lr, weight_decay=1e-5)
+    captured = {}
+    real_randn_like = torch.randn_like
+
+    def randn_like(t, *a, **k):
+        captured["eps"] = real_randn_like(t, *a, **k)
+        return captured["eps"]
+
+    def hook(mod, inp, outp):
+        captured["mask"] = ((outp != 0) | (inp[0] == 0)).to(torch.uint8)
+
+    hd = model.decoder[3].register_forward_hook(hook)
+    model.train()
+    ts, tf = torch.from_numpy(sizes), torch.from_numpy(feats)
+    eps_l, mask_l, loss_l, gn_l = [], [], [], []
+    for step in range(3):
+        torch.randn_like = randn_like
+        try:
+            mean, logvar, z, recon, segsum = model(ts, tf)
+        finally:
+            torch.randn_like = real_randn_like
+        loss, recon_loss, kld = ref_tr.VAE_Trainer.vae_loss(None, recon, segsum, mean, logvar, beta)
+        opt.zero_grad()
+        loss.backward()
+        if step == 0:
+            out.update({"g." + k: p.grad.detach().clone().numpy() for k, p in model.named_parameters()})
+            out["mean0"], out["recon0"], out["segsum0"] = mean.detach().numpy(), recon.detach().numpy(), segsum.detach().numpy()
+        gn_l.append(float(torch.nn.utils.clip_grad_norm_(model.parameters(), max_norm=1.0)))
+        opt.step()
+        eps_l.append(captured["eps"].numpy().copy())
+        mask_l.append(captured["mask"].numpy().copy())
+        loss_l.append([loss.item(), recon_loss.item(), kld.item()])
+    hd.remove()
+    out["eps"], out["mask"] = np.stack(eps_l), np.stack(mask_l)
+    out["losses"], out["gnorm"] = np.array(loss_l, dtype=np.float64), np.array(gn_l, dtype=np.float64)
+    out.update({"p3." + k: v.detach().clone().numpy() for k, v in model.state_dict().items()})
+    np.savez_compressed(os.path.join(OUT, "segvae_train.npz"), **out)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     ns = load_reference()
@@ -522,6 +585,7 @@ def main():
     gen_reg_train(ns)
     gen_vae_train(ns)
     gen_extent_text(ns)
+    gen_segvae_train(ns)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

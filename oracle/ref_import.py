@@ -151,3 +151,26 @@ def load_reference_extent():
     mod = _load("_vaex_ref_utils_extent", "scripts/pre_experiments/model_myself/utils/extent.py")
     _CACHE["extent"] = mod
     return mod
+
+
+def load_reference_seg_trainer():
+    """The reference's scripts/vae_experiments/trainer.py (VAE_Trainer.vae_loss :270-280, train_vae :33-118) with its
+    `models` package bound to the reference directory and `util_manager`'s TVM imports stubbed."""
+    if "seg_trainer" in _CACHE:
+        return _CACHE["seg_trainer"]
+    ns = load_reference()
+    base = os.path.join(REF_ROOT, "scripts/vae_experiments")
+    _stub("tvm.relay", testing=None)
+    init = _stub("tvm.relay.testing.init", create_workload=lambda *a, **k: None)
+    testing = _stub("tvm.relay.testing", init=init)
+    sys.modules["tvm.relay"].testing = testing
+    sys.modules["tvm"].relay = sys.modules["tvm.relay"]
+    models = _stub("models")
+    models.__path__ = [os.path.join(base, "models")]
+    sys.modules["models.vae"] = ns.seg_vae
+    if ns.seg_reg is not None:
+        sys.modules["models.regression"] = ns.seg_reg
+    _load("util_manager", "scripts/vae_experiments/util_manager.py")
+    mod = _load("_vaex_ref_seg_trainer", "scripts/vae_experiments/trainer.py")
+    _CACHE["seg_trainer"] = mod
+    return mod

@@ -491,3 +491,64 @@ def vae_train_steps(P0, batches, alpha_recon=1.0, beta=0.01, lr=1e-3):
         opt.step()
         losses.append([float(total), float(recon), float(kl)])
     return {k: v.detach() for k, v in P.items()}, losses, first
+
+
+# --------------------------------------------------------------------------------------
+# a15 (segment family)  SegmentVAE training step: train-mode forward (vae.py:113-137), VAE_Trainer.vae_loss
+#      (scripts/vae_experiments/trainer.py:270-280), clip_grad_norm_(1.0) + AdamW(weight_decay=1e-5) (:40,57-66)
+# --------------------------------------------------------------------------------------
+SEGVAE_PARAM_ORDER = ["segment_encoder.0.weight", "segment_encoder.0.bias", "segment_encoder.2.weight", "segment_encoder.2.bias",
+                      "norm.weight", "norm.bias", "l0.0.weight", "l0.0.bias", "l1.0.weight", "l1.0.bias", "fc_mean.weight",
+                      "fc_mean.bias", "fc_logvar.weight", "fc_logvar.bias", "decoder.0.weight", "decoder.0.bias", "decoder.1.weight",
+                      "decoder.1.bias", "decoder.4.weight", "decoder.4.bias", "decoder.5.weight", "decoder.5.bias", "decoder.7.weight",
+                      "decoder.7.bias"]
+SEGVAE_BN = ["norm", "decoder.1", "decoder.5"]
+
+
+def _bn_train(x, P, pre, running=None, momentum=0.1):
+    """BatchNorm1d with batch statistics: biased variance normalises, the unbiased one feeds running_var."""
+    n = x.shape[0]
+    mu = x.mean(dim=0)
+    var = ((x - mu) ** 2).mean(dim=0)
+    if running is not None:
+        running[pre + ".running_mean"] = (1 - momentum) * running[pre + ".running_mean"] + momentum * mu.detach()
+        running[pre + ".running_var"] = (1 - momentum) * running[pre + ".running_var"] + momentum * var.detach() * n / (n - 1)
+    return (x - mu) / torch.sqrt(var + 1e-5) * P[pre + ".weight"] + P[pre + ".bias"]
+
+
+def segvae_train_loss(P, sizes, feats, eps, drop_mask, beta, p_drop=0.1, running=None):
+    """-> (total, recon_sum, kld_sum, mean, recon, segment_sum_vec).  eps: reparameterisation noise [P, L];
+    drop_mask: keep mask [P, H] of decoder.3 (None = no dropout)."""
+    S = segment_sum(segsum_mlp_encode_rows(P, feats), sizes)
+    h = _bn_train(S, P, "norm", running)
+    h = torch.relu(_lin(h, P["l0.0.weight"], P["l0.0.bias"])) + h
+    h = torch.relu(_lin(h, P["l1.0.weight"], P["l1.0.bias"])) + h
+    mean, logvar = _lin(h, P["fc_mean.weight"], P["fc_mean.bias"]), _lin(h, P["fc_logvar.weight"], P["fc_logvar.bias"])
+    z = mean + _t(eps) * torch.exp(0.5 * logvar)
+    d = torch.relu(_bn_train(_lin(z, P["decoder.0.weight"], P["decoder.0.bias"]), P, "decoder.1", running))
+    if drop_mask is not None:
+        d = d * _t(drop_mask) / (1.0 - p_drop)
+    d = torch.relu(_bn_train(_lin(d, P["decoder.4.weight"], P["decoder.4.bias"]), P, "decoder.5", running))
+    recon = _lin(d, P["decoder.7.weight"], P["decoder.7.bias"])
+    recon_loss = ((recon - S) ** 2).sum()                          # the target keeps its graph (no detach in the reference)
+    kld = -0.5 * torch.sum(1 + logvar - mean ** 2 - torch.exp(logvar))
+    return recon_loss + beta * kld, recon_loss, kld, mean, recon, S
+
+
+def segvae_train_steps(P0, sizes, feats, eps_list, mask_list, beta, lr, weight_decay=1e-5, clip=1.0, p_drop=0.1):
+    """-> (final params, running stats, [[total, recon, kld]], first-step grads, grad norms)"""
+    P = {k: _t(P0[k]).clone().requires_grad_(True) for k in SEGVAE_PARAM_ORDER}
+    running = {b + s: _t(P0[b + s]).clone() for b in SEGVAE_BN for s in (".running_mean", ".running_var")}
+    params = [P[k] for k in SEGVAE_PARAM_ORDER]
+    opt = torch.optim.AdamW(params, lr=lr, weight_decay=weight_decay)
+    losses, norms, first = [], [], None
+    for eps, mask in zip(eps_list, mask_list):
+        opt.zero_grad()
+        total, recon, kld = segvae_train_loss(P, sizes, feats, eps, mask, beta, p_drop, running)[:3]
+        total.backward()
+        if first is None:
+            first = {k: P[k].grad.detach().clone() for k in SEGVAE_PARAM_ORDER}
+        norms.append(float(torch.nn.utils.clip_grad_norm_(params, clip)))
+        opt.step()
+        losses.append([float(total), float(recon), float(kld)])
+    return {k: v.detach() for k, v in P.items()}, running, losses, first, norms

@@ -7,7 +7,7 @@ from .dataset import Dataset, LearningTask  # noqa: F401
 from .mlp_model import (MLPModel, MLPModelInternal, SegmentDataLoader, SegmentSumMLPModule,  # noqa: F401
                         flatten_features, make_net, predict_flat)
 from .vae_model import VAE_feature_head, VAECostPredictor, snap_extents, topk  # noqa: F401
-from . import extent, feature, select, shard, seg_models, training  # noqa: F401
+from . import extent, feature, select, shard, seg_models, seg_training, training  # noqa: F401
 from .seg_models import SegmentVAE  # noqa: F401
 from .select import select_programs  # noqa: F401
 from .extent import ExtentScaler, SketchSlots, state_to_records  # noqa: F401
