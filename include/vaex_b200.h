@@ -81,6 +81,7 @@ enum {
 typedef struct vaex_model* vaex_model_t;
 typedef struct vaex_trainer* vaex_trainer_t;
 typedef struct vaex_segvae_trainer* vaex_segvae_trainer_t;
+typedef struct vaex_segreg_trainer* vaex_segreg_trainer_t;
 
 const char* vaex_last_error(void);
 int vaex_abi_version(void);
@@ -310,6 +311,26 @@ int vaex_segvae_trainer_forward_backward(vaex_segvae_trainer_t t, const float* p
                                          int64_t n_rows, const float* eps_dev_or_null, const uint8_t* drop_mask_dev_or_null,
                                          uint64_t drop_seed, float p_drop, float beta, float* bn_running_dev_or_null,
                                          float* losses_dev, float* mean_out_dev_or_null, float* recon_out_dev_or_null,
+                                         void* stream);
+/* ---- segment-family VAECostPredictor training step (Regression_Trainer, scripts/vae_experiments/trainer.py:296-568) ----
+ * Flat buffers in VAECostPredictor.parameters() order (scripts/vae_experiments/models/regression.py:34-61);
+ * vaex_segreg_trainer_param_offset maps a state_dict key, "@encoder_group" or "@predictor_group" to its slice. */
+int vaex_segreg_trainer_create(int32_t F, int32_t H, int32_t L, int32_t PH, int32_t n_layers, vaex_segreg_trainer_t* out);
+int vaex_segreg_trainer_destroy(vaex_segreg_trainer_t t);
+int64_t vaex_segreg_trainer_param_count(vaex_segreg_trainer_t t);
+int vaex_segreg_trainer_param_offset(vaex_segreg_trainer_t t, const char* name, int64_t* offset, int64_t* count);
+/* forward(use_mean=True) in train mode + compute_total_loss (trainer.py:538-556: mse + lambda_pair * pair + gamma * smooth
+ * + beta * kld) + backward.  smooth_loss_fn runs predict_cost twice more in train mode, so a step is three predictor passes
+ * (z, z, z + noise), each with its own batch statistics, dropout draws and running-statistics update, all live in z.
+ * cfg_host fp32 [5] = {lambda_pair, margin, gamma, beta, p_drop}; noise_dev fp32 [P, L] = noise_std * randn;
+ * drop_masks_dev_or_null uint8 [3][n_layers - 1][P, PH] (1 = keep), else drop_seed != 0 (Philox), else no dropout;
+ * bn_running_dev_or_null fp32 = norm {mean, var}[H] then per predictor block {mean, var}[PH];
+ * losses_dev fp32 [5] = {total, reg, pair, smooth, kld}; cost_dev_or_null fp32 [P]. */
+int vaex_segreg_trainer_forward_backward(vaex_segreg_trainer_t t, const float* params_dev, float* grads_dev,
+                                         const float* feats_dev, const int32_t* seg_offsets_dev, const float* labels_dev,
+                                         int64_t n_programs, int64_t n_rows, const float* noise_dev,
+                                         const uint8_t* drop_masks_dev_or_null, uint64_t drop_seed, const float* cfg_host,
+                                         float* bn_running_dev_or_null, float* losses_dev, float* cost_dev_or_null,
                                          void* stream);
 /* torch.optim.AdamW on the group params[off, off + cnt); the clip coefficient uses the norm of the whole gradient
  * buffer (clip_grad_norm_ over all parameters), recomputed into gnorm_dev when compute_norm != 0 */

@@ -571,6 +571,77 @@ def gen_segvae_train(ns):
     np.savez_compressed(os.path.join(OUT, "segvae_train.npz"), **out)
 
 
+def gen_segreg_train(ns):
+    """SURVEY 8a a15, segment family, regression: three steps of the reference's segment VAECostPredictor
+    (models/regression.py) exactly as Regression_Trainer.train_phase runs them (trainer.py:446-455): model.train(),
+    Regression_Trainer.compute_total_loss (three train-mode predictor passes), backward, clip_grad_norm_(1.0), AdamW with the
+    encoder / predictor groups.  The smoothness noise and the six dropout keep-masks of each step (3 passes x 2 Dropout
+    layers, in call order) are captured from the run."""
+    from oracle.ref_import import load_reference_seg_trainer
+    ref_tr = load_reference_seg_trainer()
+    torch.manual_seed(11)
+    rng = np.random.default_rng(11)
+    F, H, L, PH, P = 164, 256, 64, 256, 36
+    model = ns.seg_reg.VAECostPredictor(F, H, L, PH, 3, 0.1)
+    bns = [model.norm, model.cost_predictor[1], model.cost_predictor[5], model.cost_predictor[9]]
+    with torch.no_grad():
+        for bn in bns:
+            bn.weight.copy_(1 + 0.2 * torch.randn(bn.num_features))
+            bn.bias.copy_(0.1 * torch.randn(bn.num_features))
+            bn.running_mean.copy_(0.05 * torch.randn(bn.num_features))
+            bn.running_var.copy_(1 + 0.1 * torch.rand(bn.num_features))
+    out = {"w." + k: v.detach().clone().numpy() for k, v in model.state_dict().items()}
+    sizes = rng.integers(1, 13, size=P).astype(np.int64)
+    feats = (rng.random((int(sizes.sum()), F), dtype=np.float32) * 1.5).astype(np.float32)
+    feats[:, rng.random(F) < 0.15] = 0.0
+    labels = rng.random(P).astype(np.float32)
+    labels[5] = labels[9]                                       # a tie: sign(0) = 0 pairs contribute `margin`
+    out["sizes"], out["feats"], out["labels"] = sizes.astype(np.int32), feats, labels
+    config = {"encoder_lr": 3e-4, "predictor_lr": 1e-3, "lambda_pair": 0.3, "gamma": 0.05, "beta": 0.01, "margin": 0.1, "noise_std": 0.1}
+    out["hyper"] = np.array([config[k] for k in ("encoder_lr", "predictor_lr", "lambda_pair", "gamma", "beta", "margin", "noise_std")] + [0.1],
+                            dtype=np.float64)
+    opt = torch.optim.AdamW([{"params": model.get_encoder_params(), "lr": config["encoder_lr"]},
+                             {"params": model.get_predictor_params(), "lr": config["predictor_lr"]}], weight_decay=1e-5)
+    trainer = object.__new__(ref_tr.Regression_Trainer)         # the loss methods use no instance state
+    cap = {"masks": []}
+    real_randn_like = torch.randn_like
+
+    def randn_like(t, *a, **k):
+        cap["eps"] = real_randn_like(t, *a, **k)
+        return cap["eps"]
+
+    def hook(mod, inp, outp):
+        cap["masks"].append(((outp != 0) | (inp[0] == 0)).to(torch.uint8).numpy().copy())
+
+    hooks = [model.cost_predictor[3].register_forward_hook(hook), model.cost_predictor[7].register_forward_hook(hook)]
+    ts, tf, tl = torch.from_numpy(sizes), torch.from_numpy(feats), torch.from_numpy(labels)
+    noise_l, mask_l, loss_l, gn_l = [], [], [], []
+    for step in range(3):
+        model.train()
+        opt.zero_grad()
+        cap["masks"] = []
+        torch.randn_like = randn_like
+        try:
+            total, comp = trainer.compute_total_loss(model, ts, tf, tl, config, return_components=True)
+        finally:
+            torch.randn_like = real_randn_like
+        total.backward()
+        if step == 0:
+            out.update({"g." + k: p.grad.detach().clone().numpy() for k, p in model.named_parameters()})
+        gn_l.append(float(torch.nn.utils.clip_grad_norm_(model.parameters(), max_norm=1.0)))
+        opt.step()
+        assert len(cap["masks"]) == 6                            # call order: pass0 (d0, d1), pass1 (d0, d1), pass2 (d0, d1)
+        noise_l.append((config["noise_std"] * cap["eps"]).numpy().copy())
+        mask_l.append(np.stack(cap["masks"]).reshape(3, 2, P, PH))
+        loss_l.append([comp["total_loss"], comp["reg_loss"], comp["pair_loss"], comp["smooth_loss"], comp["kld_loss"]])
+    for h in hooks:
+        h.remove()
+    out["noise"], out["mask"] = np.stack(noise_l), np.stack(mask_l)
+    out["losses"], out["gnorm"] = np.array(loss_l, dtype=np.float64), np.array(gn_l, dtype=np.float64)
+    out.update({"p3." + k: v.detach().clone().numpy() for k, v in model.state_dict().items()})
+    np.savez_compressed(os.path.join(OUT, "segreg_train.npz"), **out)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     ns = load_reference()
@@ -586,6 +657,7 @@ def main():
     gen_vae_train(ns)
     gen_extent_text(ns)
     gen_segvae_train(ns)
+    gen_segreg_train(ns)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

@@ -552,3 +552,71 @@ def segvae_train_steps(P0, sizes, feats, eps_list, mask_list, beta, lr, weight_d
         opt.step()
         losses.append([float(total), float(recon), float(kld)])
     return {k: v.detach() for k, v in P.items()}, running, losses, first, norms
+
+
+# --------------------------------------------------------------------------------------
+# a15 (segment family, regression)  Regression_Trainer.compute_total_loss (scripts/vae_experiments/trainer.py:485-556) on the
+#      segment VAECostPredictor in train mode (models/regression.py:82-135), clip + AdamW over two groups (trainer.py:401-455)
+# --------------------------------------------------------------------------------------
+def segreg_param_order(n_layers=3):
+    enc = SEGVAE_PARAM_ORDER[:14]
+    pred = []
+    for i in range(n_layers):
+        pred += ["cost_predictor.%d.weight" % (4 * i), "cost_predictor.%d.bias" % (4 * i),
+                 "cost_predictor.%d.weight" % (4 * i + 1), "cost_predictor.%d.bias" % (4 * i + 1)]
+    pred += ["cost_predictor.%d.weight" % (4 * n_layers), "cost_predictor.%d.bias" % (4 * n_layers)]
+    return enc, pred
+
+
+def _segreg_predict_train(P, z, masks, p_drop, running, n_layers=3):
+    """One train-mode predict_cost pass: n x [Linear, BatchNorm (batch stats), ReLU, Dropout (all but the last)] + Linear."""
+    h = z
+    for i in range(n_layers):
+        pre = "cost_predictor.%d" % (4 * i)
+        h = torch.relu(_bn_train(_lin(h, P[pre + ".weight"], P[pre + ".bias"]), P, "cost_predictor.%d" % (4 * i + 1), running))
+        if i < n_layers - 1 and masks is not None:
+            h = h * _t(masks[i]) / (1.0 - p_drop)
+    pre = "cost_predictor.%d" % (4 * n_layers)
+    return _lin(h, P[pre + ".weight"], P[pre + ".bias"]).squeeze(-1)
+
+
+def segreg_total_loss(P, sizes, feats, labels, cfg, noise, masks, p_drop=0.1, running=None, n_layers=3):
+    """-> (total, reg, pair, smooth, kld).  noise [P, L] = noise_std * randn; masks [3 passes][n_layers - 1][P, PH] or None."""
+    S = segment_sum(segsum_mlp_encode_rows(P, feats), sizes)
+    h = _bn_train(S, P, "norm", running)
+    h = torch.relu(_lin(h, P["l0.0.weight"], P["l0.0.bias"])) + h
+    h = torch.relu(_lin(h, P["l1.0.weight"], P["l1.0.bias"])) + h
+    mean, logvar = _lin(h, P["fc_mean.weight"], P["fc_mean.bias"]), _lin(h, P["fc_logvar.weight"], P["fc_logvar.bias"])
+    z = mean                                                       # forward(use_mean=True)
+    m = (lambda q: None if masks is None else masks[q])
+    cost = _segreg_predict_train(P, z, m(0), p_drop, running, n_layers)
+    y = _t(labels)
+    reg = torch.mean((cost - y) ** 2)
+    pair = pair_loss(cost, y, cfg.get("margin", 0.1))
+    c1 = _segreg_predict_train(P, z, m(1), p_drop, running, n_layers)
+    c2 = _segreg_predict_train(P, z + _t(noise), m(2), p_drop, running, n_layers)
+    smooth = torch.mean((c1 - c2) ** 2)
+    kld = kld_loss(mean, logvar)
+    total = reg + cfg.get("lambda_pair", 0.1) * pair + cfg.get("gamma", 0.01) * smooth + cfg.get("beta", 0.001) * kld
+    return total, reg, pair, smooth, kld
+
+
+def segreg_train_steps(P0, sizes, feats, labels, cfg, noise_list, mask_list, encoder_lr, predictor_lr, weight_decay=1e-5, clip=1.0,
+                       p_drop=0.1, n_layers=3):
+    enc, pred = segreg_param_order(n_layers)
+    P = {k: _t(P0[k]).clone().requires_grad_(True) for k in enc + pred}
+    bns = ["norm"] + ["cost_predictor.%d" % (4 * i + 1) for i in range(n_layers)]
+    running = {b + s: _t(P0[b + s]).clone() for b in bns for s in (".running_mean", ".running_var")}
+    opt = torch.optim.AdamW([{"params": [P[k] for k in enc], "lr": encoder_lr}, {"params": [P[k] for k in pred], "lr": predictor_lr}],
+                            weight_decay=weight_decay)
+    losses, norms, first = [], [], None
+    for noise, masks in zip(noise_list, mask_list):
+        opt.zero_grad()
+        vals = segreg_total_loss(P, sizes, feats, labels, cfg, noise, masks, p_drop, running, n_layers)
+        vals[0].backward()
+        if first is None:
+            first = {k: P[k].grad.detach().clone() for k in enc + pred}
+        norms.append(float(torch.nn.utils.clip_grad_norm_([P[k] for k in enc + pred], clip)))
+        opt.step()
+        losses.append([float(v) for v in vals])
+    return {k: v.detach() for k, v in P.items()}, running, losses, first, norms

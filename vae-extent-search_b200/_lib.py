@@ -80,6 +80,11 @@ SIGNATURES = {
     "vaex_segvae_trainer_param_count": ([vp], i64),
     "vaex_segvae_trainer_param_offset": ([vp, ctypes.c_char_p, ctypes.POINTER(i64), ctypes.POINTER(i64)], ctypes.c_int),
     "vaex_segvae_trainer_forward_backward": ([vp, vp, vp, vp, vp, i64, i64, vp, vp, u64, f32, f32, vp, vp, vp, vp, vp], ctypes.c_int),
+    "vaex_segreg_trainer_create": ([i32, i32, i32, i32, i32, ctypes.POINTER(vp)], ctypes.c_int),
+    "vaex_segreg_trainer_destroy": ([vp], ctypes.c_int),
+    "vaex_segreg_trainer_param_count": ([vp], i64),
+    "vaex_segreg_trainer_param_offset": ([vp, ctypes.c_char_p, ctypes.POINTER(i64), ctypes.POINTER(i64)], ctypes.c_int),
+    "vaex_segreg_trainer_forward_backward": ([vp, vp, vp, vp, vp, vp, i64, i64, vp, vp, u64, vp, vp, vp, vp, vp], ctypes.c_int),
     "vaex_adamw_step": ([vp, vp, vp, vp, i64, i64, i64, i64, f32, f32, f32, f32, f32, f32, f32, vp, ctypes.c_int, vp], ctypes.c_int),
     "vaex_kcenter_select": ([vp, i64, i32, vp, i64, vp, i64, i32, f32, vp, vp], ctypes.c_int),
     "vaex_topk": ([vp, i64, i32, vp, vp, vp, vp, vp], ctypes.c_int),

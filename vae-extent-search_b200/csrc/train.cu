@@ -195,3 +195,4 @@ static int transpose_to(const float* W, int rows, int cols, float* Wt, cudaStrea
 #include "train_step.inc"
 #include "train_vae.inc"
 #include "train_segvae.inc"
+#include "train_segreg.inc"
