@@ -1,6 +1,6 @@
 // Probe (not product): can the box's host cores narrow fp32 features to fp16 faster than PCIe moves fp32?
 // Prints GB/s of fp32 input consumed by T threads (AVX2/F16C, streaming stores), alone and while an H2D copy
-// of the packed halves runs.  Build: nvcc -O3 -Xcompiler "-mavx2 -mf16c -pthread" tools/host_pack_probe.cu -o /tmp/probe
+// of the packed halves runs.  Build: nvcc -O3 -Xcompiler "-mavx2 -mf16c -pthread" tools/host_pack_probe.cu vae-extent-search_b200/csrc/build/host_pack.o -o tools/host_pack_probe.bin
 #include <cuda_runtime.h>
 #include <immintrin.h>
 #include <chrono>
@@ -9,7 +9,9 @@
 #include <cstring>
 #include <thread>
 #include <vector>
-static void pack(const float* in, uint16_t* out, size_t n) {
+namespace vaex { bool host_pack_f16(const float* in, uint16_t* out, size_t n); }
+static void pack(const float* in, uint16_t* out, size_t n) { vaex::host_pack_f16(in, out, n); }
+static void pack_avx2_probe(const float* in, uint16_t* out, size_t n) {
   const __m256 lim = _mm256_set1_ps(65504.f), nlim = _mm256_set1_ps(-65504.f);
   for (size_t i = 0; i < n; i += 16) {
     __m256 a = _mm256_min_ps(_mm256_max_ps(_mm256_loadu_ps(in + i), nlim), lim);
