@@ -294,6 +294,11 @@ def main_vaex(args):
         hs = np.ascontiguousarray(sizes[:Pe])
         n_e2e = max(2, min(args.steps, 5))
 
+        # several ranks share the host cores: give each its share of narrowing threads (the library default, cores - 1,
+        # is for one process per host); with one core or less per rank the call simply sends more chunks as raw fp32
+        if world > 1 and "VAEX_PACK_THREADS" not in os.environ:
+            os.environ["VAEX_PACK_THREADS"] = str(max(1, (os.cpu_count() or 1) // world - 1))
+
         def e2e_step():
             _lib.check(lib.vaex_segsum_mlp_predict_host(model.h, host.data_ptr(), hs.ctypes.data, Pe, re_, out.data_ptr(), flags))
 

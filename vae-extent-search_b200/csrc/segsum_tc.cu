@@ -250,6 +250,10 @@ __device__ __forceinline__ void flush_piece(float* dst, float s, uint32_t partia
       "{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0;\n\t@p red.global.add.f32 [%0], %1;\n\t@!p st.global.f32 [%0], %1;\n\t}"
       :: "l"(dst), "f"(s), "r"(partial) : "memory");
 }
+// Tried and measured (profiles/r01_ncu_segsum_tc_v8_notes.md): four accumulator chains instead of two (no change: the
+// `wait` stalls are not the FADD chains), __builtin_expect / goto-ordered cold blocks (ptxas lays the boundary block out as
+// the fall-through of its branch regardless of source or PTX order), the boundary path as a __noinline__ call (compact hot
+// loop, but 4.08 vs 3.85 ms: call stubs + spills).
 template <bool FOLD>
 __device__ __forceinline__ void sum_chunk(const uint32_t (&v)[16], uint32_t m, uint32_t pm, float b1, float& a0, float& a1,
                                           float*& dst) {
