@@ -296,11 +296,17 @@ def main_vaex(args):
 
         # several ranks share the host cores: give each its share of narrowing threads (the library default, cores - 1,
         # is for one process per host); with one core or less per rank the call simply sends more chunks as raw fp32
+        e2e_flags = flags
         if world > 1 and "VAEX_PACK_THREADS" not in os.environ:
             os.environ["VAEX_PACK_THREADS"] = str(max(1, (os.cpu_count() or 1) // world - 1))
+        if os.environ.get("VAEX_BENCH_NO_PACK") or (os.cpu_count() or 1) // world < 8:
+            # fewer than 8 host cores per rank: the host's memory system, not one GPU's PCIe link, bounds the copy, and the
+            # narrowing threads only add traffic (measured on 16 cores, aggregate programs/s raw vs narrowed: 1 rank 5.1e6 vs
+            # 8.3e6, 2 ranks 1.01e7 vs 1.12e7, 4 ranks 1.94e7 vs 1.51e7, 8 ranks 1.69e7 vs 1.57e7) -> send the rows as they are
+            e2e_flags = flags | _lib.F_NO_HOST_PACK
 
         def e2e_step():
-            _lib.check(lib.vaex_segsum_mlp_predict_host(model.h, host.data_ptr(), hs.ctypes.data, Pe, re_, out.data_ptr(), flags))
+            _lib.check(lib.vaex_segsum_mlp_predict_host(model.h, host.data_ptr(), hs.ctypes.data, Pe, re_, out.data_ptr(), e2e_flags))
 
         e2e_step()
         barrier()
