@@ -440,6 +440,34 @@ def test_latent_ascent_vs_oracle():
     np.testing.assert_allclose(c.cpu().numpy(), wc.numpy(), rtol=1e-3, atol=1e-4)
 
 
+@pytest.mark.parametrize("n,steps", [(1, 3), (13, 1), (256, 0), (300, 20), (1000, 200)])
+def test_latent_ascent_cluster_kernel(n, steps):
+    """The one-kernel ascent (4-CTA clusters, weights and activations on chip for all steps) against the launch-per-layer
+    path (VAEX_OPT_FUSED_ASCENT = 0) and the fp32 oracle: ragged restart counts, zero steps, the 200-step case of config 3."""
+    g = load_golden("extent_vae.npz")
+    reg = vaex_b200.VAECostPredictor(48, hidden_dim=256, latent_dim=64)
+    reg.load_state_dict(split_sd(g, "reg."))
+    reg = reg.cuda().eval()
+    rng = np.random.default_rng(n)
+    z0 = rng.standard_normal((n, 64)).astype(np.float32)
+    zt = torch.from_numpy(z0).cuda()
+    z1, c1 = reg.latent_ascent(zt, steps=steps, lr=1e-2)
+    z1b, c1b = reg.latent_ascent(zt, steps=steps, lr=1e-2)
+    assert torch.equal(z1, z1b) and torch.equal(c1, c1b)                       # deterministic
+    assert torch.equal(zt, torch.from_numpy(z0).cuda())                        # the input is not modified
+    reg.packed().set_option(_lib.OPT_FUSED_ASCENT, 0)
+    z2, c2 = reg.latent_ascent(zt, steps=steps, lr=1e-2)
+    reg.packed().set_option(_lib.OPT_FUSED_ASCENT, 1)
+    np.testing.assert_allclose(z1.cpu().numpy(), z2.cpu().numpy(), rtol=1e-3, atol=2e-4)
+    np.testing.assert_allclose(c1.cpu().numpy(), c2.cpu().numpy(), rtol=1e-3, atol=2e-4)
+    if n <= 300:
+        wz, wc = O.latent_ascent(split_sd(g, "reg."), z0, steps, 1e-2)
+        np.testing.assert_allclose(z1.cpu().numpy(), wz.numpy(), rtol=1e-3, atol=1e-4)
+        np.testing.assert_allclose(c1.cpu().numpy(), wc.numpy(), rtol=1e-3, atol=1e-4)
+    if steps == 0:
+        assert torch.equal(z1, zt)
+
+
 def test_errors_are_loud():
     lib = _lib.load()
     m = _lib.Model(_lib.KIND_SEGSUM_MLP, [164, 256, 0, 0])

@@ -10,7 +10,7 @@ LIB_PATH = os.path.join(_HERE, "libvaex_b200.so")
 
 KIND_SEGSUM_MLP, KIND_EXTENT_VAE, KIND_COST_PREDICTOR, KIND_SEGMENT_VAE, KIND_SEGMENT_COST = 1, 2, 3, 4, 5
 F_MASK_INVALID, F_FORCE_SIMT, F_FEATS_F16, F_NO_HOST_PACK = 1, 2, 4, 8
-OPT_TENSOR_CORES = 1
+OPT_TENSOR_CORES, OPT_FUSED_ASCENT = 1, 2
 SNAP_EXP, SNAP_EXPM1, SNAP_DIVISOR = 0, 1, 4
 LOSS_IDS = {"rmse": 0, "rankNetLoss": 1, "lambdaRankLoss": 2, "listNetLoss": 3}
 

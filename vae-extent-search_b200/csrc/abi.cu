@@ -246,6 +246,7 @@ int vaex_model_create(int kind, const int32_t* dims, int ndims, vaex_model_t* ou
 int vaex_model_set_option(vaex_model_t h, int option, int value) {
   VAEX_CHECK(h, "null handle");
   if (option == VAEX_OPT_TENSOR_CORES) { h->use_tensor = value ? 1 : 0; return VAEX_OK; }
+  if (option == VAEX_OPT_FUSED_ASCENT) { h->use_fused_ascent = value ? 1 : 0; return VAEX_OK; }
   set_error("unknown option");
   return VAEX_E_INVALID;
 }

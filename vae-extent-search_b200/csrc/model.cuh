@@ -56,6 +56,7 @@ struct vaex_model {
   vaex::TcPack tc;
   vaex::ChainPack dec_chain, pred_chain, enc_mu_chain, enc_lv_chain;   // extent-VAE decoder / cost predictor / encoder on tensor cores
   int use_tensor = 1;                      // VAEX_OPT_TENSOR_CORES
+  int use_fused_ascent = 1;                // VAEX_OPT_FUSED_ASCENT
   vaex::DevBuf ws[6];                  // activations / staging
   vaex::DevBuf topk_ws;
   vaex::DevBuf tc_ws;                  // first_prog + rowmask of the tcgen05 kernel
@@ -89,6 +90,8 @@ int chain_tc_run(const ChainPack& cp, const float* X, int64_t n, float* out, int
 // segsum_tc.cu
 int segsum_tc_encode(vaex_model* m, const float* feats, const int32_t* off, int64_t n_programs,
                      int64_t n_rows, float* segsum, uint8_t* valid, cudaStream_t st, bool feats_f16 = false);
+// ascent_cluster.cu
+int ascent_cluster_run(vaex_model* m, float* z, int64_t n, int steps, float lr, float* cost, cudaStream_t st);
 // host_pack.cpp
 bool host_pack_supported();
 bool host_pack_f16(const float* in, uint16_t* out, size_t n);   // true: a non-zero value became zero
