@@ -194,8 +194,8 @@ int ascent_cluster_run(vaex_model* m, float* z, int64_t n, int steps, float lr, 
   p.wd = m->w("cost_predictor.6.weight"); p.bd = m->w("cost_predictor.6.bias");
   VAEX_CHECK(p.W0 && p.b0 && p.W1 && p.b1 && p.wd && p.bd, "cost predictor weights missing");
   p.z = z; p.cost = cost; p.n = (int)n; p.steps = steps; p.lr = lr;
-  static bool attr = false;
-  if (!attr) { VAEX_CUDA(cudaFuncSetAttribute(ascent_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES)); attr = true; }
+  // per device and cheap: no process-wide "done" flag
+  VAEX_CUDA(cudaFuncSetAttribute(ascent_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
   const unsigned clusters = (unsigned)cdiv(n, ROWS);
   ascent_cluster_kernel<<<clusters * CL, T, SMEM_BYTES, st>>>(p);
   VAEX_LAUNCH_CHECK();
