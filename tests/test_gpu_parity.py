@@ -386,6 +386,19 @@ def test_snap_bit_exact_and_legalise():
     for j0 in range(0, 44, 4):
         prod = got[:, j0:j0 + 4].astype(np.int64).prod(axis=1)
         assert (ext[j0] % prod == 0).all() and (got[:, j0 + 3] <= 64).all()
+    # the shared-memory tiled kernel (d <= 64) and the plain one (d > 64), ragged row counts around the 128-row tile
+    for n, d in ((1, 4), (127, 48), (129, 45), (1000, 64), (300, 80)):
+        raw = rng.integers(1, 200, size=(n, d)).astype(np.int32)
+        e2, l2 = [], []
+        while len(e2) + 4 <= d - 1:
+            e2 += [bounds[rng.integers(len(bounds))]] * 4
+            l2 += [0, 0, 0, 1]
+        e2, l2 = e2 + [0] * (d - len(e2)), l2 + [0] * (d - len(l2))
+        t = torch.from_numpy(raw).cuda()
+        e2d, l2d = torch.tensor(e2, dtype=torch.int32).cuda(), torch.tensor(l2, dtype=torch.uint8).cuda()   # kept alive over the call
+        _lib.check(_lib.load().vaex_legalise_extents(_lib.ptr(t), n, d, _lib.ptr(e2d), _lib.ptr(l2d), None, 0, 64, None))
+        torch.cuda.synchronize()
+        assert np.array_equal(t.cpu().numpy(), O.legalise_divisor(raw, e2, l2)), (n, d)
 
 
 def test_topk_vs_oracle():

@@ -195,10 +195,56 @@ __global__ void legalise_kernel(int32_t* __restrict__ ext, int64_t n, int d,
   }
 }
 
+// Same walk with the rows staged through shared memory: a thread per row reads d consecutive ints (192 B apart from its
+// neighbour's for d = 48), which costs a full sector per element; here a CTA copies its 128 rows in and out with
+// coalesced 4-byte accesses and the walk runs on a padded (d + 1) tile without bank conflicts.  Used for d <= 64.
+constexpr int LEG_ROWS = 128;
+__global__ void __launch_bounds__(LEG_ROWS) legalise_tiled_kernel(int32_t* __restrict__ ext, int64_t n, int d,
+                                                                  const int32_t* __restrict__ slot_extent,
+                                                                  const uint8_t* __restrict__ slot_last, int max_innermost,
+                                                                  const int32_t* __restrict__ order, int n_order) {
+  extern __shared__ int32_t tile[];            // [LEG_ROWS][d + 1], then slot_extent[d], slot_last[d] (as int), order[steps]
+  const int ds = d + 1;
+  int32_t* se = tile + LEG_ROWS * ds;
+  int32_t* sl = se + d;
+  int32_t* so = sl + d;
+  const int steps = order ? n_order : d;
+  const int64_t r0 = (int64_t)blockIdx.x * LEG_ROWS;
+  const int rows = (int)min((int64_t)LEG_ROWS, n - r0);
+  for (int j = threadIdx.x; j < d; j += LEG_ROWS) { se[j] = slot_extent[j]; sl[j] = slot_last[j]; }
+  for (int j = threadIdx.x; j < steps; j += LEG_ROWS) so[j] = order ? order[j] : j;
+  int32_t* g = ext + r0 * d;
+  for (int e = threadIdx.x; e < rows * d; e += LEG_ROWS) tile[(e / d) * ds + e % d] = g[e];
+  __syncthreads();
+  if (threadIdx.x < rows) {
+    int32_t* row = tile + threadIdx.x * ds;
+    int rem = 0;
+    for (int jj = 0; jj < steps; ++jj) {
+      const int j = so[jj];
+      const int sext = se[j];
+      if (sext <= 0) { rem = 0; continue; }
+      if (rem == 0) rem = sext;
+      const int last = sl[j];
+      const int q = nearest_divisor(rem, row[j], last ? max_innermost : 0);
+      row[j] = q;
+      rem /= q;
+      if (last) rem = 0;
+    }
+  }
+  __syncthreads();
+  for (int e = threadIdx.x; e < rows * d; e += LEG_ROWS) g[e] = tile[(e / d) * ds + e % d];
+}
+
 int legalise_extents(int32_t* ext, int64_t n, int d, const int32_t* slot_extent, const uint8_t* slot_last, int max_innermost,
                      cudaStream_t st, const int32_t* order, int n_order) {
   if (n == 0) return VAEX_OK;
-  legalise_kernel<<<(unsigned)cdiv(n, 128), 128, 0, st>>>(ext, n, d, slot_extent, slot_last, max_innermost, order, n_order);
+  if (d <= 64) {
+    const size_t sh = sizeof(int32_t) * ((size_t)LEG_ROWS * (d + 1) + 3 * (size_t)d);
+    legalise_tiled_kernel<<<(unsigned)cdiv(n, LEG_ROWS), LEG_ROWS, sh, st>>>(ext, n, d, slot_extent, slot_last, max_innermost, order,
+                                                                             n_order);
+  } else {
+    legalise_kernel<<<(unsigned)cdiv(n, 128), 128, 0, st>>>(ext, n, d, slot_extent, slot_last, max_innermost, order, n_order);
+  }
   VAEX_LAUNCH_CHECK();
   return VAEX_OK;
 }
@@ -211,8 +257,7 @@ int snap_extents(const float* x, int64_t n, int d, const float* mean, const floa
   VAEX_LAUNCH_CHECK();
   if (mode & VAEX_SNAP_DIVISOR) {
     VAEX_CHECK(slot_extent && slot_last, "divisor mode needs slot tables");
-    legalise_kernel<<<(unsigned)cdiv(n, 128), 128, 0, st>>>(out, n, d, slot_extent, slot_last, max_innermost, nullptr, 0);
-    VAEX_LAUNCH_CHECK();
+    TRY(legalise_extents(out, n, d, slot_extent, slot_last, max_innermost, st, nullptr, 0));
   }
   return VAEX_OK;
 }
