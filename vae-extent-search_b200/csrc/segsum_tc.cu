@@ -168,6 +168,8 @@ __device__ __forceinline__ uint32_t load_convert_rows(const TcParams& p, uint32_
 constexpr int FAST_SLOTS = 24;                        // 16 rows * 47 units / 32 lanes
 constexpr int FAST_BATCH = 12;
 struct FastLoader {
+  static constexpr int BATCH = FAST_BATCH;
+  using Unit = float4;
   const float4* src;
   int valid_units, total;
   __device__ __forceinline__ void open(const TcParams& p, int64_t grow0, int lane) {
@@ -203,36 +205,48 @@ struct FastLoader {
 };
 
 // Same walk for features that are already fp16 in HBM (VAEX_F_FEATS_F16: the host path narrows them before the
-// PCIe copy): a unit is 4 halves = one LDG.64, stored as it is; the offset table is the fp32 one (a unit is
-// still 4 features).  Half the bytes per tile, no F2FP.
+// PCIe copy).  A lane moves 16 bytes = 8 halves per slot with one LDG.128 - two consecutive 4-feature units of the
+// table above, so a slot that straddles two rows (F % 8 == 4) simply stores its halves at two table offsets.  A
+// warp's 16-row run is a whole number of 16-byte units (16 * F * 2 bytes); only the ragged last tile can end on a
+// half unit, which is fetched with one LDG.64.  11 slots per lane (F = 164) instead of 21, no F2FP, and as many
+// bytes in flight per load as the fp32 walk (LDG.64 per 4-feature unit measured SLOWER than fp32 rows: 4.28 vs
+// 4.05 ms per 10^6 programs - the loaders are bound by bytes in flight, not by their instruction count).
 struct FastLoaderH {
-  const uint2* src;
-  int valid_units, total;
+  static constexpr int BATCH = 6;
+  using Unit = uint4;
+  const uint4* src;
+  int valid_units, total;                              // in 8-byte (4-feature) units, like the table
   __device__ __forceinline__ void open(const TcParams& p, int64_t grow0, int lane) {
     constexpr int ROWS = tc::TILE / tc::LOAD_WARPS;
     total = ROWS * (p.F >> 2);
     const int64_t vr = min((int64_t)ROWS, p.n_rows - grow0);
     valid_units = vr > 0 ? (int)vr * (p.F >> 2) : 0;
-    src = reinterpret_cast<const uint2*>(reinterpret_cast<const __half*>(p.feats) + (vr > 0 ? grow0 : 0) * p.F) + lane;
+    src = reinterpret_cast<const uint4*>(reinterpret_cast<const __half*>(p.feats) + (vr > 0 ? grow0 : 0) * p.F) + lane;
   }
-  __device__ __forceinline__ void issue(int s0, int lane, uint2 (&x)[FAST_BATCH]) const {
+  __device__ __forceinline__ void issue(int s0, int lane, uint4 (&x)[BATCH]) const {
 #pragma unroll
-    for (int j = 0; j < FAST_BATCH; ++j) {
-      const int idx = (s0 + j) * 32 + lane;
-      if (idx < valid_units) x[j] = ptx::ldg_stream_u2(src + (s0 + j) * 32);
-      else x[j] = make_uint2(0u, 0u);
+    for (int j = 0; j < BATCH; ++j) {
+      const int u = 2 * ((s0 + j) * 32 + lane);        // first 8-byte unit of this slot
+      if (u + 1 < valid_units) x[j] = ptx::ldg_stream_u4(src + (s0 + j) * 32);
+      else if (u < valid_units) {
+        const uint2 h = ptx::ldg_stream_u2(src + (s0 + j) * 32);
+        x[j] = make_uint4(h.x, h.y, 0u, 0u);
+      } else x[j] = make_uint4(0u, 0u, 0u, 0u);
     }
   }
-  __device__ __forceinline__ uint32_t commit(int s0, int lane, const uint2 (&x)[FAST_BATCH], uint32_t A0w,
+  __device__ __forceinline__ uint32_t commit(int s0, int lane, const uint4 (&x)[BATCH], uint32_t A0w,
                                              const uint16_t* tab) const {
     uint32_t mask = 0;
 #pragma unroll
-    for (int j = 0; j < FAST_BATCH; ++j) {
-      const int idx = (s0 + j) * 32 + lane;
-      if (idx < total) {
-        const uint32_t o = tab[idx];
-        ptx::sts_v2(A0w + o, x[j].x, x[j].y);
-        if ((x[j].x | x[j].y) & 0x7fff7fffu) mask |= 1u << ((o >> 7) & 15);
+    for (int j = 0; j < BATCH; ++j) {
+      const int u = 2 * ((s0 + j) * 32 + lane);
+      if (u < total) {                                  // total is even: both halves of the slot are in the tile
+        const uint32_t o = *reinterpret_cast<const uint32_t*>(tab + u);
+        const uint32_t o0 = o & 0xffffu, o1 = o >> 16;
+        ptx::sts_v2(A0w + o0, x[j].x, x[j].y);
+        ptx::sts_v2(A0w + o1, x[j].z, x[j].w);
+        if ((x[j].x | x[j].y) & 0x7fff7fffu) mask |= 1u << ((o0 >> 7) & 15);
+        if ((x[j].z | x[j].w) & 0x7fff7fffu) mask |= 1u << ((o1 >> 7) & 15);
       }
     }
     return mask;
@@ -319,7 +333,7 @@ segsum_tc_kernel(const TcParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[B_COUNT];
   __shared__ uint32_t tmem_base_slot;
-  __shared__ uint16_t a0_tab[FAST_SLOTS * 32];
+  __shared__ __align__(16) uint16_t a0_tab[FAST_SLOTS * 32];
 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const uint32_t sbase = ptx::smem_u32(smem);
@@ -404,8 +418,9 @@ segsum_tc_kernel(const TcParams p) {
     };
     if (lane == 0) { prefetch(cluster + n_clusters); prefetch(cluster + 2 * n_clusters); }
     if (al16) {
-      typename std::conditional<HALF_IN, FastLoaderH, FastLoader>::type ld;
-      typename std::conditional<HALF_IN, uint2, float4>::type x[FAST_BATCH];
+      using Loader = typename std::conditional<HALF_IN, FastLoaderH, FastLoader>::type;
+      Loader ld;
+      typename Loader::Unit x[Loader::BATCH];
       const uint32_t A0w = A0 + 2048u * warp;
       if (cluster < p.T) {
         ld.open(p, (int64_t)cluster * PAIR + rank * TILE + warp * ROWS, lane);
@@ -416,8 +431,8 @@ segsum_tc_kernel(const TcParams p) {
         if (lane == 0) prefetch(t + 3 * n_clusters);
         if (it > 0) ptx::mbar_wait_role(bar(B_A0_EMPTY), (it - 1) & 1, warp == 0, 1, 32 * LOAD_WARPS);   // layer 0 of the previous tile has read A0
         uint32_t nz = ld.commit(0, lane, x, A0w, a0_tab);
-        ld.issue(FAST_BATCH, lane, x);
-        nz |= ld.commit(FAST_BATCH, lane, x, A0w, a0_tab);
+        ld.issue(Loader::BATCH, lane, x);
+        nz |= ld.commit(Loader::BATCH, lane, x, A0w, a0_tab);
         publish(t, __reduce_or_sync(0xffffffffu, nz));
         if (t + n_clusters < p.T) {                                     // batch 0 of the next tile rides in registers
           ld.open(p, (int64_t)(t + n_clusters) * PAIR + rank * TILE + warp * ROWS, lane);

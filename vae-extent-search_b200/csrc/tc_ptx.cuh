@@ -241,6 +241,12 @@ __device__ __forceinline__ uint2 ldg_stream_u2(const void* p) {
   asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0, %1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
   return r;
 }
+__device__ __forceinline__ uint4 ldg_stream_u4(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
 // 256-bit accesses: one full 32 B sector per lane (a lane-per-row access pattern then moves only useful bytes
 // and needs half the LSU wavefronts of 128-bit accesses).  32-byte aligned addresses.
 struct F8 { float v[8]; };
