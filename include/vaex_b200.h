@@ -137,7 +137,7 @@ int vaex_segsum_mlp_predict_host(vaex_model_t h, const float* feats_host, const 
  * fp16(clamp(feats_host[i], +-65504)), round to nearest even = cvt.rn.satfinite.f16.f32.  *lossy_zero_or_null = 1 when
  * some non-zero input became a zero.  Host only (AVX2 + F16C). */
 int vaex_pack_features_f16(const float* feats_host, uint16_t* out_host, int64_t count, int32_t* lossy_zero_or_null);
-/* counters of a handle: which = 0 chunks vaex_segsum_mlp_predict_host sent narrowed to fp16, 1 = sent as fp32
+/* counters of a handle: which = 0 chunks vaex_segsum_mlp_predict_host / _blob sent narrowed to fp16, 1 = sent as fp32
  * (only calls large enough to start the narrowing threads count) */
 int vaex_model_get_counter(vaex_model_t h, int which, int64_t* value);
 
@@ -154,7 +154,9 @@ int vaex_feature_blob_unpack(const void* blob_host, int64_t nbytes, int32_t vec_
 /* MLPModel.predict from the bytes TVM's GetPerStoreFeaturesFromStates returns (mlp_model.py:832-846 with
  * feature.py:224-246): parse -> pinned staging -> chunked H2D overlapped with the kernels -> scores_host
  * [records].  The model's input width must equal the blob's vec_len (a constant task embedding is folded into
- * the first bias by the caller).  Synchronous. */
+ * the first bias by the caller).  Above 64 MiB of rows the staging pass also narrows the rows to fp16 on the host
+ * cores (same rule and same bits as vaex_segsum_mlp_predict_host; VAEX_F_NO_HOST_PACK keeps fp32 staging; counted
+ * by vaex_model_get_counter).  Synchronous. */
 int vaex_segsum_mlp_predict_blob(vaex_model_t h, const void* blob_host, int64_t nbytes, float* scores_host,
                                  int64_t n_scores, int flags);
 

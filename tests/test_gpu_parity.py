@@ -587,6 +587,51 @@ def test_predict_blob_and_embedding_fold():
         check_scores(simt[~invalid], want[~invalid], _lib.F_FORCE_SIMT)
 
 
+def test_predict_blob_narrowing_feeders():
+    """n1 on the 5.1 feeders: a blob above 64 MiB of rows is narrowed to fp16 by the worker threads while it is staged
+    (records are the unit of work, failed records become one zero row); the scores equal the fp32 host path bit for
+    bit, the chunk that holds a value too small for fp16 travels as fp32, and the handle's counters show both."""
+    from oracle import feature_blob as FB
+    from vaex_b200 import feature
+    rng = np.random.default_rng(77)
+    n = 9000
+    feats = []
+    for i in range(n):
+        if i % 211 == 0:
+            feats.append(None)
+        elif i % 307 == 0:
+            feats.append(np.zeros((3, 164), np.float32))
+        else:
+            f = (rng.random((int(rng.integers(1, 33)), 164)) * 24).astype(np.float32)
+            f[:, rng.random(164) < 0.2] = 0
+            feats.append(f)
+    feats[4000][0, 5] = 1e-9          # rounds to an fp16 zero: its chunk has to go as fp32
+    blob = FB.serialize_features(feats, rng.random(n), rng.integers(0, 3, n), rng.random(3))
+    flat, sizes, lowered, _, _, _ = feature.unpack_feature_flat(blob)
+    assert flat.nbytes >= 64 << 20
+    invalid = np.array([f is None or not f.any() for f in feats])
+    torch.manual_seed(5)
+    m = vaex_b200.MLPModelInternal(device="cuda:0", use_workload_embedding=False)
+    m.base_model = vaex_b200.SegmentSumMLPModule(164, 256, 1).cuda()
+    m.fea_norm_vec = torch.from_numpy(np.maximum(flat.max(0), 1e-3).astype(np.float32))
+    task = vaex_b200.LearningTask("k", "cuda")
+    handle = m.base_model.packed(m.fea_norm_vec, None)
+    before = handle.counter(0), handle.counter(1)
+    got = m.predict_blob(task, blob)
+    narrowed, raw = handle.counter(0) - before[0], handle.counter(1) - before[1]
+    assert narrowed >= 5 and 1 <= raw <= 2, (narrowed, raw)          # record 4482 happens to hold a 6.8e-9 of its own
+    assert np.array_equal(np.isneginf(got), invalid)
+    want = m.predict_blob(task, blob, flags=_lib.F_MASK_INVALID | _lib.F_NO_HOST_PACK)     # fp32 staging path
+    assert (handle.counter(0) - before[0], handle.counter(1) - before[1]) == (narrowed, raw)
+    assert np.array_equal(got, want)
+    objs, _, _, _ = feature.unpack_feature(blob)
+    # the flatten path plans one 128 MiB chunk: a program cut at another tile boundary is summed in another order, and
+    # a last-bit change of a segment sum can flip its fp16 rounding in the head -> the tensor-core tolerance applies
+    via = m._predict_a_task(m.base_model, task, objs, flags=_lib.F_MASK_INVALID | _lib.F_NO_HOST_PACK)
+    assert np.array_equal(np.isneginf(via), invalid)
+    check_scores(got[~invalid], via[~invalid], 0)
+
+
 def test_kcenter_select_matches_reference():
     """n2: vaex_kcenter_select against the reference's select_topk_latent_diversity picks (tests/golden/kcenter.npz),
     through the C ABI with the reference's candidate order and through the Python mirror with sets; then

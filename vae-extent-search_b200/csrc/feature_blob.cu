@@ -13,6 +13,9 @@
 // floats) into pinned memory -- the pageable -> pinned copy an H2D needs anyway -- and the chunks go to the GPU
 // while the next one is being parsed.  Host code only; no kernel in this file.
 #include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <cstdlib>
 #include <cstring>
 #include <thread>
 #include <vector>
@@ -149,6 +152,151 @@ int vaex_feature_blob_unpack(const void* blob, int64_t nbytes, int32_t vec_len, 
   return VAEX_OK;
 }
 
+// Chunk plan of both staging paths (one plan: a program cut by a 256-row tile boundary is summed in two pieces, so
+// the last bit of a score depends on where its chunk starts).  Up to 64 MiB of rows: one chunk, like
+// vaex_segsum_mlp_predict_host; above: <= 128 MiB per chunk and at least ~8 chunks so that staging, copy and kernels overlap.
+static int64_t blob_chunk_rows(const BlobIndex& ix, int F) {
+  const int64_t row_bytes = F * (int64_t)sizeof(float), total = ix.rows * row_bytes;
+  const int64_t chunk = total < (64ll << 20) ? (128ll << 20) : std::min<int64_t>(128ll << 20, std::max<int64_t>(8ll << 20, total / 8));
+  return std::max<int64_t>(1, chunk / row_bytes);
+}
+
+// Narrowing feeders for the blob: T worker threads turn the records of chunk 0, 1, 2, ... into fp16 rows in a ring of
+// pinned buffers (each thread an equal share of the chunk's rows: records are the unit, found by bisection of the
+// row prefix), the calling thread ships every chunk as soon as all T shares are in.  A chunk in which a non-zero
+// value would round to an fp16 zero (|x| <= 2^-25; it would flip the "all-zero program" rule) goes the fp32 way.
+static bool copy_done(cudaEvent_t e) {
+  if (cudaEventQuery(e) == cudaSuccess) return true;
+  (void)cudaGetLastError();   // cudaErrorNotReady is not an error of ours
+  return false;
+}
+
+static int predict_blob_narrowed(vaex_model_t h, const uint8_t* b, const BlobIndex& ix, float* scores_host, int flags, int T) {
+  const int F = h->F;
+  const int64_t max_rows = blob_chunk_rows(ix, F);
+  std::vector<int64_t> rs((size_t)ix.n + 1);           // rows before record i
+  rs[0] = 0;
+  for (int64_t i = 0; i < ix.n; ++i) rs[i + 1] = rs[i] + ix.nrows[i];
+  struct Chunk { int64_t p0, p1; };
+  std::vector<Chunk> chunks;
+  size_t slot_rows = 0;
+  for (int64_t p0 = 0; p0 < ix.n;) {
+    int64_t p1 = p0 + 1;
+    while (p1 < ix.n && rs[p1 + 1] - rs[p0] <= max_rows) ++p1;
+    chunks.push_back({p0, p1});
+    slot_rows = std::max<size_t>(slot_rows, (size_t)(rs[p1] - rs[p0]));
+    p0 = p1;
+  }
+  const int NC = (int)chunks.size();
+  constexpr int NS = 4;
+  const size_t need = std::max<size_t>(slot_rows, (size_t)max_rows) * F * sizeof(uint16_t);
+  for (int i = 0; i < NS; ++i) {
+    vaex_model::PinnedSlot& pn = h->pack_stage[i];
+    if (pn.bytes < need) {
+      if (pn.p) cudaFreeHost(pn.p);
+      pn.p = nullptr; pn.bytes = 0;
+      VAEX_CUDA(cudaHostAlloc(&pn.p, need, cudaHostAllocDefault));
+      pn.bytes = need;
+    }
+    if (!h->pack_events[i]) VAEX_CUDA(cudaEventCreateWithFlags(&h->pack_events[i], cudaEventDisableTiming));
+  }
+  std::atomic<int> released{0};                        // chunk c may be narrowed once c < released + NS
+  std::atomic<bool> abort_flag{false};
+  std::vector<std::atomic<int>> done((size_t)NC), tiny((size_t)NC);
+  for (int c = 0; c < NC; ++c) { done[c].store(0); tiny[c].store(0); }
+  std::vector<std::thread> workers;
+  for (int t = 0; t < T; ++t)
+    workers.emplace_back([&, t] {
+      for (int c = 0; c < NC; ++c) {
+        while (c >= released.load(std::memory_order_acquire) + NS) {
+          if (abort_flag.load(std::memory_order_relaxed)) return;
+          std::this_thread::sleep_for(std::chrono::microseconds(20));
+        }
+        if (abort_flag.load(std::memory_order_relaxed)) return;
+        const Chunk& ck = chunks[c];
+        const int64_t r0 = rs[ck.p0], rows = rs[ck.p1] - r0;
+        auto cut = [&](int k) {                         // first record of share k
+          if (k >= T) return ck.p1;
+          return (int64_t)(std::lower_bound(rs.begin() + ck.p0, rs.begin() + ck.p1, r0 + rows * k / T) - rs.begin());
+        };
+        uint16_t* stage = static_cast<uint16_t*>(h->pack_stage[c % NS].p);
+        bool lossy = false;
+        for (int64_t i = cut(t), z = cut(t + 1); i < z; ++i) {
+          uint16_t* d = stage + (size_t)(rs[i] - r0) * F;
+          if (ix.src[i] < 0) std::memset(d, 0, (size_t)F * sizeof(uint16_t));
+          else lossy |= host_pack_f16(reinterpret_cast<const float*>(b) + ix.src[i], d, (size_t)ix.nrows[i] * F);
+        }
+        if (lossy) tiny[c].store(1, std::memory_order_relaxed);
+        done[c].fetch_add(1, std::memory_order_release);
+      }
+    });
+  auto stop_workers = [&] {
+    abort_flag.store(true);
+    for (auto& w : workers) w.join();
+    workers.clear();
+  };
+  struct Joiner { decltype(stop_workers)& f; ~Joiner() { f(); } } joiner{stop_workers};   // every early return joins
+
+  std::vector<int32_t> off_host[2];
+  std::vector<int64_t> row_start;
+  int rel = 0;
+  for (int c = 0; c < NC; ++c) {
+    const int s = c & 1;
+    cudaStream_t st = h->copy_streams[s];
+    VAEX_CUDA(cudaStreamSynchronize(st));   // device slot s (chunk c-2) retired, incl. its D2H and its fp32 staging
+    for (;;) {
+      while (rel < c && copy_done(h->pack_events[rel % NS])) ++rel;   // ring slots whose copy is over
+      released.store(rel, std::memory_order_release);
+      if (done[c].load(std::memory_order_acquire) == T) break;
+      std::this_thread::sleep_for(std::chrono::microseconds(20));
+    }
+    const Chunk& ck = chunks[c];
+    const int64_t np = ck.p1 - ck.p0, r0 = rs[ck.p0], rows = rs[ck.p1] - r0;
+    const bool f16 = tiny[c].load(std::memory_order_relaxed) == 0;
+    off_host[s].resize((size_t)np + 1);
+    for (int64_t i = 0; i <= np; ++i) off_host[s][i] = (int32_t)(rs[ck.p0 + i] - r0);
+    vaex_model::HostSlot& sl = h->slots[s];
+    if ((size_t)rows > sl.rows) {
+      if (sl.feats) cudaFree(sl.feats);
+      sl.rows = std::max<size_t>(rows, max_rows);
+      VAEX_CUDA(cudaMalloc(&sl.feats, sl.rows * F * sizeof(float)));
+    }
+    if ((size_t)np > sl.progs) {
+      if (sl.off) cudaFree(sl.off);
+      if (sl.scores) cudaFree(sl.scores);
+      sl.progs = std::max<size_t>(np, max_rows);
+      VAEX_CUDA(cudaMalloc(&sl.off, (sl.progs + 1) * sizeof(int32_t)));
+      VAEX_CUDA(cudaMalloc(&sl.scores, sl.progs * sizeof(float)));
+    }
+    if (f16) {
+      VAEX_CUDA(cudaMemcpyAsync(sl.feats, h->pack_stage[c % NS].p, (size_t)rows * F * sizeof(uint16_t), cudaMemcpyHostToDevice, st));
+    } else {
+      vaex_model::PinnedSlot& pn = h->pinned[s];
+      const size_t bytes = (size_t)rows * F * sizeof(float);
+      if (bytes > pn.bytes) {
+        if (pn.p) cudaFreeHost(pn.p);
+        pn.p = nullptr; pn.bytes = 0;
+        VAEX_CUDA(cudaHostAlloc(&pn.p, bytes, cudaHostAllocDefault));
+        pn.bytes = bytes;
+      }
+      row_start.resize((size_t)np);
+      for (int64_t i = 0; i < np; ++i) row_start[i] = rs[ck.p0 + i] - r0;
+      blob_copy(b, ix, ck.p0, ck.p1, F, static_cast<float*>(pn.p), row_start);
+      VAEX_CUDA(cudaMemcpyAsync(sl.feats, pn.p, bytes, cudaMemcpyHostToDevice, st));
+    }
+    VAEX_CUDA(cudaEventRecord(h->pack_events[c % NS], st));   // ring slot c % NS is free once this copy is over
+    VAEX_CUDA(cudaMemcpyAsync(sl.off, off_host[s].data(), (size_t)(np + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    if (c > 0) VAEX_CUDA(cudaStreamWaitEvent(st, h->events[(c - 1) & 1], 0));   // the model's workspaces are shared
+    TRY(vaex_segsum_mlp_forward(h, sl.feats, sl.off, np, rows, sl.scores, flags | (f16 ? VAEX_F_FEATS_F16 : 0), st));
+    VAEX_CUDA(cudaEventRecord(h->events[c & 1], st));
+    VAEX_CUDA(cudaMemcpyAsync(scores_host + ck.p0, sl.scores, (size_t)np * sizeof(float), cudaMemcpyDeviceToHost, st));
+    h->pack_stats[f16 ? 0 : 1] += 1;
+  }
+  VAEX_CUDA(cudaStreamSynchronize(h->copy_streams[0]));
+  VAEX_CUDA(cudaStreamSynchronize(h->copy_streams[1]));
+  return VAEX_OK;
+}
+
 int vaex_segsum_mlp_predict_blob(vaex_model_t h, const void* blob, int64_t nbytes, float* scores_host,
                                  int64_t n_scores, int flags) {
   VAEX_CHECK(h && h->kind == VAEX_KIND_SEGSUM_MLP && h->packed, "bad handle");
@@ -159,9 +307,18 @@ int vaex_segsum_mlp_predict_blob(vaex_model_t h, const void* blob, int64_t nbyte
   if (ix.n == 0) return VAEX_OK;
   VAEX_CHECK(scores_host, "null scores");
   const uint8_t* b = static_cast<const uint8_t*>(blob);
-  const int64_t max_rows = std::max<int64_t>(1, (64ll << 20) / (F * (int64_t)sizeof(float)));
+  const int64_t max_rows = blob_chunk_rows(ix, F);
   for (int i = 0; i < 2; ++i) if (!h->copy_streams[i]) VAEX_CUDA(cudaStreamCreateWithFlags(&h->copy_streams[i], cudaStreamNonBlocking));
   for (int i = 0; i < 4; ++i) if (!h->events[i]) VAEX_CUDA(cudaEventCreateWithFlags(&h->events[i], cudaEventDisableTiming));
+  {
+    // big blobs on a host with spare AVX2/F16C cores: narrow to fp16 while staging (same rule as vaex_segsum_mlp_predict_host)
+    const int hw = (int)std::thread::hardware_concurrency();
+    int T = std::max(1, std::min(hw - 1, 32));
+    if (const char* e = getenv("VAEX_PACK_THREADS")) if (atoi(e) > 0) T = std::min(atoi(e), 64);
+    const bool pack = !(flags & (VAEX_F_FORCE_SIMT | VAEX_F_NO_HOST_PACK | VAEX_F_FEATS_F16)) && h->tc.ready && F % 4 == 0 &&
+                      hw >= 4 && ix.rows * F * (int64_t)sizeof(float) >= (64ll << 20) && host_pack_supported();
+    if (pack) return predict_blob_narrowed(h, b, ix, scores_host, flags, T);
+  }
   std::vector<int64_t> row_start;
   int64_t p0 = 0;
   int it = 0;
