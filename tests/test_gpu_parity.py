@@ -399,6 +399,23 @@ def test_snap_bit_exact_and_legalise():
         _lib.check(_lib.load().vaex_legalise_extents(_lib.ptr(t), n, d, _lib.ptr(e2d), _lib.ptr(l2d), None, 0, 64, None))
         torch.cuda.synchronize()
         assert np.array_equal(t.cpu().numpy(), O.legalise_divisor(raw, e2, l2)), (n, d)
+    # large loop bounds: the float-quotient divisibility test (remaining extent < 2^21) and the integer-modulo path
+    # above it, on primes, highly composite numbers and powers of two, targets spread over the whole range
+    big = [2097143, 2097151, 2097152, 1441440, 720720, 1048576, 999983, 2162160, 3000000, 16777259, 1 << 24]
+    e3 = [b for b in big for _ in range(3)] + [0] * 3
+    l3 = [0, 0, 1] * len(big) + [0] * 3
+    d3 = len(e3)
+    raw = np.empty((2000, d3), np.int32)
+    for j, b in enumerate(e3):
+        hi = max(b, 2)
+        col = rng.integers(1, hi + 2, size=2000)
+        col[::3] = rng.integers(1, 3000, size=len(col[::3]))          # also small targets (near the 64 cap of the last slot)
+        raw[:, j] = col
+    t = torch.from_numpy(raw).cuda()
+    e3d, l3d = torch.tensor(e3, dtype=torch.int32).cuda(), torch.tensor(l3, dtype=torch.uint8).cuda()
+    _lib.check(_lib.load().vaex_legalise_extents(_lib.ptr(t), 2000, d3, _lib.ptr(e3d), _lib.ptr(l3d), None, 0, 64, None))
+    torch.cuda.synchronize()
+    assert np.array_equal(t.cpu().numpy(), O.legalise_divisor(raw, e3, l3))
 
 
 def test_topk_vs_oracle():
