@@ -416,6 +416,29 @@ def test_snap_bit_exact_and_legalise():
     _lib.check(_lib.load().vaex_legalise_extents(_lib.ptr(t), 2000, d3, _lib.ptr(e3d), _lib.ptr(l3d), None, 0, 64, None))
     torch.cuda.synchronize()
     assert np.array_equal(t.cpu().numpy(), O.legalise_divisor(raw, e3, l3))
+    # enough rows for the persistent CTAs to build their shared-memory answer tables (extents <= 255; 240 and 180 together
+    # exceed the table space, so one of them keeps the search): the same rows in slices short enough to stay on the
+    # search path (which the oracle pins above) must give the same extents, and the head of them is checked directly
+    small = [1, 3, 4, 28, 56, 57, 64, 128, 240, 180, 255, 251, 960]
+    e4, l4 = [], []
+    for b in small:
+        e4 += [b] * 3
+        l4 += [0, 0, 1]
+    e4, l4 = e4 + [0] * 3, l4 + [0] * 3
+    d4, n4 = len(e4), 330_000
+    raw = rng.integers(-3, 300, size=(n4, d4)).astype(np.int32)
+    e4d, l4d = torch.tensor(e4, dtype=torch.int32).cuda(), torch.tensor(l4, dtype=torch.uint8).cuda()
+    whole = torch.from_numpy(raw).cuda()
+    _lib.check(_lib.load().vaex_legalise_extents(_lib.ptr(whole), n4, d4, _lib.ptr(e4d), _lib.ptr(l4d), None, 0, 64, None))
+    parts = []
+    for r0 in range(0, n4, 50_000):
+        part = torch.from_numpy(raw[r0:r0 + 50_000]).cuda()
+        _lib.check(_lib.load().vaex_legalise_extents(_lib.ptr(part), part.shape[0], d4, _lib.ptr(e4d), _lib.ptr(l4d), None, 0, 64, None))
+        parts.append(part)
+    torch.cuda.synchronize()
+    assert torch.equal(whole, torch.cat(parts))
+    assert np.array_equal(whole[:600].cpu().numpy(), O.legalise_divisor(raw[:600], e4, l4))
+    assert np.array_equal(whole[-300:].cpu().numpy(), O.legalise_divisor(raw[-300:], e4, l4))
 
 
 def test_topk_vs_oracle():

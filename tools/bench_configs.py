@@ -64,6 +64,14 @@ def config1_and_5(out):
         ms = timed(lambda: score_pipeline(vae, reg, z, mean_d, scale_d, ext_d, last_d, k), iters)
         rec = {"config": name, "latents": n, "topk": k, "ms": ms, "latents_per_s": n / ms * 1e3,
                "pipeline": "decode (tcgen05 chain) + snap + divisor legalise -> predict_cost (tcgen05 chain) -> top-k"}
+        if name == "config5":      # where the time goes (each stage timed alone, back to back launches)
+            cost5 = reg.predict_cost(z)
+            rec["stages_ms"] = {
+                "decode+snap": round(timed(lambda: vae.decode_snap(z, mean_d, scale_d), iters), 4),
+                "decode+snap+legalise": round(timed(lambda: vae.decode_snap(z, mean_d, scale_d, slot_extent=ext_d, slot_last=last_d), iters), 4),
+                "predict_cost": round(timed(lambda: reg.predict_cost(z), iters), 4),
+                "top-k": round(timed(lambda: vaex_b200.topk(cost5, k, sync=False), iters), 4),
+            }
         if name == "config1":
             from oracle import torch_oracle as O
             Pv = {k_: v.detach().cpu() for k_, v in vae.state_dict().items()}

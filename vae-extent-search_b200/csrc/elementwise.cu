@@ -1,5 +1,7 @@
 // Bandwidth-bound helpers: scan, reparameterisation, integer snap / legalise, dropout,
 // ReLU-mask products for the fused backward, z update.
+#include <algorithm>
+
 #include "common.cuh"
 #include "simt_kernels.cuh"
 #include "snap.cuh"
@@ -213,50 +215,188 @@ __global__ void legalise_kernel(int32_t* __restrict__ ext, int64_t n, int d,
 // Same walk with the rows staged through shared memory: a thread per row reads d consecutive ints (192 B apart from its
 // neighbour's for d = 48), which costs a full sector per element; here a CTA copies its 128 rows in and out with
 // coalesced 4-byte accesses and the walk runs on a padded (d + 1) tile without bank conflicts.  Used for d <= 64.
+//
+// Answer tables for small loop extents.  Every remaining extent of a split divides the loop extent E of its slots, so for
+// E <= 255 the whole function (remaining extent r | E, target v) -> nearest divisor fits a byte table of
+// ndiv(E) * (E + 1) entries (twice: with and without the innermost cap).  Each persistent CTA builds the tables of its
+// distinct extents once in shared memory (one thread per table row: a forward pass leaves the largest divisor <= v, a
+// backward pass compares it with the smallest one >= v; ties -> smaller, like the +-1 search) and a slot then costs two
+// byte loads and a float quotient instead of a data-dependent search and an integer division -- GetFactors memoises
+// per extent on the host for the same reason (utils.cc:446-463).  Larger extents, and whatever does not fit LEG_LUT
+// bytes, keep the +-1 search.  (Tried: sorted divisor lists + bisection for every extent -- slower than the +-1 search
+// on task-1264-like bounds, 0.78 vs 0.53 ms per 2 M rows.)
 constexpr int LEG_ROWS = 128;
+constexpr int LEG_LUT = 12 * 1024;             // bytes of answer tables per CTA
+constexpr int LEG_LUT_MAX_E = 255;
+
 __global__ void __launch_bounds__(LEG_ROWS) legalise_tiled_kernel(int32_t* __restrict__ ext, int64_t n, int d,
                                                                   const int32_t* __restrict__ slot_extent,
                                                                   const uint8_t* __restrict__ slot_last, int max_innermost,
-                                                                  const int32_t* __restrict__ order, int n_order) {
-  extern __shared__ int32_t tile[];            // [LEG_ROWS][d + 1], then slot_extent[d], slot_last[d] (as int), order[steps]
+                                                                  const int32_t* __restrict__ order, int n_order, int use_lut) {
+  extern __shared__ int32_t tile[];            // [LEG_ROWS][d + 1], se[d], sl[d], so[steps], nd[d], t0[d], ridx[d], rows[d], lut bytes
   const int ds = d + 1;
+  const int steps = order ? n_order : d;
   int32_t* se = tile + LEG_ROWS * ds;
   int32_t* sl = se + d;
   int32_t* so = sl + d;
-  const int steps = order ? n_order : d;
-  const int64_t r0 = (int64_t)blockIdx.x * LEG_ROWS;
-  const int rows = (int)min((int64_t)LEG_ROWS, n - r0);
-  for (int j = threadIdx.x; j < d; j += LEG_ROWS) { se[j] = slot_extent[j]; sl[j] = slot_last[j]; }
-  for (int j = threadIdx.x; j < steps; j += LEG_ROWS) so[j] = order ? order[j] : j;
-  int32_t* g = ext + r0 * d;
-  for (int e = threadIdx.x; e < rows * d; e += LEG_ROWS) tile[(e / d) * ds + e % d] = g[e];
+  int32_t* nd = so + steps;                    // owner slots: number of divisors (sharers: minus that); no table: 0
+  int32_t* t0 = nd + d;                        // first task (table row) of an owner slot
+  int32_t* ridx = t0 + d;                      // byte offset of the extent's divisor-index map [E + 1], -1: no table
+  int32_t* rows = ridx + d;                    // byte offset of its answer rows: [2][ndiv][E + 1]
+  uint8_t* lut = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(rows + d) + 15) & ~uintptr_t(15));
+  __shared__ int n_tasks;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  for (int j = tid; j < d; j += LEG_ROWS) { se[j] = slot_extent[j]; sl[j] = slot_last[j]; nd[j] = 0; ridx[j] = -1; }
+  for (int j = tid; j < steps; j += LEG_ROWS) so[j] = order ? order[j] : j;
+  if (tid == 0) n_tasks = 0;
   __syncthreads();
-  if (threadIdx.x < rows) {
-    int32_t* row = tile + threadIdx.x * ds;
-    int rem = 0;
-    for (int jj = 0; jj < steps; ++jj) {
-      const int j = so[jj];
-      const int sext = se[j];
-      if (sext <= 0) { rem = 0; continue; }
-      if (rem == 0) rem = sext;
-      const int last = sl[j];
-      const int q = nearest_divisor(rem, row[j], last ? max_innermost : 0);
-      row[j] = q;
-      rem /= q;
-      if (last) rem = 0;
+  if (use_lut) {
+    // divisors of every distinct small extent (slot j owns its extent if no earlier slot has it): a warp per owner
+    for (int j = warp; j < d; j += LEG_ROWS / 32) {
+      const int E = se[j];
+      bool owner = E > 0 && E <= LEG_LUT_MAX_E;
+      for (int i = 0; i < j && owner; ++i) owner = se[i] != E;
+      if (!owner) continue;
+      int cnt = 0;
+      for (int c0 = 1; c0 <= E; c0 += 32) cnt += __popc(__ballot_sync(0xffffffffu, c0 + lane <= E && E % (c0 + lane) == 0));
+      if (lane == 0) nd[j] = cnt;
     }
+    __syncthreads();
+    if (tid == 0) {
+      int bytes = 0, tasks = 0;
+      for (int j = 0; j < d; ++j) {
+        if (nd[j] == 0) continue;
+        const int E = se[j], head = (E + 1 + 3) & ~3, need = head + 2 * nd[j] * (E + 1);
+        if (bytes + need > LEG_LUT) { nd[j] = 0; continue; }
+        ridx[j] = bytes;
+        rows[j] = bytes + head;
+        t0[j] = tasks;
+        bytes = (bytes + need + 3) & ~3;
+        tasks += 2 * nd[j];
+      }
+      n_tasks = tasks;
+      for (int j = 0; j < d; ++j)              // the other slots of an extent share its owner's tables
+        if (se[j] > 0 && nd[j] == 0)
+          for (int i = 0; i < j; ++i)
+            if (se[i] == se[j] && nd[i] > 0) { ridx[j] = ridx[i]; rows[j] = rows[i]; nd[j] = -nd[i]; break; }
+    }
+    __syncthreads();
+    // one table row per task: owner slot j, variant (capped or not), i-th divisor r of E
+    for (int task = tid; task < n_tasks; task += LEG_ROWS) {
+      int j = 0;
+      while (!(nd[j] > 0 && task >= t0[j] && task < t0[j] + 2 * nd[j])) ++j;
+      const int E = se[j], ndiv = nd[j], k = task - t0[j], capped = k >= ndiv, i = capped ? k - ndiv : k;
+      int r = 0;
+      for (int c = 1, seen = 0; c <= E; ++c)
+        if (divides_small(E, (float)E, c, (float)c) && seen++ == i) { r = c; break; }
+      if (!capped) lut[ridx[j] + r] = (uint8_t)i;
+      uint8_t* trow = lut + rows[j] + k * (E + 1);
+      const int bound = (capped && max_innermost > 0 && max_innermost < r) ? max_innermost : r;
+      const float rf = (float)r;
+      int down = 1;
+      for (int v = 1; v <= bound; ++v) {       // largest divisor <= v
+        if (divides_small(r, rf, v, (float)v)) down = v;
+        trow[v] = (uint8_t)down;
+      }
+      int up = 0;
+      for (int v = bound; v >= 1; --v) {       // smallest divisor in [v, bound]; ties -> smaller
+        if (divides_small(r, rf, v, (float)v)) up = v;
+        const int dn = trow[v];
+        if (up != 0 && up - v < v - dn) trow[v] = (uint8_t)up;
+      }
+    }
+    __syncthreads();
+  }
+  // one 16-byte record per walk step: {slot | last << 8, extent, byte offset of the divisor-index map (-1: search),
+  // byte offset of the answer rows of this slot's variant}
+  int4* stp = reinterpret_cast<int4*>(lut + LEG_LUT);
+  for (int jj = tid; jj < steps; jj += LEG_ROWS) {
+    const int j = so[jj], E = se[j], last = sl[j] ? 1 : 0, ndiv = nd[j] < 0 ? -nd[j] : nd[j];
+    stp[jj] = make_int4(j | (last << 8), E, ridx[j], ridx[j] >= 0 ? rows[j] + (last ? ndiv * (E + 1) : 0) : 0);
   }
   __syncthreads();
-  for (int e = threadIdx.x; e < rows * d; e += LEG_ROWS) g[e] = tile[(e / d) * ds + e % d];
+  const int64_t n_tiles = (n + LEG_ROWS - 1) / LEG_ROWS;
+  const bool vec4 = d % 4 == 0 && (reinterpret_cast<uintptr_t>(ext) & 15) == 0;   // a tile starts 128 * d * 4 bytes further: aligned too
+  const int dq = vec4 ? d / 4 : d;             // units per row (int4 or int)
+  const int r_first = tid / dq, c_first = tid % dq, r_step = LEG_ROWS / dq, c_step = LEG_ROWS % dq;
+  for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+    const int64_t r0 = t * LEG_ROWS;
+    const int nrows = (int)min((int64_t)LEG_ROWS, n - r0);
+    int32_t* g = ext + r0 * d;
+    // (row, column) of element tid + 128 k kept incrementally: a division by the run-time d per element costs more than the walk
+    if (vec4) {
+      const int4* g4 = reinterpret_cast<const int4*>(g);
+      for (int e = tid, r = r_first, c = c_first; e < nrows * dq; e += LEG_ROWS) {
+        const int4 x = g4[e];
+        int32_t* w = tile + r * ds + 4 * c;
+        w[0] = x.x; w[1] = x.y; w[2] = x.z; w[3] = x.w;
+        r += r_step; c += c_step;
+        if (c >= dq) { c -= dq; ++r; }
+      }
+    } else {
+      for (int e = tid, r = r_first, c = c_first; e < nrows * d; e += LEG_ROWS) {
+        tile[r * ds + c] = g[e];
+        r += r_step; c += c_step;
+        if (c >= dq) { c -= dq; ++r; }
+      }
+    }
+    __syncthreads();
+    if (tid < nrows) {
+      int32_t* row = tile + tid * ds;
+      int rem = 0;
+      for (int jj = 0; jj < steps; ++jj) {
+        const int4 sp = stp[jj];
+        const int j = sp.x & 255, last = sp.x >> 8, sext = sp.y;
+        if (sext <= 0) { rem = 0; continue; }
+        if (rem == 0) rem = sext;
+        const int cap = last ? max_innermost : 0;
+        int q;
+        if (sp.z >= 0) {
+          const int bound = (cap > 0 && cap < rem) ? cap : rem;
+          const int v = min(max(row[j], 1), bound);
+          q = lut[sp.w + lut[sp.z + rem] * (sext + 1) + v];
+          rem = __float2int_rn(__fdividef((float)rem, (float)q));   // exact: q | rem, both <= 255
+        } else {
+          q = nearest_divisor(rem, row[j], cap);
+          rem /= q;
+        }
+        row[j] = q;
+        if (last) rem = 0;
+      }
+    }
+    __syncthreads();
+    if (vec4) {
+      int4* g4 = reinterpret_cast<int4*>(g);
+      for (int e = tid, r = r_first, c = c_first; e < nrows * dq; e += LEG_ROWS) {
+        const int32_t* w = tile + r * ds + 4 * c;
+        g4[e] = make_int4(w[0], w[1], w[2], w[3]);
+        r += r_step; c += c_step;
+        if (c >= dq) { c -= dq; ++r; }
+      }
+    } else {
+      for (int e = tid, r = r_first, c = c_first; e < nrows * d; e += LEG_ROWS) {
+        g[e] = tile[r * ds + c];
+        r += r_step; c += c_step;
+        if (c >= dq) { c -= dq; ++r; }
+      }
+    }
+    __syncthreads();
+  }
 }
 
 int legalise_extents(int32_t* ext, int64_t n, int d, const int32_t* slot_extent, const uint8_t* slot_last, int max_innermost,
                      cudaStream_t st, const int32_t* order, int n_order) {
   if (n == 0) return VAEX_OK;
   if (d <= 64) {
-    const size_t sh = sizeof(int32_t) * ((size_t)LEG_ROWS * (d + 1) + 3 * (size_t)d);
-    legalise_tiled_kernel<<<(unsigned)cdiv(n, LEG_ROWS), LEG_ROWS, sh, st>>>(ext, n, d, slot_extent, slot_last, max_innermost, order,
-                                                                             n_order);
+    const int steps = order ? n_order : d;
+    const size_t sh = sizeof(int32_t) * ((size_t)LEG_ROWS * (d + 1) + 6 * (size_t)d + (size_t)steps + 4) + LEG_LUT + 16 * (size_t)steps;
+    static int sms = 0;
+    if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
+    const int64_t tiles = cdiv(n, LEG_ROWS);
+    const unsigned grid = (unsigned)std::min<int64_t>(tiles, (int64_t)std::max(sms, 1) * 5);
+    // the tables cost a CTA about as much as walking one tile: worth it from a few tiles per CTA on
+    legalise_tiled_kernel<<<grid, LEG_ROWS, sh, st>>>(ext, n, d, slot_extent, slot_last, max_innermost, order, n_order,
+                                                      tiles >= 3 * (int64_t)grid ? 1 : 0);
   } else {
     legalise_kernel<<<(unsigned)cdiv(n, 128), 128, 0, st>>>(ext, n, d, slot_extent, slot_last, max_innermost, order, n_order);
   }
