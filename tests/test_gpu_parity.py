@@ -439,6 +439,14 @@ def test_snap_bit_exact_and_legalise():
     assert torch.equal(whole, torch.cat(parts))
     assert np.array_equal(whole[:600].cpu().numpy(), O.legalise_divisor(raw[:600], e4, l4))
     assert np.array_equal(whole[-300:].cpu().numpy(), O.legalise_divisor(raw[-300:], e4, l4))
+    # a split whose extent changes half way (no innermost mark in between): the remaining extent carries over
+    e5, l5 = [64, 64, 128, 128, 0, 56, 28, 28], [0, 0, 0, 1, 0, 0, 0, 1]
+    raw5 = rng.integers(1, 140, size=(n4, 8)).astype(np.int32)
+    t5 = torch.from_numpy(raw5).cuda()
+    e5d, l5d = torch.tensor(e5, dtype=torch.int32).cuda(), torch.tensor(l5, dtype=torch.uint8).cuda()
+    _lib.check(_lib.load().vaex_legalise_extents(_lib.ptr(t5), n4, 8, _lib.ptr(e5d), _lib.ptr(l5d), None, 0, 64, None))
+    torch.cuda.synchronize()
+    assert np.array_equal(t5[:500].cpu().numpy(), O.legalise_divisor(raw5[:500], e5, l5))
 
 
 def test_topk_vs_oracle():

@@ -229,11 +229,11 @@ constexpr int LEG_ROWS = 128;
 constexpr int LEG_LUT = 12 * 1024;             // bytes of answer tables per CTA
 constexpr int LEG_LUT_MAX_E = 255;
 
-__global__ void __launch_bounds__(LEG_ROWS) legalise_tiled_kernel(int32_t* __restrict__ ext, int64_t n, int d,
+__global__ void __launch_bounds__(LEG_ROWS, 5) legalise_tiled_kernel(int32_t* __restrict__ ext, int64_t n, int d,
                                                                   const int32_t* __restrict__ slot_extent,
                                                                   const uint8_t* __restrict__ slot_last, int max_innermost,
                                                                   const int32_t* __restrict__ order, int n_order, int use_lut) {
-  extern __shared__ int32_t tile[];            // [LEG_ROWS][d + 1], se[d], sl[d], so[steps], nd[d], t0[d], ridx[d], rows[d], lut bytes
+  extern __shared__ __align__(16) int32_t tile[];   // [LEG_ROWS][d + 1], se[d], sl[d], so[steps], nd[d], t0[d], ridx[d], rows[d], lut bytes, step records
   const int ds = d + 1;
   const int steps = order ? n_order : d;
   int32_t* se = tile + LEG_ROWS * ds;
@@ -243,7 +243,7 @@ __global__ void __launch_bounds__(LEG_ROWS) legalise_tiled_kernel(int32_t* __res
   int32_t* t0 = nd + d;                        // first task (table row) of an owner slot
   int32_t* ridx = t0 + d;                      // byte offset of the extent's divisor-index map [E + 1], -1: no table
   int32_t* rows = ridx + d;                    // byte offset of its answer rows: [2][ndiv][E + 1]
-  uint8_t* lut = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(rows + d) + 15) & ~uintptr_t(15));
+  uint8_t* lut = reinterpret_cast<uint8_t*>(tile + ((LEG_ROWS * ds + 6 * d + steps + 3) & ~3));   // 16-byte aligned, still a shared-space pointer
   __shared__ int n_tasks;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   for (int j = tid; j < d; j += LEG_ROWS) { se[j] = slot_extent[j]; sl[j] = slot_last[j]; nd[j] = 0; ridx[j] = -1; }
@@ -251,74 +251,126 @@ __global__ void __launch_bounds__(LEG_ROWS) legalise_tiled_kernel(int32_t* __res
   if (tid == 0) n_tasks = 0;
   __syncthreads();
   if (use_lut) {
-    // divisors of every distinct small extent (slot j owns its extent if no earlier slot has it): a warp per owner
-    for (int j = warp; j < d; j += LEG_ROWS / 32) {
+    // slot j's owner = the first slot with the same (small) extent; t0 holds it until the tables are laid out.  Serial
+    // scans of shared memory by one thread are what this prologue must avoid: ~30 clk per dependent load.
+    for (int j = tid; j < d; j += LEG_ROWS) {
       const int E = se[j];
-      bool owner = E > 0 && E <= LEG_LUT_MAX_E;
-      for (int i = 0; i < j && owner; ++i) owner = se[i] != E;
-      if (!owner) continue;
+      int o = -1;
+      if (E > 0 && E <= LEG_LUT_MAX_E) { o = 0; while (se[o] != E) ++o; }
+      t0[j] = o;
+    }
+    __syncthreads();
+    for (int j = warp; j < d; j += LEG_ROWS / 32) {      // a warp counts the divisors of an owner's extent
+      if (t0[j] != j) continue;
+      const int E = se[j];
       int cnt = 0;
       for (int c0 = 1; c0 <= E; c0 += 32) cnt += __popc(__ballot_sync(0xffffffffu, c0 + lane <= E && E % (c0 + lane) == 0));
       if (lane == 0) nd[j] = cnt;
     }
     __syncthreads();
+    int own = tid < d ? t0[tid] : -1;                    // (d <= 64 < LEG_ROWS)
+    __syncthreads();
     if (tid == 0) {
       int bytes = 0, tasks = 0;
       for (int j = 0; j < d; ++j) {
-        if (nd[j] == 0) continue;
-        const int E = se[j], head = (E + 1 + 3) & ~3, need = head + 2 * nd[j] * (E + 1);
+        const int cnt = nd[j];
+        if (cnt == 0) continue;
+        const int E = se[j], head = (E + 1 + 3) & ~3, need = head + 2 * cnt * (E + 1) * 2;
         if (bytes + need > LEG_LUT) { nd[j] = 0; continue; }
         ridx[j] = bytes;
         rows[j] = bytes + head;
         t0[j] = tasks;
         bytes = (bytes + need + 3) & ~3;
-        tasks += 2 * nd[j];
+        tasks += 2 * cnt;
       }
       n_tasks = tasks;
-      for (int j = 0; j < d; ++j)              // the other slots of an extent share its owner's tables
-        if (se[j] > 0 && nd[j] == 0)
-          for (int i = 0; i < j; ++i)
-            if (se[i] == se[j] && nd[i] > 0) { ridx[j] = ridx[i]; rows[j] = rows[i]; nd[j] = -nd[i]; break; }
     }
     __syncthreads();
-    // one table row per task: owner slot j, variant (capped or not), i-th divisor r of E
-    for (int task = tid; task < n_tasks; task += LEG_ROWS) {
-      int j = 0;
+    if (own >= 0 && own != tid && nd[own] > 0) {         // the other slots of an extent share its owner's tables
+      ridx[tid] = ridx[own];
+      rows[tid] = rows[own];
+      nd[tid] = -nd[own];
+    }
+    __syncthreads();
+    // one table row per task: owner slot j, variant (capped or not), i-th divisor r of E.  First the map divisor -> index,
+    // then the rows: entry (i, v) = nearest divisor q of r to v | index of r / q << 8, for every v in [1, E] (targets
+    // above the bound answer like the bound), so the walk carries the INDEX of the remaining extent and a slot is one
+    // 16-bit load whose address does not depend on anything but the previous slot's entry.
+    auto task_of = [&](int task, int& j, int& k, int& i, int& r) {
+      j = 0;
       while (!(nd[j] > 0 && task >= t0[j] && task < t0[j] + 2 * nd[j])) ++j;
-      const int E = se[j], ndiv = nd[j], k = task - t0[j], capped = k >= ndiv, i = capped ? k - ndiv : k;
-      int r = 0;
+      const int E = se[j];
+      k = task - t0[j];
+      i = k >= nd[j] ? k - nd[j] : k;
+      r = 0;
       for (int c = 1, seen = 0; c <= E; ++c)
         if (divides_small(E, (float)E, c, (float)c) && seen++ == i) { r = c; break; }
-      if (!capped) lut[ridx[j] + r] = (uint8_t)i;
-      uint8_t* trow = lut + rows[j] + k * (E + 1);
+    };
+    for (int task = tid; task < n_tasks; task += LEG_ROWS) {
+      int j, k, i, r;
+      task_of(task, j, k, i, r);
+      if (k < nd[j]) lut[ridx[j] + r] = (uint8_t)i;
+    }
+    __syncthreads();
+    for (int task = tid; task < n_tasks; task += LEG_ROWS) {
+      int j, k, i, r;
+      task_of(task, j, k, i, r);
+      const int E = se[j], capped = k >= nd[j];
+      uint16_t* trow = reinterpret_cast<uint16_t*>(lut + rows[j]) + k * (E + 1);
+      const uint8_t* index_of = lut + ridx[j];
       const int bound = (capped && max_innermost > 0 && max_innermost < r) ? max_innermost : r;
       const float rf = (float)r;
       int down = 1;
       for (int v = 1; v <= bound; ++v) {       // largest divisor <= v
         if (divides_small(r, rf, v, (float)v)) down = v;
-        trow[v] = (uint8_t)down;
+        trow[v] = (uint16_t)down;
       }
       int up = 0;
       for (int v = bound; v >= 1; --v) {       // smallest divisor in [v, bound]; ties -> smaller
         if (divides_small(r, rf, v, (float)v)) up = v;
         const int dn = trow[v];
-        if (up != 0 && up - v < v - dn) trow[v] = (uint8_t)up;
+        const int q = (up != 0 && up - v < v - dn) ? up : dn;
+        trow[v] = (uint16_t)(q | (index_of[__float2int_rn(__fdividef(rf, (float)q))] << 8));
       }
+      for (int v = bound + 1; v <= E; ++v) trow[v] = trow[bound];
     }
     __syncthreads();
   }
-  // one 16-byte record per walk step: {slot | last << 8, extent, byte offset of the divisor-index map (-1: search),
-  // byte offset of the answer rows of this slot's variant}
+  // one 16-byte record per walk step: {slot | last << 8, extent, uint16 offset of the answer rows of this slot's variant
+  // (-1: search), index of E among its divisors}
   int4* stp = reinterpret_cast<int4*>(lut + LEG_LUT);
+  const uint16_t* tab16 = reinterpret_cast<const uint16_t*>(lut);
   for (int jj = tid; jj < steps; jj += LEG_ROWS) {
     const int j = so[jj], E = se[j], last = sl[j] ? 1 : 0, ndiv = nd[j] < 0 ? -nd[j] : nd[j];
-    stp[jj] = make_int4(j | (last << 8), E, ridx[j], ridx[j] >= 0 ? rows[j] + (last ? ndiv * (E + 1) : 0) : 0);
+    stp[jj] = make_int4(j | (last << 8), E, ridx[j] >= 0 ? rows[j] / 2 + (last ? ndiv * (E + 1) : 0) : -1, ndiv - 1);
   }
   __syncthreads();
+  // slot tables in which a split changes its extent half way (no innermost mark in between) carry the remaining extent
+  // over; only the search reproduces that, so such tables switch the answer tables off
+  if (tid == 0 && n_tasks > 0) {
+    bool open = false, odd = false;
+    int prev = 0;
+    for (int jj = 0; jj < steps; ++jj) {
+      const int E = stp[jj].y;
+      if (E <= 0) { open = false; continue; }
+      if (open && E != prev) odd = true;
+      open = (stp[jj].x >> 8) == 0;
+      prev = E;
+    }
+    if (odd) n_tasks = -1;
+  }
+  __syncthreads();
+  if (n_tasks < 0) {
+    for (int jj = tid; jj < steps; jj += LEG_ROWS) stp[jj].z = -1;
+    __syncthreads();
+  }
   const int64_t n_tiles = (n + LEG_ROWS - 1) / LEG_ROWS;
   const bool vec4 = d % 4 == 0 && (reinterpret_cast<uintptr_t>(ext) & 15) == 0;   // a tile starts 128 * d * 4 bytes further: aligned too
   const int dq = vec4 ? d / 4 : d;             // units per row (int4 or int)
   const int r_first = tid / dq, c_first = tid % dq, r_step = LEG_ROWS / dq, c_step = LEG_ROWS % dq;
+  // int4 path: the 128 x d/4 units of a tile are d/4 (<= 16) per thread, moved four at a time (four loads in flight per
+  // thread); one thread asks L2 for the next tile before this one is walked.  (Holding the next tile in 64 registers
+  // instead made ptxas recompute the walk's loop invariants on every step: same time, more instructions.)
   for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
     const int64_t r0 = t * LEG_ROWS;
     const int nrows = (int)min((int64_t)LEG_ROWS, n - r0);
@@ -326,12 +378,27 @@ __global__ void __launch_bounds__(LEG_ROWS) legalise_tiled_kernel(int32_t* __res
     // (row, column) of element tid + 128 k kept incrementally: a division by the run-time d per element costs more than the walk
     if (vec4) {
       const int4* g4 = reinterpret_cast<const int4*>(g);
-      for (int e = tid, r = r_first, c = c_first; e < nrows * dq; e += LEG_ROWS) {
-        const int4 x = g4[e];
-        int32_t* w = tile + r * ds + 4 * c;
-        w[0] = x.x; w[1] = x.y; w[2] = x.z; w[3] = x.w;
-        r += r_step; c += c_step;
-        if (c >= dq) { c -= dq; ++r; }
+      const int units = nrows * dq;
+      if (tid == 0 && t + gridDim.x < n_tiles) {
+        const int64_t tn = t + gridDim.x;
+        const uint32_t bytes = (uint32_t)min((int64_t)LEG_ROWS, n - tn * LEG_ROWS) * (uint32_t)d * 4u;
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(ext + tn * LEG_ROWS * d), "r"(bytes) : "memory");
+      }
+      int r = r_first, c = c_first;
+      for (int e0 = tid; e0 < units; e0 += 4 * LEG_ROWS) {
+        int4 x[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (e0 + LEG_ROWS * k < units) x[k] = __ldcs(g4 + e0 + LEG_ROWS * k);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          if (e0 + LEG_ROWS * k < units) {
+            int32_t* w = tile + r * ds + 4 * c;
+            w[0] = x[k].x; w[1] = x[k].y; w[2] = x[k].z; w[3] = x[k].w;
+          }
+          r += r_step; c += c_step;
+          if (c >= dq) { c -= dq; ++r; }
+        }
       }
     } else {
       for (int e = tid, r = r_first, c = c_first; e < nrows * d; e += LEG_ROWS) {
@@ -343,25 +410,24 @@ __global__ void __launch_bounds__(LEG_ROWS) legalise_tiled_kernel(int32_t* __res
     __syncthreads();
     if (tid < nrows) {
       int32_t* row = tile + tid * ds;
-      int rem = 0;
+      int rem = 0, ri = -1;                    // search groups carry the remaining extent, table groups its divisor index
       for (int jj = 0; jj < steps; ++jj) {
         const int4 sp = stp[jj];
         const int j = sp.x & 255, last = sp.x >> 8, sext = sp.y;
-        if (sext <= 0) { rem = 0; continue; }
-        if (rem == 0) rem = sext;
-        const int cap = last ? max_innermost : 0;
+        if (sext <= 0) { rem = 0; ri = -1; continue; }
         int q;
         if (sp.z >= 0) {
-          const int bound = (cap > 0 && cap < rem) ? cap : rem;
-          const int v = min(max(row[j], 1), bound);
-          q = lut[sp.w + lut[sp.z + rem] * (sext + 1) + v];
-          rem = __float2int_rn(__fdividef((float)rem, (float)q));   // exact: q | rem, both <= 255
+          if (ri < 0) ri = sp.w;
+          const int v = min(max(row[j], 1), sext);
+          const int e = tab16[sp.z + ri * (sext + 1) + v];
+          q = e & 255;
+          ri = last ? -1 : e >> 8;
         } else {
-          q = nearest_divisor(rem, row[j], cap);
-          rem /= q;
+          if (rem == 0) rem = sext;
+          q = nearest_divisor(rem, row[j], last ? max_innermost : 0);
+          rem = last ? 0 : rem / q;
         }
         row[j] = q;
-        if (last) rem = 0;
       }
     }
     __syncthreads();
@@ -369,7 +435,7 @@ __global__ void __launch_bounds__(LEG_ROWS) legalise_tiled_kernel(int32_t* __res
       int4* g4 = reinterpret_cast<int4*>(g);
       for (int e = tid, r = r_first, c = c_first; e < nrows * dq; e += LEG_ROWS) {
         const int32_t* w = tile + r * ds + 4 * c;
-        g4[e] = make_int4(w[0], w[1], w[2], w[3]);
+        __stcs(g4 + e, make_int4(w[0], w[1], w[2], w[3]));
         r += r_step; c += c_step;
         if (c >= dq) { c -= dq; ++r; }
       }
