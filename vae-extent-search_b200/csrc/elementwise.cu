@@ -225,11 +225,15 @@ __global__ void legalise_kernel(int32_t* __restrict__ ext, int64_t n, int d,
 // per extent on the host for the same reason (utils.cc:446-463).  Larger extents, and whatever does not fit LEG_LUT
 // bytes, keep the +-1 search.  (Tried: sorted divisor lists + bisection for every extent -- slower than the +-1 search
 // on task-1264-like bounds, 0.78 vs 0.53 ms per 2 M rows.)
-constexpr int LEG_ROWS = 128;
+#ifndef VAEX_LEG_ROWS
+#define VAEX_LEG_ROWS 128
+#define VAEX_LEG_CTAS 5
+#endif
+constexpr int LEG_ROWS = VAEX_LEG_ROWS, LEG_CTAS = VAEX_LEG_CTAS;   // rows (= threads) per CTA, CTAs per SM
 constexpr int LEG_LUT = 12 * 1024;             // bytes of answer tables per CTA
 constexpr int LEG_LUT_MAX_E = 255;
 
-__global__ void __launch_bounds__(LEG_ROWS, 5) legalise_tiled_kernel(int32_t* __restrict__ ext, int64_t n, int d,
+__global__ void __launch_bounds__(LEG_ROWS, LEG_CTAS) legalise_tiled_kernel(int32_t* __restrict__ ext, int64_t n, int d,
                                                                   const int32_t* __restrict__ slot_extent,
                                                                   const uint8_t* __restrict__ slot_last, int max_innermost,
                                                                   const int32_t* __restrict__ order, int n_order, int use_lut) {
@@ -459,7 +463,8 @@ int legalise_extents(int32_t* ext, int64_t n, int d, const int32_t* slot_extent,
     static int sms = 0;
     if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
     const int64_t tiles = cdiv(n, LEG_ROWS);
-    const unsigned grid = (unsigned)std::min<int64_t>(tiles, (int64_t)std::max(sms, 1) * 5);
+    const unsigned grid = (unsigned)std::min<int64_t>(tiles, (int64_t)std::max(sms, 1) * LEG_CTAS);
+    if (sh > 48 * 1024) cudaFuncSetAttribute(legalise_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);
     // the tables cost a CTA about as much as walking one tile: worth it from a few tiles per CTA on
     legalise_tiled_kernel<<<grid, LEG_ROWS, sh, st>>>(ext, n, d, slot_extent, slot_last, max_innermost, order, n_order,
                                                       tiles >= 3 * (int64_t)grid ? 1 : 0);
