@@ -459,6 +459,9 @@ def test_topk_vs_oracle():
         (rng.standard_normal(5000).astype(np.float32), 100, rng.random(5000) < 0.3),
         (rng.standard_normal(50).astype(np.float32), 64, rng.random(50) < 0.5),   # k > eligible
         (np.where(rng.random(3000) < 0.5, -np.inf, rng.standard_normal(3000)).astype(np.float32), 1024, None),
+        (np.full(3_000_000, 1.5, np.float32), 320, None),                     # one score: all three index digits decide
+        (np.repeat(rng.standard_normal(700).astype(np.float32), 3000), 1000, None),   # the k-th score is a 3000-way tie
+        (np.where(rng.random(70000) < 0.1, np.nan, rng.integers(0, 40, 70000)).astype(np.float32), 500, None),  # NaN sorts last
     ]
     for s, k, mask in cases:
         mk = None if mask is None else torch.from_numpy(mask.astype(np.uint8)).cuda()
