@@ -50,6 +50,54 @@ __global__ void topk_init(TopkState* st, int k) {
   if (threadIdx.x == 0) { st->prefix = 0; st->k_rem = k; st->done = 0; st->count = 0; st->n_out = 0; st->ticket = 0; }
 }
 
+// Fixes one digit of the threshold from a complete histogram; called by all 256 threads of a CTA.
+template <bool GLOBAL>
+__device__ __forceinline__ void decide_digit(const unsigned int* hist, TopkState* st, unsigned long long prefix, int pass,
+                                             int shift, int nb, unsigned int* part) {
+  // ---- decide, in parallel (a serial walk by one thread costs ~30 clk per shared and ~1 us per global load):
+  // thread t owns the group of `per` buckets that is t-th from the TOP; an inclusive scan over t gives the number of
+  // keys in its group and above, and exactly one thread finds the k-th key inside its own group ----
+  const int per = nb / 256, t = threadIdx.x, g0 = (255 - t) * per;
+  unsigned int cnt[16];
+  unsigned int mine = 0;
+#pragma unroll
+  for (int b = 0; b < 16; ++b) {
+    cnt[b] = b < per ? (GLOBAL ? __ldcg(&hist[g0 + b]) : hist[g0 + b]) : 0u;
+    mine += cnt[b];
+  }
+  unsigned int incl = mine;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const unsigned int v = __shfl_up_sync(0xffffffffu, incl, o);
+    if ((t & 31) >= o) incl += v;
+  }
+  if ((t & 31) == 31) part[t >> 5] = incl;
+  __syncthreads();
+  unsigned int above = 0;                       // keys in the groups above this thread's
+  for (int w = 0; w < (t >> 5); ++w) above += part[w];
+  incl += above;
+  above = incl - mine;
+  const unsigned int k = st->k_rem;
+  __syncthreads();
+  if (t == 255 && incl < k) {                   // fewer eligible than k: take everything (only reachable in pass 0)
+    st->prefix = 0; st->done = 1; st->n_out = incl;
+  }
+  if (above < k && incl >= k) {                 // the k-th key is in this thread's group
+    unsigned int cum = above, c = 0;
+    int b = 0;
+    bool found = false;
+#pragma unroll
+    for (int q = 15; q >= 0; --q) {
+      if (q < per && !found) {
+        if (cum + cnt[q] >= k) { found = true; b = q; c = cnt[q]; } else cum += cnt[q];
+      }
+    }
+    st->prefix = prefix | ((unsigned long long)(g0 + b) << shift);
+    st->k_rem = k - cum;
+    if (c == k - cum || pass == TOPK_PASSES - 1) st->done = 1;
+  }
+}
+
 // One launch per digit: every CTA histograms its share of the still-eligible keys in shared memory and merges it into
 // the global histogram; the CTA that merges last (ticket) walks the buckets from the top, fixes the digit of the
 // threshold and clears the histogram for the next pass.  Launches after the threshold is isolated return at once.
@@ -87,51 +135,47 @@ topk_pass(const float* __restrict__ s, const uint8_t* __restrict__ mask, int64_t
   __syncthreads();
   if (!is_last) return;
   __threadfence();
-  // ---- decide, in parallel (a serial walk by one thread costs ~30 clk per shared and ~1 us per global load):
-  // thread t owns the group of `per` buckets that is t-th from the TOP; an inclusive scan over t gives the number of
-  // keys in its group and above, and exactly one thread finds the k-th key inside its own group ----
-  const int per = nb / 256, t = threadIdx.x, g0 = (255 - t) * per;
-  unsigned int cnt[16];
-  unsigned int mine = 0;
-#pragma unroll
-  for (int b = 0; b < 16; ++b) {
-    cnt[b] = b < per ? __ldcg(&st->hist[g0 + b]) : 0u;
-    mine += cnt[b];
-  }
-  unsigned int incl = mine;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const unsigned int v = __shfl_up_sync(0xffffffffu, incl, o);
-    if ((t & 31) >= o) incl += v;
-  }
-  if ((t & 31) == 31) part[t >> 5] = incl;
-  __syncthreads();
-  unsigned int above = 0;                       // keys in the groups above this thread's
-  for (int w = 0; w < (t >> 5); ++w) above += part[w];
-  incl += above;
-  above = incl - mine;
-  const unsigned int k = st->k_rem;
-  __syncthreads();
-  if (t == 255 && incl < k) {                   // fewer eligible than k: take everything (only reachable in pass 0)
-    st->prefix = 0; st->done = 1; st->n_out = incl;
-  }
-  if (above < k && incl >= k) {                 // the k-th key is in this thread's group
-    unsigned int cum = above, c = 0;
-    int b = 0;
-    bool found = false;
-#pragma unroll
-    for (int q = 15; q >= 0; --q) {
-      if (q < per && !found) {
-        if (cum + cnt[q] >= k) { found = true; b = q; c = cnt[q]; } else cum += cnt[q];
-      }
-    }
-    st->prefix = prefix | ((unsigned long long)(g0 + b) << shift);
-    st->k_rem = k - cum;
-    if (c == k - cum || pass == TOPK_PASSES - 1) st->done = 1;
-  }
-  if (t == 0) st->ticket = 0;
+  decide_digit<true>(st->hist, st, prefix, pass, shift, nb, part);
+  if (threadIdx.x == 0) st->ticket = 0;
   __syncthreads();
   for (int b = threadIdx.x; b < nb; b += 256) st->hist[b] = 0;
+}
+
+// Few scores (config 1's 4 096 latents, the 5k pools of select_programs): the whole select in ONE CTA -- histogram in shared
+// memory, the same digit decision, the collect -- so that the call is 2 launches (this + the sort) instead of 9; at this
+// size the launches, not the bytes, are the cost.
+constexpr int TOPK_SMALL_N = 32768;
+__global__ void __launch_bounds__(256)
+topk_small(const float* __restrict__ s, const uint8_t* __restrict__ mask, int n, TopkState* st, int k) {
+  __shared__ unsigned int h[TOPK_BUCKETS];
+  __shared__ unsigned int part[8];
+  if (threadIdx.x == 0) { st->prefix = 0; st->k_rem = k; st->done = 0; st->count = 0; st->n_out = 0; st->ticket = 0; }
+  __syncthreads();
+  for (int pass = 0; pass < TOPK_PASSES; ++pass) {
+    if (st->done) break;
+    const int shift = TOPK_SHIFT[pass], nb = 1 << TOPK_BITS[pass], hs = shift + TOPK_BITS[pass];
+    for (int b = threadIdx.x; b < nb; b += 256) h[b] = 0;
+    const unsigned long long prefix = st->prefix;
+    __syncthreads();
+    for (int i = threadIdx.x; i < n; i += 256) {
+      if (mask && !mask[i]) continue;
+      const unsigned long long key = make_key(s[i], i);
+      if (pass > 0 && (key >> hs) != (prefix >> hs)) continue;
+      atomicAdd(&h[(unsigned int)(key >> shift) & (nb - 1)], 1u);
+    }
+    __syncthreads();
+    decide_digit<false>(h, st, prefix, pass, shift, nb, part);
+    __syncthreads();
+  }
+  const unsigned long long thr = st->prefix;
+  for (int i = threadIdx.x; i < n; i += 256) {
+    if (mask && !mask[i]) continue;
+    const unsigned long long key = make_key(s[i], i);
+    if (key >= thr) {
+      const unsigned int slot = atomicAdd(&st->count, 1u);
+      if (slot < TOPK_MAX) st->cand[slot] = key;
+    }
+  }
 }
 
 __global__ void __launch_bounds__(256)
@@ -179,6 +223,13 @@ int topk(const float* scores, int64_t n, int k, const uint8_t* mask, float* out_
   VAEX_CHECK(k >= 0 && k <= TOPK_MAX, "k must be in [0, 1024]");
   VAEX_CHECK(n >= 0 && n < (1ll << 32), "n must fit in 32 bits");
   TopkState* st = reinterpret_cast<TopkState*>(workspace);
+  if (k > 0 && n > 0 && n <= TOPK_SMALL_N) {
+    topk_small<<<1, 256, 0, stream>>>(scores, mask, (int)n, st, k);
+    VAEX_LAUNCH_CHECK();
+    topk_sort<<<1, TOPK_MAX, 0, stream>>>(st, k, out_vals, out_idx, n_out);
+    VAEX_LAUNCH_CHECK();
+    return VAEX_OK;
+  }
   topk_init<<<1, 256, 0, stream>>>(st, k);
   VAEX_LAUNCH_CHECK();
   if (k > 0 && n > 0) {
