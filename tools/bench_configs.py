@@ -64,6 +64,26 @@ def config1_and_5(out):
         ms = timed(lambda: score_pipeline(vae, reg, z, mean_d, scale_d, ext_d, last_d, k), iters)
         rec = {"config": name, "latents": n, "topk": k, "ms": ms, "latents_per_s": n / ms * 1e3,
                "pipeline": "decode (tcgen05 chain) + snap + divisor legalise -> predict_cost (tcgen05 chain) -> top-k"}
+        if name == "config1":      # the same five launches replayed from a CUDA graph: what the kernels cost without Python between them
+            try:
+                side = torch.cuda.Stream()
+                side.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(side):
+                    for _ in range(3):
+                        score_pipeline(vae, reg, z, mean_d, scale_d, ext_d, last_d, k)
+                torch.cuda.current_stream().wait_stream(side)
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph):
+                    g_ext, g_vals, g_idx = score_pipeline(vae, reg, z, mean_d, scale_d, ext_d, last_d, k)
+                want = score_pipeline(vae, reg, z, mean_d, scale_d, ext_d, last_d, k)
+                graph.replay()
+                torch.cuda.synchronize()
+                same = bool(torch.equal(g_ext, want[0]) and torch.equal(g_idx, want[2]))
+                rec["cuda_graph_replay_ms"] = round(timed(graph.replay, iters), 5)
+                rec["cuda_graph_same_result"] = same
+            except Exception as e:      # capture is a convenience of the caller, not part of the path
+                rec["cuda_graph_replay_ms"] = None
+                rec["cuda_graph_error"] = str(e)[:200]
         if name == "config5":      # where the time goes (each stage timed alone, back to back launches)
             cost5 = reg.predict_cost(z)
             rec["stages_ms"] = {
