@@ -476,6 +476,48 @@ def test_topk_vs_oracle():
         assert np.array_equal(vals.cpu().numpy(), wv)
 
 
+def test_score_pipeline_is_graph_capturable():
+    """Config 1's five launches (decode + snap, legalise, predict_cost, top-k select + sort) captured once with
+    torch.cuda.graph and replayed on new latents: same extents and winners as the eager calls -- the entry points use
+    the caller's stream, stream-ordered workspaces and no host synchronisation."""
+    torch.manual_seed(2023)
+    vae = vaex_b200.VAE_feature_head(48, None, 64, 256).cuda().eval()
+    reg = vaex_b200.VAECostPredictor(48, hidden_dim=256, latent_dim=64).cuda().eval()
+    rng = np.random.default_rng(4)
+    mean = torch.from_numpy(rng.uniform(0.5, 3, 48).astype(np.float32)).cuda()
+    scale = torch.from_numpy(rng.uniform(0.3, 1.5, 48).astype(np.float32)).cuda()
+    ext, last = [], []
+    for b in rng.choice([1, 3, 4, 28, 56, 57, 64, 128], 11):
+        ext += [int(b)] * 4
+        last += [0, 0, 0, 1]
+    ext_d = torch.tensor(ext + [0] * 4, dtype=torch.int32, device="cuda")
+    last_d = torch.tensor(last + [0] * 4, dtype=torch.uint8, device="cuda")
+    z = torch.randn(4096, 64, device="cuda")
+
+    def pipeline():
+        e = vae.decode_snap(z, mean, scale, slot_extent=ext_d, slot_last=last_d)
+        vals, idx, _ = vaex_b200.topk(reg.predict_cost(z), 64, sync=False)
+        return e, vals, idx
+
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for _ in range(2):
+            pipeline()
+    torch.cuda.current_stream().wait_stream(side)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        g_e, g_vals, g_idx = pipeline()
+    for seed in (1, 2):
+        z.copy_(torch.randn(4096, 64, device="cuda", generator=torch.Generator("cuda").manual_seed(seed)))
+        graph.replay()
+        torch.cuda.synchronize()
+        got = g_e.clone(), g_vals.clone(), g_idx.clone()
+        want = pipeline()
+        torch.cuda.synchronize()
+        assert torch.equal(got[0], want[0]) and torch.equal(got[2], want[2]) and torch.equal(got[1], want[1])
+
+
 def test_select_programs_matches_reference():
     g = load_golden("select.npz")
     reg = vaex_b200.VAECostPredictor(48, hidden_dim=256, latent_dim=64)
