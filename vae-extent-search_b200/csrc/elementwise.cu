@@ -217,14 +217,16 @@ __global__ void legalise_kernel(int32_t* __restrict__ ext, int64_t n, int d,
 // coalesced 4-byte accesses and the walk runs on a padded (d + 1) tile without bank conflicts.  Used for d <= 64.
 //
 // Answer tables for small loop extents.  Every remaining extent of a split divides the loop extent E of its slots, so for
-// E <= 255 the whole function (remaining extent r | E, target v) -> nearest divisor fits a byte table of
-// ndiv(E) * (E + 1) entries (twice: with and without the innermost cap).  Each persistent CTA builds the tables of its
-// distinct extents once in shared memory (one thread per table row: a forward pass leaves the largest divisor <= v, a
-// backward pass compares it with the smallest one >= v; ties -> smaller, like the +-1 search) and a slot then costs two
-// byte loads and a float quotient instead of a data-dependent search and an integer division -- GetFactors memoises
-// per extent on the host for the same reason (utils.cc:446-463).  Larger extents, and whatever does not fit LEG_LUT
-// bytes, keep the +-1 search.  (Tried: sorted divisor lists + bisection for every extent -- slower than the +-1 search
-// on task-1264-like bounds, 0.78 vs 0.53 ms per 2 M rows.)
+// E <= 255 the whole function (remaining extent r | E, target v) -> nearest divisor fits a table of ndiv(E) * (E + 1)
+// 16-bit entries (twice: with and without the innermost cap): low byte = the divisor q, high byte = the index of r / q
+// among E's divisors.  The walk therefore carries the INDEX of the remaining extent; a slot costs one 16-byte step
+// record, the row element and one table load, instead of a data-dependent search and an integer division --
+// GetFactors memoises per extent on the host for the same reason (utils.cc:446-463).  Each persistent CTA builds the
+// tables of its distinct extents once in shared memory, one thread per table row: a forward pass leaves the largest
+// divisor <= v, a backward pass compares it with the smallest one >= v (ties -> smaller, like the +-1 search), targets
+// above the bound answer like the bound.  Larger extents, whatever does not fit LEG_LUT bytes, and slot tables in which
+// a split changes its extent half way keep the +-1 search.  History and measurements: profiles/r01_ncu_legalise_notes.md
+// (tried and dropped: sorted divisor lists + bisection, the next tile held in registers, a software-pipelined walk).
 #ifndef VAEX_LEG_ROWS
 #define VAEX_LEG_ROWS 128
 #define VAEX_LEG_CTAS 5
