@@ -374,7 +374,7 @@ __global__ void __launch_bounds__(LEG_ROWS, LEG_CTAS) legalise_tiled_kernel(int3
   const bool vec4 = d % 4 == 0 && (reinterpret_cast<uintptr_t>(ext) & 15) == 0;   // a tile starts 128 * d * 4 bytes further: aligned too
   const int dq = vec4 ? d / 4 : d;             // units per row (int4 or int)
   const int r_first = tid / dq, c_first = tid % dq, r_step = LEG_ROWS / dq, c_step = LEG_ROWS % dq;
-  // int4 path: the 128 x d/4 units of a tile are d/4 (<= 16) per thread, moved four at a time (four loads in flight per
+  // int4 path: the 128 x d/4 units of a tile are d/4 (<= 16) per thread, moved eight at a time (eight loads in flight per
   // thread); one thread asks L2 for the next tile before this one is walked.  (Holding the next tile in 64 registers
   // instead made ptxas recompute the walk's loop invariants on every step: same time, more instructions.)
   for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
@@ -391,13 +391,13 @@ __global__ void __launch_bounds__(LEG_ROWS, LEG_CTAS) legalise_tiled_kernel(int3
         asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(ext + tn * LEG_ROWS * d), "r"(bytes) : "memory");
       }
       int r = r_first, c = c_first;
-      for (int e0 = tid; e0 < units; e0 += 4 * LEG_ROWS) {
-        int4 x[4];
+      for (int e0 = tid; e0 < units; e0 += 8 * LEG_ROWS) {
+        int4 x[8];
 #pragma unroll
-        for (int k = 0; k < 4; ++k)
+        for (int k = 0; k < 8; ++k)
           if (e0 + LEG_ROWS * k < units) x[k] = __ldcs(g4 + e0 + LEG_ROWS * k);
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
+        for (int k = 0; k < 8; ++k) {
           if (e0 + LEG_ROWS * k < units) {
             int32_t* w = tile + r * ds + 4 * c;
             w[0] = x[k].x; w[1] = x[k].y; w[2] = x[k].z; w[3] = x[k].w;
