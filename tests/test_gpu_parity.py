@@ -516,6 +516,24 @@ def test_score_pipeline_is_graph_capturable():
         want = pipeline()
         torch.cuda.synchronize()
         assert torch.equal(got[0], want[0]) and torch.equal(got[2], want[2]) and torch.equal(got[1], want[1])
+    # the SegmentSumMLP forward (offset scan + row encoder + head) as well, once a warm-up call has sized its workspace
+    net = vaex_b200.SegmentSumMLPModule(164, 256, 1).cuda().eval()
+    sizes = torch.from_numpy(rng.integers(1, 33, size=20000).astype(np.int32)).cuda()
+    feats = torch.rand(int(sizes.sum()), 164, device="cuda") * 24
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side), torch.no_grad():
+        for _ in range(2):
+            net(sizes, feats)
+    torch.cuda.current_stream().wait_stream(side)
+    graph2 = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph2), torch.no_grad():
+        g_scores = net(sizes, feats)
+    feats.mul_(0.5)
+    graph2.replay()
+    torch.cuda.synchronize()
+    got_scores = g_scores.clone()
+    with torch.no_grad():
+        assert torch.equal(got_scores, net(sizes, feats))
 
 
 def test_select_programs_matches_reference():
