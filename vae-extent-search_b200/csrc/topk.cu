@@ -199,10 +199,12 @@ topk_sort(TopkState* st, int k, float* __restrict__ out_vals, int64_t* __restric
   const int t = threadIdx.x;
   a[t] = (unsigned int)t < cnt ? st->cand[t] : 0ull;
   __syncthreads();
-  for (int size = 2; size <= TOPK_MAX; size <<= 1) {
+  int S = 2;                                    // the network only has to cover the candidates there are
+  while (S < (int)cnt) S <<= 1;
+  for (int size = 2; size <= S; size <<= 1) {
     for (int stride = size >> 1; stride > 0; stride >>= 1) {
       const int j = t ^ stride;
-      if (j > t) {
+      if (j > t && j < S) {
         const bool desc = (t & size) == 0;
         const unsigned long long x = a[t], y = a[j];
         if (desc ? (x < y) : (x > y)) { a[t] = y; a[j] = x; }
