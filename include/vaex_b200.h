@@ -114,6 +114,18 @@ int vaex_model_set_option(vaex_model_t h, int option, int value);
  *      and the batch loop of MLPModelInternal._predict_a_task, :669-681) --------------------- */
 /* exclusive scan of int32 sizes[n] -> int32 offsets[n+1] (SegmentDataLoader, :91-92) */
 int vaex_segment_offsets(const int32_t* sizes_dev, int64_t n, int32_t* offsets_dev, void* stream);
+/* Allocation-free variant of vaex_segment_offsets.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same arguments and bit-identical output; the per-block sums of the
+ * scan live in a file-scope `static __device__` array of 64 KiB that every GPU loading the library holds until
+ * exit, so n is limited to VAEX_SEGMENT_OFFSETS_NOALLOC_MAX sizes (larger n: VAEX_E_INVALID, use
+ * vaex_segment_offsets).  The call makes no cudaMalloc / cudaFree / cudaMallocAsync and calls no allocating library
+ * routine; the first call on a device resolves the array's device address (cudaGetSymbolAddress, once per device,
+ * with that device current) and should therefore be made outside stream capture.  All calls on a device share the
+ * one array, which keeps the previous call's contents (nothing needs to start at zero: each call overwrites the
+ * entries it reads): calls that overlap on the GPU (different streams, no ordering between them) race. */
+#define VAEX_SEGMENT_OFFSETS_NOALLOC_MAX ((int64_t)16384 * 2048) /* 33 554 432 sizes */
+int vaex_segment_offsets_noalloc(const int32_t* sizes_dev, int64_t n, int32_t* offsets_dev, void* stream);
 /* feats_dev: fp32 [n_rows, F] row-major, rows of one program contiguous; seg_offsets_dev:
  * int32[n_programs+1]; scores_dev: fp32[n_programs]. */
 int vaex_segsum_mlp_forward(vaex_model_t h, const float* feats_dev, const int32_t* seg_offsets_dev,

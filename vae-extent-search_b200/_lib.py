@@ -30,6 +30,7 @@ SIGNATURES = {
     "vaex_model_destroy": ([vp], ctypes.c_int),
     "vaex_model_set_option": ([vp, ctypes.c_int, ctypes.c_int], ctypes.c_int),
     "vaex_segment_offsets": ([vp, i64, vp, vp], ctypes.c_int),
+    "vaex_segment_offsets_noalloc": ([vp, i64, vp, vp], ctypes.c_int),
     "vaex_segsum_mlp_forward": ([vp, vp, vp, i64, i64, vp, ctypes.c_int, vp], ctypes.c_int),
     "vaex_segsum_encode": ([vp, vp, vp, i64, i64, vp, ctypes.c_int, vp], ctypes.c_int),
     "vaex_segsum_mlp_predict_host": ([vp, vp, vp, i64, i64, vp, ctypes.c_int], ctypes.c_int),

@@ -1,6 +1,8 @@
 // Bandwidth-bound helpers: scan, reparameterisation, integer snap / legalise, dropout,
 // ReLU-mask products for the fused backward, z update.
 #include <algorithm>
+#include <mutex>
+#include <string>
 
 #include "common.cuh"
 #include "simt_kernels.cuh"
@@ -562,3 +564,61 @@ int row_l2norm(const float* g, int64_t n, int cols, float* out, cudaStream_t st)
 }
 
 }  // namespace vaex
+
+// ------------------------------------------------------------------ allocation-free exclusive scan
+// vaex_segment_offsets_noalloc: the same three scan kernels as exclusive_scan_i32, but the per-block sums live in a
+// file-scope device array instead of a stream-ordered allocation, for callers that may not allocate (CUDA graph
+// capture, tight serving loops).  Every GPU that loads the library holds the 64 KiB until exit.  In host code the
+// array's name is only a host-side stand-in: the kernels get the device address that cudaGetSymbolAddress returns,
+// resolved once per device with that device current.
+namespace vaex {
+constexpr int64_t NOALLOC_MAX_BLOCKS = 16384;                       // 64 KiB of scratch
+constexpr int64_t NOALLOC_MAX_N = NOALLOC_MAX_BLOCKS * SCAN_B;      // = VAEX_SEGMENT_OFFSETS_NOALLOC_MAX
+static_assert(NOALLOC_MAX_N == VAEX_SEGMENT_OFFSETS_NOALLOC_MAX, "header and kernel disagree on the limit");
+static __device__ __align__(256) int32_t g_scan_block_sums[NOALLOC_MAX_BLOCKS];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static int32_t* g_scan_block_sums_addr[NOALLOC_MAX_DEVICES];        // device address per device ordinal, 0 = not resolved
+static std::mutex g_scan_addr_mutex;
+
+static int scan_scratch_for_current_device(int32_t** out) {
+  int dev = -1;
+  VAEX_CUDA(cudaGetDevice(&dev));
+  VAEX_CHECK(dev >= 0 && dev < NOALLOC_MAX_DEVICES, "device ordinal out of range");
+  std::lock_guard<std::mutex> lock(g_scan_addr_mutex);
+  if (!g_scan_block_sums_addr[dev]) {
+    int32_t* p = nullptr;
+    VAEX_CUDA(cudaGetSymbolAddress((void**)&p, g_scan_block_sums));
+    VAEX_CHECK(p != nullptr, "cudaGetSymbolAddress returned a null address");
+    g_scan_block_sums_addr[dev] = p;
+  }
+  *out = g_scan_block_sums_addr[dev];
+  return VAEX_OK;
+}
+}  // namespace vaex
+
+extern "C" int vaex_segment_offsets_noalloc(const int32_t* sizes_dev, int64_t n, int32_t* offsets_dev, void* stream) {
+  using namespace vaex;
+  VAEX_CHECK(n >= 0 && offsets_dev && (sizes_dev || n == 0), "bad argument");
+  if (n > NOALLOC_MAX_N) {
+    set_error("vaex_segment_offsets_noalloc: n = " + std::to_string(n) + " exceeds the static scratch limit of " +
+              std::to_string(NOALLOC_MAX_N) + " sizes (VAEX_SEGMENT_OFFSETS_NOALLOC_MAX); use vaex_segment_offsets");
+    return VAEX_E_INVALID;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (n == 0) {
+    VAEX_CUDA(cudaMemsetAsync(offsets_dev, 0, sizeof(int32_t), st));
+    return VAEX_OK;
+  }
+  int32_t* bsum = nullptr;
+  TRY(scan_scratch_for_current_device(&bsum));
+  const int nb = (int)cdiv(n, SCAN_B);
+  // nothing has to start at zero: scan_block_sums overwrites bsum[0, nb) before anything reads it
+  scan_block_sums<<<nb, SCAN_T, 0, st>>>(sizes_dev, n, bsum);
+  VAEX_LAUNCH_CHECK();
+  scan_of_sums<<<1, SCAN_T, 0, st>>>(bsum, nb);
+  VAEX_LAUNCH_CHECK();
+  scan_final<<<nb, SCAN_T, 0, st>>>(sizes_dev, n, bsum, offsets_dev);
+  VAEX_LAUNCH_CHECK();
+  return VAEX_OK;
+}
