@@ -642,6 +642,63 @@ def gen_segreg_train(ns):
     np.savez_compressed(os.path.join(OUT, "segreg_train.npz"), **out)
 
 
+def gen_select_unc(ns):
+    """a13: select_topk_uncertainty and select_programs with an uncertainty budget (w_unc > 0), run by the reference
+    itself (utils/select.py:151-182,277-376 -> mc_predict, utils/model.py:241-273).  The predictor's nn.Dropout is
+    replaced by a subclass that takes its keep-masks from a recorded Bernoulli(0.9) draw instead of torch's private
+    stream (one mask per mc_predict pass, same x * mask / (1 - p) arithmetic), so the CUDA path can replay it."""
+    sel_ref = np.load(os.path.join(OUT, "select.npz"))
+    x = sel_ref["x"]
+    N, PH, T = x.shape[0], 256, 6
+
+    class RecordedDropout(torch.nn.Dropout):
+        def __init__(self, p, masks):
+            super().__init__(p)
+            self.masks, self.calls = masks, 0
+
+        def forward(self, inp):
+            if not self.training:
+                return inp
+            m = self.masks[self.calls % len(self.masks)]
+            self.calls += 1
+            return inp * m / (1.0 - self.p)
+
+    def model_with(masks):
+        torch.manual_seed(11)
+        reg = ns.vae_model.VAECostPredictor(48, hidden_dim=256, latent_dim=64).eval()
+        reg.load_state_dict({k[4:]: torch.from_numpy(sel_ref[k]) for k in sel_ref.files if k.startswith("reg.")})
+        assert isinstance(reg.cost_predictor[2], torch.nn.Dropout)
+        drop = RecordedDropout(reg.cost_predictor[2].p, masks)
+        reg.cost_predictor[2] = drop
+        return reg.eval(), drop
+
+    gm = torch.Generator().manual_seed(313)
+    masks = (torch.rand(T, N, PH, generator=gm) >= 0.1).float()
+    out = {"masks": masks.numpy().astype(np.uint8), "T": np.int64(T)}
+    used, remaining = set(sel_ref["used"].tolist()), set(sel_ref["remaining"].tolist())
+    # the function on its own
+    reg, drop = model_with(masks)
+    with torch.no_grad():
+        mc_mean, mc_var = reg.mc_predict(torch.from_numpy(x), T=T)
+    assert drop.calls == T
+    out.update({"mc_mean": mc_mean.numpy(), "mc_var": mc_var.numpy()})
+    reg, drop = model_with(masks)
+    sel, rem = ns.select.select_topk_uncertainty(reg, torch.from_numpy(x), set(remaining), 24, T_mc=T)
+    assert not reg.training and drop.calls == T
+    out.update({"unc24": sel, "unc24_rem": np.array(sorted(rem), np.int64)})
+    # select_programs, both branches of the uncertainty stage (select.py:350-357): whole remaining pool when few
+    # programs have been measured, the top-5k candidate pool afterwards
+    for tag, unc_topk in (("pool", 10 ** 9), ("cand", 10)):
+        reg, drop = model_with(masks)
+        sel_prog, rem_prog = ns.select.select_programs(
+            reg, x, set(used), set(remaining), num_select=64, T_mc=T, uncertainty_topk=unc_topk,
+            w_cost=0.4, w_unc=0.4, w_div=0.2, grad_num=2, rand_num=0,
+            rng=np.random.default_rng(42), device=torch.device("cpu"), topk_factor=5)
+        assert drop.calls == T
+        out.update({"sel_prog_" + tag: sel_prog, "rem_prog_" + tag: np.array(sorted(rem_prog), np.int64)})
+    np.savez_compressed(os.path.join(OUT, "select_unc.npz"), **out)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     ns = load_reference()
@@ -658,9 +715,15 @@ def main():
     gen_extent_text(ns)
     gen_segvae_train(ns)
     gen_segreg_train(ns)
+    gen_select_unc(ns)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 
 
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1:        # python oracle/gen_golden.py gen_select_unc  -> only that fixture
+        _ns = load_reference()
+        for _name in sys.argv[1:]:
+            globals()[_name](_ns)
+    else:
+        main()

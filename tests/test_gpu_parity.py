@@ -552,6 +552,45 @@ def test_select_programs_matches_reference():
     assert np.array_equal(np.array(sorted(rem_prog)), g["rem_prog"])
 
 
+def test_select_uncertainty_matches_reference():
+    """a13: select_topk_uncertainty and select_programs with an uncertainty budget against the reference's own picks
+    (oracle/gen_golden.py::gen_select_unc: the reference run with its nn.Dropout fed from recorded keep-masks)."""
+    g = load_golden("select.npz")
+    u = load_golden("select_unc.npz")
+    T = int(u["T"])
+    masks = torch.from_numpy(u["masks"]).cuda()
+    rem, used = set(g["remaining"].tolist()), set(g["used"].tolist())
+    for tc in (False, True):     # fp32 SIMT chain, then the tcgen05 chain with the dropout mask in its first epilogue
+        reg = vaex_b200.VAECostPredictor(48, hidden_dim=256, latent_dim=64)
+        reg.load_state_dict(split_sd(g, "reg."))
+        reg = reg.cuda().eval()
+        reg.set_tensor_cores(tc)
+        x = torch.from_numpy(g["x"]).cuda()
+        mc_mean, mc_var = reg.mc_predict(x, T=T, masks=masks)
+        np.testing.assert_allclose(mc_mean.cpu().numpy(), u["mc_mean"], rtol=1e-3 if tc else 2e-5, atol=1e-5 if tc else 2e-6)
+        if not tc:
+            np.testing.assert_allclose(mc_var.cpu().numpy(), u["mc_var"], rtol=2e-3, atol=1e-9)
+            sel, rem_after = vaex_b200.select.select_topk_uncertainty(reg, x, set(rem), 24, T_mc=T, mc_masks=masks)
+            assert np.array_equal(np.sort(sel), np.sort(u["unc24"]))
+            assert np.array_equal(np.array(sorted(rem_after)), u["unc24_rem"])
+            for tag, unc_topk in (("pool", 10 ** 9), ("cand", 10)):
+                sel_prog, rem_prog = vaex_b200.select_programs(
+                    reg, g["x"], set(used), set(rem), num_select=64, T_mc=T, uncertainty_topk=unc_topk,
+                    w_cost=0.4, w_unc=0.4, w_div=0.2, grad_num=2, rand_num=0, rng=np.random.default_rng(42),
+                    device=torch.device("cuda"), topk_factor=5, mc_masks=masks)
+                assert np.array_equal(sel_prog, u["sel_prog_" + tag]), tag
+                assert np.array_equal(np.array(sorted(rem_prog)), u["rem_prog_" + tag]), tag
+        else:
+            # fp16 operands: a variance of 5e-5 is a difference of predictions that carry 1e-3 relative error each, so the
+            # variance ranking is only comparable where the gaps exceed that: the reference's top-24 must sit inside the
+            # kernel's top-48 and the variances must correlate
+            v = mc_var.cpu().numpy()
+            top48 = set(np.argsort(-v)[:48].tolist())
+            hits = len(top48 & set(np.argsort(-u["mc_var"])[:24].tolist()))
+            assert hits >= 20, hits
+            assert np.corrcoef(v, u["mc_var"])[0, 1] > 0.98
+
+
 def test_latent_ascent_vs_oracle():
     g = load_golden("extent_vae.npz")
     reg = vaex_b200.VAECostPredictor(48, hidden_dim=256, latent_dim=64)

@@ -161,3 +161,58 @@ def test_gather_segments_and_fit_base_learns():
     m.fit_local(test)
     rho2 = spearmanr(m.predict(test)[task], labels[n_train:]).statistic
     assert rho2 > 0.85, rho2
+
+
+def test_mlp_model_update_refits_and_predicts(monkeypatch):
+    """MLPModel.update (mlp_model.py:824-830) on the GPU: measured pairs -> TVM's packed feature bytes (stub FFI) ->
+    Dataset.update_from_measure_pairs -> fit_base on the CUDA training kernels -> predictions that rank a held-out
+    round; the second update re-fits on both rounds."""
+    import collections
+    import sys
+    import types
+    from oracle import feature_blob as FB
+    Task = collections.namedtuple("Task", ["workload_key", "target"])
+    MeasureInput = collections.namedtuple("MeasureInput", ["task", "state"])
+    MeasureResult = collections.namedtuple("MeasureResult", ["costs"])
+
+    def get_pairs(inputs, results, skip, max_n_bufs):
+        costs = np.array([np.mean(r.costs) for r in results])
+        return FB.serialize_features([i.state for i in inputs], costs.min() / costs, np.zeros(len(inputs), np.int32), [costs.min()])
+    tvm, autos, ffi = types.ModuleType("tvm"), types.ModuleType("tvm.auto_scheduler"), types.ModuleType("tvm.auto_scheduler._ffi_api")
+    ffi.GetPerStoreFeaturesFromMeasurePairs = get_pairs
+    for name, mod in (("tvm", tvm), ("tvm.auto_scheduler", autos), ("tvm.auto_scheduler._ffi_api", ffi)):
+        monkeypatch.setitem(sys.modules, name, mod)
+
+    rng = np.random.default_rng(9)
+    w = rng.standard_normal(164).astype(np.float32)
+    task = Task("wk", "cuda")
+
+    def round_of(n):
+        states = [rng.random((int(rng.integers(1, 9)), 164), dtype=np.float32) for _ in range(n)]
+        score = np.array([s.mean(0) @ w for s in states])
+        cost = np.exp(-score)                                   # a higher hidden score = a faster program
+        return [MeasureInput(task, s) for s in states], [MeasureResult([float(c)]) for c in cost], states, score
+
+    model = vaex_b200.MLPModel()
+    model.model.use_workload_embedding = False
+    model.model.net_params["in_dim"] = 164
+    model.model.n_epoch, model.model.print_per_epoches = 12, 100
+    torch.manual_seed(0)
+    i1, r1, _, _ = round_of(3000)
+    model.update(i1, r1)
+    assert len(model.dataset) == 3000 and model.model.base_model is not None
+    i2, r2, s2, score2 = round_of(2000)
+    feats = np.empty(len(s2), dtype=object)
+    for k, s in enumerate(s2):
+        feats[k] = s
+    feats[5] = np.zeros((2, 164), np.float32)
+    pred = model.predict_features(task, feats)
+    assert np.isneginf(pred[5])
+    from scipy.stats import spearmanr
+    keep = np.arange(len(s2)) != 5
+    rho1 = spearmanr(pred[keep], score2[keep]).statistic
+    assert rho1 > 0.6, rho1
+    model.update(i2, r2)
+    assert len(model.dataset) == 5000
+    pred2 = model.predict_features(task, feats)
+    assert spearmanr(pred2[keep], score2[keep]).statistic > max(0.7, rho1 - 0.05)

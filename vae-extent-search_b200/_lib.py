@@ -125,6 +125,13 @@ def check(rc):
         raise VaexError("vaex_b200 error %d: %s" % (rc, msg.decode() if msg else "?"))
 
 
+def require_cuda(what):
+    """Every compute path is CUDA-only: fail with a VaexError instead of whatever torch raises first."""
+    import torch
+    if not torch.cuda.is_available():
+        raise VaexError("%s needs a CUDA device (vaex_b200 has no CPU fallback)" % what)
+
+
 def ptr(t):
     """Device (or host) pointer of a torch tensor / numpy array / None."""
     if t is None:

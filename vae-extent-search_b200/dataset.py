@@ -9,6 +9,11 @@ import numpy as np
 LearningTask = namedtuple("LearningTask", ["workload_key", "target"])
 
 
+def input_to_learning_task(inp):
+    """dataset.py:16-17."""
+    return LearningTask(inp.task.workload_key, str(inp.task.target))
+
+
 class Dataset:
     def __init__(self):
         self.raw_files = None
@@ -40,6 +45,23 @@ class Dataset:
             np.asarray(self.throughputs[task]) * (comb / self.min_latency[task]),
             np.asarray(throughputs) * (comb / min_latency)])
         self.min_latency[task] = comb
+
+    def update_from_measure_pairs(self, inputs, results, featurize=None):
+        """dataset.py:39-57: group the measured pairs by task, extract their per-store features and append them.
+        featurize(inputs, results) -> (features, normalized_throughputs, task_ids, min_latency) defaults to
+        feature.get_per_store_features_from_measure_pairs (TVM's extractor + this library's blob parser)."""
+        if featurize is None:
+            from .feature import get_per_store_features_from_measure_pairs as featurize
+        new_data = {}
+        for inp, res in zip(inputs, results):
+            store = new_data.setdefault(input_to_learning_task(inp), ([], []))
+            store[0].append(inp)
+            store[1].append(res)
+        for task, (t_inputs, t_results) in new_data.items():
+            features, normalized_throughputs, task_ids, min_latency = featurize(t_inputs, t_results)
+            assert not np.any(task_ids)   # all task ids should be zero
+            assert len(min_latency) == 1  # should have only one task
+            self.load_task_data(task, features, normalized_throughputs, min_latency[0])
 
     def update_from_dataset(self, dataset):
         for task in dataset.features:

@@ -61,3 +61,20 @@ def unpack_feature(byte_arr):
     for i, e in enumerate(ends):
         out[i] = feats[e - sizes[i]:e]
     return out, thr.astype(np.float64), task_ids.astype(np.int64), min_costs.astype(np.float64)
+
+
+DEFAULT_MAX_N_BUFS = 5             # feature.py:38
+
+
+def get_per_store_features_from_measure_pairs(inputs, results, skip_first_n_feature_extraction=0, max_n_bufs=None):
+    """feature.py:192-225: the extraction itself is TVM's C++ (GetPerStoreFeaturesFromMeasurePairs lowers every
+    program, src/auto_scheduler/feature.cc:1425-1470) and stays there; the bytes it returns are parsed by the C++
+    blob parser of this library instead of the per-row struct.unpack_from loop.  Needs an importable `tvm`."""
+    try:
+        from tvm.auto_scheduler import _ffi_api
+    except ImportError as e:
+        raise _lib.VaexError("feature extraction from MeasureInput/MeasureResult pairs needs TVM "
+                             "(auto_scheduler._ffi_api.GetPerStoreFeaturesFromMeasurePairs): %s" % e)
+    byte_arr = _ffi_api.GetPerStoreFeaturesFromMeasurePairs(inputs, results, skip_first_n_feature_extraction,
+                                                            max_n_bufs or DEFAULT_MAX_N_BUFS)
+    return unpack_feature(byte_arr)

@@ -103,8 +103,9 @@ class SegmentDataLoader:
         return norm_vector
 
     def __iter__(self):
-        if self.shuffle:
-            raise NotImplementedError("shuffled (training) iteration is not part of the inference path yet")
+        """mlp_model.py:107-114: a fresh permutation per epoch when shuffling (the same torch CPU stream as the
+        reference, so a seeded run visits the programs in the reference's order)."""
+        self.iter_order = torch.randperm(self.number) if self.shuffle else None
         self.pointer = 0
         return self
 
@@ -112,11 +113,24 @@ class SegmentDataLoader:
         if self.pointer >= self.number:
             raise StopIteration
         s, e = self.pointer, min(self.pointer + self.batch_size, self.number)
-        self.pointer = e
+        self.pointer += self.batch_size
+        if self.iter_order is not None:
+            return self._fetch_indices(self.iter_order[s:e])
         r0 = int(self.feature_offsets[s])
         r1 = int(self.feature_offsets[e - 1] + self.segment_sizes[e - 1])
         return (self.segment_sizes[s:e].to(self.device), self.features[r0:r1].to(self.device),
                 self.labels[s:e].to(self.device))
+
+    def _fetch_indices(self, indices):
+        """mlp_model.py:129-141 without the per-program Python loop: the rows of programs `indices`, in that order."""
+        indices = torch.as_tensor(indices, dtype=torch.int64)
+        segment_sizes = self.segment_sizes[indices]
+        sz = segment_sizes.numpy().astype(np.int64)
+        starts = np.asarray(self.feature_offsets, dtype=np.int64)[indices.numpy()]
+        ends_out = np.cumsum(sz)
+        row_idx = np.arange(int(ends_out[-1]) if len(sz) else 0, dtype=np.int64) + np.repeat(starts - (ends_out - sz), sz)
+        features = self.features[torch.from_numpy(row_idx)]
+        return (segment_sizes.to(self.device), features.to(self.device), self.labels[indices].to(self.device))
 
     def __len__(self):
         return self.number
@@ -199,8 +213,12 @@ class SegmentSumMLPModule(torch.nn.Module):
 
     # -- forward ---------------------------------------------------------------------------
     def forward(self, segment_sizes, features, params=None, flags=0, fea_norm_vec=None):
-        if self.training and torch.is_grad_enabled():
-            raise NotImplementedError("training through the CUDA path lands with the backward kernels")
+        if self.training and torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
+            # the reference trains by autograd through this forward (mlp_model.py:548-565); here the forward, the loss and
+            # the backward of a step are one C-ABI call on flat buffers, not an autograd graph
+            raise _lib.VaexError("SegmentSumMLPModule.forward builds no autograd graph: train with "
+                                 "MLPModelInternal.fit_base / fit_local or vaex_b200.train.Trainer "
+                                 "(vaex_trainer_forward_backward), or call under torch.no_grad() / .eval() to score")
         if not features.is_cuda:
             raise _lib.VaexError("SegmentSumMLPModule.forward needs CUDA tensors (no CPU fallback)")
         lib = _lib.load()
@@ -372,6 +390,7 @@ class MLPModelInternal:
 
     def _fit_a_model(self, train_set, valid_set=None, valid_train_set=None, n_epoch=None):
         from . import train as _train
+        _lib.require_cuda("MLPModelInternal._fit_a_model")
         print("=" * 60 + "\nFit a net. Train size: %d" % len(train_set))
         train_loader, valid_loader = self._loaders(train_set, valid_set, self.batch_size, True)
         n_epoch = n_epoch or self.n_epoch
@@ -404,6 +423,7 @@ class MLPModelInternal:
 
     def _fine_tune_a_model(self, model, train_set, valid_set=None, verbose=1):
         from . import train as _train
+        _lib.require_cuda("MLPModelInternal._fine_tune_a_model")
         if verbose >= 1:
             print("=" * 60 + "\nFine-tune a net. Train size: %d" % len(train_set))
         bs = self.fine_tune_batch_size or len(train_set)
@@ -509,6 +529,12 @@ class MLPModelInternal:
         base = self.base_model.cpu() if self.base_model else None
         local = self.local_model.cpu() if self.local_model and hasattr(self.local_model, "cpu") else self.local_model
         pickle.dump((base, local, self.few_shot_learning, self.fea_norm_vec), open(filename, 'wb'))
+        # mlp_model.py:803-804: the models go back to the device after the dump
+        dev = getattr(self, "device", None)
+        if dev is not None and torch.cuda.is_available():
+            self.base_model = self.base_model.to(dev) if self.base_model else None
+            if self.local_model and hasattr(self.local_model, "to"):
+                self.local_model = self.local_model.to(dev)
 
 
 class _RefUnpickler(pickle.Unpickler):
@@ -546,20 +572,50 @@ def pack_features_f16(flat):
     return out, bool(lossy.value)
 
 
-class MLPModel:
+try:        # with TVM importable the model is a PythonBasedModel, so task_scheduler.py:94-115 / SketchPolicy accept it
+    from tvm.auto_scheduler.cost_model.cost_model import PythonBasedModel
+except ImportError:
+    class PythonBasedModel:
+        """Stand-in base when TVM is absent: cost_model.py:115-130 registers update / predict / predict_stages
+        as PackedFuncs with the C++ PythonBasedModelNode; without TVM there is nothing to register with."""
+
+        def __init__(self):
+            pass
+
+        def predict_stages(self, task, states):
+            raise NotImplementedError       # cost_model.py:166-201: MLPModel does not implement it either
+
+
+class MLPModel(PythonBasedModel):
     """mlp_model.py:814-860.  `predict(task, states)` needs TVM's feature extractor
     (get_per_store_features_from_states); `predict_features(task, features)` is the same call
     from the point where the 164-d rows exist -- the boundary of this build."""
 
     def __init__(self, few_shot_learning="base_only", disable_update=False):
+        super().__init__()
         self.disable_update = disable_update
         self.model = MLPModelInternal(few_shot_learning=few_shot_learning)
         self.dataset = Dataset()
 
     def update(self, inputs, results):
+        """mlp_model.py:824-830: append the measured pairs to the data set and re-fit the base model on all of it
+        (the CUDA training kernels, train.py)."""
         if self.disable_update or len(inputs) <= 0:
             return
-        raise NotImplementedError("online re-fit needs the training row (next round)")
+        tic = time.time()
+        self.dataset.update_from_measure_pairs(inputs, results)
+        self.model.fit_base(self.dataset)
+        logger.info("MLPModel Training time: %.2f s", time.time() - tic)
+
+    def update_from_file(self, file_name, n_lines=None):
+        """mlp_model.py:848-851.  Reading measure records is TVM's RecordReader."""
+        try:
+            from tvm.auto_scheduler.measure_record import RecordReader
+        except ImportError as e:
+            raise _lib.VaexError("update_from_file needs TVM's RecordReader: %s" % e)
+        inputs, results = RecordReader(file_name).read_lines(n_lines)
+        logger.info("MLPModel: Loaded %s measurement records from %s", len(inputs), file_name)
+        self.update(inputs, results)
 
     def predict_features(self, task, features):
         learning_task = LearningTask(task.workload_key, str(task.target))

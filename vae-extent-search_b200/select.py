@@ -57,12 +57,13 @@ def select_topk_z_grad(z, cost_pred, remaining_indices, num_select):
     return util_select_topk(norm, remaining_indices, num_select)
 
 
-def select_topk_uncertainty(model, input_tensor, remaining_indices, num_select, T_mc=10):
-    """select.py:151-182: top-k of the MC-dropout variance."""
+def select_topk_uncertainty(model, input_tensor, remaining_indices, num_select, T_mc=10, mc_masks=None, mc_seed=None):
+    """select.py:151-182: top-k of the MC-dropout variance.  mc_masks (uint8 [T_mc, N, PH], 1 = keep) replays a given
+    Bernoulli draw instead of the kernel's Philox stream (parity tests); mc_seed fixes that stream."""
     if num_select == 0:
         return np.array([], dtype=np.int64), remaining_indices
     with torch.no_grad():
-        _, mc_var = model.mc_predict(input_tensor, T=T_mc)
+        _, mc_var = model.mc_predict(input_tensor, T=T_mc, masks=mc_masks, seed=mc_seed)
     return util_select_topk(mc_var, remaining_indices, num_select)
 
 
@@ -90,8 +91,8 @@ def select_topk_latent_diversity(z, candidate_indices, used_indices, select_n_di
 
 def select_programs(model, input_data_scaled, used_indices, remaining_indices, num_select=64, T_mc=10,
                     uncertainty_topk=128, w_cost=0.5, w_unc=0.3, w_div=0.2, grad_num=2, rand_num=0,
-                    rng=np.random.default_rng(42), device=torch.device("cuda"), topk_factor=5):
-    """select.py:277-376, same budget arithmetic and stage order."""
+                    rng=np.random.default_rng(42), device=torch.device("cuda"), topk_factor=5, mc_masks=None, mc_seed=None):
+    """select.py:277-376, same budget arithmetic and stage order (mc_masks / mc_seed: see select_topk_uncertainty)."""
     total = num_select
     budget = total - grad_num - rand_num
     if num_select == 0 and rand_num > 0:
@@ -115,11 +116,11 @@ def select_programs(model, input_data_scaled, used_indices, remaining_indices, n
     sel, candidate = select_topk_z_grad(z, cost_pred, candidate, grad_num)
     currently_used.update(sel.tolist())
     if len(used_indices) >= uncertainty_topk:
-        unc, candidate = select_topk_uncertainty(model, x, candidate, n_unc, T_mc=T_mc)
+        unc, candidate = select_topk_uncertainty(model, x, candidate, n_unc, T_mc=T_mc, mc_masks=mc_masks, mc_seed=mc_seed)
     else:
         pool_unc = set(remaining_indices)
         pool_unc.difference_update(currently_used)
-        unc, _ = select_topk_uncertainty(model, x, pool_unc, n_unc, T_mc=T_mc)
+        unc, _ = select_topk_uncertainty(model, x, pool_unc, n_unc, T_mc=T_mc, mc_masks=mc_masks, mc_seed=mc_seed)
         candidate.difference_update(unc.tolist())
     currently_used.update(unc.tolist())
     used_local = set(used_indices)
