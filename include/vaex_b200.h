@@ -136,6 +136,12 @@ int vaex_segsum_mlp_forward(vaex_model_t h, const float* feats_dev, const int32_
 int vaex_segsum_encode(vaex_model_t h, const float* feats_dev, const int32_t* seg_offsets_dev,
                        int64_t n_programs, int64_t n_rows, float* segsum_dev, int flags,
                        void* stream);
+/* The residual head on its own (SegmentSumMLPModule.forward after the scatter_add, mlp_model.py:210-221): segsum_dev
+ * fp32 [n_programs, H] (as written by vaex_segsum_encode) -> norm -> h += relu(l0 h) -> h += relu(l1 h) -> decoder
+ * (-> sigmoid) -> scores_dev fp32 [n_programs]; valid_dev_or_null uint8 [n_programs]: 0 -> -inf.
+ * flags: VAEX_F_FORCE_SIMT. */
+int vaex_segsum_head(vaex_model_t h, const float* segsum_dev, int64_t n_programs, const uint8_t* valid_dev_or_null,
+                     float* scores_dev, int flags, void* stream);
 /* End-to-end host call (what MLPModel.predict costs a reference user, mlp_model.py:832-846):
  * host fp32 features + int32 sizes in, host fp32 scores out; chunked H2D on two streams
  * overlapped with compute.  Synchronous.  When the tcgen05 kernel serves the model, F % 4 == 0 and the host has
@@ -383,6 +389,33 @@ int vaex_scaler_transform(const float* raw_dev, int64_t n, int32_t d, const doub
  * written (min(k, eligible)).  k <= 1024. */
 int vaex_topk(const float* scores_dev, int64_t n, int32_t k, const uint8_t* mask_dev_or_null,
               float* out_vals_dev, int64_t* out_idx_dev, int32_t* n_out_dev, void* stream);
+
+/* ---- multi-GPU: one process per GPU, NCCL over NVLink / NVSwitch.  The reference is single-GPU (its
+ *      selection sorts one numpy array, utils/select.py:54-81; its training loop is one process, mlp_model.py:512-600);
+ *      these entry points are what replaces that sort / that optimizer step when the pool or the batch is sharded.
+ *      NCCL is bound at run time (dlopen libnccl.so.2; VAEX_NCCL_LIB overrides the path); world == 1 needs none. ---- */
+typedef struct vaex_comm* vaex_comm_t;
+#define VAEX_NCCL_ID_BYTES 128
+/* rank 0: a fresh ncclUniqueId (128 bytes) that the host side hands to every rank (torch.distributed store, MPI, a file) */
+int vaex_nccl_unique_id(uint8_t* id_out_host);
+/* with the rank's device current; id_host may be NULL when world == 1 */
+int vaex_nccl_init(int32_t rank, int32_t world, const uint8_t* id_host, vaex_comm_t* out);
+int vaex_nccl_destroy(vaex_comm_t c);
+int vaex_comm_info(vaex_comm_t c, int32_t* rank_or_null, int32_t* world_or_null);
+/* Candidate merge of the sharded scoring path: local_vals_dev fp32[k] / local_idx_dev int64[k] are this rank's winners in
+ * vaex_topk order (score desc, index asc; rank-local indices), *n_local_dev_or_null how many of them are real (NULL = k);
+ * index_base = global index of the rank's first program (ranks own ascending contiguous blocks).  One ncclAllGather of
+ * k 16-byte records per rank + one single-CTA merge: out_vals_dev fp32[k], out_idx_dev int64[k] = the k best over all
+ * ranks in (score desc, global index asc) order, identical on every rank; entries past *n_out are (-inf, -1).
+ * k <= 1024 and world * k <= 8192.  Asynchronous on `stream`. */
+int vaex_topk_allgather_merge(vaex_comm_t c, const float* local_vals_dev, const int64_t* local_idx_dev,
+                              const int32_t* n_local_dev_or_null, int32_t k, int64_t index_base, float* out_vals_dev,
+                              int64_t* out_idx_dev, int32_t* n_out_dev_or_null, void* stream);
+/* data-parallel training: sum all-reduce of the flat fp32 gradient buffer, in place (the 1 / world factor is the
+ * grad_scale argument of vaex_adam_step / vaex_adamw_step / vaex_sgd_step) */
+int vaex_allreduce_grads(vaex_comm_t c, float* grads_dev, int64_t n, void* stream);
+/* recv_dev [world][bytes_per_rank] <- every rank's send_dev (the final exchange of the sharded latent ascent) */
+int vaex_allgather(vaex_comm_t c, const void* send_dev, void* recv_dev, int64_t bytes_per_rank, void* stream);
 
 #ifdef __cplusplus
 }

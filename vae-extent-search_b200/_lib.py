@@ -33,6 +33,7 @@ SIGNATURES = {
     "vaex_segment_offsets_noalloc": ([vp, i64, vp, vp], ctypes.c_int),
     "vaex_segsum_mlp_forward": ([vp, vp, vp, i64, i64, vp, ctypes.c_int, vp], ctypes.c_int),
     "vaex_segsum_encode": ([vp, vp, vp, i64, i64, vp, ctypes.c_int, vp], ctypes.c_int),
+    "vaex_segsum_head": ([vp, vp, i64, vp, vp, ctypes.c_int, vp], ctypes.c_int),
     "vaex_segsum_mlp_predict_host": ([vp, vp, vp, i64, i64, vp, ctypes.c_int], ctypes.c_int),
     "vaex_pack_features_f16": ([vp, vp, i64, vp], ctypes.c_int),
     "vaex_model_get_counter": ([vp, ctypes.c_int, ctypes.POINTER(i64)], ctypes.c_int),
@@ -88,6 +89,13 @@ SIGNATURES = {
     "vaex_segreg_trainer_forward_backward": ([vp, vp, vp, vp, vp, vp, i64, i64, vp, vp, u64, vp, vp, vp, vp, vp], ctypes.c_int),
     "vaex_adamw_step": ([vp, vp, vp, vp, i64, i64, i64, i64, f32, f32, f32, f32, f32, f32, f32, vp, ctypes.c_int, vp], ctypes.c_int),
     "vaex_kcenter_select": ([vp, i64, i32, vp, i64, vp, i64, i32, f32, vp, vp], ctypes.c_int),
+    "vaex_nccl_unique_id": ([vp], ctypes.c_int),
+    "vaex_nccl_init": ([i32, i32, vp, ctypes.POINTER(vp)], ctypes.c_int),
+    "vaex_nccl_destroy": ([vp], ctypes.c_int),
+    "vaex_comm_info": ([vp, ctypes.POINTER(i32), ctypes.POINTER(i32)], ctypes.c_int),
+    "vaex_topk_allgather_merge": ([vp, vp, vp, vp, i32, i64, vp, vp, vp, vp], ctypes.c_int),
+    "vaex_allreduce_grads": ([vp, vp, i64, vp], ctypes.c_int),
+    "vaex_allgather": ([vp, vp, vp, i64, vp], ctypes.c_int),
     "vaex_topk": ([vp, i64, i32, vp, vp, vp, vp, vp], ctypes.c_int),
 }
 

@@ -129,7 +129,7 @@ class SegmentVAETrainer:
         else:
             mask = drop
         self.forward_backward(segment_sizes, features, eps, mask, seed)
-        scale = shard.reduce_gradients(self.grads, self.group)
+        scale = shard.reduce_gradients(self.grads, self.group, getattr(self, "comm", None))
         self.optimizer_step(scale, lr)
         return self.losses
 
@@ -308,7 +308,7 @@ class SegmentRegressionTrainer:
         else:
             masks = drop
         self.forward_backward(segment_sizes, features, labels, config, noise, masks, seed)
-        scale = shard.reduce_gradients(self.grads, self.group)
+        scale = shard.reduce_gradients(self.grads, self.group, getattr(self, "comm", None))
         self.optimizer_step(scale)
         return self.losses
 

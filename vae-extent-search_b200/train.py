@@ -74,7 +74,7 @@ class Trainer:
 
     def all_reduce_grads(self):
         """Sum over ranks; the mean is folded into the optimizer kernel (grad_scale = 1 / world)."""
-        return shard.reduce_gradients(self.grads, self.group)
+        return shard.reduce_gradients(self.grads, self.group, getattr(self, "comm", None))
 
     def adam_step(self, lr, weight_decay=0.0, grad_clip=0.0, betas=(0.9, 0.999), eps=1e-8, grad_scale=1.0):
         self.t += 1

@@ -165,7 +165,7 @@ class RegressionTrainer:
             noise = config.get('noise_std', 0.1) * torch.randn(x.shape[0], self.L, device=x.device)
         self.forward_backward(x, labels, config, drop_mask, noise)
         self.model.eval()                            # smooth_loss_fn's side effect
-        scale = shard.reduce_gradients(self.grads, self.group)
+        scale = shard.reduce_gradients(self.grads, self.group, getattr(self, "comm", None))
         self.optimizer_step(grad_scale=scale)
         return self.losses
 
@@ -248,7 +248,7 @@ class VAETrainer:
         if isinstance(eps, str):
             eps = torch.randn(x.shape[0], self.L, device=x.device)
         self.forward_backward(x, eps)
-        scale = shard.reduce_gradients(self.grads, self.group)
+        scale = shard.reduce_gradients(self.grads, self.group, getattr(self, "comm", None))
         self.t += 1
         _lib.check(self.lib.vaex_adam_step(_lib.ptr(self.params), _lib.ptr(self.grads), _lib.ptr(self.m), _lib.ptr(self.v), self.n,
                                            self.t, self.lr, 0.9, 0.999, 1e-8, 0.0, 0.0, scale, None, _lib.stream_ptr()))
