@@ -345,6 +345,40 @@ def legalise_divisor(raw, slot_extent, slot_group_last, max_innermost=64):
     return out.astype(np.int32)
 
 
+def legalise_divisor_fast(raw, slot_extent, slot_group_last, max_innermost=64):
+    """legalise_divisor vectorised over the rows (numpy; same results, pinned against the loop version by
+    tests/test_oracle_golden.py): per slot the rows are grouped by their remaining extent and snapped to the nearest
+    entry of that extent's sorted divisor list (ties -> smaller) by one searchsorted.  This is what bench.py times as
+    the CPU leg of the legalise stage -- the per-element Python loop above would flatter the GPU."""
+    raw = np.asarray(raw, dtype=np.int64)
+    out = raw.copy()
+    N, D = raw.shape
+    rem = None
+    for j in range(D):
+        ext = int(slot_extent[j])
+        if ext <= 0:
+            rem = None
+            continue
+        if rem is None:
+            rem = np.full(N, ext, np.int64)
+        last = bool(slot_group_last[j])
+        v = raw[:, j]
+        res = np.empty(N, np.int64)
+        for r in np.unique(rem):
+            divs = np.array([d for d in get_factors(int(r)) if not last or d <= max_innermost], dtype=np.int64)
+            sel = rem == r
+            vv = v[sel]
+            pos = np.searchsorted(divs, vv)                              # first divisor >= v
+            lo = divs[np.clip(pos - 1, 0, len(divs) - 1)]
+            hi = divs[np.clip(pos, 0, len(divs) - 1)]
+            res[sel] = np.where(pos == 0, hi, np.where(pos == len(divs), lo, np.where(vv - lo <= hi - vv, lo, hi)))
+        out[:, j] = res
+        rem = rem // res
+        if last:
+            rem = None
+    return out.astype(np.int32)
+
+
 # --------------------------------------------------------------------------------------
 # a11 top-k   utils/select.py:54-81 (np.argsort(pred)[-k:], ascending order of score)
 # --------------------------------------------------------------------------------------
