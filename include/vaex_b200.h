@@ -60,7 +60,10 @@ enum {
   VAEX_F_FORCE_SIMT = 2,   /* run the fp32 SIMT check kernels instead of the tcgen05 kernel */
   VAEX_F_FEATS_F16 = 4,    /* feats_dev holds IEEE fp16 (saturated to +-65504) instead of fp32: the tcgen05 row encoder
                               rounds to fp16 first in any case, so the scores are bit-identical; needs F % 4 == 0 */
-  VAEX_F_NO_HOST_PACK = 8  /* vaex_segsum_mlp_predict_host: copy the fp32 rows as they are (no fp16 narrowing on the host) */
+  VAEX_F_NO_HOST_PACK = 8, /* vaex_segsum_mlp_predict_host: copy the fp32 rows as they are (no fp16 narrowing on the host) */
+  VAEX_F_FEATS_IMAGE = 16  /* feats_dev is a packed row image made by vaex_rows_pack_image (fp16, 384-byte pitch, bias-one
+                              columns pre-written): the row encoder fetches its operand tiles with TMA tensor loads, no
+                              loader warps.  Scores are bit-identical with fp32 / fp16 rows.  F <= 174 */
 };
 
 /* snap modes for vaex_snap_extents / vaex_decode_snap */
@@ -136,6 +139,15 @@ int vaex_segsum_mlp_forward(vaex_model_t h, const float* feats_dev, const int32_
 int vaex_segsum_encode(vaex_model_t h, const float* feats_dev, const int32_t* seg_offsets_dev,
                        int64_t n_programs, int64_t n_rows, float* segsum_dev, int flags,
                        void* stream);
+/* The packed row image: the device-resident form of SegmentDataLoader's flattened feature tensor (mlp_model.py:72-85)
+ * for a pool that is scored more than once -- the active-learning loop re-scores the same candidates after every
+ * re-fit (vae_extent_search.py:1720-1889), and the rows never change.  vaex_rows_image_bytes(n_rows) bytes, 128-byte
+ * aligned: fp16 [n_rows, 192] (features saturated to +-65504, round to nearest even -- what the tcgen05 row encoder
+ * does to fp32 rows on the fly -- plus the constant-1 columns that carry the biases inside the MMAs), then the per-row
+ * "any non-zero feature" bits taken from the fp32 values (the -inf rule, mlp_model.py:842-844, stays exact).  The
+ * image depends on in_dim only, not on a model.  Pass it as feats_dev with VAEX_F_FEATS_IMAGE. */
+int64_t vaex_rows_image_bytes(int64_t n_rows);
+int vaex_rows_pack_image(const float* feats_dev, int64_t n_rows, int32_t in_dim, void* image_dev, void* stream);
 /* The residual head on its own (SegmentSumMLPModule.forward after the scatter_add, mlp_model.py:210-221): segsum_dev
  * fp32 [n_programs, H] (as written by vaex_segsum_encode) -> norm -> h += relu(l0 h) -> h += relu(l1 h) -> decoder
  * (-> sigmoid) -> scores_dev fp32 [n_programs]; valid_dev_or_null uint8 [n_programs]: 0 -> -inf.
@@ -217,6 +229,15 @@ int vaex_decode_snap(vaex_model_t h, const float* z_dev, int64_t n, float* x_dev
 int vaex_predict_cost(vaex_model_t h, const float* z_dev, int64_t n, float* cost_dev,
                       const uint8_t* drop_mask_dev_or_null, uint64_t drop_seed, float p_drop,
                       void* stream);
+/* VAECostPredictor.mc_predict's T dropout-active passes (utils/model.py:241-273) on latents z [n, L] (the encoder is
+ * deterministic in eval mode, so the reference's T encodes are one): mean_dev fp32 [n] = mean over the passes,
+ * var_dev_or_null fp32 [n] = unbiased variance (predictions.var(dim=0)).  drop_masks_dev_or_null uint8 [T][n, PH]
+ * (1 = keep) replays recorded Bernoulli draws; otherwise pass t uses the Philox stream of
+ * vaex_predict_cost(drop_seed + t).  With tensor cores enabled all T passes of a 256-row tile run in ONE kernel: layer
+ * 0 once, its activations kept in registers, per pass one masked copy into the operand + one 256 x 256 GEMM + the
+ * scalar head, mean / variance by Welford updates -- no [T, n] intermediate in HBM. */
+int vaex_mc_predict_cost(vaex_model_t h, const float* z_dev, int64_t n, int32_t T, const uint8_t* drop_masks_dev_or_null,
+                         uint64_t drop_seed, float p_drop, float* mean_dev, float* var_dev_or_null, void* stream);
 /* select_topk_z_grad's autograd.grad(cost.sum(), z) (utils/select.py:128-135) */
 int vaex_cost_grad_z(vaex_model_t h, const float* z_dev, int64_t n, float* cost_dev,
                      float* grad_z_dev, float* grad_norm_dev_or_null, void* stream);

@@ -153,6 +153,44 @@ def test_segsum_mlp_properties_large():
     assert l2_err(h, a[:50000].cpu().numpy()) < 2e-4 and rel_err(h, a[:50000].cpu().numpy()) < TC_RTOL
 
 
+@pytest.mark.parametrize("F", [164, 174, 10])
+def test_rows_image_tma_path_is_bit_identical(F):
+    """The packed row image (vaex_rows_pack_image + VAEX_F_FEATS_IMAGE: TMA tensor loads of the operand tiles) against
+    the fp32-row path of the same kernel: the same fp16 operands reach the MMAs, so segment sums and scores must agree
+    bit for bit -- saturation, fp16 subnormals, values that round to an fp16 zero (the program still counts as valid),
+    all-zero programs, empty programs and ragged tails around the 256-row tile included."""
+    rng = np.random.default_rng(F)
+    torch.manual_seed(F)
+    net = vaex_b200.SegmentSumMLPModule(F, 256, 1).cuda().eval()
+    for n in (1, 7, 300, 20011):
+        sizes = rng.integers(1, 33, size=n).astype(np.int32)
+        if n > 100:
+            sizes[[3, 50, n - 1]] = 0                                             # empty programs
+        offs = np.concatenate([[0], np.cumsum(sizes)])
+        feats = (rng.random((int(offs[-1]), F), dtype=np.float32) * 24).astype(np.float32)
+        feats[rng.random(feats.shape[0]) < 0.02] *= -1.0
+        if n > 100:
+            feats[5, 3], feats[6, 7], feats[9, 1] = 1e6, -3e38, 65519.0           # saturate
+            feats[20:40, 2:9] = 3e-6                                              # fp16 subnormals
+            for p in (0, 17):
+                feats[offs[p]:offs[p + 1]] = 0.0                                  # all-zero programs
+            feats[offs[17], 0] = 1e-9                                             # ... but this one is not: rounds to an fp16 zero
+        st, fd = torch.from_numpy(sizes).cuda(), torch.from_numpy(feats).cuda()
+        img = vaex_b200.RowsImage(fd)
+        assert img.n_rows == feats.shape[0] and img.in_dim == F
+        with torch.no_grad():
+            a = net(st, fd, flags=_lib.F_MASK_INVALID).reshape(-1)
+            b = net(st, img, flags=_lib.F_MASK_INVALID).reshape(-1)
+            sa, sb = net.segment_sums(st, fd), net.segment_sums(st, img)
+        assert torch.equal(sa.view(torch.int32), sb.view(torch.int32)), "segment sums differ (n = %d)" % n
+        assert torch.equal(a.view(torch.int32), b.view(torch.int32)), "scores differ (n = %d)" % n
+        if n > 100:
+            assert np.isneginf(b[0].item()) and np.isfinite(b[17].item())
+            assert np.isneginf(b[3].item())                                       # an empty program has no non-zero row
+    with pytest.raises(_lib.VaexError):                                           # the image is a tcgen05-path format
+        net(st, img, flags=_lib.F_FORCE_SIMT)
+
+
 def test_host_narrowing_is_bit_identical():
     """vaex_segsum_mlp_predict_host narrows chunks to fp16 on the host cores (half the PCIe bytes) or sends them raw,
     whichever keeps the bus busy; the row encoder rounds to fp16 first either way, so every mix must give the same
@@ -281,6 +319,69 @@ def test_extent_vae_golden():
     # (the strict check is the fp64 one above.  With rtol 1e-5 this fp32-vs-fp32 comparison failed at ~6e-5 on two fresh
     # boxes and passed on the others with identical code and seed; the fp64 assert names the side if it recurs)
     np.testing.assert_allclose(got_z, O.reparameterize(mu.cpu(), logvar.cpu(), eps.cpu()).numpy(), rtol=2e-4, atol=1e-5)
+
+
+@pytest.mark.parametrize("n", [300, 257, 70001])
+def test_mc_predict_fused_tensor_core_passes(n):
+    """vaex_mc_predict_cost on the tcgen05 chain (all T passes of a tile in one kernel, Dropout in the first epilogue)
+    against the oracle with the SAME keep-masks, and against the fp32 SIMT path with the SAME Philox seed: the two
+    paths must draw identical masks (a different draw would move a prediction by ~10 %, not by 1e-3)."""
+    g = load_golden("extent_vae.npz")
+    reg = vaex_b200.VAECostPredictor(48, hidden_dim=256, latent_dim=64)
+    reg.load_state_dict(split_sd(g, "reg."))
+    reg = reg.cuda().eval()
+    R = split_sd(g, "reg.")
+    rng = np.random.default_rng(n)
+    z = (g["z"][:n] if n <= 300 else rng.standard_normal((n, 64)).astype(np.float32))
+    zd = torch.from_numpy(z).cuda()
+    T = 5
+    masks = (rng.random((T, n, 256)) >= 0.1).astype(np.uint8)
+    md = torch.from_numpy(masks).cuda()
+    lib = _lib.load()
+
+    def mc(tc, mk, seed):
+        reg.set_tensor_cores(tc)
+        mean, var = torch.empty(n, device="cuda"), torch.empty(n, device="cuda")
+        _lib.check(lib.vaex_mc_predict_cost(reg.packed().h, _lib.ptr(zd), n, T, _lib.ptr(mk), seed, 0.1, _lib.ptr(mean), _lib.ptr(var),
+                                            _lib.stream_ptr()))
+        return mean.cpu().numpy(), var.cpu().numpy()
+
+    preds = np.stack([O.predict_cost(R, z, drop_mask=masks[t].astype(np.float32), p_drop=0.1).numpy() for t in range(T)])
+    want_m, want_v = preds.mean(0), preds.var(0, ddof=1)
+    scale = np.sqrt((want_m ** 2).mean())
+    m_s, v_s = mc(False, md, 0)                       # fp32 SIMT path, recorded masks
+    np.testing.assert_allclose(m_s, want_m, rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(v_s, want_v, rtol=2e-3, atol=1e-8)
+    m_t, v_t = mc(True, md, 0)                        # tcgen05 chain, recorded masks
+    assert np.abs(m_t - want_m).max() < 4e-3 * scale, np.abs(m_t - want_m).max() / scale
+    assert np.linalg.norm(m_t - want_m) / np.linalg.norm(want_m) < 1e-3
+    # a variance is a difference of predictions that each carry the fp16-operand error: compare at that scale
+    assert np.abs(np.sqrt(v_t) - np.sqrt(want_v)).max() < 4e-3 * scale
+    # single pass with a mask == the first pass
+    c1 = reg.predict_cost(zd, drop_mask=md[0]).cpu().numpy()
+    assert np.abs(c1 - preds[0]).max() < 4e-3 * scale
+    # seeded: the chain's Philox draws are the SIMT path's draws (chunked re-seeding included for n > one chunk)
+    m_s2, v_s2 = mc(False, None, 1234)
+    m_t2, v_t2 = mc(True, None, 1234)
+    assert np.abs(m_t2 - m_s2).max() < 4e-3 * scale, np.abs(m_t2 - m_s2).max() / scale
+    assert np.abs(np.sqrt(v_t2) - np.sqrt(v_s2)).max() < 4e-3 * scale
+    reg.set_tensor_cores(True)
+    c_t = reg.predict_cost(zd, drop_seed=99).cpu().numpy()
+    reg.set_tensor_cores(False)
+    c_s = reg.predict_cost(zd, drop_seed=99).cpu().numpy()
+    assert np.abs(c_t - c_s).max() < 4e-3 * scale
+    # dropout is on: about 10 % of the hidden units are dropped, predictions differ from eval mode
+    reg.set_tensor_cores(True)
+    assert np.abs(c_t - reg.predict_cost(zd).cpu().numpy()).mean() > 1e-4
+    m_t3, _ = mc(True, None, 1235)
+    assert np.abs(m_t3 - m_t2).mean() > 1e-6          # another seed, another draw
+    if n > 50000:                                     # more rows than one Philox chunk (2^18): the re-seeding must agree too
+        zb = torch.randn(270001, 64, device="cuda", generator=torch.Generator(device="cuda").manual_seed(3))
+        reg.set_tensor_cores(True)
+        cb_t = reg.predict_cost(zb, drop_seed=5).cpu().numpy()
+        reg.set_tensor_cores(False)
+        cb_s = reg.predict_cost(zb, drop_seed=5).cpu().numpy()
+        assert np.abs(cb_t - cb_s).max() < 4e-3 * np.sqrt((cb_s ** 2).mean())
 
 
 @pytest.mark.parametrize("n", [1, 127, 128, 129, 300, 70001])

@@ -9,7 +9,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libvaex_b200.so")
 
 KIND_SEGSUM_MLP, KIND_EXTENT_VAE, KIND_COST_PREDICTOR, KIND_SEGMENT_VAE, KIND_SEGMENT_COST = 1, 2, 3, 4, 5
-F_MASK_INVALID, F_FORCE_SIMT, F_FEATS_F16, F_NO_HOST_PACK = 1, 2, 4, 8
+F_MASK_INVALID, F_FORCE_SIMT, F_FEATS_F16, F_NO_HOST_PACK, F_FEATS_IMAGE = 1, 2, 4, 8, 16
 OPT_TENSOR_CORES, OPT_FUSED_ASCENT = 1, 2
 SNAP_EXP, SNAP_EXPM1, SNAP_DIVISOR = 0, 1, 4
 LOSS_IDS = {"rmse": 0, "rankNetLoss": 1, "lambdaRankLoss": 2, "listNetLoss": 3}
@@ -33,6 +33,8 @@ SIGNATURES = {
     "vaex_segment_offsets_noalloc": ([vp, i64, vp, vp], ctypes.c_int),
     "vaex_segsum_mlp_forward": ([vp, vp, vp, i64, i64, vp, ctypes.c_int, vp], ctypes.c_int),
     "vaex_segsum_encode": ([vp, vp, vp, i64, i64, vp, ctypes.c_int, vp], ctypes.c_int),
+    "vaex_rows_image_bytes": ([i64], i64),
+    "vaex_rows_pack_image": ([vp, i64, i32, vp, vp], ctypes.c_int),
     "vaex_segsum_head": ([vp, vp, i64, vp, vp, ctypes.c_int, vp], ctypes.c_int),
     "vaex_segsum_mlp_predict_host": ([vp, vp, vp, i64, i64, vp, ctypes.c_int], ctypes.c_int),
     "vaex_pack_features_f16": ([vp, vp, i64, vp], ctypes.c_int),
@@ -51,6 +53,7 @@ SIGNATURES = {
     "vaex_scaler_fit": ([vp, i64, i32, vp, vp, vp, vp, i64, vp], ctypes.c_int),
     "vaex_scaler_transform": ([vp, i64, i32, vp, vp, vp, vp], ctypes.c_int),
     "vaex_predict_cost": ([vp, vp, i64, vp, vp, u64, f32, vp], ctypes.c_int),
+    "vaex_mc_predict_cost": ([vp, vp, i64, i32, vp, u64, f32, vp, vp, vp], ctypes.c_int),
     "vaex_cost_grad_z": ([vp, vp, i64, vp, vp, vp, vp], ctypes.c_int),
     "vaex_latent_ascent": ([vp, vp, i64, i32, f32, vp, vp], ctypes.c_int),
     "vaex_segvae_encode": ([vp, vp, vp, i64, i64, vp, vp, vp, ctypes.c_int, vp], ctypes.c_int),

@@ -27,6 +27,7 @@
 
 #include "common.cuh"
 #include "model.cuh"
+#include "philox.cuh"
 #include "snap.cuh"
 #include "tc_ptx.cuh"
 
@@ -62,6 +63,16 @@ struct ChainParams {
   int32_t w_bytes, a_off, bias_off, bias_count, wd_off, bar_off;
   int32_t ones_col;          // >= 0: input columns ones_col, ones_col + 1 are the constant 1 that carries layer 0's bias (hi, lo) in W0
   float b_scale[ch::MAX_LAYERS];   // 1: add the stored bias; 0: the bias rides in the MMA
+  // MODE_DOT with Dropout(p) after the first ReLU (mc_predict, utils/model.py:241-273): mc_T >= 1 passes per tile
+  // share layer 0; pass t keeps element (row, c) iff drop_mask[t][row][c] != 0, else iff the Philox draw of
+  // dropout_kernel (elementwise.cu) for seed drop_seed + t says so.  mc_T == 1: out = cost; mc_T > 1: out = mean over
+  // the passes, var_out = unbiased variance.
+  const uint8_t* drop_mask;  // [mc_T][n, 256] or null
+  float* var_out;            // [n] or null
+  uint64_t drop_seed;
+  int64_t drop_chunk;        // rows per Philox chunk (the SIMT path re-seeds every VAE_CHUNK rows)
+  float drop_p, drop_inv;    // p and 1 / (1 - p)
+  int32_t mc_T;
 };
 
 __global__ void smem_base_probe_kernel(uint32_t* out) {
@@ -79,7 +90,7 @@ chain_tc_kernel(const ChainParams p) {
   const int cluster = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + p.bar_off);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + p.bar_off + 32);
-  float* s_dot = reinterpret_cast<float*>(smem + p.bar_off + 64);     // MODE_DOT: [3][128] partial dots
+  float* s_dot = reinterpret_cast<float*>(smem + p.bar_off + 64);     // MODE_DOT: [2][3][128] partial dots (double-buffered over MC passes)
   const float* s_bias = reinterpret_cast<const float*>(smem + p.bias_off);
   const uint32_t bar0 = ptx::smem_u32(bars);
   auto bar = [&](int i) { return bar0 + 8u * i; };
@@ -170,8 +181,153 @@ chain_tc_kernel(const ChainParams p) {
       pack_z();
       publish(B_IN0);
     }
+    // ---- MC-dropout passes of the predictor (mc_T >= 1): keep bits of this thread's 32 columns of n-half nh ----
+    auto keep_bits = [&](int pass, int64_t r, int nh) -> uint32_t {
+      const int col = 128 * nh + 32 * cg;
+      uint32_t bits = 0;
+      if (r >= p.n) return 0u;
+      if (p.drop_mask) {
+        const uint8_t* mk = p.drop_mask + ((int64_t)pass * p.n + r) * HID + col;
+        if ((reinterpret_cast<uintptr_t>(mk) & 15) == 0) {
+#pragma unroll
+          for (int h2 = 0; h2 < 2; ++h2) {
+            const uint4 w = __ldg(reinterpret_cast<const uint4*>(mk) + h2);
+            const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+#pragma unroll
+              for (int e = 0; e < 4; ++e)
+                bits |= (uint32_t)(((ww[j] >> (8 * e)) & 0xffu) != 0u) << (16 * h2 + 4 * j + e);
+          }
+        } else {
+#pragma unroll 4
+          for (int e = 0; e < 32; ++e) bits |= (uint32_t)(mk[e] != 0) << e;
+        }
+      } else {
+        const int64_t chunk = r / p.drop_chunk;
+        const Philox gen(p.drop_seed + (uint64_t)pass + 0x9E3779B97F4A7C15ull * (uint64_t)chunk);
+        const uint64_t q0 = (uint64_t)(((r - chunk * p.drop_chunk) * HID + col) >> 2);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const uint4 u = gen(q0 + j, 0);
+          bits |= (uint32_t)(u01(u.x) >= p.drop_p) << (4 * j);
+          bits |= (uint32_t)(u01(u.y) >= p.drop_p) << (4 * j + 1);
+          bits |= (uint32_t)(u01(u.z) >= p.drop_p) << (4 * j + 2);
+          bits |= (uint32_t)(u01(u.w) >= p.drop_p) << (4 * j + 3);
+        }
+      }
+      return bits;
+    };
+    // masked copy of the packed layer-0 activations -> A operand k-half nh (register i holds columns 2i, 2i + 1)
+    auto store_masked = [&](const uint32_t (&hr)[16], uint32_t bits, int nh) {
+      const int cc = 4 * nh + cg;
+      const uint32_t base = a_row + (cc >> 1) * ATOM;
+      uint32_t o[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const uint32_t lo = 0u - ((bits >> (2 * i)) & 1u), hi = 0u - ((bits >> (2 * i + 1)) & 1u);
+        o[i] = hr[i] & ((lo & 0xffffu) | (hi << 16));
+      }
+#pragma unroll
+      for (int m = 0; m < 4; ++m)
+        ptx::sts_v4(base + ((((cc & 1) * 4 + m) ^ sw) << 4), o[4 * m], o[4 * m + 1], o[4 * m + 2], o[4 * m + 3]);
+    };
     for (int t = cluster; t < p.T; t += n_clusters) {
       const int64_t r = (int64_t)t * PAIR + rank * TILE + row;
+      if (p.mc_T > 0) {
+        // layer 0 once: relu(acc + b0) / (1 - p), packed fp16, kept in registers for every pass of this tile
+        uint32_t hreg[2][16];
+        uint32_t nb0 = keep_bits(0, r, 0), nb1 = keep_bits(0, r, 1);
+        {
+          const uint32_t t_acc = t_lane + 256u * (lc & 1);
+          ++lc;
+          const float bs = p.b_scale[0], inv = p.drop_inv;
+#pragma unroll
+          for (int nh = 0; nh < 2; ++nh) {
+            const int col = 128 * nh + 32 * cg;
+            const float4* b = reinterpret_cast<const float4*>(s_bias + p.b_off[0] + col);
+            if (nh == 0) { ptx::mbar_wait(bar(B_ACC0), acc_use0 & 1); ++acc_use0; }
+            else         { ptx::mbar_wait(bar(B_ACC1), acc_use1 & 1); ++acc_use1; }
+            ptx::tc_fence_after();
+            uint32_t v[32];
+            ptx::tmem_ld32(t_acc + col, v);
+            ptx::tmem_ld_wait();
+#pragma unroll
+            for (int m = 0; m < 8; ++m) {
+              const float4 bm = b[m];
+              hreg[nh][2 * m] = ptx::cvt_h2_relu_sat(fmaf(bs, bm.x, __uint_as_float(v[4 * m])) * inv,
+                                                     fmaf(bs, bm.y, __uint_as_float(v[4 * m + 1])) * inv);
+              hreg[nh][2 * m + 1] = ptx::cvt_h2_relu_sat(fmaf(bs, bm.z, __uint_as_float(v[4 * m + 2])) * inv,
+                                                         fmaf(bs, bm.w, __uint_as_float(v[4 * m + 3])) * inv);
+            }
+            store_masked(hreg[nh], nh == 0 ? nb0 : nb1, nh);
+            publish(nh == 0 ? B_IN0 : B_IN1);
+          }
+        }
+        float mean = 0.f, m2 = 0.f;
+        for (int pass = 0; pass < p.mc_T; ++pass) {
+          const bool lastp = pass + 1 == p.mc_T;
+          const uint32_t t_acc = t_lane + 256u * (lc & 1);
+          ++lc;
+          if (lastp) {
+            fetch(t + n_clusters);
+            const int64_t r2 = (int64_t)(t + 2 * n_clusters) * PAIR + rank * TILE + row;
+            if (cg < 2 && 32 * cg < p.in_dim && r2 < p.n) ptx::prefetch_l2(p.X + r2 * p.in_dim + 32 * cg);
+          } else {                                   // the next pass's keep bits are computed behind this pass's GEMM
+            nb0 = keep_bits(pass + 1, r, 0);
+            nb1 = keep_bits(pass + 1, r, 1);
+          }
+          float dot0 = 0.f, dot1 = 0.f;
+#pragma unroll
+          for (int nh = 0; nh < 2; ++nh) {
+            const int col = 128 * nh + 32 * cg;
+            const float4* b = reinterpret_cast<const float4*>(s_bias + p.b_off[1] + col);
+            const float4* w4 = reinterpret_cast<const float4*>(s_bias + p.wd_off + col);
+            if (nh == 0) { ptx::mbar_wait(bar(B_ACC0), acc_use0 & 1); ++acc_use0; }
+            else         { ptx::mbar_wait(bar(B_ACC1), acc_use1 & 1); ++acc_use1; }
+            ptx::tc_fence_after();
+            uint32_t v[32];
+            ptx::tmem_ld32(t_acc + col, v);
+            if (!lastp) {                            // k-half nh is free: every piece that reads it is behind this commit
+              store_masked(hreg[nh], nh == 0 ? nb0 : nb1, nh);
+              ptx::tmem_ld_wait();
+              publish(nh == 0 ? B_IN0 : B_IN1);
+            } else {
+              ptx::tmem_ld_wait();
+            }
+#pragma unroll
+            for (int m = 0; m < 8; ++m) {
+              const float4 w = w4[m], bm = b[m];
+              dot0 = fmaf(fmaxf(__uint_as_float(v[4 * m]) + bm.x, 0.f), w.x, dot0);
+              dot1 = fmaf(fmaxf(__uint_as_float(v[4 * m + 1]) + bm.y, 0.f), w.y, dot1);
+              dot0 = fmaf(fmaxf(__uint_as_float(v[4 * m + 2]) + bm.z, 0.f), w.z, dot0);
+              dot1 = fmaf(fmaxf(__uint_as_float(v[4 * m + 3]) + bm.w, 0.f), w.w, dot1);
+            }
+          }
+          if (lastp) {
+            ptx::tc_fence_before();
+            if (t + n_clusters < p.T) {
+              pack_z();
+              publish(B_IN0);
+            }
+          }
+          const float dot = dot0 + dot1;
+          float* sd = s_dot + (pass & 1) * 3 * TILE;
+          if (cg) sd[(cg - 1) * TILE + row] = dot;
+          ptx::bar_sync(1, WORKERS);
+          if (cg == 0) {                             // Welford over the passes (unbiased variance, torch.var)
+            const float c = ((dot + sd[row]) + (sd[TILE + row] + sd[2 * TILE + row])) + s_bias[p.wd_off + HID];
+            const float d = c - mean;
+            mean += d / (float)(pass + 1);
+            m2 = fmaf(d, c - mean, m2);
+          }
+        }
+        if (cg == 0 && r < p.n) {
+          p.out[r] = mean;
+          if (p.var_out) p.var_out[r] = m2 / (float)(p.mc_T - 1);
+        }
+        continue;
+      }
       for (int l = 0; l < p.n_mma; ++l) {
         const bool last = l + 1 == p.n_mma;
         const uint32_t t_acc = t_lane + 256u * (lc & 1);
@@ -307,7 +463,9 @@ chain_tc_kernel(const ChainParams p) {
     // ===== MMA issuer (leader CTA) =====
     uint32_t in_use0 = 0, in_use1 = 0, lc = 0;
     for (int t = cluster; t < p.T; t += n_clusters) {
-      for (int l = 0; l < p.n_mma; ++l) {
+      const int n_issue = p.mc_T > 0 ? 1 + p.mc_T : p.n_mma;
+      for (int li = 0; li < n_issue; ++li) {
+        const int l = p.mc_T > 0 ? min(li, 1) : li;
         const int K = p.K[l], N = p.N[l];
         const int n_kh = K == HID ? 2 : 1, n_nh = N == HID ? 2 : 1;
         const int n_piece = N == HID ? 128 : N;                 // columns per MMA
@@ -371,7 +529,7 @@ int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode
       if (!(fold0 && l == 0)) b += N;
     }
     if (mode == MODE_DOT) b += HID + 4;
-    return w + 4 * ATOM + b * 4 + 64 + (mode == MODE_DOT ? 3 * TILE * 4 : 0);
+    return w + 4 * ATOM + b * 4 + 64 + (mode == MODE_DOT ? 6 * TILE * 4 : 0);
   };
   const bool fold0 = smem_need(false) > SMEM_MAX && n_mma > 1 && layers[0].in + 2 <= K0 && layers[0].out == HID &&
                      smem_need(true) <= SMEM_MAX;
@@ -400,7 +558,7 @@ int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode
   P.bias_off = P.a_off + 4 * ATOM;
   P.bias_count = boff;
   P.bar_off = P.bias_off + boff * 4;
-  cp.smem_bytes = P.bar_off + 64 + (mode == MODE_DOT ? 3 * TILE * 4 : 0);
+  cp.smem_bytes = P.bar_off + 64 + (mode == MODE_DOT ? 6 * TILE * 4 : 0);
   if (cp.smem_bytes > SMEM_MAX) return VAEX_OK;
   // the kernel relies on a 1024-byte aligned dynamic shared-memory base (no static shared memory)
   {
@@ -453,13 +611,19 @@ int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode
 }
 
 int chain_tc_run(const ChainPack& cp, const float* X, int64_t n, float* out, int32_t* extents, const float* mean,
-                 const float* scale, int snap_mode, const float* wd, const float* bd, cudaStream_t st) {
+                 const float* scale, int snap_mode, const float* wd, const float* bd, cudaStream_t st, const ChainDropout* drop) {
   using namespace ch;
   VAEX_CHECK(cp.ready, "tcgen05 chain not packed");
   if (n == 0) return VAEX_OK;
   ChainParams P = *reinterpret_cast<const ChainParams*>(cp.params_storage);
   P.X = X; P.w = cp.w; P.bias = cp.bias; P.out = out; P.extents = extents; P.snap_mean = mean; P.snap_scale = scale;
   P.snap_mode = snap_mode; P.wd = wd; P.bd = bd; P.n = n; P.T = (int)cdiv(n, PAIR);
+  P.mc_T = 0; P.drop_mask = nullptr; P.var_out = nullptr; P.drop_seed = 0; P.drop_chunk = 1; P.drop_p = 0.f; P.drop_inv = 1.f;
+  if (drop) {
+    VAEX_CHECK(P.mode == MODE_DOT && P.n_mma == 2 && drop->passes >= 1, "dropout passes need the two-layer predictor chain");
+    P.mc_T = drop->passes; P.drop_mask = drop->mask; P.var_out = drop->var_out; P.drop_seed = drop->seed;
+    P.drop_chunk = std::max<int64_t>(drop->chunk_rows, 1); P.drop_p = drop->p; P.drop_inv = 1.f / (1.f - drop->p);
+  }
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

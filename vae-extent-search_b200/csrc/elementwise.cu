@@ -7,6 +7,7 @@
 #include "common.cuh"
 #include "simt_kernels.cuh"
 #include "snap.cuh"
+#include "philox.cuh"
 
 namespace vaex {
 
@@ -100,26 +101,6 @@ int exclusive_scan_i32(const int32_t* sizes, int64_t n, int32_t* offsets, cudaSt
   VAEX_CUDA(cudaFreeAsync(bsum, st));
   return VAEX_OK;
 }
-
-// ------------------------------------------------------------------ Philox4x32-10
-struct Philox {
-  uint32_t k0, k1;
-  __device__ Philox(uint64_t seed) : k0((uint32_t)seed), k1((uint32_t)(seed >> 32)) {}
-  __device__ uint4 operator()(uint64_t ctr_lo, uint64_t ctr_hi) const {
-    uint32_t c0 = (uint32_t)ctr_lo, c1 = (uint32_t)(ctr_lo >> 32), c2 = (uint32_t)ctr_hi,
-             c3 = (uint32_t)(ctr_hi >> 32);
-    uint32_t a = k0, b = k1;
-#pragma unroll
-    for (int r = 0; r < 10; ++r) {
-      const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
-      const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
-      c0 = hi1 ^ c1 ^ a; c1 = lo1; c2 = hi0 ^ c3 ^ b; c3 = lo0;
-      a += 0x9E3779B9u; b += 0xBB67AE85u;
-    }
-    return make_uint4(c0, c1, c2, c3);
-  }
-};
-__device__ __forceinline__ float u01(uint32_t x) { return (x >> 8) * (1.0f / 16777216.0f) + (0.5f / 16777216.0f); }
 
 // z = mu + eps * exp(0.5 logvar)   (utils/model.py:58-61); 4 elements per thread
 __global__ void reparam_kernel(const float* __restrict__ mu, const float* __restrict__ logvar,

@@ -85,11 +85,19 @@ int head_tc_pack(vaex_model* m, cudaStream_t st);
 int head_tc_forward(vaex_model* m, const float* S, int64_t P, const uint8_t* valid, float* scores, cudaStream_t st);
 // chain_tc.cu
 struct ChainLayer;
+// Dropout(p) after the predictor's first ReLU, `passes` times per row on shared layer-0 activations (mc_predict):
+// mask uint8 [passes][n, 256] (1 = keep) or, when null, the Philox stream of dropout_kernel with seed + pass (re-seeded
+// every chunk_rows rows like the SIMT path); passes == 1: out = cost, else out = mean and var_out = unbiased variance
+struct ChainDropout { const uint8_t* mask; uint64_t seed; float p; int passes; int64_t chunk_rows; float* var_out; };
 int chain_tc_run(const ChainPack& cp, const float* X, int64_t n, float* out, int32_t* extents, const float* mean,
-                 const float* scale, int snap_mode, const float* wd, const float* bd, cudaStream_t st);
+                 const float* scale, int snap_mode, const float* wd, const float* bd, cudaStream_t st,
+                 const ChainDropout* drop = nullptr);
 // segsum_tc.cu
+// in_mode: 0 = fp32 rows, 1 = fp16 rows, 2 = the packed row image (rows_pack_image)
 int segsum_tc_encode(vaex_model* m, const float* feats, const int32_t* off, int64_t n_programs,
-                     int64_t n_rows, float* segsum, uint8_t* valid, cudaStream_t st, bool feats_f16 = false);
+                     int64_t n_rows, float* segsum, uint8_t* valid, cudaStream_t st, int in_mode = 0);
+int64_t rows_image_bytes(int64_t n_rows);
+int rows_pack_image(const float* feats, int64_t n_rows, int F, void* image, cudaStream_t st);
 // ascent_cluster.cu
 int ascent_cluster_run(vaex_model* m, float* z, int64_t n, int steps, float lr, float* cost, cudaStream_t st);
 // host_pack.cpp

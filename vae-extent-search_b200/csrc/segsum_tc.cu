@@ -35,12 +35,15 @@
 //
 // Programs cut by a 64-row sub-block boundary receive partial sums through atomicAdd on zeroed
 // rows (two addends when S_i <= 64: order-independent, so results are deterministic).
+#include <cuda.h>
+
 #include <algorithm>
+#include <cstring>
+#include <type_traits>
 #include <vector>
 
 #include "common.cuh"
 #include "model.cuh"
-#include <type_traits>
 #include "tc_ptx.cuh"
 
 namespace vaex {
@@ -326,10 +329,19 @@ __device__ __forceinline__ void sum_irregular(uint32_t tcol, const uint2* __rest
 }
 
 // ---------------------------------------------------------------------------------------------
-template <bool FOLD, bool HALF_IN>
+// IN: how the feature rows reach the A0 operand.
+//   IN_F32   fp32 rows [n_rows, F]: loader warps, LDG.128 -> cvt -> swizzled st.shared
+//   IN_F16   fp16 rows [n_rows, F] (the host path's narrowed chunks): loader warps, LDG.128 -> st.shared
+//   IN_IMAGE the packed fp16 row image [n_rows, 192] (vaex_rows_pack_image: bias-one columns pre-written, 384-byte
+//            pitch): ONE thread per CTA issues three TMA tensor loads per tile (cp.async.bulk.tensor.2d, 128-byte
+//            swizzle = the UMMA operand layout) that complete on the leader CTA's mbarrier; no loader warps, no
+//            format-conversion instructions, 384 instead of 656 bytes of HBM per row.
+enum { IN_F32 = 0, IN_F16 = 1, IN_IMAGE = 2 };
+template <bool FOLD, int IN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(tc::THREADS, 1)
-segsum_tc_kernel(const TcParams p) {
+segsum_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
   using namespace tc;
+  constexpr bool HALF_IN = IN == IN_F16;
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[B_COUNT];
   __shared__ uint32_t tmem_base_slot;
@@ -346,7 +358,7 @@ segsum_tc_kernel(const TcParams p) {
 
   // ---- prologue -------------------------------------------------------------------------------
   if (warp == MMA_WARP && lane == 0) {
-    ptx::mbar_init(bar(B_A0_FULL), 2 * LOAD_WARPS);
+    ptx::mbar_init(bar(B_A0_FULL), IN == IN_IMAGE ? 1 : 2 * LOAD_WARPS);   // image: the leader's arrive.expect_tx
     ptx::mbar_init(bar(B_A0_EMPTY), 1);
     ptx::mbar_init(bar(B_ACC0_FULL0), 1);
     ptx::mbar_init(bar(B_ACC0_FULL1), 1);
@@ -394,7 +406,30 @@ segsum_tc_kernel(const TcParams p) {
   const uint32_t tmem = tmem_base_slot;
 
   // ---- roles ----------------------------------------------------------------------------------
-  if (warp < LOAD_WARPS) {
+  if (IN == IN_IMAGE && warp < LOAD_WARPS) {
+    // ===== TMA producer: one thread per CTA; three [64 halves x 128 rows] boxes = the three swizzle atoms of A0 =====
+    if (warp == 0 && ptx::elect_one()) {
+      const uint32_t full_leader = ptx::mapa_rank(bar(B_A0_FULL), 0);
+      const uint32_t A0 = sbase + A0_OFF;
+      const __half* img = reinterpret_cast<const __half*>(p.feats);
+      auto prefetch = [&](int t) {                     // the CTA's half tile is one contiguous 48 KB range of the image
+        if (t >= p.T) return;
+        const int64_t r0 = (int64_t)t * PAIR + rank * TILE;
+        ptx::prefetch_l2_bulk(img + r0 * K0P, (uint32_t)(TILE * K0P * 2));   // the image is padded to whole pair tiles
+      };
+      ptx::tma_prefetch_desc(&tmap);
+      prefetch(cluster + n_clusters);
+      int it = 0;
+      for (int t = cluster; t < p.T; t += n_clusters, ++it) {
+        if (it > 0) ptx::mbar_wait(bar(B_A0_EMPTY), (it - 1) & 1);      // layer 0 of the previous tile has read A0
+        const int row0 = t * PAIR + (int)rank * TILE;
+#pragma unroll
+        for (int a = 0; a < 3; ++a) ptx::tma_load_2d_2cta(A0 + a * ATOM, &tmap, full_leader, 64 * a, row0);
+        if (rank == 0) ptx::mbar_arrive_expect_tx(bar(B_A0_FULL), 2 * A0_BYTES);   // both CTAs' boxes land on this barrier
+        prefetch(t + 2 * n_clusters);
+      }
+    }
+  } else if (warp < LOAD_WARPS) {
     // ===== loaders: fp32 rows -> fp16 swizzled A0; 16 rows per warp =====
     constexpr int ROWS = TILE / LOAD_WARPS;
     const uint32_t A0 = sbase + A0_OFF;
@@ -737,18 +772,105 @@ int tc_pack(vaex_model* m, const std::vector<float>& w0, cudaStream_t st) {
   VAEX_CUDA(cudaMemcpyAsync(t.w1, i1.data(), 2 * W1_BYTES, cudaMemcpyHostToDevice, st));
   VAEX_CUDA(cudaMemcpyAsync(t.b1, m->host["segment_encoder.2.bias"].v.data(), HID * sizeof(float), cudaMemcpyHostToDevice, st));
   VAEX_CUDA(cudaStreamSynchronize(st));
-  VAEX_CUDA(cudaFuncSetAttribute(segsum_tc_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_DYN));
-  VAEX_CUDA(cudaFuncSetAttribute(segsum_tc_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_DYN));
-  VAEX_CUDA(cudaFuncSetAttribute(segsum_tc_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_DYN));
-  VAEX_CUDA(cudaFuncSetAttribute(segsum_tc_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_DYN));
+  VAEX_CUDA(cudaFuncSetAttribute(segsum_tc_kernel<true, IN_F32>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_DYN));
+  VAEX_CUDA(cudaFuncSetAttribute(segsum_tc_kernel<false, IN_F32>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_DYN));
+  VAEX_CUDA(cudaFuncSetAttribute(segsum_tc_kernel<true, IN_F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_DYN));
+  VAEX_CUDA(cudaFuncSetAttribute(segsum_tc_kernel<false, IN_F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_DYN));
+  VAEX_CUDA(cudaFuncSetAttribute(segsum_tc_kernel<true, IN_IMAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_DYN));
   t.F = F;
   t.K0P = K0P;
   t.ready = true;
   return VAEX_OK;
 }
 
+// ---------------------------------------------------------------------------------------------
+// The packed row image (IN_IMAGE): fp16 [n_rows, 192] with a 384-byte pitch -- columns [0, F) the features (saturated,
+// round to nearest even: what the loader warps produce on the fly), F and F + 1 the constant 1 that multiplies the b0
+// hi / lo columns of the W0 image, 176 and 177 the constant 1 of the b1 k-step, everything else 0 -- followed by the
+// per-row "has a non-zero feature" bits (uint32 words; taken from the fp32 values, so a value that rounds to an fp16
+// zero still counts: MLPModel.predict's rule, mlp_model.py:842-844).  One 16-byte store per thread.
+// One CTA = 32 rows x 24 chunks of 8 halves = one word of the non-zero mask: a 16-byte store per thread, one shared
+// atomic per warp-row, one plain store of the mask word (no global atomics, no memset).
+constexpr int PACK_THREADS = 32 * (tc::K0P / 8);        // 768
+__global__ void __launch_bounds__(PACK_THREADS) rows_pack_image_kernel(const float* __restrict__ feats, int64_t n_rows, int F,
+                                                                    uint4* __restrict__ img, uint32_t* __restrict__ rowmask) {
+  constexpr int CH = tc::K0P / 8;
+  __shared__ uint32_t word;
+  if (threadIdx.x == 0) word = 0;
+  __syncthreads();
+  const int rl = threadIdx.x / CH, c = threadIdx.x - rl * CH;
+  const int64_t row = (int64_t)blockIdx.x * 32 + rl;
+  const float* src = feats + row * F;
+  uint32_t w[4], any = 0;
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    float v[2];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      const int col = 8 * c + 2 * e + i;
+      float x = 0.f;
+      if (col < F) { if (row < n_rows) { x = __ldg(src + col); any |= __float_as_uint(x) << 1; } }
+      else if (col == F || col == F + 1 || col == tc::B1_COL || col == tc::B1_COL + 1) x = 1.f;
+      v[i] = x;
+    }
+    w[e] = ptx::cvt_h2_sat(v[0], v[1]);
+  }
+  img[(size_t)row * CH + c] = make_uint4(w[0], w[1], w[2], w[3]);
+  if (any) atomicOr(&word, 1u << rl);
+  __syncthreads();
+  if (threadIdx.x == 0) rowmask[blockIdx.x] = word;
+}
+
+// The image is padded to whole 256-row pair tiles and the pad rows carry the bias-one columns too: a tile load never
+// runs out of bounds.  (It must not: layer 1 of tile t still reads the b1 k-step of A0 -- columns 176, 177, the same
+// values in every row of every tile -- while the loads of tile t + 1 land; an out-of-bounds row would arrive as zeros and
+// take the bias away from the previous tile's row.)
+static int64_t image_rows_padded(int64_t n_rows) { return (n_rows + tc::PAIR - 1) / tc::PAIR * tc::PAIR; }
+static size_t image_rows_bytes(int64_t n_rows) { return (size_t)image_rows_padded(n_rows) * tc::K0P * sizeof(__half); }
+int64_t rows_image_bytes(int64_t n_rows) {
+  return (int64_t)(image_rows_bytes(n_rows) + sizeof(uint32_t) * (size_t)((n_rows + 255) / 256) * 8);
+}
+
+int rows_pack_image(const float* feats, int64_t n_rows, int F, void* image, cudaStream_t st) {
+  using namespace tc;
+  VAEX_CHECK(F >= 1 && F + 2 <= B1_COL, "the row image holds 1..174 features");
+  VAEX_CHECK(n_rows >= 0 && n_rows < (1ll << 31) - PAIR, "row count exceeds int32 indexing");
+  if (n_rows == 0) return VAEX_OK;
+  VAEX_CHECK(feats && image && (reinterpret_cast<uintptr_t>(image) & 127) == 0, "image_dev must be 128-byte aligned");
+  uint32_t* mask = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(image) + image_rows_bytes(n_rows));
+  const int64_t n_pad = image_rows_padded(n_rows);
+  rows_pack_image_kernel<<<(unsigned)(n_pad / 32), PACK_THREADS, 0, st>>>(feats, n_rows, F, reinterpret_cast<uint4*>(image), mask);
+  VAEX_LAUNCH_CHECK();
+  return VAEX_OK;
+}
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time dependency on libcuda)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static int image_tensor_map(const void* image, int64_t n_rows, CUtensorMap* out) {
+  using namespace tc;
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    VAEX_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
+    VAEX_CHECK(p && q == cudaDriverEntryPointSuccess, "cuTensorMapEncodeTiled is not available in this driver");
+    fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  const cuuint64_t dims[2] = {(cuuint64_t)K0P, (cuuint64_t)image_rows_padded(n_rows)};   // innermost first; rows padded: no OOB
+  const cuuint64_t strides[1] = {(cuuint64_t)K0P * sizeof(__half)};        // bytes between rows
+  const cuuint32_t box[2] = {64, (cuuint32_t)TILE};                        // one 128-byte-swizzle atom: 64 halves x 128 rows
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(image), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r)); return VAEX_E_CUDA; }
+  return VAEX_OK;
+}
+
 int segsum_tc_encode(vaex_model* m, const float* feats, const int32_t* off, int64_t P, int64_t R, float* segsum,
-                     uint8_t* valid, cudaStream_t st, bool feats_f16) {
+                     uint8_t* valid, cudaStream_t st, int in_mode) {
   using namespace tc;
   VAEX_CHECK(m->tc.ready, "tcgen05 weights not packed");
   VAEX_CHECK(P < (1ll << 31) && R < (1ll << 31) - PAIR, "sizes exceed int32 row indexing");
@@ -774,13 +896,23 @@ int segsum_tc_encode(vaex_model* m, const float* feats, const int32_t* off, int6
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int clusters = std::max(1, std::min(sms / 2, T));
-    if (feats_f16) {
+    CUtensorMap tmap;
+    memset(&tmap, 0, sizeof(tmap));
+    if (in_mode == IN_IMAGE) {
+      VAEX_CHECK(fold, "the row image needs F <= 174");
+      VAEX_CHECK((reinterpret_cast<uintptr_t>(feats) & 127) == 0, "the row image must be 128-byte aligned");
+      TRY(image_tensor_map(feats, R, &tmap));
+      // the non-zero bits were taken from the fp32 rows when the image was packed
+      rowmask = reinterpret_cast<uint32_t*>(const_cast<uint8_t*>(reinterpret_cast<const uint8_t*>(feats)) + image_rows_bytes(R));
+      prm.rowmask = rowmask;
+      segsum_tc_kernel<true, IN_IMAGE><<<2 * clusters, THREADS, SMEM_DYN, st>>>(prm, tmap);
+    } else if (in_mode == IN_F16) {
       VAEX_CHECK(m->F % 4 == 0 && (reinterpret_cast<uintptr_t>(feats) & 15) == 0,
                  "fp16 features need F % 4 == 0 and a 16-byte aligned pointer");
-      if (fold) segsum_tc_kernel<true, true><<<2 * clusters, THREADS, SMEM_DYN, st>>>(prm);
-      else segsum_tc_kernel<false, true><<<2 * clusters, THREADS, SMEM_DYN, st>>>(prm);
-    } else if (fold) segsum_tc_kernel<true, false><<<2 * clusters, THREADS, SMEM_DYN, st>>>(prm);
-    else segsum_tc_kernel<false, false><<<2 * clusters, THREADS, SMEM_DYN, st>>>(prm);
+      if (fold) segsum_tc_kernel<true, IN_F16><<<2 * clusters, THREADS, SMEM_DYN, st>>>(prm, tmap);
+      else segsum_tc_kernel<false, IN_F16><<<2 * clusters, THREADS, SMEM_DYN, st>>>(prm, tmap);
+    } else if (fold) segsum_tc_kernel<true, IN_F32><<<2 * clusters, THREADS, SMEM_DYN, st>>>(prm, tmap);
+    else segsum_tc_kernel<false, IN_F32><<<2 * clusters, THREADS, SMEM_DYN, st>>>(prm, tmap);
     VAEX_LAUNCH_CHECK();
   }
   if (valid) {

@@ -101,6 +101,30 @@ __device__ __forceinline__ void mbar_arrive_cluster_relaxed(uint32_t bar, uint32
       : "memory");
 }
 
+// ---- TMA (cp.async.bulk.tensor) ---------------------------------------------------------------
+// shared::cluster address of `addr` (a shared::cta address of this CTA) in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t mapa_rank(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+// one arrival + `bytes` expected transaction bytes on a barrier of this CTA
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// 2-D tiled tensor load global -> this CTA's shared memory; the completion bytes are posted on `bar_cluster`, a
+// shared::cluster address that may name the PEER CTA's barrier (cta_group::2: both CTAs of a pair signal the leader's
+// barrier, cute::SM100_TMA_2SM_LOAD_2D).  c0 = innermost coordinate (elements), c1 = row.
+__device__ __forceinline__ void tma_load_2d_2cta(uint32_t dst_smem, const void* tmap, uint32_t bar_cluster, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst_smem), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar_cluster), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const void* tmap) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tmap)) : "memory");
+}
+
 // ---- proxies / tcgen05 fences --------------------------------------------------------------
 __device__ __forceinline__ void fence_proxy_async() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");

@@ -136,6 +136,26 @@ class SegmentDataLoader:
         return self.number
 
 
+class RowsImage:
+    """A pool's feature rows packed once for repeated scoring (vaex_rows_pack_image): fp16 [n_rows, 192] with the
+    bias-one columns in place + the per-row non-zero bits.  SegmentSumMLPModule.forward / segment_sums take it in place
+    of the fp32 feature tensor; the row encoder then loads its operand tiles with TMA.  Same scores bit for bit."""
+
+    def __init__(self, features, in_dim=None):
+        if not features.is_cuda:
+            raise _lib.VaexError("RowsImage needs a CUDA tensor (no CPU fallback)")
+        feats = features.detach().contiguous().float()
+        self.n_rows, self.in_dim = int(feats.shape[0]), int(in_dim or feats.shape[1])
+        lib = _lib.load()
+        nbytes = int(lib.vaex_rows_image_bytes(self.n_rows))
+        self.data = torch.empty(max(nbytes, 128), dtype=torch.uint8, device=feats.device)
+        _lib.check(lib.vaex_rows_pack_image(_lib.ptr(feats), self.n_rows, self.in_dim, _lib.ptr(self.data), _lib.stream_ptr()))
+
+    @property
+    def device(self):
+        return self.data.device
+
+
 class SegmentSumMLPModule(torch.nn.Module):
     """mlp_model.py:147-221.  Parameters live in the same nn.Linear modules (identical
     state_dict keys, so reference pickles / checkpoints load); forward() runs the fused
@@ -219,21 +239,25 @@ class SegmentSumMLPModule(torch.nn.Module):
             raise _lib.VaexError("SegmentSumMLPModule.forward builds no autograd graph: train with "
                                  "MLPModelInternal.fit_base / fit_local or vaex_b200.train.Trainer "
                                  "(vaex_trainer_forward_backward), or call under torch.no_grad() / .eval() to score")
-        if not features.is_cuda:
+        if isinstance(features, RowsImage):
+            feats, n_rows, flags = features.data, features.n_rows, flags | _lib.F_FEATS_IMAGE
+        elif not features.is_cuda:
             raise _lib.VaexError("SegmentSumMLPModule.forward needs CUDA tensors (no CPU fallback)")
-        lib = _lib.load()
-        m = self.packed(fea_norm_vec)
-        if features.dtype == torch.float16:      # rows already narrowed (the tcgen05 kernel rounds to fp16 first anyway)
+        elif features.dtype == torch.float16:      # rows already narrowed (the tcgen05 kernel rounds to fp16 first anyway)
             feats, flags = features.detach().contiguous(), flags | _lib.F_FEATS_F16
+            n_rows = feats.shape[0]
         else:
             feats = features.detach().contiguous().float()
+            n_rows = feats.shape[0]
+        lib = _lib.load()
+        m = self.packed(fea_norm_vec)
         sizes = segment_sizes.detach().to(device=feats.device, dtype=torch.int32).contiguous()
         n = sizes.shape[0]
         offsets = torch.empty(n + 1, dtype=torch.int32, device=feats.device)
         scores = torch.empty(n, dtype=torch.float32, device=feats.device)
         st = _lib.stream_ptr()
         _lib.check(lib.vaex_segment_offsets(_lib.ptr(sizes), n, _lib.ptr(offsets), st))
-        _lib.check(lib.vaex_segsum_mlp_forward(m.h, _lib.ptr(feats), _lib.ptr(offsets), n, feats.shape[0],
+        _lib.check(lib.vaex_segsum_mlp_forward(m.h, _lib.ptr(feats), _lib.ptr(offsets), n, n_rows,
                                                 _lib.ptr(scores), flags, st))
         return scores.squeeze()
 
@@ -241,18 +265,22 @@ class SegmentSumMLPModule(torch.nn.Module):
         """[n_programs, hidden] per-program sums of the row encoder's output -- the tensor
         `scatter_add(...)` produces at mlp_model.py:200-208 (and SegmentVAE.segment_sum,
         scripts/vae_experiments/models/vae.py:68-85)."""
-        if not features.is_cuda:
+        if isinstance(features, RowsImage):
+            feats, n_rows, flags = features.data, features.n_rows, flags | _lib.F_FEATS_IMAGE
+        elif not features.is_cuda:
             raise _lib.VaexError("SegmentSumMLPModule.segment_sums needs CUDA tensors (no CPU fallback)")
+        else:
+            feats = features.detach().contiguous().float()
+            n_rows = feats.shape[0]
         lib = _lib.load()
         m = self.packed(fea_norm_vec)
-        feats = features.detach().contiguous().float()
         sizes = segment_sizes.detach().to(device=feats.device, dtype=torch.int32).contiguous()
         n = sizes.shape[0]
         offsets = torch.empty(n + 1, dtype=torch.int32, device=feats.device)
         out = torch.empty(n, self.segment_encoder[0].out_features, dtype=torch.float32, device=feats.device)
         st = _lib.stream_ptr()
         _lib.check(lib.vaex_segment_offsets(_lib.ptr(sizes), n, _lib.ptr(offsets), st))
-        _lib.check(lib.vaex_segsum_encode(m.h, _lib.ptr(feats), _lib.ptr(offsets), n, feats.shape[0], _lib.ptr(out), flags, st))
+        _lib.check(lib.vaex_segsum_encode(m.h, _lib.ptr(feats), _lib.ptr(offsets), n, n_rows, _lib.ptr(out), flags, st))
         return out
 
 

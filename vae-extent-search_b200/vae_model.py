@@ -246,10 +246,16 @@ class VAECostPredictor(_Packed, nn.Module):
         mu, _ = self._encode(input_tensor, want_logvar=False)
         if seed is None:
             seed = int(torch.randint(1, 2 ** 62, (1,)).item())
-        preds = torch.stack([
-            self.predict_cost(mu, drop_mask=None if masks is None else masks[t], drop_seed=0 if masks is not None else seed + t)
-            for t in range(T)], dim=0)
-        return preds.mean(dim=0), preds.var(dim=0)
+        n = mu.shape[0]
+        mean, var = torch.empty(n, device=mu.device), torch.empty(n, device=mu.device)
+        mk = None
+        if masks is not None:
+            mk = masks.to(device=mu.device, dtype=torch.uint8).contiguous()
+            if mk.shape[0] < T:
+                raise ValueError("masks holds %d passes, T = %d" % (mk.shape[0], T))
+        _lib.check(_lib.load().vaex_mc_predict_cost(self.packed().h, _lib.ptr(mu), n, int(T), _lib.ptr(mk), 0 if mk is not None else int(seed),
+                                                   float(self.cost_predictor[2].p), _lib.ptr(mean), _lib.ptr(var), _lib.stream_ptr()))
+        return mean, var
 
     def cost_grad_z(self, z):
         """(cost, d cost.sum()/d z, ||grad||_2 per row) in one call (select_topk_z_grad, select.py:111-148)."""
