@@ -303,10 +303,25 @@ def main_vaex(args):
         _lib.check(lib.vaex_decode_snap(vmodel.h, _lib.ptr(zz), n, None, _lib.ptr(out), _lib.ptr(mean_d), _lib.ptr(scale_d), SNAP,
                                         _lib.ptr(ext_d), _lib.ptr(last_d), 64, st))
 
+    # The pool's rows are packed ONCE into the fp16 row image (vaex_rows_pack_image) and scored from it every step: the
+    # candidates of an active-learning search do not change between scoring rounds, only the model does
+    # (vae_extent_search.py:1720-1889).  The row encoder rounds fp32 rows to fp16 before its first MMA in any case, so the
+    # scores are bit-identical (asserted below); the step from the fp32 rows is timed beside it (value_fp32_rows).
+    image = torch.empty(int(lib.vaex_rows_image_bytes(rows)), dtype=torch.uint8, device=dev)
+    pk0, pk1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    _lib.check(lib.vaex_rows_pack_image(_lib.ptr(feats), rows, F, _lib.ptr(image), st))
+    pk0.record(stream)
+    _lib.check(lib.vaex_rows_pack_image(_lib.ptr(feats), rows, F, _lib.ptr(image), st))
+    pk1.record(stream)
+    torch.cuda.synchronize()
+    pack_ms = pk0.elapsed_time(pk1)
+    row_src = {"buf": image, "flags": flags | _lib.F_FEATS_IMAGE}
+
     def step():
         decode_stage(z, extents, P)
         _lib.check(lib.vaex_segment_offsets(_lib.ptr(sizes_d), P, _lib.ptr(offsets), st))
-        _lib.check(lib.vaex_segsum_mlp_forward(model.h, _lib.ptr(feats), _lib.ptr(offsets), P, rows, _lib.ptr(scores), flags, st))
+        _lib.check(lib.vaex_segsum_mlp_forward(model.h, _lib.ptr(row_src["buf"]), _lib.ptr(offsets), P, rows, _lib.ptr(scores),
+                                               row_src["flags"], st))
         _lib.check(lib.vaex_topk(_lib.ptr(scores), P, TOPK, None, _lib.ptr(top_v), _lib.ptr(top_i), _lib.ptr(n_out), st))
         if world > 1:       # candidate merge: the path's only exchange (one ncclAllGather of 16-byte records + one merge CTA)
             _lib.check(lib.vaex_topk_allgather_merge(comm.h, _lib.ptr(top_v), _lib.ptr(top_i), _lib.ptr(n_out), TOPK, rank * P,
@@ -333,6 +348,14 @@ def main_vaex(args):
     for _ in range(max(args.warmup, 3)):
         step()
     barrier()
+    # the same step from the fp32 rows: bit-identical scores
+    sc_img = scores.clone()
+    row_src.update(buf=feats, flags=flags)
+    step()
+    torch.cuda.synchronize()
+    assert torch.equal(sc_img.view(torch.int32), scores.view(torch.int32)), "row image and fp32 rows disagree"
+    row_src.update(buf=image, flags=flags | _lib.F_FEATS_IMAGE)
+    del sc_img
     # sanity: invalid programs are -inf, everything else finite
     sc = scores.cpu().numpy()
     assert np.isneginf(sc[bad]).all() and np.isfinite(np.delete(sc, bad)).all(), "bad scores"
@@ -368,6 +391,22 @@ def main_vaex(args):
     launches = lib.vaex_launch_count() - l0
     ms = e0.elapsed_time(e1) / args.steps
     torch.cuda.cudart().cudaProfilerStop()
+    # the same timed loop with the rows resident as fp32 (loader warps instead of TMA)
+    row_src.update(buf=feats, flags=flags)
+    step()
+    barrier()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record(stream)
+    for _ in range(args.steps):
+        step()
+    f1.record(stream)
+    barrier()
+    ms_f32 = f0.elapsed_time(f1) / args.steps
+    row_src.update(buf=image, flags=flags | _lib.F_FEATS_IMAGE)
+    tf = torch.tensor([ms_f32], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(tf, op=dist.ReduceOp.MAX)
+    ms_f32 = float(tf.item())
 
     t = torch.tensor([ms], device=dev, dtype=torch.float64)
     ms_ranks = [ms]
@@ -392,8 +431,10 @@ def main_vaex(args):
     it = max(3, min(args.steps, 10))
     segsum = torch.empty(P, H, device=dev)
     sampler.active = True
-    kms = timed(lambda: _lib.check(lib.vaex_segsum_encode(model.h, _lib.ptr(feats), _lib.ptr(offsets), P, rows, _lib.ptr(segsum), 0, st)), it)
+    kms = timed(lambda: _lib.check(lib.vaex_segsum_encode(model.h, _lib.ptr(image), _lib.ptr(offsets), P, rows, _lib.ptr(segsum),
+                                                          _lib.F_FEATS_IMAGE, st)), it)
     sampler.active = False
+    kms_f32 = timed(lambda: _lib.check(lib.vaex_segsum_encode(model.h, _lib.ptr(feats), _lib.ptr(offsets), P, rows, _lib.ptr(segsum), 0, st)), it)
     kernels = []
 
     def tensor_entry(name, ms_, flop, note):
@@ -406,7 +447,10 @@ def main_vaex(args):
         kernels.append({"kernel": name, "bound": "hbm", "ms": ms_, "achieved": ach, "peak": hpeak, "unit": "GB/s",
                         "frac": ach / hpeak, "work": note})
 
-    tensor_entry("segsum_tc_kernel (row encoder + segment sum)", kms, rows * FLOP_PER_ROW, "%d rows x 215 040 FLOP" % rows)
+    tensor_entry("segsum_tc_kernel<IN_IMAGE> (row encoder + segment sum, TMA-fed from the row image)", kms, rows * FLOP_PER_ROW,
+                 "%d rows x 215 040 FLOP" % rows)
+    tensor_entry("segsum_tc_kernel<IN_F32> (same, fp32 rows through loader warps)", kms_f32, rows * FLOP_PER_ROW,
+                 "%d rows x 215 040 FLOP" % rows)
     if not args.no_kernels:
         valid = torch.ones(P, dtype=torch.uint8, device=dev)
         hms = timed(lambda: _lib.check(lib.vaex_segsum_head(model.h, _lib.ptr(segsum), P, _lib.ptr(valid), _lib.ptr(scores), 0, st)), it)
@@ -613,21 +657,25 @@ def main_vaex(args):
                 pass
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-            "ms_per_step": ms_max, "ms_per_step_ranks": ms_ranks, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": ms_max, "ms_per_step_ranks": ms_ranks, "value_fp32_rows": world * P / (ms_f32 * 1e-3),
+            "ms_per_step_fp32_rows": ms_f32, "rows_pack_ms": pack_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f16xf16->f32",
             "data": "synthetic",
             "config": {"workload": WORKLOAD, "programs_per_gpu": P, "rows_per_gpu": rows, "features": F, "hidden": H,
                        "latent": L_LAT, "extent_slots": D_EXT, "topk": TOPK,
                        "step": "decode + snap + divisor legalise (P latents) -> offsets scan -> row encoder + segment sum -> head "
                                "-> top-k (-> all-gather merge at N > 1)",
-                       "l2": "inputs (%.1f GB/GPU) exceed L2; no flush needed" % (rows * F * 4 / 1e9),
+                       "rows": "fp16 row image [rows, 192] (%.1f GB/GPU), packed once per pool from the fp32 rows by "
+                               "vaex_rows_pack_image (%.2f ms, outside the step: the pool is static across scoring rounds); scores "
+                               "bit-identical with the fp32-row path, which is timed in value_fp32_rows" % (image.numel() / 1e9, pack_ms),
+                       "l2": "inputs (%.1f GB/GPU) exceed L2; no flush needed" % (image.numel() / 1e9),
                        "parallelism": "candidates sharded over %d GPU(s); top-k all-gather merge only" % world,
                        "merged_equals_global_topk": merged_ok},
             "e2e": e2e, "gpu_launches": int(launches), "clocks": sampler.summary(),
             "roofline": {"bound": "tensor", "achieved": ach, "peak": tpeak, "unit": "TFLOP/s", "frac": ach / tpeak,
-                         "traffic": traffic, "kernel": "segsum_tc_kernel (fused row encoder + segment sum)",
+                         "traffic": traffic, "kernel": "segsum_tc_kernel<IN_IMAGE> (fused row encoder + segment sum, TMA-fed)",
                          "kernel_ms": kms, "flop_per_launch": rows * FLOP_PER_ROW, "peak_source": peak_src,
-                         "hbm_gbs_algorithmic": (rows * F * 4 + P * H * 4) / (kms * 1e-3) / 1e9},
+                         "hbm_gbs_algorithmic": (rows * 384 + P * H * 4) / (kms * 1e-3) / 1e9},
             "roofline_kernels": kernels, "configs": configs, "parity": parity,
         }
         if cpu_baseline:

@@ -472,6 +472,20 @@ def test_snap_bit_exact_and_legalise():
     exact1 = np.maximum(np.rint(np.expm1(adv.astype(np.float64)).astype(np.float32)), 1).astype(np.int32)
     got1 = vaex_b200.snap_extents(torch.from_numpy(adv).cuda(), zero, one, log1p=True).cpu().numpy()
     assert np.array_equal(got1, exact1)
+    # the same around the boundaries of the expm1 form: expm1(v) = k + 0.5
+    base1 = np.log1p(k + 0.5).astype(np.float32)
+    adv1 = np.stack([base1] + [np.nextafter(base1, np.float32(s_)) for s_ in (np.inf, -np.inf)], 1)
+    for _ in range(2):
+        adv1 = np.concatenate([adv1, np.nextafter(adv1[:, -2:-1], np.float32(np.inf)), np.nextafter(adv1[:, -1:], np.float32(-np.inf))], 1)
+    adv1 = np.ascontiguousarray(adv1.astype(np.float32))
+    ex1 = np.maximum(np.rint(np.expm1(adv1.astype(np.float64)).astype(np.float32)), 1).astype(np.int32)
+    assert np.array_equal(vaex_b200.snap_extents(torch.from_numpy(adv1).cuda(), zero, one, log1p=True).cpu().numpy(), ex1)
+    # large and negative arguments, both modes
+    wide = np.linspace(-30, 25, 400001).astype(np.float32).reshape(-1, 7)
+    for l1p, fn in ((False, np.exp), (True, np.expm1)):
+        r64 = np.rint(fn(wide.astype(np.float64)).astype(np.float32))
+        exw = np.where(r64 < 2147483648.0, np.maximum(r64, 1), 1).astype(np.int32)
+        assert np.array_equal(vaex_b200.snap_extents(torch.from_numpy(wide).cuda(), zero, one, log1p=l1p).cpu().numpy(), exw)
     # (torch's vectorised CPU expf is a 1-ulp routine, so on boundary cases it may itself differ from the exact result)
     assert (O.snap_round_clamp(adv, zero, one).numpy() != exact).mean() < 0.02
     # divisor legalisation against the utils.cc:446-463 restatement; task-1264-like loop bounds
@@ -668,7 +682,12 @@ def test_select_uncertainty_matches_reference():
         reg.set_tensor_cores(tc)
         x = torch.from_numpy(g["x"]).cuda()
         mc_mean, mc_var = reg.mc_predict(x, T=T, masks=masks)
-        np.testing.assert_allclose(mc_mean.cpu().numpy(), u["mc_mean"], rtol=1e-3 if tc else 2e-5, atol=1e-5 if tc else 2e-6)
+        if tc:        # two chained fp16-operand kernels (encode, then the MC predictor): norm-wise 2e-3, worst 6e-3 of the RMS
+            dm = mc_mean.cpu().numpy() - u["mc_mean"]
+            assert np.linalg.norm(dm) / np.linalg.norm(u["mc_mean"]) < 2e-3
+            assert np.abs(dm).max() < 6e-3 * np.sqrt((u["mc_mean"] ** 2).mean())
+        else:
+            np.testing.assert_allclose(mc_mean.cpu().numpy(), u["mc_mean"], rtol=2e-5, atol=2e-6)
         if not tc:
             np.testing.assert_allclose(mc_var.cpu().numpy(), u["mc_var"], rtol=2e-3, atol=1e-9)
             sel, rem_after = vaex_b200.select.select_topk_uncertainty(reg, x, set(rem), 24, T_mc=T, mc_masks=masks)

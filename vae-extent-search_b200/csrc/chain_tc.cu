@@ -174,7 +174,8 @@ chain_tc_kernel(const ChainParams p) {
     const bool vec_ok = (p.out_dim & 3) == 0 &&
         ((reinterpret_cast<uintptr_t>(p.out) | reinterpret_cast<uintptr_t>(p.extents) | reinterpret_cast<uintptr_t>(p.snap_mean) |
           reinterpret_cast<uintptr_t>(p.snap_scale)) & 15) == 0;
-    const bool vec8_ok = (p.out_dim & 7) == 0 && ((reinterpret_cast<uintptr_t>(p.out) | reinterpret_cast<uintptr_t>(p.extents)) & 31) == 0;
+    const bool vec8_ok = (p.out_dim & 7) == 0 && ((reinterpret_cast<uintptr_t>(p.out) | reinterpret_cast<uintptr_t>(p.extents)) & 31) == 0 &&
+        ((reinterpret_cast<uintptr_t>(p.snap_mean) | reinterpret_cast<uintptr_t>(p.snap_scale)) & 15) == 0;
     uint32_t acc_use0 = 0, acc_use1 = 0, lc = 0;
     fetch(cluster);
     if (cluster < p.T) {
@@ -419,8 +420,8 @@ chain_tc_kernel(const ChainParams p) {
                                        y[8 * j + 5], y[8 * j + 6], y[8 * j + 7]);
                 if (p.extents) {
                   int q[8];
-#pragma unroll
-                  for (int e = 0; e < 8; ++e) q[e] = snap_one(y[8 * j + e], __ldg(p.snap_mean + c + e), __ldg(p.snap_scale + c + e), p.snap_mode);
+                  const float y8[8] = {y[8 * j], y[8 * j + 1], y[8 * j + 2], y[8 * j + 3], y[8 * j + 4], y[8 * j + 5], y[8 * j + 6], y[8 * j + 7]};
+                  snap_vec8(y8, p.snap_mean + c, p.snap_scale + c, p.snap_mode, q);
                   ptx::stg_i8(p.extents + r * p.out_dim + c, q[0], q[1], q[2], q[3], q[4], q[5], q[6], q[7]);
                 }
               }

@@ -366,8 +366,8 @@ segsum_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
     ptx::mbar_init(bar(B_A1_FULL1), 2 * 4);
     ptx::mbar_init(bar(B_ACC1_FULL0), 1);
     ptx::mbar_init(bar(B_ACC1_FULL1), 1);
-    ptx::mbar_init(bar(B_ACC1_EMPTY0), 2 * 4);
-    ptx::mbar_init(bar(B_ACC1_EMPTY1), 2 * 4);
+    ptx::mbar_init(bar(B_ACC1_EMPTY0), IN == IN_IMAGE ? 2 * 8 : 2 * 4);    // epi-1 warps of the block, both CTAs
+    ptx::mbar_init(bar(B_ACC1_EMPTY1), IN == IN_IMAGE ? 2 * 8 : 2 * 4);
     ptx::fence_mbar_init();
   }
   if (warp == EPI1_WARP0) ptx::tmem_alloc_2cta(ptx::smem_u32(&tmem_base_slot), 512);
@@ -406,30 +406,7 @@ segsum_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
   const uint32_t tmem = tmem_base_slot;
 
   // ---- roles ----------------------------------------------------------------------------------
-  if (IN == IN_IMAGE && warp < LOAD_WARPS) {
-    // ===== TMA producer: one thread per CTA; three [64 halves x 128 rows] boxes = the three swizzle atoms of A0 =====
-    if (warp == 0 && ptx::elect_one()) {
-      const uint32_t full_leader = ptx::mapa_rank(bar(B_A0_FULL), 0);
-      const uint32_t A0 = sbase + A0_OFF;
-      const __half* img = reinterpret_cast<const __half*>(p.feats);
-      auto prefetch = [&](int t) {                     // the CTA's half tile is one contiguous 48 KB range of the image
-        if (t >= p.T) return;
-        const int64_t r0 = (int64_t)t * PAIR + rank * TILE;
-        ptx::prefetch_l2_bulk(img + r0 * K0P, (uint32_t)(TILE * K0P * 2));   // the image is padded to whole pair tiles
-      };
-      ptx::tma_prefetch_desc(&tmap);
-      prefetch(cluster + n_clusters);
-      int it = 0;
-      for (int t = cluster; t < p.T; t += n_clusters, ++it) {
-        if (it > 0) ptx::mbar_wait(bar(B_A0_EMPTY), (it - 1) & 1);      // layer 0 of the previous tile has read A0
-        const int row0 = t * PAIR + (int)rank * TILE;
-#pragma unroll
-        for (int a = 0; a < 3; ++a) ptx::tma_load_2d_2cta(A0 + a * ATOM, &tmap, full_leader, 64 * a, row0);
-        if (rank == 0) ptx::mbar_arrive_expect_tx(bar(B_A0_FULL), 2 * A0_BYTES);   // both CTAs' boxes land on this barrier
-        prefetch(t + 2 * n_clusters);
-      }
-    }
-  } else if (warp < LOAD_WARPS) {
+  if (IN != IN_IMAGE && warp < LOAD_WARPS) {
     // ===== loaders: fp32 rows -> fp16 swizzled A0; 16 rows per warp =====
     constexpr int ROWS = TILE / LOAD_WARPS;
     const uint32_t A0 = sbase + A0_OFF;
@@ -482,7 +459,7 @@ segsum_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
         publish(t, al8 ? load_convert_rows<2>(p, A0, row0, warp * ROWS, lane) : load_convert_rows<1>(p, A0, row0, warp * ROWS, lane));
       }
     }
-  } else if (warp < EPI1_WARP0) {
+  } else if (warp >= LOAD_WARPS && warp < EPI1_WARP0) {
     // ===== epi 0: acc0 -> ReLU -> fp16 -> A1 (K-major, 128B swizzle); lane = tile row =====
     const int q = warp & 3;
     const uint32_t lane_base = (uint32_t)(32 * q) << 16;
@@ -536,8 +513,14 @@ segsum_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
     // Two groups of four warps (one per TMEM lane quarter); group g drains block g while the
     // tensor pipe fills the other one.  One loop body per 32 columns (two instantiations of the
     // statically indexed 16-column code, ping-pong TMEM loads), four steps per block.
+    // IN_IMAGE: the eight former loader warps drain too -- sixteen warps, four per (block g, sub-block h): a warp
+    // walks 64 columns instead of 128, which halves the drain latency that bounds the tile period.
     const int q = warp & 3;
-    const int g = (warp - EPI1_WARP0) >> 2;
+    const int e1 = warp < LOAD_WARPS ? warp : warp - (EPI1_WARP0 - LOAD_WARPS);   // image: 0..15; else 8..15
+    const int g = IN == IN_IMAGE ? (e1 >> 2) & 1 : (warp - EPI1_WARP0) >> 2;
+    const int s_begin = IN == IN_IMAGE ? 2 * (e1 >> 3) : 0, s_end = IN == IN_IMAGE ? s_begin + 2 : 4;
+    constexpr int GROUP_THREADS = IN == IN_IMAGE ? 256 : 128;
+    const bool poller = IN == IN_IMAGE ? (e1 & 11) == 0 : q == 0;                 // one polling warp per block
     const uint32_t lane_base = (uint32_t)(32 * q) << 16;
     const int hu = rank * TILE + 32 * q + lane;   // hidden unit of this lane
     const float b1 = FOLD ? 0.f : p.b1[hu];
@@ -561,15 +544,15 @@ segsum_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
       const uint4 ma = na, mc = nc;
       const uint2 mb = nb, md = nd;
       fetch_meta(t + n_clusters);
-      ptx::mbar_wait_role(bar(B_ACC1_FULL0 + g), it & 1, q == 0, 3 + g, 128);
+      ptx::mbar_wait_role(bar(B_ACC1_FULL0 + g), it & 1, poller, 3 + g, GROUP_THREADS);
       ptx::tc_fence_after();
-      ptx::tmem_ld16(tbase, va);
+      ptx::tmem_ld16(tbase + 32 * s_begin, va);
       float* dst = out_h;
       float a0 = 0.f, a1 = 0.f;
       uint32_t em = 0, pm = 0;
       bool regular = true;
 #pragma unroll 1
-      for (int s = 0; s < 4; ++s) {                        // columns [32s, 32s+32) of the block
+      for (int s = s_begin; s < s_end; ++s) {              // columns [32s, 32s+32) of the block
         if ((s & 1) == 0) {                                // a new sub-block: 4t + 2h + g, h = s >> 1
           const bool h = s != 0;
           regular = (h ? md.y : mb.y) == 0u;
@@ -593,7 +576,7 @@ segsum_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
           sum_irregular(tcol, p.desc + (size_t)sub * SUB, min(SUB, (int)p.n_rows - sub * SUB), b1, out_h);
         }
         ptx::tmem_ld_wait();
-        if (s != 3) ptx::tmem_ld16(tcol + 32, va);
+        if (s + 1 != s_end) ptx::tmem_ld16(tcol + 32, va);
         if (__builtin_expect(regular, 1)) sum_chunk<FOLD>(vb, em >> 16, pm >> 16, b1, a0, a1, dst);
       }
       ptx::tc_fence_before();
@@ -602,7 +585,38 @@ segsum_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
     }
   } else {
     // ===== MMA issuer: one thread of the leader CTA =====
+    // IN_IMAGE: the same thread of each CTA is the TMA producer of its half tile: three [64 halves x 128 rows] boxes =
+    // the three swizzle atoms of A0, completing on the LEADER's A0_FULL barrier (cta_group::2).  The leader issues its
+    // loads inline, at the point of its sequence where layer 0 of the current tile is known to be complete; the peer
+    // CTA's warp 20 has nothing else to do and simply waits for A0_EMPTY.
+    const __half* img = reinterpret_cast<const __half*>(p.feats);
+    auto tma_tile = [&](int t) {                         // one thread
+      const uint32_t full_leader = ptx::mapa_rank(bar(B_A0_FULL), 0);
+      const int row0 = t * PAIR + (int)rank * TILE;
+#pragma unroll
+      for (int a = 0; a < 3; ++a) ptx::tma_load_2d_2cta(sbase + A0_OFF + a * ATOM, &tmap, full_leader, 64 * a, row0);
+      if (rank == 0) ptx::mbar_arrive_expect_tx(bar(B_A0_FULL), 2 * A0_BYTES);   // both CTAs' boxes land on this barrier
+      const int t2 = t + 2 * n_clusters;                 // the CTA's half tile is one contiguous 48 KB range of the image
+      if (t2 < p.T) ptx::prefetch_l2_bulk(img + ((int64_t)t2 * PAIR + rank * TILE) * K0P, (uint32_t)(TILE * K0P * 2));
+    };
+    if (IN == IN_IMAGE && rank != 0) {
+      if (ptx::elect_one()) {
+        ptx::tma_prefetch_desc(&tmap);
+        int it = 0;
+        for (int t = cluster; t < p.T; t += n_clusters, ++it) {
+          if (it > 0) ptx::mbar_wait(bar(B_A0_EMPTY), (it - 1) & 1);    // layer 0 of the previous tile has read A0
+          tma_tile(t);
+        }
+      }
+    }
     if (rank == 0) {
+      if (IN == IN_IMAGE && cluster < p.T && ptx::elect_one()) {
+        ptx::tma_prefetch_desc(&tmap);
+        const int t1 = cluster + n_clusters;
+        if (t1 < p.T) ptx::prefetch_l2_bulk(img + ((int64_t)t1 * PAIR + rank * TILE) * K0P, (uint32_t)(TILE * K0P * 2));
+        tma_tile(cluster);
+      }
+      __syncwarp();
       const uint32_t idesc_n128 = ptx::umma_idesc_f16(256, 128);
       const uint64_t dW0 = ptx::umma_desc_sw128(sbase + W0_OFF), dW1 = ptx::umma_desc_sw128(sbase + W1_OFF);
       const uint64_t dA0 = ptx::umma_desc_sw128(sbase + A0_OFF), dA1 = ptx::umma_desc_sw128(sbase + A1_OFF);
@@ -638,6 +652,12 @@ segsum_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
         __syncwarp();
         ptx::mbar_wait(bar(B_A1_FULL1), it & 1);
         ptx::tc_fence_after();
+        if (IN == IN_IMAGE && t + n_clusters < p.T) {
+          // epi 0 has drained both halves of acc0, so layer 0 is complete and A0_EMPTY has fired: this wait falls through
+          ptx::mbar_wait(bar(B_A0_EMPTY), it & 1);
+          if (ptx::elect_one()) tma_tile(t + n_clusters);
+          __syncwarp();
+        }
         if (ptx::elect_one()) {
 #pragma unroll
           for (int k = 8; k < 16; ++k) ptx::umma_f16_2cta(tmem + 256, dW1 + kadv(k), dA1 + kadv(k), idesc_n128, 1);
