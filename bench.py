@@ -514,30 +514,28 @@ def main_vaex(args):
                               "latents_per_s": world * n5 / (ms5 * 1e-3), "n_gpus": world, "merged_equals_global_topk": ok5,
                               "tensor_frac": n5 * (FLOP_DECODE + FLOP_PREDICT) / (ms5 * 1e-3) / 1e12 / tpeak}
         del z5, ext5, cost5
-        # config 3: 256 restarts x 200 steps of z += lr * d score/dz, restarts sharded, one all-gather of (best cost, z*)
+        # config 3: 256 restarts x 200 steps of z += lr * d score/dz, restarts sharded over the ranks, one all-gather of
+        # (score, z*) per restart.  Both graphs of SURVEY 8d: the reference's predictor(z) (utils/select.py:128-135) and the
+        # north-star head(decoder_trunk(z)) with the fused backward through both models.
         R, S3 = 256, 200
-        lo, hi = shard.shard_range(R, rank, world)
         xr = torch.randn(R, D_EXT, device=dev, generator=torch.Generator(device=dev).manual_seed(3))
-        z0 = reg.encode(xr, use_mean=True)[lo:hi].contiguous()
-        zr, cr = z0.clone(), torch.empty(hi - lo, device=dev)
-        gath = torch.empty(world, (R // world + 1) * (L_LAT + 1), device=dev)
-
-        def step3():
-            zr.copy_(z0)
-            _lib.check(lib.vaex_latent_ascent(rmodel.h, _lib.ptr(zr), hi - lo, S3, 1e-2, _lib.ptr(cr), st))
+        z0 = reg.encode(xr, use_mean=True).contiguous()
+        graphs = {"predictor(z) (the reference's graph, utils/select.py:128-135)": lambda zb: reg.latent_ascent(zb, steps=S3, lr=1e-2),
+                  "head(decoder_trunk(z)) (north-star graph: decoder.{0,2,4} -> SegmentSumMLP l0, l1, decoder)":
+                      lambda zb: vae.latent_ascent_through(net, zb, steps=S3, lr=1e-2)}
+        res3 = []
+        for gname, fn in graphs.items():
+            ms3 = timed(lambda: shard.latent_ascent(fn, z0, comm=comm), 5, warm=2)
+            t3 = torch.tensor([ms3], device=dev, dtype=torch.float64)
             if world > 1:
-                send = torch.zeros(gath.shape[1], device=dev)
-                send[:(hi - lo) * (L_LAT + 1)] = torch.cat([cr[:, None], zr], dim=1).reshape(-1)
-                _lib.check(lib.vaex_allgather(comm.h, _lib.ptr(send), _lib.ptr(gath), gath.shape[1] * 4, st))
-        ms3 = timed(step3, 5, warm=2)
-        t3 = torch.tensor([ms3], device=dev, dtype=torch.float64)
-        if world > 1:
-            dist.all_reduce(t3, op=dist.ReduceOp.MAX)
-        ms3 = float(t3.item())
-        configs["config3"] = {"what": "latent ascent through the cost predictor, 256 restarts x 200 steps, %d restarts per GPU, "
-                                      "one all-gather of (cost, z*) per restart" % (hi - lo),
-                              "graph": "predictor(z) (utils/select.py:128-135)", "ms_per_search": ms3,
-                              "us_per_step": ms3 * 1e3 / S3, "restart_steps_per_s": R * S3 / (ms3 * 1e-3), "n_gpus": world}
+                dist.all_reduce(t3, op=dist.ReduceOp.MAX)
+            ms3 = float(t3.item())
+            res3.append({"graph": gname, "ms_per_search": ms3, "us_per_step": ms3 * 1e3 / S3,
+                         "restart_steps_per_s": R * S3 / (ms3 * 1e-3)})
+        lo, hi = shard.shard_range(R, rank, world)
+        configs["config3"] = {"what": "latent ascent, 256 restarts x 200 steps, %d restarts per GPU, one all-gather of (score, z*) "
+                                      "per restart; all steps of a restart in ONE cluster kernel" % (hi - lo),
+                              "n_gpus": world, "graphs": res3}
 
     # ---- parity on this run's own inputs + the CPU leg (rank 0, N = 1): the oracle scores the first programs of rank 0 ----
     parity, cpu_baseline = None, None

@@ -252,6 +252,16 @@ int vaex_kcenter_select(const float* z_dev, int64_t n, int32_t L, const int64_t*
 int vaex_latent_ascent(vaex_model_t h, float* z_inout_dev, int64_t n, int32_t steps, float lr,
                        float* cost_dev, void* stream);
 
+/* The north-star ascent graph (BASELINE.json north_star (3), config 3): score(z) = head(decoder_trunk(z)) -- the decoder's
+ * three hidden layers (VAE_feature_head.decoder.{0,2,4}, utils/model.py:31-39) feeding the SegmentSumMLP's residual head
+ * (l0, l1, decoder; mlp_model.py:210-221) on the 256-d vector -- and `steps` plain ascent steps z += lr * d score / d z
+ * with the fused backward pass through both models, all steps in one cluster kernel (eight CTAs per sixteen restarts,
+ * fp32).  vae: kind VAEX_KIND_EXTENT_VAE (L = 64, H = 256); mlp: kind VAEX_KIND_SEGSUM_MLP (H = 256, no norm / sigmoid).
+ * z_inout_dev fp32 [n, 64], score_dev fp32 [n] = the score of the final z.  The single-step precedent in the reference is
+ * select_topk_z_grad (utils/select.py:128-135). */
+int vaex_latent_ascent_decoder_head(vaex_model_t vae, vaex_model_t mlp, float* z_inout_dev, int64_t n, int32_t steps,
+                                    float lr, float* score_dev, void* stream);
+
 /* ---- segment-VAE family (eval mode: BatchNorm folded to affines, Dropout = identity) -------- */
 /* SegmentVAE.forward steps 1-3 (vae.py:113-128) / VAECostPredictor.encode (regression.py:82-101):
  * row encoder -> segment sum -> norm -> residual l0, l1 -> fc_mean, fc_logvar.

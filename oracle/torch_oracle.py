@@ -403,6 +403,23 @@ def latent_ascent(P, z0, steps, lr):
     return z, predict_cost(P, z).detach()
 
 
+def decoder_head_score(Pv, Pm, z):
+    """The north-star ascent graph (BASELINE.json north_star (3)): the decoder's three hidden layers
+    (utils/model.py:31-39) feeding the SegmentSumMLP residual head (mlp_model.py:210-221) on the 256-d vector."""
+    a = _mlp_relu(z if isinstance(z, torch.Tensor) else _t(z), Pv, "decoder", (0, 2, 4))
+    return _lin(segsum_mlp_head(Pm, a), Pm["decoder.weight"], Pm["decoder.bias"]).squeeze(-1)
+
+
+def latent_ascent_decoder_head(Pv, Pm, z0, steps, lr):
+    """plain torch.autograd loop around the composed modules"""
+    z = _t(z0).clone()
+    for _ in range(steps):
+        zz = z.clone().requires_grad_(True)
+        g = torch.autograd.grad(decoder_head_score(Pv, Pm, zz).sum(), zz)[0]
+        z = z + lr * g
+    return z, decoder_head_score(Pv, Pm, z).detach()
+
+
 def kcenter_select(z, cand, used, k, eps=1e-12):
     """select_topk_latent_diversity (utils/select.py:185-270) on an explicit candidate order: k-center greedy
     over L2-normalised rows, centres initialised with `used`; returns the chosen entries of cand in order."""

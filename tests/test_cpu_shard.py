@@ -121,3 +121,25 @@ def test_reduce_gradients_world2_gloo(tmp_path):
         z = np.load(tmp_path / ("g%d.npz" % r))
         assert np.array_equal(z["g"], want) and float(z["scale"]) == 0.5
     assert shard.reduce_gradients(torch.ones(4)) == 1.0                # no process group: identity
+
+
+def _ascent_worker(rank, world, port, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        z0 = torch.arange(7 * 4, dtype=torch.float32).reshape(7, 4)           # 7 restarts over 2 ranks: blocks of 4 and 3
+        z, score = shard.latent_ascent(lambda zb: (zb * 2 + 1, zb.sum(dim=1)), z0)
+        np.savez(os.path.join(out_dir, "a%d.npz" % rank), z=z.numpy(), score=score.numpy())
+    finally:
+        dist.destroy_process_group()
+
+
+def test_latent_ascent_world2_gloo(tmp_path):
+    """config 3 sharded: each rank ascends its block of restarts, one all-gather of (score, z*) rebuilds the whole set"""
+    mp.spawn(_ascent_worker, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
+    z0 = np.arange(28, dtype=np.float32).reshape(7, 4)
+    for r in range(2):
+        a = np.load(tmp_path / ("a%d.npz" % r))
+        assert np.array_equal(a["z"], z0 * 2 + 1) and np.array_equal(a["score"], z0.sum(1))
+    z, s = shard.latent_ascent(lambda zb: (zb + 1, zb[:, 0]), torch.from_numpy(z0))     # no process group: identity sharding
+    assert np.array_equal(z.numpy(), z0 + 1) and np.array_equal(s.numpy(), z0[:, 0])

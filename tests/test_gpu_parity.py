@@ -751,6 +751,47 @@ def test_latent_ascent_cluster_kernel(n, steps):
         assert torch.equal(z1, zt)
 
 
+@pytest.mark.parametrize("n,steps,lr", [(1, 3, 0.5), (13, 1, 0.5), (256, 0, 0.5), (300, 50, 0.5), (256, 200, 0.2), (1000, 20, 0.5)])
+def test_latent_ascent_decoder_head_kernel(n, steps, lr):
+    """The north-star ascent graph score(z) = head(decoder_trunk(z)) (vaex_latent_ascent_decoder_head: 8-CTA clusters,
+    fused forward + backward through both models, all steps on chip) against torch.autograd over the composed oracle
+    modules: ragged restart counts, zero steps, config 3's 256 restarts x 200 steps.  The learning rates are large enough
+    for z to move by O(1) so that the comparison sees the gradients, not just z0."""
+    g = load_golden("extent_vae.npz")
+    vae = vaex_b200.VAE_feature_head(48, None, 64, 256)
+    vae.load_state_dict(split_sd(g, "vae."))
+    vae = vae.cuda().eval()
+    gm = load_golden("segsum_mlp_f164.npz")
+    net = make_net(gm, 164)
+    Pv, Pm = split_sd(g, "vae."), split_sd(gm, "w.")
+    rng = np.random.default_rng(n + steps)
+    z0 = rng.standard_normal((n, 64)).astype(np.float32)
+    zt = torch.from_numpy(z0).cuda()
+    z1, s1 = vae.latent_ascent_through(net, zt, steps=steps, lr=lr)
+    z1b, s1b = vae.latent_ascent_through(net, zt, steps=steps, lr=lr)
+    assert torch.equal(z1, z1b) and torch.equal(s1, s1b)                       # deterministic
+    assert torch.equal(zt, torch.from_numpy(z0).cuda())                        # the input is not modified
+    if steps == 0:
+        assert torch.equal(z1, zt)
+    m = min(n, 300)
+    wz, ws = O.latent_ascent_decoder_head(Pv, Pm, z0[:m], steps, lr)
+    moved = np.abs(wz.numpy() - z0[:m]).max()
+    if steps >= 20:
+        assert moved > 0.05, moved                                             # the ascent really went somewhere
+    # rtol 1e-3; over many steps at this learning rate a pre-activation that sits within rounding distance of zero may flip
+    # its ReLU under another fp32 summation order, which moves single coordinates by O(lr * 1e-3): at most 0.5 % of the
+    # elements may exceed the tolerance and none by more than 2 % of the distance travelled
+    dz = np.abs(z1[:m].cpu().numpy() - wz.numpy())
+    bad = dz > 1e-4 + 1e-3 * moved + 1e-3 * np.abs(wz.numpy())
+    assert bad.mean() <= (0.005 if steps >= 20 else 0.0), bad.mean()
+    assert dz.max() <= 2e-2 * max(moved, 0.05), (dz.max(), moved)
+    ds = np.abs(s1[:m].cpu().numpy() - ws.numpy())
+    assert (ds > 1e-4 + 1e-3 * np.abs(ws.numpy())).mean() <= (0.01 if steps >= 20 else 0.0) and ds.max() < 5e-3
+    if steps > 0:
+        s0 = O.decoder_head_score(Pv, Pm, torch.from_numpy(z0[:m])).numpy()
+        assert (s1[:m].cpu().numpy() >= s0 - 1e-5).mean() > 0.95                # ascent: the score does not go down
+
+
 def test_errors_are_loud():
     lib = _lib.load()
     m = _lib.Model(_lib.KIND_SEGSUM_MLP, [164, 256, 0, 0])

@@ -56,6 +56,7 @@ SIGNATURES = {
     "vaex_mc_predict_cost": ([vp, vp, i64, i32, vp, u64, f32, vp, vp, vp], ctypes.c_int),
     "vaex_cost_grad_z": ([vp, vp, i64, vp, vp, vp, vp], ctypes.c_int),
     "vaex_latent_ascent": ([vp, vp, i64, i32, f32, vp, vp], ctypes.c_int),
+    "vaex_latent_ascent_decoder_head": ([vp, vp, vp, i64, i32, f32, vp, vp], ctypes.c_int),
     "vaex_segvae_encode": ([vp, vp, vp, i64, i64, vp, vp, vp, ctypes.c_int, vp], ctypes.c_int),
     "vaex_segvae_decode": ([vp, vp, i64, vp, vp], ctypes.c_int),
     "vaex_segcost_predict": ([vp, vp, i64, vp, vp], ctypes.c_int),

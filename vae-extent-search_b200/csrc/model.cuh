@@ -100,6 +100,8 @@ int64_t rows_image_bytes(int64_t n_rows);
 int rows_pack_image(const float* feats, int64_t n_rows, int F, void* image, cudaStream_t st);
 // ascent_cluster.cu
 int ascent_cluster_run(vaex_model* m, float* z, int64_t n, int steps, float lr, float* cost, cudaStream_t st);
+// ascent_compose.cu
+int ascent_compose_run(vaex_model* vae, vaex_model* mlp, float* z, int64_t n, int steps, float lr, float* score, cudaStream_t st);
 // host_pack.cpp
 bool host_pack_supported();
 bool host_pack_f16(const float* in, uint16_t* out, size_t n);   // true: a non-zero value became zero

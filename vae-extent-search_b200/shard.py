@@ -130,6 +130,38 @@ def reduce_gradients(flat_grads, group=None, comm=None):
     return 1.0 / world
 
 
+def latent_ascent(ascent_fn, z0, comm=None, group=None):
+    """Config 3 sharded: restarts are independent, so rank r runs ascent_fn on its contiguous block
+    of z0's rows (ascent_fn(z_block) -> (z*, score)) and ONE all-gather of (score, z*) per restart gives every rank
+    the full result.  comm (a shard.Comm) = the library's NCCL communicator; otherwise torch.distributed (any backend).
+    -> (z* [R, L], score [R]) identical on every rank."""
+    if comm is not None:
+        rank, world = comm.rank, comm.world
+    else:
+        world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+        rank = dist.get_rank(group) if world > 1 else 0
+    R, Ld = z0.shape
+    lo, hi = shard_range(R, rank, world)
+    z, score = ascent_fn(z0[lo:hi].contiguous())
+    if world == 1:
+        return z, score
+    per = -(-R // world)                                   # every rank sends the same number of rows (padded)
+    send = torch.zeros(per, Ld + 1, dtype=torch.float32, device=z0.device)
+    send[:hi - lo, 0] = score
+    send[:hi - lo, 1:] = z
+    if comm is not None:
+        allr = comm.allgather(send)
+    else:
+        allr = torch.empty(world, per, Ld + 1, dtype=torch.float32, device=z0.device)
+        dist.all_gather_into_tensor(allr.view(-1), send.view(-1), group=group)
+    parts = []
+    for r in range(world):
+        a, b = shard_range(R, r, world)
+        parts.append(allr[r, :b - a])
+    full = torch.cat(parts, dim=0)
+    return full[:, 1:].contiguous(), full[:, 0].contiguous()
+
+
 def _default_topk(values, k, mask):
     from . import vae_model
     return vae_model.topk(values, k, mask, sync=False)

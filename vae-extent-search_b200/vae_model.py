@@ -127,6 +127,15 @@ class VAE_feature_head(_Packed, nn.Module):
                                                _lib.ptr(scale), mode, _lib.ptr(se), _lib.ptr(sl), max_innermost, _lib.stream_ptr()))
         return x, out
 
+    def latent_ascent_through(self, cost_model, z0, steps=200, lr=1e-2):
+        """BASELINE config 3, north-star graph: `steps` ascent steps on score(z) = head(decoder_trunk(z)) where head is
+        cost_model's (a SegmentSumMLPModule) residual head.  -> (z, score of the final z)."""
+        z = _need_cuda(z0).clone()
+        score = torch.empty(z.shape[0], device=z.device)
+        _lib.check(_lib.load().vaex_latent_ascent_decoder_head(self.packed().h, cost_model.packed().h, _lib.ptr(z), z.shape[0],
+                                                              int(steps), float(lr), _lib.ptr(score), _lib.stream_ptr()))
+        return z, score
+
     def predict_feature(self, z):
         raise NotImplementedError("feature_predictor head (alpha_feature experiments) is outside the hot path")
 
