@@ -573,6 +573,45 @@ def main_vaex(args):
         cpu_baseline = {"value": ns / tcpu, "unit": UNIT, "cores": cores, "kind": "port",
                         "sample": "the first %d candidates of rank 0's inputs, one step; %s" % (ns, CPU_KIND_NOTE)}
 
+    # ---- "the bar" of SURVEY section 2: the reference's own eager PyTorch forward (cuBLAS / ATen kernels) on THIS GPU ----
+    torch_gpu = None
+    if not args.no_cpu and world == 1:
+        import torch.nn.functional as Fn
+        nt = min(P, 262144)
+        offs_t = np.concatenate([[0], np.cumsum(sizes[:nt], dtype=np.int64)])
+        W = {k: v.detach() for k, v in net.state_dict().items()}
+        inv_norm = (1.0 / norm).to(dev)
+
+        def eager_forward(batch, autocast):
+            """SegmentSumMLPModule.forward as the reference writes it (mlp_model.py:179-221): two Linear+ReLU on the rows,
+            repeat_interleave + scatter_add segment sum, residual head, decoder; batches of `batch` programs as
+            MLPModelInternal._predict_a_task iterates them (infer_batch_size 4096, :399)."""
+            outs = []
+            with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
+                for b0 in range(0, nt, batch):
+                    b1 = min(nt, b0 + batch)
+                    x = feats[int(offs_t[b0]):int(offs_t[b1])] * inv_norm
+                    seg = sizes_d[b0:b1].long()
+                    h = Fn.relu(Fn.linear(x, W["segment_encoder.0.weight"], W["segment_encoder.0.bias"]))
+                    h = Fn.relu(Fn.linear(h, W["segment_encoder.2.weight"], W["segment_encoder.2.bias"]))
+                    idx = torch.repeat_interleave(torch.arange(b1 - b0, device=dev), seg)
+                    ssum = torch.zeros(b1 - b0, H, device=dev, dtype=h.dtype).scatter_add_(0, idx[:, None].expand(-1, H), h)
+                    y = Fn.relu(Fn.linear(ssum, W["l0.0.weight"], W["l0.0.bias"])) + ssum
+                    y = Fn.relu(Fn.linear(y, W["l1.0.weight"], W["l1.0.bias"])) + y
+                    outs.append(Fn.linear(y, W["decoder.weight"], W["decoder.bias"]).squeeze(-1).float())
+            return torch.cat(outs)
+        torch_gpu = {"programs": nt, "unit": UNIT, "what": "the reference's eager SegmentSumMLPModule.forward (torch %s, cuBLAS / ATen) on the "
+                     "same GPU, cost model only (no decode / legalise / top-k), rows resident in HBM" % torch.__version__}
+        with torch.no_grad():
+            for tag, batch, ac in (("fp32_batch4096", 4096, False), ("fp32_batch65536", 65536, False), ("bf16_autocast_batch65536", 65536, True)):
+                ms_t = timed(lambda: eager_forward(batch, ac), 3, warm=1)
+                torch_gpu[tag] = nt / (ms_t * 1e-3)
+            ref_sc = eager_forward(65536, False)
+        fin_t = torch.isfinite(scores[:nt])
+        dt_ = (scores[:nt] - ref_sc)[fin_t].double()
+        torch_gpu["vaex_vs_eager_fp32_l2_rel"] = float(dt_.norm() / ref_sc[fin_t].double().norm())
+        del ref_sc
+
     # ---- e2e through the host C-ABI calls (rank-local pinned buffers) ------------------------
     e2e = None
     if not args.no_e2e:
@@ -645,9 +684,9 @@ def main_vaex(args):
     if rank == 0:
         ach = rows * FLOP_PER_ROW / (kms * 1e-3) / 1e12
         traffic = None          # dram read+write bytes per launch of the same kernel/workload from the committed ncu capture
-        for name in ("r02_traffic.json", "r01_traffic.json"):
+        for name in ("r02_traffic.json",):
             try:
-                tr = json.load(open(os.path.join(ROOT, "profiles", name)))["segsum_tc_kernel"]
+                tr = json.load(open(os.path.join(ROOT, "profiles", name)))["segsum_tc_kernel_image"]
                 if tr["rows"] == rows and tr["programs"] == P:
                     traffic = tr["dram_bytes_read"] + tr["dram_bytes_write"]
                     break
@@ -678,6 +717,8 @@ def main_vaex(args):
         }
         if cpu_baseline:
             line["cpu_baseline"] = cpu_baseline
+        if torch_gpu:
+            line["torch_gpu_baseline"] = torch_gpu
         print(json.dumps(line))
     if comm is not None:
         comm.close()

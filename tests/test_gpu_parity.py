@@ -792,6 +792,21 @@ def test_latent_ascent_decoder_head_kernel(n, steps, lr):
         assert (s1[:m].cpu().numpy() >= s0 - 1e-5).mean() > 0.95                # ascent: the score does not go down
 
 
+def test_topk_more_than_1024_winners():
+    """k above the kernel's 1024-winner limit is taken in rounds (select_programs with num_select >= 205)"""
+    rng = np.random.default_rng(3)
+    sc = rng.standard_normal(50000).astype(np.float32)
+    sc[rng.integers(0, 50000, 5000)] = 0.25                                    # ties
+    mask = (rng.random(50000) < 0.7).astype(np.uint8)
+    for k in (1025, 3000):
+        v, i = vaex_b200.topk(torch.from_numpy(sc).cuda(), k, torch.from_numpy(mask).cuda())
+        keep = np.nonzero(mask)[0]
+        wv, wi = O.topk_desc(sc[keep], k)
+        assert np.array_equal(i.cpu().numpy(), keep[wi]) and np.array_equal(v.cpu().numpy(), wv)
+    v, i = vaex_b200.topk(torch.from_numpy(sc[:1500]).cuda(), 5000)            # fewer scores than k
+    assert v.numel() == 1500 and np.array_equal(i.cpu().numpy(), O.topk_desc(sc[:1500], 1500)[1])
+
+
 def test_errors_are_loud():
     lib = _lib.load()
     m = _lib.Model(_lib.KIND_SEGSUM_MLP, [164, 256, 0, 0])

@@ -706,7 +706,7 @@ __global__ void tc_prepare_kernel(const int32_t* __restrict__ off, int P, int n_
       uint2* d = desc + (size_t)gid * tc::SUB;
       int p = lo, r = r0;
       k = 0;
-      while (r < r1) {
+      while (r < r1 && p < P) {                   // p < P: offsets that end before n_rows (caller error) must not walk off the array
         const int s = off[p], e = off[p + 1];
         if (e > r) {                              // skips empty programs
           const int ee = min(e, r1);

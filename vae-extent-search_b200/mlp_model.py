@@ -181,9 +181,19 @@ class SegmentSumMLPModule(torch.nn.Module):
 
     # -- packing ---------------------------------------------------------------------------
     def _version_key(self, norm_vec):
-        key = tuple((id(p), p._version) for p in self.state_dict(keep_vars=True).values())
-        nk = None if norm_vec is None else (id(norm_vec), getattr(norm_vec, "_version", 0))
+        """Cache key of the packed weights: storage address + autograd version + a cheap content probe per tensor
+        (writes through .data do not bump _version; id() can be reused after garbage collection), and the norm vector's
+        bytes.  invalidate_packed() drops the cache explicitly."""
+        key = tuple((p.data_ptr(), p._version, float(p.detach().reshape(-1)[:: max(1, p.numel() // 16)].double().sum()))
+                    for p in self.state_dict(keep_vars=True).values())
+        nk = None
+        if norm_vec is not None:
+            nv = norm_vec.detach().cpu().numpy() if hasattr(norm_vec, "detach") else np.asarray(norm_vec)
+            nk = hash(np.ascontiguousarray(nv, dtype=np.float32).tobytes())
         return key, nk
+
+    def invalidate_packed(self):
+        self._packed = {}
 
     def packed(self, fea_norm_vec=None, embedding=None):
         """Returns the packed kernel-side model (re-packed when weights / norm vector change).

@@ -33,7 +33,8 @@ class _Packed:
         raise NotImplementedError
 
     def packed(self):
-        key = tuple((id(p), p._version) for p in self.state_dict(keep_vars=True).values())
+        key = tuple((p.data_ptr(), p._version, float(p.detach().reshape(-1)[:: max(1, p.numel() // 16)].double().sum()))
+                    for p in self.state_dict(keep_vars=True).values())
         cached = self.__dict__.get("_packed_cache")
         if cached is not None and cached[1] == key:
             return cached[0]
@@ -214,6 +215,13 @@ class VAECostPredictor(_Packed, nn.Module):
         return mu if use_mean else (mu, logvar)
 
     def predict_cost(self, z, drop_mask=None, drop_seed=0):
+        """utils/model.py:168-170.  Inference only: Dropout is active only when a mask or a seed is given (mc_predict
+        passes them), whatever self.training says, and the backward returns d cost / d z but no parameter gradients --
+        training runs through training.RegressionTrainer (vaex_reg_trainer_forward_backward)."""
+        if self.training and torch.is_grad_enabled() and any(p.requires_grad for p in self.cost_predictor.parameters()) \
+                and drop_mask is None and not drop_seed:
+            raise _lib.VaexError("VAECostPredictor.predict_cost in train mode builds no parameter gradients and applies no "
+                                 "Dropout: call .eval() / torch.no_grad() to score, or train with training.RegressionTrainer")
         if z.requires_grad and torch.is_grad_enabled():
             return _PredictCostFn.apply(z, self)
         zc = _need_cuda(z)
@@ -284,12 +292,35 @@ class VAECostPredictor(_Packed, nn.Module):
         return z, cost
 
 
+TOPK_MAX = 1024      # winners per vaex_topk call (csrc/topk.cu)
+
+
 def topk(scores, k, mask=None, sync=True):
     """GPU top-k with the deterministic (score desc, index asc) order -> (values, int64 indices).
     sync=False skips the host read of the winner count and returns (values[k], indices[k],
     count) with count a device int32 tensor; entries past count are unspecified."""
     s = _need_cuda(scores)
     k = int(min(k, s.shape[0]))
+    if k > TOPK_MAX:
+        # vaex_topk selects at most 1024 winners per call (one CTA sorts them); larger k -- select_programs' pool of
+        # topk_factor * num_select candidates for num_select >= 205, utils/select.py:329-334 -- is taken in rounds of 1024
+        # with the winners masked out: the concatenation is still (score desc, index asc)
+        mk = torch.ones(s.shape[0], dtype=torch.uint8, device=s.device) if mask is None else \
+            mask.to(device=s.device, dtype=torch.uint8).clone()
+        vs, ix, left = [], [], k
+        while left > 0:
+            v, i = topk(s, min(left, TOPK_MAX), mk, sync=True)
+            if v.numel() == 0:
+                break
+            vs.append(v)
+            ix.append(i)
+            mk[i] = 0
+            left -= v.numel()
+        vals = torch.cat(vs) if vs else torch.empty(0, device=s.device)
+        idx = torch.cat(ix) if ix else torch.empty(0, dtype=torch.int64, device=s.device)
+        if sync:
+            return vals, idx
+        return vals, idx, torch.tensor([vals.numel()], dtype=torch.int32, device=s.device)
     vals = torch.empty(k, device=s.device)
     idx = torch.empty(k, dtype=torch.int64, device=s.device)
     n_out = torch.zeros(1, dtype=torch.int32, device=s.device)
