@@ -477,6 +477,19 @@ def main_vaex(args):
         hbm_entry("topk (radix select, k = 320)", ms_t, P * 4, "%d scores x 4 B per needed pass (latency-bound at 4 MB)" % P)
         ms_s = timed(lambda: _lib.check(lib.vaex_segment_offsets(_lib.ptr(sizes_d), P, _lib.ptr(offsets), st)), it)
         hbm_entry("exclusive_scan_i32 (3 launches)", ms_s, P * 8, "%d sizes x 8 B" % P)
+        # segment-VAE family (a7 / a8): row encoder from the image, then the latent heads / predictor on the head kernel
+        torch.manual_seed(5)
+        sreg = vaex_b200.seg_models.VAECostPredictor(F, H, 128, H, 3).to(dev).eval()
+        smodel = sreg.packed(norm.cpu())
+        smean, slogv = torch.empty(P, 128, device=dev), torch.empty(P, 128, device=dev)
+        ms_se = timed(lambda: _lib.check(lib.vaex_segvae_encode(smodel.h, _lib.ptr(image), _lib.ptr(offsets), P, rows, _lib.ptr(smean),
+                                                                 _lib.ptr(slogv), None, _lib.F_FEATS_IMAGE, st)), it)
+        tensor_entry("segment VAECostPredictor.encode (row encoder + norm + l0 + l1 + fc_mean | fc_logvar, L = 128)", ms_se,
+                     rows * FLOP_PER_ROW + P * 2 * (2 * H * H + H * 256), "%d rows x 215 040 + %d programs x 393 216 FLOP" % (rows, P))
+        ms_sp = timed(lambda: _lib.check(lib.vaex_segcost_predict(smodel.h, _lib.ptr(smean), P, _lib.ptr(cost), st)), it)
+        tensor_entry("segment VAECostPredictor.predict_cost (128 -> 256 -> 256 -> 256 -> 1, BN folded)", ms_sp,
+                     P * 2 * (128 * H + 2 * H * H + H), "%d latents x 328 192 FLOP" % P)
+        del smean, slogv, sreg, smodel
         del xs, cost, mu, lv, valid
     del segsum
 

@@ -108,6 +108,9 @@ int vaex_model_destroy(vaex_model_t h);
 /* per-model options.  VAEX_OPT_TENSOR_CORES (default 1): extent-VAE decode / predict_cost run the fused
  * tcgen05 chains (fp16 operands, fp32 accumulate: 1e-3 relative) when the shapes allow; 0 = fp32 SIMT
  * kernels (1e-5).  The SegmentSumMLP entry points take VAEX_F_FORCE_SIMT per call instead. */
+/* Segment-VAE family: 1 also puts the latent heads (norm, l0, l1, fc_mean | fc_logvar) and the cost predictor on the tcgen05
+ * head kernel, one launch per layer; the SegmentVAE *decoder* joins only at value 2 (on the shipped checkpoints its output
+ * is a cancellation that fp16 operands resolve to ~7 % only). */
 enum { VAEX_OPT_TENSOR_CORES = 1,
        /* (default 1) vaex_latent_ascent runs all steps in one cluster kernel (L = 64, PH = 256); 0 = one launch per layer */
        VAEX_OPT_FUSED_ASCENT = 2 };

@@ -829,12 +829,13 @@ def test_segment_vae_checkpoint_golden(flags):
     vae = vaex_b200.SegmentVAE(164, hidden_dim=int(g["hidden"]), latent_dim=int(g["latent"]))
     vae.load_state_dict(split_sd(g, "w."))
     vae = vae.cuda().eval()
+    vae.set_tensor_cores(not flags)               # flags = FORCE_SIMT: everything fp32; 0: row encoder AND heads on tensor cores
     rel = 1e-4 if flags else 2e-3
     sizes, feats = torch.from_numpy(g["sizes"]).cuda(), torch.from_numpy(g["feats"]).cuda()
     mean, logvar, S = vae.encode_segments(sizes, feats, flags=flags)
     assert _seg_close(S.cpu(), g["segsum"], rel)
     assert _seg_close(mean.cpu(), g["mean"], rel) and _seg_close(logvar.cpu(), g["logvar"], rel)
-    assert _seg_close(vae.decode(torch.from_numpy(g["mean"]).cuda()).cpu(), g["recon"], 1e-4)
+    assert _seg_close(vae.decode(torch.from_numpy(g["mean"]).cuda()).cpu(), g["recon"], 1e-4)      # the decoder stays fp32 (see header)
     fm, fl, fz, frecon, fS = vae(sizes, feats, use_mean=True, eps=torch.from_numpy(g["fwd_eps"]).cuda(), flags=flags)
     assert not fl.any() and _seg_close((fz - fm).cpu(), g["fwd_eps"], 1e-5)
     assert _seg_close(frecon.cpu(), g["fwd_recon"], 5 * rel)
@@ -852,19 +853,57 @@ def test_segment_cost_predictor_checkpoint_golden(flags):
     reg = vaex_b200.seg_models.VAECostPredictor(d[0], d[1], d[2], d[3], d[4])
     reg.load_state_dict(split_sd(g, "w."))
     reg = reg.cuda().eval()
+    reg.set_tensor_cores(not flags)
     rel = 1e-4 if flags else 2e-3
     sizes, raw = torch.from_numpy(g["sizes"]).cuda(), torch.from_numpy(g["raw"]).cuda()
     cost, mean, logvar, z = reg(sizes, raw, use_mean=True, flags=flags, fea_norm_vec=torch.from_numpy(g["norm"]))
     assert z is mean
     assert _seg_close(mean.cpu(), g["mean"], rel) and _seg_close(logvar.cpu(), g["logvar"], rel)
     assert _seg_close(cost.cpu(), g["cost"], 2 * rel)
-    assert _seg_close(reg.predict_cost(torch.from_numpy(g["z_test"]).cuda()).cpu(), g["cost_z"], 1e-4)
+    assert _seg_close(reg.predict_cost(torch.from_numpy(g["z_test"]).cuda()).cpu(), g["cost_z"], rel)
     # the same encoder through load_pretrained_encoder of a SegmentVAE-style state dict
     reg2 = vaex_b200.seg_models.VAECostPredictor(d[0], d[1], d[2], d[3], d[4])
     reg2.load_pretrained_encoder({"model_state_dict": split_sd(g, "w.")})
     reg2 = reg2.cuda().eval()
     m2, _, _ = reg2.encode(sizes, raw, flags=flags, fea_norm_vec=torch.from_numpy(g["norm"]))
     assert torch.equal(m2, mean)
+
+
+@pytest.mark.parametrize("n", [1, 257, 20011])
+def test_segment_family_heads_on_tensor_cores(n):
+    """a7 / a8 at size: the latent heads, the decoder and the cost predictor as single-layer launches of the tcgen05 head
+    kernel against the fp32 SIMT chains of the same (BN-folded) weights, ragged program counts around the 256-row tile,
+    latent 128 (the shipped predictor) and 64 (the shipped VAEs)."""
+    rng = np.random.default_rng(n)
+    sizes_np = rng.integers(1, 33, size=n).astype(np.int32)
+    feats_np = rng.random((int(sizes_np.sum()), 164), dtype=np.float32)
+    sizes, feats = torch.from_numpy(sizes_np).cuda(), torch.from_numpy(feats_np).cuda()
+    torch.manual_seed(n)
+    reg = vaex_b200.seg_models.VAECostPredictor(164, 256, 128, 256, 3).cuda()
+    vae = vaex_b200.SegmentVAE(164, hidden_dim=256, latent_dim=64).cuda()
+    for mod in (reg, vae):                        # non-trivial BatchNorm statistics, as in a trained checkpoint
+        for bn in [m_ for m_ in mod.modules() if isinstance(m_, torch.nn.BatchNorm1d)]:
+            bn.running_mean.uniform_(-0.5, 0.5)
+            bn.running_var.uniform_(0.5, 2.0)
+            bn.weight.data.uniform_(0.5, 1.5)
+            bn.bias.data.uniform_(-0.3, 0.3)
+        mod.eval()
+
+    def close(a, b, rel):
+        a, b = a.double(), b.double()
+        return float((a - b).norm() / b.norm().clamp_min(1e-9)) < rel and float((a - b).abs().max()) < 4 * rel * float(b.abs().max().clamp_min(1e-9))
+
+    outs = {}
+    for tc in (False, True):
+        reg.set_tensor_cores(tc), vae.set_tensor_cores(tc)
+        vae.packed().set_option(_lib.OPT_TENSOR_CORES, 2 if tc else 0)       # 2: the decoder too (opt-in)
+        fl = 0 if tc else _lib.F_FORCE_SIMT
+        cost, mean, logvar, _ = reg(sizes, feats, use_mean=True, flags=fl)
+        vm, vl, vS = vae.encode_segments(sizes, feats, flags=fl)
+        outs[tc] = (cost, mean, logvar, vm, vl, vae.decode(vm), reg.predict_cost(mean))
+    for got, want in zip(outs[True], outs[False]):
+        assert got.shape == want.shape and torch.isfinite(got).all()
+        assert close(got, want, 2e-3), (float((got - want).abs().max()), float(want.abs().max()))
 
 
 def test_predict_blob_and_embedding_fold():

@@ -82,6 +82,49 @@ static int pack_linear_bn(vaex_model* m, const std::string& lin, const std::stri
   }
   TRY(upload(m, out_name + ".weight", w.data(), w.size(), st));
   TRY(upload(m, out_name + ".bias", b.data(), b.size(), st));
+  m->host[out_name + ".weight"] = HostTensor{out, in, w};       // folded copies (the tensor-core images are made from them)
+  m->host[out_name + ".bias"] = HostTensor{1, out, b};
+  return VAEX_OK;
+}
+
+// fp16 image + zero-padded fp32 bias of one <= 256-wide layer for head_tc_linear; `rows` stacks several host tensors
+// (fc_mean over fc_logvar)
+static int pack_head_layer(vaex_model* m, const std::string& name, const std::vector<std::string>& rows, cudaStream_t st) {
+  std::vector<float> w, b;
+  int in = 0, out = 0;
+  for (const std::string& r : rows) {
+    const HostTensor& hw = m->host[r + ".weight"];
+    const HostTensor& hb = m->host[r + ".bias"];
+    if (in && hw.cols != in) { set_error("stacked layers of " + name + " differ in width"); return VAEX_E_INVALID; }
+    in = hw.cols;
+    out += hw.rows;
+    w.insert(w.end(), hw.v.begin(), hw.v.end());
+    b.insert(b.end(), hb.v.begin(), hb.v.end());
+  }
+  if (out > 256 || in > 256) return VAEX_OK;                     // stays on the SIMT path
+  b.resize(256, 0.f);
+  TRY(head_tc_pack_layer(w, out, in, &m->head_img[name], st));
+  TRY(upload(m, name + ".bias256", b.data(), 256, st));
+  return VAEX_OK;
+}
+static int pack_segment_heads(vaex_model* m, cudaStream_t st) {
+  m->head_ready = false;
+  if (m->H != 256 || m->L % 32 != 0 || 2 * m->L > 256) return VAEX_OK;
+  TRY(pack_head_layer(m, "l0.0", {"l0.0"}, st));
+  TRY(pack_head_layer(m, "l1.0", {"l1.0"}, st));
+  TRY(pack_head_layer(m, "fc", {"fc_mean", "fc_logvar"}, st));
+  if (m->kind == VAEX_KIND_SEGMENT_VAE) {
+    TRY(pack_head_layer(m, "dec0", {"dec0"}, st));
+    TRY(pack_head_layer(m, "dec1", {"dec1"}, st));
+    TRY(pack_head_layer(m, "decoder.7", {"decoder.7"}, st));
+  } else {
+    if (m->PH != 256) return VAEX_OK;
+    for (int i = 0; i < m->n_pred; ++i) TRY(pack_head_layer(m, "pred" + std::to_string(i), {"pred" + std::to_string(i)}, st));
+    std::vector<float> wd = m->host["cost_predictor." + std::to_string(4 * m->n_pred) + ".weight"].v;
+    wd.resize(256, 0.f);
+    TRY(upload(m, "pred.wd256", wd.data(), 256, st));
+  }
+  m->head_ready = true;
   return VAEX_OK;
 }
 
@@ -181,6 +224,7 @@ static int pack_model(vaex_model* m, const float* norm, cudaStream_t st) {
       TRY(pack_linear_bn(m, "decoder.0", "decoder.1", "dec0", m->H, m->L, st));
       TRY(pack_linear_bn(m, "decoder.4", "decoder.5", "dec1", m->H, m->H, st));
       TRY(pack_linear(m, "decoder.7", m->H, m->H, st));
+      TRY(pack_segment_heads(m, st));
       return VAEX_OK;
     }
     case VAEX_KIND_SEGMENT_COST: {
@@ -191,6 +235,7 @@ static int pack_model(vaex_model* m, const float* norm, cudaStream_t st) {
         TRY(pack_linear_bn(m, "cost_predictor." + std::to_string(4 * i), "cost_predictor." + std::to_string(4 * i + 1),
                            "pred" + std::to_string(i), m->PH, i == 0 ? m->L : m->PH, st));
       TRY(pack_linear(m, "cost_predictor." + std::to_string(4 * m->n_pred), 1, m->PH, st));
+      TRY(pack_segment_heads(m, st));
       return VAEX_OK;
     }
   }
@@ -245,7 +290,7 @@ int vaex_model_create(int kind, const int32_t* dims, int ndims, vaex_model_t* ou
 
 int vaex_model_set_option(vaex_model_t h, int option, int value) {
   VAEX_CHECK(h, "null handle");
-  if (option == VAEX_OPT_TENSOR_CORES) { h->use_tensor = value ? 1 : 0; return VAEX_OK; }
+  if (option == VAEX_OPT_TENSOR_CORES) { h->use_tensor = value < 0 ? 0 : value > 2 ? 2 : value; return VAEX_OK; }
   if (option == VAEX_OPT_FUSED_ASCENT) { h->use_fused_ascent = value ? 1 : 0; return VAEX_OK; }
   set_error("unknown option");
   return VAEX_E_INVALID;
@@ -274,6 +319,7 @@ int vaex_model_pack(vaex_model_t h, const float* fea_norm_vec_host, void* stream
 int vaex_model_destroy(vaex_model_t h) {
   if (!h) return VAEX_OK;
   for (auto& kv : h->dev) cudaFree(kv.second);
+  for (auto& kv : h->head_img) if (kv.second) cudaFree(kv.second);
   for (auto& b : h->ws) b.release();
   h->topk_ws.release();
   h->tc_ws.release();

@@ -23,6 +23,7 @@
 // the step boundary only converts them into the operand (tcgen05.ld -> fp16 -> st.shared).
 // Warp 16 of the leader CTA issues the MMAs.
 #include <algorithm>
+#include <cstring>
 #include <vector>
 
 #include "common.cuh"
@@ -59,7 +60,15 @@ struct HeadParams {
   const uint8_t* valid;      // [P] or null
   float* scores;             // [P]
   int32_t P, T, sigmoid;
+  // single-layer mode (HF_STOP0): out = act(X Wl0^T + bl0) [+ X], as a vector or reduced with wd -- the building block of
+  // the segment-VAE family's latent heads, decoder and cost predictor (vae.py:87-111, regression.py:82-111)
+  int32_t flags, k_in;       // k_in: valid input columns (a multiple of 32; the rest of the 256-wide operand is zero)
+  int64_t pitch;             // floats between input rows
+  float* out0;               // HF_OUT_VEC: columns [0, n0) -> out0 [P, n0]; columns [n0, n0 + n1) -> out1 [P, n1]
+  float* out1;
+  int32_t n0, n1;
 };
+enum { HF_RELU0 = 1, HF_RES0 = 2, HF_STOP0 = 16, HF_OUT_VEC = 32 };
 
 __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&v)[32]) {
   asm volatile(
@@ -107,7 +116,7 @@ head_tc_kernel(const HeadParams p) {
     uint4* s1 = reinterpret_cast<uint4*>(smem + WL1_OFF);
     for (int i = threadIdx.x; i < W_BYTES / 16; i += THREADS) { s0[i] = __ldg(g0 + i); s1[i] = __ldg(g1 + i); }
     for (int i = threadIdx.x; i < HID; i += THREADS) {
-      s_bl0[i] = p.bl0[i]; s_bl1[i] = p.bl1[i]; s_wd[i] = p.wd[i];
+      s_bl0[i] = p.bl0[i]; s_bl1[i] = p.bl1 ? p.bl1[i] : 0.f; s_wd[i] = p.wd ? p.wd[i] : 0.f;
       s_ns[i] = has_norm ? p.nscale[i] : 1.f;
       s_nb[i] = has_norm ? p.nshift[i] : 0.f;
     }
@@ -126,13 +135,13 @@ head_tc_kernel(const HeadParams p) {
     const uint32_t a_row = sbase + A_OFF + (row >> 3) * 1024 + (row & 7) * 128;
     const int sw = row & 7;
     const uint32_t t_res = tmem + ((uint32_t)(32 * q) << 16), t_acc = t_res + 256;
-    const float bd = p.bd[0];
+    const float bd = p.bd ? p.bd[0] : 0.f;
     float4 x[8];                                     // 32 floats of the next step's row (one half at a time)
 
     auto load_half = [&](int t, int h) {
       const int64_t prog = (int64_t)t * PAIR + rank * TILE + row;
-      if (t < p.T && prog < p.P) {
-        const float* src = p.S + prog * HID + 128 * h + 32 * cg;
+      if (t < p.T && prog < p.P && 128 * h + 32 * cg < p.k_in) {
+        const float* src = p.S + prog * p.pitch + 128 * h + 32 * cg;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           const ptx::F8 f = ptx::ldg_stream_f8(src + 8 * j);
@@ -148,7 +157,7 @@ head_tc_kernel(const HeadParams p) {
       if (lane != 0 || t >= p.T) return;
       const int64_t r0 = (int64_t)t * PAIR + rank * TILE + warp * 8;
       const int64_t nr = min((int64_t)8, (int64_t)p.P - r0);
-      if (nr > 0) ptx::prefetch_l2_bulk(p.S + r0 * HID, (uint32_t)(nr * HID * 4));
+      if (nr > 0 && p.pitch == p.k_in) ptx::prefetch_l2_bulk(p.S + r0 * p.pitch, (uint32_t)(nr * p.pitch * 4));
     };
     // 32 fp32 values -> 64 B of the fp16 A operand, 32-column chunk cc of the row
     auto pack32 = [&](const uint32_t (&v)[32], int cc) {
@@ -202,6 +211,79 @@ head_tc_kernel(const HeadParams p) {
     tmem_st_wait();
     pack_half(0);
     pack_half(1);
+    if (p.flags & HF_STOP0) {
+      // ===== single layer per tile: epilogue of half h, then the next tile's half h goes into the freed residual columns;
+      // the operand is rewritten once both accumulator halves have been committed (every MMA of the tile is complete) =====
+      const bool relu = p.flags & HF_RELU0, res = p.flags & HF_RES0, vec = p.flags & HF_OUT_VEC;
+      for (int t = cluster; t < p.T; t += n_clusters) {
+        prefetch_l2(t + 2 * n_clusters);
+        const int64_t prog = (int64_t)t * PAIR + rank * TILE + row;
+        float dot0 = 0.f, dot1 = 0.f;
+#pragma unroll 1
+        for (int h = 0; h < 2; ++h) {
+          const int col = 128 * h + 32 * cg;
+          if (h == 0) { ptx::mbar_wait(bar(B_ACC0), acc_use0 & 1); ++acc_use0; }
+          else        { ptx::mbar_wait(bar(B_ACC1), acc_use1 & 1); ++acc_use1; }
+          ptx::tc_fence_after();
+          {
+            uint32_t v[32];
+            ptx::tmem_ld32(t_acc + col, v);
+            ptx::tmem_ld_wait();
+            const float* bp = s_bl0 + col;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const float a = __uint_as_float(v[j]) + bp[j];
+              v[j] = __float_as_uint(relu ? fmaxf(a, 0.f) : a);
+            }
+            if (res) {
+              uint32_t r[32];
+              ptx::tmem_ld32(t_res + col, r);
+              ptx::tmem_ld_wait();
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(r[j]));
+            }
+            if (vec) {
+              if (prog < p.P && col < p.n0 + p.n1) {
+                float* dst = col < p.n0 ? p.out0 + prog * p.n0 + col : p.out1 + prog * p.n1 + (col - p.n0);
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                  ptx::stg_f8(dst + 8 * j, __uint_as_float(v[8 * j]), __uint_as_float(v[8 * j + 1]), __uint_as_float(v[8 * j + 2]),
+                              __uint_as_float(v[8 * j + 3]), __uint_as_float(v[8 * j + 4]), __uint_as_float(v[8 * j + 5]),
+                              __uint_as_float(v[8 * j + 6]), __uint_as_float(v[8 * j + 7]));
+              }
+            } else {
+              const float4* w4 = reinterpret_cast<const float4*>(s_wd + col);
+#pragma unroll
+              for (int j4 = 0; j4 < 8; ++j4) {
+                const float4 w = w4[j4];
+                dot0 = fmaf(__uint_as_float(v[4 * j4]), w.x, dot0); dot1 = fmaf(__uint_as_float(v[4 * j4 + 1]), w.y, dot1);
+                dot0 = fmaf(__uint_as_float(v[4 * j4 + 2]), w.z, dot0); dot1 = fmaf(__uint_as_float(v[4 * j4 + 3]), w.w, dot1);
+              }
+            }
+          }
+          load_half(t + n_clusters, h);                    // the next tile's rows (L2 hits: bulk-prefetched two tiles ahead)
+          commit_half(h);                                  // residual half h is free: the next tile's rows go in
+        }
+        tmem_st_wait();
+        ptx::tc_fence_before();
+        if (t + n_clusters < p.T) {
+          pack_half(0);
+          pack_half(1);
+        }
+        if (!vec) {
+          const float dot = dot0 + dot1;
+          if (cg) s_dot[(cg - 1) * TILE + row] = dot;
+          ptx::bar_sync(1, WORKERS);
+          if (cg == 0 && prog < p.P) {
+            float sc = ((dot + s_dot[row]) + (s_dot[TILE + row] + s_dot[2 * TILE + row])) + bd;
+            if (p.sigmoid) sc = 1.f / (1.f + expf(-sc));
+            if (p.valid && !p.valid[prog]) sc = -INFINITY;
+            p.scores[prog] = sc;
+          }
+          ptx::bar_sync(1, WORKERS);                       // s_dot is reused by the next tile
+        }
+      }
+    } else
     for (int t = cluster; t < p.T; t += n_clusters) {
       prefetch_l2(t + 2 * n_clusters);
       float dot0 = 0.f, dot1 = 0.f;
@@ -307,6 +389,7 @@ head_tc_kernel(const HeadParams p) {
         piece(WL0_OFF, 1, 1); ptx::umma_commit_2cta(bar(B_ACC1), 3);
       }
       __syncwarp();
+      if (p.flags & HF_STOP0) continue;                    // single-layer mode: the next tile's operand is the next wait
       // GEMM 1: accumulator half h is free when the layer-0 epilogue of half h has published
       wait_in(0);
       if (ptx::elect_one()) piece(WL1_OFF, 0, 0);
@@ -329,6 +412,56 @@ head_tc_kernel(const HeadParams p) {
 
 // ---------------------------------------------------------------------------------------------
 static __half hh_clamp(float x) { return __float2half_rn(std::min(std::max(x, -65504.f), 65504.f)); }
+
+// [out_rows <= 256, in_cols <= 256] fp32 weight, zero-padded to 256 x 256, as the per-rank swizzled fp16 images of one
+// head_tc layer (each GEMM is issued as two 128-column MMAs: image rows [64 h, +64) of rank r = units 128 h + 64 r + [0, 64))
+int head_tc_pack_layer(const std::vector<float>& w, int out_rows, int in_cols, __half** dev, cudaStream_t st) {
+  using namespace hd;
+  VAEX_CHECK(out_rows >= 1 && out_rows <= HID && in_cols >= 1 && in_cols <= HID, "layer outside the 256 x 256 head kernel");
+  std::vector<__half> img(2 * W_BYTES / 2, __float2half_rn(0.f));
+  for (int r = 0; r < 2; ++r)
+    for (int row = 0; row < TILE; ++row) {
+      const int unit = 128 * (row >> 6) + 64 * r + (row & 63);
+      if (unit >= out_rows) continue;
+      for (int k = 0; k < in_cols; ++k)
+        img[(size_t)r * (W_BYTES / 2) + sw128_off(row, k) / 2] = hh_clamp(w[(size_t)unit * in_cols + k]);
+    }
+  if (!*dev) VAEX_CUDA(cudaMalloc(dev, 2 * W_BYTES));
+  VAEX_CUDA(cudaMemcpyAsync(*dev, img.data(), 2 * W_BYTES, cudaMemcpyHostToDevice, st));
+  VAEX_CUDA(cudaStreamSynchronize(st));
+  VAEX_CUDA(cudaFuncSetAttribute(head_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_DYN));
+  return VAEX_OK;
+}
+
+// One layer on tensor cores: Y = act(X W^T + b) [+ X]  ->  vector outputs (out0 [P, n0], out1 [P, n1]) or the scalar
+// wd . Y + bd.  X fp32 [P, k_in] with `pitch` floats between rows (k_in, n0, n1 multiples of 32); w_img from
+// head_tc_pack_layer; bias256 / wd256: fp32 [256], zero padded.
+int head_tc_linear(const HeadLinear& a, cudaStream_t st) {
+  using namespace hd;
+  if (a.P == 0) return VAEX_OK;
+  VAEX_CHECK(a.k_in % 32 == 0 && a.k_in <= HID && a.pitch % 8 == 0 && a.pitch >= a.k_in, "bad input shape for the head kernel");
+  VAEX_CHECK((reinterpret_cast<uintptr_t>(a.X) & 31) == 0, "input must be 32-byte aligned");
+  HeadParams prm;
+  memset(&prm, 0, sizeof(prm));
+  prm.S = a.X; prm.wl0 = a.w_img; prm.wl1 = a.w_img; prm.bl0 = a.bias256; prm.bl1 = nullptr;
+  prm.wd = a.wd256; prm.bd = a.bd; prm.nscale = a.nscale; prm.nshift = a.nshift; prm.valid = nullptr; prm.scores = a.score;
+  prm.P = (int)a.P; prm.T = (int)cdiv(a.P, PAIR); prm.sigmoid = 0;
+  prm.flags = HF_STOP0 | (a.relu ? HF_RELU0 : 0) | (a.residual ? HF_RES0 : 0) | (a.score ? 0 : HF_OUT_VEC);
+  prm.k_in = a.k_in; prm.pitch = a.pitch; prm.out0 = a.out0; prm.n0 = a.n0; prm.out1 = a.out1; prm.n1 = a.n1;
+  if (!a.score) {
+    VAEX_CHECK(a.out0 && a.n0 % 32 == 0 && a.n1 % 32 == 0 && a.n0 + a.n1 <= HID && (a.n1 == 0 || a.out1), "bad vector output");
+    VAEX_CHECK(((reinterpret_cast<uintptr_t>(a.out0) | reinterpret_cast<uintptr_t>(a.out1)) & 31) == 0, "outputs must be 32-byte aligned");
+  } else {
+    VAEX_CHECK(a.wd256 && a.bd, "the scalar output needs wd and bd");
+  }
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int clusters = std::max(1, std::min(sms / 2, prm.T));
+  head_tc_kernel<<<2 * clusters, THREADS, SMEM_DYN, st>>>(prm);
+  VAEX_LAUNCH_CHECK();
+  return VAEX_OK;
+}
 
 int head_tc_pack(vaex_model* m, cudaStream_t st) {
   using namespace hd;
@@ -367,6 +500,7 @@ int head_tc_forward(vaex_model* m, const float* S, int64_t P, const uint8_t* val
   prm.nscale = m->use_norm ? m->w("norm.scale") : nullptr;
   prm.nshift = m->use_norm ? m->w("norm.shift") : nullptr;
   prm.valid = valid; prm.scores = scores; prm.P = (int)P; prm.T = (int)cdiv(P, PAIR); prm.sigmoid = m->add_sigmoid;
+  prm.flags = 0; prm.k_in = HID; prm.pitch = HID; prm.out0 = prm.out1 = nullptr; prm.n0 = prm.n1 = 0;
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

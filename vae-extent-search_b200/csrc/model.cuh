@@ -54,7 +54,9 @@ struct vaex_model {
   std::map<std::string, vaex::HostTensor> host;
   std::map<std::string, float*> dev;   // packed fp32 device tensors, by name
   vaex::TcPack tc;
+  std::map<std::string, __half*> head_img;   // fp16 images of 256-wide layers for head_tc_linear, by name (segment family)
   vaex::ChainPack dec_chain, pred_chain, enc_mu_chain, enc_lv_chain;   // extent-VAE decoder / cost predictor / encoder on tensor cores
+  bool head_ready = false;                 // segment family: every latent / decoder / predictor layer has a head_tc image
   int use_tensor = 1;                      // VAEX_OPT_TENSOR_CORES
   int use_fused_ascent = 1;                // VAEX_OPT_FUSED_ASCENT
   vaex::DevBuf ws[6];                  // activations / staging
@@ -83,6 +85,17 @@ int tc_pack(vaex_model* m, const std::vector<float>& w0_folded, cudaStream_t st)
 // head_tc.cu
 int head_tc_pack(vaex_model* m, cudaStream_t st);
 int head_tc_forward(vaex_model* m, const float* S, int64_t P, const uint8_t* valid, float* scores, cudaStream_t st);
+// one 256-wide layer on the head kernel (head_tc.cu): Y = act(X W^T + b) [+ X] -> vector outputs or wd . Y + bd
+struct HeadLinear {
+  const float* X; int64_t P; int k_in; int64_t pitch;
+  const __half* w_img; const float* bias256;
+  bool relu, residual;
+  const float *nscale, *nshift;          // optional per-column affine on X first (eval-mode BatchNorm), fp32 [256]
+  float* out0; int n0; float* out1; int n1;
+  float* score; const float* wd256; const float* bd;
+};
+int head_tc_pack_layer(const std::vector<float>& w, int out_rows, int in_cols, __half** dev, cudaStream_t st);
+int head_tc_linear(const HeadLinear& a, cudaStream_t st);
 // chain_tc.cu
 struct ChainLayer;
 // Dropout(p) after the predictor's first ReLU, `passes` times per row on shared layer-0 activations (mc_predict):

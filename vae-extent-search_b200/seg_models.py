@@ -5,6 +5,7 @@ model_final/checkpoints/*.pt and for_inference/*.pth load with load_state_dict),
 return tuples.  Inference (eval mode) runs in libvaex_b200.so: row encoder + segment sum on the
 tcgen05 kernel, BatchNorm folded into affines at pack time, Dropout = identity.  CUDA tensors
 only -- no CPU fallback; training mode raises until the backward kernels land."""
+import numpy as np
 import torch
 import torch.nn as nn
 
@@ -19,15 +20,30 @@ class _SegmentBase(nn.Module):
         raise NotImplementedError
 
     def packed(self, fea_norm_vec=None):
-        key = (tuple((id(p), p._version) for p in self.state_dict(keep_vars=True).values()),
-               None if fea_norm_vec is None else (id(fea_norm_vec), getattr(fea_norm_vec, "_version", 0)))
+        nk = None
+        if fea_norm_vec is not None:
+            nv = fea_norm_vec.detach().cpu().numpy() if hasattr(fea_norm_vec, "detach") else fea_norm_vec
+            nk = hash(np.ascontiguousarray(nv, dtype=np.float32).tobytes())
+        key = (tuple((p.data_ptr(), p._version, float(p.detach().reshape(-1)[:: max(1, p.numel() // 16)].double().sum()))
+                     for p in self.state_dict(keep_vars=True).values()), nk)
         cached = self.__dict__.get("_packed_cache")
         if cached is not None and cached[1] == key:
             return cached[0]
         m = _lib.Model(self._kind, self._dims())
         m.load_state(self.state_dict(), fea_norm_vec)
+        m.set_option(_lib.OPT_TENSOR_CORES, int(self.__dict__.get("_tensor_cores", True)))
         self.__dict__["_packed_cache"] = (m, key)
         return m
+
+    def set_tensor_cores(self, on=True):
+        """True (default): the latent heads, the decoder and the cost predictor run as single-layer launches of the tcgen05
+        head kernel (fp16 operands, fp32 accumulate and residuals: ~1e-3 of the reference's fp32); False: fp32 SIMT (1e-5).
+        The row encoder takes VAEX_F_FORCE_SIMT per call (flags=)."""
+        self.__dict__["_tensor_cores"] = bool(on)
+        cached = self.__dict__.get("_packed_cache")
+        if cached is not None:
+            cached[0].set_option(_lib.OPT_TENSOR_CORES, int(bool(on)))
+        return self
 
     def __getstate__(self):
         d = self.__dict__.copy()
