@@ -550,6 +550,73 @@ def main_vaex(args):
                                       "per restart; all steps of a restart in ONE cluster kernel" % (hi - lo),
                               "n_gpus": world, "graphs": res3}
 
+    # ---- config 4: data-parallel training of the SegmentSumMLP on records resident in HBM (mlp_model.py:512-600) ----
+    if not args.no_configs:
+        from vaex_b200 import train as vtrain
+        n4 = min(P, 204800)                                   # records per GPU in the timed epoch (400 batches of 512)
+        offs4 = np.concatenate([[0], np.cumsum(sizes[:n4], dtype=np.int64)])
+
+        class _Set:                                           # the first n4 programs of this rank's rows, already resident
+            pass
+        ds4 = _Set()
+        ds4.device, ds4.n, ds4.F = dev, n4, F
+        ds4.features = (feats[:int(offs4[-1])] * (1.0 / norm).to(dev)).contiguous()     # SegmentDataLoader.normalize
+        ds4.offsets = offsets[:n4 + 1].contiguous()
+        ds4.sizes_i32 = np.ascontiguousarray(sizes[:n4])
+        wlab = torch.randn(F, device=dev, generator=torch.Generator(device=dev).manual_seed(4))
+        seg_mean = torch.zeros(n4, F, device=dev).index_add_(0, torch.repeat_interleave(torch.arange(n4, device=dev), sizes_d[:n4].long()),
+                                                             ds4.features) / sizes_d[:n4, None].float()
+        sc4 = seg_mean @ wlab
+        ds4.labels = (torch.argsort(torch.argsort(sc4)).float() / n4).contiguous()      # noisy-free monotone label: percentile of a hidden score
+        del seg_mean, sc4
+        torch.manual_seed(0)
+        net4 = vaex_b200.SegmentSumMLPModule(F, H, 1).to(dev)
+        tr4 = vtrain.Trainer(net4, "lambdaRankLoss", dev)
+        solo = shard.Comm(rank=0, world=1)                    # same call without the all-reduce
+        order4 = torch.randperm(n4, generator=torch.Generator().manual_seed(rank))
+
+        def epoch4(c):
+            tr4.comm = c
+            return tr4.epoch(ds4, order4, 512, 7e-4, 1e-6, 0.5, "adam", None)
+        epoch4(comm if world > 1 else solo)                   # warm-up (buffers sized)
+        res4 = {}
+        for tag, c in (("with_allreduce", comm if world > 1 else solo), ("no_allreduce", solo)):
+            barrier()
+            a4, b4 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0 = time.perf_counter()
+            a4.record(stream)
+            avg4, nb4 = epoch4(c)
+            b4.record(stream)
+            barrier()
+            wall = time.perf_counter() - t0
+            t4 = torch.tensor([a4.elapsed_time(b4), wall * 1e3], device=dev, dtype=torch.float64)
+            if world > 1:
+                dist.all_reduce(t4, op=dist.ReduceOp.MAX)
+            res4[tag] = {"ms_per_epoch_device": float(t4[0]), "ms_per_epoch_wall": float(t4[1]), "batches": nb4,
+                         "records_per_s": world * n4 / (float(t4[1]) * 1e-3)}
+        solo.close()
+        configs["config4"] = {
+            "what": "SegmentSumMLP training (LambdaRank loss, clip 0.5, Adam lr 7e-4), batch 512 per GPU, %d records per GPU resident in "
+                    "HBM, one vaex_trainer_epoch call per epoch; data parallel: one NCCL all-reduce of the 0.96 MB gradient per step" % n4,
+            "n_gpus": world, "records_per_s": res4["with_allreduce"]["records_per_s"], "ms_per_step": res4["with_allreduce"]["ms_per_epoch_wall"] / max(1, nb4),
+            "allreduce_share": max(0.0, 1.0 - res4["no_allreduce"]["ms_per_epoch_wall"] / res4["with_allreduce"]["ms_per_epoch_wall"]) if world > 1 else 0.0,
+            "detail": res4, "final_moving_average_loss": float(avg4.item())}
+        if world == 1 and not args.no_cpu:                    # the reference's loop on the host cores, a few batches
+            from oracle import torch_oracle as O
+            nbc = 6
+            fh4, lab4 = ds4.features[:int(offs4[nbc * 512])].cpu().numpy(), ds4.labels[:nbc * 512].cpu().numpy()
+            batches = [(sizes[b * 512:(b + 1) * 512], fh4[int(offs4[b * 512]):int(offs4[(b + 1) * 512])], lab4[b * 512:(b + 1) * 512])
+                       for b in range(nbc)]
+            torch.set_num_threads(os.cpu_count() or 1)
+            P0 = {k: v.detach().cpu() for k, v in net4.state_dict().items()}
+            O.train_steps(P0, batches[:1], "lambdaRankLoss")
+            t0 = time.perf_counter()
+            O.train_steps(P0, batches, "lambdaRankLoss")
+            configs["config4"]["cpu_reference_records_per_s"] = nbc * 512 / (time.perf_counter() - t0)
+            configs["config4"]["cpu_reference"] = "oracle port of _fit_a_model's step (torch CPU autograd, %d cores), %d batches of 512" % (os.cpu_count() or 1, nbc)
+        tr4.close()
+        del ds4, net4, tr4
+
     # ---- parity on this run's own inputs + the CPU leg (rank 0, N = 1): the oracle scores the first programs of rank 0 ----
     parity, cpu_baseline = None, None
     if not args.no_cpu and world == 1:

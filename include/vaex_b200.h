@@ -312,6 +312,23 @@ int vaex_adam_step(float* params_dev, const float* grads_dev, float* m_dev, floa
 int vaex_sgd_step(float* params_dev, const float* grads_dev, int64_t n, float lr, float weight_decay,
                   float grad_scale, void* stream);
 
+/* One epoch of the loop above in a single call (MLPModelInternal._fit_a_model's inner loop, mlp_model.py:545-570; the SGD
+ * fine-tuning loop :628-640 with optimizer = 1): for every batch of `batch` (<= 4096) programs order[s : s + batch) of the
+ * device-resident set -- vaex_gather_segments, vaex_trainer_forward_backward, vaex_allreduce_grads over comm_or_null (data
+ * parallel: every rank passes its own shard and order; the mean gradient is applied), clip_grad_norm_ + Adam (optimizer 0;
+ * betas 0.9 / 0.999, eps 1e-8, L2 weight decay) or SGD (1) -- and the reference's moving-average loss
+ * (avg = 0.95 avg + 0.05 loss; the first batch initialises it when first_batch_initialises_avg != 0) in *avg_loss_dev.
+ * sizes_host int32 [programs of the set] (rows per program, the host copy of the loader's segment_sizes), order_host /
+ * order_dev: the same int64 permutation on both sides.  *step_inout is Adam's step counter.  Asynchronous on `stream`
+ * except for host-side buffer growth. */
+typedef struct vaex_comm* vaex_comm_t;
+int vaex_trainer_epoch(vaex_trainer_t t, vaex_comm_t comm_or_null, float* params_dev, float* grads_dev, float* m_dev,
+                       float* v_dev, const float* feats_dev, const int32_t* seg_offsets_dev, const int32_t* sizes_host,
+                       const float* labels_dev, const int64_t* order_host, const int64_t* order_dev, int64_t n,
+                       int32_t batch, int loss_type, int optimizer, float lr, float weight_decay, float clip_norm,
+                       int64_t* step_inout, float* avg_loss_dev, int first_batch_initialises_avg, int64_t* batches_out,
+                       void* stream);
+
 /* ---- training of the extent-family VAECostPredictor (train_regression, vae_extent_search.py:1413-1440; losses
  *      utils/training.py:133-226) ---------------------------------------------------------------------------- */
 /* pair_loss_fn (training.py:144-166): mean over i < j of max(0, -sign(t_j - t_i) (p_j - p_i) + margin); n <= 4096 */

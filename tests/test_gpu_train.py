@@ -217,3 +217,40 @@ def test_mlp_model_update_refits_and_predicts(monkeypatch):
     assert len(model.dataset) == 10000
     pred2 = model.predict_features(task, feats)
     assert spearmanr(pred2[keep], score2[keep]).statistic > max(0.7, rho1 - 0.05)
+
+
+def test_trainer_epoch_equals_the_step_loop():
+    """vaex_trainer_epoch (the whole per-batch loop in one C-ABI call) == the same batches driven one by one through
+    gather + Trainer.step, bit for bit: parameters, Adam moments, step counter and the moving-average loss; ragged last
+    batch, Adam with clipping and the SGD fine-tuning form."""
+    rng = np.random.default_rng(21)
+    n = 1500
+    feats = np.empty(n, dtype=object)
+    for i in range(n):
+        feats[i] = rng.random((int(rng.integers(1, 9)), 164), dtype=np.float32)
+    labels = rng.random(n).astype(np.float32)
+    ds = vaex_b200.Dataset.create_one_task(vaex_b200.LearningTask("wk", "cuda"), feats, labels)
+    loader = vaex_b200.SegmentDataLoader(ds, 512, "cuda:0", False, False, {})
+    data = train.ResidentSet(loader, "cuda:0")
+    for optimizer, lr, wd, clip in (("adam", 7e-4, 1e-6, 0.5), ("sgd", 4e-2, 0.0, 0.0)):
+        torch.manual_seed(3)
+        net_a = vaex_b200.SegmentSumMLPModule(164, 256, 1).cuda()
+        net_b = vaex_b200.SegmentSumMLPModule(164, 256, 1).cuda()
+        net_b.load_state_dict(net_a.state_dict())
+        ta, tb = train.Trainer(net_a, "lambdaRankLoss"), train.Trainer(net_b, "lambdaRankLoss")
+        order = torch.randperm(n, generator=torch.Generator().manual_seed(5))
+        avg_a, nb = None, 0
+        for _ in range(2):                                         # two epochs: the average carries over
+            avg_a, nb = ta.epoch(data, order, 512, lr, wd, clip, optimizer, avg_a)
+        assert nb == 3
+        avg_b = None
+        for _ in range(2):
+            for s in range(0, n, 512):
+                idx = order[s:s + 512]
+                off, bf, bl = data.batch(idx.numpy(), idx.cuda())
+                loss = tb.step(off, bf, bl, lr, wd, clip, optimizer)
+                avg_b = loss.clone() if avg_b is None else avg_b * 0.95 + loss * 0.05
+        assert torch.equal(ta.params, tb.params) and ta.t == tb.t
+        if optimizer == "adam":
+            assert torch.equal(ta.m, tb.m) and torch.equal(ta.v, tb.v)
+        np.testing.assert_allclose(avg_a.item(), avg_b.item(), rtol=1e-6)

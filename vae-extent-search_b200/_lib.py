@@ -66,6 +66,8 @@ SIGNATURES = {
     "vaex_trainer_param_offset": ([vp, ctypes.c_char_p, ctypes.POINTER(i64), ctypes.POINTER(i64)], ctypes.c_int),
     "vaex_gather_segments": ([vp, i32, vp, vp, i64, vp, vp, vp, vp, vp], ctypes.c_int),
     "vaex_trainer_forward_backward": ([vp, vp, vp, vp, vp, vp, i64, i64, ctypes.c_int, vp, vp, vp], ctypes.c_int),
+    "vaex_trainer_epoch": ([vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, ctypes.c_int, ctypes.c_int, f32, f32, f32,
+                            ctypes.POINTER(i64), vp, ctypes.c_int, ctypes.POINTER(i64), vp], ctypes.c_int),
     "vaex_loss_eval": ([ctypes.c_int, vp, vp, i64, vp, vp, vp], ctypes.c_int),
     "vaex_adam_step": ([vp, vp, vp, vp, i64, i64, f32, f32, f32, f32, f32, f32, f32, vp, vp], ctypes.c_int),
     "vaex_sgd_step": ([vp, vp, i64, f32, f32, f32, vp], ctypes.c_int),

@@ -193,6 +193,7 @@ static int transpose_to(const float* W, int rows, int cols, float* Wt, cudaStrea
 
 #include "train_loss.inc"
 #include "train_step.inc"
+#include "train_epoch.inc"
 #include "train_vae.inc"
 #include "train_segvae.inc"
 #include "train_segreg.inc"

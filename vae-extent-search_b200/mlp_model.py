@@ -409,22 +409,10 @@ class MLPModelInternal:
         return train_loader, valid_loader
 
     def _epoch(self, trainer, data, batch_size, shuffle, lr, wd, clip, optimizer, avg):
-        """One pass over the resident set; the running loss (moving_average, momentum 0.95) stays on
-        the device and is read back once by the caller."""
+        """One pass over the resident set in one C-ABI call (Trainer.epoch -> vaex_trainer_epoch); the running loss
+        (moving_average, momentum 0.95) stays on the device and is read back once by the caller."""
         order = torch.randperm(data.n) if shuffle else torch.arange(data.n)       # same CPU stream as the reference
-        order_dev = order.to(data.device)
-        order_host = order.numpy()
-        n_batches = 0
-        for s in range(0, data.n, batch_size):
-            e = min(s + batch_size, data.n)
-            off, feats, labels = data.batch(order_host[s:e], order_dev[s:e])
-            loss = trainer.step(off, feats, labels, lr, wd, clip, optimizer)
-            if avg is None:
-                avg = loss.clone()
-            else:
-                avg.mul_(0.95).add_(loss, alpha=0.05)
-            n_batches += 1
-        return avg, n_batches
+        return trainer.epoch(data, order, batch_size, lr, wd, clip, optimizer, avg)
 
     def _fit_a_model(self, train_set, valid_set=None, valid_train_set=None, n_epoch=None):
         from . import train as _train

@@ -96,6 +96,30 @@ class Trainer:
             self.sgd_step(lr, weight_decay, grad_scale=scale)
         return self.loss
 
+    def epoch(self, data, order, batch_size, lr, weight_decay=0.0, grad_clip=0.0, optimizer="adam", avg=None):
+        """One pass over the resident set `data` in the order `order` (int64 CPU tensor) as ONE C-ABI call
+        (vaex_trainer_epoch): gather, forward + loss + backward, all-reduce (self.comm, a shard.Comm, when set), clip +
+        Adam / SGD and the moving-average loss for every batch, no Python between the launches.
+        -> (moving-average loss as a device scalar, number of batches)."""
+        order = order.to(torch.int64).contiguous()
+        order_dev = order.to(self.device)
+        first = avg is None
+        if first:
+            avg = torch.zeros(1, device=self.device)
+        step, nb = _lib.i64(self.t), _lib.i64(0)
+        comm = getattr(self, "comm", None)
+        if comm is None and self.world() > 1:
+            raise _lib.VaexError("data-parallel epochs run through the library's communicator: set trainer.comm = shard.Comm()")
+        _lib.check(self.lib.vaex_trainer_epoch(
+            self.h, comm.h if comm is not None else None, _lib.ptr(self.params), _lib.ptr(self.grads), _lib.ptr(self.m), _lib.ptr(self.v),
+            _lib.ptr(data.features), _lib.ptr(data.offsets), data.sizes_i32.ctypes.data, _lib.ptr(data.labels),
+            order.data_ptr(), _lib.ptr(order_dev), order.shape[0], int(batch_size), self.loss_id, 0 if optimizer == "adam" else 1,
+            float(lr), float(weight_decay), float(grad_clip or 0.0), ctypes.byref(step), _lib.ptr(avg), int(first), ctypes.byref(nb),
+            _lib.stream_ptr()))
+        self.t = int(step.value)
+        self._keep = (order, order_dev)              # alive until the stream has consumed them
+        return avg, int(nb.value)
+
     def loss_value(self, preds, labels):
         """self.loss_func(preds, labels) on the GPU (<= 4096 predictions) -> device scalar."""
         out = torch.zeros(1, device=preds.device)
@@ -122,6 +146,7 @@ class ResidentSet:
     def __init__(self, loader, device):
         self.device = torch.device(device)
         self.sizes_host = loader.segment_sizes.numpy().astype(np.int64)
+        self.sizes_i32 = np.ascontiguousarray(loader.segment_sizes.numpy().astype(np.int32))
         self.n = len(self.sizes_host)
         self.features = loader.features.to(self.device, torch.float32).contiguous()
         self.labels = loader.labels.to(self.device, torch.float32).contiguous()
