@@ -59,6 +59,7 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-configs", action="store_true", help="skip the config 3 / config 5 lines")
+    ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of replaying the captured step graph")
     ap.add_argument("--no-kernels", action="store_true", help="skip the per-kernel roofline list")
     return ap.parse_args()
 
@@ -317,8 +318,9 @@ def main_vaex(args):
     pack_ms = pk0.elapsed_time(pk1)
     row_src = {"buf": image, "flags": flags | _lib.F_FEATS_IMAGE}
 
-    def step():
-        decode_stage(z, extents, P)
+    def step(st=st):
+        _lib.check(lib.vaex_decode_snap(vmodel.h, _lib.ptr(z), P, None, _lib.ptr(extents), _lib.ptr(mean_d), _lib.ptr(scale_d), SNAP,
+                                        _lib.ptr(ext_d), _lib.ptr(last_d), 64, st))
         _lib.check(lib.vaex_segment_offsets(_lib.ptr(sizes_d), P, _lib.ptr(offsets), st))
         _lib.check(lib.vaex_segsum_mlp_forward(model.h, _lib.ptr(row_src["buf"]), _lib.ptr(offsets), P, rows, _lib.ptr(scores),
                                                row_src["flags"], st))
@@ -326,6 +328,32 @@ def main_vaex(args):
         if world > 1:       # candidate merge: the path's only exchange (one ncclAllGather of 16-byte records + one merge CTA)
             _lib.check(lib.vaex_topk_allgather_merge(comm.h, _lib.ptr(top_v), _lib.ptr(top_i), _lib.ptr(n_out), TOPK, rank * P,
                                                      _lib.ptr(mer_v), _lib.ptr(mer_i), _lib.ptr(mer_n), st))
+
+    graph_note = {"graph": False}
+
+    def graphed(fn):
+        """The step's 18 launches captured ONCE into a CUDA graph (every entry point of the step is stream-ordered: grow-only
+        workspaces, cudaMallocAsync scratch, no host read-back) and replayed per step: the timed loop is then one
+        cudaGraphLaunch per step whatever the box's host cores are doing.  --no-graph (or a failed capture) times the
+        eager launches instead; `config.cuda_graph` says which."""
+        if args.no_graph:
+            return fn
+        try:
+            side = torch.cuda.Stream(device=dev)
+            side.wait_stream(stream)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=side, capture_error_mode="thread_local"):
+                fn(side.cuda_stream)
+            stream.wait_stream(side)
+            torch.cuda.synchronize()
+            g.replay()
+            torch.cuda.synchronize()
+            graph_note["graph"] = True
+            return lambda: g.replay()
+        except Exception as e:      # noqa: BLE001 -- eager launches are the same kernels
+            graph_note["error"] = str(e)[:200]
+            torch.cuda.synchronize()
+            return fn
 
     def barrier():
         if world > 1:
@@ -379,26 +407,32 @@ def main_vaex(args):
     sampler = ClockSampler(local)
     sampler.start()
     l0 = lib.vaex_launch_count()
+    step()
+    launches_per_step = lib.vaex_launch_count() - l0     # counted on an eager step: a graph replay runs the same nodes
+    run_step = graphed(step)
+    run_step()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     sampler.active = True
     e0.record(stream)
     for _ in range(args.steps):
-        step()
+        run_step()
     e1.record(stream)
     barrier()
     sampler.active = False
-    launches = lib.vaex_launch_count() - l0
+    launches = launches_per_step * args.steps
     ms = e0.elapsed_time(e1) / args.steps
     torch.cuda.cudart().cudaProfilerStop()
     # the same timed loop with the rows resident as fp32 (loader warps instead of TMA)
     row_src.update(buf=feats, flags=flags)
     step()
+    run_f32 = graphed(step)
+    run_f32()
     barrier()
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     f0.record(stream)
     for _ in range(args.steps):
-        step()
+        run_f32()
     f1.record(stream)
     barrier()
     ms_f32 = f0.elapsed_time(f1) / args.steps
@@ -785,6 +819,7 @@ def main_vaex(args):
                        "rows": "fp16 row image [rows, 192] (%.1f GB/GPU), packed once per pool from the fp32 rows by "
                                "vaex_rows_pack_image (%.2f ms, outside the step: the pool is static across scoring rounds); scores "
                                "bit-identical with the fp32-row path, which is timed in value_fp32_rows" % (image.numel() / 1e9, pack_ms),
+                       "cuda_graph": graph_note,
                        "l2": "inputs (%.1f GB/GPU) exceed L2; no flush needed" % (image.numel() / 1e9),
                        "parallelism": "candidates sharded over %d GPU(s); top-k all-gather merge only" % world,
                        "merged_equals_global_topk": merged_ok},

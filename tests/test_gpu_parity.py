@@ -407,12 +407,14 @@ def test_extent_chain_tensor_cores(n):
     got_x = vae.decode(zd).cpu().numpy()
     assert l2_err(got_x, want_x) < TC_RTOL, l2_err(got_x, want_x)
     assert rel_err(got_x, want_x) < 4 * TC_RTOL, rel_err(got_x, want_x)
-    # encoder trunk + latent heads (two passes of the chain kernel when logvar is wanted)
+    # encoder trunk + latent heads (one pass of the chain kernel: [fc_mu; fc_logvar] stacked into a 128-wide output layer)
     x = g["x"][:n].copy() if n <= 300 else (rng.standard_normal((n, 48)) * g["x"].std()).astype(np.float32)
     want_mu, want_lv = O.vae_encode(split_sd(g, "vae."), x)
     got_mu, got_lv = vae.encode(torch.from_numpy(x).cuda())
     for got, want in ((got_mu, want_mu), (got_lv, want_lv), (vae.encode(torch.from_numpy(x).cuda(), use_mean=True), want_mu)):
         assert l2_err(got.cpu().numpy(), want.numpy()) < TC_RTOL and rel_err(got.cpu().numpy(), want.numpy()) < 4 * TC_RTOL
+    # the stacked two-head pass and the mu-only chain run the same k-order on the same fp16 operands
+    assert torch.equal(got_mu, vae.encode(torch.from_numpy(x).cuda(), use_mean=True))
     got_c = reg.predict_cost(zd).cpu().numpy()
     assert got_c.shape == (n,)
     assert l2_err(got_c, want_c) < TC_RTOL, l2_err(got_c, want_c)

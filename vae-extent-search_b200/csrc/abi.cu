@@ -170,7 +170,7 @@ static int pack_encoder(vaex_model* m, cudaStream_t st) {
 }
 
 struct ChainLayer { const std::vector<float>* w; const std::vector<float>* b; int out, in; };
-int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode, cudaStream_t st);
+int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode, cudaStream_t st, int two_heads = 0);
 
 static ChainLayer chain_layer(vaex_model* m, const std::string& pre) {
   HostTensor& w = m->host[pre + ".weight"];
@@ -185,6 +185,19 @@ static int pack_encoder_chains(vaex_model* m, cudaStream_t st) {
                                       chain_layer(m, "fc_mu")}, 0, st));
   TRY(chain_tc_pack(m->enc_lv_chain, {chain_layer(m, "encoder.0"), chain_layer(m, "encoder.2"), chain_layer(m, "encoder.4"),
                                       chain_layer(m, "fc_logvar")}, 0, st));
+  // both heads in ONE pass: [fc_mu; fc_logvar] stacked as a 128-wide output layer, W0 in the operand's free atom
+  if (m->L == 64) {
+    HostTensor& both = m->host["fc_both.weight"];
+    HostTensor& bothb = m->host["fc_both.bias"];
+    both.rows = 2 * m->L; both.cols = m->H;
+    both.v = m->host["fc_mu.weight"].v;
+    both.v.insert(both.v.end(), m->host["fc_logvar.weight"].v.begin(), m->host["fc_logvar.weight"].v.end());
+    bothb.rows = 1; bothb.cols = 2 * m->L;
+    bothb.v = m->host["fc_mu.bias"].v;
+    bothb.v.insert(bothb.v.end(), m->host["fc_logvar.bias"].v.begin(), m->host["fc_logvar.bias"].v.end());
+    TRY(chain_tc_pack(m->enc_both_chain, {chain_layer(m, "encoder.0"), chain_layer(m, "encoder.2"), chain_layer(m, "encoder.4"),
+                                          chain_layer(m, "fc_both")}, 0, st, 1));
+  }
   return VAEX_OK;
 }
 
@@ -330,8 +343,9 @@ int vaex_model_destroy(vaex_model_t h) {
   if (h->tc.wl0) cudaFree(h->tc.wl0);
   if (h->tc.wl1) cudaFree(h->tc.wl1);
   for (auto& sl : h->slots) { if (sl.feats) cudaFree(sl.feats); if (sl.off) cudaFree(sl.off); if (sl.scores) cudaFree(sl.scores); }
-  for (ChainPack* cp : {&h->dec_chain, &h->pred_chain, &h->enc_mu_chain, &h->enc_lv_chain}) {
+  for (ChainPack* cp : {&h->dec_chain, &h->pred_chain, &h->enc_mu_chain, &h->enc_lv_chain, &h->enc_both_chain}) {
     if (cp->w) cudaFree(cp->w);
+    if (cp->w0) cudaFree(cp->w0);
     if (cp->bias) cudaFree(cp->bias);
   }
   for (auto& pn : h->pinned) if (pn.p) cudaFreeHost(pn.p);

@@ -67,6 +67,12 @@ struct ChainParams {
   // share layer 0; pass t keeps element (row, c) iff drop_mask[t][row][c] != 0, else iff the Philox draw of
   // dropout_kernel (elementwise.cu) for seed drop_seed + t says so.  mc_T == 1: out = cost; mc_T > 1: out = mean over
   // the passes, var_out = unbiased variance.
+  // encoder with both latent heads in one pass: the output layer is [fc_mu; fc_logvar] stacked (N = 2 * out_dim), columns
+  // [out_dim, 2 out_dim) go to out2; W0 is then NOT resident -- its one-atom image lives in atom 2 of the operand (free
+  // while layer 0 runs, overwritten by layer 0's second epilogue) and is re-stored from registers for every tile
+  float* out2;
+  const __half* w0_img;      // [2][16 KB] per-rank images of layer 0 when w0_in_a
+  int32_t w0_in_a;
   const uint8_t* drop_mask;  // [mc_T][n, 256] or null
   float* var_out;            // [n] or null
   uint64_t drop_seed;
@@ -165,6 +171,19 @@ chain_tc_kernel(const ChainParams p) {
                     ptx::cvt_h2_sat(xin[8 * m], xin[8 * m + 1]), ptx::cvt_h2_sat(xin[8 * m + 2], xin[8 * m + 3]),
                     ptx::cvt_h2_sat(xin[8 * m + 4], xin[8 * m + 5]), ptx::cvt_h2_sat(xin[8 * m + 6], xin[8 * m + 7]));
     };
+    uint4 w0r[2] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};      // this thread's 32 B of the W0 image (w0_in_a)
+    if (p.w0_in_a) {
+      const uint4* g = reinterpret_cast<const uint4*>(p.w0_img) + (size_t)rank * (ATOM / 16) + 2 * threadIdx.x;
+      w0r[0] = __ldg(g);
+      w0r[1] = __ldg(g + 1);
+    }
+    auto store_w0 = [&]() {
+      if (p.w0_in_a) {
+        const uint32_t dst = sbase + p.a_off + 2 * ATOM + 32u * threadIdx.x;
+        ptx::sts_v4(dst, w0r[0].x, w0r[0].y, w0r[0].z, w0r[0].w);
+        ptx::sts_v4(dst + 16, w0r[1].x, w0r[1].y, w0r[1].z, w0r[1].w);
+      }
+    };
     auto publish = [&](int b) {
       ptx::fence_proxy_async();
       ptx::tc_fence_before();
@@ -179,7 +198,7 @@ chain_tc_kernel(const ChainParams p) {
     uint32_t acc_use0 = 0, acc_use1 = 0, lc = 0;
     fetch(cluster);
     if (cluster < p.T) {
-      pack_z();
+      { pack_z(); store_w0(); }
       publish(B_IN0);
     }
     // ---- MC-dropout passes of the predictor (mc_T >= 1): keep bits of this thread's 32 columns of n-half nh ----
@@ -207,14 +226,17 @@ chain_tc_kernel(const ChainParams p) {
       } else {
         const int64_t chunk = r / p.drop_chunk;
         const Philox gen(p.drop_seed + (uint64_t)pass + 0x9E3779B97F4A7C15ull * (uint64_t)chunk);
-        const uint64_t q0 = (uint64_t)(((r - chunk * p.drop_chunk) * HID + col) >> 2);
+        const uint64_t q0 = (uint64_t)(((r - chunk * p.drop_chunk) * HID + col) >> 3);
+        const uint32_t thr = dropout_threshold(p.drop_p);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
+        for (int j = 0; j < 4; ++j) {                      // eight 16-bit draws per call (dropout_kernel's layout)
           const uint4 u = gen(q0 + j, 0);
-          bits |= (uint32_t)(u01(u.x) >= p.drop_p) << (4 * j);
-          bits |= (uint32_t)(u01(u.y) >= p.drop_p) << (4 * j + 1);
-          bits |= (uint32_t)(u01(u.z) >= p.drop_p) << (4 * j + 2);
-          bits |= (uint32_t)(u01(u.w) >= p.drop_p) << (4 * j + 3);
+          const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            bits |= (uint32_t)((w[k] & 0xffffu) >= thr) << (8 * j + 2 * k);
+            bits |= (uint32_t)((w[k] >> 16) >= thr) << (8 * j + 2 * k + 1);
+          }
         }
       }
       return bits;
@@ -308,7 +330,7 @@ chain_tc_kernel(const ChainParams p) {
           if (lastp) {
             ptx::tc_fence_before();
             if (t + n_clusters < p.T) {
-              pack_z();
+              { pack_z(); store_w0(); }
               publish(B_IN0);
             }
           }
@@ -381,7 +403,7 @@ chain_tc_kernel(const ChainParams p) {
             // every MMA of this tile has completed: z of the next tile goes in first, then the scalar head
             ptx::tc_fence_before();
             if (t + n_clusters < p.T) {
-              pack_z();
+              { pack_z(); store_w0(); }
               publish(B_IN0);
             }
             const float dot = dot0 + dot1;
@@ -390,19 +412,42 @@ chain_tc_kernel(const ChainParams p) {
             if (cg == 0 && r < p.n) p.out[r] = ((dot + s_dot[row]) + (s_dot[TILE + row] + s_dot[2 * TILE + row])) + s_bias[p.wd_off + HID];
           }
         } else {
-          // output layer (N = 64): 16 columns of this row -> fp32 x and / or snapped extents
-          const int c0 = 16 * cg;
-          const float4* b = reinterpret_cast<const float4*>(s_bias + p.b_off[l] + c0);
+          // output layer (N <= 64): 16 columns of this row -> fp32 x and / or snapped extents; two stacked heads (N = 128,
+          // out2): 32 columns, the upper 64 go to out2
+          const bool two = p.out2 != nullptr;
           ptx::mbar_wait(bar(B_ACC0), acc_use0 & 1);
           ++acc_use0;
           ptx::tc_fence_after();
-          uint32_t v[16];
-          ptx::tmem_ld16(t_acc + c0, v);
+          uint32_t v[16], v2[16];
+          ptx::tmem_ld16(t_acc + (two ? 32 * cg : 16 * cg), v);
+          if (two) ptx::tmem_ld16(t_acc + 32 * cg + 16, v2);
           if (t + n_clusters < p.T) {
-            pack_z();
+            { pack_z(); store_w0(); }
             publish(B_IN0);
           }
           ptx::tmem_ld_wait();
+          if (two) {
+            if (r < p.n) {
+              const int cb = 32 * cg;                                   // column in the stacked layer
+              float* dst = (cb < p.out_dim ? p.out : p.out2) + r * p.out_dim + (cb & (p.out_dim - 1));
+              const float* bb = s_bias + p.b_off[l] + cb;
+#pragma unroll
+              for (int j = 0; j < 2; ++j) {
+                ptx::stg_f8(dst + 8 * j, __uint_as_float(v[8 * j]) + bb[8 * j], __uint_as_float(v[8 * j + 1]) + bb[8 * j + 1],
+                            __uint_as_float(v[8 * j + 2]) + bb[8 * j + 2], __uint_as_float(v[8 * j + 3]) + bb[8 * j + 3],
+                            __uint_as_float(v[8 * j + 4]) + bb[8 * j + 4], __uint_as_float(v[8 * j + 5]) + bb[8 * j + 5],
+                            __uint_as_float(v[8 * j + 6]) + bb[8 * j + 6], __uint_as_float(v[8 * j + 7]) + bb[8 * j + 7]);
+                ptx::stg_f8(dst + 16 + 8 * j, __uint_as_float(v2[8 * j]) + bb[16 + 8 * j], __uint_as_float(v2[8 * j + 1]) + bb[17 + 8 * j],
+                            __uint_as_float(v2[8 * j + 2]) + bb[18 + 8 * j], __uint_as_float(v2[8 * j + 3]) + bb[19 + 8 * j],
+                            __uint_as_float(v2[8 * j + 4]) + bb[20 + 8 * j], __uint_as_float(v2[8 * j + 5]) + bb[21 + 8 * j],
+                            __uint_as_float(v2[8 * j + 6]) + bb[22 + 8 * j], __uint_as_float(v2[8 * j + 7]) + bb[23 + 8 * j]);
+              }
+            }
+            ptx::tc_fence_before();
+            continue;
+          }
+          const int c0 = 16 * cg;
+          const float4* b = reinterpret_cast<const float4*>(s_bias + p.b_off[l] + c0);
           if (r < p.n && c0 < p.N[l] && vec8_ok) {
             // two 256-bit stores per output: full sectors for the lane-per-row pattern
             float y[16];
@@ -510,7 +555,7 @@ struct ChainLayer { const std::vector<float>* w; const std::vector<float>* b; in
 
 // Packs `layers` (row-major [out, in] fp32) into the per-rank swizzled images + fp16 biases and fills the
 // shape part of ChainParams.  The last entry of a MODE_DOT chain is the scalar head (kept fp32, not an MMA).
-int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode, cudaStream_t st) {
+int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode, cudaStream_t st, int two_heads) {
   using namespace ch;
   cp.ready = false;
   const int n_mma = mode == MODE_DOT ? (int)layers.size() - 1 : (int)layers.size();
@@ -519,38 +564,45 @@ int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode
   static_assert(sizeof(ChainParams) <= sizeof(cp.params_storage), "ChainPack::params_storage too small");
   P.mode = mode;
   P.n_mma = n_mma;
+  const int out_max = two_heads ? 128 : 64;              // two stacked 64-wide heads: one N = 128 output layer
   // When the fp32 biases do not fit beside the weights and the operand (the encoder: 160 KB + 64 KB + 3.3 KB), layer 0's
   // bias rides in its GEMM instead: two spare input columns hold the constant 1 and W0 gets fp16 hi / lo parts of b0.
-  auto smem_need = [&](bool fold0) {
+  // When even that does not fit (both latent heads: 176 KB of weights), W0's one-atom image moves into the operand.
+  auto smem_need = [&](bool fold0, bool w0a) {
     int w = 0, b = 0;
     for (int l = 0; l < n_mma; ++l) {
       const bool out_layer = mode == MODE_VECTOR && l == n_mma - 1;
       const int N = out_layer ? std::max(16, (layers[l].out + 15) / 16 * 16) : HID;
-      w += (N / 2) * (l == 0 ? K0 : HID) * 2;
+      if (!(w0a && l == 0)) w += (N / 2) * (l == 0 ? K0 : HID) * 2;
       if (!(fold0 && l == 0)) b += N;
     }
     if (mode == MODE_DOT) b += HID + 4;
     return w + 4 * ATOM + b * 4 + 64 + (mode == MODE_DOT ? 6 * TILE * 4 : 0);
   };
-  const bool fold0 = smem_need(false) > SMEM_MAX && n_mma > 1 && layers[0].in + 2 <= K0 && layers[0].out == HID &&
-                     smem_need(true) <= SMEM_MAX;
+  const bool can_fold = n_mma > 1 && layers[0].in + 2 <= K0 && layers[0].out == HID;
+  const bool fold0 = smem_need(false, false) > SMEM_MAX && can_fold;
+  const bool w0a = fold0 && smem_need(true, false) > SMEM_MAX && smem_need(true, true) <= SMEM_MAX;
+  if (smem_need(fold0, w0a) > SMEM_MAX) return VAEX_OK;
   P.ones_col = fold0 ? layers[0].in : -1;
+  P.w0_in_a = w0a ? 1 : 0;
   int woff = 0, boff = 0;
   for (int l = 0; l < n_mma; ++l) {
     const ChainLayer& L = layers[l];
     const int K = l == 0 ? K0 : HID;
     const bool out_layer = mode == MODE_VECTOR && l == n_mma - 1;
     const int N = out_layer ? std::max(16, (L.out + 15) / 16 * 16) : HID;
-    if ((l == 0 ? L.in > K0 : L.in != HID) || (out_layer ? L.out > 64 : L.out != HID)) return VAEX_OK;   // shape outside this kernel
+    if ((l == 0 ? L.in > K0 : L.in != HID) || (out_layer ? L.out > out_max : L.out != HID)) return VAEX_OK;   // shape outside this kernel
     P.K[l] = K; P.N[l] = N; P.w_off[l] = woff; P.b_off[l] = boff;
     P.b_scale[l] = (fold0 && l == 0) ? 0.f : 1.f;
-    woff += (N / 2) * K * 2;
+    if (!(w0a && l == 0)) woff += (N / 2) * K * 2;
     if (!(fold0 && l == 0)) boff += N;
   }
   P.in_dim = layers[0].in;
-  P.out_dim = mode == MODE_VECTOR ? layers[n_mma - 1].out : 1;
+  P.out_dim = mode == MODE_VECTOR ? (two_heads ? layers[n_mma - 1].out / 2 : layers[n_mma - 1].out) : 1;
+  if (two_heads && (mode != MODE_VECTOR || layers[n_mma - 1].out != 128)) return VAEX_OK;
   P.w_bytes = woff;
   P.a_off = woff;
+  if (w0a) P.w_off[0] = P.a_off + 2 * ATOM;              // atom 2 of the operand
   P.wd_off = boff;
   if (mode == MODE_DOT) {
     if (layers[n_mma].in != HID || layers[n_mma].out != 1) return VAEX_OK;
@@ -574,6 +626,7 @@ int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode
     if (h & 1023u) return VAEX_OK;                     // stay on the SIMT path
   }
   std::vector<__half> img((size_t)woff, __float2half_rn(0.f));   // 2 ranks x (woff bytes / 2) halves
+  std::vector<__half> img0(w0a ? (size_t)ATOM : 0, __float2half_rn(0.f));   // 2 ranks x one atom (16 KB) when W0 lives in the operand
   std::vector<float> bias((size_t)boff, 0.f);
   for (int l = 0; l < n_mma; ++l) {
     const ChainLayer& L = layers[l];
@@ -583,7 +636,7 @@ int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode
         // a 256-wide layer is issued as two 128-column MMAs: image rows [64 h, +64) of rank r = units 128 h + 64 r + [0, 64)
         const int unit = P.N[l] == HID ? 128 * (u >> 6) + 64 * r + (u & 63) : r * nh + u;
         if (unit >= L.out) continue;
-        __half* dst = img.data() + (size_t)r * (woff / 2) + P.w_off[l] / 2;
+        __half* dst = (w0a && l == 0) ? img0.data() + (size_t)r * (ATOM / 2) : img.data() + (size_t)r * (woff / 2) + P.w_off[l] / 2;
         for (int k = 0; k < L.in; ++k) dst[sw_off(nh, u, k) / 2] = c_clamp((*L.w)[(size_t)unit * L.in + k]);
         if (fold0 && l == 0) {
           const __half hi = c_clamp((*L.b)[unit]);
@@ -605,6 +658,10 @@ int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode
   VAEX_CUDA(cudaMalloc(&cp.bias, std::max<size_t>(bias.size(), 1) * sizeof(float)));
   VAEX_CUDA(cudaMemcpyAsync(cp.w, img.data(), img.size() * sizeof(__half), cudaMemcpyHostToDevice, st));
   VAEX_CUDA(cudaMemcpyAsync(cp.bias, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice, st));
+  if (w0a) {
+    if (!cp.w0) VAEX_CUDA(cudaMalloc(&cp.w0, 2 * ATOM));
+    VAEX_CUDA(cudaMemcpyAsync(cp.w0, img0.data(), 2 * ATOM, cudaMemcpyHostToDevice, st));
+  }
   VAEX_CUDA(cudaStreamSynchronize(st));
   VAEX_CUDA(cudaFuncSetAttribute(chain_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_MAX));
   cp.ready = true;
@@ -612,13 +669,17 @@ int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode
 }
 
 int chain_tc_run(const ChainPack& cp, const float* X, int64_t n, float* out, int32_t* extents, const float* mean,
-                 const float* scale, int snap_mode, const float* wd, const float* bd, cudaStream_t st, const ChainDropout* drop) {
+                 const float* scale, int snap_mode, const float* wd, const float* bd, cudaStream_t st, const ChainDropout* drop,
+                 float* out2) {
   using namespace ch;
   VAEX_CHECK(cp.ready, "tcgen05 chain not packed");
   if (n == 0) return VAEX_OK;
   ChainParams P = *reinterpret_cast<const ChainParams*>(cp.params_storage);
   P.X = X; P.w = cp.w; P.bias = cp.bias; P.out = out; P.extents = extents; P.snap_mean = mean; P.snap_scale = scale;
   P.snap_mode = snap_mode; P.wd = wd; P.bd = bd; P.n = n; P.T = (int)cdiv(n, PAIR);
+  P.out2 = out2; P.w0_img = cp.w0;
+  VAEX_CHECK(!out2 || (P.mode == MODE_VECTOR && P.N[P.n_mma - 1] == 128 && P.out_dim == 64 && out), "two-head output needs the stacked 128-wide layer");
+  VAEX_CHECK(out2 || P.mode != MODE_VECTOR || P.N[P.n_mma - 1] <= 64, "the stacked two-head chain needs both outputs");
   P.mc_T = 0; P.drop_mask = nullptr; P.var_out = nullptr; P.drop_seed = 0; P.drop_chunk = 1; P.drop_p = 0.f; P.drop_inv = 1.f;
   if (drop) {
     VAEX_CHECK(P.mode == MODE_DOT && P.n_mma == 2 && drop->passes >= 1, "dropout passes need the two-layer predictor chain");

@@ -40,6 +40,28 @@ void count_launch(int n = 1);
 
 static inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
+// Stream-ordered scratch for the handle-less entry points (top-k, offsets scan, k-center, KLD partials): the device's
+// default pool releases freed blocks to the OS at every synchronisation unless a release threshold is set, and the
+// next cudaMallocAsync then pays an OS allocation (hundreds of microseconds on a busy host).  The scratch of these
+// entry points is a few KB, so keeping up to 64 MB in the pool costs nothing and makes the calls allocation-free in
+// steady state.  Set once per device, on first use.
+static inline cudaError_t scratch_alloc(void** p, size_t bytes, cudaStream_t st) {
+  static bool kept[64] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev >= 0 && dev < 64 && !kept[dev]) {
+    cudaMemPool_t pool;
+    unsigned long long keep = 64ull << 20, cur = 0;
+    if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess &&
+        cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &cur) == cudaSuccess && cur < keep)
+      (void)cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    (void)cudaGetLastError();
+    kept[dev] = true;
+  }
+  return cudaMallocAsync(p, bytes, st);
+}
+
 // epilogues of the SIMT linear kernel
 enum Epi {
   EPI_NONE = 0,

@@ -91,7 +91,7 @@ int exclusive_scan_i32(const int32_t* sizes, int64_t n, int32_t* offsets, cudaSt
   }
   const int nb = (int)cdiv(n, SCAN_B);
   int32_t* bsum = nullptr;
-  VAEX_CUDA(cudaMallocAsync(&bsum, sizeof(int32_t) * nb, st));
+  VAEX_CUDA(scratch_alloc((void**)&bsum, sizeof(int32_t) * nb, st));
   scan_block_sums<<<nb, SCAN_T, 0, st>>>(sizes, n, bsum);
   VAEX_LAUNCH_CHECK();
   scan_of_sums<<<1, SCAN_T, 0, st>>>(bsum, nb);
@@ -474,20 +474,25 @@ int snap_extents(const float* x, int64_t n, int d, const float* mean, const floa
 }
 
 // ------------------------------------------------------------------ dropout / backward helpers
+// Dropout(p) in place: keep element e iff mask[e] != 0, or -- without a mask -- iff the 16-bit draw of e is >= round(p * 65536):
+// Philox call q = e >> 3 yields eight 16-bit draws (word (e >> 1) & 3, half e & 1).  Sixteen bits per element instead of
+// thirty-two halve the generator work, which is what bounds the MC-dropout passes of the tcgen05 predictor chain
+// (chain_tc.cu draws the same bits); the drop probability is quantised to 1 / 65536 (0.100006 for p = 0.1).
 __global__ void dropout_kernel(float* __restrict__ h, int64_t count, const uint8_t* __restrict__ mask,
                                uint64_t seed, float p) {
   const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const int64_t e0 = q * 4;
+  const int64_t e0 = q * 8;
   if (e0 >= count) return;
   const float inv = 1.f / (1.f - p);
+  const uint32_t thr = dropout_threshold(p);
   uint4 r = make_uint4(0, 0, 0, 0);
   if (!mask) r = Philox(seed)((uint64_t)q, 0);
   const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
+  for (int i = 0; i < 8; ++i) {
     const int64_t e = e0 + i;
     if (e < count) {
-      const bool keep = mask ? mask[e] != 0 : u01(rr[i]) >= p;
+      const bool keep = mask ? mask[e] != 0 : ((rr[i >> 1] >> (16 * (i & 1))) & 0xffffu) >= thr;
       h[e] = keep ? h[e] * inv : 0.f;
     }
   }
@@ -497,7 +502,7 @@ int dropout_apply(float* h, int64_t n, int cols, const uint8_t* mask, uint64_t s
                   cudaStream_t st) {
   const int64_t count = n * cols;
   if (count == 0) return VAEX_OK;
-  dropout_kernel<<<(unsigned)cdiv(cdiv(count, 4), 256), 256, 0, st>>>(h, count, mask, seed, p);
+  dropout_kernel<<<(unsigned)cdiv(cdiv(count, 8), 256), 256, 0, st>>>(h, count, mask, seed, p);
   VAEX_LAUNCH_CHECK();
   return VAEX_OK;
 }

@@ -128,7 +128,7 @@ extern "C" int vaex_kcenter_select(const float* z, int64_t n, int32_t L, const i
   cudaStream_t st = (cudaStream_t)stream;
   float* ws = nullptr;
   const size_t floats = (size_t)(M + U) * L + M + 1;
-  VAEX_CUDA(cudaMallocAsync(&ws, floats * sizeof(float), st));
+  VAEX_CUDA(scratch_alloc((void**)&ws, floats * sizeof(float), st));
   float* zc = ws;
   float* zu = zc + (size_t)M * L;
   float* min_d = zu + (size_t)U * L;

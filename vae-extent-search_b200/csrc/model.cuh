@@ -30,10 +30,11 @@ struct TcPack {
 // packed weights of a fused tcgen05 MLP chain (chain_tc.cu)
 struct ChainPack {
   __half* w = nullptr;
+  __half* w0 = nullptr;    // layer-0 image when it lives in the operand (encoder with both latent heads)
   float* bias = nullptr;
   int smem_bytes = 0;
   bool ready = false;
-  alignas(8) unsigned char params_storage[320] = {};   // shape part of ChainParams
+  alignas(8) unsigned char params_storage[384] = {};   // shape part of ChainParams
 };
 
 struct DevBuf {
@@ -55,7 +56,7 @@ struct vaex_model {
   std::map<std::string, float*> dev;   // packed fp32 device tensors, by name
   vaex::TcPack tc;
   std::map<std::string, __half*> head_img;   // fp16 images of 256-wide layers for head_tc_linear, by name (segment family)
-  vaex::ChainPack dec_chain, pred_chain, enc_mu_chain, enc_lv_chain;   // extent-VAE decoder / cost predictor / encoder on tensor cores
+  vaex::ChainPack dec_chain, pred_chain, enc_mu_chain, enc_lv_chain, enc_both_chain;   // extent-VAE decoder / cost predictor / encoder on tensor cores
   bool head_ready = false;                 // segment family: every latent / decoder / predictor layer has a head_tc image
   int use_tensor = 1;                      // VAEX_OPT_TENSOR_CORES
   int use_fused_ascent = 1;                // VAEX_OPT_FUSED_ASCENT
@@ -104,7 +105,7 @@ struct ChainLayer;
 struct ChainDropout { const uint8_t* mask; uint64_t seed; float p; int passes; int64_t chunk_rows; float* var_out; };
 int chain_tc_run(const ChainPack& cp, const float* X, int64_t n, float* out, int32_t* extents, const float* mean,
                  const float* scale, int snap_mode, const float* wd, const float* bd, cudaStream_t st,
-                 const ChainDropout* drop = nullptr);
+                 const ChainDropout* drop = nullptr, float* out2 = nullptr);
 // segsum_tc.cu
 // in_mode: 0 = fp32 rows, 1 = fp16 rows, 2 = the packed row image (rows_pack_image)
 int segsum_tc_encode(vaex_model* m, const float* feats, const int32_t* off, int64_t n_programs,

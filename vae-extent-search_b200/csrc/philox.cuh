@@ -23,6 +23,8 @@ struct Philox {
   }
 };
 __device__ __forceinline__ float u01(uint32_t x) { return (x >> 8) * (1.0f / 16777216.0f) + (0.5f / 16777216.0f); }
+// Dropout keeps an element iff its 16-bit draw is >= this threshold (drop probability round(p * 65536) / 65536)
+__host__ __device__ __forceinline__ uint32_t dropout_threshold(float p) { return (uint32_t)(p * 65536.f + 0.5f); }
 
 
 }  // namespace vaex
