@@ -318,24 +318,31 @@ def main_vaex(args):
     pack_ms = pk0.elapsed_time(pk1)
     row_src = {"buf": image, "flags": flags | _lib.F_FEATS_IMAGE}
 
-    def step(st=st):
+    def step(st=st, merge=True):
         _lib.check(lib.vaex_decode_snap(vmodel.h, _lib.ptr(z), P, None, _lib.ptr(extents), _lib.ptr(mean_d), _lib.ptr(scale_d), SNAP,
                                         _lib.ptr(ext_d), _lib.ptr(last_d), 64, st))
         _lib.check(lib.vaex_segment_offsets(_lib.ptr(sizes_d), P, _lib.ptr(offsets), st))
         _lib.check(lib.vaex_segsum_mlp_forward(model.h, _lib.ptr(row_src["buf"]), _lib.ptr(offsets), P, rows, _lib.ptr(scores),
                                                row_src["flags"], st))
         _lib.check(lib.vaex_topk(_lib.ptr(scores), P, TOPK, None, _lib.ptr(top_v), _lib.ptr(top_i), _lib.ptr(n_out), st))
+        if merge:
+            merge_stage(st)
+
+    def merge_stage(st=st):
         if world > 1:       # candidate merge: the path's only exchange (one ncclAllGather of 16-byte records + one merge CTA)
             _lib.check(lib.vaex_topk_allgather_merge(comm.h, _lib.ptr(top_v), _lib.ptr(top_i), _lib.ptr(n_out), TOPK, rank * P,
                                                      _lib.ptr(mer_v), _lib.ptr(mer_i), _lib.ptr(mer_n), st))
 
     graph_note = {"graph": False}
+    graphs = []
 
     def graphed(fn):
-        """The step's 18 launches captured ONCE into a CUDA graph (every entry point of the step is stream-ordered: grow-only
-        workspaces, cudaMallocAsync scratch, no host read-back) and replayed per step: the timed loop is then one
-        cudaGraphLaunch per step whatever the box's host cores are doing.  --no-graph (or a failed capture) times the
-        eager launches instead; `config.cuda_graph` says which."""
+        """The step's 18 local launches captured ONCE into a CUDA graph (every entry point of the step is stream-ordered:
+        grow-only workspaces, cudaMallocAsync scratch, no host read-back) and replayed per step: the timed loop is then one
+        cudaGraphLaunch per step (plus, at N > 1, the eager all-gather merge behind it on the same stream -- NCCL work
+        stays out of the graph, so the communicator's teardown never waits on a live graph) whatever the box's host
+        cores are doing.  --no-graph (or a failed capture) times the eager launches instead; `config.cuda_graph` says
+        which."""
         if args.no_graph:
             return fn
         try:
@@ -343,13 +350,18 @@ def main_vaex(args):
             side.wait_stream(stream)
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g, stream=side, capture_error_mode="thread_local"):
-                fn(side.cuda_stream)
+                fn(side.cuda_stream, False)
             stream.wait_stream(side)
             torch.cuda.synchronize()
-            g.replay()
+            graphs.append(g)
+
+            def replay():
+                g.replay()
+                merge_stage()
+            replay()
             torch.cuda.synchronize()
             graph_note["graph"] = True
-            return lambda: g.replay()
+            return replay
         except Exception as e:      # noqa: BLE001 -- eager launches are the same kernels
             graph_note["error"] = str(e)[:200]
             torch.cuda.synchronize()
@@ -836,6 +848,9 @@ def main_vaex(args):
             line["torch_gpu_baseline"] = torch_gpu
         print(json.dumps(line))
     if comm is not None:
+        torch.cuda.synchronize()
+        for g in graphs:
+            g.reset()
         comm.close()
     if world > 1:
         dist.destroy_process_group()

@@ -451,6 +451,9 @@ typedef struct vaex_comm* vaex_comm_t;
 int vaex_nccl_unique_id(uint8_t* id_out_host);
 /* with the rank's device current; id_host may be NULL when world == 1 */
 int vaex_nccl_init(int32_t rank, int32_t world, const uint8_t* id_host, vaex_comm_t* out);
+/* The collectives below may be stream-captured into a CUDA graph; NCCL then keeps the communicator alive for the
+ * graph, and ncclCommDestroy waits for it: destroy (or reset) every such graph BEFORE vaex_nccl_destroy, or the call
+ * does not return (seen: a 2-rank bench that held its step graphs at exit).  bench.py keeps NCCL work out of its graph. */
 int vaex_nccl_destroy(vaex_comm_t c);
 int vaex_comm_info(vaex_comm_t c, int32_t* rank_or_null, int32_t* world_or_null);
 /* Candidate merge of the sharded scoring path: local_vals_dev fp32[k] / local_idx_dev int64[k] are this rank's winners in
