@@ -249,6 +249,13 @@ static int pack_model(vaex_model* m, const float* norm, cudaStream_t st) {
                            "pred" + std::to_string(i), m->PH, i == 0 ? m->L : m->PH, st));
       TRY(pack_linear(m, "cost_predictor." + std::to_string(4 * m->n_pred), 1, m->PH, st));
       TRY(pack_segment_heads(m, st));
+      // the whole (BN-folded) predictor as ONE resident-weight chain: L <= 128 -> 256 x n_pred -> 1
+      if (m->PH == 256 && m->n_pred >= 1 && m->n_pred <= 3 && m->L <= 128) {
+        std::vector<ChainLayer> ls;
+        for (int i = 0; i < m->n_pred; ++i) ls.push_back(chain_layer(m, "pred" + std::to_string(i)));
+        ls.push_back(chain_layer(m, "cost_predictor." + std::to_string(4 * m->n_pred)));
+        TRY(chain_tc_pack(m->pred_chain, ls, 1, st));
+      }
       return VAEX_OK;
     }
   }

@@ -34,7 +34,7 @@
 namespace vaex {
 
 namespace ch {
-constexpr int TILE = 128, PAIR = 256, ATOM = 128 * 128, HID = 256, K0 = 64;
+constexpr int TILE = 128, PAIR = 256, ATOM = 128 * 128, HID = 256;   // layer 0's K is 64 or 128 (one or two operand atoms)
 constexpr int WORKER_WARPS = 16, WORKERS = 32 * WORKER_WARPS, THREADS = WORKERS + 32;
 constexpr int MAX_LAYERS = 4;
 enum { B_IN0 = 0, B_IN1 = 1, B_ACC0 = 2, B_ACC1 = 3 };
@@ -73,6 +73,7 @@ struct ChainParams {
   float* out2;
   const __half* w0_img;      // [2][16 KB] per-rank images of layer 0 when w0_in_a
   int32_t w0_in_a;
+  int32_t bias_global;       // the fp32 biases (+ scalar head) are read from `bias` in global memory (L1) instead of a shared copy
   const uint8_t* drop_mask;  // [mc_T][n, 256] or null
   float* var_out;            // [n] or null
   uint64_t drop_seed;
@@ -86,6 +87,7 @@ __global__ void smem_base_probe_kernel(uint32_t* out) {
   if (threadIdx.x == 0) *out = ptx::smem_u32(probe_smem);
 }
 
+template <bool BIAS_G, int KZ>     // KZ: atoms of the layer-0 operand (1: K = 64, 2: K = 128)
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(ch::THREADS, 1)
 chain_tc_kernel(const ChainParams p) {
   using namespace ch;
@@ -97,7 +99,7 @@ chain_tc_kernel(const ChainParams p) {
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + p.bar_off);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + p.bar_off + 32);
   float* s_dot = reinterpret_cast<float*>(smem + p.bar_off + 64);     // MODE_DOT: [2][3][128] partial dots (double-buffered over MC passes)
-  const float* s_bias = reinterpret_cast<const float*>(smem + p.bias_off);
+  const float* s_bias = BIAS_G ? p.bias : reinterpret_cast<const float*>(smem + p.bias_off);
   const uint32_t bar0 = ptx::smem_u32(bars);
   auto bar = [&](int i) { return bar0 + 8u * i; };
 
@@ -113,8 +115,10 @@ chain_tc_kernel(const ChainParams p) {
     const uint4* g = reinterpret_cast<const uint4*>(p.w) + (size_t)rank * (p.w_bytes / 16);
     uint4* s = reinterpret_cast<uint4*>(smem);
     for (int i = threadIdx.x; i < p.w_bytes / 16; i += THREADS) s[i] = __ldg(g + i);
-    float* sb = reinterpret_cast<float*>(smem + p.bias_off);
-    for (int i = threadIdx.x; i < p.bias_count; i += THREADS) sb[i] = p.bias[i];
+    if (!BIAS_G) {
+      float* sb = reinterpret_cast<float*>(smem + p.bias_off);
+      for (int i = threadIdx.x; i < p.bias_count; i += THREADS) sb[i] = p.bias[i];
+    }
   }
   ptx::fence_proxy_async();
   ptx::tc_fence_before();
@@ -130,46 +134,49 @@ chain_tc_kernel(const ChainParams p) {
     const uint32_t a_row = sbase + p.a_off + (row >> 3) * 1024 + (row & 7) * 128;
     const int sw = row & 7;
     const uint32_t t_lane = tmem + ((uint32_t)(32 * q) << 16);
-    float xin[16];                                   // this thread's 16 columns of the next input row
+    constexpr int kz = KZ;
+    uint32_t xh[8 * KZ];                               // this thread's 16 kz columns of the next input row, packed fp16
 
     auto fetch = [&](int t) {
       const int64_t r = (int64_t)t * PAIR + rank * TILE + row;
       const bool ok = t < p.T && r < p.n;
       const float* src = p.X + (ok ? r : 0) * p.in_dim;
-      if (ok && (p.in_dim & 7) == 0 && ((reinterpret_cast<uintptr_t>(p.X) & 31) == 0)) {
+      const bool vec = ok && (p.in_dim & 7) == 0 && ((reinterpret_cast<uintptr_t>(p.X) & 31) == 0);
 #pragma unroll
-        for (int j = 0; j < 2; ++j) {                // full 32 B sectors per lane
-          const int c = 16 * cg + 8 * j;
-          if (c < p.in_dim) {
-            const ptx::F8 f = ptx::ldg_stream_f8(src + c);
+      for (int j = 0; j < 2 * kz; ++j) {
+        {
+          const int c = 16 * kz * cg + 8 * j;
+          float f[8];
+          if (vec) {                                 // full 32 B sectors per lane
+            if (c < p.in_dim) {
+              const ptx::F8 v = ptx::ldg_stream_f8(src + c);
 #pragma unroll
-            for (int e = 0; e < 8; ++e) xin[8 * j + e] = f.v[e];
+              for (int e = 0; e < 8; ++e) f[e] = v.v[e];
+            } else {
+#pragma unroll
+              for (int e = 0; e < 8; ++e) f[e] = 0.f;
+            }
           } else {
 #pragma unroll
-            for (int e = 0; e < 8; ++e) xin[8 * j + e] = 0.f;
+            for (int e = 0; e < 8; ++e) f[e] = (ok && c + e < p.in_dim) ? __ldg(src + c + e) : 0.f;
           }
-        }
-      } else {
+          if (p.ones_col >= 0) {
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const int c = 16 * cg + j;
-          xin[j] = (ok && c < p.in_dim) ? __ldg(src + c) : 0.f;
-        }
-      }
-      if (p.ones_col >= 0) {
+            for (int e = 0; e < 8; ++e)
+              if ((unsigned)(c + e - p.ones_col) < 2u) f[e] = 1.f;
+          }
 #pragma unroll
-        for (int j = 0; j < 16; ++j)
-          if ((unsigned)(16 * cg + j - p.ones_col) < 2u) xin[j] = 1.f;
+          for (int e = 0; e < 4; ++e) xh[4 * j + e] = ptx::cvt_h2_sat(f[2 * e], f[2 * e + 1]);
+        }
       }
     };
-    // z: 16 fp32 -> 32 B of atom 3 (the layer-0 A operand)
+    // z: 16 kz halves -> 2 kz 16-byte chunks of the layer-0 A operand (the last kz atoms)
     auto pack_z = [&]() {
-      const uint32_t base = a_row + 3 * ATOM;
 #pragma unroll
-      for (int m = 0; m < 2; ++m)
-        ptx::sts_v4(base + (((2 * cg + m) ^ sw) << 4),
-                    ptx::cvt_h2_sat(xin[8 * m], xin[8 * m + 1]), ptx::cvt_h2_sat(xin[8 * m + 2], xin[8 * m + 3]),
-                    ptx::cvt_h2_sat(xin[8 * m + 4], xin[8 * m + 5]), ptx::cvt_h2_sat(xin[8 * m + 6], xin[8 * m + 7]));
+      for (int m = 0; m < 2 * kz; ++m) {
+          const int gc = 2 * kz * cg + m;
+          ptx::sts_v4(a_row + (4 - kz + (gc >> 3)) * ATOM + (((gc & 7) ^ sw) << 4), xh[4 * m], xh[4 * m + 1], xh[4 * m + 2], xh[4 * m + 3]);
+        }
     };
     uint4 w0r[2] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};      // this thread's 32 B of the W0 image (w0_in_a)
     if (p.w0_in_a) {
@@ -295,7 +302,7 @@ chain_tc_kernel(const ChainParams p) {
           if (lastp) {
             fetch(t + n_clusters);
             const int64_t r2 = (int64_t)(t + 2 * n_clusters) * PAIR + rank * TILE + row;
-            if (cg < 2 && 32 * cg < p.in_dim && r2 < p.n) ptx::prefetch_l2(p.X + r2 * p.in_dim + 32 * cg);
+            if (32 * cg < p.in_dim && r2 < p.n) ptx::prefetch_l2(p.X + r2 * p.in_dim + 32 * cg);
           } else {                                   // the next pass's keep bits are computed behind this pass's GEMM
             nb0 = keep_bits(pass + 1, r, 0);
             nb1 = keep_bits(pass + 1, r, 1);
@@ -358,7 +365,7 @@ chain_tc_kernel(const ChainParams p) {
         if (last) {
           fetch(t + n_clusters);                     // the next rows stream in behind the last GEMM
           const int64_t r2 = (int64_t)(t + 2 * n_clusters) * PAIR + rank * TILE + row;
-          if (cg < 2 && 32 * cg < p.in_dim && r2 < p.n) ptx::prefetch_l2(p.X + r2 * p.in_dim + 32 * cg);   // and the rows after those reach L2
+          if (32 * cg < p.in_dim && r2 < p.n) ptx::prefetch_l2(p.X + r2 * p.in_dim + 32 * cg);   // and the rows after those reach L2
         }
         if (!last || p.mode == MODE_DOT) {
           // hidden layer: n-half nh -> 32 columns of this row: bias + ReLU (+ fp16 pack | + dot)
@@ -519,13 +526,13 @@ chain_tc_kernel(const ChainParams p) {
         const uint32_t idesc = ptx::umma_idesc_f16(256, n_piece);
         const uint32_t acc = tmem + 256u * (lc & 1);
         ++lc;
-        const uint64_t dA = ptx::umma_desc_sw128(sbase + p.a_off + (K == HID ? 0 : 3 * ATOM));
+        const uint64_t dA = ptx::umma_desc_sw128(sbase + p.a_off + (K == HID ? 0 : (4 - (K >> 6)) * ATOM));
         for (int kh = 0; kh < n_kh; ++kh) {
           if (kh == 0) { ptx::mbar_wait(bar(B_IN0), in_use0 & 1); ++in_use0; }
           else         { ptx::mbar_wait(bar(B_IN1), in_use1 & 1); ++in_use1; }
           ptx::tc_fence_after();
           if (ptx::elect_one()) {
-            const int steps = K == HID ? 8 : 4;
+            const int steps = K == HID ? 8 : K >> 4;
             for (int nh = 0; nh < n_nh; ++nh) {
               const uint64_t dW = ptx::umma_desc_sw128(sbase + p.w_off[l] + nh * 64 * 128);
               for (int i = 0; i < steps; ++i) {
@@ -568,7 +575,10 @@ int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode
   // When the fp32 biases do not fit beside the weights and the operand (the encoder: 160 KB + 64 KB + 3.3 KB), layer 0's
   // bias rides in its GEMM instead: two spare input columns hold the constant 1 and W0 gets fp16 hi / lo parts of b0.
   // When even that does not fit (both latent heads: 176 KB of weights), W0's one-atom image moves into the operand.
-  auto smem_need = [&](bool fold0, bool w0a) {
+  if (layers[0].in > 128) return VAEX_OK;
+  const int K0 = layers[0].in <= 64 ? 64 : 128;          // one or two atoms of layer-0 operand
+  const int dot_bytes = mode == MODE_DOT ? (n_mma == 2 ? 6 : 3) * TILE * 4 : 0;   // double-buffered over MC passes (two-layer predictor only)
+  auto smem_need = [&](bool fold0, bool w0a, bool bias_g = false) {
     int w = 0, b = 0;
     for (int l = 0; l < n_mma; ++l) {
       const bool out_layer = mode == MODE_VECTOR && l == n_mma - 1;
@@ -577,12 +587,16 @@ int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode
       if (!(fold0 && l == 0)) b += N;
     }
     if (mode == MODE_DOT) b += HID + 4;
-    return w + 4 * ATOM + b * 4 + 64 + (mode == MODE_DOT ? 6 * TILE * 4 : 0);
+    return w + 4 * ATOM + (bias_g ? 0 : b * 4) + 64 + dot_bytes;
   };
   const bool can_fold = n_mma > 1 && layers[0].in + 2 <= K0 && layers[0].out == HID;
   const bool fold0 = smem_need(false, false) > SMEM_MAX && can_fold;
-  const bool w0a = fold0 && smem_need(true, false) > SMEM_MAX && smem_need(true, true) <= SMEM_MAX;
-  if (smem_need(fold0, w0a) > SMEM_MAX) return VAEX_OK;
+  const bool w0a = fold0 && K0 == 64 && smem_need(true, false) > SMEM_MAX && smem_need(true, true) <= SMEM_MAX;
+  // last resort (the segment cost predictor, 128 -> 256 -> 256 -> 256 -> 1: 160 KB of weights and no spare input column
+  // to fold a bias into): the 4 KB of fp32 biases are read through L1 instead of from a shared copy
+  const bool bias_g = K0 == 128 && smem_need(fold0, w0a) > SMEM_MAX;
+  if (smem_need(fold0, w0a, bias_g) > SMEM_MAX) return VAEX_OK;
+  P.bias_global = bias_g ? 1 : 0;
   P.ones_col = fold0 ? layers[0].in : -1;
   P.w0_in_a = w0a ? 1 : 0;
   int woff = 0, boff = 0;
@@ -610,8 +624,8 @@ int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode
   }
   P.bias_off = P.a_off + 4 * ATOM;
   P.bias_count = boff;
-  P.bar_off = P.bias_off + boff * 4;
-  cp.smem_bytes = P.bar_off + 64 + (mode == MODE_DOT ? 6 * TILE * 4 : 0);
+  P.bar_off = P.bias_off + (bias_g ? 0 : boff * 4);
+  cp.smem_bytes = P.bar_off + 64 + dot_bytes;
   if (cp.smem_bytes > SMEM_MAX) return VAEX_OK;
   // the kernel relies on a 1024-byte aligned dynamic shared-memory base (no static shared memory)
   {
@@ -663,7 +677,9 @@ int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode
     VAEX_CUDA(cudaMemcpyAsync(cp.w0, img0.data(), 2 * ATOM, cudaMemcpyHostToDevice, st));
   }
   VAEX_CUDA(cudaStreamSynchronize(st));
-  VAEX_CUDA(cudaFuncSetAttribute(chain_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_MAX));
+  VAEX_CUDA(cudaFuncSetAttribute(chain_tc_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_MAX));
+  VAEX_CUDA(cudaFuncSetAttribute(chain_tc_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_MAX));
+  VAEX_CUDA(cudaFuncSetAttribute(chain_tc_kernel<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_MAX));
   cp.ready = true;
   return VAEX_OK;
 }
@@ -690,7 +706,9 @@ int chain_tc_run(const ChainPack& cp, const float* X, int64_t n, float* out, int
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   const int clusters = std::max(1, std::min(sms / 2, P.T));
-  chain_tc_kernel<<<2 * clusters, THREADS, cp.smem_bytes, st>>>(P);
+  if (P.K[0] == 64) chain_tc_kernel<false, 1><<<2 * clusters, THREADS, cp.smem_bytes, st>>>(P);
+  else if (P.bias_global) chain_tc_kernel<true, 2><<<2 * clusters, THREADS, cp.smem_bytes, st>>>(P);
+  else chain_tc_kernel<false, 2><<<2 * clusters, THREADS, cp.smem_bytes, st>>>(P);
   VAEX_LAUNCH_CHECK();
   return VAEX_OK;
 }

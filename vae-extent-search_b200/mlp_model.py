@@ -181,10 +181,10 @@ class SegmentSumMLPModule(torch.nn.Module):
 
     # -- packing ---------------------------------------------------------------------------
     def _version_key(self, norm_vec):
-        """Cache key of the packed weights: storage address + autograd version + a cheap content probe per tensor
-        (writes through .data do not bump _version; id() can be reused after garbage collection), and the norm vector's
-        bytes.  invalidate_packed() drops the cache explicitly."""
-        key = tuple((p.data_ptr(), p._version, float(p.detach().reshape(-1)[:: max(1, p.numel() // 16)].double().sum()))
+        """Cache key of the packed weights: storage address + autograd version per tensor (id() can be reused after garbage
+        collection) and the norm vector's bytes.  No device read: the key must cost nothing on the scoring path and be legal
+        under CUDA-graph capture.  Writes through .data do not bump _version: call invalidate_packed() after them."""
+        key = tuple((p.data_ptr(), p._version)
                     for p in self.state_dict(keep_vars=True).values())
         nk = None
         if norm_vec is not None:

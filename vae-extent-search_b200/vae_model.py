@@ -33,7 +33,7 @@ class _Packed:
         raise NotImplementedError
 
     def packed(self):
-        key = tuple((p.data_ptr(), p._version, float(p.detach().reshape(-1)[:: max(1, p.numel() // 16)].double().sum()))
+        key = tuple((p.data_ptr(), p._version)
                     for p in self.state_dict(keep_vars=True).values())
         cached = self.__dict__.get("_packed_cache")
         if cached is not None and cached[1] == key:
@@ -43,6 +43,11 @@ class _Packed:
         m.set_option(_lib.OPT_TENSOR_CORES, int(self.__dict__.get("_tensor_cores", True)))
         self.__dict__["_packed_cache"] = (m, key)
         return m
+
+    def invalidate_packed(self):
+        """Drops the packed copy.  The cache key is (storage address, autograd version) per tensor -- no device read, so a
+        call costs nothing and is legal under CUDA-graph capture -- and writes through .data do not bump the version."""
+        self.__dict__.pop("_packed_cache", None)
 
     def set_tensor_cores(self, on=True):
         """True (default): decoder / cost predictor on the fused tcgen05 chain (fp16 operands, fp32
