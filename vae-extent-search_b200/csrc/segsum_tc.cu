@@ -63,6 +63,14 @@ constexpr int SMEM_DYN = SMEM_TILES + 1024;            // + slack to align the b
 constexpr int SUB = 64;              // rows per segment-descriptor sub-block (= rows one CTA feeds a layer-1 block)
 constexpr int LOAD_WARPS = 8, EPI1_WARP0 = 12, MMA_WARP = 20;   // 0-7 loaders, 8-11 epi 0, 12-19 epi 1, 20 MMA issuer
 constexpr int THREADS = 32 * (MMA_WARP + 1);   // 672
+// L1_N256: layer 1 as ONE N = 256 MMA per k-step instead of two N = 128 row blocks.  tcgen05.mma M256 N128 K16 issues
+// every 93.6 clk whatever N <= 128 is, M256 N256 K16 every 128.1 clk (tools/mma_rate.cu, profiles/r02_mma_rate.txt: 1 494
+// vs 2 210 TFLOP/s chip-wide), so the 34 layer-1 MMAs of a tile (3 182 clk) would become 17 (2 178 clk).  Measured: SLOWER
+// (3.06 vs 2.76 ms on 16.5 M rows, results identical).  With one 256-column accumulator both row blocks complete together
+// and all sixteen epi-1 warps drain at once (~4 K clk: the SM's issue slots, not the tensor pipe, bound the drain) before
+// the next tile's layer 1 may start, where the two N = 128 blocks let block 0 drain under block 1's MMAs; TMEM has no
+// room for a second 256-column accumulator beside acc0.  Kept as a switch for the record.
+constexpr bool L1_N256 = false;
 constexpr int B1_COL = 176;          // k columns of the b1 hi/lo halves (spare k-step 11 of the W0 / A0 images)
 enum { B_A0_FULL = 0, B_A0_EMPTY, B_ACC0_FULL0, B_ACC0_FULL1, B_A1_FULL0, B_A1_FULL1, B_ACC1_FULL0, B_ACC1_FULL1,
        B_ACC1_EMPTY0, B_ACC1_EMPTY1, B_COUNT };
@@ -525,7 +533,11 @@ segsum_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
     const int hu = rank * TILE + 32 * q + lane;   // hidden unit of this lane
     const float b1 = FOLD ? 0.f : p.b1[hu];
     float* const out_h = p.out + hu;
-    const uint32_t tbase = tmem + lane_base + 256 + 128 * g;
+    // accumulator columns of (block g, 32-column step s).  Two N = 128 row blocks: block g = columns [128 g, +128), CTA h's
+    // rows at [64 h, +64) of it.  One N = 256 MMA: column = 128 * CTA + row, so CTA h's rows [64 g, +64) are at 128 h + 64 g.
+    auto tcol_of = [&](int s) -> uint32_t {
+      return tmem + lane_base + 256 + (L1_N256 ? 128 * (s >> 1) + 64 * g + 32 * (s & 1) : 128 * g + 32 * s);
+    };
     uint32_t va[16], vb[16];
     // sub-block metadata of this tile (na, nb: h = 0; nc, nd: h = 1), fetched one tile ahead
     uint4 na = make_uint4(0, 0, 0, 0), nc = na;
@@ -546,7 +558,7 @@ segsum_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
       fetch_meta(t + n_clusters);
       ptx::mbar_wait_role(bar(B_ACC1_FULL0 + g), it & 1, poller, 3 + g, GROUP_THREADS);
       ptx::tc_fence_after();
-      ptx::tmem_ld16(tbase + 32 * s_begin, va);
+      ptx::tmem_ld16(tcol_of(s_begin), va);
       float* dst = out_h;
       float a0 = 0.f, a1 = 0.f;
       uint32_t em = 0, pm = 0;
@@ -566,7 +578,7 @@ segsum_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
           em = h ? mc.y : ma.y;
           pm = h ? mc.w : ma.w;
         }
-        const uint32_t tcol = tbase + 32 * s;
+        const uint32_t tcol = tcol_of(s);
         ptx::tmem_ld_wait();
         ptx::tmem_ld16(tcol + 16, vb);
         if (__builtin_expect(regular, 1)) {
@@ -576,7 +588,7 @@ segsum_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
           sum_irregular(tcol, p.desc + (size_t)sub * SUB, min(SUB, (int)p.n_rows - sub * SUB), b1, out_h);
         }
         ptx::tmem_ld_wait();
-        if (s + 1 != s_end) ptx::tmem_ld16(tcol + 32, va);
+        if (s + 1 != s_end) ptx::tmem_ld16(tcol_of(s + 1), va);
         if (__builtin_expect(regular, 1)) sum_chunk<FOLD>(vb, em >> 16, pm >> 16, b1, a0, a1, dst);
       }
       ptx::tc_fence_before();
@@ -617,7 +629,7 @@ segsum_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
         tma_tile(cluster);
       }
       __syncwarp();
-      const uint32_t idesc_n128 = ptx::umma_idesc_f16(256, 128);
+      const uint32_t idesc_n128 = ptx::umma_idesc_f16(256, 128), idesc_n256 = ptx::umma_idesc_f16(256, 256);
       const uint64_t dW0 = ptx::umma_desc_sw128(sbase + W0_OFF), dW1 = ptx::umma_desc_sw128(sbase + W1_OFF);
       const uint64_t dA0 = ptx::umma_desc_sw128(sbase + A0_OFF), dA1 = ptx::umma_desc_sw128(sbase + A1_OFF);
       // +32 B per K=16 step inside an atom (encoded >>4 -> +2), +ATOM per 64 columns
@@ -639,6 +651,38 @@ segsum_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
           ptx::umma_commit_2cta(bar(B_A0_EMPTY), 3);
         }
         __syncwarp();
+        if (L1_N256) {
+          // ---- layer 1, all 256 rows per MMA: K half 0 as soon as epi 0 has delivered it, then K half 1 ----
+          if (it > 0) {
+            ptx::mbar_wait(bar(B_ACC1_EMPTY0), (it - 1) & 1);
+            ptx::mbar_wait(bar(B_ACC1_EMPTY1), (it - 1) & 1);
+          }
+          ptx::mbar_wait(bar(B_A1_FULL0), it & 1);
+          ptx::tc_fence_after();
+          if (ptx::elect_one()) {
+            if (FOLD) ptx::umma_f16_2cta(tmem + 256, dW0 + kadv(KB1), dA0 + kadv(KB1), idesc_n256, 0);
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+              ptx::umma_f16_2cta(tmem + 256, dW1 + kadv(k), dA1 + kadv(k), idesc_n256, FOLD || k > 0);
+          }
+          __syncwarp();
+          ptx::mbar_wait(bar(B_A1_FULL1), it & 1);
+          ptx::tc_fence_after();
+          if (IN == IN_IMAGE && t + n_clusters < p.T) {
+            // epi 0 has drained both halves of acc0, so layer 0 is complete and A0_EMPTY has fired: this wait falls through
+            ptx::mbar_wait(bar(B_A0_EMPTY), it & 1);
+            if (ptx::elect_one()) tma_tile(t + n_clusters);
+            __syncwarp();
+          }
+          if (ptx::elect_one()) {
+#pragma unroll
+            for (int k = 8; k < 16; ++k) ptx::umma_f16_2cta(tmem + 256, dW1 + kadv(k), dA1 + kadv(k), idesc_n256, 1);
+            ptx::umma_commit_2cta(bar(B_ACC1_FULL0), 3);
+            ptx::umma_commit_2cta(bar(B_ACC1_FULL1), 3);
+          }
+          __syncwarp();
+          continue;
+        }
         // ---- layer 1, row block 0 (rows [0,64) of both CTAs): K half 0 then K half 1 ----
         if (it > 0) ptx::mbar_wait(bar(B_ACC1_EMPTY0), (it - 1) & 1);
         ptx::mbar_wait(bar(B_A1_FULL0), it & 1);
