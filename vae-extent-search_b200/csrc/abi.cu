@@ -169,8 +169,6 @@ static int pack_encoder(vaex_model* m, cudaStream_t st) {
   return VAEX_OK;
 }
 
-struct ChainLayer { const std::vector<float>* w; const std::vector<float>* b; int out, in; };
-int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode, cudaStream_t st, int two_heads = 0);
 
 static ChainLayer chain_layer(vaex_model* m, const std::string& pre) {
   HostTensor& w = m->host[pre + ".weight"];
@@ -350,11 +348,7 @@ int vaex_model_destroy(vaex_model_t h) {
   if (h->tc.wl0) cudaFree(h->tc.wl0);
   if (h->tc.wl1) cudaFree(h->tc.wl1);
   for (auto& sl : h->slots) { if (sl.feats) cudaFree(sl.feats); if (sl.off) cudaFree(sl.off); if (sl.scores) cudaFree(sl.scores); }
-  for (ChainPack* cp : {&h->dec_chain, &h->pred_chain, &h->enc_mu_chain, &h->enc_lv_chain, &h->enc_both_chain}) {
-    if (cp->w) cudaFree(cp->w);
-    if (cp->w0) cudaFree(cp->w0);
-    if (cp->bias) cudaFree(cp->bias);
-  }
+  for (ChainPack* cp : {&h->dec_chain, &h->pred_chain, &h->enc_mu_chain, &h->enc_lv_chain, &h->enc_both_chain}) chain_tc_release(*cp);
   for (auto& pn : h->pinned) if (pn.p) cudaFreeHost(pn.p);
   for (auto& pn : h->pack_stage) if (pn.p) cudaFreeHost(pn.p);
   for (auto& s : h->copy_streams) if (s) cudaStreamDestroy(s);

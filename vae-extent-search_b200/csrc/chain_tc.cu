@@ -22,6 +22,7 @@
 // atom 3 (the last one the layer-0 epilogue rewrites) right after the last layer's commit, so
 // layer 0 of tile t+1 runs behind the output epilogue of tile t.
 // Workers: 16 warps, thread = (row, 32-column group of the n-half); warp 16 of the leader CTA issues.
+#include <cstdlib>
 #include <algorithm>
 #include <vector>
 
@@ -558,13 +559,12 @@ chain_tc_kernel(const ChainParams p) {
 // ---------------------------------------------------------------------------------------------
 static __half c_clamp(float x) { return __float2half_rn(std::min(std::max(x, -65504.f), 65504.f)); }
 
-struct ChainLayer { const std::vector<float>* w; const std::vector<float>* b; int out, in; };
 
 // Packs `layers` (row-major [out, in] fp32) into the per-rank swizzled images + fp16 biases and fills the
 // shape part of ChainParams.  The last entry of a MODE_DOT chain is the scalar head (kept fp32, not an MMA).
-int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode, cudaStream_t st, int two_heads) {
+static int chain2_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode, cudaStream_t st, int two_heads) {
   using namespace ch;
-  cp.ready = false;
+  cp.v2 = false;
   const int n_mma = mode == MODE_DOT ? (int)layers.size() - 1 : (int)layers.size();
   if (n_mma < 1 || n_mma > MAX_LAYERS) return VAEX_OK;
   ChainParams& P = *new (cp.params_storage) ChainParams();
@@ -680,8 +680,33 @@ int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode
   VAEX_CUDA(cudaFuncSetAttribute(chain_tc_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_MAX));
   VAEX_CUDA(cudaFuncSetAttribute(chain_tc_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_MAX));
   VAEX_CUDA(cudaFuncSetAttribute(chain_tc_kernel<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_MAX));
-  cp.ready = true;
+  cp.v2 = true;
   return VAEX_OK;
+}
+
+// Packs both kernels' images: chain_tc3.cu (two tiles in flight, streamed weights) runs every plain chain it has a shape
+// for, this file's resident-weight kernel runs the MC-dropout passes and whatever v3 does not take.
+int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode, cudaStream_t st, int two_heads) {
+  cp.ready = false;
+  TRY(chain2_pack(cp, layers, mode, st, two_heads));
+  TRY(chain3_pack(cp, layers, mode, st, two_heads));
+  cp.ready = cp.v2 || cp.v3 != nullptr;
+  return VAEX_OK;
+}
+
+void chain_tc_release(ChainPack& cp) {
+  if (cp.w) cudaFree(cp.w);
+  if (cp.w0) cudaFree(cp.w0);
+  if (cp.bias) cudaFree(cp.bias);
+  cp.w = nullptr; cp.w0 = nullptr; cp.bias = nullptr;
+  chain3_release(cp);
+  cp.ready = cp.v2 = false;
+}
+
+// VAEX_CHAIN_V2=1 keeps every chain on this file's kernel (A/B runs)
+static bool chain_force_v2() {
+  static const bool f = [] { const char* e = getenv("VAEX_CHAIN_V2"); return e && e[0] == '1'; }();
+  return f;
 }
 
 int chain_tc_run(const ChainPack& cp, const float* X, int64_t n, float* out, int32_t* extents, const float* mean,
@@ -690,6 +715,8 @@ int chain_tc_run(const ChainPack& cp, const float* X, int64_t n, float* out, int
   using namespace ch;
   VAEX_CHECK(cp.ready, "tcgen05 chain not packed");
   if (n == 0) return VAEX_OK;
+  if (cp.v3 && !drop && !(cp.v2 && chain_force_v2())) return chain3_run(cp, X, n, out, extents, mean, scale, snap_mode, st, out2);
+  VAEX_CHECK(cp.v2, "this chain has no resident-weight image (MC-dropout passes need the two-layer 64-wide predictor)");
   ChainParams P = *reinterpret_cast<const ChainParams*>(cp.params_storage);
   P.X = X; P.w = cp.w; P.bias = cp.bias; P.out = out; P.extents = extents; P.snap_mean = mean; P.snap_scale = scale;
   P.snap_mode = snap_mode; P.wd = wd; P.bd = bd; P.n = n; P.T = (int)cdiv(n, PAIR);

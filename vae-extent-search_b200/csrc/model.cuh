@@ -32,6 +32,8 @@ struct ChainPack {
   __half* w = nullptr;
   __half* w0 = nullptr;    // layer-0 image when it lives in the operand (encoder with both latent heads)
   float* bias = nullptr;
+  void* v3 = nullptr;      // Chain3Pack (chain_tc3.cu: two tiles in flight, streamed weights) when the shape fits it
+  bool v2 = false;         // chain_tc.cu's resident-weight kernel is packed (MC-dropout passes need it)
   int smem_bytes = 0;
   bool ready = false;
   alignas(8) unsigned char params_storage[384] = {};   // shape part of ChainParams
@@ -98,7 +100,14 @@ struct HeadLinear {
 int head_tc_pack_layer(const std::vector<float>& w, int out_rows, int in_cols, __half** dev, cudaStream_t st);
 int head_tc_linear(const HeadLinear& a, cudaStream_t st);
 // chain_tc.cu
-struct ChainLayer;
+struct ChainLayer { const std::vector<float>* w; const std::vector<float>* b; int out, in; };   // row-major [out, in] fp32 + bias
+int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode, cudaStream_t st, int two_heads = 0);
+void chain_tc_release(ChainPack& cp);
+// chain_tc3.cu
+int chain3_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode, cudaStream_t st, int two_heads);
+int chain3_run(const ChainPack& cp, const float* X, int64_t n, float* out, int32_t* extents, const float* mean, const float* scale,
+               int snap_mode, cudaStream_t st, float* out2);
+void chain3_release(ChainPack& cp);
 // Dropout(p) after the predictor's first ReLU, `passes` times per row on shared layer-0 activations (mc_predict):
 // mask uint8 [passes][n, 256] (1 = keep) or, when null, the Philox stream of dropout_kernel with seed + pass (re-seeded
 // every chunk_rows rows like the SIMT path); passes == 1: out = cost, else out = mean and var_out = unbiased variance
