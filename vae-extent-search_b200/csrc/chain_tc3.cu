@@ -80,7 +80,7 @@ __device__ unsigned long long c3_prof[64];
 #define C3P(i, v) do { if (blockIdx.x == 0) sp[i] += (unsigned long long)(v); } while (0)
 #define C3T() clock64()
 #else
-#define C3P(i, v) do { } while (0)
+#define C3P(i, v) do { (void)(v); } while (0)
 #define C3T() 0ll
 #endif
 
@@ -180,7 +180,7 @@ chain3_kernel(const Chain3Params p, const __grid_constant__ CUtensorMap tmap) {
       C3P(0, C3T() - tt0);
     }
     __syncwarp();
-  } else {
+  } else if (warp == PRODUCER_WARP) {
     if (ptx::elect_one()) {
       // ===== weight producer: one thread per CTA streams this CTA's half of every piece =====
       ptx::tma_prefetch_desc(&tmap);
