@@ -71,6 +71,12 @@ constexpr int THREADS = 32 * (MMA_WARP + 1);   // 672
 // the next tile's layer 1 may start, where the two N = 128 blocks let block 0 drain under block 1's MMAs; TMEM has no
 // room for a second 256-column accumulator beside acc0.  Kept as a switch for the record.
 constexpr bool L1_N256 = false;
+// L0_N256: layer 0 as ONE N = 256 MMA per k-step (11 x 128.1 = 1 409 clk instead of 22 x 93.6 = 2 059; accumulator
+// column c then holds hidden unit c, so W1's K order is the identity).  Measured: the image path gets SLOWER (3.06 vs
+// 2.76-2.90 ms), the fp32-row path faster (3.69 vs 3.96-4.23 ms): with both hidden halves completing together, epi 0's
+// four warps start on half 0 no earlier than before and layer 1 waits for them with an idle pipe, where the two N = 128
+// halves keep the pipe busy under epi 0.  Off; kept as a switch for the record.
+constexpr bool L0_N256 = false;
 constexpr int B1_COL = 176;          // k columns of the b1 hi/lo halves (spare k-step 11 of the W0 / A0 images)
 enum { B_A0_FULL = 0, B_A0_EMPTY, B_ACC0_FULL0, B_ACC0_FULL1, B_A1_FULL0, B_A1_FULL1, B_ACC1_FULL0, B_ACC1_FULL1,
        B_ACC1_EMPTY0, B_ACC1_EMPTY1, B_COUNT };
@@ -81,6 +87,7 @@ __host__ __device__ inline uint32_t sw128_off(int row, int k) {
 }
 // hidden unit held by layer-0 accumulator column c (two N=128 halves, 64 units per CTA each)
 __host__ __device__ inline int hidden_of_col(int c) {
+  if (L0_N256) return c;
   const int h = c >> 7, j = c & 127;
   return j < 64 ? 64 * h + j : 128 + 64 * h + (j - 64);
 }
@@ -642,11 +649,17 @@ segsum_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
         ptx::mbar_wait(bar(B_A0_FULL), it & 1);
         ptx::tc_fence_after();
         if (ptx::elect_one()) {
-          for (int k = 0; k < p.k0_steps; ++k)
-            ptx::umma_f16_2cta(tmem + 0, dA0 + kadv(k), dW0 + kadv(k), idesc_n128, k > 0);
-          ptx::umma_commit_2cta(bar(B_ACC0_FULL0), 3);
-          for (int k = 0; k < p.k0_steps; ++k)
-            ptx::umma_f16_2cta(tmem + 128, dA0 + kadv(k), dW0 + rows64 + kadv(k), idesc_n128, k > 0);
+          if (L0_N256) {
+            for (int k = 0; k < p.k0_steps; ++k)
+              ptx::umma_f16_2cta(tmem + 0, dA0 + kadv(k), dW0 + kadv(k), idesc_n256, k > 0);
+            ptx::umma_commit_2cta(bar(B_ACC0_FULL0), 3);
+          } else {
+            for (int k = 0; k < p.k0_steps; ++k)
+              ptx::umma_f16_2cta(tmem + 0, dA0 + kadv(k), dW0 + kadv(k), idesc_n128, k > 0);
+            ptx::umma_commit_2cta(bar(B_ACC0_FULL0), 3);
+            for (int k = 0; k < p.k0_steps; ++k)
+              ptx::umma_f16_2cta(tmem + 128, dA0 + kadv(k), dW0 + rows64 + kadv(k), idesc_n128, k > 0);
+          }
           ptx::umma_commit_2cta(bar(B_ACC0_FULL1), 3);
           ptx::umma_commit_2cta(bar(B_A0_EMPTY), 3);
         }
