@@ -160,6 +160,16 @@ def stream_ptr():
     return torch.cuda.current_stream().cuda_stream
 
 
+def check_device(t):
+    """The library packs onto, and launches on, the CURRENT device's stream: a tensor that lives on another GPU would be
+    dereferenced from the wrong context.  Fail loudly instead (wrap the call in `with torch.cuda.device(t.device):`)."""
+    import torch
+    if t.is_cuda and t.device.index is not None and t.device.index != torch.cuda.current_device():
+        raise VaexError("tensor on cuda:%d while the current device is cuda:%d: wrap the call in torch.cuda.device(tensor.device)"
+                        % (t.device.index, torch.cuda.current_device()))
+    return t
+
+
 class Model:
     """Owns a vaex_model_t.  weights: dict name -> array-like (reference state_dict keys)."""
 

@@ -144,7 +144,7 @@ class RowsImage:
     def __init__(self, features, in_dim=None):
         if not features.is_cuda:
             raise _lib.VaexError("RowsImage needs a CUDA tensor (no CPU fallback)")
-        feats = features.detach().contiguous().float()
+        feats = _lib.check_device(features).detach().contiguous().float()
         self.n_rows, self.in_dim = int(feats.shape[0]), int(in_dim or feats.shape[1])
         lib = _lib.load()
         nbytes = int(lib.vaex_rows_image_bytes(self.n_rows))
@@ -254,10 +254,10 @@ class SegmentSumMLPModule(torch.nn.Module):
         elif not features.is_cuda:
             raise _lib.VaexError("SegmentSumMLPModule.forward needs CUDA tensors (no CPU fallback)")
         elif features.dtype == torch.float16:      # rows already narrowed (the tcgen05 kernel rounds to fp16 first anyway)
-            feats, flags = features.detach().contiguous(), flags | _lib.F_FEATS_F16
+            feats, flags = _lib.check_device(features).detach().contiguous(), flags | _lib.F_FEATS_F16
             n_rows = feats.shape[0]
         else:
-            feats = features.detach().contiguous().float()
+            feats = _lib.check_device(features).detach().contiguous().float()
             n_rows = feats.shape[0]
         lib = _lib.load()
         m = self.packed(fea_norm_vec)
@@ -280,7 +280,7 @@ class SegmentSumMLPModule(torch.nn.Module):
         elif not features.is_cuda:
             raise _lib.VaexError("SegmentSumMLPModule.segment_sums needs CUDA tensors (no CPU fallback)")
         else:
-            feats = features.detach().contiguous().float()
+            feats = _lib.check_device(features).detach().contiguous().float()
             n_rows = feats.shape[0]
         lib = _lib.load()
         m = self.packed(fea_norm_vec)

@@ -22,7 +22,7 @@ def _mlp(dims, last_act=True):
 def _need_cuda(t):
     if not t.is_cuda:
         raise _lib.VaexError("vaex_b200 needs CUDA tensors (no CPU fallback)")
-    return t.detach().contiguous().float()
+    return _lib.check_device(t).detach().contiguous().float()
 
 
 class _Packed:
