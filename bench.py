@@ -805,7 +805,28 @@ def main_vaex(args):
         # chunks that crossed PCIe narrowed to fp16 by the host cores vs as the caller's fp32 rows (same scores bit for bit)
         nar, raw = model.counter(0) - cnt0[0], model.counter(1) - cnt0[1]
         frac16 = nar / max(1, nar + raw)
+        # the bare copy ceiling of this box: every rank pushes 1 GiB of pinned memory through cudaMemcpyAsync at the same
+        # time (device-timed, max over ranks); e2e moves h2d_bytes_per_step per rank over the same link
+        probe_n = min(host.numel() * 4, 1 << 30)
+        probe_dst = torch.empty(probe_n, dtype=torch.uint8, device=dev)
+        probe_src = host.view(torch.uint8).reshape(-1)[:probe_n]
+        probe_dst.copy_(probe_src, non_blocking=True)
+        barrier()
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        c0.record(stream)
+        for _ in range(3):
+            probe_dst.copy_(probe_src, non_blocking=True)
+        c1.record(stream)
+        barrier()
+        tc_ = torch.tensor([c0.elapsed_time(c1) / 3], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(tc_, op=dist.ReduceOp.MAX)
+        h2d_gbs = probe_n / (float(tc_.item()) * 1e-3) / 1e9          # per rank, all ranks copying
+        del probe_dst, probe_src
+        h2d_step = int(re_ * F * 4 * (1 - frac16) + re_ * F * 2 * frac16 + Pe * 4 + Pe * L_LAT * 4)
         e2e = {"value": world * Pe / float(tt.item()), "unit": UNIT,
+               "h2d_gbs_bare_per_rank": h2d_gbs,
+               "frac_of_bare_copy": (h2d_step / (h2d_gbs * 1e9)) / float(tt.item()),
                "h2d_bytes_per_step": int(re_ * F * 4 * (1 - frac16) + re_ * F * 2 * frac16 + Pe * 4 + Pe * L_LAT * 4),
                "d2h_bytes_per_step": int(Pe * 4 + Pe * D_EXT * 4), "programs_per_gpu": Pe, "steps": n_e2e,
                "host_input_bytes_per_step": int(re_ * F * 4 + Pe * 4 + Pe * L_LAT * 4),
