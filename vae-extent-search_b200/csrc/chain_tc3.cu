@@ -16,13 +16,15 @@
 //     columns [0, 256) and [256, 512); while the eight worker warps of X run an epilogue, the tensor pipe runs Y's MMAs;
 //   * weights are NOT resident: each layer is cut into k-quarter pieces ([N/2 rows x 64 halves] per CTA, <= 16 KB, the
 //     exact SWIZZLE_128B operand image), and one producer thread per CTA streams them through a 5-slot ring with
-//     cp.async.bulk.tensor (cta_group::2: both CTAs' boxes complete on the leader's mbarrier).  A piece is used by X
-//     and by Y before tcgen05.commit releases its slot, so the L2 traffic is 80 KB per tile per CTA;
-//   * issue order per layer: X(k0) X(k2) Y(k0) Y(k2) X(k1) X(k3) Y(k1) Y(k3) -> commit ACC_X after X(k3), ACC_Y after
-//     Y(k3): X's epilogue (first half done ~0.3 us after ACC_X) hides under Y's second half, and vice versa;
+//     cp.async.bulk.tensor (cta_group::2: both CTAs' boxes complete on the leader's mbarrier); tcgen05.commit releases
+//     a slot.  Issue order per layer: all of X's pieces (k0 k2 k1 k3), commit ACC_X, all of Y's, commit ACC_Y -- every
+//     tile gets its own copy of a piece (160 KB per tile per CTA from L2).  Sharing a piece between X and Y halves that
+//     traffic but couples the tiles: each then waits for the other's epilogue inside every layer (measured slower);
 //   * worker thread = (row, half of the 256 columns): four 32-column TMEM loads, bias + ReLU + fp16 pack into two
 //     k-quarter atoms of the next layer's operand, one IN[kq] arrival per atom; DRAIN after the last TMEM load lets
-//     the next layer overwrite the accumulator.
+//     the next layer overwrite the accumulator;
+//   * no local memory: with 227 KB of shared memory carved out the L1 is a few KB and every local access is an L2
+//     round trip (a dynamically indexed phase array and 172 B of spills made the first version 1.5 x slower than v2).
 // MC-dropout passes stay on chain_tc.cu (their layer-0 activations live in registers across passes).
 #include <cuda.h>
 
