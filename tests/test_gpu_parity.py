@@ -1045,3 +1045,21 @@ def test_kcenter_select_matches_reference():
         device=torch.device("cuda"), topk_factor=5)
     assert np.array_equal(sel_prog, g["sel_prog_div"])
     assert np.array_equal(np.array(sorted(rem_prog)), g["rem_prog_div"])
+
+
+@pytest.mark.gpu
+def test_resident_weight_chain_kernel_still_agrees():
+    """chain_tc.cu (one tile per CTA pair, resident weights) serves the MC-dropout passes and is the fallback of
+    chain_tc3.cu; VAEX_CHAIN_V2=1 routes every chain through it.  The switch is read once per process, so the chain
+    parity tests are re-run in a child process with it set (both encoder heads in one pass with W0 in the operand, the
+    128-wide layer 0 of the segment predictor with its biases read through L1)."""
+    import os
+    import subprocess
+    import sys
+    if os.environ.get("VAEX_CHAIN_V2") == "1":
+        pytest.skip("already the child")
+    env = dict(os.environ, VAEX_CHAIN_V2="1")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-q", "-x", "-m", "gpu", "-k",
+                        "extent_chain_tensor_cores or segment_family_heads or extent_vae_golden"],
+                       env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
