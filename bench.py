@@ -334,7 +334,7 @@ def main_vaex(args):
                                                      _lib.ptr(mer_v), _lib.ptr(mer_i), _lib.ptr(mer_n), st))
 
     graph_note = {"graph": False}
-    graphs = []
+    cuda_graphs = []
 
     def graphed(fn):
         """The step's 18 local launches captured ONCE into a CUDA graph (every entry point of the step is stream-ordered:
@@ -353,7 +353,7 @@ def main_vaex(args):
                 fn(side.cuda_stream, False)
             stream.wait_stream(side)
             torch.cuda.synchronize()
-            graphs.append(g)
+            cuda_graphs.append(g)
 
             def replay():
                 g.replay()
@@ -877,7 +877,7 @@ def main_vaex(args):
         print(json.dumps(line))
     if comm is not None:
         torch.cuda.synchronize()
-        for g in graphs:
+        for g in cuda_graphs:
             g.reset()
         comm.close()
     if world > 1:
