@@ -384,7 +384,7 @@ def test_mc_predict_fused_tensor_core_passes(n):
         assert np.abs(cb_t - cb_s).max() < 4e-3 * np.sqrt((cb_s ** 2).mean())
 
 
-@pytest.mark.parametrize("n", [1, 127, 128, 129, 300, 70001])
+@pytest.mark.parametrize("n", [1, 127, 128, 129, 300, 513, 70001])
 def test_extent_chain_tensor_cores(n):
     """the fused tcgen05 chains (decoder 64-256-256-256-48 [+ snap epilogue]; predictor 64-256-256-1) against the
     oracle at the fp16-operand tolerance, on ragged batch sizes around the 128-row tile; the fused snap must be
@@ -1063,3 +1063,33 @@ def test_resident_weight_chain_kernel_still_agrees():
                         "extent_chain_tensor_cores or segment_family_heads or extent_vae_golden"],
                        env=env, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("D,L,n", [(45, 16, 1000), (15, 64, 333), (45, 64, 5000)])
+def test_extent_chain_odd_widths(D, L, n):
+    """The notebook's real widths (MAX_SEQ_LENGTH = 45 extents, vae_sch_extent.ipynb cell 15; 15 for the README's CPU
+    example; latent 16 by default, utils/model.py:6): rows that are not a multiple of 8 floats take the scalar load /
+    store paths of the chain kernels, and the fused snap must still equal the snap of the kernel's own x."""
+    torch.manual_seed(D * 100 + L)
+    vae = vaex_b200.VAE_feature_head(D, None, L, 256).cuda().eval()
+    reg = vaex_b200.VAECostPredictor(D, hidden_dim=256, latent_dim=L).cuda().eval()
+    sdv = {k: v.detach().cpu() for k, v in vae.state_dict().items()}
+    sdr = {k: v.detach().cpu() for k, v in reg.state_dict().items()}
+    rng = np.random.default_rng(n)
+    z = rng.standard_normal((n, L)).astype(np.float32)
+    x = rng.standard_normal((n, D)).astype(np.float32)
+    zd, xd = torch.from_numpy(z).cuda(), torch.from_numpy(x).cuda()
+    got_x = vae.decode(zd)
+    want_x = O.vae_decode(sdv, z).numpy()
+    assert l2_err(got_x.cpu().numpy(), want_x) < TC_RTOL and rel_err(got_x.cpu().numpy(), want_x) < 4 * TC_RTOL
+    want_mu, want_lv = O.vae_encode(sdv, x)
+    got_mu, got_lv = vae.encode(xd)
+    assert l2_err(got_mu.cpu().numpy(), want_mu.numpy()) < TC_RTOL and l2_err(got_lv.cpu().numpy(), want_lv.numpy()) < TC_RTOL
+    got_c = reg.predict_cost(zd).cpu().numpy()
+    assert l2_err(got_c, O.predict_cost(sdr, z).numpy()) < TC_RTOL
+    mean = rng.uniform(0.5, 3, D).astype(np.float32)
+    std = rng.uniform(0.3, 1.5, D).astype(np.float32)
+    x2, ext = vae.decode_and_snap(zd, mean, std)
+    assert torch.equal(x2, got_x)
+    assert torch.equal(ext, vaex_b200.snap_extents(x2, mean, std))
