@@ -352,6 +352,16 @@ __device__ __forceinline__ void sum_irregular(uint32_t tcol, const uint2* __rest
 //            swizzle = the UMMA operand layout) that complete on the leader CTA's mbarrier; no loader warps, no
 //            format-conversion instructions, 384 instead of 656 bytes of HBM per row.
 enum { IN_F32 = 0, IN_F16 = 1, IN_IMAGE = 2 };
+// -DSEGSUM_PROF: clock64 accounting of cluster 0 in shared memory (issuer waits per barrier, epi 0 / epi 1 waits and work of
+// their polling warps), dumped to seg_prof at exit; read with vaex_debug_segsum_prof (tools/prof_segsum.py)
+#ifdef SEGSUM_PROF
+__device__ unsigned long long seg_prof[32];
+#define SGP(i, v) do { if (blockIdx.x == 0) sprof[i] += (unsigned long long)(v); } while (0)
+#define SGT() clock64()
+#else
+#define SGP(i, v) do { (void)(v); } while (0)
+#define SGT() 0ll
+#endif
 template <bool FOLD, int IN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(tc::THREADS, 1)
 segsum_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
@@ -361,6 +371,10 @@ segsum_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
   __shared__ __align__(8) uint64_t bars[B_COUNT];
   __shared__ uint32_t tmem_base_slot;
   __shared__ __align__(16) uint16_t a0_tab[FAST_SLOTS * 32];
+#ifdef SEGSUM_PROF
+  __shared__ unsigned long long sprof[32];
+  if (threadIdx.x < 32) sprof[threadIdx.x] = 0;
+#endif
 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const uint32_t sbase = ptx::smem_u32(smem);
@@ -495,12 +509,15 @@ segsum_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
     for (int t = cluster; t < p.T; t += n_clusters, ++it) {
 #pragma unroll 1
       for (int g = 0; g < 2; ++g) {                        // hidden half g = acc0 columns [128g, 128g+128)
+        const long long p0 = SGT();
         if (q == 0) {
           ptx::mbar_wait(bar(B_ACC0_FULL0 + g), it & 1);
           if (g == 0 && it > 0) ptx::mbar_wait(bar(B_ACC1_FULL1), (it - 1) & 1);   // layer 1 of the previous tile has read A1
         }
         ptx::bar_sync(2, 128);
         ptx::tc_fence_after();
+        const long long p1 = SGT();
+        if (warp == LOAD_WARPS && lane == 0) SGP(8 + 2 * g, p1 - p0);
         const uint32_t tcol = tmem + lane_base + 128 * g;
         uint32_t va[32], vb[32];
         ptx::tmem_ld32(tcol, va);
@@ -519,6 +536,7 @@ segsum_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
         ptx::tc_fence_before();
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive_cluster_relaxed(bar(B_A1_FULL0 + g), 0);
+        if (warp == LOAD_WARPS && lane == 0) SGP(9 + 2 * g, SGT() - p1);
       }
     }
   } else if (warp < MMA_WARP) {
@@ -563,8 +581,11 @@ segsum_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
       const uint4 ma = na, mc = nc;
       const uint2 mb = nb, md = nd;
       fetch_meta(t + n_clusters);
+      const long long q0 = SGT();
       ptx::mbar_wait_role(bar(B_ACC1_FULL0 + g), it & 1, poller, 3 + g, GROUP_THREADS);
       ptx::tc_fence_after();
+      const long long q1 = SGT();
+      if (poller && lane == 0) SGP(12 + 2 * g, q1 - q0);
       ptx::tmem_ld16(tcol_of(s_begin), va);
       float* dst = out_h;
       float a0 = 0.f, a1 = 0.f;
@@ -601,6 +622,7 @@ segsum_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_cluster_relaxed(bar(B_ACC1_EMPTY0 + g), 0);
+      if (poller && lane == 0) SGP(13 + 2 * g, SGT() - q1);
     }
   } else {
     // ===== MMA issuer: one thread of the leader CTA =====
@@ -646,8 +668,12 @@ segsum_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
       int it = 0;
       for (int t = cluster; t < p.T; t += n_clusters, ++it) {
         // ---- layer 0: two hidden halves ----
+        const long long i0 = SGT();
+        if (lane == 0) { SGP(0, 1); if (it == 1) SGP(7, 0); }
         ptx::mbar_wait(bar(B_A0_FULL), it & 1);
         ptx::tc_fence_after();
+        const long long i1 = SGT();
+        if (lane == 0) SGP(1, i1 - i0);
         if (ptx::elect_one()) {
           if (L0_N256) {
             for (int k = 0; k < p.k0_steps; ++k)
@@ -697,9 +723,13 @@ segsum_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
           continue;
         }
         // ---- layer 1, row block 0 (rows [0,64) of both CTAs): K half 0 then K half 1 ----
+        const long long i2 = SGT();
         if (it > 0) ptx::mbar_wait(bar(B_ACC1_EMPTY0), (it - 1) & 1);
+        const long long i3 = SGT();
         ptx::mbar_wait(bar(B_A1_FULL0), it & 1);
         ptx::tc_fence_after();
+        const long long i4 = SGT();
+        if (lane == 0) { SGP(2, i3 - i2); SGP(3, i4 - i3); }
         if (ptx::elect_one()) {
           if (FOLD) ptx::umma_f16_2cta(tmem + 256, dW0 + kadv(KB1), dA0 + kadv(KB1), idesc_n128, 0);
 #pragma unroll
@@ -707,8 +737,10 @@ segsum_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
             ptx::umma_f16_2cta(tmem + 256, dW1 + kadv(k), dA1 + kadv(k), idesc_n128, FOLD || k > 0);
         }
         __syncwarp();
+        const long long i5 = SGT();
         ptx::mbar_wait(bar(B_A1_FULL1), it & 1);
         ptx::tc_fence_after();
+        if (lane == 0) SGP(4, SGT() - i5);
         if (IN == IN_IMAGE && t + n_clusters < p.T) {
           // epi 0 has drained both halves of acc0, so layer 0 is complete and A0_EMPTY has fired: this wait falls through
           ptx::mbar_wait(bar(B_A0_EMPTY), it & 1);
@@ -722,8 +754,10 @@ segsum_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
         }
         __syncwarp();
         // ---- layer 1, row block 1 (rows [64,128) of both CTAs) ----
+        const long long i6 = SGT();
         if (it > 0) ptx::mbar_wait(bar(B_ACC1_EMPTY1), (it - 1) & 1);
         ptx::tc_fence_after();
+        if (lane == 0) { SGP(5, SGT() - i6); SGP(6, SGT() - i0); }
         if (ptx::elect_one()) {
           if (FOLD) ptx::umma_f16_2cta(tmem + 384, dW0 + kadv(KB1), dA0 + rows64 + kadv(KB1), idesc_n128, 0);
 #pragma unroll
@@ -741,6 +775,9 @@ segsum_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
   __syncthreads();
   ptx::cluster_sync();
   if (warp == EPI1_WARP0) ptx::tmem_dealloc_2cta(tmem, 512);
+#ifdef SEGSUM_PROF
+  if (blockIdx.x == 0 && threadIdx.x < 32) seg_prof[threadIdx.x] = sprof[threadIdx.x];
+#endif
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1000,3 +1037,9 @@ int segsum_tc_encode(vaex_model* m, const float* feats, const int32_t* off, int6
 }
 
 }  // namespace vaex
+
+#ifdef SEGSUM_PROF
+extern "C" int vaex_debug_segsum_prof(unsigned long long* out) {
+  return (int)cudaMemcpyFromSymbol(out, vaex::seg_prof, sizeof(unsigned long long) * 32);
+}
+#endif
