@@ -75,7 +75,8 @@ constexpr bool L1_N256 = false;
 // column c then holds hidden unit c, so W1's K order is the identity).  Measured: the image path gets SLOWER (3.06 vs
 // 2.76-2.90 ms), the fp32-row path faster (3.69 vs 3.96-4.23 ms): with both hidden halves completing together, epi 0's
 // four warps start on half 0 no earlier than before and layer 1 waits for them with an idle pipe, where the two N = 128
-// halves keep the pipe busy under epi 0.  Off; kept as a switch for the record.
+// halves keep the pipe busy under epi 0.  Both switches on: 2.95 ms (the 3.6 K clk of MMAs per tile would allow 1.5 x, but
+// a block's drain takes 2.5 K clk -- profiles/r02_chain_cycles.md -- and nothing hides it).  Off; kept for the record.
 constexpr bool L0_N256 = false;
 constexpr int B1_COL = 176;          // k columns of the b1 hi/lo halves (spare k-step 11 of the W0 / A0 images)
 enum { B_A0_FULL = 0, B_A0_EMPTY, B_ACC0_FULL0, B_ACC0_FULL1, B_A1_FULL0, B_A1_FULL1, B_ACC1_FULL0, B_ACC1_FULL1,
