@@ -519,7 +519,7 @@ def main_vaex(args):
         ms_e = timed(lambda: _lib.check(lib.vaex_vae_encode(vmodel.h, _lib.ptr(xs), P, _lib.ptr(mu), _lib.ptr(lv), st)), it)
         tensor_entry("chain3 encode (mu, logvar in one pass)", ms_e, P * FLOP_ENCODE, "%d rows x 352 256 FLOP" % P, P * (3 * H + 128) * 4)
         ms_mc = timed(lambda: _lib.check(lib.vaex_predict_cost(rmodel.h, _lib.ptr(z), P, _lib.ptr(cost), None, 12345, 0.1, st)), 3, warm=1)
-        tensor_entry("chain_tc predict_cost with MC-dropout (one of mc_predict's T passes; Philox keep bits in the epilogue)", ms_mc, P * FLOP_PREDICT,
+        tensor_entry("chain_mc3 predict_cost with MC-dropout (one of mc_predict's T passes; Philox keep bits in the epilogue)", ms_mc, P * FLOP_PREDICT,
                      "%d latents x 164 352 FLOP" % P, P * 2 * H * 4)
         ms_l = timed(lambda: _lib.check(lib.vaex_legalise_extents(_lib.ptr(extents), P, D_EXT, _lib.ptr(ext_d), _lib.ptr(last_d), None, 0, 64, st)), it)
         hbm_entry("legalise_tiled_kernel", ms_l, P * D_EXT * 8, "%d x 48 extents x 8 B (in place)" % P)

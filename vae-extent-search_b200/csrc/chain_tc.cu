@@ -233,7 +233,7 @@ chain_tc_kernel(const ChainParams p) {
         }
       } else {
         const int64_t chunk = r / p.drop_chunk;
-        const Philox gen(p.drop_seed + (uint64_t)pass + 0x9E3779B97F4A7C15ull * (uint64_t)chunk);
+        const PhiloxDrop gen(p.drop_seed + (uint64_t)pass + 0x9E3779B97F4A7C15ull * (uint64_t)chunk);
         const uint64_t q0 = (uint64_t)(((r - chunk * p.drop_chunk) * HID + col) >> 3);
         const uint32_t thr = dropout_threshold(p.drop_p);
 #pragma unroll
@@ -690,6 +690,7 @@ int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode
   cp.ready = false;
   TRY(chain2_pack(cp, layers, mode, st, two_heads));
   TRY(chain3_pack(cp, layers, mode, st, two_heads));
+  if (mode == ch::MODE_DOT) TRY(chain_mc3_pack(cp, layers, st));
   cp.ready = cp.v2 || cp.v3 != nullptr;
   return VAEX_OK;
 }
@@ -700,6 +701,7 @@ void chain_tc_release(ChainPack& cp) {
   if (cp.bias) cudaFree(cp.bias);
   cp.w = nullptr; cp.w0 = nullptr; cp.bias = nullptr;
   chain3_release(cp);
+  chain_mc3_release(cp);
   cp.ready = cp.v2 = false;
 }
 
@@ -716,6 +718,7 @@ int chain_tc_run(const ChainPack& cp, const float* X, int64_t n, float* out, int
   VAEX_CHECK(cp.ready, "tcgen05 chain not packed");
   if (n == 0) return VAEX_OK;
   if (cp.v3 && !drop && !(cp.v2 && chain_force_v2())) return chain3_run(cp, X, n, out, extents, mean, scale, snap_mode, st, out2);
+  if (drop && cp.mc3 && !(cp.v2 && chain_force_v2())) return chain_mc3_run(cp, X, n, out, *drop, st);
   VAEX_CHECK(cp.v2, "this chain has no resident-weight image (MC-dropout passes need the two-layer 64-wide predictor)");
   ChainParams P = *reinterpret_cast<const ChainParams*>(cp.params_storage);
   P.X = X; P.w = cp.w; P.bias = cp.bias; P.out = out; P.extents = extents; P.snap_mean = mean; P.snap_scale = scale;

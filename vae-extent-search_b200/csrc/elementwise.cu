@@ -486,7 +486,7 @@ __global__ void dropout_kernel(float* __restrict__ h, int64_t count, const uint8
   const float inv = 1.f / (1.f - p);
   const uint32_t thr = dropout_threshold(p);
   uint4 r = make_uint4(0, 0, 0, 0);
-  if (!mask) r = Philox(seed)((uint64_t)q, 0);
+  if (!mask) r = PhiloxDrop(seed)((uint64_t)q, 0);
   const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
 #pragma unroll
   for (int i = 0; i < 8; ++i) {

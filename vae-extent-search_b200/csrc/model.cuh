@@ -33,6 +33,7 @@ struct ChainPack {
   __half* w0 = nullptr;    // layer-0 image when it lives in the operand (encoder with both latent heads)
   float* bias = nullptr;
   void* v3 = nullptr;      // Chain3Pack (chain_tc3.cu: two tiles in flight, streamed weights) when the shape fits it
+  void* mc3 = nullptr;     // Mc3Pack (chain_mc3.cu: the MC-dropout passes with layer 0's accumulator kept in TMEM)
   bool v2 = false;         // chain_tc.cu's resident-weight kernel is packed (MC-dropout passes need it)
   int smem_bytes = 0;
   bool ready = false;
@@ -112,6 +113,10 @@ void chain3_release(ChainPack& cp);
 // mask uint8 [passes][n, 256] (1 = keep) or, when null, the Philox stream of dropout_kernel with seed + pass (re-seeded
 // every chunk_rows rows like the SIMT path); passes == 1: out = cost, else out = mean and var_out = unbiased variance
 struct ChainDropout { const uint8_t* mask; uint64_t seed; float p; int passes; int64_t chunk_rows; float* var_out; };
+// chain_mc3.cu
+int chain_mc3_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, cudaStream_t st);
+int chain_mc3_run(const ChainPack& cp, const float* X, int64_t n, float* out, const ChainDropout& drop, cudaStream_t st);
+void chain_mc3_release(ChainPack& cp);
 int chain_tc_run(const ChainPack& cp, const float* X, int64_t n, float* out, int32_t* extents, const float* mean,
                  const float* scale, int snap_mode, const float* wd, const float* bd, cudaStream_t st,
                  const ChainDropout* drop = nullptr, float* out2 = nullptr);
