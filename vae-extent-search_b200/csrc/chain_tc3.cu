@@ -25,7 +25,7 @@
 //     the next layer overwrite the accumulator;
 //   * no local memory: with 227 KB of shared memory carved out the L1 is a few KB and every local access is an L2
 //     round trip (a dynamically indexed phase array and 172 B of spills made the first version 1.5 x slower than v2).
-// MC-dropout passes stay on chain_tc.cu (their layer-0 activations live in registers across passes).
+// MC-dropout passes: chain_mc3.cu (one tile per CTA pair, layer 0's accumulator kept in TMEM across the passes).
 #include <cuda.h>
 
 #include <algorithm>
