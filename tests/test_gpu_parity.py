@@ -1060,7 +1060,7 @@ def test_resident_weight_chain_kernel_still_agrees():
         pytest.skip("already the child")
     env = dict(os.environ, VAEX_CHAIN_V2="1")
     r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-q", "-x", "-m", "gpu", "-k",
-                        "extent_chain_tensor_cores or segment_family_heads or extent_vae_golden"],
+                        "extent_chain_tensor_cores or segment_family_heads or extent_vae_golden or mc_predict"],
                        env=env, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
 

@@ -685,7 +685,7 @@ static int chain2_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int
 }
 
 // Packs both kernels' images: chain_tc3.cu (two tiles in flight, streamed weights) runs every plain chain it has a shape
-// for, this file's resident-weight kernel runs the MC-dropout passes and whatever v3 does not take.
+// for, chain_mc3.cu the MC-dropout passes; this file is the fallback for both (VAEX_CHAIN_V2=1 or a shape they do not take).
 int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode, cudaStream_t st, int two_heads) {
   cp.ready = false;
   TRY(chain2_pack(cp, layers, mode, st, two_heads));
