@@ -1093,3 +1093,29 @@ def test_extent_chain_odd_widths(D, L, n):
     x2, ext = vae.decode_and_snap(zd, mean, std)
     assert torch.equal(x2, got_x)
     assert torch.equal(ext, vaex_b200.snap_extents(x2, mean, std))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("L,n,T", [(16, 1, 2), (16, 129, 3), (40, 700, 1)])
+def test_mc_predict_small_latents(L, n, T):
+    """The MC-dropout kernel with latent widths below one operand atom (16: the reference's default, utils/model.py:6; 40: a
+    row that is not a multiple of 32 bytes takes the scalar load path), one row, and T = 1 with a variance buffer: the
+    tensor-core passes against the fp32 SIMT passes with the same Philox seed."""
+    torch.manual_seed(L + n)
+    reg = vaex_b200.VAECostPredictor(48, hidden_dim=256, latent_dim=L).cuda().eval()
+    zd = torch.randn(n, L, device="cuda")
+    lib = _lib.load()
+
+    def mc(tc):
+        reg.set_tensor_cores(tc)
+        mean, var = torch.empty(n, device="cuda"), torch.full((n,), -1.0, device="cuda")
+        _lib.check(lib.vaex_mc_predict_cost(reg.packed().h, _lib.ptr(zd), n, T, None, 4242, 0.1, _lib.ptr(mean), _lib.ptr(var),
+                                            _lib.stream_ptr()))
+        return mean.cpu().numpy(), var.cpu().numpy()
+
+    m_s, v_s = mc(False)
+    m_t, v_t = mc(True)
+    scale = max(float(np.sqrt((m_s ** 2).mean())), 1e-3)
+    assert np.abs(m_t - m_s).max() < 4e-3 * scale, np.abs(m_t - m_s).max() / scale
+    if T > 1:
+        assert np.abs(np.sqrt(v_t) - np.sqrt(v_s)).max() < 4e-3 * scale
