@@ -125,6 +125,22 @@ static int pack_segment_heads(vaex_model* m, cudaStream_t st) {
     TRY(upload(m, "pred.wd256", wd.data(), 256, st));
   }
   m->head_ready = true;
+  {
+    // the three latent layers as ONE launch (reshead3.cu); the stacked fc weights are the rows of fc_mean over fc_logvar
+    HostTensor& fw = m->host["fc_stack.weight"];
+    HostTensor& fb = m->host["fc_stack.bias"];
+    fw.rows = 2 * m->L; fw.cols = m->H;
+    fw.v = m->host["fc_mean.weight"].v;
+    fw.v.insert(fw.v.end(), m->host["fc_logvar.weight"].v.begin(), m->host["fc_logvar.weight"].v.end());
+    fb.rows = 1; fb.cols = 2 * m->L;
+    fb.v = m->host["fc_mean.bias"].v;
+    fb.v.insert(fb.v.end(), m->host["fc_logvar.bias"].v.begin(), m->host["fc_logvar.bias"].v.end());
+    auto lay = [&](const std::string& pre) {
+      HostTensor& w = m->host[pre + ".weight"];
+      return ChainLayer{&w.v, &m->host[pre + ".bias"].v, w.rows, w.cols};
+    };
+    TRY(latent_heads3_pack(&m->latent3, lay("l0.0"), lay("l1.0"), lay("fc_stack"), m->L, st));
+  }
   return VAEX_OK;
 }
 
@@ -338,6 +354,7 @@ int vaex_model_destroy(vaex_model_t h) {
   if (!h) return VAEX_OK;
   for (auto& kv : h->dev) cudaFree(kv.second);
   for (auto& kv : h->head_img) if (kv.second) cudaFree(kv.second);
+  latent_heads3_release(&h->latent3);
   for (auto& b : h->ws) b.release();
   h->topk_ws.release();
   h->tc_ws.release();

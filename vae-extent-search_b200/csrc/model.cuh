@@ -61,6 +61,7 @@ struct vaex_model {
   std::map<std::string, __half*> head_img;   // fp16 images of 256-wide layers for head_tc_linear, by name (segment family)
   vaex::ChainPack dec_chain, pred_chain, enc_mu_chain, enc_lv_chain, enc_both_chain;   // extent-VAE decoder / cost predictor / encoder on tensor cores
   bool head_ready = false;                 // segment family: every latent / decoder / predictor layer has a head_tc image
+  void* latent3 = nullptr;                 // R3Pack (reshead3.cu): norm -> l0 -> l1 -> [fc_mean; fc_logvar] in one launch
   int use_tensor = 1;                      // VAEX_OPT_TENSOR_CORES
   int use_fused_ascent = 1;                // VAEX_OPT_FUSED_ASCENT
   vaex::DevBuf ws[6];                  // activations / staging
@@ -104,6 +105,11 @@ int head_tc_linear(const HeadLinear& a, cudaStream_t st);
 struct ChainLayer { const std::vector<float>* w; const std::vector<float>* b; int out, in; };   // row-major [out, in] fp32 + bias
 int chain_tc_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode, cudaStream_t st, int two_heads = 0);
 void chain_tc_release(ChainPack& cp);
+// reshead3.cu
+int latent_heads3_pack(void** slot, const ChainLayer& l0, const ChainLayer& l1, const ChainLayer& fc, int L, cudaStream_t st);
+int latent_heads3_run(void* pack, const float* S, int64_t n, const float* nscale, const float* nshift, float* mean, float* logvar,
+                      cudaStream_t st);
+void latent_heads3_release(void** slot);
 // chain_tc3.cu
 int chain3_pack(ChainPack& cp, const std::vector<ChainLayer>& layers, int mode, cudaStream_t st, int two_heads);
 int chain3_run(const ChainPack& cp, const float* X, int64_t n, float* out, int32_t* extents, const float* mean, const float* scale,
