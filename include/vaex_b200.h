@@ -204,6 +204,13 @@ int vaex_reparam(const float* mu_dev, const float* logvar_dev, const float* eps_
                  void* stream);
 /* VAE_feature_head.decode (utils/model.py:63-64) -> x_cont fp32 [n, D] */
 int vaex_vae_decode(vaex_model_t h, const float* z_dev, int64_t n, float* x_dev, void* stream);
+/* VAE_feature_head.predict_feature (scripts/pre_experiments/model_myself/utils/model.py:43-50,66-67): the optional
+ * head z [n, L] -> relu(Linear) -> relu(Linear) -> Linear -> features [n, feature_dim], present when the state_dict
+ * carries feature_predictor.{0,2,4}.  feature_dim <= 64 runs as one tcgen05 chain, wider heads on the fp32 kernels.
+ * VAEX_E_INVALID when the model was packed without the head. */
+int vaex_vae_predict_feature(vaex_model_t h, const float* z_dev, int64_t n, float* feat_dev, void* stream);
+/* width of that head (0: none) */
+int vaex_vae_feature_dim(vaex_model_t h, int32_t* feature_dim);
 /* postprocess + clamp (vae_sch_extent.ipynb:1374-1383,1457) and optional divisor legalise.
  * mean/scale: fp32[D] (StandardScaler.mean_/scale_); slot_extent int32[D] (0 = free slot),
  * slot_last uint8[D] (1 = innermost length of a split) only for VAEX_SNAP_DIVISOR. */

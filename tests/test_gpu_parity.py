@@ -1119,3 +1119,27 @@ def test_mc_predict_small_latents(L, n, T):
     assert np.abs(m_t - m_s).max() < 4e-3 * scale, np.abs(m_t - m_s).max() / scale
     if T > 1:
         assert np.abs(np.sqrt(v_t) - np.sqrt(v_s)).max() < 4e-3 * scale
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("feature_dim,n", [(10, 300), (57, 1), (164, 777)])
+def test_feature_predictor_head(feature_dim, n):
+    """VAE_feature_head.predict_feature (utils/model.py:43-50,66-67): the optional z -> 256 -> 256 -> feature_dim head.  Up to
+    64 features it is one tcgen05 chain (fp16-operand tolerance), wider heads run on the fp32 kernels (1e-5); forward()
+    returns it as the fifth element like the reference."""
+    torch.manual_seed(feature_dim)
+    vae = vaex_b200.VAE_feature_head(48, feature_dim, 64, 256).cuda().eval()
+    z = torch.randn(n, 64, device="cuda")
+    with torch.no_grad():
+        want = vae.feature_predictor(z)                 # the module's own torch layers: plain fp32 reference of the same op
+        got = vae.predict_feature(z)
+        out = vae(torch.randn(n, 48, device="cuda"))
+    assert got.shape == (n, feature_dim)
+    tol = TC_RTOL if feature_dim <= 64 else 1e-5
+    assert l2_err(got.cpu().numpy(), want.cpu().numpy()) < tol, l2_err(got.cpu().numpy(), want.cpu().numpy())
+    assert out[4] is not None and out[4].shape == (n, feature_dim)
+    with torch.no_grad():
+        assert l2_err(out[4].cpu().numpy(), vae.feature_predictor(out[3]).cpu().numpy()) < tol
+    plain = vaex_b200.VAE_feature_head(48, None, 64, 256).cuda().eval()
+    with pytest.raises(AttributeError):
+        plain.predict_feature(z)

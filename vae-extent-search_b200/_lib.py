@@ -42,6 +42,8 @@ SIGNATURES = {
     "vaex_vae_encode": ([vp, vp, i64, vp, vp, vp], ctypes.c_int),
     "vaex_reparam": ([vp, vp, vp, u64, u64, vp, i64, i32, vp], ctypes.c_int),
     "vaex_vae_decode": ([vp, vp, i64, vp, vp], ctypes.c_int),
+    "vaex_vae_predict_feature": ([vp, vp, i64, vp, vp], ctypes.c_int),
+    "vaex_vae_feature_dim": ([vp, vp], ctypes.c_int),
     "vaex_feature_blob_scan": ([vp, i64, i32, vp], ctypes.c_int),
     "vaex_feature_blob_unpack": ([vp, i64, i32, vp, vp, vp, vp, vp, vp], ctypes.c_int),
     "vaex_segsum_mlp_predict_blob": ([vp, vp, i64, vp, i64, ctypes.c_int], ctypes.c_int),

@@ -227,6 +227,17 @@ static int pack_model(vaex_model* m, const float* norm, cudaStream_t st) {
       TRY(chain_tc_pack(m->dec_chain, {chain_layer(m, "decoder.0"), chain_layer(m, "decoder.2"), chain_layer(m, "decoder.4"),
                                        chain_layer(m, "decoder.6")}, 0, st));
       TRY(pack_encoder_chains(m, st));
+      m->feat_dim = 0;
+      if (m->host.count("feature_predictor.0.weight") && m->host.count("feature_predictor.4.weight")) {   // optional head
+        const int Fd = m->host["feature_predictor.4.weight"].rows;
+        TRY(pack_linear(m, "feature_predictor.0", m->H, m->L, st));
+        TRY(pack_linear(m, "feature_predictor.2", m->H, m->H, st));
+        TRY(pack_linear(m, "feature_predictor.4", Fd, m->H, st));
+        m->feat_dim = Fd;
+        if (Fd <= 64)
+          TRY(chain_tc_pack(m->feat_chain, {chain_layer(m, "feature_predictor.0"), chain_layer(m, "feature_predictor.2"),
+                                            chain_layer(m, "feature_predictor.4")}, 0, st));
+      }
       return VAEX_OK;
     }
     case VAEX_KIND_COST_PREDICTOR: {
@@ -365,7 +376,7 @@ int vaex_model_destroy(vaex_model_t h) {
   if (h->tc.wl0) cudaFree(h->tc.wl0);
   if (h->tc.wl1) cudaFree(h->tc.wl1);
   for (auto& sl : h->slots) { if (sl.feats) cudaFree(sl.feats); if (sl.off) cudaFree(sl.off); if (sl.scores) cudaFree(sl.scores); }
-  for (ChainPack* cp : {&h->dec_chain, &h->pred_chain, &h->enc_mu_chain, &h->enc_lv_chain, &h->enc_both_chain}) chain_tc_release(*cp);
+  for (ChainPack* cp : {&h->dec_chain, &h->pred_chain, &h->enc_mu_chain, &h->enc_lv_chain, &h->enc_both_chain, &h->feat_chain}) chain_tc_release(*cp);
   for (auto& pn : h->pinned) if (pn.p) cudaFreeHost(pn.p);
   for (auto& pn : h->pack_stage) if (pn.p) cudaFreeHost(pn.p);
   for (auto& s : h->copy_streams) if (s) cudaStreamDestroy(s);

@@ -53,13 +53,14 @@ struct DevBuf {
 struct vaex_model {
   int kind = 0;
   int F = 0, H = 0, L = 0, D = 0, PH = 0, n_pred = 0;
+  int feat_dim = 0;                          // extent VAE: width of the optional feature_predictor head (0: none)
   int use_norm = 0, add_sigmoid = 0;
   bool packed = false;
   std::map<std::string, vaex::HostTensor> host;
   std::map<std::string, float*> dev;   // packed fp32 device tensors, by name
   vaex::TcPack tc;
   std::map<std::string, __half*> head_img;   // fp16 images of 256-wide layers for head_tc_linear, by name (segment family)
-  vaex::ChainPack dec_chain, pred_chain, enc_mu_chain, enc_lv_chain, enc_both_chain;   // extent-VAE decoder / cost predictor / encoder on tensor cores
+  vaex::ChainPack dec_chain, pred_chain, enc_mu_chain, enc_lv_chain, enc_both_chain, feat_chain;   // extent-VAE decoder / cost predictor / encoder on tensor cores
   bool head_ready = false;                 // segment family: every latent / decoder / predictor layer has a head_tc image
   void* latent3 = nullptr;                 // R3Pack (reshead3.cu): norm -> l0 -> l1 -> [fc_mean; fc_logvar] in one launch
   int use_tensor = 1;                      // VAEX_OPT_TENSOR_CORES

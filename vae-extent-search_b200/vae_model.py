@@ -39,7 +39,7 @@ class _Packed:
         if cached is not None and cached[1] == key:
             return cached[0]
         m = _lib.Model(self._kind, self._dims())
-        m.load_state({k: v for k, v in self.state_dict().items() if not k.startswith("feature_predictor")})
+        m.load_state(dict(self.state_dict()))
         m.set_option(_lib.OPT_TENSOR_CORES, int(self.__dict__.get("_tensor_cores", True)))
         self.__dict__["_packed_cache"] = (m, key)
         return m
@@ -143,12 +143,18 @@ class VAE_feature_head(_Packed, nn.Module):
         return z, score
 
     def predict_feature(self, z):
-        raise NotImplementedError("feature_predictor head (alpha_feature experiments) is outside the hot path")
+        """utils/model.py:66-67: z -> feature_predictor(z) (only when the module was built with feature_dim)."""
+        if not self.use_feature:
+            raise AttributeError("this VAE_feature_head was built without feature_dim: it has no feature_predictor")
+        z = _need_cuda(z)
+        out = torch.empty(z.shape[0], self.feature_predictor[-1].out_features, device=z.device)
+        _lib.check(_lib.load().vaex_vae_predict_feature(self.packed().h, _lib.ptr(z), z.shape[0], _lib.ptr(out), _lib.stream_ptr()))
+        return out
 
     def forward(self, x, use_mean=True):
         mu, logvar = self._encode(x)
         z = mu if use_mean else self.reparameterize(mu, logvar)
-        return self.decode(z), mu, logvar, z, None
+        return self.decode(z), mu, logvar, z, (self.predict_feature(z) if self.use_feature else None)
 
 
 def snap_extents(x, mean, scale, log1p=False, slot_extent=None, slot_last=None, max_innermost=64):
