@@ -258,6 +258,18 @@ int vaex_cost_grad_z(vaex_model_t h, const float* z_dev, int64_t n, float* cost_
 int vaex_kcenter_select(const float* z_dev, int64_t n, int32_t L, const int64_t* cand_dev, int64_t M,
                         const int64_t* used_dev, int64_t U, int32_t k, float eps, int64_t* out_sel_dev,
                         void* stream);
+/* Farthest-point sampling on the RAW rows z[cand] (no row normalisation) from a given first pick: out_sel_dev[0] =
+ * cand[first_pos]; every further pick is the candidate with the largest minimum Euclidean distance to the picks so far
+ * (lowest candidate position on ties).  Replaces the host loops of select_features
+ * (scripts/pre_experiments/for_inference/tuning_improved.py:138-170, first pick = the best acquisition score) and of
+ * select_init_latent_diversity (scripts/pre_experiments/model_myself/utils/select.py:413-428, first pick random).
+ * cand_dev_or_null int64[M] (null: rows [0, M) of z).  Returns after the selection is complete. */
+int vaex_fps_select(const float* z_dev, int64_t n, int32_t L, const int64_t* cand_dev_or_null, int64_t M, int64_t first_pos,
+                    int32_t k, int64_t* out_sel_dev, void* stream);
+/* out_d_dev[j] = min_u ||zc_j - zu_u||_2 over raw rows (+inf when U = 0): the distance of every unlabeled latent to the
+ * labeled set, tuning_improved.py:96-112 (which forms it through ||a||^2 + ||b||^2 - 2 a.b; here the direct difference). */
+int vaex_latent_min_dist(const float* zc_dev, int64_t M, const float* zu_dev, int64_t U, int32_t L, float* out_d_dev,
+                         void* stream);
 /* multi-step ascent z += lr * dcost/dz (new surface, BASELINE config 3) */
 int vaex_latent_ascent(vaex_model_t h, float* z_inout_dev, int64_t n, int32_t steps, float lr,
                        float* cost_dev, void* stream);
@@ -284,6 +296,16 @@ int vaex_segvae_encode(vaex_model_t h, const float* feats_dev, const int32_t* se
 int vaex_segvae_decode(vaex_model_t h, const float* z_dev, int64_t n, float* recon_dev, void* stream);
 /* VAECostPredictor.predict_cost (regression.py:109-111): z [n, L] -> cost [n].  Kind 5. */
 int vaex_segcost_predict(vaex_model_t h, const float* z_dev, int64_t n, float* cost_dev, void* stream);
+/* T dropout-active passes of the segment cost predictor on latents z [n, L] (the model API select_features calls,
+ * tuning_improved.py:89: model.mc_predict(seg_sizes, feats, T, use_mean=True) -- the segment VAECostPredictor of
+ * scripts/vae_experiments/models/regression.py:49-60 has Dropout(p) after every predictor block but the last; the
+ * method itself is absent from the reference, its extent-family namesake is utils/model.py:241-273).  mean_dev fp32 [n],
+ * var_dev_or_null fp32 [n] = unbiased variance over the passes.  drop_masks_dev_or_null uint8
+ * [T][predictor_layers - 1][n, PH] (1 = keep) replays recorded draws; otherwise pass t, dropout layer j uses the Philox
+ * stream drop_seed + t (predictor_layers - 1) + j over the elements of the [n, PH] activation matrix.  Block 0 is
+ * computed once; per pass one dropout + one single-layer launch per remaining block (tcgen05 head kernel when enabled). */
+int vaex_segcost_mc_predict(vaex_model_t h, const float* z_dev, int64_t n, int32_t T, const uint8_t* drop_masks_dev_or_null,
+                            uint64_t drop_seed, float p_drop, float* mean_dev, float* var_dev_or_null, void* stream);
 
 /* ---- training of the SegmentSumMLP (MLPModelInternal._fit_a_model / _fine_tune_a_model,
  *      mlp_model.py:512-600,609-651).  Parameters, gradients and the Adam moments are flat fp32

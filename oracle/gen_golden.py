@@ -375,6 +375,68 @@ def gen_kcenter(ns):
     np.savez_compressed(os.path.join(OUT, "kcenter.npz"), **out)
 
 
+def gen_acquisition(ns):
+    """select_features (for_inference/tuning_improved.py:11-175) run unmodified on the shipped segment VAECostPredictor
+    (for_inference/vae_latent_augmented_best.pth).  The two model methods it calls are absent from the reference's model
+    class, so they are bound here from the reference's own layers: get_latent_embedding = encode()[0]; mc_predict = T
+    passes through reg.cost_predictor with every Dropout module replaced by a recorded keep-mask."""
+    from oracle.ref_import import load_reference_tuning
+    tun = load_reference_tuning()
+    ref = os.environ.get("VAEX_REFERENCE_ROOT", "/root/reference")
+    ck = torch.load(os.path.join(ref, "scripts/pre_experiments/for_inference/vae_latent_augmented_best.pth"),
+                    map_location="cpu", weights_only=False)
+    cfg = ck["config"]
+    reg = ns.seg_reg.VAECostPredictor(cfg["input_dim"], cfg["hidden_dim"], cfg["latent_dim"], cfg["predictor_hidden"],
+                                      cfg["predictor_layers"], cfg["dropout"])
+    reg.load_state_dict(ck["model_state_dict"])
+    reg.eval()
+    norm = np.asarray(ck["fea_norm_vec"], np.float32).reshape(-1)
+    norm = np.where(norm == 0, 1.0, norm).astype(np.float32)
+    rng = np.random.default_rng(4242)
+    n_all, n_used, T_mc, num_select = 120, 24, 6, 8
+    progs = synth_programs(rng, n_all, zero_frac=0.0)
+    used = np.sort(rng.choice(n_all, n_used, replace=False)).astype(np.int64)
+    p = float(cfg["dropout"])
+    n_u, PH, ND = n_all - n_used, cfg["predictor_hidden"], cfg["predictor_layers"] - 1
+    masks = (rng.random((T_mc, ND, n_u, PH)) >= p).astype(np.uint8)
+    rec = {}
+
+    def get_latent_embedding(segment_sizes, features, use_mean=True):
+        with torch.no_grad():
+            return reg.encode(segment_sizes, features)[0]
+
+    def mc_predict(segment_sizes, features, T=20, use_mean=True):
+        with torch.no_grad():
+            z = reg.encode(segment_sizes, features)[0]
+            outs = []
+            for t in range(T):
+                x, j = z, 0
+                for mod in reg.cost_predictor:
+                    if isinstance(mod, torch.nn.Dropout):
+                        x = x * torch.from_numpy(masks[t, j]).float() / (1.0 - p)
+                        j += 1
+                    else:
+                        x = mod(x)
+                outs.append(x.squeeze(-1))
+            o = torch.stack(outs)
+            rec["z_mc"], rec["mu"], rec["var"] = z.numpy(), o.mean(0).numpy(), o.var(0).numpy()
+            return o.mean(0), o.var(0)
+
+    reg.get_latent_embedding, reg.mc_predict = get_latent_embedding, mc_predict
+    sel = tun.select_features(reg, progs, set(used.tolist()), torch.from_numpy(norm), num_select=num_select, T_mc=T_mc,
+                              w_cost=0.5, w_unc=0.3, w_dist=0.2, topk_factor=5)
+    unl = [i for i in range(n_all) if i not in set(used.tolist())]
+    with torch.no_grad():
+        sz = torch.tensor([len(progs[i]) for i in unl])
+        z_u = reg.encode(sz, torch.from_numpy(np.vstack([progs[i] / norm for i in unl])))[0].numpy()
+        z_l = reg.encode(torch.tensor([len(progs[i]) for i in used]), torch.from_numpy(np.vstack([progs[i] / norm for i in used])))[0].numpy()
+    np.savez_compressed(os.path.join(OUT, "acquisition.npz"), raw=np.concatenate(progs, 0),
+                        sizes=np.array([len(q) for q in progs], np.int32), used=used, norm=norm,
+                        masks=np.packbits(masks), masks_shape=np.array(masks.shape), p=np.float32(p),
+                        num_select=np.int64(num_select), T_mc=np.int64(T_mc), sel=np.array(sel, np.int64),
+                        z_u=z_u, z_l=z_l, z_mc=rec["z_mc"], mu=rec["mu"], var=rec["var"])
+
+
 def gen_feature_blob(ns):
     """A packed per-store feature blob (layout of SerializeFeatures, feature.cc:1562-1622, written by
     oracle/feature_blob.serialize_features) through the reference's own unpack_feature (feature.py:49-158)."""
@@ -716,6 +778,7 @@ def main():
     gen_segvae_train(ns)
     gen_segreg_train(ns)
     gen_select_unc(ns)
+    gen_acquisition(ns)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

@@ -14,6 +14,7 @@ Modules loaded:
   scripts/pre_experiments/model_myself/utils/{model,select,common}.py
   scripts/vae_experiments/models/{vae,regression}.py
   python/tvm/auto_scheduler/feature.py (unpack_feature only; load_reference_feature())
+  scripts/pre_experiments/for_inference/tuning_improved.py (select_features only; load_reference_tuning())
 """
 import importlib.machinery
 import importlib.util
@@ -173,4 +174,14 @@ def load_reference_seg_trainer():
     _load("util_manager", "scripts/vae_experiments/util_manager.py")
     mod = _load("_vaex_ref_seg_trainer", "scripts/vae_experiments/trainer.py")
     _CACHE["seg_trainer"] = mod
+    return mod
+
+
+def load_reference_tuning():
+    """The reference's for_inference/tuning_improved.py (select_features, :11-175) under the stub tvm package."""
+    if "tuning" in _CACHE:
+        return _CACHE["tuning"]
+    load_reference()
+    mod = _load("_vaex_ref_tuning_improved", "scripts/pre_experiments/for_inference/tuning_improved.py")
+    _CACHE["tuning"] = mod
     return mod

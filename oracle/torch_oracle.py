@@ -440,6 +440,65 @@ def kcenter_select(z, cand, used, k, eps=1e-12):
     return np.array(sel, dtype=np.int64)
 
 
+def fps_select(z, cand, first_pos, k):
+    """Farthest-point sampling on raw rows from a given first pick: the greedy loops of select_features
+    (for_inference/tuning_improved.py:138-170) and select_init_latent_diversity (utils/select.py:413-428); lowest
+    candidate position on ties (the strict > of :161, torch.argmax of :424).  Returns the chosen entries of cand."""
+    z = np.asarray(z, dtype=np.float32)
+    cand = np.arange(len(z), dtype=np.int64) if cand is None else np.asarray(cand, dtype=np.int64)
+    zc = z[cand]
+    dist = lambda j: np.sqrt(((zc - zc[j]) ** 2).sum(axis=1, dtype=np.float32), dtype=np.float32)
+    sel = [int(first_pos)]
+    min_d = dist(first_pos)
+    min_d[first_pos] = -np.inf
+    for _ in range(1, int(k)):
+        j = int(np.argmax(min_d))
+        sel.append(j)
+        min_d = np.minimum(min_d, dist(j))
+        min_d[j] = -np.inf
+    return cand[np.array(sel, dtype=np.int64)]
+
+
+def acquisition_select(z_u, z_l, mu, var, num_select, w_cost=0.5, w_unc=0.3, w_dist=0.2, topk_factor=5):
+    """The scoring and selection arithmetic of select_features (tuning_improved.py:95-172) on given unlabeled / labeled
+    latents and MC mean / variance: positions into the unlabeled pool, in pick order, and the scores."""
+    z_u = np.asarray(z_u, np.float32)
+    mu, var = np.asarray(mu, np.float32), np.asarray(var, np.float32)
+    if z_l is not None and len(z_l):
+        z_l = np.asarray(z_l, np.float32)
+        d2 = (z_u ** 2).sum(1, keepdims=True) + (z_l ** 2).sum(1, keepdims=True).T - 2 * z_u @ z_l.T      # :103-106
+        d_min = np.sqrt(np.maximum(d2, 0).min(axis=1))
+    else:
+        d_min = np.ones(len(z_u))
+    norm01 = lambda x: (x - x.min()) / (x.max() - x.min() + 1e-8)
+    scores = w_cost * norm01(-mu) + w_unc * norm01(var) + w_dist * norm01(d_min)
+    K = min(num_select * topk_factor, len(z_u))
+    top = np.argsort(scores)[::-1][:K]
+    return fps_select(z_u, top, 0, min(num_select, K)), scores
+
+
+def segcost_mc_predict(P, z, masks, p_drop):
+    """T dropout passes of the segment cost predictor (regression.py:49-60: Linear, BatchNorm (eval), ReLU, Dropout after
+    every block but the last, then Linear -> 1) with recorded keep-masks [T, blocks - 1, n, PH]: (mean, unbiased var)."""
+    z = _t(z)
+    masks = torch.as_tensor(np.asarray(masks)).float()
+    nb = masks.shape[1] + 1
+    outs = []
+    for t in range(masks.shape[0]):
+        x = z
+        for i in range(nb):
+            w, b = _t(P["cost_predictor.%d.weight" % (4 * i)]), _t(P["cost_predictor.%d.bias" % (4 * i)])
+            bn = "cost_predictor.%d." % (4 * i + 1)
+            x = x @ w.T + b
+            x = (x - _t(P[bn + "running_mean"])) / torch.sqrt(_t(P[bn + "running_var"]) + 1e-5) * _t(P[bn + "weight"]) + _t(P[bn + "bias"])
+            x = torch.relu(x)
+            if i + 1 < nb:
+                x = x * masks[t, i] / (1.0 - p_drop)
+        outs.append((x @ _t(P["cost_predictor.%d.weight" % (4 * nb)]).T + _t(P["cost_predictor.%d.bias" % (4 * nb)])).squeeze(-1))
+    o = torch.stack(outs)
+    return o.mean(0), (o.var(0) if o.shape[0] > 1 else torch.zeros_like(o[0]))
+
+
 # --------------------------------------------------------------------------------------
 # a15  regression losses and training step of the extent-family VAECostPredictor
 #      (utils/training.py:133-226; train_regression, vae_extent_search.py:1413-1440)

@@ -1143,3 +1143,98 @@ def test_feature_predictor_head(feature_dim, n):
     plain = vaex_b200.VAE_feature_head(48, None, 64, 256).cuda().eval()
     with pytest.raises(AttributeError):
         plain.predict_feature(z)
+
+
+@pytest.mark.gpu
+def test_select_features_matches_reference():
+    """n2 (second half): the acquisition-score selection of for_inference/tuning_improved.py:11-175 on the shipped segment
+    cost predictor against the picks of the unmodified reference function (tests/golden/acquisition.npz): latents,
+    MC-dropout mean / variance with the recorded keep-masks, min distance to the labeled set, score, top-K and
+    farthest-point sampling all on the GPU.  The fp32 kernels must pick what the reference picked; with the tcgen05 heads
+    the picks must be what the oracle's arithmetic picks from the GPU's own latents / mean / variance."""
+    g, gs = load_golden("acquisition.npz"), load_golden("segment_cost.npz")
+    d = [int(x) for x in gs["dims"]]
+    reg = vaex_b200.seg_models.VAECostPredictor(d[0], d[1], d[2], d[3], d[4])
+    reg.load_state_dict(split_sd(gs, "w."))
+    reg = reg.cuda().eval()
+    sizes, raw = g["sizes"], g["raw"]
+    offs = np.concatenate([[0], np.cumsum(sizes)])
+    progs = [raw[offs[i]:offs[i + 1]] for i in range(len(sizes))]
+    used = set(g["used"].tolist())
+    unl = np.array([i for i in range(len(sizes)) if i not in used], np.int64)
+    lab = np.array(sorted(used), np.int64)
+    norm = torch.from_numpy(g["norm"])
+    masks = torch.from_numpy(np.unpackbits(g["masks"])[:int(np.prod(g["masks_shape"]))].reshape(tuple(g["masks_shape"])).copy())
+    T, k = int(g["T_mc"]), int(g["num_select"])
+
+    def batch(idx):
+        return torch.from_numpy(sizes[idx]).cuda(), torch.from_numpy(np.vstack([progs[i] for i in idx])).cuda()
+
+    su, fu = batch(unl)
+    sl, fl = batch(lab)
+    for tc in (False, True):
+        reg.set_tensor_cores(tc)
+        rel = 2e-3 if tc else 1e-4
+        fl_ = 0 if tc else _lib.F_FORCE_SIMT
+        z_u = reg.get_latent_embedding(su, fu, fea_norm_vec=norm, flags=fl_)
+        z_l = reg.get_latent_embedding(sl, fl, fea_norm_vec=norm, flags=fl_)
+        assert _seg_close(z_u.cpu(), g["z_u"], rel) and _seg_close(z_l.cpu(), g["z_l"], rel)
+        mu, var = reg.mc_predict(su, fu, T=T, masks=masks, flags=fl_)
+        assert _seg_close(mu.cpu(), g["mu"], 2 * rel), float((mu.cpu() - torch.from_numpy(g["mu"])).abs().max())
+        assert _seg_close(var.cpu(), g["var"], 10 * rel)
+        dmin = torch.empty(len(unl), device="cuda")
+        _lib.check(_lib.load().vaex_latent_min_dist(_lib.ptr(z_u), len(unl), _lib.ptr(z_l), len(lab), z_u.shape[1], _lib.ptr(dmin),
+                                                   _lib.stream_ptr()))
+        want = torch.cdist(z_u.double().cpu(), z_l.double().cpu()).min(1).values
+        assert float(((dmin.cpu().double() - want).abs() / want.clamp_min(1e-9)).max()) < 1e-5
+        sel = vaex_b200.select.select_features(reg, progs, used, norm, num_select=k, T_mc=T, mc_masks=masks, flags=fl_)
+        picks, _ = O.acquisition_select(z_u.cpu().numpy(), z_l.cpu().numpy(), mu.cpu().numpy(), var.cpu().numpy(), k)
+        assert sel == unl[picks].tolist(), (tc, sel, unl[picks])
+        if not tc:
+            assert sel == g["sel"].tolist()
+    # the Philox stream instead of recorded masks: every pass a different draw, the mean close to the dropout-free cost
+    reg.set_tensor_cores(True)
+    m1, v1 = reg.mc_predict(su, fu, T=8, seed=77)
+    m2, v2 = reg.mc_predict(su, fu, T=8, seed=77)
+    m3, _ = reg.mc_predict(su, fu, T=8, seed=78)
+    assert torch.equal(m1, m2) and torch.equal(v1, v2) and not torch.equal(m1, m3) and bool((v1 > 0).any())
+    # edge cases of the selection: nothing left, fewer left than asked for, nothing labeled yet
+    assert vaex_b200.select.select_features(reg, progs, set(range(len(progs))), norm) == []
+    few = set(range(len(progs) - 3))
+    assert vaex_b200.select.select_features(reg, progs, few, norm, num_select=8) == [len(progs) - 3, len(progs) - 2, len(progs) - 1]
+    got = vaex_b200.select.select_features(reg, progs, set(), norm, num_select=5, T_mc=2, mc_seed=5)
+    assert len(set(got)) == 5
+
+
+@pytest.mark.gpu
+def test_farthest_point_sampling_vs_oracle():
+    """vaex_fps_select against the oracle's restatement of the greedy loops (tuning_improved.py:138-170,
+    utils/select.py:413-428): with and without a candidate list, k = 1, k = M, and the Python mirror
+    select_init_latent_diversity (first point given) on the extent model's encoder means."""
+    rng = np.random.default_rng(12)
+    z = (rng.standard_normal((5000, 64)) * rng.random((5000, 1)) * 4).astype(np.float32)
+    zd = torch.from_numpy(z).cuda()
+    lib = _lib.load()
+    cand = rng.permutation(5000)[:700].astype(np.int64)
+    for cnd, M, first, k in ((cand, 700, 13, 48), (None, 5000, 4999, 33), (cand[:9], 9, 0, 9), (cand, 700, 699, 1)):
+        cd = torch.from_numpy(cnd).cuda() if cnd is not None else None
+        sel = torch.empty(k, dtype=torch.int64, device="cuda")
+        _lib.check(lib.vaex_fps_select(_lib.ptr(zd), 5000, 64, _lib.ptr(cd), M, first, k, _lib.ptr(sel), _lib.stream_ptr()))
+        assert np.array_equal(sel.cpu().numpy(), O.fps_select(z, cnd, first, k)), (M, first, k)
+    bad = torch.tensor([5, 5000], dtype=torch.int64, device="cuda")
+    sel = torch.empty(2, dtype=torch.int64, device="cuda")
+    with pytest.raises(_lib.VaexError, match="out of range"):
+        _lib.check(lib.vaex_fps_select(_lib.ptr(zd), 5000, 64, _lib.ptr(bad), 2, 0, 2, _lib.ptr(sel), _lib.stream_ptr()))
+    with pytest.raises(_lib.VaexError, match="first pick"):
+        _lib.check(lib.vaex_fps_select(_lib.ptr(zd), 5000, 64, None, 10, 10, 2, _lib.ptr(sel), _lib.stream_ptr()))
+    gx = load_golden("select.npz")
+    reg = vaex_b200.VAECostPredictor(48, hidden_dim=256, latent_dim=64)
+    reg.load_state_dict(split_sd(gx, "reg."))
+    reg = reg.cuda()
+    reg.set_tensor_cores(False)
+    rem = set(range(len(gx["x"])))
+    got, rem2 = vaex_b200.select.select_init_latent_diversity(reg, gx["x"], rem, 16, first=7)
+    with torch.no_grad():
+        zz = reg.encode(torch.from_numpy(gx["x"]).cuda(), use_mean=True).cpu().numpy()
+    assert np.array_equal(got, O.fps_select(zz, None, 7, 16))
+    assert rem2 is rem and len(rem) == len(gx["x"]) - 16 and not (set(got.tolist()) & rem)

@@ -97,6 +97,9 @@ SIGNATURES = {
     "vaex_segreg_trainer_forward_backward": ([vp, vp, vp, vp, vp, vp, i64, i64, vp, vp, u64, vp, vp, vp, vp, vp], ctypes.c_int),
     "vaex_adamw_step": ([vp, vp, vp, vp, i64, i64, i64, i64, f32, f32, f32, f32, f32, f32, f32, vp, ctypes.c_int, vp], ctypes.c_int),
     "vaex_kcenter_select": ([vp, i64, i32, vp, i64, vp, i64, i32, f32, vp, vp], ctypes.c_int),
+    "vaex_fps_select": ([vp, i64, i32, vp, i64, i64, i32, vp, vp], ctypes.c_int),
+    "vaex_latent_min_dist": ([vp, i64, vp, i64, i32, vp, vp], ctypes.c_int),
+    "vaex_segcost_mc_predict": ([vp, vp, i64, i32, vp, u64, f32, vp, vp, vp], ctypes.c_int),
     "vaex_nccl_unique_id": ([vp], ctypes.c_int),
     "vaex_nccl_init": ([i32, i32, vp, ctypes.POINTER(vp)], ctypes.c_int),
     "vaex_nccl_destroy": ([vp], ctypes.c_int),

@@ -10,6 +10,7 @@
 
 #include "common.cuh"
 #include "model.cuh"
+#include "philox.cuh"
 #include "simt_kernels.cuh"
 
 namespace vaex {

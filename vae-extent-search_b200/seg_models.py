@@ -24,15 +24,19 @@ class _SegmentBase(nn.Module):
         if fea_norm_vec is not None:
             nv = fea_norm_vec.detach().cpu().numpy() if hasattr(fea_norm_vec, "detach") else fea_norm_vec
             nk = hash(np.ascontiguousarray(nv, dtype=np.float32).tobytes())
-        key = (tuple((p.data_ptr(), p._version)
-                     for p in self.state_dict(keep_vars=True).values()), nk)
-        cached = self.__dict__.get("_packed_cache")
+        key = tuple((p.data_ptr(), p._version) for p in self.state_dict(keep_vars=True).values())
+        cache = self.__dict__.setdefault("_packed_cache", {})           # one packed copy per fea_norm_vec (select_features
+        cached = cache.get(nk)                                           # alternates between a folded and a raw one)
         if cached is not None and cached[1] == key:
             return cached[0]
         m = _lib.Model(self._kind, self._dims())
         m.load_state(self.state_dict(), fea_norm_vec)
         m.set_option(_lib.OPT_TENSOR_CORES, int(self.__dict__.get("_tensor_cores", True)))
-        self.__dict__["_packed_cache"] = (m, key)
+        for k in [k for k, v in cache.items() if v[1] != key]:           # copies of weights that have since changed
+            del cache[k]
+        while len(cache) >= 2:
+            del cache[next(iter(cache))]
+        cache[nk] = (m, key)
         return m
 
     def invalidate_packed(self):
@@ -45,8 +49,7 @@ class _SegmentBase(nn.Module):
         head kernel (fp16 operands, fp32 accumulate and residuals: ~1e-3 of the reference's fp32); False: fp32 SIMT (1e-5).
         The row encoder takes VAEX_F_FORCE_SIMT per call (flags=)."""
         self.__dict__["_tensor_cores"] = bool(on)
-        cached = self.__dict__.get("_packed_cache")
-        if cached is not None:
+        for cached in self.__dict__.get("_packed_cache", {}).values():
             cached[0].set_option(_lib.OPT_TENSOR_CORES, int(bool(on)))
         return self
 
@@ -186,6 +189,33 @@ class VAECostPredictor(_SegmentBase):
         mean, logvar, _ = self._encode_segments(segment_sizes, features, flags, fea_norm_vec, want_segsum=False)
         z = mean if use_mean else self.reparameterize(mean, logvar, eps)
         return self.predict_cost(z), mean, logvar, z
+
+    def get_latent_embedding(self, segment_sizes, features, use_mean=True, fea_norm_vec=None, flags=0):
+        """The latent of every program, as select_features asks the model for it
+        (scripts/pre_experiments/for_inference/tuning_improved.py:74): the encoder mean, or a reparameterised draw."""
+        mean, logvar, _ = self._encode_segments(segment_sizes, features, flags, fea_norm_vec, want_segsum=False)
+        return mean if use_mean else self.reparameterize(mean, logvar)
+
+    def mc_predict(self, segment_sizes, features, T=20, use_mean=True, masks=None, seed=None, fea_norm_vec=None, flags=0):
+        """T dropout-active passes of the cost predictor -> (mean, unbiased variance) over the passes: the call
+        select_features makes (tuning_improved.py:89); the reference's segment model does not define it, the extent
+        family's is utils/model.py:241-273.  The encoder runs once (eval mode: deterministic).  masks (uint8
+        [T, predictor_layers - 1, N, predictor_hidden], 1 = keep) replays a given Bernoulli draw."""
+        z = self.get_latent_embedding(segment_sizes, features, use_mean, fea_norm_vec, flags)
+        n = z.shape[0]
+        if seed is None:
+            seed = int(torch.randint(1, 2 ** 62, (1,)).item())
+        mk = None
+        if masks is not None:
+            mk = masks.to(device=z.device, dtype=torch.uint8).contiguous()
+            want = (self.predictor_layers - 1, n, self.predictor_hidden)
+            if mk.dim() != 4 or mk.shape[0] < T or tuple(mk.shape[1:]) != want:
+                raise ValueError("masks must be [>= %d, %d, %d, %d], got %s" % ((T,) + want + (tuple(mk.shape),)))
+        mean, var = torch.empty(n, device=z.device), torch.empty(n, device=z.device)
+        _lib.check(_lib.load().vaex_segcost_mc_predict(self.packed(fea_norm_vec).h, _lib.ptr(z), n, int(T), _lib.ptr(mk),
+                                                      0 if mk is not None else int(seed), float(getattr(self.cost_predictor[3], "p", 0.0)),
+                                                      _lib.ptr(mean), _lib.ptr(var), _lib.stream_ptr()))
+        return mean, var
 
     def get_encoder_params(self):
         """regression.py:137-146."""
