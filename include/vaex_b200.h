@@ -270,6 +270,14 @@ int vaex_fps_select(const float* z_dev, int64_t n, int32_t L, const int64_t* can
  * labeled set, tuning_improved.py:96-112 (which forms it through ||a||^2 + ||b||^2 - 2 a.b; here the direct difference). */
 int vaex_latent_min_dist(const float* zc_dev, int64_t M, const float* zu_dev, int64_t U, int32_t L, float* out_d_dev,
                          void* stream);
+/* The 164-d per-statement feature rows of a fixed sketch, evaluated from the loop extents of n candidates:
+ * what GetPerStoreFeaturesWorkerFunc + PerStoreFeatureExtractor + GetPerStoreFeature (src/auto_scheduler/feature.cc:1296-1368,
+ * :609-1048, :1053-1188) produce by lowering each candidate with TVM on the CPU, here from a template of the sketch's
+ * lowered loop nest.  program_dev: the int32 program of vae-extent-search_b200/sketch_features.py SketchTemplate.compile()
+ * (layout in csrc/sketch_features.cu); extents_dev int32 [n, slots]; rows_dev fp32 [n * rows, 164], candidate-major, i.e.
+ * a SegmentSum-MLP batch whose segments all have `rows` statements.  Reads the program header back (one sync). */
+int vaex_sketch_features(const int32_t* program_dev, int32_t program_words, const int32_t* extents_dev, int64_t n,
+                         float* rows_dev, void* stream);
 /* multi-step ascent z += lr * dcost/dz (new surface, BASELINE config 3) */
 int vaex_latent_ascent(vaex_model_t h, float* z_inout_dev, int64_t n, int32_t steps, float lr,
                        float* cost_dev, void* stream);

@@ -1,0 +1,74 @@
+"""n4: the CUDA evaluator of sketch templates (csrc/sketch_features.cu) against the restated PerStoreFeatureExtractor
+(oracle/perstore_features.py, pinned to the reference's known-answer tests in tests/test_oracle_perstore.py) on the same
+templates and the same random extents.  Counts, one-hot fields and integer-valued features must agree exactly; log2-valued
+ones within 2e-6 relative (device log2f against numpy's)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import perstore_features as PF
+from vaex_b200 import _lib, sketch_features as SF
+from test_oracle_perstore import fusion_template, matmul_gpu_template
+
+pytestmark = pytest.mark.gpu
+
+
+def check(template, extents):
+    sk = SF.SketchFeatures(template)
+    got = sk.rows(torch.from_numpy(np.asarray(extents, np.int32)).cuda()).cpu().numpy().reshape(len(extents), sk.n_rows, 164)
+    td = template.as_dict()
+    worst = 0.0
+    for i, e in enumerate(extents):
+        want, bufs = PF.evaluate(td, list(e))
+        assert bufs == template.stored_buffers()
+        assert np.isfinite(got[i]).all()
+        err = np.abs(got[i] - want) / np.maximum(1.0, np.abs(want))
+        worst = max(worst, float(err.max()))
+        assert err.max() < 2e-6, (i, list(e), np.argwhere(err > 2e-6)[:8].tolist(), got[i][err > 2e-6][:8], want[err > 2e-6][:8])
+    return worst
+
+
+def test_known_answer_templates():
+    check(SF.matmul_cpu_template(512, 512, 512), [[32, 64, 512, 8, 16]])
+    check(fusion_template(64, 32), [[64, 32]])
+    check(matmul_gpu_template(), [[1]])
+
+
+def test_matmul_template_random_extents():
+    rng = np.random.default_rng(3)
+    div = np.array([1, 1, 2, 3, 4, 7, 8, 16, 32, 64, 128, 512])
+    ext = rng.choice(div, size=(300, 5))
+    ext[0] = 1                                   # every loop trivial: no loop nest at all
+    ext[1] = [1, 1, 512, 1, 1]
+    check(SF.matmul_cpu_template(512, 512, 512), ext.tolist())
+
+
+def test_conv2d_template_random_extents():
+    t = SF.conv2d_nhwc_cpu_template()
+    rng = np.random.default_rng(4)
+    div = np.array([1, 1, 2, 3, 4, 7, 8, 14, 16, 28])
+    ext = rng.choice(div, size=(200, t.n_slots))
+    ext[0] = SF.CONV2D_README_EXTENTS
+    check(t, ext.tolist())
+
+
+def test_ragged_batch_and_errors():
+    t = SF.matmul_cpu_template(64, 64, 64)
+    sk = SF.SketchFeatures(t)
+    for n in (1, 31, 33, 64, 65, 1000):
+        e = torch.randint(1, 9, (n, 5), dtype=torch.int32, device="cuda")
+        rows = sk.rows(e)
+        assert rows.shape == (n * sk.n_rows, 164) and torch.isfinite(rows).all()
+        again = sk.rows(e[n // 2:n // 2 + 1])
+        assert torch.equal(again, rows[(n // 2) * sk.n_rows:(n // 2 + 1) * sk.n_rows])     # a row depends on its candidate only
+    assert sk.rows(torch.empty(0, 5, dtype=torch.int32, device="cuda")).shape == (0, 164)
+    with pytest.raises(ValueError):
+        sk.rows(torch.ones(4, 6, dtype=torch.int32, device="cuda"))
+    with pytest.raises(_lib.VaexError):
+        sk.rows(torch.ones(4, 5, dtype=torch.int32))
+    bad = sk.program.clone()
+    bad[0] = 7
+    out = torch.empty(4, 164, device="cuda")
+    with pytest.raises(_lib.VaexError, match="not a sketch program"):
+        _lib.check(_lib.load().vaex_sketch_features(_lib.ptr(bad), bad.numel(), _lib.ptr(torch.ones(4, 5, dtype=torch.int32, device="cuda")),
+                                                   4, _lib.ptr(out), _lib.stream_ptr()))

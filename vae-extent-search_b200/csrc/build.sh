@@ -7,7 +7,7 @@ NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 FLAGS="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC"
 mkdir -p build
 pids=()
-for f in abi simt_kernels elementwise topk segsum_tc head_tc chain_tc chain_tc3 chain_mc3 reshead3 train feature_blob kcenter extent_text ascent_cluster ascent_compose collective; do
+for f in abi simt_kernels elementwise topk segsum_tc head_tc chain_tc chain_tc3 chain_mc3 reshead3 train feature_blob kcenter sketch_features extent_text ascent_cluster ascent_compose collective; do
   if [ ! -f build/$f.o ] || [ $f.cu -nt build/$f.o ] || [ -n "$(find . -maxdepth 1 \( -name '*.cuh' -o -name '*.inc' \) -newer build/$f.o)" ] || [ ../../include/vaex_b200.h -nt build/$f.o ]; then
     $NVCC $FLAGS ${VAEX_PTXAS_V:+-Xptxas -v} -c $f.cu -o build/$f.o &
     pids+=($!)

@@ -1,0 +1,445 @@
+"""Per-statement feature rows of a FIXED sketch as a function of its loop extents.
+
+The reference gets the 164 features of every BufferStore by lowering each candidate with TVM on the CPU
+(GetPerStoreFeaturesWorkerFunc, src/auto_scheduler/feature.cc:1296-1368) and walking the TIR with
+PerStoreFeatureExtractor (:609-1048).  Within one sketch the candidates of the extent search differ only in their
+tile extents: the loop structure, the buffer accesses and the operation counts of every statement are the same.  A
+SketchTemplate states that structure once -- loops whose extents are products / quotients of entries of the extent
+vector, buffer accesses as index expressions over the loop variables, operation counts per statement -- and
+`compile()` flattens it into an int32 program that the CUDA kernel `vaex_sketch_features` (csrc/sketch_features.cu)
+evaluates for every candidate: the extractor's walk (touched regions per loop level, reuse type / distance, strides,
+the arithmetic-intensity curve, allocation and outer-scope features) with the candidate's extents substituted, one
+164-d row per stored buffer written straight into the row matrix the SegmentSum-MLP scores.  Extents go in (4 bytes
+each); no feature row crosses PCIe.
+
+A template is data, not code: `as_dict()` is the form the test oracle (oracle/perstore_features.py) walks with the
+reference's algorithm; parity tests compare the two on random extents.  What a template cannot certify is that it equals
+the loop nest TVM's lowering would emit for the sketch -- TVM is not built here.
+"""
+import contextlib
+
+import numpy as np
+import torch
+
+from . import _lib
+
+ROW = 164
+KINDS = {"for": 0, "vectorize": 1, "unroll": 2, "parallel": 3}
+THREADS = ["blockIdx.x", "blockIdx.y", "blockIdx.z", "threadIdx.x", "threadIdx.y", "threadIdx.z", "vthread"]
+OPS = ["float_mad", "float_addsub", "float_mul", "float_divmod", "float_cmp", "float_math_func", "float_other_func",
+       "int_mad", "int_addsub", "int_mul", "int_divmod", "int_cmp", "int_math_func", "int_other_func", "bool_op",
+       "select_op"]
+K_READ, K_WRITE, K_READWRITE, K_UNKNOWN = 0, 1, 2, 3
+# device program limits (csrc/sketch_features.cu)
+MAX_SLOTS, MAX_SCALARS, MAX_LOOPS, MAX_BUFS, MAX_DEPTH, MAX_DIMS, MAX_TOKENS, SCALAR_SLOTS, MAX_ACC, MAX_EXPR, MAX_PROG = \
+    64, 64, 32, 6, 24, 4, 32, 8, 5, 40, 4096
+OP_FOR, OP_FOR_END, OP_THREAD, OP_THREAD_END, OP_PRAGMA, OP_PRAGMA_END, OP_REALIZE_END, OP_STORE = range(8)
+T_VAR, T_CONST, T_ADD, T_MUL, T_DIV, T_MOD = range(6)
+MAGIC = 0x56465831
+
+
+def V(loop):
+    """the loop variable of a loop / thread node"""
+    return ("v", loop)
+
+
+def C(scalar):
+    return ("c", scalar)
+
+
+def add(a, b):
+    return ("+", a, b)
+
+
+def mul(a, b):
+    return ("*", a, b)
+
+
+def floordiv(a, b):
+    return ("//", a, b)
+
+
+def floormod(a, b):
+    return ("%", a, b)
+
+
+def _expr_key(e):
+    if e[0] == "v":
+        return ("v", id(e[1]))
+    if e[0] == "c":
+        return e
+    return (e[0], _expr_key(e[1]), _expr_key(e[2]))
+
+
+class SketchTemplate:
+    def __init__(self, n_slots):
+        if not 0 < n_slots <= MAX_SLOTS:
+            raise ValueError("1..%d extent slots" % MAX_SLOTS)
+        self.n_slots = n_slots
+        self.scalars, self._scalar_ix = [], {}
+        self.buffers = []
+        self.body = []
+        self._open = [self.body]
+
+    # ---- scalars: const * prod(extents[mul]) // prod(extents[div]) + add ----
+    def scalar(self, const=1, mul=(), div=(), add=0):
+        key = (int(const), tuple(sorted(mul)), tuple(sorted(div)), int(add))
+        if any(not 0 <= s < self.n_slots for s in key[1] + key[2]):
+            raise ValueError("slot out of range")
+        if len(key[1]) + len(key[2]) > SCALAR_SLOTS:
+            raise ValueError("a scalar multiplies / divides at most %d slots" % SCALAR_SLOTS)
+        if key not in self._scalar_ix:
+            self._scalar_ix[key] = len(self.scalars)
+            self.scalars.append(key)
+        return self._scalar_ix[key]
+
+    def slot(self, j):
+        return self.scalar(1, (j,))
+
+    def const(self, v):
+        return self.scalar(v)
+
+    def buffer(self, name, shape, nbytes=4):
+        if len(shape) > MAX_DIMS:
+            raise ValueError("at most %d dimensions" % MAX_DIMS)
+        self.buffers.append({"name": name, "shape": [int(x) for x in shape], "bytes": int(nbytes)})
+        return len(self.buffers) - 1
+
+    # ---- structure ----
+    @contextlib.contextmanager
+    def _scope(self, node):
+        node["body"] = []
+        self._open[-1].append(node)
+        self._open.append(node["body"])
+        try:
+            yield node
+        finally:
+            self._open.pop()
+
+    def loop(self, name, extent, kind="for"):
+        """a For loop; extent = scalar id.  Loops whose extent evaluates to 1 vanish for that candidate (ScheduleOps drops
+        trivial loops), their variable reads as 0."""
+        if kind not in KINDS:
+            raise ValueError(kind)
+        return self._scope({"kind": kind, "name": name, "extent": extent})
+
+    @contextlib.contextmanager
+    def loops(self, *specs):
+        """a perfect nest, outermost first: specs = (name, extent) or (name, extent, kind); yields the loop nodes"""
+        with contextlib.ExitStack() as es:
+            yield [es.enter_context(self.loop(*sp)) for sp in specs]
+
+    def thread(self, name, extent):
+        """AttrStmt thread_extent (blockIdx.* / threadIdx.*) or virtual_thread ("vthread")"""
+        if name not in THREADS:
+            raise ValueError(name)
+        return self._scope({"kind": "thread", "name": name, "extent": extent})
+
+    def pragma_unroll(self, value):
+        """AttrStmt pragma_auto_unroll_max_step; value = scalar id"""
+        return self._scope({"kind": "pragma_unroll", "value": value})
+
+    def realize(self, buffer, bounds):
+        """BufferRealize of a non-output stage at its attach point; bounds = scalar ids of the realised extents"""
+        return self._scope({"kind": "realize", "buffer": buffer, "bounds": list(bounds)})
+
+    def store(self, buffer, indices, reads=(), ops=None):
+        """BufferStore buffer[indices] = f(reads); reads = [(buffer, indices), ...] in expression order; ops = counts of
+        MathOpCounter (feature.cc:246-339) by name"""
+        ops = dict(ops or {})
+        if set(ops) - set(OPS):
+            raise ValueError("unknown op counters %r" % (set(ops) - set(OPS)))
+        self._open[-1].append({"kind": "store", "buffer": buffer, "indices": list(indices),
+                               "reads": [(b, list(ix)) for b, ix in reads], "ops": ops})
+
+    def as_dict(self):
+        return {"slots": self.n_slots, "scalars": [(c, list(m), list(d), a) for c, m, d, a in self.scalars],
+                "buffers": self.buffers, "body": self.body}
+
+    # ---- device program ----
+    def stored_buffers(self):
+        order = []
+
+        def walk(nodes):
+            for n in nodes:
+                if n["kind"] == "store":
+                    if n["buffer"] not in order:
+                        order.append(n["buffer"])
+                elif "body" in n:
+                    walk(n["body"])
+        walk(self.body)
+        return order
+
+    @property
+    def n_rows(self):
+        return len(self.stored_buffers())
+
+    def compile(self):
+        """int32 program for vaex_sketch_features (layout: csrc/sketch_features.cu)"""
+        if len(self.scalars) > MAX_SCALARS or len(self.buffers) > MAX_BUFS:
+            raise ValueError("too many scalars / buffers for the device program")
+        rows = self.stored_buffers()
+        loop_id = {}
+        instr, stores, exprs = [], [], []
+
+        def expr_tokens(e, out):
+            k = e[0]
+            if k == "v":
+                out.append(T_VAR | (loop_id[id(e[1])] << 4))
+            elif k == "c":
+                out.append(T_CONST | (e[1] << 4))
+            else:
+                expr_tokens(e[1], out)
+                expr_tokens(e[2], out)
+                t = {"+": T_ADD, "*": T_MUL, "//": T_DIV, "%": T_MOD}[k]
+                imm = 0                                   # Mul: which operand is an immediate leaf (1 = left, 2 = right)
+                if k == "*":
+                    imm = 1 if e[1][0] == "c" else 2 if e[2][0] == "c" else 0
+                out.append(t | (imm << 4))
+
+        expr_cache = {}
+
+        def expr(e):
+            key = repr(_expr_key(e))
+            if key in expr_cache:
+                return expr_cache[key]
+            toks = []
+            expr_tokens(e, toks)
+            if len(toks) > MAX_TOKENS:
+                raise ValueError("index expression longer than %d tokens" % MAX_TOKENS)
+            off = expr_cache[key] = len(exprs)
+            exprs.extend([len(toks)] + toks)
+            return off
+
+        def emit_store(n):
+            acc = {n["buffer"]: [K_WRITE, [n["indices"]]]}            # BufferAccessExtractor, feature.cc:342-379
+            for b, ix in n["reads"]:
+                a = acc.setdefault(b, [K_UNKNOWN, []])
+                if a[0] == K_WRITE:
+                    a[0] = K_READWRITE
+                elif a[0] == K_UNKNOWN:
+                    a[0] = K_READ
+                if a[0] != K_READWRITE:
+                    a[1].append(ix)
+            if len(acc) > MAX_ACC or sum(len(t) * len(self.buffers[b]["shape"]) for b, (_, t) in acc.items()) > MAX_EXPR:
+                raise ValueError("a statement touches at most %d buffers / %d index expressions" % (MAX_ACC, MAX_EXPR))
+            off = len(stores)
+            stores.extend([n["buffer"], len(acc)] + [int(n["ops"].get(k, 0)) for k in OPS])
+            for b, (acc_type, tuples) in acc.items():
+                nd = len(self.buffers[b]["shape"])
+                if any(len(ix) != nd for ix in tuples) or len(tuples) > 4:
+                    raise ValueError("access to %s: %d-d indices expected, at most 4 distinct reads" % (self.buffers[b]["name"], nd))
+                stores.extend([b, acc_type, len(tuples), nd])
+                for ix in tuples:
+                    stores.extend(expr(e) for e in ix)
+            loads = [expr(e) for _, ix in n["reads"] for e in ix]          # every BufferLoad's indices: their arithmetic
+            stores.extend([len(loads)] + loads)                            # counts as int ops (MathOpCounter)
+            return off
+
+        def walk(nodes, depth=0):
+            for n in nodes:
+                k = n["kind"]
+                if k in KINDS or k == "thread":
+                    # a loop's id is its nesting depth: unique among the loops that enclose a statement, which is all an
+                    # index expression can name (ids are bits of a 32-bit mask on the device)
+                    lid = loop_id[id(n)] = depth
+                    if k == "thread":
+                        instr.append((OP_THREAD, lid, n["extent"], THREADS.index(n["name"])))
+                        walk(n["body"], depth + 1)
+                        instr.append((OP_THREAD_END, lid, 0, THREADS.index(n["name"])))
+                    else:
+                        instr.append((OP_FOR, lid, n["extent"], KINDS[k]))
+                        walk(n["body"], depth + 1)
+                        instr.append((OP_FOR_END, lid, 0, KINDS[k]))
+                elif k == "pragma_unroll":
+                    instr.append((OP_PRAGMA, 0, n["value"], 0))
+                    walk(n["body"], depth)
+                    instr.append((OP_PRAGMA_END, 0, 0, 0))
+                elif k == "realize":
+                    walk(n["body"], depth)
+                    if len(n["bounds"]) > MAX_DIMS:
+                        raise ValueError("realize bounds")
+                    off = len(stores)
+                    stores.extend([len(n["bounds"])] + list(n["bounds"]))
+                    instr.append((OP_REALIZE_END, n["buffer"], off, 0))
+                else:
+                    instr.append([OP_STORE, emit_store(n), 0, n["buffer"]])
+
+        def depth_of(nodes):
+            return max([0] + [(1 if n["kind"] in KINDS or n["kind"] == "thread" else 0) + depth_of(n["body"])
+                              for n in nodes if "body" in n])
+
+        if depth_of(self.body) > MAX_DEPTH:
+            raise ValueError("loops nested deeper than %d" % MAX_DEPTH)
+        walk(self.body)
+        seen = set()
+        for ins in reversed(instr):                       # the features a buffer keeps are those of its LAST store
+            if ins[0] == OP_STORE:
+                if ins[3] not in seen:
+                    seen.add(ins[3])
+                    ins[2] = 1
+                ins[3] = 0
+        sc = []
+        for c, m, d, a in self.scalars:
+            if not (-2 ** 31 <= c < 2 ** 31 and -2 ** 31 <= a < 2 ** 31):
+                raise ValueError("scalar constant out of int32 range")
+            sc.extend([c, len(m), len(d), a] + list(m) + list(d) + [0] * (SCALAR_SLOTS - len(m) - len(d)))
+        bf = []
+        for i, b in enumerate(self.buffers):
+            bf.extend([b["bytes"], len(b["shape"])] + b["shape"] + [1] * (MAX_DIMS - len(b["shape"])) + [rows.index(i) if i in rows else -1])
+        head = 12
+        off_sc = head
+        off_bf = off_sc + len(sc)
+        off_in = off_bf + len(bf)
+        off_st = off_in + 4 * len(instr)
+        off_ex = off_st + len(stores)
+        total = off_ex + len(exprs)
+        prog = [MAGIC, self.n_slots, len(self.scalars), len(self.buffers), len(loop_id), len(rows), len(instr), off_sc, off_bf,
+                off_in, off_st, off_ex]
+        prog[4] = MAX_DEPTH
+        prog += sc + bf + [w for ins in instr for w in ins] + stores + exprs
+        assert len(prog) == total
+        if total > MAX_PROG:
+            raise ValueError("sketch program of %d words (limit %d)" % (total, MAX_PROG))
+        return np.asarray(prog, dtype=np.int32)
+
+
+class SketchFeatures:
+    """A compiled template resident on the device.  rows(extents) -> float32 [n * n_rows, 164] in candidate-major order
+    (candidate i owns rows [i * n_rows, (i + 1) * n_rows)), i.e. a SegmentSum-MLP batch with every segment n_rows long."""
+
+    def __init__(self, template, device="cuda"):
+        self.template = template
+        self.n_rows, self.n_slots = template.n_rows, template.n_slots
+        self.program = torch.from_numpy(template.compile()).to(device)
+
+    def rows(self, extents, out=None):
+        e = extents
+        if not e.is_cuda:
+            raise _lib.VaexError("vaex_b200 needs CUDA tensors (no CPU fallback)")
+        _lib.check_device(e)
+        e = e.to(torch.int32).contiguous()
+        if e.dim() != 2 or e.shape[1] != self.n_slots:
+            raise ValueError("extents must be [n, %d]" % self.n_slots)
+        n = e.shape[0]
+        if out is None:
+            out = torch.empty(n * self.n_rows, ROW, device=e.device)
+        _lib.check(_lib.load().vaex_sketch_features(_lib.ptr(self.program), self.program.numel(), _lib.ptr(e), n, _lib.ptr(out),
+                                                   _lib.stream_ptr()))
+        return out
+
+    def segment_sizes(self, n, device="cuda"):
+        return torch.full((n,), self.n_rows, dtype=torch.int32, device=device)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# templates
+# ---------------------------------------------------------------------------------------------------------------
+def tiled(t, parts):
+    """index of an axis split into loops `parts` = [(loop, inner_scalar_or_None), ...] outermost first:
+    ((p0 * c0) + (p1 * c1)) + p_last  -- the sum a split chain lowers to (outer * factor + inner, distributed)"""
+    e = None
+    for lp, c in parts:
+        term = V(lp) if c is None else mul(V(lp), C(c))
+        e = term if e is None else add(e, term)
+    return e
+
+
+def matmul_cpu_template(N, M, K):
+    """C[i, j] = sum_k A[i, k] * B[k, j] under the schedule of the reference's feature test
+    (tests/python/unittest/test_auto_scheduler_feature.py:31-75): i -> (i.0, i.1), j -> (j.0, j.1), order
+    (i.0, j.0, k, j.1, i.1), i.0 / j.0 parallel, k unrolled, j.1 vectorised.  Extent vector: [i.0, j.0, k, j.1, i.1]
+    (walk order of the printed state).  The reduction's init statement sits in front of the k loop with its own copies
+    of the inner spatial loops (te::MakeReduction)."""
+    t = SketchTemplate(5)
+    A, B, Cb = t.buffer("A", (N, K)), t.buffer("B", (K, M)), t.buffer("C", (N, M))
+    e_i0, e_j0, e_k, e_j1, e_i1 = (t.slot(j) for j in range(5))
+    with t.loop("i.0", e_i0, "parallel") as i0:
+        with t.loop("j.0", e_j0, "parallel") as j0:
+            with t.loop("j.1.init", e_j1, "vectorize") as j1i:
+                with t.loop("i.1.init", e_i1) as i1i:
+                    t.store(Cb, [tiled(t, [(i0, e_i1), (i1i, None)]), tiled(t, [(j0, e_j1), (j1i, None)])])
+            with t.loop("k", e_k, "unroll") as k:
+                with t.loop("j.1", e_j1, "vectorize") as j1:
+                    with t.loop("i.1", e_i1) as i1:
+                        ci, cj = tiled(t, [(i0, e_i1), (i1, None)]), tiled(t, [(j0, e_j1), (j1, None)])
+                        t.store(Cb, [ci, cj], reads=[(Cb, [ci, cj]), (A, [ci, V(k)]), (B, [V(k), cj])],
+                                ops={"float_addsub": 1, "float_mul": 1})
+    return t
+
+
+def lin(terms):
+    """((t0 * c0) + (t1 * c1)) + ... : terms = [(expr, coefficient scalar or None)], outermost first"""
+    e = None
+    for x, c in terms:
+        term = x if c is None else mul(x, C(c))
+        e = term if e is None else add(e, term)
+    return e
+
+
+# slots of conv2d_nhwc_cpu_template: four tile levels of every spatial axis, two of every reduction axis, the unroll pragma
+CONV2D_SLOTS = {"n": (0, 1, 2, 3), "y": (4, 5, 6, 7), "x": (8, 9, 10, 11), "f": (12, 13, 14, 15), "ry": (16, 17), "rx": (18, 19),
+                "rc": (20, 21), "unroll": 22}
+# the schedule printed in the reference README (:86-108): 1 x 56 x 56 x 64 -> 1 x 28 x 28 x 128, 3 x 3, stride 2
+CONV2D_README_EXTENTS = [1, 1, 1, 1, 1, 1, 1, 28, 4, 7, 1, 1, 2, 8, 1, 8, 1, 3, 3, 1, 4, 16, 16]
+
+
+def conv2d_nhwc_cpu_template(N=1, H=56, W=56, CI=64, CO=128, KH=3, KW=3, stride=2, pad_after=1):
+    """conv2d NHWC + bias + ReLU under Ansor's CPU multi-level tiling sketch ("SSRSRS" with the consumer fused at the second
+    tile level, the padding stage computed at the fused outer loop, the outer spatial tiles fused and parallelised, the
+    innermost channel tile vectorised): the structure of the program the reference README prints (:86-108; PaddedInput /
+    Conv2dOutput / T_relu; its loop extents are CONV2D_README_EXTENTS here).  Extent vector (23 slots, CONV2D_SLOTS): the
+    tile factors n, y, x, f (4 levels each, outermost first), ry, rx, rc (2 levels each) and auto_unroll_max_step.  Three
+    statement rows per candidate."""
+    OH, OW = (H + pad_after - KH) // stride + 1, (W + pad_after - KW) // stride + 1
+    t = SketchTemplate(23)
+    data, kernel, bias = t.buffer("placeholder", (N, H, W, CI)), t.buffer("placeholder", (KH, KW, CI, CO)), t.buffer("placeholder", (1, 1, 1, CO))
+    Pad, Conv, Relu = (t.buffer("PaddedInput", (N, H + pad_after, W + pad_after, CI)), t.buffer("Conv2dOutput", (N, OH, OW, CO)),
+                       t.buffer("T_relu", (N, OH, OW, CO)))
+    sl = CONV2D_SLOTS
+    S = lambda *slots, const=1, add=0: t.scalar(const, tuple(slots), (), add)
+    n, y, x, f, ry, rx, rc = (sl[k] for k in ("n", "y", "x", "f", "ry", "rx", "rc"))
+    zero = t.const(0)
+    with t.loop("ax0.0@ax1.0@ax2.0@", S(n[0], y[0], x[0]), "parallel") as p:
+        n0 = floordiv(V(p), C(S(y[0], x[0])))
+        y0 = floormod(floordiv(V(p), C(S(x[0]))), C(S(y[0])))
+        x0 = floormod(V(p), C(S(x[0])))
+        rows, cols = S(*y[1:], const=stride, add=KH - stride), S(*x[1:], const=stride, add=KW - stride)
+        with t.realize(Pad, [S(*n[1:]), rows, cols, t.const(CI)]):
+            with t.loops(("i0", S(*n[1:])), ("i1", rows), ("i2", cols), ("i3", t.const(CI))) as (i0, i1, i2, i3):
+                ix = [lin([(n0, S(*n[1:])), (V(i0), None)]), lin([(y0, S(*y[1:], const=stride)), (V(i1), None)]),
+                      lin([(x0, S(*x[1:], const=stride)), (V(i2), None)]), V(i3)]
+                t.store(Pad, ix, reads=[(data, ix)], ops={"float_math_func": 1, "int_cmp": 2, "bool_op": 1})
+        with t.loops(("ax3.0", S(f[0])), ("ax0.1", S(n[1])), ("ax1.1", S(y[1])), ("ax2.1", S(x[1])), ("ax3.1", S(f[1]))) as (f0, n1, y1, x1, f1):
+            outer = lambda ax, v0, v1: [(v0, S(*ax[1:])), (V(v1), S(*ax[2:]))]
+            fo = [(V(f0), S(*f[1:])), (V(f1), S(*f[2:]))]
+            with t.realize(Conv, [S(*n[2:]), S(*y[2:]), S(*x[2:]), S(*f[2:])]):
+                with t.pragma_unroll(S(sl["unroll"])):
+                    with t.loops(("nn.2.init", S(n[2])), ("yy.2.init", S(y[2])), ("xx.2.init", S(x[2])), ("ff.2.init", S(f[2])),
+                                 ("nn.3.init", S(n[3])), ("yy.3.init", S(y[3])), ("xx.3.init", S(x[3])),
+                                 ("ff.3.init", S(f[3]), "vectorize")) as (a2, b2, c2, d2, a3, b3, c3, d3):
+                        t.store(Conv, [lin(outer(n, n0, n1) + [(V(a2), S(n[3])), (V(a3), None)]),
+                                       lin(outer(y, y0, y1) + [(V(b2), S(y[3])), (V(b3), None)]),
+                                       lin(outer(x, x0, x1) + [(V(c2), S(x[3])), (V(c3), None)]),
+                                       lin(fo + [(V(d2), S(f[3])), (V(d3), None)])])
+                    with t.loops(("ry.0", S(ry[0])), ("rx.0", S(rx[0])), ("rc.0", S(rc[0])), ("nn.2", S(n[2])), ("yy.2", S(y[2])),
+                                 ("xx.2", S(x[2])), ("ff.2", S(f[2])), ("ry.1", S(ry[1])), ("rx.1", S(rx[1])), ("rc.1", S(rc[1])),
+                                 ("nn.3", S(n[3])), ("yy.3", S(y[3])), ("xx.3", S(x[3])), ("ff.3", S(f[3]), "vectorize")) as \
+                            (r0, s0, q0, a2, b2, c2, d2, r1, s1, q1, a3, b3, c3, d3):
+                        nn = lin(outer(n, n0, n1) + [(V(a2), S(n[3])), (V(a3), None)])
+                        yy = lin(outer(y, y0, y1) + [(V(b2), S(y[3])), (V(b3), None)])
+                        xx = lin(outer(x, x0, x1) + [(V(c2), S(x[3])), (V(c3), None)])
+                        ff = lin(fo + [(V(d2), S(f[3])), (V(d3), None)])
+                        kr, ks, kq = (lin([(V(r0), S(ry[1])), (V(r1), None)]), lin([(V(s0), S(rx[1])), (V(s1), None)]),
+                                      lin([(V(q0), S(rc[1])), (V(q1), None)]))
+                        py = lin([(y0, S(*y[1:], const=stride)), (V(y1), S(*y[2:], const=stride)), (V(b2), S(y[3], const=stride)),
+                                  (V(b3), t.const(stride)), (V(r0), S(ry[1])), (V(r1), None)])
+                        px = lin([(x0, S(*x[1:], const=stride)), (V(x1), S(*x[2:], const=stride)), (V(c2), S(x[3], const=stride)),
+                                  (V(c3), t.const(stride)), (V(s0), S(rx[1])), (V(s1), None)])
+                        t.store(Conv, [nn, yy, xx, ff], reads=[(Conv, [nn, yy, xx, ff]), (Pad, [nn, py, px, kq]), (kernel, [kr, ks, kq, ff])],
+                                ops={"float_addsub": 1, "float_mul": 1})
+            with t.loops(("ax0.2", S(*n[2:])), ("ax1.2", S(*y[2:])), ("ax2.2", S(*x[2:])), ("ax3.2", S(*f[2:]), "vectorize")) as (a, b, c, d):
+                ix = [lin(outer(n, n0, n1) + [(V(a), None)]), lin(outer(y, y0, y1) + [(V(b), None)]), lin(outer(x, x0, x1) + [(V(c), None)]),
+                      lin(fo + [(V(d), None)])]
+                t.store(Relu, ix, reads=[(Conv, ix), (bias, [C(zero), C(zero), C(zero), ix[3]])], ops={"float_addsub": 1, "float_cmp": 1})
+    return t
