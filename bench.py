@@ -600,6 +600,46 @@ def main_vaex(args):
                                       "per restart; all steps of a restart in ONE cluster kernel" % (hi - lo),
                               "n_gpus": world, "graphs": res3}
 
+    # ---- the north-star chain with the features IMPLIED by the decoded extents: z -> decode + snap + legalise
+    # (the 23 tile extents of the conv2d sketch of the reference README) -> 3 statement rows per candidate evaluated from the
+    # sketch template on the device -> SegmentSum-MLP -> top-k -> merge.  Nothing but the merged top-k leaves the GPU.
+    if not args.no_configs:
+        from vaex_b200 import sketch_features as SF
+        n6 = 1 << 20
+        torch.manual_seed(2023)
+        vae6 = vaex_b200.VAE_feature_head(23, None, L_LAT, H).to(dev).eval()
+        rng6 = np.random.default_rng(2023)
+        se6, sl6 = SF.conv2d_slot_tables()
+        scorer = SF.SketchScorer(vae6, rng6.uniform(0.5, 3, 23).astype(np.float32), rng6.uniform(0.3, 1.5, 23).astype(np.float32),
+                                 SF.conv2d_nhwc_cpu_template(derive_outer=True), net, se6, sl6, fea_norm_vec=None)
+        z6 = gen_latents(n6, 6000 + rank, dev)
+        box6 = {}
+
+        def step6():
+            sc6, ext6 = scorer.score(z6)
+            box6["ext"] = ext6
+            _lib.check(lib.vaex_topk(_lib.ptr(sc6), n6, TOPK, None, _lib.ptr(top_v), _lib.ptr(top_i), _lib.ptr(n_out), st))
+            if world > 1:
+                _lib.check(lib.vaex_topk_allgather_merge(comm.h, _lib.ptr(top_v), _lib.ptr(top_i), _lib.ptr(n_out), TOPK, rank * n6,
+                                                         _lib.ptr(mer_v), _lib.ptr(mer_i), _lib.ptr(mer_n), st))
+        step6()
+        barrier()
+        ms6 = timed(step6, 5)
+        ms6_rows = timed(lambda: scorer.features.rows(box6["ext"], out=scorer._buffers(n6, dev)[1]), 5)
+        t6 = torch.tensor([ms6, ms6_rows], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t6, op=dist.ReduceOp.MAX)
+        ms6, ms6_rows = float(t6[0].item()), float(t6[1].item())
+        R6 = scorer.features.n_rows
+        configs["sketch_pipeline"] = {
+            "what": "per rank 2^20 latents -> decode + snap + legalise (23 tile extents, conv2d sketch) -> %d feature rows per candidate "
+                    "from the sketch template (vaex_sketch_features) -> SegmentSum-MLP -> top-%d -> merge; device-resident" % (R6, TOPK),
+            "latents_per_gpu": n6, "n_gpus": world, "ms_per_step": ms6, "candidates_per_s": world * n6 / (ms6 * 1e-3),
+            "ms_feature_rows": ms6_rows, "feature_rows_GBps_written": n6 * R6 * F * 4 / (ms6_rows * 1e-3) / 1e9,
+            "note": "the feature kernel interprets the template per candidate (about 1e5 instructions each): instruction-bound, "
+                    "not HBM-bound; template fidelity to TVM's lowering is unpinned (DESIGN section 2)"}
+        del z6
+
     # ---- config 4: data-parallel training of the SegmentSumMLP on records resident in HBM (mlp_model.py:512-600) ----
     if not args.no_configs:
         from vaex_b200 import train as vtrain

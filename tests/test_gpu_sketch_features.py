@@ -72,3 +72,39 @@ def test_ragged_batch_and_errors():
     with pytest.raises(_lib.VaexError, match="not a sketch program"):
         _lib.check(_lib.load().vaex_sketch_features(_lib.ptr(bad), bad.numel(), _lib.ptr(torch.ones(4, 5, dtype=torch.int32, device="cuda")),
                                                    4, _lib.ptr(out), _lib.stream_ptr()))
+
+
+def test_sketch_scorer_pipeline():
+    """z -> decode + snap + legalise -> feature rows -> SegmentSum-MLP, device-resident: the extents are legal tile factors of
+    the conv2d task, the rows are the oracle's for those extents, and the scores are the cost model's on those rows (the
+    reference order of operations: decode, lower + extract on the CPU, MLPModel.predict)."""
+    import vaex_b200
+    from oracle import torch_oracle as O
+    torch.manual_seed(5)
+    t = SF.conv2d_nhwc_cpu_template(derive_outer=True)
+    se, sl = SF.conv2d_slot_tables()
+    vae = vaex_b200.VAE_feature_head(23, None, 64, 256).cuda().eval()
+    net = vaex_b200.SegmentSumMLPModule(164, 256, 1).cuda().eval()
+    rng = np.random.default_rng(5)
+    mean, scale = rng.uniform(0.5, 3, 23).astype(np.float32), rng.uniform(0.3, 1.5, 23).astype(np.float32)
+    sc = SF.SketchScorer(vae, mean, scale, t, net, se, sl)
+    n = 777
+    z = torch.randn(n, 64, device="cuda")
+    scores, ext = sc.score(z)
+    e = ext.cpu().numpy()
+    assert e.shape == (n, 23) and (e >= 1).all()
+    for key, E in (("y", 28), ("x", 28), ("f", 128), ("ry", 3), ("rx", 3), ("rc", 64)):
+        inner = e[:, list(SF.CONV2D_SLOTS[key][1:])].astype(np.int64).prod(1)
+        assert (E % inner == 0).all(), key                                   # SplitStep lengths multiply to a divisor of the axis
+    td = t.as_dict()
+    pick = rng.choice(n, 40, replace=False)
+    rows = sc.features.rows(ext).cpu().numpy().reshape(n, 3, 164)
+    for i in pick:
+        want, _ = PF.evaluate(td, e[i].tolist())
+        assert np.abs(rows[i] - want).max() < 2e-6 * max(1.0, np.abs(want).max())
+    P = {k: v.detach().cpu() for k, v in net.state_dict().items()}
+    want = O.segsum_mlp_forward(P, np.full(n, 3, np.int32), torch.from_numpy(rows.reshape(-1, 164))).numpy()
+    got = scores.cpu().numpy()
+    assert np.linalg.norm(got - want) / np.linalg.norm(want) < 1e-3
+    again, _ = sc.score(z)
+    assert torch.equal(again, scores)

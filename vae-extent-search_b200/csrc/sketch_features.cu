@@ -13,24 +13,25 @@
 // Program layout (int32 words):
 //   [0] magic  [1] slots  [2] scalars  [3] buffers  [4] loops  [5] rows  [6] instructions
 //   [7] scalar table  [8] buffer table  [9] instruction table  [10] store table  [11] expression pool   (word offsets)
-//   scalar: const, n_mul, n_div, add, slot[8]          value = const * prod(extents[mul]) / prod(extents[div]) + add
+//   scalar: const, n_mul, n_div, add, slot[12]         value = const * prod(extents[mul]) / prod(extents[div]) + add
 //   buffer: bytes, ndim, shape[4], row (-1: never stored)
 //   instruction: op, a, b, c                            FOR(loop, scalar, kind) FOR_END THREAD(loop, scalar, which) THREAD_END
 //                                                       PRAGMA(-, scalar) PRAGMA_END REALIZE_END(buffer, aux) STORE(store)
 //   store: buffer, n_access, ops[16], then per access: buffer, acc_type, n_tuples, ndim, expression offset[n_tuples * ndim],
 //          then n_loads, expression offset[n_loads] (the indices of every BufferLoad: their arithmetic counts as int ops)
-//   expression: n_tokens, token[n]; token = kind | arg << 4: VAR(loop) CONST(scalar) ADD MUL(which operand is a leaf) DIV MOD
+//   expression: n_tokens, ADD mask, MUL mask, DIV|MOD mask (a bit per token), token[n]; token = kind | arg << 4: VAR(loop) CONST(scalar) ADD MUL(which operand is a leaf) DIV MOD
 //
 // Each warp stages its 32 rows in shared memory and writes them out as contiguous 656-byte rows (coalesced).
 #include <cstdint>
+#include <cstdlib>
 
 #include "../../include/vaex_b200.h"
 #include "common.cuh"
 
 namespace vaex {
 namespace sf {
-constexpr int MAX_SLOTS = 64, MAX_SCALARS = 64, MAX_LOOPS = 32, MAX_BUFS = 6, MAX_DIMS = 4, SCALAR_SLOTS = 8;       // an expression has at most 32 tokens
-constexpr int MAX_DEPTH = 24, MAX_ACC = 5, MAX_EXPR = 40, ROW = 164, ROW_PAD = 165, WARPS = 2, THREADS = 32 * WARPS;
+constexpr int MAX_SLOTS = 64, MAX_SCALARS = 48, MAX_LOOPS = 32, MAX_BUFS = 6, MAX_DIMS = 4, SCALAR_SLOTS = 12;       // an expression has at most 32 tokens
+constexpr int MAX_DEPTH = 24, MAX_ACC = 5, MAX_EXPR = 40, ROW = 164, WARPS = 2, THREADS = 32 * WARPS;
 constexpr int MAX_PROG = 4096;                            // words of program kept in shared memory
 constexpr int MAGIC = 0x56465831;
 enum { OP_FOR, OP_FOR_END, OP_THREAD, OP_THREAD_END, OP_PRAGMA, OP_PRAGMA_END, OP_REALIZE_END, OP_STORE };
@@ -49,8 +50,8 @@ struct Walk {
   // for_touch_regions_ of the loops on the stack, as the aggregates the walk reads (:1028)
   uint8_t cnt[MAX_DEPTH][MAX_BUFS];                       // accesses recorded for (loop, buffer)
   float min_sz[MAX_DEPTH][MAX_BUFS];                      // smallest touched size among them
-  double first_sz[MAX_DEPTH][MAX_BUFS];                   // touched size of the first one
-  double sum_all[MAX_DEPTH], sum_b1[MAX_DEPTH], sum_read[MAX_DEPTH];   // sum size * bytes; sum bytes; the same over reads
+  double first_sz[MAX_BUFS];                              // touched size of the first one, outermost loop only (:863)
+  float sum_all[MAX_DEPTH], sum_b1[MAX_DEPTH], sum_read[MAX_DEPTH];    // sum size * bytes; sum bytes; the first over reads
   float row_prod[MAX_BUFS][3];                            // vec / unroll / parallel _prod persist across stores of a buffer
   float row_outer[MAX_BUFS];
   float alloc[MAX_BUFS][4];
@@ -69,30 +70,41 @@ struct Prog {
   __device__ __forceinline__ const int32_t* expr(int off) const { return w + w[11] + off; }
 };
 
+// The expression stacks live in registers: four entries (the compiler checks that no index expression needs more), moved
+// by hand instead of indexed, so that no evaluation touches local memory.
+template <class T>
+struct Stack4 {
+  T s0, s1, s2, s3;                                       // s0 = top
+  __device__ __forceinline__ void push(const T& x) { s3 = s2; s2 = s1; s1 = s0; s0 = x; }
+  __device__ __forceinline__ void pop2(T& a, T& b) { b = s0; a = s1; s0 = s2; s1 = s3; }       // a was pushed before b
+};
+__device__ __forceinline__ int n_tokens(const int32_t* e) { return e[0]; }
+__device__ __forceinline__ int token(const int32_t* e, int i) { return e[4 + i]; }               // e[1..3]: ADD / MUL / DIV|MOD masks
+
 // Which tokens survive the folds of Simplify (a bit per token; the survivors are again a postfix expression, or none = 0)
 __device__ uint32_t simplify(const Prog& P, const Walk& W, const int32_t* e, uint32_t* var_mask) {
-  const int n = e[0];
+  const int n = n_tokens(e);
   uint32_t alive = n >= 32 ? 0xffffffffu : ((1u << n) - 1u);
-  struct Ent { int64_t fhi, val; int8_t start; bool zero, imm; };
-  Ent st[8];
-  int sp = 0;
-  auto kill = [&](int from, int to) { for (int i = from; i <= to; ++i) alive &= ~(1u << i); };
+  uint32_t vm = 0;
+  struct Ent { int64_t fhi, val; int start; bool zero, imm; };
+  Stack4<Ent> st;
+  auto kill = [&](int from, int to) { alive &= ~((0xffffffffu >> (31 - to)) & (0xffffffffu << from)); };
   for (int i = 0; i < n; ++i) {
-    const int tok = e[1 + i], k = tok & 15, arg = tok >> 4;
+    const int tok = token(e, i), k = tok & 15, arg = tok >> 4;
     if (k == T_VAR) {
-      Ent x; x.start = (int8_t)i; x.imm = false; x.val = 0;
+      Ent x; x.start = i; x.imm = false; x.val = 0;
       if (W.pos[arg] < 0) { x.zero = true; x.fhi = 0; kill(i, i); }
-      else { x.zero = false; x.fhi = W.ext[arg] - 1; }
-      st[sp++] = x;
+      else { x.zero = false; x.fhi = W.ext[arg] - 1; vm |= 1u << i; }
+      st.push(x);
     } else if (k == T_CONST) {
-      Ent x; x.start = (int8_t)i; x.val = W.S[arg]; x.fhi = x.val; x.zero = x.val == 0; x.imm = !x.zero;
+      Ent x; x.start = i; x.val = W.S[arg]; x.fhi = x.val; x.zero = x.val == 0; x.imm = !x.zero;
       if (x.zero) kill(i, i);
-      st[sp++] = x;
+      st.push(x);
     } else {
-      const Ent b = st[--sp], a = st[--sp];
+      Ent a, b;
+      st.pop2(a, b);
       Ent r; r.start = a.start; r.imm = false; r.val = 0; r.zero = false; r.fhi = 0;
-      const int b_end = i - 1;                            // b's tokens are [b.start, i - 1], a's [a.start, b.start - 1]
-      if (k == T_ADD) {
+      if (k == T_ADD) {                                   // b's tokens are [b.start, i - 1], a's [a.start, b.start - 1]
         if (a.zero && b.zero) { r.zero = true; kill(i, i); }
         else if (a.zero) { r = b; r.start = a.start; kill(i, i); }
         else if (b.zero) { r = a; kill(i, i); }
@@ -111,73 +123,132 @@ __device__ uint32_t simplify(const Prog& P, const Walk& W, const int32_t* e, uin
           if (k == T_DIV) { r.zero = true; kill(a.start, i); } else { r = a; kill(b.start, i); }
         } else r.fhi = k == T_DIV ? a.fhi / c : min(a.fhi, c - 1);
       }
-      (void)b_end;
-      st[sp++] = r;
+      st.push(r);
     }
   }
-  uint32_t vm = 0;
-  for (int i = 0; i < n; ++i)
-    if (((alive >> i) & 1u) && (e[1 + i] & 15) == T_VAR) vm |= 1u << (e[1 + i] >> 4);
-  *var_mask |= vm;
+  vm &= alive;                                            // variables inside a folded subtree are gone
+  uint32_t loops = 0;
+  while (vm) { const int i = __ffs(vm) - 1; vm &= vm - 1; loops |= 1u << (token(e, i) >> 4); }
+  *var_mask |= loops;
   return alive;
 }
 
 // const_int_bound of the surviving expression with loops at stack positions >= level over their range, the others at 0
 __device__ void bound(const Prog& P, const Walk& W, const int32_t* e, uint32_t alive, int level, int64_t* lo_out, int64_t* hi_out) {
-  int64_t lo[8], hi[8];
-  int sp = 0;
-  const int n = e[0];
+  struct Iv { int64_t lo, hi; };
+  Stack4<Iv> st;
+  st.s0 = Iv{0, 0};
+  const int n = n_tokens(e);
   for (int i = 0; i < n; ++i) {
     if (!((alive >> i) & 1u)) continue;
-    const int tok = e[1 + i], k = tok & 15, arg = tok >> 4;
-    if (k == T_VAR) { lo[sp] = 0; hi[sp] = W.pos[arg] >= level ? W.ext[arg] - 1 : 0; ++sp; }
-    else if (k == T_CONST) { lo[sp] = hi[sp] = W.S[arg]; ++sp; }
+    const int tok = token(e, i), k = tok & 15, arg = tok >> 4;
+    if (k == T_VAR) st.push(Iv{0, W.pos[arg] >= level ? (int64_t)W.ext[arg] - 1 : 0});
+    else if (k == T_CONST) st.push(Iv{W.S[arg], W.S[arg]});
     else {
-      --sp;
-      const int64_t bl = lo[sp], bh = hi[sp], al = lo[sp - 1], ah = hi[sp - 1];
-      int64_t rl, rh;
-      if (k == T_ADD) { rl = al + bl; rh = ah + bh; }
+      Iv a, b, r;
+      st.pop2(a, b);
+      if (k == T_ADD) { r.lo = a.lo + b.lo; r.hi = a.hi + b.hi; }
       else if (k == T_MUL) {
-        const int64_t c0 = al * bl, c1 = al * bh, c2 = ah * bl, c3 = ah * bh;
-        rl = min(min(c0, c1), min(c2, c3)); rh = max(max(c0, c1), max(c2, c3));
+        const int64_t c0 = a.lo * b.lo, c1 = a.lo * b.hi, c2 = a.hi * b.lo, c3 = a.hi * b.hi;
+        r.lo = min(min(c0, c1), min(c2, c3)); r.hi = max(max(c0, c1), max(c2, c3));
       } else if (k == T_DIV) {
         auto fd = [](int64_t x, int64_t c) { int64_t q = x / c; return (x % c != 0 && (x < 0)) ? q - 1 : q; };
-        rl = fd(al, bl); rh = fd(ah, bl);
+        r.lo = fd(a.lo, b.lo); r.hi = fd(a.hi, b.lo);
       } else {
-        if (al >= 0) { if (ah < bl) { rl = al; rh = ah; } else { rl = 0; rh = min(ah, bl - 1); } }
-        else { rl = 0; rh = bl - 1; }
+        if (a.lo >= 0) { if (a.hi < b.lo) r = a; else { r.lo = 0; r.hi = min(a.hi, b.lo - 1); } }
+        else { r.lo = 0; r.hi = b.lo - 1; }
       }
-      lo[sp - 1] = rl; hi[sp - 1] = rh;
+      st.push(r);
     }
   }
-  if (sp == 0) { *lo_out = 0; *hi_out = 0; } else { *lo_out = lo[0]; *hi_out = hi[0]; }
+  *lo_out = alive ? st.s0.lo : 0;
+  *hi_out = alive ? st.s0.hi : 0;
+}
+
+// The same bounds for ALL levels in one pass, when every term of the expression depends on one loop variable (sums of
+// var * c, floordiv / floormod chains of a single var, constants -- what a split / fuse lowers an index to): a term is
+// [zlo, zhi] while its variable is pinned at 0 and [lo, hi] once the variable's loop is bound, so
+//   lo(level) = sum zlo + sum over terms whose loop sits at position >= level of (lo - zlo),  likewise hi.
+// Interval arithmetic adds term by term, so this equals bound() at every level.  The per-position deltas are ADDED into
+// dlo / dhi (the caller clears them).  Returns false (caller falls back to bound() per level) for anything else: a
+// product of two variables, floordiv / floormod or a scale of a sum.
+__device__ bool bound_all_levels(const Prog& P, const Walk& W, const int32_t* e, uint32_t alive, int64_t* dlo, int64_t* dhi,
+                                 int64_t* base_lo, int64_t* base_hi) {
+  struct Ent { int64_t lo, hi, zlo, zhi; int pos; };     // pos: stack position of the term's variable, -1 constant, -2 flushed sum
+  Stack4<Ent> st;
+  st.s0 = Ent{0, 0, 0, 0, -1};
+  int64_t bl = 0, bh = 0;
+  auto flush = [&](const Ent& x) {
+    if (x.pos == -2) return;
+    bl += x.zlo; bh += x.zhi;
+    if (x.pos >= 0) { dlo[x.pos] += x.lo - x.zlo; dhi[x.pos] += x.hi - x.zhi; }
+  };
+  auto fd = [](int64_t x, int64_t c) { const int64_t q = x / c; return (x % c != 0 && x < 0) ? q - 1 : q; };
+  const int n = n_tokens(e);
+  for (int i = 0; i < n; ++i) {
+    if (!((alive >> i) & 1u)) continue;
+    const int tok = token(e, i), k = tok & 15, arg = tok >> 4;
+    if (k == T_VAR) { st.push(Ent{0, (int64_t)W.ext[arg] - 1, 0, 0, (int)W.pos[arg]}); continue; }
+    if (k == T_CONST) { const int64_t v = W.S[arg]; st.push(Ent{v, v, v, v, -1}); continue; }
+    Ent a, b, r;
+    st.pop2(a, b);
+    if (k == T_ADD) {
+      flush(a); flush(b);
+      r = Ent{0, 0, 0, 0, -2};
+    } else if (k == T_MUL) {
+      const bool ac = a.pos == -1, bc = b.pos == -1;
+      if (!(ac || bc)) return false;
+      const Ent x = ac ? b : a;
+      const int64_t c = ac ? a.lo : b.lo;
+      if (x.pos == -2) return false;
+      r = x;
+      r.lo = min(x.lo * c, x.hi * c); r.hi = max(x.lo * c, x.hi * c);
+      r.zlo = min(x.zlo * c, x.zhi * c); r.zhi = max(x.zlo * c, x.zhi * c);
+    } else {
+      if (a.pos == -2 || b.pos != -1) return false;
+      const int64_t c = b.lo;
+      r = a;
+      if (k == T_DIV) { r.lo = fd(a.lo, c); r.hi = fd(a.hi, c); r.zlo = fd(a.zlo, c); r.zhi = fd(a.zhi, c); }
+      else {
+        auto md = [c](int64_t l, int64_t h, int64_t* ol, int64_t* oh) {
+          if (l >= 0) { if (h < c) { *ol = l; *oh = h; } else { *ol = 0; *oh = min(h, c - 1); } }
+          else { *ol = 0; *oh = c - 1; }
+        };
+        md(a.lo, a.hi, &r.lo, &r.hi);
+        md(a.zlo, a.zhi, &r.zlo, &r.zhi);
+      }
+    }
+    st.push(r);
+  }
+  if (alive) flush(st.s0);
+  *base_lo = bl; *base_hi = bh;
+  return true;
 }
 
 // CoefficientExtractor::ExtractCoefficient (:382-443) on the surviving tokens; returns visited_var through *found
 __device__ int64_t coefficient(const Prog& P, const Walk& W, const int32_t* e, uint32_t alive, int loop, bool* found) {
   bool var = false, mul = false, add = false;
   int64_t stride = 0;
-  // whether an operand is an immediate leaf must be judged on the SURVIVING tree: remember what the last two operands were
-  bool leaf[8];
-  int64_t val[8];
-  int sp = 0;
-  const int n = e[0];
+  struct LV { int64_t val; bool leaf; };                  // whether an operand is an immediate leaf is judged on the SURVIVING tree
+  Stack4<LV> st;
+  const int n = n_tokens(e);
   for (int i = 0; i < n; ++i) {
     if (!((alive >> i) & 1u)) continue;
-    const int tok = e[1 + i], k = tok & 15, arg = tok >> 4;
-    if (k == T_VAR) { if (arg == loop) { var = true; stride = 2; } leaf[sp] = false; val[sp] = 0; ++sp; }
-    else if (k == T_CONST) { leaf[sp] = true; val[sp] = W.S[arg]; ++sp; }
+    const int tok = token(e, i), k = tok & 15, arg = tok >> 4;
+    if (k == T_VAR) { if (arg == loop) { var = true; stride = 2; } st.push(LV{0, false}); }
+    else if (k == T_CONST) st.push(LV{W.S[arg], true});
     else {
-      --sp;
+      LV a, b;
+      st.pop2(a, b);
       if (k == T_MUL) {
         if (var && !add) {
-          if (leaf[sp - 1]) { mul = true; stride = val[sp - 1]; }
-          else if (leaf[sp]) { mul = true; stride = val[sp]; }
+          if (a.leaf) { mul = true; stride = a.val; }
+          else if (b.leaf) { mul = true; stride = b.val; }
         }
       } else if (k == T_ADD) {
         if (var && !mul) { add = true; stride = 1; }
       }
-      leaf[sp - 1] = false;
+      st.push(LV{0, false});
     }
   }
   *found = var;

@@ -32,7 +32,7 @@ OPS = ["float_mad", "float_addsub", "float_mul", "float_divmod", "float_cmp", "f
 K_READ, K_WRITE, K_READWRITE, K_UNKNOWN = 0, 1, 2, 3
 # device program limits (csrc/sketch_features.cu)
 MAX_SLOTS, MAX_SCALARS, MAX_LOOPS, MAX_BUFS, MAX_DEPTH, MAX_DIMS, MAX_TOKENS, SCALAR_SLOTS, MAX_ACC, MAX_EXPR, MAX_PROG = \
-    64, 64, 32, 6, 24, 4, 32, 8, 5, 40, 4096
+    64, 48, 32, 6, 24, 4, 32, 12, 5, 40, 4096
 OP_FOR, OP_FOR_END, OP_THREAD, OP_THREAD_END, OP_PRAGMA, OP_PRAGMA_END, OP_REALIZE_END, OP_STORE = range(8)
 T_VAR, T_CONST, T_ADD, T_MUL, T_DIV, T_MOD = range(6)
 MAGIC = 0x56465831
@@ -207,8 +207,15 @@ class SketchTemplate:
             expr_tokens(e, toks)
             if len(toks) > MAX_TOKENS:
                 raise ValueError("index expression longer than %d tokens" % MAX_TOKENS)
+            depth = peak = 0
+            for tk in toks:                               # the device keeps the evaluation stack in four registers
+                depth += 1 if (tk & 15) in (T_VAR, T_CONST) else -1
+                peak = max(peak, depth)
+            if peak > 4:
+                raise ValueError("index expression needs an evaluation stack deeper than 4 (write sums left to right)")
+            masks = [sum(1 << i for i, tk in enumerate(toks) if (tk & 15) in kinds) for kinds in ((T_ADD,), (T_MUL,), (T_DIV, T_MOD))]
             off = expr_cache[key] = len(exprs)
-            exprs.extend([len(toks)] + toks)
+            exprs.extend([len(toks)] + [m - (1 << 32) if m >= (1 << 31) else m for m in masks] + toks)
             return off
 
         def emit_store(n):
@@ -225,15 +232,22 @@ class SketchTemplate:
                 raise ValueError("a statement touches at most %d buffers / %d index expressions" % (MAX_ACC, MAX_EXPR))
             off = len(stores)
             stores.extend([n["buffer"], len(acc)] + [int(n["ops"].get(k, 0)) for k in OPS])
+            listed = []                                                    # expression offsets in the order the device lists them
             for b, (acc_type, tuples) in acc.items():
                 nd = len(self.buffers[b]["shape"])
                 if any(len(ix) != nd for ix in tuples) or len(tuples) > 4:
                     raise ValueError("access to %s: %d-d indices expected, at most 4 distinct reads" % (self.buffers[b]["name"], nd))
                 stores.extend([b, acc_type, len(tuples), nd])
                 for ix in tuples:
-                    stores.extend(expr(e) for e in ix)
-            loads = [expr(e) for _, ix in n["reads"] for e in ix]          # every BufferLoad's indices: their arithmetic
-            stores.extend([len(loads)] + loads)                            # counts as int ops (MathOpCounter)
+                    offs = [expr(e) for e in ix]
+                    stores.extend(offs)
+                    listed.extend(offs)
+            # every BufferLoad's indices: their arithmetic counts as int ops (MathOpCounter): (position in the list above or
+            # -1, expression offset) per index
+            loads = [expr(e) for _, ix in n["reads"] for e in ix]
+            stores.append(len(loads))
+            for o in loads:
+                stores.extend([listed.index(o) if o in listed else -1, o])
             return off
 
         def walk(nodes, depth=0):
@@ -384,20 +398,38 @@ CONV2D_SLOTS = {"n": (0, 1, 2, 3), "y": (4, 5, 6, 7), "x": (8, 9, 10, 11), "f": 
 CONV2D_README_EXTENTS = [1, 1, 1, 1, 1, 1, 1, 28, 4, 7, 1, 1, 2, 8, 1, 8, 1, 3, 3, 1, 4, 16, 16]
 
 
-def conv2d_nhwc_cpu_template(N=1, H=56, W=56, CI=64, CO=128, KH=3, KW=3, stride=2, pad_after=1):
+def conv2d_nhwc_cpu_template(N=1, H=56, W=56, CI=64, CO=128, KH=3, KW=3, stride=2, pad_after=1, derive_outer=False):
     """conv2d NHWC + bias + ReLU under Ansor's CPU multi-level tiling sketch ("SSRSRS" with the consumer fused at the second
     tile level, the padding stage computed at the fused outer loop, the outer spatial tiles fused and parallelised, the
     innermost channel tile vectorised): the structure of the program the reference README prints (:86-108; PaddedInput /
     Conv2dOutput / T_relu; its loop extents are CONV2D_README_EXTENTS here).  Extent vector (23 slots, CONV2D_SLOTS): the
     tile factors n, y, x, f (4 levels each, outermost first), ry, rx, rc (2 levels each) and auto_unroll_max_step.  Three
-    statement rows per candidate."""
+    statement rows per candidate.  derive_outer: the outermost level of every axis is not read from the vector but derived
+    as axis length // product of the inner levels -- the form a SplitStep has (it stores the inner lengths only,
+    transform_step.cc:1015-1023) and the divisor legaliser guarantees to be exact (conv2d_slot_tables)."""
     OH, OW = (H + pad_after - KH) // stride + 1, (W + pad_after - KW) // stride + 1
     t = SketchTemplate(23)
+    length = {0: N, 4: OH, 8: OW, 12: CO, 16: KH, 18: KW, 20: CI}         # first slot of an axis -> the axis length
     data, kernel, bias = t.buffer("placeholder", (N, H, W, CI)), t.buffer("placeholder", (KH, KW, CI, CO)), t.buffer("placeholder", (1, 1, 1, CO))
     Pad, Conv, Relu = (t.buffer("PaddedInput", (N, H + pad_after, W + pad_after, CI)), t.buffer("Conv2dOutput", (N, OH, OW, CO)),
                        t.buffer("T_relu", (N, OH, OW, CO)))
     sl = CONV2D_SLOTS
-    S = lambda *slots, const=1, add=0: t.scalar(const, tuple(slots), (), add)
+    groups = {g[0]: g for g in (sl[k] for k in ("n", "y", "x", "f", "ry", "rx", "rc"))}
+
+    def S(*slots, const=1, add=0):
+        mul_, div_ = [], []
+        for j in slots:
+            if derive_outer and j in length:
+                const *= length[j]
+                div_ += list(groups[j][1:])
+            else:
+                mul_.append(j)
+        for j in list(mul_):                                              # an inner level both multiplied and divided cancels
+            if j in div_:
+                mul_.remove(j)
+                div_.remove(j)
+        return t.scalar(const, tuple(mul_), tuple(div_), add)
+
     n, y, x, f, ry, rx, rc = (sl[k] for k in ("n", "y", "x", "f", "ry", "rx", "rc"))
     zero = t.const(0)
     with t.loop("ax0.0@ax1.0@ax2.0@", S(n[0], y[0], x[0]), "parallel") as p:
@@ -443,3 +475,74 @@ def conv2d_nhwc_cpu_template(N=1, H=56, W=56, CI=64, CO=128, KH=3, KW=3, stride=
                       lin(fo + [(V(d), None)])]
                 t.store(Relu, ix, reads=[(Conv, ix), (bias, [C(zero), C(zero), C(zero), ix[3]])], ops={"float_addsub": 1, "float_cmp": 1})
     return t
+
+
+def conv2d_slot_tables(N=1, H=56, W=56, CI=64, CO=128, KH=3, KW=3, stride=2, pad_after=1, max_innermost=64):
+    """(slot_extent int32[23], slot_last uint8[23]) for vaex_decode_snap / vaex_legalise_extents in divisor mode with
+    conv2d_nhwc_cpu_template(derive_outer=True): the inner levels of an axis are the lengths of its SplitStep (their product
+    must divide the axis length, the innermost one at most max_innermost); the outermost levels and the unroll slot are free."""
+    OH, OW = (H + pad_after - KH) // stride + 1, (W + pad_after - KW) // stride + 1
+    ext, last = np.zeros(23, np.int32), np.zeros(23, np.uint8)
+    for key, E in (("n", N), ("y", OH), ("x", OW), ("f", CO), ("ry", KH), ("rx", KW), ("rc", CI)):
+        g = CONV2D_SLOTS[key]
+        ext[list(g[1:])] = E
+        last[g[-1]] = 1
+    return ext, last
+
+
+class SketchScorer:
+    """The north-star scoring chain for one sketch, device-resident end to end:
+
+        z [n, L] -> VAE decoder -> snap -> divisor legalise -> extents [n, slots]          (vaex_decode_snap)
+                 -> the sketch's per-statement feature rows [n * rows, 164]                 (vaex_sketch_features)
+                 -> SegmentSum-MLP score per candidate [n]                                  (vaex_segsum_mlp_forward)
+
+    The reference runs the middle step on the CPU through TVM and moves 656 bytes per statement to the cost model; here
+    only the latents (or nothing, when they are produced on the device) cross PCIe.  vae: VAE_feature_head whose output
+    width is the template's slot count; cost_model: SegmentSumMLPModule; mean / scale: the extent scaler; slot_extent /
+    slot_last: the legaliser's tables for the template (e.g. conv2d_slot_tables())."""
+
+    def __init__(self, vae, mean, scale, template, cost_model, slot_extent=None, slot_last=None, log1p=True, max_innermost=64,
+                 fea_norm_vec=None):
+        dev = next(vae.parameters()).device
+        if dev.type != "cuda":
+            raise _lib.VaexError("vaex_b200 needs the models on a CUDA device (no CPU fallback)")
+        if vae.decoder[-1].out_features != template.n_slots:
+            raise ValueError("the decoder emits %d extents, the template reads %d" % (vae.decoder[-1].out_features, template.n_slots))
+        self.vae, self.cost_model, self.features = vae, cost_model, SketchFeatures(template, dev)
+        self.mean = torch.as_tensor(mean, dtype=torch.float32).to(dev).contiguous()
+        self.scale = torch.as_tensor(scale, dtype=torch.float32).to(dev).contiguous()
+        self.slot_extent = None if slot_extent is None else torch.as_tensor(slot_extent, dtype=torch.int32).to(dev).contiguous()
+        self.slot_last = None if slot_last is None else torch.as_tensor(slot_last, dtype=torch.uint8).to(dev).contiguous()
+        self.mode = (_lib.SNAP_EXPM1 if log1p else _lib.SNAP_EXP) | (_lib.SNAP_DIVISOR if slot_extent is not None else 0)
+        self.max_innermost, self.fea_norm_vec = max_innermost, fea_norm_vec
+        self._buf = {}
+
+    def _buffers(self, n, dev):
+        b = self._buf.get(n)
+        if b is None:
+            R = self.features.n_rows
+            b = self._buf[n] = (torch.empty(n, self.features.n_slots, dtype=torch.int32, device=dev),
+                                torch.empty(n * R, ROW, device=dev),
+                                torch.arange(0, (n + 1) * R, R, dtype=torch.int32, device=dev),
+                                torch.empty(n, device=dev))
+            if len(self._buf) > 4:
+                self._buf.pop(next(iter(self._buf)))
+        return b
+
+    def score(self, z):
+        """-> (scores fp32 [n], extents int32 [n, slots]); buffers are reused between calls of the same n"""
+        if not z.is_cuda:
+            raise _lib.VaexError("vaex_b200 needs CUDA tensors (no CPU fallback)")
+        _lib.check_device(z)
+        z = z.detach().contiguous().float()
+        n, lib, st = z.shape[0], _lib.load(), _lib.stream_ptr()
+        ext, rows, offsets, scores = self._buffers(n, z.device)
+        if n == 0:
+            return scores, ext
+        _lib.check(lib.vaex_decode_snap(self.vae.packed().h, _lib.ptr(z), n, None, _lib.ptr(ext), _lib.ptr(self.mean), _lib.ptr(self.scale),
+                                        self.mode, _lib.ptr(self.slot_extent), _lib.ptr(self.slot_last), self.max_innermost, st))
+        self.features.rows(ext, out=rows)
+        _lib.check(lib.vaex_segsum_mlp_forward(self.cost_model.packed(self.fea_norm_vec).h, _lib.ptr(rows), _lib.ptr(offsets), n,
+                                               rows.shape[0], _lib.ptr(scores), 0, st))
+        return scores, ext
