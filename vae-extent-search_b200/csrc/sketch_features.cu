@@ -19,7 +19,9 @@
 //                                                       PRAGMA(-, scalar) PRAGMA_END REALIZE_END(buffer, aux) STORE(store)
 //   store: buffer, n_access, ops[16], then per access: buffer, acc_type, n_tuples, ndim, expression offset[n_tuples * ndim],
 //          then n_loads, expression offset[n_loads] (the indices of every BufferLoad: their arithmetic counts as int ops)
-//   expression: n_tokens, ADD mask, MUL mask, DIV|MOD mask (a bit per token), token[n]; token = kind | arg << 4: VAR(loop) CONST(scalar) ADD MUL(which operand is a leaf) DIV MOD
+//   expression: n_tokens, ADD mask, MUL mask, DIV|MOD mask (a bit per token), n_terms (-1: none), token[n], term[n_terms][4];
+//               term = kind | loop << 4, coefficient scalar (-1: none), c1, c2 -- the stack-free form of a sum of
+//               v * c, (v // c1) * c, (v % c1) * c, ((v // c1) % c2) * c and constants;  token = kind | arg << 4: VAR(loop) CONST(scalar) ADD MUL(which operand is a leaf) DIV MOD
 //
 // Each warp stages its 32 rows in shared memory and writes them out as contiguous 656-byte rows (coalesced).
 #include <cstdint>
@@ -79,7 +81,9 @@ struct Stack4 {
   __device__ __forceinline__ void pop2(T& a, T& b) { b = s0; a = s1; s0 = s2; s1 = s3; }       // a was pushed before b
 };
 __device__ __forceinline__ int n_tokens(const int32_t* e) { return e[0]; }
-__device__ __forceinline__ int token(const int32_t* e, int i) { return e[4 + i]; }               // e[1..3]: ADD / MUL / DIV|MOD masks
+__device__ __forceinline__ int token(const int32_t* e, int i) { return e[5 + i]; }               // e[1..3]: ADD / MUL / DIV|MOD masks
+__device__ __forceinline__ int n_terms(const int32_t* e) { return e[4]; }                        // -1: no term form
+__device__ __forceinline__ const int32_t* term_at(const int32_t* e, int i) { return e + 5 + e[0] + 4 * i; }
 
 // Which tokens survive the folds of Simplify (a bit per token; the survivors are again a postfix expression, or none = 0)
 __device__ uint32_t simplify(const Prog& P, const Walk& W, const int32_t* e, uint32_t* var_mask) {
@@ -250,6 +254,73 @@ __device__ int64_t coefficient(const Prog& P, const Walk& W, const int32_t* e, u
       }
       st.push(LV{0, false});
     }
+  }
+  *found = var;
+  return (var && !mul && !add) ? 1 : stride;
+}
+
+// ---- the term form: most indices are a left-to-right sum of  base [* c]  with base = v | v // c1 | v % c1 | (v // c1) % c2, or
+// constants.  Each term is folded, bounded and counted on its own -- no expression stack, a handful of instructions per term
+// instead of a token loop.  The rules are those of simplify() / bound() / coefficient() applied to that shape of tree.
+enum { TERM_PLAIN, TERM_DIV, TERM_MOD, TERM_DIVMOD, TERM_CONST };
+struct Term { int64_t w, coef; int pos, loop, n_dm; bool alive, has_mul, is_const; };
+
+__device__ __forceinline__ Term term_eval(const Walk& W, const int32_t* t) {
+  Term r;
+  const int kind = t[0] & 15;
+  r.loop = t[0] >> 4; r.is_const = kind == TERM_CONST; r.n_dm = 0; r.w = 0; r.has_mul = false; r.coef = 1; r.pos = -1; r.alive = false;
+  if (r.is_const) { r.w = W.S[t[1]]; r.alive = r.w != 0; return r; }          // w carries the constant's value
+  r.pos = W.pos[r.loop];
+  if (r.pos < 0) return r;
+  int64_t fhi = (int64_t)W.ext[r.loop] - 1;
+  if (kind == TERM_DIV || kind == TERM_DIVMOD) {
+    const int64_t c = W.S[t[2]];
+    if (c != 1) { if (fhi < c) return r; fhi /= c; ++r.n_dm; }
+  }
+  if (kind == TERM_MOD || kind == TERM_DIVMOD) {
+    const int64_t c = W.S[kind == TERM_MOD ? t[2] : t[3]];
+    if (c == 1) return r;
+    if (fhi >= c) { fhi = c - 1; ++r.n_dm; }
+  }
+  r.alive = true;
+  if (t[1] >= 0) { r.coef = W.S[t[1]]; r.has_mul = r.coef != 1; }
+  r.w = fhi * r.coef;
+  return r;
+}
+
+// loops that occur in the folded expression; packed node counts: adds | muls << 8 | floordiv + floormod << 16
+__device__ uint32_t terms_summary(const Walk& W, const int32_t* e, uint32_t* var_mask) {
+  int n_alive = 0, n_mul = 0, n_dm = 0;
+  for (int i = 0; i < n_terms(e); ++i) {
+    const Term t = term_eval(W, term_at(e, i));
+    if (!t.alive) continue;
+    ++n_alive;
+    if (!t.is_const) { *var_mask |= 1u << t.loop; n_mul += t.has_mul; n_dm += t.n_dm; }
+  }
+  return (uint32_t)max(n_alive - 1, 0) | ((uint32_t)n_mul << 8) | ((uint32_t)n_dm << 16);
+}
+
+// acc[position of the term's loop] += the width the term adds to the index once that loop is bound
+__device__ void terms_widths(const Walk& W, const int32_t* e, int64_t* acc) {
+  for (int i = 0; i < n_terms(e); ++i) {
+    const Term t = term_eval(W, term_at(e, i));
+    if (t.alive && !t.is_const) acc[t.pos] += t.w;
+  }
+}
+
+// CoefficientExtractor on ((t0 + t1) + t2) ...: per term the variable, then its Mul node, then (from the second term on) the Add
+__device__ int64_t terms_coefficient(const Walk& W, const int32_t* e, int loop, bool* found) {
+  bool var = false, mul = false, add = false, first = true;
+  int64_t stride = 0;
+  for (int i = 0; i < n_terms(e); ++i) {
+    const Term t = term_eval(W, term_at(e, i));
+    if (!t.alive) continue;
+    if (!t.is_const) {
+      if (t.loop == loop) { var = true; stride = 2; }
+      if (t.has_mul && var && !add) { mul = true; stride = t.coef; }
+    }
+    if (!first && var && !mul) { add = true; stride = 1; }
+    first = false;
   }
   *found = var;
   return (var && !mul && !add) ? 1 : stride;

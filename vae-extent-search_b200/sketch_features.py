@@ -63,6 +63,47 @@ def floormod(a, b):
     return ("%", a, b)
 
 
+TERM_PLAIN, TERM_DIV, TERM_MOD, TERM_DIVMOD, TERM_CONST = range(5)
+MAX_TERMS = 8
+
+
+def _terms(e):
+    """The canonical form most indices have -- a left-to-right sum of terms base [* c] with base = v | v // c | v % c |
+    (v // c1) % c2, or a constant -- as [(kind, loop node, coef scalar or -1, c1 scalar, c2 scalar)]; None for anything else
+    (the device then walks the token form).  The device evaluates this form without an expression stack."""
+    def base(x):
+        if x[0] == "v":
+            return (TERM_PLAIN, x[1], -1, -1)
+        if x[0] in ("//", "%") and x[2][0] == "c":
+            if x[1][0] == "v":
+                return (TERM_DIV if x[0] == "//" else TERM_MOD, x[1][1], x[2][1], -1)
+            if x[0] == "%" and x[1][0] == "//" and x[1][1][0] == "v" and x[1][2][0] == "c":
+                return (TERM_DIVMOD, x[1][1][1], x[1][2][1], x[2][1])
+        return None
+
+    def term(x):
+        if x[0] == "c":
+            return (TERM_CONST, None, x[1], -1, -1)
+        if x[0] == "*":
+            if x[2][0] == "c" and x[1][0] != "c":
+                b, c = base(x[1]), x[2][1]
+            elif x[1][0] == "c" and x[2][0] != "c":
+                b, c = base(x[2]), x[1][1]
+            else:
+                return None
+        else:
+            b, c = base(x), -1
+        return None if b is None else (b[0], b[1], c, b[2], b[3])
+
+    parts = []
+    while e[0] == "+":
+        parts.append(e[2])
+        e = e[1]
+    parts.append(e)
+    out = [term(x) for x in reversed(parts)]
+    return None if any(t is None for t in out) else out
+
+
 def _expr_key(e):
     if e[0] == "v":
         return ("v", id(e[1]))
@@ -214,8 +255,13 @@ class SketchTemplate:
             if peak > 4:
                 raise ValueError("index expression needs an evaluation stack deeper than 4 (write sums left to right)")
             masks = [sum(1 << i for i, tk in enumerate(toks) if (tk & 15) in kinds) for kinds in ((T_ADD,), (T_MUL,), (T_DIV, T_MOD))]
+            terms = _terms(e)
+            tw = []
+            if terms is not None and len(terms) <= MAX_TERMS:
+                for kind, lp, coef, c1, c2 in terms:
+                    tw.extend([kind | ((loop_id[id(lp)] if lp is not None else 0) << 4), coef, c1, c2])
             off = expr_cache[key] = len(exprs)
-            exprs.extend([len(toks)] + [m - (1 << 32) if m >= (1 << 31) else m for m in masks] + toks)
+            exprs.extend([len(toks)] + [m - (1 << 32) if m >= (1 << 31) else m for m in masks] + [len(tw) // 4 if tw else -1] + toks + tw)
             return off
 
         def emit_store(n):
