@@ -630,12 +630,31 @@ def main_vaex(args):
         if world > 1:
             dist.all_reduce(t6, op=dist.ReduceOp.MAX)
         ms6, ms6_rows = float(t6[0].item()), float(t6[1].item())
+        # the same chain fed from the host: pinned latents up, the merged / local top-k down, every step
+        z6_host = z6.cpu().pin_memory()
+        tv_host, ti_host = torch.empty(TOPK, pin_memory=True), torch.empty(TOPK, dtype=torch.int64, pin_memory=True)
+
+        def step6_host():
+            z6.copy_(z6_host, non_blocking=True)
+            step6()
+            tv_host.copy_(mer_v if world > 1 else top_v, non_blocking=True)
+            ti_host.copy_(mer_i if world > 1 else top_i, non_blocking=True)
+            stream.synchronize()
+        ms6_host = timed(step6_host, 5)
+        t6h = torch.tensor([ms6_host], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t6h, op=dist.ReduceOp.MAX)
+        ms6_host = float(t6h.item())
+        del z6_host
         R6 = scorer.features.n_rows
         configs["sketch_pipeline"] = {
             "what": "per rank 2^20 latents -> decode + snap + legalise (23 tile extents, conv2d sketch) -> %d feature rows per candidate "
                     "from the sketch template (vaex_sketch_features) -> SegmentSum-MLP -> top-%d -> merge; device-resident" % (R6, TOPK),
             "latents_per_gpu": n6, "n_gpus": world, "ms_per_step": ms6, "candidates_per_s": world * n6 / (ms6 * 1e-3),
             "ms_feature_rows": ms6_rows, "feature_rows_GBps_written": n6 * R6 * F * 4 / (ms6_rows * 1e-3) / 1e9,
+            "e2e": {"what": "host latents in (pinned, %d B per candidate), top-%d out, copies inside the timed region" % (4 * L_LAT, TOPK),
+                    "ms_per_step": ms6_host, "candidates_per_s": world * n6 / (ms6_host * 1e-3),
+                    "h2d_bytes_per_step": n6 * L_LAT * 4, "d2h_bytes_per_step": TOPK * 12},
             "note": "the feature kernel interprets the template per candidate (about 1e5 instructions each): instruction-bound, "
                     "not HBM-bound; template fidelity to TVM's lowering is unpinned (DESIGN section 2)"}
         del z6
