@@ -1,0 +1,88 @@
+"""Host side of n4 (no GPU): the template builder / compiler of vae-extent-search_b200/sketch_features.py -- program layout,
+term recognition, limits -- and template-level properties checked through the oracle."""
+import numpy as np
+import pytest
+
+from oracle import perstore_features as PF
+from vaex_b200 import sketch_features as SF
+
+
+def test_program_layout_and_limits():
+    t = SF.conv2d_nhwc_cpu_template()
+    prog = t.compile()
+    assert prog.dtype == np.int32 and prog[0] == SF.MAGIC and prog[1] == 23 and prog[5] == 3 == t.n_rows
+    assert prog[2] == len(t.scalars) <= SF.MAX_SCALARS and prog[3] == 6 and len(prog) <= SF.MAX_PROG
+    offs = prog[7:12]
+    assert list(offs) == sorted(offs) and offs[-1] < len(prog)
+    n_instr = prog[6]
+    instr = prog[offs[2]:offs[2] + 4 * n_instr].reshape(-1, 4)
+    stores = instr[instr[:, 0] == SF.OP_STORE]
+    assert len(stores) == 4 and stores[:, 2].tolist() == [1, 0, 1, 1]       # init, update of Conv2dOutput: only the update keeps a row
+    assert (instr[:, 0] == SF.OP_FOR).sum() == (instr[:, 0] == SF.OP_FOR_END).sum() == 36
+    assert instr[instr[:, 0] == SF.OP_FOR][:, 1].max() < SF.MAX_DEPTH        # loop ids are nesting depths
+    with pytest.raises(ValueError):
+        SF.SketchTemplate(0)
+    with pytest.raises(ValueError):
+        SF.SketchTemplate(4).scalar(1, (4,))
+    with pytest.raises(ValueError):
+        SF.SketchTemplate(4).buffer("x", (1, 2, 3, 4, 5))
+    deep = SF.SketchTemplate(1)
+    b = deep.buffer("b", (4,))
+    with deep.loops(*[("l%d" % i, deep.slot(0)) for i in range(SF.MAX_DEPTH + 1)]) as ls:
+        deep.store(b, [SF.V(ls[-1])])
+    with pytest.raises(ValueError, match="nested deeper"):
+        deep.compile()
+
+
+def test_term_recognition():
+    t = SF.SketchTemplate(2)
+    with t.loop("a", t.slot(0)) as a, t.loop("b", t.slot(1)) as b:
+        c4, c3 = t.const(4), t.const(3)
+        canon = SF.lin([(SF.floormod(SF.floordiv(SF.V(a), SF.C(c4)), SF.C(c3)), c4), (SF.V(b), c3), (SF.V(a), None)])
+        terms = SF._terms(canon)
+        assert [k for k, *_ in terms] == [SF.TERM_DIVMOD, SF.TERM_PLAIN, SF.TERM_PLAIN] and terms[0][2:] == (c4, c4, c3)
+        assert SF._terms(SF.add(SF.V(a), SF.C(c4)))[1][0] == SF.TERM_CONST
+        assert SF._terms(SF.floordiv(SF.add(SF.mul(SF.V(a), SF.C(c4)), SF.V(b)), SF.C(c3))) is None      # floordiv of a sum: token form
+        assert SF._terms(SF.mul(SF.V(a), SF.V(b))) is None
+        assert SF._terms(SF.add(SF.V(a), SF.add(SF.V(b), SF.C(c4)))) is None                              # right-nested sum: token form
+
+
+def test_derived_outer_levels_equal_explicit_ones():
+    """conv2d template: the outermost tile level derived as axis length // product(inner levels) gives the rows of the
+    explicit 23-slot form, for legal tilings."""
+    full, derived = SF.conv2d_nhwc_cpu_template(), SF.conv2d_nhwc_cpu_template(derive_outer=True)
+    rng = np.random.default_rng(0)
+    length = {"n": 1, "y": 28, "x": 28, "f": 128, "ry": 3, "rx": 3, "rc": 64}
+    for _ in range(12):
+        e = np.ones(23, np.int64)
+        for key, E in length.items():
+            sl, rest = SF.CONV2D_SLOTS[key], E
+            for j in sl[:0:-1]:
+                divs = [d for d in range(1, rest + 1) if rest % d == 0]
+                e[j] = rng.choice(divs)
+                rest //= e[j]
+            e[sl[0]] = rest
+        e[22] = rng.choice([0, 16, 64, 512])
+        a, _ = PF.evaluate(full.as_dict(), e.tolist())
+        junk = e.copy()
+        junk[[0, 4, 8, 12, 16, 18, 20]] = 777                     # the derived form never reads the outer slots
+        b, _ = PF.evaluate(derived.as_dict(), junk.tolist())
+        assert np.array_equal(a, b)
+    se, sl_ = SF.conv2d_slot_tables()
+    assert se[[5, 6, 7]].tolist() == [28, 28, 28] and se[[0, 4, 8, 12, 16, 18, 20, 22]].tolist() == [0] * 8
+    assert sl_.nonzero()[0].tolist() == [3, 7, 11, 15, 17, 19, 21]
+
+
+def test_rows_are_invariant_to_what_the_extractor_cannot_see():
+    """Properties of the extractor on the matmul template: the total work (float_mul = N * M * K) does not depend on the
+    tiling; swapping in a trivial tile leaves the row of the same nest written without that loop (checked in
+    test_oracle_perstore); every value is finite and the one-hot groups sum to one."""
+    t = SF.matmul_cpu_template(256, 256, 256)
+    names = PF.feature_names()
+    for e in ([16, 32, 256, 8, 16], [256, 256, 256, 1, 1], [1, 1, 256, 256, 256], [4, 2, 256, 128, 64]):
+        rows, _ = PF.evaluate(t.as_dict(), e)
+        fea = dict(zip(names, rows[0]))
+        assert np.isfinite(rows).all()
+        assert abs(fea["float_mul"] - np.log2(256.0 ** 3 + 1)) < 1e-5
+        for grp in ("vec_type.", "unroll_type.", "parallel_type.", "B0.acc_type.", "B0.reuse_type."):
+            assert sum(v for k, v in fea.items() if k.startswith(grp)) == 1.0
