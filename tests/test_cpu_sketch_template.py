@@ -86,3 +86,44 @@ def test_rows_are_invariant_to_what_the_extractor_cannot_see():
         assert abs(fea["float_mul"] - np.log2(256.0 ** 3 + 1)) < 1e-5
         for grp in ("vec_type.", "unroll_type.", "parallel_type.", "B0.acc_type.", "B0.reuse_type."):
             assert sum(v for k, v in fea.items() if k.startswith(grp)) == 1.0
+
+
+def test_conv2d_template_reproduces_the_readme_program():
+    """The one lowered-program listing the reference ships for this sketch (README.md:86-108, kept as a fixture in
+    oracle/gen_golden.py): with its extents the template's non-trivial loops are that listing, loop for loop -- annotation,
+    extent, nesting and the statement each nest ends in.  (PrintState does not list the reduction's init nest.)"""
+    import re
+    from oracle.gen_golden import README_STATE
+    want = []
+    for line in README_STATE.splitlines()[1:]:
+        ind = (len(line) - len(line.lstrip())) // 2
+        m = re.match(r"\s*(parallel|vectorize|unroll|for) \S+ \(.*?(\d+)\)\s*$", line)
+        if m:
+            want.append((ind, m.group(1), int(m.group(2))))
+        elif "auto_unroll" in line:
+            want.append((ind, "pragma", int(line.rsplit(":", 1)[1])))
+        elif line.strip().endswith("= ..."):
+            want.append((ind, "store", line.split("=")[0].strip()))
+    t = SF.conv2d_nhwc_cpu_template()
+    S = PF.scalar_values(t.as_dict(), SF.CONV2D_README_EXTENTS)
+    got = []
+
+    def walk(nodes, ind):
+        for n in nodes:
+            k = n["kind"]
+            if k in SF.KINDS:
+                if S[n["extent"]] == 1 or n["name"].endswith(".init"):
+                    walk(n["body"], ind)                      # trivial loops are not printed
+                    continue
+                got.append((ind, k, S[n["extent"]]))
+                walk(n["body"], ind + 1)
+            elif k == "pragma_unroll":
+                got.append((ind, "pragma", S[n["value"]]))
+                walk(n["body"], ind)
+            elif k == "realize":
+                walk(n["body"], ind)
+            elif k == "store":
+                if n.get("reads"):
+                    got.append((ind, "store", t.buffers[n["buffer"]]["name"]))
+    walk(t.body, 0)
+    assert got == want, (got, want)
