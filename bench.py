@@ -762,6 +762,69 @@ def main_vaex(args):
         cpu_baseline = {"value": ns / tcpu, "unit": UNIT, "cores": cores, "kind": "port",
                         "sample": "the first %d candidates of rank 0's inputs, one step; %s" % (ns, CPU_KIND_NOTE)}
 
+    # ---- the remaining CPU baselines of BASELINE.md section 4 (B2b, B3, B4), beside their GPU counterparts ----
+    if not args.no_cpu and not args.no_configs and world == 1:
+        from oracle import torch_oracle as O
+        cores = os.cpu_count() or 1
+        torch.set_num_threads(cores)
+        extra = {}
+        # B2b: SegmentSumMLPModule.forward only, pre-flattened tensors, batch 4096 (kernel-equivalent comparison)
+        nb = min(P, 32768)
+        offs_b = np.concatenate([[0], np.cumsum(sizes[:nb], dtype=np.int64)])
+        fb = (feats[:int(offs_b[-1])].cpu() / norm.cpu()).contiguous()
+        Pseg = {k: v.detach().cpu() for k, v in net.state_dict().items()}
+
+        def b2b():
+            with torch.no_grad():
+                for i0 in range(0, nb, 4096):
+                    i1 = min(nb, i0 + 4096)
+                    O.segsum_mlp_forward(Pseg, sizes[i0:i1], fb[int(offs_b[i0]):int(offs_b[i1])])
+        b2b()
+        t0 = time.perf_counter()
+        b2b()
+        extra["B2b_forward_only"] = {"programs_per_s_cpu": nb / (time.perf_counter() - t0), "programs": nb, "cores": cores,
+                                     "gpu_counterpart": "roofline_kernels: segsum_tc_kernel + head_tc_kernel"}
+        # B3: the compute stages of select_programs on a pool of 4096 (encode, predict, z-gradient, MC-dropout T = 20, k-center)
+        xp = torch.randn(4096, D_EXT, generator=torch.Generator().manual_seed(33))
+        Preg = {k: v.detach().cpu() for k, v in reg.state_dict().items()}
+        mk = (torch.rand(20, 4096, H, generator=torch.Generator().manual_seed(34)) >= 0.1).to(torch.uint8)
+        perm = np.random.default_rng(35).permutation(4096)
+
+        def b3_cpu():
+            with torch.no_grad():
+                zc, _ = O.vae_encode(Preg, xp)
+                O.predict_cost(Preg, zc)
+                O.mc_predict(Preg, xp, mk)
+            O.cost_grad_z(Preg, zc)
+            O.kcenter_select(zc, perm[:320], perm[320:448], 12)
+        b3_cpu()
+        t0 = time.perf_counter()
+        b3_cpu()
+        t_b3 = time.perf_counter() - t0
+        xg = xp.numpy()
+
+        def b3_gpu():
+            vaex_b200.select_programs(reg, xg, set(perm[320:448].tolist()), set(perm[:3968].tolist()), num_select=64, T_mc=20,
+                                      uncertainty_topk=128, device=dev, mc_seed=7)
+        b3_gpu()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(5):
+            b3_gpu()
+        torch.cuda.synchronize()
+        extra["B3_select_programs_pool4096"] = {
+            "ms_cpu_compute_stages": t_b3 * 1e3, "cores": cores,
+            "ms_gpu_select_programs": (time.perf_counter() - t0) / 5 * 1e3,
+            "note": "CPU: the oracle's encode + predict + z-gradient + 20 MC-dropout passes + k-center on the pool; GPU: the whole "
+                    "select_programs mirror (wall clock, host set bookkeeping included)"}
+        # B4: latent ascent 256 x 200 on the CPU (torch autograd over the oracle's predictor), config 3's first graph
+        z0c = O.vae_encode(Preg, torch.randn(256, D_EXT, generator=torch.Generator().manual_seed(3)))[0]
+        t0 = time.perf_counter()
+        O.latent_ascent(Preg, z0c, 200, 1e-2)
+        extra["B4_latent_ascent_256x200"] = {"ms_cpu_per_search": (time.perf_counter() - t0) * 1e3, "cores": cores,
+                                             "gpu_counterpart": "configs.config3.graphs[0].ms_per_search"}
+        configs["cpu_baselines"] = extra
+
     # ---- "the bar" of SURVEY section 2: the reference's own eager PyTorch forward (cuBLAS / ATen kernels) on THIS GPU ----
     torch_gpu = None
     if not args.no_cpu and world == 1:
