@@ -41,7 +41,9 @@ enum { T_VAR, T_CONST, T_ADD, T_MUL, T_DIV, T_MOD };
 enum { K_READ, K_WRITE, K_READWRITE };
 enum { KIND_FOR, KIND_VEC, KIND_UNROLL, KIND_PAR, KIND_THREAD };
 
-__device__ __forceinline__ float slog(float x) { return x < 0.f ? -log2f(-x + 1.f) : log2f(x + 1.f); }   // feature.cc:1051
+// feature.cc:1051.  __log2f (the special-function unit: 2^-22 absolute on [0.5, 2], 2 ulp elsewhere) against the reference's
+// log2f: below the 2e-6 the parity tests allow, a twentieth of the instructions -- and every row has 100+ of these
+__device__ __forceinline__ float slog(float x) { return x < 0.f ? -__log2f(-x + 1.f) : __log2f(x + 1.f); }
 
 struct Walk {
   int64_t S[MAX_SCALARS];
@@ -296,6 +298,18 @@ __device__ uint32_t terms_summary(const Walk& W, const int32_t* e, uint32_t* var
     if (!t.alive) continue;
     ++n_alive;
     if (!t.is_const) { *var_mask |= 1u << t.loop; n_mul += t.has_mul; n_dm += t.n_dm; }
+  }
+  return (uint32_t)max(n_alive - 1, 0) | ((uint32_t)n_mul << 8) | ((uint32_t)n_dm << 16);
+}
+
+// terms_summary and terms_widths in one pass over the terms
+__device__ uint32_t terms_summary_widths(const Walk& W, const int32_t* e, uint32_t* var_mask, int64_t* acc) {
+  int n_alive = 0, n_mul = 0, n_dm = 0;
+  for (int i = 0; i < n_terms(e); ++i) {
+    const Term t = term_eval(W, term_at(e, i));
+    if (!t.alive) continue;
+    ++n_alive;
+    if (!t.is_const) { *var_mask |= 1u << t.loop; n_mul += t.has_mul; n_dm += t.n_dm; acc[t.pos] += t.w; }
   }
   return (uint32_t)max(n_alive - 1, 0) | ((uint32_t)n_mul << 8) | ((uint32_t)n_dm << 16);
 }
