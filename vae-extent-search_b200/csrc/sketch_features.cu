@@ -43,7 +43,7 @@ enum { KIND_FOR, KIND_VEC, KIND_UNROLL, KIND_PAR, KIND_THREAD };
 
 // feature.cc:1051.  __log2f (the special-function unit: 2^-22 absolute on [0.5, 2], 2 ulp elsewhere) against the reference's
 // log2f: below the 2e-6 the parity tests allow, a twentieth of the instructions -- and every row has 100+ of these
-__device__ __forceinline__ float slog(float x) { return x < 0.f ? -__log2f(-x + 1.f) : __log2f(x + 1.f); }
+__device__ __forceinline__ float slog(float x) { return copysignf(__log2f(fabsf(x) + 1.f), x); }
 
 struct Walk {
   int64_t S[MAX_SCALARS];
@@ -302,7 +302,8 @@ __device__ uint32_t terms_summary(const Walk& W, const int32_t* e, uint32_t* var
   return (uint32_t)max(n_alive - 1, 0) | ((uint32_t)n_mul << 8) | ((uint32_t)n_dm << 16);
 }
 
-// terms_summary and terms_widths in one pass over the terms
+// terms_summary, and in the same pass acc[position of the term's loop] += the width the term adds to the index once that
+// loop is bound
 __device__ uint32_t terms_summary_widths(const Walk& W, const int32_t* e, uint32_t* var_mask, int64_t* acc) {
   int n_alive = 0, n_mul = 0, n_dm = 0;
   for (int i = 0; i < n_terms(e); ++i) {
@@ -312,14 +313,6 @@ __device__ uint32_t terms_summary_widths(const Walk& W, const int32_t* e, uint32
     if (!t.is_const) { *var_mask |= 1u << t.loop; n_mul += t.has_mul; n_dm += t.n_dm; acc[t.pos] += t.w; }
   }
   return (uint32_t)max(n_alive - 1, 0) | ((uint32_t)n_mul << 8) | ((uint32_t)n_dm << 16);
-}
-
-// acc[position of the term's loop] += the width the term adds to the index once that loop is bound
-__device__ void terms_widths(const Walk& W, const int32_t* e, int64_t* acc) {
-  for (int i = 0; i < n_terms(e); ++i) {
-    const Term t = term_eval(W, term_at(e, i));
-    if (t.alive && !t.is_const) acc[t.pos] += t.w;
-  }
 }
 
 // CoefficientExtractor on ((t0 + t1) + t2) ...: per term the variable, then its Mul node, then (from the second term on) the Add
