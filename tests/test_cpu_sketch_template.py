@@ -127,3 +127,16 @@ def test_conv2d_template_reproduces_the_readme_program():
                     got.append((ind, "store", t.buffers[n["buffer"]]["name"]))
     walk(t.body, 0)
     assert got == want, (got, want)
+
+
+def test_conv2d_template_matches_task_1264s_flop_count():
+    """README.md:63-66: task 1264 (the conv2d + bias + ReLU workload the template states) has flop_ct 115806208.  The
+    template's statements -- ops per BufferStore times the trip count of its nest, the way the extractor counts them --
+    give exactly that (the if_then_else of the padding stage is a call, which TVM's FLOP estimator does not count)."""
+    t = SF.conv2d_nhwc_cpu_template()
+    fs = PF.feature_sets(t.as_dict(), SF.CONV2D_README_EXTENTS)
+    flops = sum(float(f[k]) for f in fs.values() for k in ("float_mad", "float_addsub", "float_mul", "float_divmod", "float_cmp"))
+    assert flops == 115806208.0
+    assert sorted(t.buffers[b]["name"] for b in fs) == ["Conv2dOutput", "PaddedInput", "T_relu"]
+    pad = fs[[b for b in fs if t.buffers[b]["name"] == "PaddedInput"][0]]
+    assert float(pad["int_cmp"]) == 4 * 218880 and float(pad["bool_op"]) == 3 * 218880 and float(pad["float_math_func"]) == 218880

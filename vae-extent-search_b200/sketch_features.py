@@ -444,20 +444,22 @@ CONV2D_SLOTS = {"n": (0, 1, 2, 3), "y": (4, 5, 6, 7), "x": (8, 9, 10, 11), "f": 
 CONV2D_README_EXTENTS = [1, 1, 1, 1, 1, 1, 1, 28, 4, 7, 1, 1, 2, 8, 1, 8, 1, 3, 3, 1, 4, 16, 16]
 
 
-def conv2d_nhwc_cpu_template(N=1, H=56, W=56, CI=64, CO=128, KH=3, KW=3, stride=2, pad_after=1, derive_outer=False):
+def conv2d_nhwc_cpu_template(N=1, H=56, W=56, CI=64, CO=128, KH=3, KW=3, stride=2, pad_before=1, pad_after=0, derive_outer=False):
     """conv2d NHWC + bias + ReLU under Ansor's CPU multi-level tiling sketch ("SSRSRS" with the consumer fused at the second
     tile level, the padding stage computed at the fused outer loop, the outer spatial tiles fused and parallelised, the
-    innermost channel tile vectorised): the structure of the program the reference README prints (:86-108; PaddedInput /
-    Conv2dOutput / T_relu; its loop extents are CONV2D_README_EXTENTS here).  Extent vector (23 slots, CONV2D_SLOTS): the
+    innermost channel tile vectorised): task 1264 of the reference README -- its compute DAG (README.md:64-76) gives the
+    statements (PaddedInput with its four comparisons, the Conv2dOutput update, T_add inlined into T_relu), the program it
+    prints (:86-108) the loop structure; that program's extents are CONV2D_README_EXTENTS here.  Extent vector (23 slots, CONV2D_SLOTS): the
     tile factors n, y, x, f (4 levels each, outermost first), ry, rx, rc (2 levels each) and auto_unroll_max_step.  Three
     statement rows per candidate.  derive_outer: the outermost level of every axis is not read from the vector but derived
     as axis length // product of the inner levels -- the form a SplitStep has (it stores the inner lengths only,
     transform_step.cc:1015-1023) and the divisor legaliser guarantees to be exact (conv2d_slot_tables)."""
-    OH, OW = (H + pad_after - KH) // stride + 1, (W + pad_after - KW) // stride + 1
+    pad = pad_before + pad_after
+    OH, OW = (H + pad - KH) // stride + 1, (W + pad - KW) // stride + 1
     t = SketchTemplate(23)
     length = {0: N, 4: OH, 8: OW, 12: CO, 16: KH, 18: KW, 20: CI}         # first slot of an axis -> the axis length
     data, kernel, bias = t.buffer("placeholder", (N, H, W, CI)), t.buffer("placeholder", (KH, KW, CI, CO)), t.buffer("placeholder", (1, 1, 1, CO))
-    Pad, Conv, Relu = (t.buffer("PaddedInput", (N, H + pad_after, W + pad_after, CI)), t.buffer("Conv2dOutput", (N, OH, OW, CO)),
+    Pad, Conv, Relu = (t.buffer("PaddedInput", (N, H + pad, W + pad, CI)), t.buffer("Conv2dOutput", (N, OH, OW, CO)),
                        t.buffer("T_relu", (N, OH, OW, CO)))
     sl = CONV2D_SLOTS
     groups = {g[0]: g for g in (sl[k] for k in ("n", "y", "x", "f", "ry", "rx", "rc"))}
@@ -487,7 +489,11 @@ def conv2d_nhwc_cpu_template(N=1, H=56, W=56, CI=64, CO=128, KH=3, KW=3, stride=
             with t.loops(("i0", S(*n[1:])), ("i1", rows), ("i2", cols), ("i3", t.const(CI))) as (i0, i1, i2, i3):
                 ix = [lin([(n0, S(*n[1:])), (V(i0), None)]), lin([(y0, S(*y[1:], const=stride)), (V(i1), None)]),
                       lin([(x0, S(*x[1:], const=stride)), (V(i2), None)]), V(i3)]
-                t.store(Pad, ix, reads=[(data, ix)], ops={"float_math_func": 1, "int_cmp": 2, "bool_op": 1})
+                # PaddedInput(i0, i1, i2, i3) = tir.if_then_else(i1 >= 1 && i1 < 57 && i2 >= 1 && i2 < 57,
+                #                                                   placeholder[i0, i1 - 1, i2 - 1, i3], 0f)   (README.md:70)
+                shift = t.const(-pad_before)
+                src = [ix[0], add(ix[1], C(shift)), add(ix[2], C(shift)), ix[3]] if pad_before else ix
+                t.store(Pad, ix, reads=[(data, src)], ops={"float_math_func": 1, "int_cmp": 4, "bool_op": 3})
         with t.loops(("ax3.0", S(f[0])), ("ax0.1", S(n[1])), ("ax1.1", S(y[1])), ("ax2.1", S(x[1])), ("ax3.1", S(f[1]))) as (f0, n1, y1, x1, f1):
             outer = lambda ax, v0, v1: [(v0, S(*ax[1:])), (V(v1), S(*ax[2:]))]
             fo = [(V(f0), S(*f[1:])), (V(f1), S(*f[2:]))]
@@ -519,15 +525,17 @@ def conv2d_nhwc_cpu_template(N=1, H=56, W=56, CI=64, CO=128, KH=3, KW=3, stride=
             with t.loops(("ax0.2", S(*n[2:])), ("ax1.2", S(*y[2:])), ("ax2.2", S(*x[2:])), ("ax3.2", S(*f[2:]), "vectorize")) as (a, b, c, d):
                 ix = [lin(outer(n, n0, n1) + [(V(a), None)]), lin(outer(y, y0, y1) + [(V(b), None)]), lin(outer(x, x0, x1) + [(V(c), None)]),
                       lin(fo + [(V(d), None)])]
-                t.store(Relu, ix, reads=[(Conv, ix), (bias, [C(zero), C(zero), C(zero), ix[3]])], ops={"float_addsub": 1, "float_cmp": 1})
+                # T_relu = max(Conv2dOutput[ax0, ax1, ax2, ax3] + placeholder[ax0, 0, 0, ax3], 0f)  (T_add inlined; README.md:74-75)
+                t.store(Relu, ix, reads=[(Conv, ix), (bias, [ix[0], C(zero), C(zero), ix[3]])], ops={"float_addsub": 1, "float_cmp": 1})
     return t
 
 
-def conv2d_slot_tables(N=1, H=56, W=56, CI=64, CO=128, KH=3, KW=3, stride=2, pad_after=1, max_innermost=64):
+def conv2d_slot_tables(N=1, H=56, W=56, CI=64, CO=128, KH=3, KW=3, stride=2, pad_before=1, pad_after=0, max_innermost=64):
     """(slot_extent int32[23], slot_last uint8[23]) for vaex_decode_snap / vaex_legalise_extents in divisor mode with
     conv2d_nhwc_cpu_template(derive_outer=True): the inner levels of an axis are the lengths of its SplitStep (their product
     must divide the axis length, the innermost one at most max_innermost); the outermost levels and the unroll slot are free."""
-    OH, OW = (H + pad_after - KH) // stride + 1, (W + pad_after - KW) // stride + 1
+    pad = pad_before + pad_after
+    OH, OW = (H + pad - KH) // stride + 1, (W + pad - KW) // stride + 1
     ext, last = np.zeros(23, np.int32), np.zeros(23, np.uint8)
     for key, E in (("n", N), ("y", OH), ("x", OW), ("f", CO), ("ry", KH), ("rx", KW), ("rc", CI)):
         g = CONV2D_SLOTS[key]
