@@ -108,3 +108,28 @@ def test_sketch_scorer_pipeline():
     assert np.linalg.norm(got - want) / np.linalg.norm(want) < 1e-3
     again, _ = sc.score(z)
     assert torch.equal(again, scores)
+
+
+def test_rows_at_bench_size_are_position_independent():
+    """Size-independent properties at the bench's batch (2^20 candidates would need 2 GB twice; 2^18 here): every value is
+    finite, a candidate's rows do not depend on where it sits in the batch (a permutation of the extents permutes the rows
+    bit for bit), and the work-invariant features agree across all candidates of the task (float ops of the Conv2dOutput row:
+    57.8 M multiplies whatever the tiling)."""
+    t = SF.conv2d_nhwc_cpu_template(derive_outer=True)
+    sk = SF.SketchFeatures(t)
+    n = 1 << 18
+    g = torch.Generator(device="cuda").manual_seed(9)
+    e = torch.ones(n, 23, dtype=torch.int32, device="cuda")
+    divs = {"y": [1, 2, 4, 7, 14, 28], "x": [1, 2, 4, 7, 14, 28], "f": [1, 2, 4, 8, 16, 32], "rc": [1, 2, 4, 8, 16, 64], "ry": [1, 3], "rx": [1, 3]}
+    for key, ds in divs.items():
+        sl = SF.CONV2D_SLOTS[key]
+        d = torch.tensor(ds, dtype=torch.int32, device="cuda")
+        e[:, sl[-1]] = d[torch.randint(0, len(ds), (n,), device="cuda", generator=g)]          # one non-trivial inner level per axis
+    e[:, 22] = torch.tensor([0, 16, 64, 512], dtype=torch.int32, device="cuda")[torch.randint(0, 4, (n,), device="cuda", generator=g)]
+    rows = sk.rows(e).view(n, 3, 164)
+    assert torch.isfinite(rows).all()
+    perm = torch.randperm(n, device="cuda", generator=g)
+    assert torch.equal(sk.rows(e[perm].contiguous()).view(n, 3, 164), rows[perm])
+    conv = rows[:, 1, :]
+    want = float(np.log2(28 * 28 * 128 * 3 * 3 * 64 + 1.0))
+    assert float((conv[:, 2] - want).abs().max()) < 1e-5 and float((conv[:, 1] - want).abs().max()) < 1e-5     # float_mul, float_addsub
