@@ -140,3 +140,19 @@ def test_conv2d_template_matches_task_1264s_flop_count():
     assert sorted(t.buffers[b]["name"] for b in fs) == ["Conv2dOutput", "PaddedInput", "T_relu"]
     pad = fs[[b for b in fs if t.buffers[b]["name"] == "PaddedInput"][0]]
     assert float(pad["int_cmp"]) == 4 * 218880 and float(pad["bool_op"]) == 3 * 218880 and float(pad["float_math_func"]) == 218880
+
+
+def test_matmul_multi_level_tiling_template():
+    """Work invariants of the cache-write matmul sketch: 2 rows (C.local, C); M * N * K multiplies and M * N stores whatever the
+    tiling; the derived-outer form equals the explicit one on legal tilings."""
+    full, derived = SF.matmul_mlt_cpu_template(256, 128, 64), SF.matmul_mlt_cpu_template(256, 128, 64, derive_outer=True)
+    names = PF.feature_names()
+    for e in ([4, 4, 4, 4, 2, 2, 4, 8, 8, 8, 64], [256, 1, 1, 1, 1, 1, 1, 128, 1, 64, 0], [1, 1, 1, 256, 128, 1, 1, 1, 64, 1, 512]):
+        rows, bufs = PF.evaluate(full.as_dict(), e)
+        assert [full.buffers[b]["name"] for b in bufs] == ["C.local", "C"]
+        local, out = dict(zip(names, rows[0])), dict(zip(names, rows[1]))
+        assert abs(local["float_mul"] - np.log2(256 * 128 * 64 + 1.0)) < 1e-5 and abs(out["outer_prod"] - np.log2(256 * 128 + 1.0)) < 1e-5
+        junk = list(e)
+        junk[0] = junk[4] = junk[8] = 999
+        rows_d, _ = PF.evaluate(derived.as_dict(), junk)
+        assert np.array_equal(rows, rows_d)

@@ -52,6 +52,16 @@ def test_conv2d_template_random_extents():
     check(t, ext.tolist())
 
 
+def test_matmul_multi_level_tiling_template_random_extents():
+    rng = np.random.default_rng(6)
+    div = np.array([1, 1, 2, 4, 8, 16, 32, 64])
+    for derive in (False, True):
+        t = SF.matmul_mlt_cpu_template(512, 512, 512, derive_outer=derive)
+        ext = rng.choice(div, size=(150, t.n_slots))
+        ext[:, 10] = rng.choice([0, 16, 64, 512], size=150)
+        check(t, ext.tolist())
+
+
 def test_ragged_batch_and_errors():
     t = SF.matmul_cpu_template(64, 64, 64)
     sk = SF.SketchFeatures(t)

@@ -600,3 +600,57 @@ class SketchScorer:
         _lib.check(lib.vaex_segsum_mlp_forward(self.cost_model.packed(self.fea_norm_vec).h, _lib.ptr(rows), _lib.ptr(offsets), n,
                                                rows.shape[0], _lib.ptr(scores), 0, st))
         return scores, ext
+
+
+# slots of matmul_mlt_cpu_template: four tile levels of i and j, two of k, the unroll pragma
+MATMUL_SLOTS = {"i": (0, 1, 2, 3), "j": (4, 5, 6, 7), "k": (8, 9), "unroll": 10}
+
+
+def matmul_mlt_cpu_template(M=512, N=512, K=512, derive_outer=False):
+    """C[i, j] = sum_k A[i, k] * B[k, j] under Ansor's CPU sketch for an output stage without a consumer: multi-level tiling
+    "SSRSRS" on a cache-write stage C.local computed at the second tile level of C, the two outer tile levels of C fused and
+    parallelised, the innermost j tile vectorised in both stages (the CPU counterpart of the loop nest printed at
+    tests/python/unittest/test_auto_scheduler_feature.py:173-195).  Extent vector (11 slots, MATMUL_SLOTS): i and j in four
+    levels, k in two, auto_unroll_max_step.  Two statement rows per candidate (C.local, C)."""
+    t = SketchTemplate(11)
+    A, B = t.buffer("A", (M, K)), t.buffer("B", (K, N))
+    Cl, Cb = t.buffer("C.local", (M, N)), t.buffer("C", (M, N))
+    sl = MATMUL_SLOTS
+    length = {0: M, 4: N, 8: K}
+    groups = {g[0]: g for g in (sl["i"], sl["j"], sl["k"])}
+
+    def S(*slots, const=1, add=0):
+        mul_, div_ = [], []
+        for s_ in slots:
+            if derive_outer and s_ in length:
+                const *= length[s_]
+                div_ += list(groups[s_][1:])
+            else:
+                mul_.append(s_)
+        for s_ in list(mul_):
+            if s_ in div_:
+                mul_.remove(s_)
+                div_.remove(s_)
+        return t.scalar(const, tuple(mul_), tuple(div_), add)
+
+    i, j, k = sl["i"], sl["j"], sl["k"]
+    with t.loop("i.0@j.0@", S(i[0], j[0]), "parallel") as p:
+        i0, j0 = floordiv(V(p), C(S(j[0]))), floormod(V(p), C(S(j[0])))
+        with t.loops(("i.1", S(i[1])), ("j.1", S(j[1]))) as (i1, j1):
+            io = [(i0, S(*i[1:])), (V(i1), S(*i[2:]))]
+            jo = [(j0, S(*j[1:])), (V(j1), S(*j[2:]))]
+            with t.realize(Cl, [S(*i[2:]), S(*j[2:])]):
+                with t.pragma_unroll(S(sl["unroll"])):
+                    with t.loops(("i_c.2.init", S(i[2])), ("j_c.2.init", S(j[2])), ("i_c.3.init", S(i[3])),
+                                 ("j_c.3.init", S(j[3]), "vectorize")) as (a2, b2, a3, b3):
+                        t.store(Cl, [lin(io + [(V(a2), S(i[3])), (V(a3), None)]), lin(jo + [(V(b2), S(j[3])), (V(b3), None)])])
+                    with t.loops(("k.0", S(k[0])), ("i_c.2", S(i[2])), ("j_c.2", S(j[2])), ("k.1", S(k[1])), ("i_c.3", S(i[3])),
+                                 ("j_c.3", S(j[3]), "vectorize")) as (k0, a2, b2, k1, a3, b3):
+                        ci = lin(io + [(V(a2), S(i[3])), (V(a3), None)])
+                        cj = lin(jo + [(V(b2), S(j[3])), (V(b3), None)])
+                        kk = lin([(V(k0), S(k[1])), (V(k1), None)])
+                        t.store(Cl, [ci, cj], reads=[(Cl, [ci, cj]), (A, [ci, kk]), (B, [kk, cj])], ops={"float_addsub": 1, "float_mul": 1})
+            with t.loops(("i.2", S(*i[2:])), ("j.2", S(*j[2:]), "vectorize")) as (a, b):
+                ix = [lin(io + [(V(a), None)]), lin(jo + [(V(b), None)])]
+                t.store(Cb, ix, reads=[(Cl, ix)])
+    return t
