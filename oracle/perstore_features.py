@@ -43,7 +43,7 @@ def scalar_values(template, extents):
         for s in mul:
             v *= int(extents[s])
         for s in div:
-            v //= int(extents[s])
+            v //= max(int(extents[s]), 1)
         out.append(v + int(add))
     return out
 
@@ -242,12 +242,12 @@ class _Walker:
     def _loop_of(self, n, kind):
         lp = self.loops.get(id(n))
         if lp is None:
-            lp = self.loops[id(n)] = _Loop(n["name"], self.S[n["extent"]], kind)
+            lp = self.loops[id(n)] = _Loop(n["name"], max(self.S[n["extent"]], 1), kind)
             n["_loop"] = lp
         return lp
 
     def _for(self, n):
-        ext = self.S[n["extent"]]
+        ext = max(self.S[n["extent"]], 1)               # an extent below 1 cannot come out of the snap; read as 1
         if ext == 1:                              # ScheduleOps drops trivial loops (MakeLoopNest, debug_keep_trivial_loop
             n["_loop"] = None                     # = false at feature.cc:1308): the var is its minimum, 0
             self.run(n["body"])
@@ -266,7 +266,7 @@ class _Walker:
 
     def _thread(self, n):
         """AttrStmt thread_extent / virtual_thread, feature.cc:613-658: a fake parallel For is pushed, even at extent 1."""
-        name, ext = n["name"], self.S[n["extent"]]
+        name, ext = n["name"], max(self.S[n["extent"]], 1)
         before = self.tlen[name]
         self.tlen[name] = self.tlen[name] * ext if name == "vthread" else ext
         self.is_gpu = True

@@ -58,6 +58,8 @@ def test_matmul_multi_level_tiling_template_random_extents():
     for derive in (False, True):
         t = SF.matmul_mlt_cpu_template(512, 512, 512, derive_outer=derive)
         ext = rng.choice(div, size=(150, t.n_slots))
+        if derive:                                # the derived outer level needs a legal tiling: inner levels multiply to a divisor of 512
+            ext = rng.choice(np.array([1, 2, 4, 8]), size=(150, t.n_slots))
         ext[:, 10] = rng.choice([0, 16, 64, 512], size=150)
         check(t, ext.tolist())
 

@@ -122,7 +122,7 @@ __device__ uint32_t simplify(const Prog& P, const Walk& W, const int32_t* e, uin
         else if (b.imm && b.val == 1) { r = a; kill(b.start, i); }
         else r.fhi = a.fhi * b.fhi;
       } else {                                            // floordiv / floormod by a positive constant
-        const int64_t c = b.val;
+        const int64_t c = max(b.val, (int64_t)1);
         if (a.zero) { r.zero = true; kill(a.start, i); }
         else if (c == 1) {
           if (k == T_DIV) { r = a; kill(b.start, i); } else { r.zero = true; kill(a.start, i); }
@@ -160,10 +160,12 @@ __device__ void bound(const Prog& P, const Walk& W, const int32_t* e, uint32_t a
         r.lo = min(min(c0, c1), min(c2, c3)); r.hi = max(max(c0, c1), max(c2, c3));
       } else if (k == T_DIV) {
         auto fd = [](int64_t x, int64_t c) { int64_t q = x / c; return (x % c != 0 && (x < 0)) ? q - 1 : q; };
-        r.lo = fd(a.lo, b.lo); r.hi = fd(a.hi, b.lo);
+        const int64_t c = max(b.lo, (int64_t)1);
+        r.lo = fd(a.lo, c); r.hi = fd(a.hi, c);
       } else {
-        if (a.lo >= 0) { if (a.hi < b.lo) r = a; else { r.lo = 0; r.hi = min(a.hi, b.lo - 1); } }
-        else { r.lo = 0; r.hi = b.lo - 1; }
+        const int64_t c = max(b.lo, (int64_t)1);
+        if (a.lo >= 0) { if (a.hi < c) r = a; else { r.lo = 0; r.hi = min(a.hi, c - 1); } }
+        else { r.lo = 0; r.hi = c - 1; }
       }
       st.push(r);
     }
@@ -213,7 +215,7 @@ __device__ bool bound_all_levels(const Prog& P, const Walk& W, const int32_t* e,
       r.zlo = min(x.zlo * c, x.zhi * c); r.zhi = max(x.zlo * c, x.zhi * c);
     } else {
       if (a.pos == -2 || b.pos != -1) return false;
-      const int64_t c = b.lo;
+      const int64_t c = max(b.lo, (int64_t)1);
       r = a;
       if (k == T_DIV) { r.lo = fd(a.lo, c); r.hi = fd(a.hi, c); r.zlo = fd(a.zlo, c); r.zhi = fd(a.zhi, c); }
       else {
@@ -277,11 +279,11 @@ __device__ __forceinline__ Term term_eval(const Walk& W, const int32_t* t) {
   if (r.pos < 0) return r;
   int64_t fhi = (int64_t)W.ext[r.loop] - 1;
   if (kind == TERM_DIV || kind == TERM_DIVMOD) {
-    const int64_t c = W.S[t[2]];
+    const int64_t c = max(W.S[t[2]], (int64_t)1);               // a divisor below 1 only arises from an illegal tiling
     if (c != 1) { if (fhi < c) return r; fhi /= c; ++r.n_dm; }
   }
   if (kind == TERM_MOD || kind == TERM_DIVMOD) {
-    const int64_t c = W.S[kind == TERM_MOD ? t[2] : t[3]];
+    const int64_t c = max(W.S[kind == TERM_MOD ? t[2] : t[3]], (int64_t)1);
     if (c == 1) return r;
     if (fhi >= c) { fhi = c - 1; ++r.n_dm; }
   }
