@@ -145,3 +145,31 @@ def test_rows_at_bench_size_are_position_independent():
     conv = rows[:, 1, :]
     want = float(np.log2(28 * 28 * 128 * 3 * 3 * 64 + 1.0))
     assert float((conv[:, 2] - want).abs().max()) < 1e-5 and float((conv[:, 1] - want).abs().max()) < 1e-5     # float_mul, float_addsub
+
+
+def test_sketch_chain_is_graph_capturable():
+    """After one warm-up call the whole chain (decode + snap + legalise -> feature rows -> SegmentSum-MLP) launches without
+    touching the host: captured once into a CUDA graph, a replay on new latents reproduces the eager scores bit for bit."""
+    import vaex_b200
+    torch.manual_seed(11)
+    t = SF.conv2d_nhwc_cpu_template(derive_outer=True)
+    se, sl = SF.conv2d_slot_tables()
+    vae = vaex_b200.VAE_feature_head(23, None, 64, 256).cuda().eval()
+    net = vaex_b200.SegmentSumMLPModule(164, 256, 1).cuda().eval()
+    rng = np.random.default_rng(11)
+    sc = SF.SketchScorer(vae, rng.uniform(0.5, 3, 23).astype(np.float32), rng.uniform(0.3, 1.5, 23).astype(np.float32), t, net, se, sl)
+    z = torch.randn(4096, 64, device="cuda")
+    sc.score(z)                                            # warm-up: packs the models, checks the program, sizes the workspaces
+    torch.cuda.synchronize()
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=side, capture_error_mode="thread_local"):
+        out, _ = sc.score(z)
+    torch.cuda.current_stream().wait_stream(side)
+    z.copy_(torch.randn(4096, 64, device="cuda"))
+    g.replay()
+    torch.cuda.synchronize()
+    replayed = out.clone()
+    eager, _ = sc.score(z)
+    assert torch.equal(replayed, eager)

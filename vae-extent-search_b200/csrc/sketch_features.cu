@@ -24,7 +24,9 @@
 //               v * c, (v // c1) * c, (v % c1) * c, ((v // c1) % c2) * c and constants;  token = kind | arg << 4: VAR(loop) CONST(scalar) ADD MUL(which operand is a leaf) DIV MOD
 //
 // Each warp stages its 32 rows in shared memory and writes them out as contiguous 656-byte rows (coalesced).
+#include <algorithm>
 #include <cstdint>
+#include <mutex>
 #include <cstdlib>
 
 #include "../../include/vaex_b200.h"
