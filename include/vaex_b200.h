@@ -276,7 +276,7 @@ int vaex_latent_min_dist(const float* zc_dev, int64_t M, const float* zu_dev, in
  * lowered loop nest.  program_dev: the int32 program of vae-extent-search_b200/sketch_features.py SketchTemplate.compile()
  * (layout in csrc/sketch_features.cu); extents_dev int32 [n, slots]; rows_dev fp32 [n * rows, 164], candidate-major, i.e.
  * a SegmentSum-MLP batch whose segments all have `rows` statements.  The first call with a given program (device address,
- * length) reads its header back and checks it (one sync); later calls launch without touching the host, so the call is
+ * length) reads the program back and checks every offset, count and id in it (one sync; VAEX_E_INVALID for a damaged program); later calls launch without touching the host, so the call is
  * capturable into a CUDA graph after a warm-up call.  A buffer that is reused for a DIFFERENT program must not keep its
  * address and length (the Python wrapper allocates one tensor per compiled template). */
 int vaex_sketch_features(const int32_t* program_dev, int32_t program_words, const int32_t* extents_dev, int64_t n,

@@ -173,3 +173,25 @@ def test_sketch_chain_is_graph_capturable():
     replayed = out.clone()
     eager, _ = sc.score(z)
     assert torch.equal(replayed, eager)
+
+
+def test_corrupted_programs_are_rejected():
+    """The library checks every offset, count and id of a program the first time it sees it: a damaged program is an error
+    return, not a kernel walking off its tables."""
+    t = SF.conv2d_nhwc_cpu_template()
+    good = t.compile()
+    e = torch.ones(4, 23, dtype=torch.int32, device="cuda")
+    out = torch.empty(12, 164, device="cuda")
+    lib = _lib.load()
+    o_in, o_st, o_ex = int(good[9]), int(good[10]), int(good[11])
+    cases = {"token count": (o_ex, 1000), "instruction": (o_in, 99), "loop id": (o_in + 1, 5), "store buffer": (o_st, 77),
+             "section order": (9, int(good[10]) + 5), "slots": (1, 0)}
+    for name, (pos, val) in cases.items():
+        bad = good.copy()
+        bad[pos] = val
+        prog = torch.from_numpy(bad).cuda()
+        with pytest.raises(_lib.VaexError, match="sketch program"):
+            _lib.check(lib.vaex_sketch_features(_lib.ptr(prog), prog.numel(), _lib.ptr(e), 4, _lib.ptr(out), _lib.stream_ptr()))
+    prog = torch.from_numpy(good).cuda()
+    _lib.check(lib.vaex_sketch_features(_lib.ptr(prog), prog.numel(), _lib.ptr(e), 4, _lib.ptr(out), _lib.stream_ptr()))
+    assert torch.isfinite(out).all()

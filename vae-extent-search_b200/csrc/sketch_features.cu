@@ -27,6 +27,7 @@
 #include <algorithm>
 #include <cstdint>
 #include <mutex>
+#include <vector>
 #include <cstdlib>
 
 #include "../../include/vaex_b200.h"
