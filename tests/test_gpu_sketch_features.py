@@ -195,3 +195,40 @@ def test_corrupted_programs_are_rejected():
     prog = torch.from_numpy(good).cuda()
     _lib.check(lib.vaex_sketch_features(_lib.ptr(prog), prog.numel(), _lib.ptr(e), 4, _lib.ptr(out), _lib.stream_ptr()))
     assert torch.isfinite(out).all()
+
+
+def test_mlpmodel_predict_extents_matches_predict_on_the_same_rows():
+    """MLPModel.predict_extents(task, template, extents) = MLPModel.predict's scoring (mlp_model.py:832-846) on the rows the
+    template implies: equal, at the tensor path's tolerance, to the reference order of operations -- rows for every
+    candidate (here the oracle's), normalised by fea_norm_vec, SegmentSumMLP forward -- with and without the task embedding."""
+    import vaex_b200
+    from oracle import torch_oracle as O
+
+    class _Task:
+        workload_key, target = "dense-softmax-key", "llvm"
+
+    t = SF.matmul_mlt_cpu_template(256, 256, 256)
+    rng = np.random.default_rng(21)
+    ext = rng.choice([1, 2, 4, 8, 16], size=(300, 11)).astype(np.int32)
+    rows = np.concatenate([PF.evaluate(t.as_dict(), e.tolist())[0] for e in ext], 0)
+    for emb_on in (False, True):
+        torch.manual_seed(6)
+        mm = vaex_b200.MLPModel()
+        mm.model = vaex_b200.MLPModelInternal(device="cuda:0", use_workload_embedding=emb_on)
+        F = 174 if emb_on else 164
+        mm.model.base_model = vaex_b200.SegmentSumMLPModule(F, 256, 1).cuda()
+        norm = np.concatenate([np.maximum(rows.max(0), 1e-3), np.full(F - 164, 1.0, np.float32)]).astype(np.float32)
+        mm.model.fea_norm_vec = torch.from_numpy(norm)
+        got = mm.predict_extents(_Task, t, ext)
+        assert got.shape == (300,) and np.isfinite(got).all()
+        emb = mm.model._task_embedding(vaex_b200.LearningTask(_Task.workload_key, _Task.target))
+        full = rows if emb is None else np.concatenate([rows, np.broadcast_to(emb, (len(rows), 10))], 1)
+        P = {k: v.detach().cpu() for k, v in mm.model.base_model.state_dict().items()}
+        want = O.segsum_mlp_forward(P, np.full(300, t.n_rows, np.int32), torch.from_numpy((full / norm).astype(np.float32))).numpy()
+        # fp16 operands on two-row programs with scores around 0.03: 1.6e-3 measured; the fp32 kernels pin the arithmetic
+        assert np.linalg.norm(got - want) / np.linalg.norm(want) < 3e-3
+        simt = mm.predict_extents(_Task, t, ext, flags=_lib.F_MASK_INVALID | _lib.F_FORCE_SIMT)
+        assert np.linalg.norm(simt - want) / np.linalg.norm(want) < 2e-5
+    mm = vaex_b200.MLPModel()
+    mm.model = None
+    assert mm.predict_extents(_Task, t, ext).shape == (300,)              # no trained model: random scores, like predict

@@ -672,6 +672,33 @@ class MLPModel(PythonBasedModel):
             ret[np.maximum.reduceat(np.abs(flat).max(axis=1), starts) == 0] = float('-inf')
         return ret
 
+    def predict_extents(self, task, features_of_sketch, extents, flags=_lib.F_MASK_INVALID):
+        """predict(task, states) (mlp_model.py:832-846) for candidates of ONE sketch given by their tile extents: the rows
+        get_per_store_features_from_states would extract through TVM come from the sketch's template on the GPU
+        (sketch_features.SketchFeatures), and never leave it.  extents: int32 [n, slots] (CUDA tensor or array).
+        -> np.float32[n] scores (random scores without a trained model, like predict).  flags: VAEX_F_* of the row encoder."""
+        from . import sketch_features as SF
+        if not isinstance(features_of_sketch, SF.SketchFeatures):
+            features_of_sketch = SF.SketchFeatures(features_of_sketch)
+        e = extents if isinstance(extents, torch.Tensor) else torch.as_tensor(np.asarray(extents, dtype=np.int32))
+        e = e.to(device=features_of_sketch.program.device, dtype=torch.int32)
+        n = e.shape[0]
+        if self.model is None or n == 0:
+            return np.random.uniform(0, 1, (n,))
+        learning_task = LearningTask(task.workload_key, str(task.target))
+        inner = self.model
+        net = inner.local_model[learning_task] if inner.few_shot_learning.startswith("local_only") else inner.base_model
+        if net is None:
+            return np.zeros(n, dtype=np.float32)
+        rows = features_of_sketch.rows(e)
+        R = features_of_sketch.n_rows
+        offsets = torch.arange(0, (n + 1) * R, R, dtype=torch.int32, device=rows.device)
+        scores = torch.empty(n, device=rows.device)
+        m = net.packed(inner.fea_norm_vec, inner._task_embedding(learning_task))
+        _lib.check(_lib.load().vaex_segsum_mlp_forward(m.h, _lib.ptr(rows), _lib.ptr(offsets), n, rows.shape[0], _lib.ptr(scores),
+                                                      flags, _lib.stream_ptr()))
+        return scores.cpu().numpy()
+
     def predict(self, task, states):
         """mlp_model.py:832-846.  Needs TVM for the feature extraction itself; the packed bytes it returns go
         straight to the C++ parser (feature.py:224-246 without unpack_feature)."""
