@@ -288,6 +288,26 @@ class SketchTemplate:
                     offs = [expr(e) for e in ix]
                     stores.extend(offs)
                     listed.extend(offs)
+                # one read (or the write) whose indices are all in term form: its terms, innermost loop first (a loop's id is
+                # its nesting depth), constants last -- the device then takes the access through all loop levels in one walk
+                # with the per-dimension widths in registers.  entry = loop id + 1 (0: constant) | dim << 8 | term << 12
+                walk_ = []
+                if len(tuples) == 1:
+                    per_dim = [_terms(e) for e in tuples[0]]
+                    if all(tm is not None and len(tm) <= MAX_TERMS for tm in per_dim):
+                        for d_, tm in enumerate(per_dim):
+                            for ti, (kind, lp, _, _, _) in enumerate(tm):
+                                walk_.append(((loop_id[id(lp)] + 1) if kind != TERM_CONST else 0, d_, ti))
+                        walk_.sort(key=lambda w_: -w_[0])
+                    else:
+                        walk_ = None
+                else:
+                    walk_ = None
+                if walk_ is None:
+                    stores.append(-1)
+                else:
+                    stores.append(len(walk_))
+                    stores.extend(l_ | (d_ << 8) | (ti << 12) for l_, d_, ti in walk_)
             # every BufferLoad's indices: their arithmetic counts as int ops (MathOpCounter): (position in the list above or
             # -1, expression offset) per index
             loads = [expr(e) for _, ix in n["reads"] for e in ix]
