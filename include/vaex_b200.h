@@ -281,6 +281,11 @@ int vaex_latent_min_dist(const float* zc_dev, int64_t M, const float* zu_dev, in
  * address and length (the Python wrapper allocates one tensor per compiled template). */
 int vaex_sketch_features(const int32_t* program_dev, int32_t program_words, const int32_t* extents_dev, int64_t n,
                          float* rows_dev, void* stream);
+/* The same rows narrowed to IEEE fp16 with cvt.rn.satfinite (rows_f16_dev [n * rows, 164] halves): the input the tcgen05 row
+ * encoder takes under VAEX_F_FEATS_F16 -- it rounds fp32 rows to fp16 in exactly this way before its first GEMM, so the
+ * scores are bit-identical while half the bytes are written and read. */
+int vaex_sketch_features_f16(const int32_t* program_dev, int32_t program_words, const int32_t* extents_dev, int64_t n,
+                             uint16_t* rows_f16_dev, void* stream);
 /* multi-step ascent z += lr * dcost/dz (new surface, BASELINE config 3) */
 int vaex_latent_ascent(vaex_model_t h, float* z_inout_dev, int64_t n, int32_t steps, float lr,
                        float* cost_dev, void* stream);

@@ -232,3 +232,26 @@ def test_mlpmodel_predict_extents_matches_predict_on_the_same_rows():
     mm = vaex_b200.MLPModel()
     mm.model = None
     assert mm.predict_extents(_Task, t, ext).shape == (300,)              # no trained model: random scores, like predict
+
+
+def test_fp16_rows_are_the_narrowed_fp32_rows_and_score_identically():
+    """vaex_sketch_features_f16 = cvt.rn.satfinite of the fp32 rows, element for element (odd batch sizes, the row tail of
+    36 values, the allocation features patched in at the end); and because the tcgen05 row encoder narrows fp32 rows in the
+    same way before its first GEMM, the SegmentSum-MLP scores from either are bit-identical."""
+    import vaex_b200
+    torch.manual_seed(13)
+    net = vaex_b200.SegmentSumMLPModule(164, 256, 1).cuda().eval()
+    for tmpl in (SF.conv2d_nhwc_cpu_template(), SF.matmul_mlt_cpu_template(256, 256, 256)):
+        sk = SF.SketchFeatures(tmpl)
+        for n in (1, 31, 65, 4097):
+            e = torch.randint(1, 9, (n, tmpl.n_slots), dtype=torch.int32, device="cuda")
+            r32 = sk.rows(e)
+            r16 = sk.rows(e, half=True)
+            assert r16.dtype == torch.float16 and torch.equal(r16, r32.clamp(-65504, 65504).half())
+            off = torch.arange(0, (n + 1) * sk.n_rows, sk.n_rows, dtype=torch.int32, device="cuda")
+            s32, s16 = torch.empty(n, device="cuda"), torch.empty(n, device="cuda")
+            h = net.packed().h
+            _lib.check(_lib.load().vaex_segsum_mlp_forward(h, _lib.ptr(r32), _lib.ptr(off), n, r32.shape[0], _lib.ptr(s32), 0, _lib.stream_ptr()))
+            _lib.check(_lib.load().vaex_segsum_mlp_forward(h, _lib.ptr(r16), _lib.ptr(off), n, r16.shape[0], _lib.ptr(s16), _lib.F_FEATS_F16,
+                                                           _lib.stream_ptr()))
+            assert torch.equal(s32, s16)

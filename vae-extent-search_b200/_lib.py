@@ -99,6 +99,7 @@ SIGNATURES = {
     "vaex_kcenter_select": ([vp, i64, i32, vp, i64, vp, i64, i32, f32, vp, vp], ctypes.c_int),
     "vaex_fps_select": ([vp, i64, i32, vp, i64, i64, i32, vp, vp], ctypes.c_int),
     "vaex_sketch_features": ([vp, i32, vp, i64, vp, vp], ctypes.c_int),
+    "vaex_sketch_features_f16": ([vp, i32, vp, i64, vp, vp], ctypes.c_int),
     "vaex_latent_min_dist": ([vp, i64, vp, i64, i32, vp, vp], ctypes.c_int),
     "vaex_segcost_mc_predict": ([vp, vp, i64, i32, vp, u64, f32, vp, vp, vp], ctypes.c_int),
     "vaex_nccl_unique_id": ([vp], ctypes.c_int),

@@ -393,7 +393,8 @@ class SketchFeatures:
         self.n_rows, self.n_slots = template.n_rows, template.n_slots
         self.program = torch.from_numpy(template.compile()).to(device)
 
-    def rows(self, extents, out=None):
+    def rows(self, extents, out=None, half=False):
+        """half: fp16 rows (cvt.rn.satfinite) for the row encoder's VAEX_F_FEATS_F16 input -- same scores, half the bytes"""
         e = extents
         if not e.is_cuda:
             raise _lib.VaexError("vaex_b200 needs CUDA tensors (no CPU fallback)")
@@ -403,9 +404,10 @@ class SketchFeatures:
             raise ValueError("extents must be [n, %d]" % self.n_slots)
         n = e.shape[0]
         if out is None:
-            out = torch.empty(n * self.n_rows, ROW, device=e.device)
-        _lib.check(_lib.load().vaex_sketch_features(_lib.ptr(self.program), self.program.numel(), _lib.ptr(e), n, _lib.ptr(out),
-                                                   _lib.stream_ptr()))
+            out = torch.empty(n * self.n_rows, ROW, device=e.device, dtype=torch.float16 if half else torch.float32)
+        half = out.dtype == torch.float16
+        fn = _lib.load().vaex_sketch_features_f16 if half else _lib.load().vaex_sketch_features
+        _lib.check(fn(_lib.ptr(self.program), self.program.numel(), _lib.ptr(e), n, _lib.ptr(out), _lib.stream_ptr()))
         return out
 
     def segment_sizes(self, n, device="cuda"):
@@ -597,7 +599,7 @@ class SketchScorer:
         if b is None:
             R = self.features.n_rows
             b = self._buf[n] = (torch.empty(n, self.features.n_slots, dtype=torch.int32, device=dev),
-                                torch.empty(n * R, ROW, device=dev),
+                                torch.empty(n * R, ROW, device=dev, dtype=torch.float16),       # the row encoder's fp16 input
                                 torch.arange(0, (n + 1) * R, R, dtype=torch.int32, device=dev),
                                 torch.empty(n, device=dev))
             if len(self._buf) > 4:
@@ -618,7 +620,7 @@ class SketchScorer:
                                         self.mode, _lib.ptr(self.slot_extent), _lib.ptr(self.slot_last), self.max_innermost, st))
         self.features.rows(ext, out=rows)
         _lib.check(lib.vaex_segsum_mlp_forward(self.cost_model.packed(self.fea_norm_vec).h, _lib.ptr(rows), _lib.ptr(offsets), n,
-                                               rows.shape[0], _lib.ptr(scores), 0, st))
+                                               rows.shape[0], _lib.ptr(scores), _lib.F_FEATS_F16, st))
         return scores, ext
 
 
