@@ -671,7 +671,8 @@ def main_vaex(args):
             "what": "per rank 2^20 latents -> decode + snap + legalise (23 tile extents, conv2d sketch) -> %d feature rows per candidate "
                     "from the sketch template (vaex_sketch_features) -> SegmentSum-MLP -> top-%d -> merge; device-resident" % (R6, TOPK),
             "latents_per_gpu": n6, "n_gpus": world, "ms_per_step": ms6, "candidates_per_s": world * n6 / (ms6 * 1e-3),
-            "ms_feature_rows": ms6_rows, "feature_rows_GBps_written": n6 * R6 * F * 4 / (ms6_rows * 1e-3) / 1e9,
+            "ms_feature_rows": ms6_rows, "feature_rows_dtype": "fp16 (the row encoder's VAEX_F_FEATS_F16 input: same scores bit for bit)",
+            "feature_rows_GBps_written": n6 * R6 * F * 2 / (ms6_rows * 1e-3) / 1e9,
             "e2e": {"what": "host latents in (pinned, %d B per candidate, four chunks uploaded under the scoring of the previous one), top-%d out, "
                             "copies inside the timed region" % (4 * L_LAT, TOPK),
                     "ms_per_step": ms6_host, "candidates_per_s": world * n6 / (ms6_host * 1e-3),
