@@ -55,9 +55,11 @@ def main():
     rows = torch.empty(n * sk.n_rows, 164, device=dev)
     ms_dec = timed(decode)
     ms_rows = timed(lambda: sk.rows(ext, out=rows))
+    rows16 = torch.empty(n * sk.n_rows, 164, device=dev, dtype=torch.float16)
+    ms_rows16 = timed(lambda: sk.rows(ext, out=rows16))
     # scoring: the SegmentSum-MLP on the generated rows
     out = {"n": n, "rows_per_candidate": sk.n_rows, "program_words": int(sk.program.numel()), "ms_decode_snap_legalise": ms_dec,
-           "ms_sketch_rows": ms_rows, "candidates_per_s_rows": n / (ms_rows * 1e-3), "rows_GBps": n * sk.n_rows * 656 / (ms_rows * 1e-3) / 1e9,
+           "ms_sketch_rows": ms_rows, "ms_sketch_rows_f16": ms_rows16, "candidates_per_s_rows": n / (ms_rows * 1e-3), "rows_GBps": n * sk.n_rows * 656 / (ms_rows * 1e-3) / 1e9,
            "extent_sample": e[:3].tolist(), "distinct_candidates_in_first_4096": int(len({tuple(r) for r in e[:4096].tolist()}))}
     print(json.dumps(out))
 
