@@ -39,7 +39,7 @@
 namespace vaex {
 namespace sf {
 constexpr int MAX_SLOTS = 64, MAX_SCALARS = 48, MAX_LOOPS = 32, MAX_BUFS = 6, MAX_DIMS = 4, SCALAR_SLOTS = 12;       // an expression has at most 32 tokens
-constexpr int MAX_DEPTH = 24, MAX_ACC = 5, MAX_EXPR = 40, ROW = 164, WARPS = 2, THREADS = 32 * WARPS;
+constexpr int MAX_DEPTH = 24, MAX_ACC = 5, MAX_EXPR = 40, ROW = 164, WARPS = 8, THREADS = 32 * WARPS;
 constexpr int MAX_PROG = 4096;                            // words of program kept in shared memory
 constexpr int MAGIC = 0x56465831;
 enum { OP_FOR, OP_FOR_END, OP_THREAD, OP_THREAD_END, OP_PRAGMA, OP_PRAGMA_END, OP_REALIZE_END, OP_STORE };
