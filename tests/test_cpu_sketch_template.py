@@ -156,3 +156,59 @@ def test_matmul_multi_level_tiling_template():
         junk[0] = junk[4] = junk[8] = 999
         rows_d, _ = PF.evaluate(derived.as_dict(), junk)
         assert np.array_equal(rows, rows_d)
+
+
+# The transform steps of a measured llvm program of the same workload function (conv2d NHWC + bias + ReLU, hash 12b88bed...)
+# shipped with the reference: tutorials/auto_scheduler/ci_logs/resnet-50-NHWC-B1-llvm.json, line 14.
+CI_LOG_STEPS = [["CI", 5], ["SP", 3, 0, 1, [1, 1, 1], 1], ["SP", 3, 4, 112, [1, 1, 4], 1], ["SP", 3, 8, 112, [4, 2, 1], 1],
+                ["SP", 3, 12, 64, [1, 1, 16], 1], ["SP", 3, 16, 7, [7], 1], ["SP", 3, 18, 7, [7], 1], ["SP", 3, 20, 3, [3], 1],
+                ["RE", 3, [0, 4, 8, 12, 1, 5, 9, 13, 16, 18, 20, 2, 6, 10, 14, 17, 19, 21, 3, 7, 11, 15]],
+                ["FSP", 6, 0, 1, 2], ["FSP", 6, 3, 2, 2], ["FSP", 6, 6, 3, 2], ["FSP", 6, 9, 4, 2],
+                ["RE", 6, [0, 3, 6, 9, 1, 4, 7, 10, 2, 5, 8, 11]], ["CA", 3, 6, 7], ["CA", 1, 6, 3], ["FU", 6, [0, 1, 2]],
+                ["AN", 6, 0, 3], ["PR", 3, 0, "auto_unroll_max_step$64"], ["AN", 1, 3, 2], ["AN", 3, 21, 2], ["AN", 6, 9, 2]]
+
+
+def test_conv2d_template_has_the_structure_of_a_measured_ansor_record():
+    """The sketch the template states is the one Ansor's CPU policy produced for this workload in the reference's own logs:
+    the order of the 22 tile loops of Conv2dOutput (the record's reorder step: S S R S R S with ry, rx, rc inside each reduction
+    level), the consumer tiled to follow the two outer levels, Conv2dOutput attached under the consumer's second-level channel
+    loop, the three outer spatial tiles fused and parallelised, the innermost channel tiles vectorised, the unroll pragma on
+    Conv2dOutput.  (Where the padding stage is attached and how it is annotated varies from record to record.)"""
+    steps = CI_LOG_STEPS
+    # iterators of stage 3 after its seven splits: n 0-3, yy 4-7, xx 8-11, ff 12-15, ry 16-17, rx 18-19, rc 20-21
+    name = {}
+    for base, ax, levels in ((0, "nn", 4), (4, "yy", 4), (8, "xx", 4), (12, "ff", 4), (16, "ry", 2), (18, "rx", 2), (20, "rc", 2)):
+        for l in range(levels):
+            name[base + l] = "%s.%d" % (ax, l)
+    conv_order = [name[i] for i in [s for s in steps if s[0] == "RE" and s[1] == 3][0][2]]
+    cons = {}
+    for base, ax in ((0, "ax0"), (3, "ax1"), (6, "ax2"), (9, "ax3")):
+        for l in range(3):
+            cons[base + l] = "%s.%d" % (ax, l)
+    cons_order = [cons[i] for i in [s for s in steps if s[0] == "RE" and s[1] == 6][0][2]]
+    assert cons_order[:8] == ["ax0.0", "ax1.0", "ax2.0", "ax3.0", "ax0.1", "ax1.1", "ax2.1", "ax3.1"]
+    assert ["CA", 3, 6, 7] in steps and cons_order[7] == "ax3.1"            # Conv2dOutput computed at the consumer's ax3.1
+    assert ["FU", 6, [0, 1, 2]] in steps and ["AN", 6, 0, 3] in steps       # n.0, y.0, x.0 fused, parallel
+    t = SF.conv2d_nhwc_cpu_template()
+    path = {}                                                                # store buffer name (update store) -> enclosing loops
+
+    def walk(nodes, stack):
+        for n in nodes:
+            if n["kind"] in SF.KINDS:
+                walk(n["body"], stack + [(n["name"], n["kind"])])
+            elif n["kind"] in ("realize", "pragma_unroll"):
+                walk(n["body"], stack + ([("pragma", "pragma")] if n["kind"] == "pragma_unroll" else []))
+            elif n["kind"] == "store" and n.get("reads"):
+                path[t.buffers[n["buffer"]]["name"]] = stack
+    walk(t.body, [])
+    conv = path["Conv2dOutput"]
+    names = [nm for nm, _ in conv]
+    # consumer's outer loops (fused n.0 y.0 x.0, then ax3.0, ax0.1 .. ax3.1), the pragma, then Conv2dOutput's own 14 inner loops
+    assert names[:6] == ["ax0.0@ax1.0@ax2.0@", "ax3.0", "ax0.1", "ax1.1", "ax2.1", "ax3.1"] and conv[0][1] == "parallel"
+    assert names[6] == "pragma"
+    assert names[7:] == conv_order[8:]                                       # ry.0 rx.0 rc.0 | nn.2 .. ff.2 | ry.1 rx.1 rc.1 | nn.3 .. ff.3
+    assert conv[-1] == ("ff.3", "vectorize") and ["AN", 3, 21, 2] in steps and conv_order[21] == "ff.3"    # iterator 21 after the reorder
+    relu = path["T_relu"]
+    assert [nm for nm, _ in relu] == ["ax0.0@ax1.0@ax2.0@", "ax3.0", "ax0.1", "ax1.1", "ax2.1", "ax3.1", "ax0.2", "ax1.2", "ax2.2", "ax3.2"]
+    assert relu[-1][1] == "vectorize" and ["AN", 6, 9, 2] in steps          # after the fuse, iterator 9 of the consumer is ax3.2
+    assert [s for s in steps if s[0] == "PR"] == [["PR", 3, 0, "auto_unroll_max_step$64"]]
