@@ -212,3 +212,25 @@ def test_conv2d_template_has_the_structure_of_a_measured_ansor_record():
     assert [nm for nm, _ in relu] == ["ax0.0@ax1.0@ax2.0@", "ax3.0", "ax0.1", "ax1.1", "ax2.1", "ax3.1", "ax0.2", "ax1.2", "ax2.2", "ax3.2"]
     assert relu[-1][1] == "vectorize" and ["AN", 6, 9, 2] in steps          # after the fuse, iterator 9 of the consumer is ax3.2
     assert [s for s in steps if s[0] == "PR"] == [["PR", 3, 0, "auto_unroll_max_step$64"]]
+
+
+def test_template_and_extents_from_the_measured_record():
+    """conv2d_template_from_record on the reference's ci_logs record (224 x 224 x 3 -> 112 x 112 x 64, 7 x 7, stride 2): the
+    shapes and the padding (3 before, 2 after) from the workload key, the tile extents from the SplitSteps (each axis multiplies
+    back to its length), the padding stage attached one loop further in and vectorised as that record has it; the rows the
+    extractor then gives carry the workload's operation count."""
+    key = '["12b88bedece6984af589a28b43e0f3c4", 1, 224, 224, 3, 7, 7, 3, 64, 1, 1, 1, 64, 1, 112, 112, 64]'
+    rec = {"i": [[key, "llvm -keys=cpu -link-params=0 -mcpu=core-avx2"], [[], CI_LOG_STEPS]]}
+    t, ext = SF.conv2d_template_from_record(rec)
+    assert ext == [1, 1, 1, 1, 28, 1, 1, 4, 14, 4, 2, 1, 4, 1, 1, 16, 1, 7, 1, 7, 1, 3, 64]
+    for key, E in (("n", 1), ("y", 112), ("x", 112), ("f", 64), ("ry", 7), ("rx", 7), ("rc", 3)):
+        assert int(np.prod([ext[j] for j in SF.CONV2D_SLOTS[key]])) == E
+    assert t.buffers[3]["name"] == "PaddedInput" and t.buffers[3]["shape"] == [1, 229, 229, 3]
+    fs = PF.feature_sets(t.as_dict(), ext)
+    flops = sum(float(f[k]) for f in fs.values() for k in ("float_addsub", "float_mul", "float_cmp"))
+    assert flops == 2.0 * 112 * 112 * 64 * 7 * 7 * 3 + 2.0 * 112 * 112 * 64
+    pad = fs[3]
+    assert float(pad["vec_len"]) == 3.0 and float(pad["num_loops"]) == 5.0      # fused, ax3.0, i1, i2, i3 (vectorised); i0 is trivial
+    bad = {"i": [[key, "llvm"], [[], [s for s in CI_LOG_STEPS if s[0] != "RE"]]]}
+    with pytest.raises(ValueError):
+        SF.conv2d_template_from_record(bad)

@@ -52,6 +52,17 @@ def test_conv2d_template_random_extents():
     check(t, ext.tolist())
 
 
+def test_record_derived_conv2d_template():
+    """The template and extents read off the reference's measured ci_logs record (padding stage attached under ax3.0 and
+    vectorised, 7 x 7 stride-2 conv on 224 x 224 x 3), plus random tilings of it."""
+    from test_cpu_sketch_template import CI_LOG_STEPS
+    key = '["12b88bedece6984af589a28b43e0f3c4", 1, 224, 224, 3, 7, 7, 3, 64, 1, 1, 1, 64, 1, 112, 112, 64]'
+    t, ext = SF.conv2d_template_from_record({"i": [[key, "llvm"], [[], CI_LOG_STEPS]]})
+    rng = np.random.default_rng(8)
+    more = rng.choice(np.array([1, 1, 2, 4, 7, 8, 16]), size=(120, t.n_slots))
+    check(t, [ext] + more.tolist())
+
+
 def test_matmul_multi_level_tiling_template_random_extents():
     rng = np.random.default_rng(6)
     div = np.array([1, 1, 2, 4, 8, 16, 32, 64])

@@ -466,7 +466,8 @@ CONV2D_SLOTS = {"n": (0, 1, 2, 3), "y": (4, 5, 6, 7), "x": (8, 9, 10, 11), "f": 
 CONV2D_README_EXTENTS = [1, 1, 1, 1, 1, 1, 1, 28, 4, 7, 1, 1, 2, 8, 1, 8, 1, 3, 3, 1, 4, 16, 16]
 
 
-def conv2d_nhwc_cpu_template(N=1, H=56, W=56, CI=64, CO=128, KH=3, KW=3, stride=2, pad_before=1, pad_after=0, derive_outer=False):
+def conv2d_nhwc_cpu_template(N=1, H=56, W=56, CI=64, CO=128, KH=3, KW=3, stride=2, pad_before=1, pad_after=0, derive_outer=False,
+                             pad_at="fused", pad_vectorize=False):
     """conv2d NHWC + bias + ReLU under Ansor's CPU multi-level tiling sketch ("SSRSRS" with the consumer fused at the second
     tile level, the padding stage computed at the fused outer loop, the outer spatial tiles fused and parallelised, the
     innermost channel tile vectorised): task 1264 of the reference README -- its compute DAG (README.md:64-76) gives the
@@ -475,7 +476,12 @@ def conv2d_nhwc_cpu_template(N=1, H=56, W=56, CI=64, CO=128, KH=3, KW=3, stride=
     tile factors n, y, x, f (4 levels each, outermost first), ry, rx, rc (2 levels each) and auto_unroll_max_step.  Three
     statement rows per candidate.  derive_outer: the outermost level of every axis is not read from the vector but derived
     as axis length // product of the inner levels -- the form a SplitStep has (it stores the inner lengths only,
-    transform_step.cc:1015-1023) and the divisor legaliser guarantees to be exact (conv2d_slot_tables)."""
+    transform_step.cc:1015-1023) and the divisor legaliser guarantees to be exact (conv2d_slot_tables).  pad_at / pad_vectorize:
+    where the padding stage is computed ("fused": under the fused outer loop, as in the README program; "ax3.0": one loop
+    further in, as in the reference's ci_logs record -- Ansor samples this location per program) and whether its channel loop
+    is vectorised."""
+    if pad_at not in ("fused", "ax3.0"):
+        raise ValueError(pad_at)
     pad = pad_before + pad_after
     OH, OW = (H + pad - KH) // stride + 1, (W + pad - KW) // stride + 1
     t = SketchTemplate(23)
@@ -507,16 +513,24 @@ def conv2d_nhwc_cpu_template(N=1, H=56, W=56, CI=64, CO=128, KH=3, KW=3, stride=
         y0 = floormod(floordiv(V(p), C(S(x[0]))), C(S(y[0])))
         x0 = floormod(V(p), C(S(x[0])))
         rows, cols = S(*y[1:], const=stride, add=KH - stride), S(*x[1:], const=stride, add=KW - stride)
-        with t.realize(Pad, [S(*n[1:]), rows, cols, t.const(CI)]):
-            with t.loops(("i0", S(*n[1:])), ("i1", rows), ("i2", cols), ("i3", t.const(CI))) as (i0, i1, i2, i3):
-                ix = [lin([(n0, S(*n[1:])), (V(i0), None)]), lin([(y0, S(*y[1:], const=stride)), (V(i1), None)]),
-                      lin([(x0, S(*x[1:], const=stride)), (V(i2), None)]), V(i3)]
-                # PaddedInput(i0, i1, i2, i3) = tir.if_then_else(i1 >= 1 && i1 < 57 && i2 >= 1 && i2 < 57,
-                #                                                   placeholder[i0, i1 - 1, i2 - 1, i3], 0f)   (README.md:70)
-                shift = t.const(-pad_before)
-                src = [ix[0], add(ix[1], C(shift)), add(ix[2], C(shift)), ix[3]] if pad_before else ix
-                t.store(Pad, ix, reads=[(data, src)], ops={"float_math_func": 1, "int_cmp": 4, "bool_op": 3})
-        with t.loops(("ax3.0", S(f[0])), ("ax0.1", S(n[1])), ("ax1.1", S(y[1])), ("ax2.1", S(x[1])), ("ax3.1", S(f[1]))) as (f0, n1, y1, x1, f1):
+
+        def padding_stage():
+          with t.realize(Pad, [S(*n[1:]), rows, cols, t.const(CI)]):
+            with t.loops(("i0", S(*n[1:])), ("i1", rows), ("i2", cols),
+                         ("i3", t.const(CI), "vectorize" if pad_vectorize else "for")) as (i0, i1, i2, i3):
+                  ix = [lin([(n0, S(*n[1:])), (V(i0), None)]), lin([(y0, S(*y[1:], const=stride)), (V(i1), None)]),
+                        lin([(x0, S(*x[1:], const=stride)), (V(i2), None)]), V(i3)]
+                  # PaddedInput(i0, i1, i2, i3) = tir.if_then_else(i1 >= 1 && i1 < 57 && i2 >= 1 && i2 < 57,
+                  #                                                   placeholder[i0, i1 - 1, i2 - 1, i3], 0f)   (README.md:70)
+                  shift = t.const(-pad_before)
+                  src = [ix[0], add(ix[1], C(shift)), add(ix[2], C(shift)), ix[3]] if pad_before else ix
+                  t.store(Pad, ix, reads=[(data, src)], ops={"float_math_func": 1, "int_cmp": 4, "bool_op": 3})
+        if pad_at == "fused":
+            padding_stage()
+        with t.loop("ax3.0", S(f[0])) as f0:
+          if pad_at == "ax3.0":
+            padding_stage()
+          with t.loops(("ax0.1", S(n[1])), ("ax1.1", S(y[1])), ("ax2.1", S(x[1])), ("ax3.1", S(f[1]))) as (n1, y1, x1, f1):
             outer = lambda ax, v0, v1: [(v0, S(*ax[1:])), (V(v1), S(*ax[2:]))]
             fo = [(V(f0), S(*f[1:])), (V(f1), S(*f[2:]))]
             with t.realize(Conv, [S(*n[2:]), S(*y[2:]), S(*x[2:]), S(*f[2:])]):
@@ -676,3 +690,43 @@ def matmul_mlt_cpu_template(M=512, N=512, K=512, derive_outer=False):
                 ix = [lin(io + [(V(a), None)]), lin(jo + [(V(b), None)])]
                 t.store(Cb, ix, reads=[(Cl, ix)])
     return t
+
+
+def conv2d_template_from_record(record):
+    """(template, extents) for one measure record of the conv2d NHWC + bias + ReLU workload function (the records of
+    `tutorials/auto_scheduler/ci_logs/resnet-50-NHWC-B1-llvm.json`, TenSet's task 1264, ...): the shapes from the workload key
+    [hash, N, H, W, CI, KH, KW, CI, CO, 1, 1, 1, CO, N, OH, OW, CO], the tile extents from the seven SplitSteps of the
+    Conv2dOutput stage (their lengths are the inner levels; the outermost is extent // product), the unroll pragma, and the
+    two things Ansor samples per program about the padding stage: where it is attached and whether its channel loop is
+    vectorised.  Raises ValueError for a record of another sketch (different step pattern)."""
+    import json
+    rec = json.loads(record) if isinstance(record, (str, bytes)) else record
+    key = json.loads(rec["i"][0][0])
+    steps = rec["i"][1][1]
+    if len(key) != 17:
+        raise ValueError("not a conv2d NHWC + bias + ReLU workload key")
+    N, H, W, CI, KH, KW, _, CO = key[1:9]
+    OH, OW = key[14], key[15]
+    stride = max(1, round(H / OH))
+    total = (OH - 1) * stride + KH - H
+    sp = [s_ for s_ in steps if s_[0] == "SP" and s_[1] == 3]
+    if len(sp) != 7 or [len(s_[4]) for s_ in sp] != [3, 3, 3, 3, 1, 1, 1] or [s_[3] for s_ in sp] != [N, OH, OW, CO, KH, KW, CI]:
+        raise ValueError("the record's Conv2dOutput stage is not tiled S S R S R S (4 x 3 lengths, 3 x 1)")
+    reorder = [s_ for s_ in steps if s_[0] == "RE" and s_[1] == 3]
+    if not reorder or reorder[0][2] != [0, 4, 8, 12, 1, 5, 9, 13, 16, 18, 20, 2, 6, 10, 14, 17, 19, 21, 3, 7, 11, 15]:
+        raise ValueError("the record's loop order is not the template's")
+    if ["CA", 3, 6, 7] not in steps or ["FU", 6, [0, 1, 2]] not in steps:
+        raise ValueError("the record attaches / fuses the stages differently from the template")
+    ext = []
+    for s_ in sp:
+        inner = [int(v) for v in s_[4]]
+        ext += [int(s_[3]) // int(np.prod(inner))] + inner
+    pr = [s_ for s_ in steps if s_[0] == "PR" and s_[1] == 3]
+    ext.append(int(pr[0][3].split("$")[1]) if pr else 0)
+    pad_ca = [s_ for s_ in steps if s_[0] == "CA" and s_[1] == 1 and s_[2] == 6]
+    if not pad_ca or pad_ca[0][3] not in (2, 3):
+        raise ValueError("the padding stage is attached somewhere this template does not state")
+    pad_at = "ax3.0" if pad_ca[0][3] == 3 else "fused"        # iterators of the consumer before the fuse: n.0 y.0 x.0 f.0 ...
+    t = conv2d_nhwc_cpu_template(N, H, W, CI, CO, KH, KW, stride, (total + 1) // 2, total // 2, pad_at=pad_at,
+                                 pad_vectorize=["AN", 1, 3, 2] in steps)
+    return t, ext
