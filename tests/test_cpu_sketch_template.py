@@ -234,3 +234,27 @@ def test_template_and_extents_from_the_measured_record():
     bad = {"i": [[key, "llvm"], [[], [s for s in CI_LOG_STEPS if s[0] != "RE"]]]}
     with pytest.raises(ValueError):
         SF.conv2d_template_from_record(bad)
+
+
+def test_ranked_candidates_go_back_out_as_measure_records():
+    """conv2d_sketch_slots: the template's extent vector written back into the record's SplitSteps / pragma -- the record's
+    own extents reproduce its steps, a different legal tiling changes exactly the lengths, an illegal one is refused."""
+    import json
+    key = '["12b88bedece6984af589a28b43e0f3c4", 1, 224, 224, 3, 7, 7, 3, 64, 1, 1, 1, 64, 1, 112, 112, 64]'
+    rec = {"i": [[key, "llvm -keys=cpu -link-params=0 -mcpu=core-avx2"], [[], CI_LOG_STEPS]], "r": [[0.00025], 0, 0.3, 1606961659], "v": "v0.5"}
+    slots = SF.conv2d_sketch_slots(rec)
+    t, ext = SF.conv2d_template_from_record(rec)
+    back = json.loads(slots.records_from_extents(np.array([ext]))[0])
+    assert back["i"][1][1] == CI_LOG_STEPS and back["i"][0] == rec["i"][0]
+    other = list(ext)
+    other[5:8] = [2, 2, 7]                         # y: 112 = 4 * 2 * 2 * 7
+    other[22] = 512
+    steps = json.loads(slots.records_from_extents(np.array([other]))[0])["i"][1][1]
+    assert steps[2] == ["SP", 3, 4, 112, [2, 2, 7], 1] and steps[18] == ["PR", 3, 0, "auto_unroll_max_step$512"]
+    assert [s for k, s in enumerate(steps) if k not in (2, 18)] == [s for k, s in enumerate(CI_LOG_STEPS) if k not in (2, 18)]
+    other[5:8] = [3, 2, 7]
+    with pytest.raises(ValueError):
+        slots.records_from_extents(np.array([other]))
+    se, sl = slots.legalise_tables()[:2]
+    want_se, want_sl = SF.conv2d_slot_tables(1, 224, 224, 3, 64, 7, 7, 2, 3, 2)
+    assert np.array_equal(se, want_se) and np.array_equal(sl, want_sl)

@@ -730,3 +730,25 @@ def conv2d_template_from_record(record):
     t = conv2d_nhwc_cpu_template(N, H, W, CI, CO, KH, KW, stride, (total + 1) // 2, total // 2, pad_at=pad_at,
                                  pad_vectorize=["AN", 1, 3, 2] in steps)
     return t, ext
+
+
+def conv2d_sketch_slots(record):
+    """The extent.SketchSlots of the 23-slot vector of conv2d_nhwc_cpu_template for one measure record of that sketch: the
+    inner tile levels are the lengths of the record's SplitSteps, slot 22 its unroll pragma, the outermost levels derived.
+    With it the candidates the chain ranks highest go back out as measure-record lines (SketchSlots.records_from_extents),
+    the form the reference's search loop hands to TVM for measurement."""
+    import json
+    from .extent import SketchSlots
+    rec = json.loads(record) if isinstance(record, (str, bytes)) else record
+    steps = rec["i"][1][1]
+    sp = [k for k, s_ in enumerate(steps) if s_[0] == "SP" and s_[1] == 3]
+    pr = [k for k, s_ in enumerate(steps) if s_[0] == "PR" and s_[1] == 3]
+    if len(sp) != 7:
+        raise ValueError("not a record of the conv2d sketch")
+    slots = [None] * 23
+    for key, k in zip(("n", "y", "x", "f", "ry", "rx", "rc"), sp):
+        for level, j in enumerate(CONV2D_SLOTS[key][1:]):
+            slots[j] = ("SP", k, level)
+    if pr:
+        slots[22] = ("PR", pr[0])
+    return SketchSlots(rec, slots)
