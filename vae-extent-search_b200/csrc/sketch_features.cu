@@ -17,19 +17,23 @@
 //   buffer: bytes, ndim, shape[4], row (-1: never stored)
 //   instruction: op, a, b, c                            FOR(loop, scalar, kind) FOR_END THREAD(loop, scalar, which) THREAD_END
 //                                                       PRAGMA(-, scalar) PRAGMA_END REALIZE_END(buffer, aux) STORE(store)
+//   instruction STORE: b = 1 for the last store of its buffer (the one whose features the buffer keeps)
 //   store: buffer, n_access, ops[16], then per access: buffer, acc_type, n_tuples, ndim, expression offset[n_tuples * ndim],
-//          then n_loads, expression offset[n_loads] (the indices of every BufferLoad: their arithmetic counts as int ops)
+//          n_walk (-1: none), walk entry[n_walk] -- the terms of all dimensions sorted by loop, innermost first, constants
+//          last: loop id + 1 (0: constant) | dimension << 8 | term << 12; only for one index tuple all in term form;
+//          then n_loads, (position in the store's expression list or -1, expression offset)[n_loads]: the indices of
+//          every BufferLoad -- their arithmetic counts as int ops
 //   expression: n_tokens, ADD mask, MUL mask, DIV|MOD mask (a bit per token), n_terms (-1: none), token[n], term[n_terms][4];
 //               term = kind | loop << 4, coefficient scalar (-1: none), c1, c2 -- the stack-free form of a sum of
 //               v * c, (v // c1) * c, (v % c1) * c, ((v // c1) % c2) * c and constants;  token = kind | arg << 4: VAR(loop) CONST(scalar) ADD MUL(which operand is a leaf) DIV MOD
 //
-// Each warp stages its 32 rows in shared memory and writes them out as contiguous 656-byte rows (coalesced).
+// One block of 256 threads per SM, a thread per candidate.  Each warp stages its rows through a 32 x 33-word tile of shared
+// memory and writes them out in 128-byte segments (fp32 rows, or fp16 rows for the row encoder's VAEX_F_FEATS_F16 input).
 #include <algorithm>
 #include <cstdint>
 #include <mutex>
 #include <type_traits>
 #include <vector>
-#include <cstdlib>
 
 #include <cuda_fp16.h>
 
